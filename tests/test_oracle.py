@@ -1,0 +1,127 @@
+"""The oracle (oracle/vitomr_oracle.py) against the reference's own outputs and known answers.
+
+Golden entries were produced by the unmodified reference (tests/golden/make_golden.py).
+CPU only; this is the pin that lets the GPU tests trust the oracle."""
+import torch
+
+from oracle import vitomr_oracle as O
+
+TOL = dict(atol=2e-5, rtol=1e-4)
+
+
+def sub(sd, prefix):
+    return {k[len(prefix):]: v for k, v in sd.items() if k.startswith(prefix)}
+
+
+def test_encoder_batchify_and_forward(golden):
+    g = golden["encoder"]
+    cfg = dict(g["cfg"], stacks=["encoder_blocks"])
+    emb, mask = O.encoder_batchify(g["imgs"], g["sd"], 4, 6, 10)
+    assert torch.equal(mask, g["mask"])
+    assert torch.allclose(emb, g["batchify"], **TOL)
+    y, _ = O.encoder_forward(g["imgs"], g["sd"], cfg, fast_path_pad_fill=True)
+    assert torch.allclose(y, g["out_eval"], **TOL)  # includes pad rows == final-norm bias
+    y_t, _ = O.encoder_forward(g["imgs"], g["sd"], cfg, fast_path_pad_fill=False)
+    valid = ~g["mask"]
+    assert torch.allclose(y_t[valid], g["out_train"][valid], **TOL)
+    y1, _ = O.encoder_forward([g["imgs"][1]], g["sd"], cfg)
+    assert torch.allclose(y1, g["out_single"], **TOL)
+
+
+def test_finetune_encoder_with_interpolated_pe(golden):
+    g = golden["finetune_encoder"]
+    assert torch.allclose(O.interpolate_pe(g["sd"]["pos_embedding"], 6, 3), g["pe_interp_6x3"], atol=1e-6)
+    cfg = dict(patch_size=4, pe_max_height=4, pe_max_width=6, num_heads=2, interpolate=True,
+               stacks=["frozen_blocks", "fine_tune_blocks"])
+    emb, mask = O.encoder_batchify(g["imgs"], g["sd"], 4, 4, 6, interpolate=True)
+    assert torch.equal(mask, g["mask"])
+    assert torch.allclose(emb, g["batchify"], **TOL)
+    y, _ = O.encoder_forward(g["imgs"], g["sd"], cfg)
+    assert torch.allclose(y, g["out_eval"], **TOL)
+
+
+def test_decoder_paths(golden):
+    g = golden["decoder"]
+    sd, H = g["sd"], g["cfg"]["num_heads"]
+    tf = O.decoder_forward(g["tokens"], g["memory"], sd, H, g["lmx_mask"], g["mem_mask"])
+    assert torch.allclose(tf, g["tf_logits"], **TOL)
+    gen = O.decoder_forward(g["tokens"], g["memory"], sd, H, None, g["mem_mask"])
+    assert torch.allclose(gen, g["gen_logits"], **TOL)
+    st = O.prepare_caches(g["memory"], sd, H)
+    assert torch.allclose(st.k_cross[0], g["k_cross0"], **TOL)
+    assert torch.allclose(st.v_cross[0], g["v_cross0"], **TOL)
+    steps = [O.cached_generate(g["tokens"][:, t:t + 1], t, st, sd, H, g["mem_mask"]).squeeze(1)
+             for t in range(g["tokens"].shape[1])]
+    assert torch.allclose(torch.stack(steps, 1), g["cached_logits"], **TOL)
+    assert torch.allclose(st.k_self[2], g["k_self2"], **TOL)
+    try:
+        O.cached_generate(g["tokens"][:, :1], 24, st, sd, H)
+    except RuntimeError:
+        pass
+    else:
+        raise AssertionError("time_step >= max_lmx_seq_len must raise (models.py:519-520)")
+
+
+def test_vitomr_greedy_and_teacher_forcing(golden):
+    g = golden["vitomr"]
+    sd = g["sd"]
+    enc_cfg = dict(patch_size=4, pe_max_height=6, pe_max_width=10, num_heads=4, interpolate=True,
+                   stacks=["fine_tune_blocks"])
+    lat, lat_mask = O.encoder_forward(g["imgs"], sub(sd, "encoder."), enc_cfg)
+    lat = O.transition_head(lat, sd)
+    assert torch.equal(lat_mask, g["latent_mask"])
+    assert torch.allclose(lat, g["latent"], **TOL)
+    seqs, logp, m, _ = O.cached_greedy_generate(lat, sub(sd, "decoder."), 4, lat_mask, max_len=20)
+    assert torch.equal(seqs, g["seqs"])          # token-exact, incl. the time_step=t quirk
+    assert torch.equal(m, g["seq_mask"])
+    assert torch.allclose(logp, g["log_probs"], **TOL)
+    # a fixture that exercises both early-stopping rows and never-stopping rows
+    assert bool((g["seqs"] == 2).any()) and not bool((g["seqs"] == 2).any(dim=1).all())
+    cfg = dict(encoder=enc_cfg, decoder_heads=4, pad_idx=1)
+    pred, tgt = O.teacher_forced_forward(list(zip(g["imgs"], g["lmx"])), sd, cfg)
+    assert torch.equal(tgt, g["tf_target"])
+    assert torch.allclose(pred, g["tf_pred"], **TOL)
+    assert torch.allclose(O.ce_loss(pred, tgt, 1), g["tf_loss"], **TOL)
+
+
+def test_mae_forward_and_loss(golden):
+    g = golden["mae"]
+    cfg = dict(mask_ratio=0.75, patch_size=4, pe_max_height=6, pe_max_width=10, encoder_heads=4, decoder_heads=2)
+    pred, lmask, target = O.mae_forward(list(zip(g["imgs"], g["targets"])), g["sd"], cfg, g["noises"])
+    assert torch.equal(lmask, g["loss_mask"])
+    assert torch.equal(target, g["target"])
+    valid = lmask  # masked & non-pad rows are what the loss reads
+    assert torch.allclose(pred[valid], g["pred"][valid], **TOL)
+    assert torch.allclose(O.mae_loss(pred, lmask, target), g["loss"], **TOL)
+
+
+def test_mae_loss_known_answer():
+    """Reference tests/test_mae.py:169-180."""
+    target = torch.cat([
+        torch.tensor([[1, 1, 1], [2, 2, 2]], dtype=torch.float).unsqueeze(-1).repeat(1, 1, 6),
+        torch.tensor([[2, 2, 2], [3, 3, 3]], dtype=torch.float).unsqueeze(-1).repeat(1, 1, 6)], dim=-1)
+    pred = torch.tensor([[2, 2, 2], [3, 3, 4]], dtype=torch.float).unsqueeze(-1).repeat(1, 1, 12)
+    loss_mask = torch.tensor([[1, 0, 0], [1, 0, 1]], dtype=torch.float)
+    assert O.mae_loss(pred, loss_mask, target) == 10.583329200744629
+
+
+def test_batchify_known_answers():
+    """Reference tests/test_vitomr.py:27-49 (identity projection, all-ones PE, incl. interpolated PE)."""
+    sd = {"pos_embedding": torch.ones(50, 50, 4)}
+    x = [torch.ones(1, 4, 4), torch.ones(1, 4, 8)]
+    emb, mask = O.encoder_batchify(x, sd, 2, 60, 200, interpolate=True, identity_projection=True)
+    first = torch.cat([torch.ones(1, 4, 4) + 1, torch.zeros(1, 4, 4)], dim=1)
+    assert torch.equal(emb, torch.cat([first, torch.ones(1, 8, 4) + 1]))
+    assert torch.equal(mask, torch.cat([(torch.arange(8) >= 4)[None], (torch.arange(8) >= 8)[None]]))
+    sd = {"pos_embedding": torch.ones(60, 200, 4)}
+    emb, _ = O.encoder_batchify([torch.ones(1, 10, 600)], sd, 2, 60, 200, interpolate=True, identity_projection=True)
+    assert torch.equal(emb, torch.ones(1, 1500, 4) + 1)
+
+
+def test_split_lmx_known_answer():
+    """Reference tests/test_vitomr.py:151-172."""
+    seqs = [torch.tensor([0, 2, 3, 226]), torch.tensor([0, 2, 2, 3, 4, 226])]
+    inp, tgt, mask = O.batchify_and_split_lmx_seqs(seqs, 1)
+    assert torch.equal(inp, torch.tensor([[0, 2, 3, 226, 1], [0, 2, 2, 3, 4]]))
+    assert torch.equal(tgt, torch.tensor([[2, 3, 226, 1, 1], [2, 2, 3, 4, 226]]))
+    assert torch.equal(mask, torch.tensor([[False, False, False, False, True], [False] * 5]))

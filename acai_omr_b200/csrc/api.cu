@@ -1,0 +1,72 @@
+// Library-level entry points: version, per-thread error string, device check, and the
+// acai_linear_fwd dispatcher (tcgen05 tensor-core GEMM when the problem qualifies, SIMT otherwise).
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace acai {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int num_sms() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    else
+      return 148;
+  }
+  return cached;
+}
+
+int linear_simt(const void* a, int a_dt, int64_t lda, const void* w, int w_dt, int64_t ldw, const float* bias,
+                const void* res, int res_dt, int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K,
+                int act, cudaStream_t st);
+// returns ACAI_ERR_UNSUPPORTED when the problem does not qualify for the tensor-core path
+int linear_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res,
+                   int res_dt, int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K, int act,
+                   cudaStream_t st);
+
+}  // namespace acai
+
+using namespace acai;
+
+extern "C" int acai_version(void) { return 100; }
+extern "C" const char* acai_last_error(void) { return g_err; }
+
+extern "C" int acai_device_ok(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { set_error("no CUDA device"); cudaGetLastError(); return 0; }
+  int dev = 0, major = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  if (major != 10) { set_error("device compute capability %d.x is not sm_100", major); return 0; }
+  return 1;
+}
+
+extern "C" int acai_linear_fwd(const void* a, int32_t a_dtype, int64_t lda, const void* w, int32_t w_dtype,
+                               int64_t ldw, const float* bias, const void* residual, int32_t res_dtype, int64_t ldr,
+                               void* out, int32_t out_dtype, int64_t ldo, int32_t M, int32_t N, int32_t K,
+                               int32_t act, void* stream) {
+  ACAI_CHECK_ARG(a && w && out, "acai_linear_fwd: null pointer");
+  ACAI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && lda >= K && ldw >= K && ldo >= N, "acai_linear_fwd: bad sizes M=%d N=%d K=%d", M, N, K);
+  ACAI_CHECK_ARG(dtype_valid(a_dtype) && dtype_valid(w_dtype) && dtype_valid(out_dtype) &&
+                 (!residual || (dtype_valid(res_dtype) && ldr >= N)), "acai_linear_fwd: bad dtype/ldr");
+  ACAI_CHECK_ARG(act == ACAI_ACT_NONE || act == ACAI_ACT_GELU, "acai_linear_fwd: bad activation %d", act);
+  if (M == 0) return ACAI_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (a_dtype == ACAI_BF16 && w_dtype == ACAI_BF16) {
+    int rc = linear_tcgen05(a, lda, w, ldw, bias, residual, res_dtype, ldr, out, out_dtype, ldo, M, N, K, act, st);
+    if (rc != ACAI_ERR_UNSUPPORTED) return rc;
+  }
+  return linear_simt(a, a_dtype, lda, w, w_dtype, ldw, bias, residual, res_dtype, ldr, out, out_dtype, ldo, M, N, K, act, st);
+}

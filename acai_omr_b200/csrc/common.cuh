@@ -1,0 +1,101 @@
+// Shared helpers for libacai_b200.so (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/acai_b200.h"
+
+namespace acai {
+
+void set_error(const char* fmt, ...);
+
+#define ACAI_CHECK_ARG(cond, ...)        \
+  do {                                   \
+    if (!(cond)) {                       \
+      ::acai::set_error(__VA_ARGS__);    \
+      return ACAI_ERR_INVALID;           \
+    }                                    \
+  } while (0)
+
+#define ACAI_CUDA(call)                                                                 \
+  do {                                                                                  \
+    cudaError_t e__ = (call);                                                           \
+    if (e__ != cudaSuccess) {                                                           \
+      ::acai::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return ACAI_ERR_CUDA;                                                             \
+    }                                                                                   \
+  } while (0)
+
+inline int launch_status(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("launch of %s failed: %s", what, cudaGetErrorString(e));
+    return ACAI_ERR_CUDA;
+  }
+  return ACAI_OK;
+}
+
+inline size_t dtype_size(int dt) { return dt == ACAI_BF16 ? 2 : 4; }
+inline bool dtype_valid(int dt) { return dt == ACAI_F32 || dt == ACAI_BF16; }
+
+// ---- runtime-typed element access for the generic (any-shape) kernels ----
+__device__ __forceinline__ float ld_as_float(const void* p, int64_t i, int dt) {
+  return dt == ACAI_BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i])
+                         : reinterpret_cast<const float*>(p)[i];
+}
+__device__ __forceinline__ void st_from_float(void* p, int64_t i, int dt, float v) {
+  if (dt == ACAI_BF16) reinterpret_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(v);
+  else reinterpret_cast<float*>(p)[i] = v;
+}
+
+__device__ __forceinline__ float gelu_erf(float x) {
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024 (multiple of 32); `red` is >= 32 floats of smem.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();  // protect `red` from a previous use
+  if (lane == 0) red[wid] = v;
+  __syncthreads();
+  float r = (lane < nw) ? red[lane] : 0.0f;
+  return warp_sum(r);
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_max(v);
+  __syncthreads();
+  if (lane == 0) red[wid] = v;
+  __syncthreads();
+  float r = (lane < nw) ? red[lane] : -INFINITY;
+  return warp_max(r);
+}
+
+// Index of the sequence that packed row `row` belongs to: largest b with cu[b] <= row.
+__device__ __forceinline__ int find_sequence(const int32_t* __restrict__ cu, int batch, int row) {
+  int lo = 0, hi = batch;  // invariant: cu[lo] <= row < cu[hi]
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (__ldg(cu + mid) <= row) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+int num_sms();
+
+}  // namespace acai

@@ -1,0 +1,173 @@
+// Row-wise memory-bound kernels: LayerNorm(+residual), token embedding, greedy epilogue,
+// packed <-> padded conversion, KV append.  All HBM-bound; one CTA (or warp) per row,
+// coalesced loads along the feature dimension.
+#include "common.cuh"
+
+namespace acai {
+
+// y = LN(x + residual) * gamma + beta ; biased variance, computed as mean((v-mu)^2) (two-pass, as torch).
+// The row is staged in dynamic shared memory as fp32 so x/residual are read exactly once.
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const void* __restrict__ x, int x_dt, const void* __restrict__ res, int res_dt,
+                 const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                 void* __restrict__ out, int out_dt, void* __restrict__ out2, int out2_dt, int cols) {
+  extern __shared__ float rowbuf[];
+  __shared__ float red[32];
+  const int64_t base = (int64_t)blockIdx.x * cols;
+  float s = 0.0f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    float v = ld_as_float(x, base + c, x_dt);
+    if (res) v += ld_as_float(res, base + c, res_dt);
+    rowbuf[c] = v;
+    s += v;
+  }
+  const float mu = block_sum(s, red) / (float)cols;
+  float q = 0.0f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) { float d = rowbuf[c] - mu; q += d * d; }
+  const float rstd = rsqrtf(block_sum(q, red) / (float)cols + eps);
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    float y = (rowbuf[c] - mu) * rstd * __ldg(gamma + c) + __ldg(beta + c);
+    st_from_float(out, base + c, out_dt, y);
+    if (out2) st_from_float(out2, base + c, out2_dt, y);
+  }
+}
+
+__global__ void embed_tokens_kernel(const int64_t* __restrict__ ids, const float* __restrict__ table,
+                                    const float* __restrict__ pos, const int32_t* __restrict__ pos_ids,
+                                    int pos_offset, int period, void* __restrict__ out, int out_dt, int dim) {
+  const int r = blockIdx.x;
+  const int64_t tok = ids[r];
+  const int p = pos_ids ? pos_ids[r] : pos_offset + (period > 0 ? r % period : 0);
+  for (int c = threadIdx.x; c < dim; c += blockDim.x)
+    st_from_float(out, (int64_t)r * dim + c, out_dt, __ldg(table + tok * dim + c) + __ldg(pos + (int64_t)p * dim + c));
+}
+
+// One warp per row: argmax (lowest index among equal maxima, as torch.argmax) and
+// log_softmax(row)[argmax] = max - (max + log(sum exp(x - max))) = -log(sum exp(x - max)).
+__global__ void argmax_logprob_kernel(const void* __restrict__ logits, int dt, int64_t ld, int rows, int vocab,
+                                      int64_t* __restrict__ next_token, float* __restrict__ chosen) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  float best = -INFINITY; int idx = 0x7fffffff;
+  for (int c = lane; c < vocab; c += 32) {
+    float v = ld_as_float(logits, (int64_t)row * ld + c, dt);
+    if (v > best || (v == best && c < idx)) { best = v; idx = c; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float ob = __shfl_xor_sync(0xffffffffu, best, o); int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+    if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+  }
+  float s = 0.0f;
+  for (int c = lane; c < vocab; c += 32) s += expf(ld_as_float(logits, (int64_t)row * ld + c, dt) - best);
+  s = warp_sum(s);
+  if (lane == 0) { next_token[row] = idx; chosen[row] = -logf(s); }
+}
+
+__global__ void unpack_padded_kernel(const void* __restrict__ packed, int in_dt, const int32_t* __restrict__ cu,
+                                     int max_len, int dim, const float* __restrict__ fill,
+                                     void* __restrict__ out, int out_dt) {
+  const int b = blockIdx.y, t = blockIdx.x;
+  const int start = cu[b], len = cu[b + 1] - start;
+  const int64_t o = ((int64_t)b * max_len + t) * dim;
+  if (t < len) {
+    const int64_t i = (int64_t)(start + t) * dim;
+    for (int c = threadIdx.x; c < dim; c += blockDim.x) st_from_float(out, o + c, out_dt, ld_as_float(packed, i + c, in_dt));
+  } else {
+    for (int c = threadIdx.x; c < dim; c += blockDim.x) st_from_float(out, o + c, out_dt, fill ? __ldg(fill + c) : 0.0f);
+  }
+}
+
+__global__ void pack_padded_kernel(const void* __restrict__ padded, int in_dt, const int32_t* __restrict__ cu,
+                                   int max_len, int dim, void* __restrict__ out, int out_dt) {
+  const int b = blockIdx.y, t = blockIdx.x;
+  const int start = cu[b], len = cu[b + 1] - start;
+  if (t >= len) return;
+  const int64_t i = ((int64_t)b * max_len + t) * dim, o = (int64_t)(start + t) * dim;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) st_from_float(out, o + c, out_dt, ld_as_float(padded, i + c, in_dt));
+}
+
+__global__ void kv_append_kernel(const void* __restrict__ k_new, const void* __restrict__ v_new, int src_dt,
+                                 int64_t sbs, int64_t shs, int64_t sts, void* __restrict__ kc, void* __restrict__ vc,
+                                 int c_dt, int64_t bs, int64_t hs, int64_t ts, int heads, int d, int pos, int n_new) {
+  const int b = blockIdx.x, j = blockIdx.y;
+  for (int i = threadIdx.x; i < heads * d; i += blockDim.x) {
+    const int h = i / d, e = i - h * d;
+    const int64_t src = (int64_t)b * sbs + (int64_t)h * shs + (int64_t)j * sts + e;
+    const int64_t dst = (int64_t)b * bs + (int64_t)h * hs + (int64_t)(pos + j) * ts + e;
+    st_from_float(kc, dst, c_dt, ld_as_float(k_new, src, src_dt));
+    st_from_float(vc, dst, c_dt, ld_as_float(v_new, src, src_dt));
+  }
+}
+
+}  // namespace acai
+
+using namespace acai;
+
+extern "C" int acai_layernorm_fwd(const void* x, int32_t x_dtype, const void* residual, int32_t res_dtype,
+                                  const float* gamma, const float* beta, float eps, void* out, int32_t out_dtype,
+                                  void* out2, int32_t out2_dtype, int32_t rows, int32_t cols, void* stream) {
+  ACAI_CHECK_ARG(x && gamma && beta && out, "acai_layernorm_fwd: null pointer");
+  ACAI_CHECK_ARG(rows >= 0 && cols > 0 && cols <= 12288, "acai_layernorm_fwd: rows=%d cols=%d out of range", rows, cols);
+  ACAI_CHECK_ARG(dtype_valid(x_dtype) && dtype_valid(out_dtype) && (!residual || dtype_valid(res_dtype)) &&
+                 (!out2 || dtype_valid(out2_dtype)), "acai_layernorm_fwd: bad dtype");
+  if (rows == 0) return ACAI_OK;
+  const int threads = cols >= 1024 ? 256 : (cols >= 256 ? 128 : 64);
+  layernorm_kernel<<<rows, threads, cols * sizeof(float), (cudaStream_t)stream>>>(
+      x, x_dtype, residual, res_dtype, gamma, beta, eps, out, out_dtype, out2, out2_dtype, cols);
+  return launch_status("layernorm");
+}
+
+extern "C" int acai_embed_tokens(const int64_t* ids, int32_t rows, const float* table, const float* pos,
+                                 const int32_t* pos_ids, int32_t pos_offset, int32_t period, void* out,
+                                 int32_t out_dtype, int32_t dim, void* stream) {
+  ACAI_CHECK_ARG(ids && table && pos && out && dim > 0 && rows >= 0, "acai_embed_tokens: bad argument");
+  ACAI_CHECK_ARG(dtype_valid(out_dtype), "acai_embed_tokens: bad dtype");
+  if (rows == 0) return ACAI_OK;
+  embed_tokens_kernel<<<rows, dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(ids, table, pos, pos_ids, pos_offset,
+                                                                                period, out, out_dtype, dim);
+  return launch_status("embed_tokens");
+}
+
+extern "C" int acai_argmax_logprob(const void* logits, int32_t dtype, int64_t ld, int32_t rows, int32_t vocab,
+                                   int64_t* next_token, float* chosen_logprob, void* stream) {
+  ACAI_CHECK_ARG(logits && next_token && chosen_logprob && vocab > 0 && rows >= 0 && dtype_valid(dtype),
+                 "acai_argmax_logprob: bad argument");
+  if (rows == 0) return ACAI_OK;
+  argmax_logprob_kernel<<<(rows + 3) / 4, 128, 0, (cudaStream_t)stream>>>(logits, dtype, ld, rows, vocab, next_token,
+                                                                          chosen_logprob);
+  return launch_status("argmax_logprob");
+}
+
+extern "C" int acai_unpack_padded(const void* packed, int32_t in_dtype, const int32_t* cu_seqlens, int32_t batch,
+                                  int32_t max_len, int32_t dim, const float* fill, void* out, int32_t out_dtype,
+                                  void* stream) {
+  ACAI_CHECK_ARG(packed && cu_seqlens && out && batch > 0 && max_len > 0 && dim > 0, "acai_unpack_padded: bad argument");
+  ACAI_CHECK_ARG(dtype_valid(in_dtype) && dtype_valid(out_dtype) && batch <= 65535, "acai_unpack_padded: bad dtype/batch");
+  unpack_padded_kernel<<<dim3(max_len, batch), dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(
+      packed, in_dtype, cu_seqlens, max_len, dim, fill, out, out_dtype);
+  return launch_status("unpack_padded");
+}
+
+extern "C" int acai_pack_padded(const void* padded, int32_t in_dtype, const int32_t* cu_seqlens, int32_t batch,
+                                int32_t max_len, int32_t dim, void* out, int32_t out_dtype, void* stream) {
+  ACAI_CHECK_ARG(padded && cu_seqlens && out && batch > 0 && max_len > 0 && dim > 0, "acai_pack_padded: bad argument");
+  ACAI_CHECK_ARG(dtype_valid(in_dtype) && dtype_valid(out_dtype) && batch <= 65535, "acai_pack_padded: bad dtype/batch");
+  pack_padded_kernel<<<dim3(max_len, batch), dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(
+      padded, in_dtype, cu_seqlens, max_len, dim, out, out_dtype);
+  return launch_status("pack_padded");
+}
+
+extern "C" int acai_kv_append(const void* k_new, const void* v_new, int32_t src_dtype, int64_t src_batch_stride,
+                              int64_t src_head_stride, int64_t src_tok_stride, int32_t n_new,
+                              void* k_cache, void* v_cache, int32_t cache_dtype, int64_t kv_batch_stride,
+                              int64_t kv_head_stride, int64_t kv_tok_stride, int32_t batch, int32_t heads,
+                              int32_t head_dim, int32_t pos, void* stream) {
+  ACAI_CHECK_ARG(k_new && v_new && k_cache && v_cache && batch > 0 && heads > 0 && head_dim > 0 && pos >= 0 && n_new > 0,
+                 "acai_kv_append: bad argument");
+  ACAI_CHECK_ARG(dtype_valid(src_dtype) && dtype_valid(cache_dtype) && n_new <= 65535, "acai_kv_append: bad dtype");
+  kv_append_kernel<<<dim3(batch, n_new), 256, 0, (cudaStream_t)stream>>>(
+      k_new, v_new, src_dtype, src_batch_stride, src_head_stride, src_tok_stride, k_cache, v_cache, cache_dtype,
+      kv_batch_stride, kv_head_stride, kv_tok_stride, heads, head_dim, pos, n_new);
+  return launch_status("kv_append");
+}

@@ -1,0 +1,312 @@
+"""Parameter shells + packed (cu_seqlens) transformer blocks over the sm_100a kernels.
+
+The shells keep torch's parameter names (`self_attn.in_proj_weight`, `linear1.weight`,
+`norm1.bias`, `layers.N`, `norm` ...) so reference checkpoints load unchanged, but
+no torch compute module is ever called: every forward below goes through `acai_omr_b200.ops`.
+
+Precision policy (mirrors the reference's use of autocast, vitomr_inference.py:80-84):
+  * inside `torch.autocast("cuda", dtype=torch.bfloat16)`  -> bf16 operands / fp32 accumulate,
+    weights cached as bf16 copies, LayerNorm statistics in fp32;
+  * otherwise -> fp32 end to end (the token-exact mode).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+from torch import nn
+
+from . import ops
+
+
+def compute_dtype() -> torch.dtype:
+    if torch.is_autocast_enabled("cuda") and torch.get_autocast_dtype("cuda") == torch.bfloat16:
+        return torch.bfloat16
+    return torch.float32
+
+
+class _WeightCache:
+    """bf16 copies of fp32 master parameters, refreshed when the parameter is updated in place."""
+
+    def __init__(self):
+        self._store = {}
+
+    def get(self, p: torch.Tensor, dtype: torch.dtype, rows=None):
+        if p is None:
+            return None
+        if p.dtype == dtype and rows is None:
+            return p.detach()
+        key = (id(p), dtype, rows)
+        hit = self._store.get(key)
+        ver = (p._version, p.data_ptr())
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        src = p.detach() if rows is None else p.detach()[rows[0]:rows[1]]
+        t = src.to(dtype).contiguous()
+        self._store[key] = (ver, t)
+        return t
+
+    def clear(self):
+        self._store.clear()
+
+
+WEIGHTS = _WeightCache()
+
+
+def w_(p, dtype, rows=None):
+    """Parameter `p` (optionally a row slice) in the GEMM operand dtype."""
+    return WEIGHTS.get(p, dtype, rows)
+
+
+class Linear(nn.Linear):
+    """nn.Linear parameters (same init); forward = acai_linear_fwd."""
+
+    def forward(self, x, act=ops.ACT_NONE, residual=None, out_dtype=None):
+        dt = compute_dtype()
+        if x.dtype != dt:
+            x = x.to(dt)
+        return ops.linear(x, w_(self.weight, dt), self.bias, act=act, residual=residual, out_dtype=out_dtype or dt)
+
+
+class LayerNorm(nn.LayerNorm):
+    """nn.LayerNorm parameters; forward = acai_layernorm_fwd (optionally fused residual add)."""
+
+    def forward(self, x, residual=None, out_dtype=None, out2_dtype=None):
+        return ops.layernorm(x, self.weight, self.bias, self.eps, residual=residual,
+                             out_dtype=out_dtype or x.dtype, out2_dtype=out2_dtype)
+
+
+class MultiheadAttention(nn.Module):
+    """Parameter layout and init of nn.MultiheadAttention(batch_first=True, bias=True):
+    `in_proj_weight` [3D, D] = [Wq; Wk; Wv], `in_proj_bias` [3D], `out_proj.{weight,bias}`."""
+
+    def __init__(self, embed_dim, num_heads, dropout=0.0, batch_first=True, bias=True, device=None, dtype=None):
+        super().__init__()
+        if embed_dim % num_heads != 0:
+            raise AssertionError("embed_dim must be divisible by num_heads")
+        if not (batch_first and bias):
+            raise ValueError("only batch_first=True, bias=True are supported (what the reference uses)")
+        kw = dict(device=device, dtype=dtype)
+        self.embed_dim, self.num_heads, self.dropout, self.batch_first = embed_dim, num_heads, dropout, batch_first
+        self.head_dim = embed_dim // num_heads
+        self.in_proj_weight = nn.Parameter(torch.empty(3 * embed_dim, embed_dim, **kw))
+        self.in_proj_bias = nn.Parameter(torch.empty(3 * embed_dim, **kw))
+        self.out_proj = Linear(embed_dim, embed_dim, bias=True, **kw)
+        nn.init.xavier_uniform_(self.in_proj_weight)
+        nn.init.constant_(self.in_proj_bias, 0.0)
+        nn.init.constant_(self.out_proj.bias, 0.0)
+
+    # ---- packed helpers -------------------------------------------------------------------
+    def self_attention_packed(self, x, cu, max_len, causal, residual):
+        """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D]."""
+        dt, D = x.dtype, self.embed_dim
+        qkv = ops.linear(x, w_(self.in_proj_weight, dt), self.in_proj_bias, out_dtype=dt)
+        a = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], cu, cu, max_len, self.num_heads,
+                            self.head_dim, causal=causal, out_dtype=dt)
+        return ops.linear(a, w_(self.out_proj.weight, dt), self.out_proj.bias, residual=residual, out_dtype=dt)
+
+    def project_memory_packed(self, mem):
+        """[K | V] = mem . W_kv^T + b_kv  (kv_caching.py:241-245) over packed memory rows."""
+        dt, D = mem.dtype, self.embed_dim
+        return ops.linear(mem, w_(self.in_proj_weight, dt, rows=(D, 3 * D)), self.in_proj_bias[D:], out_dtype=dt)
+
+    def cross_attention_packed(self, x, kv, cu_q, cu_k, max_q, residual):
+        dt, D = x.dtype, self.embed_dim
+        q = ops.linear(x, w_(self.in_proj_weight, dt, rows=(0, D)), self.in_proj_bias[:D], out_dtype=dt)
+        a = ops.attn_varlen(q, kv[:, :D], kv[:, D:], cu_q, cu_k, max_q, self.num_heads, self.head_dim,
+                            causal=False, out_dtype=dt)
+        return ops.linear(a, w_(self.out_proj.weight, dt), self.out_proj.bias, residual=residual, out_dtype=dt)
+
+
+class Packed:
+    """Ragged batch as packed rows: `cu` int32 device offsets, `lens` host list, `max_len`."""
+
+    def __init__(self, lens, device):
+        self.lens = [int(v) for v in lens]
+        self.batch = len(self.lens)
+        self.total = sum(self.lens)
+        self.max_len = max(self.lens) if self.lens else 0
+        off = [0]
+        for v in self.lens:
+            off.append(off[-1] + v)
+        self.cu = torch.tensor(off, dtype=torch.int32).to(device, non_blocking=True)
+
+    def mask(self, device, max_len=None):
+        """True = padding, (B, L_max)  (create_attention_mask, models.py:70-73)."""
+        L = max_len or self.max_len
+        m = torch.arange(L)[None, :] >= torch.tensor(self.lens)[:, None]
+        m = m.to(device, non_blocking=True)
+        m._acai_lens = self.lens  # lets downstream modules re-pack without a device sync
+        return m
+
+
+def lens_from_mask(mask, batch, length):
+    """Host lengths from a (B, L) True=padding mask.  Uses the lengths attached by `Packed.mask`
+    when present; otherwise reads the mask back (one sync) and requires suffix-only padding."""
+    if mask is None:
+        return [length] * batch
+    lens = getattr(mask, "_acai_lens", None)
+    if lens is not None and len(lens) == batch and mask.shape[1] == length:
+        return list(lens)
+    m = mask.bool()
+    lens_t = (~m).sum(dim=1)
+    ok = (m == (torch.arange(length, device=m.device)[None, :] >= lens_t[:, None])).all()
+    lens = lens_t.tolist()
+    if not bool(ok):
+        raise ValueError("acai_omr_b200 packs ragged batches: padding masks must mark a suffix of each row")
+    return lens
+
+
+class TransformerEncoderLayer(nn.Module):
+    """Post-norm encoder layer with nn.TransformerEncoderLayer's parameter names (models.py:31)."""
+
+    def __init__(self, d_model, nhead, dim_feedforward=2048, dropout=0.1, activation="gelu", layer_norm_eps=1e-5,
+                 batch_first=True, norm_first=False, bias=True, device=None, dtype=None):
+        super().__init__()
+        if activation != "gelu" and activation is not torch.nn.functional.gelu:
+            raise ValueError("only the exact-erf GELU activation is implemented")
+        if norm_first:
+            raise ValueError("only post-norm (norm_first=False) is implemented")
+        kw = dict(device=device, dtype=dtype)
+        self.self_attn = MultiheadAttention(d_model, nhead, dropout=dropout, **kw)
+        self.linear1 = Linear(d_model, dim_feedforward, **kw)
+        self.linear2 = Linear(dim_feedforward, d_model, **kw)
+        self.norm1 = LayerNorm(d_model, eps=layer_norm_eps, **kw)
+        self.norm2 = LayerNorm(d_model, eps=layer_norm_eps, **kw)
+        self.dropout_p = dropout
+
+    def forward_packed(self, x, pk: Packed):
+        dt = x.dtype
+        y = self.self_attn.self_attention_packed(x, pk.cu, pk.max_len, False, residual=x)
+        x = self.norm1(y, out_dtype=dt)
+        h = ops.linear(x, w_(self.linear1.weight, dt), self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+        y = ops.linear(h, w_(self.linear2.weight, dt), self.linear2.bias, residual=x, out_dtype=dt)
+        return self.norm2(y, out_dtype=dt)
+
+
+def _check_dropout(module, p):
+    if module.training and p > 0.0:
+        raise NotImplementedError(
+            "acai_omr_b200 implements the deterministic path (eval mode, or train mode with dropout 0); "
+            f"got training=True with dropout={p}")
+
+
+class TransformerEncoder(nn.Module):
+    """nn.TransformerEncoder-shaped container: `.layers`, `.norm`, `.num_layers` (models.py:30-34)."""
+
+    def __init__(self, make_layer, num_layers, norm=None):
+        super().__init__()
+        self.layers = nn.ModuleList([make_layer() for _ in range(num_layers)])
+        self.num_layers = num_layers
+        self.norm = norm
+        # nn.TransformerEncoder deep-copies one prototype layer: all layers start identical
+        for layer in self.layers[1:]:
+            layer.load_state_dict(self.layers[0].state_dict())
+
+    def forward_packed(self, x, pk: Packed, final_dtype=None):
+        for layer in self.layers:
+            _check_dropout(self, layer.dropout_p)
+            x = layer.forward_packed(x, pk)
+        if self.norm is not None:
+            x = self.norm(x, out_dtype=final_dtype or x.dtype)
+        return x
+
+    def forward(self, src, mask=None, src_key_padding_mask=None):
+        """Padded API: src (B, L, D), src_key_padding_mask (B, L) True = padding."""
+        if mask is not None:
+            raise NotImplementedError("attention masks other than key padding are not used by the reference encoder")
+        B, L, D = src.shape
+        pk = Packed(lens_from_mask(src_key_padding_mask, B, L), src.device)
+        dt = compute_dtype()
+        x = ops.pack_padded(src, pk.cu, pk.total, out_dtype=dt)
+        x = self.forward_packed(x, pk, final_dtype=torch.float32 if self.norm is not None else None)
+        fill = self.norm.bias if (self.norm is not None and not self.training) else None
+        return ops.unpack_padded(x, pk.cu, B, L, fill=fill)
+
+
+class TransformerDecoderLayer(nn.Module):
+    """Post-norm decoder layer with nn.TransformerDecoderLayer's parameter names (models.py:423)."""
+
+    def __init__(self, d_model, nhead, dim_feedforward=2048, dropout=0.1, activation="gelu", layer_norm_eps=1e-5,
+                 batch_first=True, norm_first=False, bias=True, device=None, dtype=None):
+        super().__init__()
+        if activation != "gelu" and activation is not torch.nn.functional.gelu:
+            raise ValueError("only the exact-erf GELU activation is implemented")
+        if norm_first:
+            raise ValueError("only post-norm (norm_first=False) is implemented")
+        kw = dict(device=device, dtype=dtype)
+        self.self_attn = self._make_attention(d_model, nhead, dropout, **kw)
+        self.multihead_attn = self._make_attention(d_model, nhead, dropout, **kw)
+        self.linear1 = Linear(d_model, dim_feedforward, **kw)
+        self.linear2 = Linear(dim_feedforward, d_model, **kw)
+        self.norm1 = LayerNorm(d_model, eps=layer_norm_eps, **kw)
+        self.norm2 = LayerNorm(d_model, eps=layer_norm_eps, **kw)
+        self.norm3 = LayerNorm(d_model, eps=layer_norm_eps, **kw)
+        self.dropout_p = dropout
+
+    def _make_attention(self, d_model, nhead, dropout, **kw):
+        return MultiheadAttention(d_model, nhead, dropout=dropout, **kw)
+
+    def mlp_packed(self, x):
+        dt = x.dtype
+        h = ops.linear(x, w_(self.linear1.weight, dt), self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+        y = ops.linear(h, w_(self.linear2.weight, dt), self.linear2.bias, residual=x, out_dtype=dt)
+        return self.norm3(y, out_dtype=dt)
+
+    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True):
+        dt = x.dtype
+        y = self.self_attn.self_attention_packed(x, tgt.cu, tgt.max_len, causal, residual=x)
+        x = self.norm1(y, out_dtype=dt)
+        kv = self.multihead_attn.project_memory_packed(mem)
+        y = self.multihead_attn.cross_attention_packed(x, kv, tgt.cu, mem_pk.cu, tgt.max_len, residual=x)
+        x = self.norm2(y, out_dtype=dt)
+        return self.mlp_packed(x)
+
+
+class TransformerDecoder(nn.Module):
+    """nn.TransformerDecoder-shaped container (models.py:422-426)."""
+
+    def __init__(self, make_layer, num_layers, norm=None):
+        super().__init__()
+        self.layers = nn.ModuleList([make_layer() for _ in range(num_layers)])
+        self.num_layers = num_layers
+        self.norm = norm
+        for layer in self.layers[1:]:
+            layer.load_state_dict(self.layers[0].state_dict())
+
+    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True, final_dtype=None):
+        for layer in self.layers:
+            _check_dropout(self, layer.dropout_p)
+            x = layer.forward_packed(x, tgt, mem, mem_pk, causal)
+        if self.norm is not None:
+            x = self.norm(x, out_dtype=final_dtype or x.dtype)
+        return x
+
+    def forward(self, tgt, memory, tgt_mask=None, memory_mask=None, tgt_key_padding_mask=None,
+                memory_key_padding_mask=None, tgt_is_causal=None, memory_is_causal=False):
+        """Padded API of nn.TransformerDecoder.forward.  `tgt_mask` must be the causal triu mask (or None);
+        it is not read: causality is applied inside the attention kernel."""
+        if memory_mask is not None:
+            raise NotImplementedError("memory_mask is not used by the reference")
+        B, T, D = tgt.shape
+        S = memory.shape[1]
+        tp = Packed(lens_from_mask(tgt_key_padding_mask, B, T), tgt.device)
+        mp = Packed(lens_from_mask(memory_key_padding_mask, B, S), tgt.device)
+        dt = compute_dtype()
+        x = ops.pack_padded(tgt, tp.cu, tp.total, out_dtype=dt)
+        mem = ops.pack_padded(memory, mp.cu, mp.total, out_dtype=dt)
+        x = self.forward_packed(x, tp, mem, mp, causal=tgt_mask is not None or bool(tgt_is_causal),
+                                final_dtype=torch.float32 if self.norm is not None else None)
+        return ops.unpack_padded(x, tp.cu, B, T)
+
+
+def gelu_mlp_head(x, lin_a: Linear, lin_b: Linear, out_dtype=None):
+    """Linear -> exact GELU -> Linear with the activation fused into the first GEMM's epilogue."""
+    dt = compute_dtype()
+    if x.dtype != dt:
+        x = x.to(dt)
+    h = ops.linear(x, w_(lin_a.weight, dt), lin_a.bias, act=ops.ACT_GELU, out_dtype=dt)
+    return ops.linear(h, w_(lin_b.weight, dt), lin_b.bias, out_dtype=out_dtype or dt)
+
+
+SQRT_HALF = 1.0 / math.sqrt(2.0)

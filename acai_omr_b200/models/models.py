@@ -1,0 +1,456 @@
+"""Drop-in for `acai_omr/models/models.py` (jsnchon/acai-omr @ 5819ae3) on sm_100a kernels.
+
+Same class names, constructor signatures, forward-path methods, attributes and `state_dict` keys
+as the reference; reference line numbers are cited per method.  Internally ragged
+batches are never padded: images become packed token rows + `cu_seqlens` straight out of the
+patch-embedding kernel, every layer runs on packed rows, and padding only reappears at the API
+boundary (`to_padded_tensor` semantics) because callers expect `(B, L_max, E)` + a mask.
+"""
+from __future__ import annotations
+
+import os
+import re
+
+import torch
+from torch import nn
+
+from .. import ops
+from ..config import LMX_BOS_TOKEN, LMX_EOS_TOKEN, LMX_PAD_TOKEN
+from ..layers import (LayerNorm, Linear, Packed, TransformerDecoder, TransformerDecoderLayer, TransformerEncoder,
+                      TransformerEncoderLayer, compute_dtype, gelu_mlp_head, lens_from_mask, w_)
+from .kv_caching import CachedTransformerDecoder, CachedTransformerDecoderLayer
+
+NUM_CHANNELS = 1  # models.py:11
+
+
+def _encoder_stack(hidden_dim, num_heads, mlp_dim, dropout, num_layers, final_norm):
+    return TransformerEncoder(
+        lambda: TransformerEncoderLayer(d_model=hidden_dim, nhead=num_heads, dim_feedforward=mlp_dim, dropout=dropout,
+                                        activation="gelu", batch_first=True),
+        num_layers=num_layers,
+        norm=LayerNorm(hidden_dim, eps=1e-6) if final_norm else None)
+
+
+class Encoder(nn.Module):
+    """models.py:14-96."""
+    _interpolate_pe = False
+
+    def __init__(self, patch_size, pe_max_height, pe_max_width, num_layers=12, hidden_dim=768, num_heads=12,
+                 mlp_dim=3072, transformer_dropout=0.0):
+        super().__init__()
+        self.patch_size = patch_size
+        self.pe_max_height = pe_max_height
+        self.pe_max_width = pe_max_width
+        self.hidden_dim = hidden_dim
+        self.pos_embedding = nn.Parameter(torch.zeros(self.pe_max_height, self.pe_max_width, self.hidden_dim))
+        nn.init.trunc_normal_(self.pos_embedding, std=0.1)
+        self.projection = Linear(NUM_CHANNELS * self.patch_size ** 2, self.hidden_dim)
+        self.encoder_blocks = _encoder_stack(hidden_dim, num_heads, mlp_dim, transformer_dropout, num_layers, True)
+
+    # ---- packed internals -----------------------------------------------------------------
+    def _image_list(self, x):
+        imgs = []
+        for t in x:  # a bare (1,H,W) tensor iterates as one (H,W) image (vitomr_inference.py:81)
+            if t.dim() == 2:
+                t = t.unsqueeze(0)
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                t = t.float().contiguous()
+            imgs.append(t)
+        return imgs
+
+    def _grid_check(self, h_p, w_p):
+        if not self._interpolate_pe and (h_p > self.pe_max_height or w_p > self.pe_max_width):
+            raise ValueError(f"{h_p} x {w_p} image is too large for max positional embedding grid of shape "
+                             f"{self.pe_max_height} x {self.pe_max_width}")
+
+    def embed_packed(self, x, out_dtype=None, keep=None):
+        """K1: ragged images -> (packed rows [sum L, E], Packed).  `keep`: optional (lens, patch_index) for MAE."""
+        imgs = self._image_list(x)
+        P = self.patch_size
+        lens = []
+        for t in imgs:
+            h_p, w_p = t.shape[-2] // P, t.shape[-1] // P
+            self._grid_check(h_p, w_p)
+            lens.append(h_p * w_p)
+        dev = self.pos_embedding.device
+        patch_index = None
+        if keep is not None:
+            lens, patch_index = keep
+        pk = Packed(lens, dev)
+        descs = ops.make_image_descs(imgs, P, dev)
+        out = ops.patch_embed(imgs, descs, pk.cu, pk.total, P, imgs[0].shape[0], self.projection.weight,
+                              self.projection.bias, self.pos_embedding, self._interpolate_pe,
+                              out_dtype or compute_dtype(), patch_index=patch_index)
+        return out, pk
+
+    def _stacks(self):
+        return [self.encoder_blocks]
+
+    def encode_packed(self, x):
+        """Ragged images -> (packed latent rows after all layers + final norm (fp32), Packed)."""
+        h, pk = self.embed_packed(x)
+        stacks = self._stacks()
+        for s in stacks:
+            h = s.forward_packed(h, pk, final_dtype=torch.float32 if s.norm is not None else None)
+        return h, pk
+
+    # ---- reference API --------------------------------------------------------------------------
+    def batchify(self, x):
+        """models.py:36-66: (B, L_m, E) embeddings (+PE) and the (B, L_m) True=padding mask.  Padding rows
+        hold projection(0) = the projection bias, as in the reference."""
+        h, pk = self.embed_packed(x)
+        emb = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self.projection.bias)
+        return emb, pk.mask(emb.device)
+
+    def create_attention_mask(self, seq_lens, max_len):
+        """models.py:70-73."""
+        return torch.arange(end=max_len).unsqueeze(0) >= torch.tensor(seq_lens).unsqueeze(1)
+
+    def _pad_fill(self):
+        # eval-mode nn.TransformerEncoder returns LayerNorm(0) = norm.bias on padding rows;
+        # in train mode the reference leaves arbitrary finite values there; we write zeros.
+        last = self._stacks()[-1]
+        return last.norm.bias if (last.norm is not None and not self.training) else None
+
+    def forward(self, x):
+        """models.py:76-79 -> (x:(B,L_m,E), src_key_padding_mask:(B,L_m) True=padding)."""
+        h, pk = self.encode_packed(x)
+        out = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
+        mask = pk.mask(out.device)
+        out._acai_packed = (h, pk)  # lets ViTOMR feed the decoder without re-packing
+        return out, mask
+
+    def embed_single_image(self, x):
+        """models.py:81-90."""
+        h, pk = self.embed_packed([x])
+        return h.view(1, pk.total, self.hidden_dim)
+
+    def generate(self, x):
+        """models.py:93-96: one (C,H,W) image -> (1, L, E)."""
+        h, pk = self.encode_packed([x])
+        return h.view(1, pk.total, self.hidden_dim)
+
+
+class OMREncoder(Encoder):
+    """models.py:290-332: as Encoder, but oversize images get a bilinearly resized PE grid."""
+    _interpolate_pe = True
+
+    def interpolate_pe(self, h_p, w_p):
+        """models.py:291-302.  Evaluated by the patch-embedding kernel's 4-tap sampler on a zero image."""
+        P = self.patch_size
+        zero = torch.zeros(NUM_CHANNELS, h_p * P, w_p * P, device=self.pos_embedding.device)
+        pk = Packed([h_p * w_p], zero.device)
+        descs = ops.make_image_descs([zero], P, zero.device)
+        pe = ops.patch_embed([zero], descs, pk.cu, pk.total, P, NUM_CHANNELS, self.projection.weight, None,
+                             self.pos_embedding, True, torch.float32)
+        return pe.view(h_p, w_p, self.hidden_dim)
+
+
+class FineTuneOMREncoder(OMREncoder):
+    """models.py:334-376."""
+
+    def __init__(self, patch_size, pe_max_height, pe_max_width, fine_tune_depth, num_layers=12, hidden_dim=768,
+                 num_heads=12, mlp_dim=3072, transformer_dropout=0.05):
+        super().__init__(patch_size, pe_max_height, pe_max_width, num_layers, hidden_dim, num_heads, mlp_dim)
+        assert fine_tune_depth > 0, "If using FineTuneOMREncoder, fine-tune depth should be at least 1"
+        del self.encoder_blocks
+        self.fine_tune_depth = fine_tune_depth
+        self.num_layers = num_layers
+        self.num_frozen_layers = self.num_layers - self.fine_tune_depth
+        self.superclass_kwargs = {"num_heads": num_heads, "mlp_dim": mlp_dim, "transformer_dropout": transformer_dropout}
+        if self.num_frozen_layers == 0:
+            self.frozen_blocks = None
+        else:
+            self.frozen_blocks = _encoder_stack(hidden_dim, num_heads, mlp_dim, 0.0, self.num_frozen_layers, False)
+        self.fine_tune_blocks = _encoder_stack(hidden_dim, num_heads, mlp_dim, transformer_dropout,
+                                               self.fine_tune_depth, True)
+
+    def _stacks(self):
+        return ([self.frozen_blocks] if self.frozen_blocks is not None else []) + [self.fine_tune_blocks]
+
+
+class TransitionHead(nn.Sequential):
+    """nn.Sequential(Linear, GELU, Dropout, Linear) with the reference's child indices ("0", "3";
+    models.py:655-660); forward fuses the GELU into the first projection's epilogue."""
+
+    def forward(self, x):
+        if self.training and self[2].p > 0.0:
+            raise NotImplementedError("transition head dropout > 0 in training mode is not implemented")
+        packed = getattr(x, "_acai_packed", None)
+        if packed is None:
+            return gelu_mlp_head(x, self[0], self[3])
+        # came straight from the encoder: run on the packed rows of valid patches only and re-pad with zeros
+        # (the reference computes head(padding row) there; those rows are masked everywhere downstream)
+        h, pk = packed
+        hp = gelu_mlp_head(h, self[0], self[3])
+        out = ops.unpack_padded(hp, pk.cu, pk.batch, x.shape[1])
+        out._acai_packed = (hp, pk)
+        return out
+
+
+class OMRDecoder(nn.Module):
+    """models.py:378-528."""
+
+    def __init__(self, max_lmx_seq_len, lmx_vocab_path, num_layers=10, hidden_dim=1024, num_heads=16, mlp_dim=4096,
+                 transformer_dropout=0.1, use_caching=False, max_batch_size=None, cache_dtype=None):
+        super().__init__()
+        self.max_lmx_seq_len = max_lmx_seq_len
+        self.lmx_vocab_path = lmx_vocab_path
+        self.num_layers = num_layers
+        self.hidden_dim = hidden_dim
+        self.num_heads = num_heads
+        self.head_dim = hidden_dim / num_heads  # a float in the reference too (models.py:388)
+        self.mlp_dim = mlp_dim
+        self.transformer_dropout = transformer_dropout
+        with open(lmx_vocab_path, "r") as f:
+            tokens = [line.strip() for line in f if line.strip()]
+        self.tokens_to_idxs = {token: i for i, token in enumerate(tokens)}
+        self.idxs_to_tokens = {i: token for i, token in enumerate(tokens)}
+        self.pad_idx = self.tokens_to_idxs[LMX_PAD_TOKEN]
+        self.bos_idx = self.tokens_to_idxs[LMX_BOS_TOKEN]
+        self.eos_idx = self.tokens_to_idxs[LMX_EOS_TOKEN]
+        self.vocab_size = len(tokens)
+        self.vocab_embedding = nn.Embedding(self.vocab_size, self.hidden_dim, padding_idx=self.pad_idx)
+        self.pos_embedding = nn.Parameter(torch.zeros(self.max_lmx_seq_len, self.hidden_dim))
+        nn.init.trunc_normal_(self.pos_embedding, std=0.1)
+        layer_kwargs = dict(d_model=self.hidden_dim, nhead=num_heads, dim_feedforward=mlp_dim,
+                            dropout=transformer_dropout, activation="gelu", batch_first=True)
+        if use_caching:
+            self.decoder_blocks = CachedTransformerDecoder(
+                decoder_layer=CachedTransformerDecoderLayer(**layer_kwargs), num_layers=num_layers,
+                max_batch_size=max_batch_size, max_decoder_seq_len=max_lmx_seq_len, cache_dtype=cache_dtype,
+                norm=LayerNorm(self.hidden_dim, eps=1e-6))
+        else:
+            self.decoder_blocks = TransformerDecoder(lambda: TransformerDecoderLayer(**layer_kwargs),
+                                                     num_layers=num_layers, norm=LayerNorm(self.hidden_dim, eps=1e-6))
+        self.unembed = Linear(self.hidden_dim, self.vocab_size)
+
+    def to_cached_version(self, max_batch_size, cache_dtype):
+        """models.py:431-443."""
+        return OMRDecoder(self.max_lmx_seq_len, self.lmx_vocab_path, self.num_layers, self.hidden_dim, self.num_heads,
+                          self.mlp_dim, self.transformer_dropout, use_caching=True, max_batch_size=max_batch_size,
+                          cache_dtype=cache_dtype)
+
+    # ---- teacher-forced / uncached -----------------------------------------------------------
+    def _memory_packed(self, img_latent, latent_attention_mask, dt):
+        packed = getattr(img_latent, "_acai_packed", None)
+        B, S = img_latent.shape[0], img_latent.shape[1]
+        lens = lens_from_mask(latent_attention_mask, B, S)
+        if packed is not None and packed[1].lens == lens:
+            mem, mp = packed
+            return (mem if mem.dtype == dt else mem.to(dt)), mp
+        mp = Packed(lens, img_latent.device)
+        return ops.pack_padded(img_latent, mp.cu, mp.total, out_dtype=dt), mp
+
+    def _decode_packed(self, input_seqs, img_latent, tgt_lens, latent_attention_mask, token_idxs_input):
+        B, T = input_seqs.shape[0], input_seqs.shape[1]
+        dt = compute_dtype()
+        dev = self.pos_embedding.device
+        tp = Packed(tgt_lens, dev)
+        if token_idxs_input:
+            x = ops.embed_tokens(input_seqs, self.vocab_embedding.weight, self.pos_embedding, dt, period=T)  # (B,T,D)
+            x = ops.pack_padded(x, tp.cu, tp.total)
+        else:
+            raise NotImplementedError("embedding-space inputs (scheduled sampling, models.py:833) are not implemented yet")
+        mem, mp = self._memory_packed(img_latent, latent_attention_mask, dt)
+        h = self.decoder_blocks.forward_packed(x, tp, mem, mp, causal=True)
+        logits = ops.linear(h, w_(self.unembed.weight, dt), self.unembed.bias, out_dtype=dt)
+        return ops.unpack_padded(logits, tp.cu, B, T)
+
+    def forward(self, input_seqs, img_latent, lmx_attention_mask, latent_attention_mask, token_idxs_input=True,
+                checkpoint_grads=False):
+        """models.py:445-483 -> (B, T, vocab).  Rows of padded target positions come back as zeros (the
+        reference leaves unspecified finite values there; the loss ignores them)."""
+        T = input_seqs.shape[1]
+        if T > self.max_lmx_seq_len:
+            raise ValueError(f"{T} long lmx sequence length is too long for max sequence length of {self.max_lmx_seq_len}")
+        lens = lens_from_mask(lmx_attention_mask, input_seqs.shape[0], T)
+        return self._decode_packed(input_seqs, img_latent, lens, latent_attention_mask, token_idxs_input)
+
+    def generate(self, input_seqs, img_latent, latent_attention_mask=None):
+        """models.py:487-500."""
+        seq_len = input_seqs.shape[1]
+        if seq_len > self.max_lmx_seq_len:
+            raise ValueError(f"{seq_len} long lmx sequence length is too long for max sequence length of {self.max_lmx_seq_len}")
+        return self._decode_packed(input_seqs, img_latent, [seq_len] * input_seqs.shape[0], latent_attention_mask, True)
+
+    # ---- KV-cached ------------------------------------------------------------------------------
+    def prepare_caches(self, encoder_memory):
+        """models.py:503-507."""
+        if not isinstance(self.decoder_blocks, CachedTransformerDecoder):
+            raise RuntimeError("Trying to use cached inference pathway with an uncached TransformerDecoder instance")
+        self.decoder_blocks.prepare_caches(encoder_memory)
+
+    def cached_generate(self, token_t, time_step, latent_attention_mask=None):
+        """models.py:518-528: token_t (B,1) -> next-token logits (B,1,V)."""
+        if time_step >= self.max_lmx_seq_len:
+            raise RuntimeError(f"{time_step + 1} decoding steps is too long for max sequence length of {self.max_lmx_seq_len}")
+        dt = compute_dtype()
+        emb = ops.embed_tokens(token_t, self.vocab_embedding.weight, self.pos_embedding, dt, pos_offset=time_step)
+        h = self.decoder_blocks.cached_generate(emb, memory_key_padding_mask=latent_attention_mask)
+        return ops.linear(h, w_(self.unembed.weight, dt), self.unembed.bias, out_dtype=dt)
+
+
+def batchify_and_split_lmx_seqs(lmx_seqs, pad_idx, device):
+    """models.py:531-540 (host-side index bookkeeping; no arithmetic)."""
+    T = max(int(s.shape[0]) for s in lmx_seqs)
+    padded = torch.full((len(lmx_seqs), T), pad_idx, dtype=torch.long, device=lmx_seqs[0].device)
+    for i, s in enumerate(lmx_seqs):
+        padded[i, : s.shape[0]] = s
+    input_seqs, target_seqs = padded[:, :-1], padded[:, 1:]
+    lmx_attention_mask = (input_seqs == pad_idx).to(device)
+    return input_seqs, target_seqs, lmx_attention_mask
+
+
+class ViTOMR(nn.Module):
+    """models.py:542-647."""
+
+    def __init__(self, encoder, transition_head, decoder):
+        super().__init__()
+        self.encoder = encoder
+        self.transition_head = transition_head
+        self.decoder = decoder
+
+    def create_inference_mask(self, seqs):
+        """models.py:550-559 (integer bookkeeping on the finished sequences)."""
+        eos_mask = seqs == self.decoder.eos_idx
+        seen_eos_mask = eos_mask.int().cumsum(dim=-1)
+        first_eos_mask = eos_mask & (seen_eos_mask == 1)
+        return (seen_eos_mask == 0) | first_eos_mask
+
+    def cached_set_up_inference(self, img_latent, max_len):
+        """models.py:562-573; `finished` lives on the device here (no per-step host sync)."""
+        device = img_latent.device
+        self.decoder.prepare_caches(img_latent)
+        num_seqs = img_latent.shape[0]
+        seqs = torch.full([num_seqs, max_len], fill_value=self.decoder.pad_idx, dtype=torch.long, device=device)
+        seqs[:, 0] = self.decoder.bos_idx
+        seq_log_probs = torch.zeros_like(seqs, dtype=torch.float)
+        finished_seqs = torch.zeros([num_seqs], dtype=torch.bool, device=device)
+        return seqs, seq_log_probs, finished_seqs
+
+    def cached_get_next_token(self, seqs, t, latent_attention_mask):
+        """models.py:575-583, including `time_step = t` for the token at index t-1."""
+        logits = self.decoder.cached_generate(seqs[:, t - 1].unsqueeze(1), t, latent_attention_mask).squeeze(1)
+        return ops.argmax_logprob(logits)
+
+    def mask_and_clip_seqs(self, seqs, seq_log_probs):
+        """models.py:585-596."""
+        seq_mask = self.create_inference_mask(seqs)
+        seqs = seqs.masked_fill(~seq_mask, self.decoder.pad_idx)
+        seq_log_probs = seq_log_probs.masked_fill(~seq_mask, 0.0)
+        max_seq_len = int(torch.max(seq_mask.sum(dim=-1)))
+        return seqs[:, :max_seq_len], seq_log_probs[:, :max_seq_len], seq_mask[:, :max_seq_len]
+
+    EOS_POLL_INTERVAL = 16
+
+    def cached_greedy_generate(self, img_latent, latent_attention_mask=None, max_len=1536):
+        """models.py:600-615.  The all-finished test is polled every EOS_POLL_INTERVAL steps instead of
+        every step; the extra steps only write positions after every row's first <eos>, which
+        mask_and_clip_seqs discards, so the returned tensors are identical."""
+        seqs, seq_log_probs, finished = self.cached_set_up_inference(img_latent, max_len)
+        for t in range(1, max_len):
+            nxt, lp = self.cached_get_next_token(seqs, t, latent_attention_mask)
+            seqs[:, t] = nxt
+            seq_log_probs[:, t] = lp
+            finished |= nxt == self.decoder.eos_idx
+            if t % self.EOS_POLL_INTERVAL == 0 and bool(finished.all()):
+                break
+        return self.mask_and_clip_seqs(seqs, seq_log_probs)
+
+    def streamed_cached_greedy_generate(self, img_latent, latent_attention_mask=None, max_len=1536, flush_interval=25):
+        """models.py:625-647 (event dicts use the reference's InferenceEvent string values)."""
+        if img_latent.shape[0] != 1:
+            raise ValueError("Streamed generation only supports single image batches")
+        seqs, seq_log_probs, finished = self.cached_set_up_inference(img_latent, max_len)
+        token_buffer = torch.full([seqs.shape[0], flush_interval], fill_value=self.decoder.pad_idx, dtype=torch.int,
+                                  device=seqs.device)
+        for t in range(1, max_len):
+            nxt, lp = self.cached_get_next_token(seqs, t, latent_attention_mask)
+            seqs[:, t] = nxt
+            seq_log_probs[:, t] = lp
+            token_buffer[:, (t - 1) % flush_interval] = nxt
+            finished |= nxt == self.decoder.eos_idx
+            if bool(finished.all()):
+                break
+            if t % flush_interval == 0:
+                yield {"type": "step", "payload": {"tokens": token_buffer}}
+        seqs, seq_log_probs, seq_mask = self.mask_and_clip_seqs(seqs, seq_log_probs)
+        yield {"type": "inference_finish", "payload": {"sequence": seqs, "log_probs": seq_log_probs, "mask": seq_mask}}
+
+
+class TeacherForcedViTOMR(ViTOMR):
+    """models.py:649-781."""
+
+    def __init__(self, omr_encoder, pretrained_mae_state_dict, omr_decoder, transition_head_dim=4096,
+                 transition_head_dropout=0.05):
+        encoder, decoder = omr_encoder, omr_decoder
+        transition_head = TransitionHead(
+            Linear(encoder.hidden_dim, transition_head_dim), nn.GELU(), nn.Dropout(transition_head_dropout),
+            Linear(transition_head_dim, decoder.hidden_dim))
+        super().__init__(encoder, transition_head, decoder)
+        if pretrained_mae_state_dict:
+            encoder.load_state_dict(self.create_omr_encoder_state_dict_from_mae(pretrained_mae_state_dict))
+        if isinstance(self.encoder, FineTuneOMREncoder) and self.encoder.frozen_blocks:
+            for param in self.encoder.frozen_blocks.parameters():
+                param.requires_grad = False
+            for param in self.encoder.projection.parameters():
+                param.requires_grad = False
+            self.encoder.pos_embedding.requires_grad = False
+        elif isinstance(self.encoder, OMREncoder) and not isinstance(self.encoder, FineTuneOMREncoder):
+            for param in self.encoder.parameters():
+                param.requires_grad = False
+
+    def create_omr_encoder_state_dict_from_mae(self, pretrained_mae_state_dict):
+        """models.py:679-713: MAE `encoder.encoder_blocks.*` keys -> frozen/fine-tune block keys."""
+        sd = {k[len("encoder."):]: v for k, v in pretrained_mae_state_dict.items() if k.startswith("encoder.")}
+        if not isinstance(self.encoder, FineTuneOMREncoder):
+            return sd
+        out = {}
+        threshold = self.encoder.num_layers - self.encoder.fine_tune_depth
+        layer_num = re.compile(r"(?:\w|\.)+?(\d+)(?:\w|\.)+")
+        for key, value in sd.items():
+            m = layer_num.match(key)
+            if m:
+                n = int(m.group(1))
+                if n < threshold:
+                    new = key.replace("encoder_blocks", "frozen_blocks")
+                else:
+                    new = key.replace("encoder_blocks", "fine_tune_blocks").replace(f"layers.{n}", f"layers.{n - threshold}")
+                out[new] = value
+            elif key in ("encoder_blocks.norm.weight", "encoder_blocks.norm.bias"):
+                out[key.replace("encoder_blocks", "fine_tune_blocks")] = value
+            else:
+                out[key] = value
+        return out
+
+    def forward(self, x):
+        """models.py:722-736: list[(img, lmx_seq)] -> (pred (B,T,V), target_seqs (B,T))."""
+        imgs, lmx_seqs = zip(*x)
+        img_latent, latent_attention_mask = self.encoder(imgs)
+        img_latent = self.transition_head(img_latent)
+        input_seqs, target_seqs, lmx_attention_mask = batchify_and_split_lmx_seqs(lmx_seqs, self.decoder.pad_idx,
+                                                                                  img_latent.device)
+        T = input_seqs.shape[1]
+        lmx_attention_mask._acai_lens = [min(int(s.shape[0]), T) for s in lmx_seqs]
+        pred = self.decoder(input_seqs, img_latent, lmx_attention_mask, latent_attention_mask)
+        return pred, target_seqs
+
+    def create_fine_tune_param_groups(self, base_lr, fine_tune_base_lr, fine_tune_decay_factor):
+        """models.py:761-781."""
+        param_groups = [{"params": self.decoder.parameters(), "lr": base_lr},
+                        {"params": self.transition_head.parameters(), "lr": base_lr}]
+        layer_lrs = []
+        for i, layer in enumerate(reversed(self.encoder.fine_tune_blocks.layers)):
+            layer_lr = fine_tune_base_lr * (fine_tune_decay_factor ** i)
+            param_groups.append({"params": layer.parameters(), "lr": layer_lr})
+            layer_lrs.append(layer_lr)
+        min_layer_lr = layer_lrs[-1]
+        param_groups.append({"params": self.encoder.fine_tune_blocks.norm.parameters(), "lr": fine_tune_base_lr})
+        param_groups.append({"params": (p for p in [self.encoder.pos_embedding]), "lr": min_layer_lr})
+        param_groups.append({"params": self.encoder.projection.parameters(), "lr": min_layer_lr})
+        return param_groups, layer_lrs
+
+
+def default_vocab_path():
+    return os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data", "lmx_vocab.txt")

@@ -1,0 +1,265 @@
+"""Tensor-level wrappers over the C ABI (include/acai_b200.h).
+
+torch is used for device memory and the current stream only; every arithmetic op here is a
+launch of one of this repo's sm_100a kernels.  CPU tensors are rejected: there is no fallback.
+`launch_count()` reports how many kernels were enqueued through this module (bench.py's
+`gpu_launches`).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import _lib
+from ._lib import AcaiError, ImageDesc
+
+F32, BF16 = 0, 1
+ACT_NONE, ACT_GELU = 0, 1
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+_launches = 0
+
+
+def launch_count() -> int:
+    return _launches
+
+
+def _bump(n=1):
+    global _launches
+    _launches += n
+
+
+def _dt(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise AcaiError(f"unsupported dtype {t.dtype} (fp32 and bf16 only)") from None
+
+
+def _cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise AcaiError("acai_omr_b200 ops need CUDA tensors (got a CPU tensor); there is no CPU fallback")
+    _lib.require_device()
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f32c(t):
+    """fp32 contiguous view/copy of a (small) parameter tensor."""
+    if t is None:
+        return None
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _rows2d(x):
+    """View x as [rows, cols] with a unit inner stride; returns (tensor, rows, cols, ld)."""
+    cols = x.shape[-1]
+    if x.dim() == 2 and x.stride(1) == 1:
+        return x, x.shape[0], cols, x.stride(0)
+    x2 = x.reshape(-1, cols)
+    if x2.stride(1) != 1:
+        x2 = x2.contiguous()
+    return x2, x2.shape[0], cols, x2.stride(0)
+
+
+# ------------------------------------------------------------------------------------------
+def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None):
+    """act(x @ weight.T + bias) + residual over the last dim (acai_linear_fwd)."""
+    _cuda(x, weight, bias, residual)
+    x2, M, K, lda = _rows2d(x)
+    w = weight.detach()
+    if w.stride(-1) != 1:
+        w = w.contiguous()
+    N = w.shape[0]
+    if w.shape[1] != K:
+        raise AcaiError(f"linear: x has {K} features, weight expects {w.shape[1]}")
+    out_dtype = out_dtype or x.dtype
+    out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    r2, ldr, rdt = None, 0, 0
+    if residual is not None:
+        r2, rm, rn, ldr = _rows2d(residual)
+        if rm != M or rn != N:
+            raise AcaiError("linear: residual shape mismatch")
+        rdt = _dt(r2)
+    b = _f32c(bias)
+    lib = _lib.load()
+    _lib.check(lib.acai_linear_fwd(_p(x2), _dt(x2), lda, _p(w), _dt(w), w.stride(0), _p(b), _p(r2), rdt, ldr,
+                                   _p(out), _DT[out_dtype], N, M, N, K, act, _stream()), "acai_linear_fwd")
+    _bump()
+    return out.view(*x.shape[:-1], N)
+
+
+def layernorm(x, gamma, beta, eps, residual=None, out_dtype=None, out2_dtype=None):
+    """LayerNorm(x + residual) (acai_layernorm_fwd).  Returns out, or (out, out2) if out2_dtype."""
+    _cuda(x, gamma, beta, residual)
+    x2, rows, cols, ld = _rows2d(x)
+    if ld != cols:
+        x2 = x2.contiguous()
+    r2 = None
+    if residual is not None:
+        r2 = residual.reshape(-1, cols).contiguous()
+        if r2.shape[0] != rows:
+            raise AcaiError("layernorm: residual shape mismatch")
+    out_dtype = out_dtype or x.dtype
+    out = torch.empty((rows, cols), dtype=out_dtype, device=x.device)
+    out2 = torch.empty((rows, cols), dtype=out2_dtype, device=x.device) if out2_dtype is not None else None
+    g, b = _f32c(gamma), _f32c(beta)
+    lib = _lib.load()
+    _lib.check(lib.acai_layernorm_fwd(_p(x2), _dt(x2), _p(r2), _dt(r2) if r2 is not None else 0, _p(g), _p(b),
+                                      float(eps), _p(out), _DT[out_dtype], _p(out2),
+                                      _DT[out2_dtype] if out2_dtype is not None else 0, rows, cols, _stream()),
+               "acai_layernorm_fwd")
+    _bump()
+    out = out.view(x.shape)
+    return out if out2 is None else (out, out2.view(x.shape))
+
+
+def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_dtype=None, scale=None):
+    """Packed ragged attention.  q:[Tq, >=H*d] k,v:[Tk, >=H*d] row-strided views (acai_attn_varlen_fwd)."""
+    _cuda(q, k, v, cu_q, cu_k)
+    if not (q.dtype == k.dtype == v.dtype):
+        raise AcaiError("attn_varlen: q/k/v dtype mismatch")
+    for t in (q, k, v):
+        if t.dim() != 2 or t.stride(1) != 1:
+            raise AcaiError("attn_varlen: q/k/v must be 2-D with unit inner stride")
+    out_dtype = out_dtype or q.dtype
+    D = heads * head_dim
+    out = torch.empty((q.shape[0], D), dtype=out_dtype, device=q.device)
+    lib = _lib.load()
+    _lib.check(lib.acai_attn_varlen_fwd(_p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0), v.stride(0),
+                                        _p(cu_q), _p(cu_k), cu_q.numel() - 1, int(max_q), heads, head_dim,
+                                        1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
+                                        _p(out), _DT[out_dtype], D, _stream()), "acai_attn_varlen_fwd")
+    _bump()
+    return out
+
+
+def patch_embed(images, descs_dev, cu_seqlens, total_tokens, patch_size, channels, weight, bias, pos_embedding,
+                interpolate, out_dtype, patch_index=None):
+    """K1 over a ragged image list.  `images` is only kept alive here; `descs_dev` is the device table."""
+    _cuda(descs_dev, cu_seqlens, weight, pos_embedding, *images)
+    E = weight.shape[0]
+    out = torch.empty((total_tokens, E), dtype=out_dtype, device=weight.device)
+    w, b, pe = _f32c(weight), _f32c(bias), _f32c(pos_embedding)
+    lib = _lib.load()
+    _lib.check(lib.acai_patch_embed_fwd(_p(descs_dev), len(images), _p(cu_seqlens), _p(patch_index), total_tokens,
+                                        patch_size, channels, _p(w), _p(b), _p(pe), pe.shape[0], pe.shape[1],
+                                        1 if interpolate else 0, _p(out), _DT[out_dtype], E, _stream()),
+               "acai_patch_embed_fwd")
+    _bump()
+    return out
+
+
+def make_image_descs(images, patch_size, device):
+    """Host-side table of acai_image_desc for a ragged list of (C,H,W) fp32 CUDA tensors -> device bytes."""
+    arr = (ImageDesc * len(images))()
+    for i, t in enumerate(images):
+        H, W = t.shape[-2], t.shape[-1]
+        arr[i] = ImageDesc(t.data_ptr(), H, W, H // patch_size, W // patch_size)
+    host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+    return host.to(device, non_blocking=False)
+
+
+def decode_attn(q, k, v, kv_len, heads, head_dim, key_padding_mask=None, out_dtype=None, scale=None):
+    """q:[B, H*d]; k,v: (B,H,T,d)-strided caches (acai_decode_attn)."""
+    _cuda(q, k, v, key_padding_mask)
+    B = q.shape[0]
+    if k.stride(-1) != 1 or v.stride(-1) != 1 or k.stride() != v.stride() or k.dtype != v.dtype:
+        raise AcaiError("decode_attn: k/v must share strides/dtype with a unit inner stride")
+    if q.stride(-1) != 1:
+        q = q.contiguous()
+    mask = None
+    if key_padding_mask is not None:
+        mask = key_padding_mask.to(torch.uint8) if key_padding_mask.dtype != torch.uint8 else key_padding_mask
+        mask = mask.contiguous()
+    out_dtype = out_dtype or q.dtype
+    out = torch.empty((B, heads * head_dim), dtype=out_dtype, device=q.device)
+    lib = _lib.load()
+    _lib.check(lib.acai_decode_attn(_p(q), _dt(q), q.stride(0), _p(k), _p(v), _dt(k), k.stride(0), k.stride(1),
+                                    k.stride(2), B, heads, head_dim, int(kv_len), _p(mask),
+                                    mask.stride(0) if mask is not None else 0,
+                                    float(scale or 1.0 / math.sqrt(head_dim)), _p(out), _DT[out_dtype],
+                                    out.stride(0), None, 0, _stream()), "acai_decode_attn")
+    _bump()
+    return out
+
+
+def kv_append(k_new, v_new, k_cache, v_cache, pos):
+    """k_new/v_new: (B,H,s,d) strided views -> caches[:B,:,pos:pos+s] (acai_kv_append)."""
+    _cuda(k_new, v_new, k_cache, v_cache)
+    B, H, s, d = k_new.shape
+    if k_new.stride(-1) != 1 or k_new.stride() != v_new.stride():
+        k_new, v_new = k_new.contiguous(), v_new.contiguous()
+    lib = _lib.load()
+    _lib.check(lib.acai_kv_append(_p(k_new), _p(v_new), _dt(k_new), k_new.stride(0), k_new.stride(1), k_new.stride(2),
+                                  s, _p(k_cache), _p(v_cache), _dt(k_cache), k_cache.stride(0), k_cache.stride(1),
+                                  k_cache.stride(2), B, H, d, int(pos), _stream()), "acai_kv_append")
+    _bump()
+
+
+def embed_tokens(ids, table, pos, out_dtype, pos_offset=0, period=0, pos_ids=None):
+    """table[ids] + pos[...] (acai_embed_tokens); ids any integer dtype, any shape."""
+    _cuda(ids, table, pos, pos_ids)
+    flat = ids.reshape(-1)
+    if flat.dtype != torch.int64:
+        flat = flat.long()
+    flat = flat.contiguous()
+    dim = table.shape[1]
+    out = torch.empty((flat.numel(), dim), dtype=out_dtype, device=table.device)
+    t, p = _f32c(table), _f32c(pos)
+    lib = _lib.load()
+    _lib.check(lib.acai_embed_tokens(_p(flat), flat.numel(), _p(t), _p(p), _p(pos_ids), int(pos_offset), int(period),
+                                     _p(out), _DT[out_dtype], dim, _stream()), "acai_embed_tokens")
+    _bump()
+    return out.view(*ids.shape, dim)
+
+
+def argmax_logprob(logits):
+    """(next_token int64 [B], chosen log-prob fp32 [B]) from [B, V] logits (acai_argmax_logprob)."""
+    _cuda(logits)
+    l2, rows, vocab, ld = _rows2d(logits)
+    nxt = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    lp = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    lib = _lib.load()
+    _lib.check(lib.acai_argmax_logprob(_p(l2), _dt(l2), ld, rows, vocab, _p(nxt), _p(lp), _stream()),
+               "acai_argmax_logprob")
+    _bump()
+    return nxt, lp
+
+
+def unpack_padded(packed, cu_seqlens, batch, max_len, fill=None, out_dtype=None):
+    _cuda(packed, cu_seqlens, fill)
+    dim = packed.shape[-1]
+    packed = packed.contiguous()
+    out_dtype = out_dtype or packed.dtype
+    out = torch.empty((batch, max_len, dim), dtype=out_dtype, device=packed.device)
+    f = _f32c(fill)
+    lib = _lib.load()
+    _lib.check(lib.acai_unpack_padded(_p(packed), _dt(packed), _p(cu_seqlens), batch, max_len, dim, _p(f), _p(out),
+                                      _DT[out_dtype], _stream()), "acai_unpack_padded")
+    _bump()
+    return out
+
+
+def pack_padded(padded, cu_seqlens, total, out_dtype=None):
+    _cuda(padded, cu_seqlens)
+    B, L, dim = padded.shape
+    padded = padded.contiguous()
+    out_dtype = out_dtype or padded.dtype
+    out = torch.empty((total, dim), dtype=out_dtype, device=padded.device)
+    lib = _lib.load()
+    _lib.check(lib.acai_pack_padded(_p(padded), _dt(padded), _p(cu_seqlens), B, L, dim, _p(out), _DT[out_dtype],
+                                    _stream()), "acai_pack_padded")
+    _bump()
+    return out

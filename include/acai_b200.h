@@ -1,0 +1,151 @@
+/*
+ * acai_b200.h — C ABI of libacai_b200.so, the sm_100a kernels behind the
+ * `acai_omr_b200.models` drop-in for jsnchon/acai-omr's ViTOMR hot path.
+ *
+ * The reference (pure Python/PyTorch, no FFI of its own) does all arithmetic on
+ * this path through torch ops; each entry point below names the reference call
+ * site(s) (file:line in jsnchon/acai-omr @ 5819ae3) whose arithmetic it
+ * replaces.  The binding a maintainer would add on the reference side is the
+ * ctypes stub in INTEGRATION.md (it is what acai_omr_b200/_lib.py does).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its comment says "host";
+ *   - row-major, innermost dimension contiguous; `ld*` / `*_stride` are in ELEMENTS;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it and
+ *     nothing synchronises; the library allocates nothing (workspaces are passed in);
+ *   - return value: ACAI_OK (0) or a negative acai_status; acai_last_error() gives the
+ *     message for the calling thread.  There is no CPU fallback anywhere.
+ */
+#ifndef ACAI_B200_H_
+#define ACAI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  ACAI_OK = 0,
+  ACAI_ERR_INVALID = -1,     /* bad argument (shape, alignment, null pointer)          */
+  ACAI_ERR_UNSUPPORTED = -2, /* shape/dtype combination this build has no kernel for   */
+  ACAI_ERR_CUDA = -3         /* a CUDA runtime/driver call failed; see acai_last_error */
+} acai_status;
+
+typedef enum { ACAI_F32 = 0, ACAI_BF16 = 1 } acai_dtype;
+typedef enum { ACAI_ACT_NONE = 0, ACAI_ACT_GELU = 1 /* exact erf */ } acai_act;
+
+int acai_version(void);
+const char* acai_last_error(void);
+/* 1 if a CUDA device of compute capability 10.x is present and the kernels can launch. */
+int acai_device_ok(void);
+
+/* ---- K1: fused patchify + embed + 2-D position -----------------------------------------
+ * Replaces Encoder.batchify / OMREncoder.batchify / MAEEncoder.batchify (models.py:36-66,
+ * 304-332, 128-173): nn.Unfold im2col, nn.Linear(C*P*P -> E), + pos_embedding[:h_p,:w_p]
+ * (or its bilinear resize, models.py:291-302, when h_p/w_p exceed the grid and
+ * `interpolate` != 0), over a ragged list of images, written PACKED (no padding rows). */
+typedef struct {
+  const float* pixels; /* (C, H, W) contiguous fp32                                  */
+  int32_t height, width;
+  int32_t hp, wp;      /* patches per column / row = H / P, W / P                     */
+} acai_image_desc;
+
+int acai_patch_embed_fwd(const acai_image_desc* images, /* device array [num_images]             */
+                         int32_t num_images,
+                         const int32_t* cu_seqlens,      /* [num_images+1] packed token offsets   */
+                         const int32_t* patch_index,     /* [total_tokens] token -> patch id in its image,
+                                                            or NULL for identity (MAE keeps 25 %) */
+                         int32_t total_tokens, int32_t patch_size, int32_t channels,
+                         const float* weight,            /* [E, C*P*P] fp32 (nn.Linear layout)    */
+                         const float* bias,              /* [E] or NULL                            */
+                         const float* pos_embedding,     /* [pe_h, pe_w, E] fp32                   */
+                         int32_t pe_h, int32_t pe_w, int32_t interpolate,
+                         void* out, int32_t out_dtype, int32_t embed_dim, void* stream);
+
+/* ---- K2: dense projections ----------------------------------------------------------------
+ * out[M,N] = act(a[M,K] . w[N,K]^T + bias) + residual.   Replaces every nn.Linear / F.linear on
+ * the path: QKV in_proj, out_proj, linear1/linear2, transition head (models.py:655-660), cross
+ * K/V projection (kv_caching.py:241-245), q projections (kv_caching.py:193,215), unembed
+ * (models.py:482,527).  bf16 x bf16 problems with K % 64 == 0 and 16-byte aligned rows run on
+ * tcgen05 tensor cores (TMA-fed, TMEM accumulators); everything else runs the fp32-accumulating
+ * SIMT kernel.  `residual` may alias nothing; `out` may alias `residual`. */
+int acai_linear_fwd(const void* a, int32_t a_dtype, int64_t lda,
+                    const void* w, int32_t w_dtype, int64_t ldw,
+                    const float* bias,
+                    const void* residual, int32_t res_dtype, int64_t ldr,
+                    void* out, int32_t out_dtype, int64_t ldo,
+                    int32_t M, int32_t N, int32_t K, int32_t act, void* stream);
+
+/* ---- K5: LayerNorm(x + residual) ---------------------------------------------------------
+ * Post-norm sublayer tail `norm(x + sublayer(x))` (kv_caching.py:208,220,222; the
+ * nn.TransformerEncoderLayer/DecoderLayer internals) and the final stack norm (eps 1e-6).
+ * Optionally writes a second copy `out2` (e.g. bf16 operand for the next GEMM). */
+int acai_layernorm_fwd(const void* x, int32_t x_dtype, const void* residual, int32_t res_dtype,
+                       const float* gamma, const float* beta, float eps,
+                       void* out, int32_t out_dtype, void* out2, int32_t out2_dtype,
+                       int32_t rows, int32_t cols, void* stream);
+
+/* ---- K3: packed variable-length attention ----------------------------------------------------
+ * softmax(q k^T * scale [causal]) v per (sequence, head) over packed rows delimited by
+ * cu_seqlens, no padding rows.  Replaces the nn.MultiheadAttention / SDPA inside
+ * nn.TransformerEncoder (models.py:30-34,78,186-195,356-366) and nn.TransformerDecoder
+ * (models.py:422-426,480): key-padding masks become sequence boundaries.  q/k/v rows are
+ * [heads*head_dim] slices of wider rows (e.g. the fused QKV buffer), hence the strides. */
+int acai_attn_varlen_fwd(const void* q, const void* k, const void* v, int32_t dtype,
+                         int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                         const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                         int32_t batch, int32_t max_seqlen_q, int32_t heads, int32_t head_dim,
+                         int32_t causal, float scale,
+                         void* out, int32_t out_dtype, int64_t o_stride, void* stream);
+
+/* ---- K4: decode step ---------------------------------------------------------------------------
+ * One query row per (sequence, head) against a KV cache.  Replaces
+ * CachedMultiheadAttention.cached_forward's SDPA (kv_caching.py:123-136) for both the
+ * self-attention cache and the encoder-memory cache.
+ *
+ * acai_decode_attn: strided (B,H,T,d) caches exactly as the reference KVCache lays them out
+ * (kv_caching.py:35-41).  `kv_len` keys are attended; `key_padding_mask` ([B, mask_stride] bytes,
+ * nonzero = ignore; kv_caching.py:126-128) may be NULL. */
+int acai_decode_attn(const void* q, int32_t q_dtype, int64_t q_batch_stride,
+                     const void* k, const void* v, int32_t kv_dtype,
+                     int64_t kv_batch_stride, int64_t kv_head_stride, int64_t kv_tok_stride,
+                     int32_t batch, int32_t heads, int32_t head_dim, int32_t kv_len,
+                     const uint8_t* key_padding_mask, int64_t mask_stride, float scale,
+                     void* out, int32_t out_dtype, int64_t o_batch_stride,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* KVCache.update (kv_caching.py:57-109): writes `n_new` new positions k_new/v_new (logical
+ * (B,H,n_new,d), d contiguous, strides given) at tokens pos..pos+n_new-1 of the (B,H,T,d) caches. */
+int acai_kv_append(const void* k_new, const void* v_new, int32_t src_dtype, int64_t src_batch_stride,
+                   int64_t src_head_stride, int64_t src_tok_stride, int32_t n_new,
+                   void* k_cache, void* v_cache, int32_t cache_dtype,
+                   int64_t kv_batch_stride, int64_t kv_head_stride, int64_t kv_tok_stride,
+                   int32_t batch, int32_t heads, int32_t head_dim, int32_t pos, void* stream);
+
+/* Token embedding + learned 1-D position (models.py:460-466, 492-495, 522-524):
+ * out[r,:] = table[ids[r],:] + pos[pos_ids ? pos_ids[r] : pos_offset + (r % period), :]. */
+int acai_embed_tokens(const int64_t* ids, int32_t rows, const float* table, const float* pos,
+                      const int32_t* pos_ids, int32_t pos_offset, int32_t period,
+                      void* out, int32_t out_dtype, int32_t dim, void* stream);
+
+/* Greedy epilogue (models.py:579-581): argmax over the vocab (first max wins, as torch.argmax),
+ * and log_softmax(logits)[argmax], per row. */
+int acai_argmax_logprob(const void* logits, int32_t dtype, int64_t ld, int32_t rows, int32_t vocab,
+                        int64_t* next_token, float* chosen_logprob, void* stream);
+
+/* Packed rows -> padded (B, L_max, dim) with `fill` (per-feature vector, or NULL = 0) on the
+ * padding rows: the `to_padded_tensor` half of the API (models.py:55-61) and the eval fast
+ * path's LayerNorm(0) = norm.bias padding rows. */
+int acai_unpack_padded(const void* packed, int32_t in_dtype, const int32_t* cu_seqlens, int32_t batch,
+                       int32_t max_len, int32_t dim, const float* fill,
+                       void* out, int32_t out_dtype, void* stream);
+/* Padded (B, L_max, dim) -> packed rows (drops padding rows). */
+int acai_pack_padded(const void* padded, int32_t in_dtype, const int32_t* cu_seqlens, int32_t batch,
+                     int32_t max_len, int32_t dim, void* out, int32_t out_dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACAI_B200_H_ */

@@ -1,0 +1,121 @@
+"""CPU: host-side logic of the drop-in (constructors, state_dict layout, error conventions, masks,
+sequence bookkeeping).  No kernel is launched here."""
+import pytest
+import torch
+
+from acai_omr_b200.layers import Packed, lens_from_mask
+from acai_omr_b200.models import kv_caching as K
+from acai_omr_b200.models import models as M
+
+VOCAB = M.default_vocab_path()
+
+
+def test_vitomr_state_dict_layout_matches_reference(golden):
+    g = golden["vitomr"]
+    enc = M.FineTuneOMREncoder(4, 6, 10, 2, num_layers=2, hidden_dim=32, num_heads=4, mlp_dim=64)
+    dec = M.OMRDecoder(20, VOCAB, num_layers=2, hidden_dim=48, num_heads=4, mlp_dim=96, use_caching=True,
+                       max_batch_size=4, cache_dtype=torch.float)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=40)
+    assert {k: tuple(v.shape) for k, v in vit.state_dict().items()} == golden["vitomr_keys"]
+    vit.load_state_dict(g["sd"])  # strict
+    # KV caches are non-persistent buffers (kv_caching.py:36-44)
+    assert not any("cache" in k for k in vit.state_dict())
+    # full fine-tune: nothing frozen (models.py:677)
+    enc_full = M.FineTuneOMREncoder(4, 6, 10, 2, num_layers=2, hidden_dim=32, num_heads=4, mlp_dim=64)
+    assert enc_full.frozen_blocks is None
+    assert all(p.requires_grad for p in M.TeacherForcedViTOMR(enc_full, None, dec, 40).parameters())
+
+
+def test_freezing_semantics():
+    """models.py:667-676."""
+    dec = M.OMRDecoder(20, VOCAB, num_layers=1, hidden_dim=16, num_heads=2, mlp_dim=16)
+    enc = M.FineTuneOMREncoder(4, 6, 10, 1, num_layers=3, hidden_dim=16, num_heads=2, mlp_dim=16)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, 8)
+    assert not any(p.requires_grad for p in vit.encoder.frozen_blocks.parameters())
+    assert not vit.encoder.pos_embedding.requires_grad and not vit.encoder.projection.weight.requires_grad
+    assert all(p.requires_grad for p in vit.encoder.fine_tune_blocks.parameters())
+    vit2 = M.TeacherForcedViTOMR(M.OMREncoder(4, 6, 10, num_layers=1, hidden_dim=16, num_heads=2, mlp_dim=16), None, dec, 8)
+    assert not any(p.requires_grad for p in vit2.encoder.parameters())
+    groups, lrs = vit.create_fine_tune_param_groups(1e-3, 1e-4, 0.5)
+    assert len(groups) == 2 + 1 + 3 and lrs == [1e-4]
+
+
+def test_mae_to_encoder_key_mapping():
+    """models.py:679-713."""
+    dec = M.OMRDecoder(20, VOCAB, num_layers=1, hidden_dim=16, num_heads=2, mlp_dim=16)
+    enc = M.FineTuneOMREncoder(4, 6, 10, 1, num_layers=3, hidden_dim=16, num_heads=2, mlp_dim=16)
+    src = M.Encoder(4, 6, 10, num_layers=3, hidden_dim=16, num_heads=2, mlp_dim=16)
+    mae_sd = {"encoder." + k: v for k, v in src.state_dict().items()}
+    mae_sd["mask_token"] = torch.zeros(1)
+    vit = M.TeacherForcedViTOMR(enc, mae_sd, dec, 8)
+    assert torch.equal(vit.encoder.frozen_blocks.layers[1].linear1.weight, src.encoder_blocks.layers[1].linear1.weight)
+    assert torch.equal(vit.encoder.fine_tune_blocks.layers[0].linear1.weight, src.encoder_blocks.layers[2].linear1.weight)
+    assert torch.equal(vit.encoder.fine_tune_blocks.norm.weight, src.encoder_blocks.norm.weight)
+
+
+def test_decoder_attributes_and_tokeniser():
+    dec = M.OMRDecoder(15, VOCAB, num_layers=2, hidden_dim=24, num_heads=4, mlp_dim=48)
+    assert (dec.bos_idx, dec.pad_idx, dec.eos_idx, dec.vocab_size) == (0, 1, 2, 227)
+    # reference tests/test_omr_teacher_force_train.py:22-23
+    assert [dec.tokens_to_idxs[t] for t in "measure key:fifths:-7 time".split()] == [3, 4, 19]
+    assert dec.head_dim == 6.0 and dec.decoder_blocks.layers[0].self_attn.head_dim == 6
+    assert dec.vocab_embedding.weight[dec.pad_idx].abs().sum() == 0  # padding_idx row
+    cached = dec.to_cached_version(4, torch.float32)
+    assert isinstance(cached.decoder_blocks, K.CachedTransformerDecoder)
+    cached.load_state_dict(dec.state_dict())
+    assert cached.decoder_blocks.self_attn_caches[0].k_cache.shape == (4, 4, 15, 6)
+    with pytest.raises(RuntimeError):
+        dec.prepare_caches(torch.zeros(1, 2, 24))
+    with pytest.raises(RuntimeError):
+        cached.cached_generate(torch.zeros(1, 1, dtype=torch.long), 15)
+    with pytest.raises(ValueError):
+        dec.generate(torch.zeros(1, 16, dtype=torch.long), torch.zeros(1, 2, 24))
+    with pytest.raises(AssertionError):
+        K.CachedTransformerDecoder(M.TransformerDecoderLayer(8, 2), 1, 1, 4, torch.float32)
+    with pytest.raises(AssertionError):
+        M.FineTuneOMREncoder(4, 6, 10, 0)
+
+
+def test_encoder_grid_errors_fire_before_any_launch():
+    enc = M.Encoder(2, 3, 3, num_layers=1, hidden_dim=8, num_heads=1, mlp_dim=8)
+    with pytest.raises(ValueError):
+        enc.batchify([torch.ones(1, 8, 4)])  # 4 x 2 patches > 3 x 3 grid   (models.py:45-46)
+    assert enc.create_attention_mask([4, 8], 8).tolist() == [[False] * 4 + [True] * 4, [False] * 8]
+
+
+def test_kvcache_host_logic():
+    c = K.KVCache(2, 3, 2, 6, dtype=torch.float)
+    assert c.size == 0 and c.k_cache.shape == (2, 2, 3, 6) and c.cache_pos.tolist() == [0, 1, 2]
+    with pytest.raises(ValueError):
+        c.update(torch.zeros(3, 2, 1, 6), torch.zeros(3, 2, 1, 6))  # kv_caching.py:84-88
+    with pytest.raises(AssertionError):
+        c.update(torch.zeros(2, 2, 4, 6), torch.zeros(2, 2, 4, 6))  # kv_caching.py:90
+    assert "k_cache" not in c.state_dict()
+
+
+def test_packed_and_masks():
+    pk = Packed([3, 5, 1], "cpu")
+    assert pk.cu.tolist() == [0, 3, 8, 9] and pk.total == 9 and pk.max_len == 5
+    m = pk.mask("cpu")
+    assert m.tolist() == [[False] * 3 + [True] * 2, [False] * 5, [False] + [True] * 4]
+    assert lens_from_mask(m, 3, 5) == [3, 5, 1]
+    assert lens_from_mask(m.clone(), 3, 5) == [3, 5, 1]  # without the attached lengths (read back)
+    assert lens_from_mask(None, 2, 7) == [7, 7]
+    bad = torch.tensor([[False, True, False]])
+    with pytest.raises(ValueError):
+        lens_from_mask(bad, 1, 3)
+
+
+def test_split_lmx_and_inference_mask():
+    """reference tests/test_vitomr.py:151-172; models.py:550-559."""
+    seqs = [torch.tensor([0, 2, 3, 226]), torch.tensor([0, 2, 2, 3, 4, 226])]
+    inp, tgt, mask = M.batchify_and_split_lmx_seqs(seqs, 1, "cpu")
+    assert torch.equal(inp, torch.tensor([[0, 2, 3, 226, 1], [0, 2, 2, 3, 4]]))
+    assert torch.equal(tgt, torch.tensor([[2, 3, 226, 1, 1], [2, 2, 3, 4, 226]]))
+    assert mask.tolist() == [[False] * 4 + [True], [False] * 5]
+    dec = M.OMRDecoder(8, VOCAB, num_layers=1, hidden_dim=8, num_heads=1, mlp_dim=8)
+    vit = M.ViTOMR(None, None, dec)
+    s = torch.tensor([[0, 5, 2, 7, 2], [0, 5, 6, 7, 8]])
+    assert vit.create_inference_mask(s).tolist() == [[True, True, True, False, False], [True] * 5]
+    a, b, c = vit.mask_and_clip_seqs(s, torch.ones(2, 5))
+    assert a.tolist() == [[0, 5, 2, 1, 1], [0, 5, 6, 7, 8]] and b[0].tolist() == [1, 1, 1, 0, 0]

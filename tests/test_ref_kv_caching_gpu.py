@@ -1,0 +1,143 @@
+"""GPU: the bodies of the reference's tests/test_kv_caching.py (the acceptance test BASELINE.json names),
+re-stated against the drop-in on cuda:0.  Where the reference compares its cached modules with stock
+torch modules, the comparison here is the drop-in's cached path vs (a) the drop-in's uncached path and
+(b) the CPU oracle on the same weights, at the reference's tolerances (atol 1e-6 / rtol 1e-5 there;
+different summation order on the GPU needs atol 2e-5 here)."""
+import pytest
+import torch
+
+from acai_omr_b200 import ops
+from acai_omr_b200.models import models as M
+from acai_omr_b200.models.kv_caching import (CachedMultiheadAttention, CachedTransformerDecoder,
+                                              CachedTransformerDecoderLayer, KVCache, MemoryCache)
+from oracle import vitomr_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+TOL = dict(atol=2e-5, rtol=1e-4)
+LAYER_KW = dict(d_model=12, nhead=2, dim_feedforward=48, dropout=0.1, activation="gelu", batch_first=True)
+
+
+def cpu_sd(m, prefix=""):
+    return {prefix + k: v.detach().cpu() for k, v in m.state_dict().items()}
+
+
+def test_cached_mha():
+    """reference tests/test_kv_caching.py:13-57."""
+    head_dim, num_heads = 6, 2
+    D = head_dim * num_heads
+    mha = CachedMultiheadAttention(embed_dim=D, num_heads=num_heads, dropout=0.1, batch_first=True).to(DEV).eval()
+    B, T = 2, 3
+    cache = KVCache(B, T, num_heads, head_dim, dtype=torch.float).to(DEV)
+    full = torch.rand(B, T, D)
+    out = torch.empty(B, T, D)
+    for t in range(T):
+        tok = full[:, t:t + 1].to(DEV)
+        qkv = ops.linear(tok, mha.in_proj_weight, mha.in_proj_bias)
+        q_t, k_t, v_t = (c.view(B, num_heads, 1, head_dim) for c in qkv.chunk(3, dim=-1))
+        K_t, V_t = cache.update(k_t, v_t)
+        assert K_t.shape == (B, num_heads, t + 1, head_dim) and cache.size == t + 1
+        out[:, t] = mha.cached_forward(q_t, K_t, V_t).squeeze(1).cpu()
+    sd = cpu_sd(mha)
+    ref = O.mha(full, full, sd["in_proj_weight"], sd["in_proj_bias"], sd["out_proj.weight"], sd["out_proj.bias"],
+                num_heads, causal=True)
+    assert torch.allclose(out, ref, **TOL)
+
+
+def test_cached_cross_attn_with_memory_mask():
+    """reference tests/test_kv_caching.py:59-111."""
+    layer = CachedTransformerDecoderLayer(**LAYER_KW).to(DEV).eval()
+    D, H, d = 12, 2, 6
+    tok, latent = torch.rand(1, 1, D), torch.rand(1, 2, D)
+    mc = MemoryCache()
+    mc.cache_memory_keys_and_vals(latent.to(DEV), layer)
+    K_c, V_c = mc.get_cached_keys_and_vals()
+    assert K_c.shape == (1, H, 2, d)
+    att = layer.multihead_attn
+    q = ops.linear(tok.to(DEV), att.in_proj_weight[:D], att.in_proj_bias[:D]).view(1, H, 1, d)
+    sd = cpu_sd(att)
+    for mask in (None, torch.tensor([[False, True]])):
+        got = att.cached_forward(q, K_c, V_c, memory_key_padding_mask=None if mask is None else mask.to(DEV))
+        ref = O.mha(tok, latent, sd["in_proj_weight"], sd["in_proj_bias"], sd["out_proj.weight"], sd["out_proj.bias"],
+                    H, key_pad_mask=mask)
+        assert torch.allclose(got.cpu(), ref, **TOL)
+
+
+def test_memory_cache_resets_between_batches():
+    """reference tests/test_kv_caching.py:186-221."""
+    layer = CachedTransformerDecoderLayer(**LAYER_KW).to(DEV).eval()
+    D, H, d, B, S = 12, 2, 6, 2, 8
+    sd = cpu_sd(layer.multihead_attn)
+    for seed in (0, 1):
+        latent = torch.rand(B, S, D, generator=torch.Generator().manual_seed(seed))
+        mc = MemoryCache()
+        mc.cache_memory_keys_and_vals(latent.to(DEV), layer)
+        K_c, V_c = mc.get_cached_keys_and_vals()
+        kv = O.linear(latent, sd["in_proj_weight"][D:], sd["in_proj_bias"][D:])
+        ek, ev = (c.view(B, S, H, d).transpose(1, 2) for c in kv.chunk(2, dim=-1))
+        assert torch.allclose(K_c.cpu(), ek, **TOL) and torch.allclose(V_c.cpu(), ev, **TOL)
+
+
+@pytest.mark.parametrize("batch", [4, 3])
+def test_cached_transformer_decoder(batch):
+    """reference tests/test_kv_caching.py:223-317 (masking, batch < max_batch, uncached path of the same module)."""
+    dec = CachedTransformerDecoder(CachedTransformerDecoderLayer(**LAYER_KW), num_layers=3, max_batch_size=4,
+                                   max_decoder_seq_len=200, cache_dtype=torch.float,
+                                   norm=M.LayerNorm(12, eps=1e-6))
+    g = torch.Generator().manual_seed(batch)
+    with torch.no_grad():
+        for p in dec.parameters():  # make the layers differ
+            p.add_(0.1 * torch.randn(p.shape, generator=g))
+    dec = dec.to(DEV).eval()
+    S, T, D = 8, 3, 12
+    latent = torch.rand(batch, S, D, generator=g)
+    mask = torch.zeros(batch, S, dtype=torch.bool)
+    mask[0, 3:] = True
+    mask[2, 6:] = True
+    for use_mask in (False, True, True):  # second masked pass checks prepare_caches really resets
+        dec.prepare_caches(latent.to(DEV))
+        full = torch.rand(batch, T, D, generator=g)
+        got = torch.stack([dec.cached_generate(full[:, t:t + 1].to(DEV),
+                                               memory_key_padding_mask=mask.to(DEV) if use_mask else None).squeeze(1)
+                           for t in range(T)], dim=1)
+        causal = torch.triu(torch.ones(T, T), diagonal=1).bool()
+        uncached = dec(full.to(DEV), memory=latent.to(DEV), tgt_mask=causal.to(DEV),
+                       memory_key_padding_mask=mask.to(DEV) if use_mask else None)
+        ref = O.decoder_stack(full, latent, cpu_sd(dec, "decoder_blocks."), 2, True, None, mask if use_mask else None)
+        assert torch.allclose(got.cpu(), ref, **TOL)
+        assert torch.allclose(uncached.cpu(), ref, **TOL)
+
+
+def test_omr_decoder_with_caching():
+    """reference tests/test_kv_caching.py:319-376."""
+    kw = dict(max_lmx_seq_len=15, lmx_vocab_path=M.default_vocab_path(), num_layers=5, hidden_dim=24, num_heads=4, mlp_dim=48)
+    unc = M.OMRDecoder(**kw)
+    cac = M.OMRDecoder(**kw, use_caching=True, max_batch_size=8, cache_dtype=torch.float)
+    g = torch.Generator().manual_seed(0)
+    with torch.no_grad():
+        for p in unc.parameters():
+            p.add_(0.1 * torch.randn(p.shape, generator=g))
+    cac.load_state_dict(unc.state_dict())
+    unc, cac = unc.to(DEV).eval(), cac.to(DEV).eval()
+    assert torch.equal(unc.decoder_blocks.layers[0].self_attn.in_proj_weight,
+                       cac.decoder_blocks.layers[0].self_attn.in_proj_weight)
+    B, S, T = 8, 20, 10
+    latent = torch.rand(B, S, 24, generator=g)
+    mask = torch.zeros(B, S, dtype=torch.bool)
+    mask[0, 16:] = True
+    mask[2, 13:] = True
+    mask[3, 14:] = True
+    full = torch.randint(0, cac.vocab_size, (B, T), generator=g, dtype=torch.int)  # int32 ids, as the reference test
+    cac.prepare_caches(latent.to(DEV))
+    got = torch.stack([cac.cached_generate(full[:, t:t + 1].to(DEV), t, latent_attention_mask=mask.to(DEV)).squeeze(1)
+                       for t in range(T)], dim=1)
+    ref = O.decoder_forward(full, latent, cpu_sd(unc), 4, None, mask)
+    unc_out = unc.generate(full.to(DEV), latent.to(DEV), latent_attention_mask=mask.to(DEV))
+    assert torch.allclose(got.cpu(), ref, **TOL)
+    assert torch.allclose(unc_out.cpu(), ref, **TOL)
+    tf = cac.forward(full.to(DEV), latent.to(DEV), None, latent_attention_mask=mask.to(DEV))
+    assert torch.allclose(tf.cpu(), ref, **TOL)
+    cac.prepare_caches(latent.to(DEV))
+    with pytest.raises(RuntimeError):
+        for t in range(16):
+            cac.cached_generate(torch.randint(0, 227, (B, 1)).to(DEV), t, latent_attention_mask=mask.to(DEV))

@@ -32,6 +32,9 @@ attn_varlen_simt(const void* __restrict__ q, const void* __restrict__ k, const v
     qr[e] = (valid && e < d) ? ld_as_float(q, (int64_t)(q0 + row) * qs + (int64_t)h * d + e, dt) * scale : 0.0f;
     acc[e] = 0.0f;
   }
+  // columns d..DMAX-1 of the tiles are never loaded; zero them once so q[e]=0 times them stays 0
+  for (int i = tid; i < KT * DMAX; i += QB) { (&Ks[0][0])[i] = 0.0f; (&Vs[0][0])[i] = 0.0f; }
+  __syncthreads();
   float m = -INFINITY, l = 0.0f;
   int kv_end = lk;
   if (causal) { int last = qb * QB + QB - 1 + shift + 1; kv_end = last < lk ? (last < 0 ? 0 : last) : lk; }

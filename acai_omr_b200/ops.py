@@ -86,6 +86,8 @@ def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None):
         raise AcaiError(f"linear: x has {K} features, weight expects {w.shape[1]}")
     out_dtype = out_dtype or x.dtype
     out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    if M == 0:
+        return out.view(*x.shape[:-1], N)
     r2, ldr, rdt = None, 0, 0
     if residual is not None:
         r2, rm, rn, ldr = _rows2d(residual)
@@ -114,6 +116,8 @@ def layernorm(x, gamma, beta, eps, residual=None, out_dtype=None, out2_dtype=Non
     out_dtype = out_dtype or x.dtype
     out = torch.empty((rows, cols), dtype=out_dtype, device=x.device)
     out2 = torch.empty((rows, cols), dtype=out2_dtype, device=x.device) if out2_dtype is not None else None
+    if rows == 0:
+        return out.view(x.shape) if out2 is None else (out.view(x.shape), out2.view(x.shape))
     g, b = _f32c(gamma), _f32c(beta)
     lib = _lib.load()
     _lib.check(lib.acai_layernorm_fwd(_p(x2), _dt(x2), _p(r2), _dt(r2) if r2 is not None else 0, _p(g), _p(b),

@@ -97,12 +97,13 @@ class MultiheadAttention(nn.Module):
         nn.init.constant_(self.out_proj.bias, 0.0)
 
     # ---- packed helpers -------------------------------------------------------------------
-    def self_attention_packed(self, x, cu, max_len, causal, residual):
+    def self_attention_packed(self, x, pk, causal, residual):
         """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D]."""
         dt, D = x.dtype, self.embed_dim
         qkv = ops.linear(x, w_(self.in_proj_weight, dt), self.in_proj_bias, out_dtype=dt)
-        a = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], cu, cu, max_len, self.num_heads,
-                            self.head_dim, causal=causal, out_dtype=dt)
+        a = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pk.cu, pk.cu, pk.max_len, self.num_heads,
+                            self.head_dim, causal=causal, out_dtype=dt,
+                            flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0))
         return ops.linear(a, w_(self.out_proj.weight, dt), self.out_proj.bias, residual=residual, out_dtype=dt)
 
     def project_memory_packed(self, mem):
@@ -110,11 +111,12 @@ class MultiheadAttention(nn.Module):
         dt, D = mem.dtype, self.embed_dim
         return ops.linear(mem, w_(self.in_proj_weight, dt, rows=(D, 3 * D)), self.in_proj_bias[D:], out_dtype=dt)
 
-    def cross_attention_packed(self, x, kv, cu_q, cu_k, max_q, residual):
+    def cross_attention_packed(self, x, kv, pq, pk, residual):
         dt, D = x.dtype, self.embed_dim
         q = ops.linear(x, w_(self.in_proj_weight, dt, rows=(0, D)), self.in_proj_bias[:D], out_dtype=dt)
-        a = ops.attn_varlen(q, kv[:, :D], kv[:, D:], cu_q, cu_k, max_q, self.num_heads, self.head_dim,
-                            causal=False, out_dtype=dt)
+        a = ops.attn_varlen(q, kv[:, :D], kv[:, D:], pq.cu, pk.cu, pq.max_len, self.num_heads, self.head_dim,
+                            causal=False, out_dtype=dt,
+                            flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)))
         return ops.linear(a, w_(self.out_proj.weight, dt), self.out_proj.bias, residual=residual, out_dtype=dt)
 
 
@@ -126,6 +128,7 @@ class Packed:
         self.batch = len(self.lens)
         self.total = sum(self.lens)
         self.max_len = max(self.lens) if self.lens else 0
+        self.sum_sq = float(sum(v * v for v in self.lens))
         off = [0]
         for v in self.lens:
             off.append(off[-1] + v)
@@ -177,7 +180,7 @@ class TransformerEncoderLayer(nn.Module):
 
     def forward_packed(self, x, pk: Packed):
         dt = x.dtype
-        y = self.self_attn.self_attention_packed(x, pk.cu, pk.max_len, False, residual=x)
+        y = self.self_attn.self_attention_packed(x, pk, False, residual=x)
         x = self.norm1(y, out_dtype=dt)
         h = ops.linear(x, w_(self.linear1.weight, dt), self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
         y = ops.linear(h, w_(self.linear2.weight, dt), self.linear2.bias, residual=x, out_dtype=dt)
@@ -255,10 +258,10 @@ class TransformerDecoderLayer(nn.Module):
 
     def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True):
         dt = x.dtype
-        y = self.self_attn.self_attention_packed(x, tgt.cu, tgt.max_len, causal, residual=x)
+        y = self.self_attn.self_attention_packed(x, tgt, causal, residual=x)
         x = self.norm1(y, out_dtype=dt)
         kv = self.multihead_attn.project_memory_packed(mem)
-        y = self.multihead_attn.cross_attention_packed(x, kv, tgt.cu, mem_pk.cu, tgt.max_len, residual=x)
+        y = self.multihead_attn.cross_attention_packed(x, kv, tgt, mem_pk, residual=x)
         x = self.norm2(y, out_dtype=dt)
         return self.mlp_packed(x)
 

@@ -30,6 +30,46 @@ def _bump(n=1):
     _launches += n
 
 
+class Profile:
+    """Per-launch CUDA-event timing (bench.py's roofline leg).  Inside `with Profile() as p:` every kernel launched
+    through this module is bracketed by two events on the launching stream; `p.summary()` groups device time,
+    algorithmic FLOPs and algorithmic bytes by entry point."""
+    active = None
+
+    def __init__(self):
+        self.records = []
+
+    def __enter__(self):
+        Profile.active = self
+        return self
+
+    def __exit__(self, *exc):
+        Profile.active = None
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, e0, e1, flops, nbytes in self.records:
+            d = out.setdefault(name, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0))
+            d["launches"] += 1
+            d["ms"] += e0.elapsed_time(e1)
+            d["flops"] += flops
+            d["bytes"] += nbytes
+        return out
+
+
+def _call(name, fn, *args, flops=0.0, nbytes=0.0):
+    prof = Profile.active
+    if prof is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+    _lib.check(fn(*args), name)
+    if prof is not None:
+        e1.record()
+        prof.records.append((name, e0, e1, flops, nbytes))
+    _bump()
+
+
 def _dt(t: torch.Tensor) -> int:
     try:
         return _DT[t.dtype]
@@ -96,9 +136,9 @@ def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None):
         rdt = _dt(r2)
     b = _f32c(bias)
     lib = _lib.load()
-    _lib.check(lib.acai_linear_fwd(_p(x2), _dt(x2), lda, _p(w), _dt(w), w.stride(0), _p(b), _p(r2), rdt, ldr,
-                                   _p(out), _DT[out_dtype], N, M, N, K, act, _stream()), "acai_linear_fwd")
-    _bump()
+    _call("acai_linear_fwd", lib.acai_linear_fwd, _p(x2), _dt(x2), lda, _p(w), _dt(w), w.stride(0), _p(b), _p(r2), rdt, ldr,
+                                   _p(out), _DT[out_dtype], N, M, N, K, act, _stream(),
+          flops=2.0 * M * N * K, nbytes=float(x2.element_size() * M * K + w.element_size() * N * K + out.element_size() * M * N))
     return out.view(*x.shape[:-1], N)
 
 
@@ -120,16 +160,14 @@ def layernorm(x, gamma, beta, eps, residual=None, out_dtype=None, out2_dtype=Non
         return out.view(x.shape) if out2 is None else (out.view(x.shape), out2.view(x.shape))
     g, b = _f32c(gamma), _f32c(beta)
     lib = _lib.load()
-    _lib.check(lib.acai_layernorm_fwd(_p(x2), _dt(x2), _p(r2), _dt(r2) if r2 is not None else 0, _p(g), _p(b),
+    _call("acai_layernorm_fwd", lib.acai_layernorm_fwd, _p(x2), _dt(x2), _p(r2), _dt(r2) if r2 is not None else 0, _p(g), _p(b),
                                       float(eps), _p(out), _DT[out_dtype], _p(out2),
-                                      _DT[out2_dtype] if out2_dtype is not None else 0, rows, cols, _stream()),
-               "acai_layernorm_fwd")
-    _bump()
+                                      _DT[out2_dtype] if out2_dtype is not None else 0, rows, cols, _stream())
     out = out.view(x.shape)
     return out if out2 is None else (out, out2.view(x.shape))
 
 
-def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_dtype=None, scale=None):
+def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_dtype=None, scale=None, flops=0.0):
     """Packed ragged attention.  q:[Tq, >=H*d] k,v:[Tk, >=H*d] row-strided views (acai_attn_varlen_fwd)."""
     _cuda(q, k, v, cu_q, cu_k)
     if not (q.dtype == k.dtype == v.dtype):
@@ -141,11 +179,10 @@ def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_d
     D = heads * head_dim
     out = torch.empty((q.shape[0], D), dtype=out_dtype, device=q.device)
     lib = _lib.load()
-    _lib.check(lib.acai_attn_varlen_fwd(_p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0), v.stride(0),
+    _call("acai_attn_varlen_fwd", lib.acai_attn_varlen_fwd, _p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0), v.stride(0),
                                         _p(cu_q), _p(cu_k), cu_q.numel() - 1, int(max_q), heads, head_dim,
                                         1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
-                                        _p(out), _DT[out_dtype], D, _stream()), "acai_attn_varlen_fwd")
-    _bump()
+                                        _p(out), _DT[out_dtype], D, _stream(), flops=flops)
     return out
 
 
@@ -157,11 +194,9 @@ def patch_embed(images, descs_dev, cu_seqlens, total_tokens, patch_size, channel
     out = torch.empty((total_tokens, E), dtype=out_dtype, device=weight.device)
     w, b, pe = _f32c(weight), _f32c(bias), _f32c(pos_embedding)
     lib = _lib.load()
-    _lib.check(lib.acai_patch_embed_fwd(_p(descs_dev), len(images), _p(cu_seqlens), _p(patch_index), total_tokens,
+    _call("acai_patch_embed_fwd", lib.acai_patch_embed_fwd, _p(descs_dev), len(images), _p(cu_seqlens), _p(patch_index), total_tokens,
                                         patch_size, channels, _p(w), _p(b), _p(pe), pe.shape[0], pe.shape[1],
-                                        1 if interpolate else 0, _p(out), _DT[out_dtype], E, _stream()),
-               "acai_patch_embed_fwd")
-    _bump()
+                                        1 if interpolate else 0, _p(out), _DT[out_dtype], E, _stream())
     return out
 
 
@@ -190,12 +225,11 @@ def decode_attn(q, k, v, kv_len, heads, head_dim, key_padding_mask=None, out_dty
     out_dtype = out_dtype or q.dtype
     out = torch.empty((B, heads * head_dim), dtype=out_dtype, device=q.device)
     lib = _lib.load()
-    _lib.check(lib.acai_decode_attn(_p(q), _dt(q), q.stride(0), _p(k), _p(v), _dt(k), k.stride(0), k.stride(1),
+    _call("acai_decode_attn", lib.acai_decode_attn, _p(q), _dt(q), q.stride(0), _p(k), _p(v), _dt(k), k.stride(0), k.stride(1),
                                     k.stride(2), B, heads, head_dim, int(kv_len), _p(mask),
                                     mask.stride(0) if mask is not None else 0,
                                     float(scale or 1.0 / math.sqrt(head_dim)), _p(out), _DT[out_dtype],
-                                    out.stride(0), None, 0, _stream()), "acai_decode_attn")
-    _bump()
+                                    out.stride(0), None, 0, _stream())
     return out
 
 
@@ -206,10 +240,9 @@ def kv_append(k_new, v_new, k_cache, v_cache, pos):
     if k_new.stride(-1) != 1 or k_new.stride() != v_new.stride():
         k_new, v_new = k_new.contiguous(), v_new.contiguous()
     lib = _lib.load()
-    _lib.check(lib.acai_kv_append(_p(k_new), _p(v_new), _dt(k_new), k_new.stride(0), k_new.stride(1), k_new.stride(2),
+    _call("acai_kv_append", lib.acai_kv_append, _p(k_new), _p(v_new), _dt(k_new), k_new.stride(0), k_new.stride(1), k_new.stride(2),
                                   s, _p(k_cache), _p(v_cache), _dt(k_cache), k_cache.stride(0), k_cache.stride(1),
-                                  k_cache.stride(2), B, H, d, int(pos), _stream()), "acai_kv_append")
-    _bump()
+                                  k_cache.stride(2), B, H, d, int(pos), _stream())
 
 
 def embed_tokens(ids, table, pos, out_dtype, pos_offset=0, period=0, pos_ids=None):
@@ -223,9 +256,8 @@ def embed_tokens(ids, table, pos, out_dtype, pos_offset=0, period=0, pos_ids=Non
     out = torch.empty((flat.numel(), dim), dtype=out_dtype, device=table.device)
     t, p = _f32c(table), _f32c(pos)
     lib = _lib.load()
-    _lib.check(lib.acai_embed_tokens(_p(flat), flat.numel(), _p(t), _p(p), _p(pos_ids), int(pos_offset), int(period),
-                                     _p(out), _DT[out_dtype], dim, _stream()), "acai_embed_tokens")
-    _bump()
+    _call("acai_embed_tokens", lib.acai_embed_tokens, _p(flat), flat.numel(), _p(t), _p(p), _p(pos_ids), int(pos_offset), int(period),
+                                     _p(out), _DT[out_dtype], dim, _stream())
     return out.view(*ids.shape, dim)
 
 
@@ -236,9 +268,7 @@ def argmax_logprob(logits):
     nxt = torch.empty(rows, dtype=torch.int64, device=logits.device)
     lp = torch.empty(rows, dtype=torch.float32, device=logits.device)
     lib = _lib.load()
-    _lib.check(lib.acai_argmax_logprob(_p(l2), _dt(l2), ld, rows, vocab, _p(nxt), _p(lp), _stream()),
-               "acai_argmax_logprob")
-    _bump()
+    _call("acai_argmax_logprob", lib.acai_argmax_logprob, _p(l2), _dt(l2), ld, rows, vocab, _p(nxt), _p(lp), _stream())
     return nxt, lp
 
 
@@ -250,9 +280,8 @@ def unpack_padded(packed, cu_seqlens, batch, max_len, fill=None, out_dtype=None)
     out = torch.empty((batch, max_len, dim), dtype=out_dtype, device=packed.device)
     f = _f32c(fill)
     lib = _lib.load()
-    _lib.check(lib.acai_unpack_padded(_p(packed), _dt(packed), _p(cu_seqlens), batch, max_len, dim, _p(f), _p(out),
-                                      _DT[out_dtype], _stream()), "acai_unpack_padded")
-    _bump()
+    _call("acai_unpack_padded", lib.acai_unpack_padded, _p(packed), _dt(packed), _p(cu_seqlens), batch, max_len, dim, _p(f), _p(out),
+                                      _DT[out_dtype], _stream())
     return out
 
 
@@ -263,7 +292,6 @@ def pack_padded(padded, cu_seqlens, total, out_dtype=None):
     out_dtype = out_dtype or padded.dtype
     out = torch.empty((total, dim), dtype=out_dtype, device=padded.device)
     lib = _lib.load()
-    _lib.check(lib.acai_pack_padded(_p(padded), _dt(padded), _p(cu_seqlens), B, L, dim, _p(out), _DT[out_dtype],
-                                    _stream()), "acai_pack_padded")
-    _bump()
+    _call("acai_pack_padded", lib.acai_pack_padded, _p(padded), _dt(padded), _p(cu_seqlens), B, L, dim, _p(out), _DT[out_dtype],
+                                    _stream())
     return out

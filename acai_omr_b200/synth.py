@@ -1,0 +1,60 @@
+"""Synthetic workloads of BASELINE.json's shapes: "pianoform system" images whose
+resolutions follow the reference's DynamicResize maths (acai_omr/utils/utils.py:344-354), and
+re-randomised weights so that no two layers are equal.  Host-side helpers only (no kernels)."""
+from __future__ import annotations
+
+import math
+
+import torch
+
+
+def dynamic_resize_shape(aspect: int, max_tokens: int, patch: int = 16):
+    """(H, W) for an integer aspect ratio a = W // H under a token budget: H = P*floor(sqrt(N/a)), W = a*H."""
+    h = patch * int(math.floor(math.sqrt(max_tokens / aspect)))
+    return h, aspect * h
+
+
+def system_shapes(num_systems: int, max_tokens: int = 1024, aspects=(1, 2, 3, 4, 5, 6, 7, 8)):
+    """The config-2 mix: the 8 aspect ratios cycled (64 systems -> sum L = 63 664 for N = 1024)."""
+    return [dynamic_resize_shape(aspects[i % len(aspects)], max_tokens) for i in range(num_systems)]
+
+
+def synth_system(h: int, w: int, seed: int) -> torch.Tensor:
+    """White canvas, 2 x 5 staff lines of 2 px, ~60 dark ellipses/stems, Gaussian noise 0.03; fp32 (1,H,W) in [0,1]."""
+    g = torch.Generator().manual_seed(1234 + seed)
+    img = torch.ones(h, w)
+    for staff in (0.25, 0.65):
+        for line in range(5):
+            y = int(h * (staff + 0.025 * line))
+            img[y:y + 2, :] = 0.0
+    ys = torch.randint(2, max(3, h - 6), (60,), generator=g)
+    xs = torch.randint(2, max(3, w - 6), (60,), generator=g)
+    for y, x in zip(ys.tolist(), xs.tolist()):
+        img[y:y + 4, x:x + 5] = 0.05
+        img[max(0, y - 12):y, x + 4:x + 5] = 0.05
+    img = img + 0.03 * torch.randn(h, w, generator=g)
+    return img.clamp_(0.0, 1.0).unsqueeze(0).contiguous()
+
+
+def rerandomise_(module: torch.nn.Module, seed: int = 1):
+    """Every parameter re-drawn (weights N(0,0.02), biases N(0,0.01), LayerNorm weight 1+N(0,0.02)) so layers differ."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in module.named_parameters():
+            if "norm" in name and name.endswith("weight"):
+                v = 1.0 + 0.02 * torch.randn(p.shape, generator=g)
+            elif name.endswith("bias"):
+                v = 0.01 * torch.randn(p.shape, generator=g)
+            else:
+                v = 0.02 * torch.randn(p.shape, generator=g)
+            p.copy_(v.to(p.device, p.dtype))
+    return module
+
+
+def encoder_flops(lens, layers=12, d=768, mlp=3072, patch_feats=256):
+    """Algorithmic FLOPs of the encoder forward: per token 2*(3d^2 + d^2 + 2*d*mlp) per layer
+    + 2*patch_feats*d for the embedding; attention 4*L^2*d per layer per image (QK^T and PV, 2 FLOP/MAC)."""
+    per_tok_layer = 2.0 * (4 * d * d + 2 * d * mlp)
+    lin = sum(lens) * (layers * per_tok_layer + 2.0 * patch_feats * d)
+    attn = layers * 4.0 * d * sum(l * l for l in lens)
+    return lin + attn

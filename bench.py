@@ -1,0 +1,300 @@
+"""bench.py - BASELINE.json's metric on BASELINE.json's config, one JSON line on stdout.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run)
+    python bench.py --impl reference ...                      (the reference algorithm on the host cores)
+
+Workload at N = 1 (configs[1]): ragged encoder-only forward, 64 synthetic pianoform systems of mixed
+resolutions (DynamicResize shapes, sum L = 63 664 tokens), full-size FineTuneOMREncoder(16, 60, 200, 12),
+bf16 operands / fp32 accumulate, random-init weights.  A "step" is one pass over the 64 systems.
+  value      systems/s with the images already resident in HBM (CUDA events, L2 flushed between steps)
+  e2e        systems/s through the public module API from pinned HOST images, H2D and D2H inside the timed region
+  roofline   the dominant kernel (tcgen05 GEMM) against the measured bf16 peak, timed per launch with CUDA events
+  cpu_baseline   the CPU oracle (a port of the reference algorithm) on a bounded sample, rank 0, N = 1 only
+N > 1: every rank runs its own 64 systems (weak scaling, no data-path collective); time = max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+NUM_SYSTEMS = 64
+METRIC = "ragged-batch ViTOMR encoder systems/sec"
+UNIT = "systems/s"
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm_gbs=p["hbm_gbs"], bf16_tflops=p["bf16_tflops"],
+                    bf16_tflops_sustained=p.get("bf16_tflops_sustained", p["bf16_tflops"]), source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 6 and parts[0].isdigit():
+                self.rows.append(parts)
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(int(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------ workload
+def encoder_kwargs():
+    # omr_teacher_force_train.py:23-27,270-275 in the reference: FineTuneOMREncoder(16, 60, 200, fine_tune_depth=12)
+    return dict(patch_size=16, pe_max_height=60, pe_max_width=200, fine_tune_depth=12, num_layers=12, hidden_dim=768,
+                num_heads=12, mlp_dim=3072)
+
+
+def host_images(num, seed0=0):
+    from acai_omr_b200 import synth
+    return [synth.synth_system(h, w, seed0 + i) for i, (h, w) in enumerate(synth.system_shapes(num))]
+
+
+def build_encoder(device):
+    from acai_omr_b200 import synth
+    from acai_omr_b200.models import models as M
+    torch.manual_seed(0)
+    enc = M.FineTuneOMREncoder(**encoder_kwargs(), transformer_dropout=0.05)
+    synth.rerandomise_(enc, 1)
+    return enc.to(device).eval()
+
+
+def run_ours(args, rank, world, device):
+    from acai_omr_b200 import ops, synth
+    enc = build_encoder(device)
+    imgs_host = [t.pin_memory() for t in host_images(NUM_SYSTEMS, seed0=rank * NUM_SYSTEMS)]
+    imgs_dev = [t.to(device) for t in imgs_host]
+    lens = [(t.shape[-2] // 16) * (t.shape[-1] // 16) for t in imgs_host]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+
+    def step_resident():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            return enc.encode_packed(imgs_dev)[0]
+
+    def step_e2e():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            dev = [t.to(device, non_blocking=True) for t in imgs_host]
+            out, mask = enc(dev)
+        return out.cpu(), mask.cpu()
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, wall=False):
+        total = 0.0
+        for _ in range(steps):
+            flush.zero_()
+            if wall:
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                fn()
+                torch.cuda.synchronize()
+                total += (time.perf_counter() - t0) * 1e3
+            else:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                fn()
+                e1.record()
+                e1.synchronize()
+                total += e0.elapsed_time(e1)
+        return total
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    barrier()
+    n0 = ops.launch_count()
+    with ClockSampler(index=torch.cuda.current_device()) as clocks:
+        ms_total = timed(step_resident, args.steps)
+        barrier()
+    launches = ops.launch_count() - n0
+    step_e2e()
+    barrier()
+    e2e_ms = timed(step_e2e, max(2, min(args.steps, 5)), wall=True) / max(2, min(args.steps, 5))
+    barrier()
+    with ops.Profile() as prof:
+        step_resident()
+    kern = prof.summary()
+
+    t = torch.tensor([ms_total, e2e_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms_step, e2e_ms = t[0].item() / args.steps, t[1].item()
+    if rank != 0:
+        return None
+    peaks = load_peaks()
+    g = kern.get("acai_linear_fwd", dict(ms=1.0, flops=0.0, launches=1))
+    gemm_tflops = g["flops"] / (g["ms"] * 1e-3) / 1e12
+    total_ms = sum(v["ms"] for v in kern.values())
+    flops = synth.encoder_flops(lens)
+    line = {
+        "metric": METRIC, "value": world * NUM_SYSTEMS / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "configs[1]: ragged encoder-only forward, 64 systems/GPU of mixed resolutions "
+                               "(sum L = %d tokens), FineTuneOMREncoder(16,60,200,12) 768d x 12 layers" % sum(lens),
+                   "systems_per_gpu": NUM_SYSTEMS, "tokens_per_gpu": sum(lens), "l2": "flushed between steps (256 MB memset)",
+                   "weights": "random-init, re-randomised per layer", "parallelism": f"dp{world} (sharded systems, no collective)"},
+        "clocks": clocks.summary(),
+        "e2e": {"value": world * NUM_SYSTEMS / (e2e_ms * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": sum(t.numel() * 4 for t in imgs_host),
+                "d2h_bytes_per_step": NUM_SYSTEMS * max(lens) * 768 * 4 + NUM_SYSTEMS * max(lens)},
+        "gpu_launches": launches,
+        "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05 (acai_linear_fwd)", "achieved": gemm_tflops,
+                     "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                     "frac": gemm_tflops / peaks["bf16_tflops_sustained"], "traffic": None,
+                     "peak_source": peaks["source"] + " (sustained bf16, MEASURED_PEAKS.json)",
+                     "kernel_share_of_step": g["ms"] / total_ms, "launches_per_step": g["launches"],
+                     "whole_step_tflops": flops / (ms_step * 1e-3) / 1e12,
+                     "whole_step_frac": flops / (ms_step * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]},
+        "kernels_ms_per_step": {k: round(v["ms"], 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1]["ms"])},
+    }
+    return line
+
+
+# ------------------------------------------------------------------------------------------ CPU arms
+def oracle_encoder_step(imgs, sd, threads):
+    """The reference algorithm (oracle port, fp32, CPU) for the encoder forward on `imgs`."""
+    from oracle import vitomr_oracle as O
+    torch.set_num_threads(threads)
+    cfg = dict(patch_size=16, pe_max_height=60, pe_max_width=200, num_heads=12, interpolate=True,
+               stacks=["fine_tune_blocks"])
+    with torch.no_grad():
+        return O.encoder_forward(imgs, sd, cfg)[0]
+
+
+def cpu_state_dict():
+    from acai_omr_b200 import synth
+    from acai_omr_b200.models import models as M
+    torch.manual_seed(0)
+    enc = M.FineTuneOMREncoder(**encoder_kwargs(), transformer_dropout=0.05)
+    synth.rerandomise_(enc, 1)
+    return {k: v.detach() for k, v in enc.state_dict().items()}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_baseline(sample_systems=8):
+    cores = host_cores()
+    sd = cpu_state_dict()
+    imgs = host_images(sample_systems)
+    oracle_encoder_step(imgs[:1], sd, cores)  # warm-up (thread pool, allocator)
+    t0 = time.perf_counter()
+    oracle_encoder_step(imgs, sd, cores)
+    dt = time.perf_counter() - t0
+    return {"value": sample_systems / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{sample_systems} systems of the same mix (fp32 oracle port of the reference encoder, "
+                      f"torch CPU ops, {cores} threads), {dt:.1f} s"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU algorithm for the path (oracle port; the reference is Python and cannot
+    travel to the GPU box), all host threads, one system per step."""
+    if rank != 0:
+        return None
+    cores = host_cores()
+    sd = cpu_state_dict()
+    imgs = host_images(8)
+    per_step = 1
+    for i in range(args.warmup):
+        oracle_encoder_step(imgs[i % 8:i % 8 + per_step], sd, cores)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        oracle_encoder_step(imgs[i % 8:i % 8 + per_step], sd, cores)
+    dt = time.perf_counter() - t0
+    val = per_step * args.steps / dt
+    sample = f"{per_step} system per step ({args.steps} steps) of the config-2 mix, fp32, {cores} host threads"
+    return {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[1] encoder-only forward, bounded sample: " + sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        line = run_reference(args, rank, world)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback for the product path")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.distributed.init_process_group("nccl", device_id=device)
+    line = run_ours(args, rank, world, device)
+    if line is not None:
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

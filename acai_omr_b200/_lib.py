@@ -37,7 +37,7 @@ SIGNATURES = {
     "acai_patch_embed_fwd": [_p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _i32, _i32, _p],
     "acai_linear_fwd": [_p, _i32, _i64, _p, _i32, _i64, _p, _p, _i32, _i64, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p],
     "acai_layernorm_fwd": [_p, _i32, _p, _i32, _p, _p, _f32, _p, _i32, _p, _i32, _i32, _i32, _p],
-    "acai_attn_varlen_fwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32,
+    "acai_attn_varlen_fwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32,
                              _i64, _p],
     "acai_decode_attn": [_p, _i32, _i64, _p, _p, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i64, _f32, _p,
                          _i32, _i64, _p, _sz, _p],

@@ -134,23 +134,32 @@ decode_attn_simt(const void* __restrict__ q, int q_dt, int64_t q_bs, const void*
   }
 }
 
+int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs,
+                   const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
+                   int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, cudaStream_t st);
+
 }  // namespace acai
 
 using namespace acai;
 
 extern "C" int acai_attn_varlen_fwd(const void* q, const void* k, const void* v, int32_t dtype, int64_t q_stride,
                                     int64_t k_stride, int64_t v_stride, const int32_t* cu_seqlens_q,
-                                    const int32_t* cu_seqlens_k, int32_t batch, int32_t max_seqlen_q, int32_t heads,
-                                    int32_t head_dim, int32_t causal, float scale, void* out, int32_t out_dtype,
-                                    int64_t o_stride, void* stream) {
+                                    const int32_t* cu_seqlens_k, int32_t batch, int32_t max_seqlen_q, int32_t total_q,
+                                    int32_t total_k, int32_t heads, int32_t head_dim, int32_t causal, float scale,
+                                    void* out, int32_t out_dtype, int64_t o_stride, void* stream) {
   ACAI_CHECK_ARG(q && k && v && cu_seqlens_q && cu_seqlens_k && out, "acai_attn_varlen_fwd: null pointer");
   ACAI_CHECK_ARG(batch > 0 && heads > 0 && head_dim > 0 && max_seqlen_q >= 0, "acai_attn_varlen_fwd: bad sizes");
   ACAI_CHECK_ARG(dtype_valid(dtype) && dtype_valid(out_dtype), "acai_attn_varlen_fwd: bad dtype");
   if (head_dim > 128) { set_error("acai_attn_varlen_fwd: head_dim %d > 128 unsupported", head_dim); return ACAI_ERR_UNSUPPORTED; }
   ACAI_CHECK_ARG(heads <= 65535 && batch <= 65535, "acai_attn_varlen_fwd: heads/batch too large for the grid");
-  if (max_seqlen_q == 0) return ACAI_OK;
-  dim3 grid((max_seqlen_q + QB - 1) / QB, heads, batch);
+  if (max_seqlen_q == 0 || total_q == 0) return ACAI_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  {
+    int rc = attn_varlen_tc(q, k, v, dtype, q_stride, k_stride, v_stride, cu_seqlens_q, cu_seqlens_k, batch,
+                            max_seqlen_q, total_q, total_k, heads, head_dim, causal, scale, out, out_dtype, o_stride, st);
+    if (rc != ACAI_ERR_UNSUPPORTED) return rc;
+  }
+  dim3 grid((max_seqlen_q + QB - 1) / QB, heads, batch);
 #define LAUNCH(D) attn_varlen_simt<D><<<grid, QB, 0, st>>>(q, k, v, dtype, q_stride, k_stride, v_stride, cu_seqlens_q, \
                                                            cu_seqlens_k, head_dim, causal, scale, out, out_dtype, o_stride)
   if (head_dim <= 16) LAUNCH(16);

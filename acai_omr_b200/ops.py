@@ -180,7 +180,7 @@ def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_d
     out = torch.empty((q.shape[0], D), dtype=out_dtype, device=q.device)
     lib = _lib.load()
     _call("acai_attn_varlen_fwd", lib.acai_attn_varlen_fwd, _p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0), v.stride(0),
-                                        _p(cu_q), _p(cu_k), cu_q.numel() - 1, int(max_q), heads, head_dim,
+                                        _p(cu_q), _p(cu_k), cu_q.numel() - 1, int(max_q), q.shape[0], k.shape[0], heads, head_dim,
                                         1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
                                         _p(out), _DT[out_dtype], D, _stream(), flops=flops)
     return out

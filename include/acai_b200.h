@@ -92,11 +92,13 @@ int acai_layernorm_fwd(const void* x, int32_t x_dtype, const void* residual, int
  * cu_seqlens, no padding rows.  Replaces the nn.MultiheadAttention / SDPA inside
  * nn.TransformerEncoder (models.py:30-34,78,186-195,356-366) and nn.TransformerDecoder
  * (models.py:422-426,480): key-padding masks become sequence boundaries.  q/k/v rows are
- * [heads*head_dim] slices of wider rows (e.g. the fused QKV buffer), hence the strides. */
+ * [heads*head_dim] slices of wider rows (e.g. the fused QKV buffer), hence the strides; total_q/total_k
+ * are the packed row counts (= cu_seqlens[batch]).  bf16 with head_dim 64 runs the tcgen05 kernel. */
 int acai_attn_varlen_fwd(const void* q, const void* k, const void* v, int32_t dtype,
                          int64_t q_stride, int64_t k_stride, int64_t v_stride,
                          const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
-                         int32_t batch, int32_t max_seqlen_q, int32_t heads, int32_t head_dim,
+                         int32_t batch, int32_t max_seqlen_q, int32_t total_q, int32_t total_k,
+                         int32_t heads, int32_t head_dim,
                          int32_t causal, float scale,
                          void* out, int32_t out_dtype, int64_t o_stride, void* stream);
 

@@ -211,3 +211,31 @@ def test_patch_embed_interpolated_pe():
     sd = {"projection.weight": w.cpu(), "projection.bias": b.cpu(), "pos_embedding": pe.cpu()}
     emb, mask = O.encoder_batchify([i.cpu() for i in imgs], sd, P, 4, 6, interpolate=True)
     close(y.cpu(), emb[~mask], 1e-5, 1e-5)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("lens", [[1024, 968, 972], [1, 127, 128, 129, 300], [64], [257, 5]])
+def test_attn_varlen_tcgen05_d64(lens, causal):
+    """bf16, head_dim 64 -> the tcgen05 kernel (attn_tc.cu); reference = fp32 math on the same bf16 inputs."""
+    H, d = 3, 64
+    T, D = sum(lens), H * d
+    qkv = rnd(T, 3 * D, seed=len(lens) + 7).bfloat16()
+    pk = Packed(lens, DEV)
+    y = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pk.cu, pk.cu, pk.max_len, H, d, causal=causal)
+    ref = ref_varlen(qkv[:, :D].float().contiguous(), qkv[:, D:2 * D].float().contiguous(),
+                     qkv[:, 2 * D:].float().contiguous(), lens, lens, H, d, causal)
+    assert y.dtype == torch.bfloat16
+    close(y, ref, 2e-2, 2e-2)
+    y32 = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pk.cu, pk.cu, pk.max_len, H, d, causal=causal,
+                          out_dtype=torch.float32)
+    close(y32, ref, 1e-2, 1e-2)
+
+
+def test_attn_varlen_tcgen05_cross():
+    H, d = 2, 64
+    lq, lk = [200, 3, 130], [1000, 140, 17]
+    q, kv = rnd(sum(lq), H * d, seed=1).bfloat16(), rnd(sum(lk), 2 * H * d, seed=2).bfloat16()
+    pq, pk = Packed(lq, DEV), Packed(lk, DEV)
+    y = ops.attn_varlen(q, kv[:, :H * d], kv[:, H * d:], pq.cu, pk.cu, pq.max_len, H, d)
+    ref = ref_varlen(q.float(), kv[:, :H * d].float().contiguous(), kv[:, H * d:].float().contiguous(), lq, lk, H, d, False)
+    close(y, ref, 2e-2, 2e-2)

@@ -136,7 +136,9 @@ def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None):
         rdt = _dt(r2)
     b = _f32c(bias)
     lib = _lib.load()
-    _call("acai_linear_fwd", lib.acai_linear_fwd, _p(x2), _dt(x2), lda, _p(w), _dt(w), w.stride(0), _p(b), _p(r2), rdt, ldr,
+    name = "acai_linear_fwd" if Profile.active is None else \
+        f"acai_linear_fwd[{M}x{N}x{K}{',gelu' if act else ''}{',res' if r2 is not None else ''}]"
+    _call(name, lib.acai_linear_fwd, _p(x2), _dt(x2), lda, _p(w), _dt(w), w.stride(0), _p(b), _p(r2), rdt, ldr,
                                    _p(out), _DT[out_dtype], N, M, N, K, act, _stream(),
           flops=2.0 * M * N * K, nbytes=float(x2.element_size() * M * K + w.element_size() * N * K + out.element_size() * M * N))
     return out.view(*x.shape[:-1], N)

@@ -170,7 +170,16 @@ def run_ours(args, rank, world, device):
     if rank != 0:
         return None
     peaks = load_peaks()
-    g = kern.get("acai_linear_fwd", dict(ms=1.0, flops=0.0, launches=1))
+    g = dict(ms=0.0, flops=0.0, launches=0)
+    for k_, v_ in kern.items():
+        if k_.startswith("acai_linear_fwd"):
+            for f_ in g:
+                g[f_] += v_[f_]
+    gemm_shapes = {k_: {"ms": round(v_["ms"], 3), "tflops": round(v_["flops"] / (v_["ms"] * 1e-3) / 1e12, 1),
+                        "launches": v_["launches"]} for k_, v_ in kern.items() if k_.startswith("acai_linear_fwd")}
+    merged = {}
+    for k_, v_ in kern.items():
+        merged.setdefault(k_.split("[")[0], dict(ms=0.0))["ms"] += v_["ms"]
     gemm_tflops = g["flops"] / (g["ms"] * 1e-3) / 1e12
     total_ms = sum(v["ms"] for v in kern.values())
     flops = synth.encoder_flops(lens)
@@ -194,7 +203,8 @@ def run_ours(args, rank, world, device):
                      "kernel_share_of_step": g["ms"] / total_ms, "launches_per_step": g["launches"],
                      "whole_step_tflops": flops / (ms_step * 1e-3) / 1e12,
                      "whole_step_frac": flops / (ms_step * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]},
-        "kernels_ms_per_step": {k: round(v["ms"], 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1]["ms"])},
+        "kernels_ms_per_step": {k: round(v["ms"], 3) for k, v in sorted(merged.items(), key=lambda kv: -kv[1]["ms"])},
+        "gemm_shapes": gemm_shapes,
     }
     return line
 

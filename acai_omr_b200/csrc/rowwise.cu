@@ -32,6 +32,80 @@ layernorm_kernel(const void* __restrict__ x, int x_dt, const void* __restrict__ 
   }
 }
 
+// ---- vectorised path: one warp per row, the row lives in registers (cols % 8 == 0, cols <= 8*32*NV) ----
+__device__ __forceinline__ void load8(const void* p, int64_t idx, int dt, float (&v)[8]) {
+  if (dt == ACAI_BF16) {
+    uint4 raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p) + idx);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+  } else {
+    const float4* q = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p) + idx);
+    float4 a = q[0], b = q[1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+}
+__device__ __forceinline__ void store8(void* p, int64_t idx, int dt, const float (&v)[8]) {
+  if (dt == ACAI_BF16) {
+    uint4 raw; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p) + idx) = raw;
+  } else {
+    float4* q = reinterpret_cast<float4*>(reinterpret_cast<float*>(p) + idx);
+    q[0] = make_float4(v[0], v[1], v[2], v[3]); q[1] = make_float4(v[4], v[5], v[6], v[7]);
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256)
+layernorm_warp_kernel(const void* __restrict__ x, int x_dt, const void* __restrict__ res, int res_dt,
+                      const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                      void* __restrict__ out, int out_dt, void* __restrict__ out2, int out2_dt, int rows, int cols) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int64_t base = (int64_t)row * cols;
+  float v[NV][8];
+  float s = 0.0f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * 8;
+    if (c < cols) {
+      load8(x, base + c, x_dt, v[i]);
+      if (res) {
+        float r[8]; load8(res, base + c, res_dt, r);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[i][e] += r[e];
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s += v[i][e];
+    }
+  }
+  const float mu = warp_sum(s) / (float)cols;
+  float q = 0.0f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * 8;
+    if (c < cols) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { const float d = v[i][e] - mu; q += d * d; }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)cols + eps);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * 8;
+    if (c < cols) {
+      float g[8], b[8], y[8];
+      load8(gamma, c, ACAI_F32, g); load8(beta, c, ACAI_F32, b);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) y[e] = (v[i][e] - mu) * rstd * g[e] + b[e];
+      store8(out, base + c, out_dt, y);
+      if (out2) store8(out2, base + c, out2_dt, y);
+    }
+  }
+}
+
 __global__ void embed_tokens_kernel(const int64_t* __restrict__ ids, const float* __restrict__ table,
                                     const float* __restrict__ pos, const int32_t* __restrict__ pos_ids,
                                     int pos_offset, int period, void* __restrict__ out, int out_dt, int dim) {
@@ -112,6 +186,19 @@ extern "C" int acai_layernorm_fwd(const void* x, int32_t x_dtype, const void* re
   ACAI_CHECK_ARG(dtype_valid(x_dtype) && dtype_valid(out_dtype) && (!residual || dtype_valid(res_dtype)) &&
                  (!out2 || dtype_valid(out2_dtype)), "acai_layernorm_fwd: bad dtype");
   if (rows == 0) return ACAI_OK;
+  const bool aligned = cols % 8 == 0 && cols <= 2048 && !((uintptr_t)x & 15) && !((uintptr_t)out & 15) &&
+                       !((uintptr_t)gamma & 15) && !((uintptr_t)beta & 15) && (!residual || !((uintptr_t)residual & 15)) &&
+                       (!out2 || !((uintptr_t)out2 & 15));
+  if (aligned) {
+    const int nv = (cols / 8 + 31) / 32;
+    dim3 grid((rows + 7) / 8);
+    cudaStream_t st = (cudaStream_t)stream;
+#define LN(NV) layernorm_warp_kernel<NV><<<grid, 256, 0, st>>>(x, x_dtype, residual, res_dtype, gamma, beta, eps, out, \
+                                                              out_dtype, out2, out2_dtype, rows, cols)
+    if (nv <= 1) LN(1); else if (nv <= 2) LN(2); else if (nv <= 3) LN(3); else if (nv <= 4) LN(4); else LN(8);
+#undef LN
+    return launch_status("layernorm_warp");
+  }
   const int threads = cols >= 1024 ? 256 : (cols >= 256 ? 128 : 64);
   layernorm_kernel<<<rows, threads, cols * sizeof(float), (cudaStream_t)stream>>>(
       x, x_dtype, residual, res_dtype, gamma, beta, eps, out, out_dtype, out2, out2_dtype, cols);

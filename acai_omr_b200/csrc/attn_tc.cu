@@ -130,6 +130,7 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
 #pragma unroll
     for (int e = 0; e < D; ++e) acc[e] = 0.0f;
     float m = -INFINITY, l = 0.0f;
+    const float scale_log2 = p.scale_log2;
     const uint32_t row_off = (uint32_t)(r >> 3) * 1024 + (uint32_t)(r & 7) * 128;
     const uint32_t sw = (uint32_t)(r & 7);
 
@@ -149,39 +150,60 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
       ptx::mbar_wait(s_full, j & 1);
       ptx::tc_fence_after();
       const int kbase = j * BKV;
+      const bool full = kbase + BKV <= my_end;      // no key of this block is masked for this row
       float rmax = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t s[32];
-        ptx::tmem_ld_32x32(tmem_s + lane_addr + c * 32, s);
+      for (int c = 0; c < 4; c += 2) {
+        uint32_t s0[32], s1[32];
+        ptx::tmem_ld_32x32(tmem_s + lane_addr + c * 32, s0);
+        ptx::tmem_ld_32x32(tmem_s + lane_addr + c * 32 + 32, s1);
         ptx::tmem_ld_wait();
+        if (full) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (kbase + c * 32 + i < my_end) rmax = fmaxf(rmax, __uint_as_float(s[i]));
+          for (int i = 0; i < 32; ++i) rmax = fmaxf(rmax, fmaxf(__uint_as_float(s0[i]), __uint_as_float(s1[i])));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            if (kbase + c * 32 + i < my_end) rmax = fmaxf(rmax, __uint_as_float(s0[i]));
+            if (kbase + c * 32 + 32 + i < my_end) rmax = fmaxf(rmax, __uint_as_float(s1[i]));
+          }
+        }
       }
       const float m_new = fmaxf(m, rmax);
       const float m_use = m_new == -INFINITY ? 0.0f : m_new;
-      const float corr = exp2f((m - m_use) * p.scale_log2);        // m = -inf -> 0
+      const float corr = fast_exp2((m - m_use) * scale_log2);        // m = -inf -> 0
       l *= corr;
 #pragma unroll
       for (int e = 0; e < D; ++e) acc[e] *= corr;
-      const float moff = m_use * p.scale_log2;
+      const float moff = m_use * scale_log2;
       uint8_t* const p_lo = smem + OFF_K + (j & 1) * TILE;
       uint8_t* const p_hi = smem + OFF_PHI;
+      float lsum0 = 0.0f, lsum1 = 0.0f;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         uint32_t s[32];
         ptx::tmem_ld_32x32(tmem_s + lane_addr + c * 32, s);
         ptx::tmem_ld_wait();
         uint32_t pk[16];
+        if (full) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int kk = kbase + c * 32 + 2 * i;
-          const float p0 = kk < my_end ? exp2f(fmaf(__uint_as_float(s[2 * i]), p.scale_log2, -moff)) : 0.0f;
-          const float p1 = kk + 1 < my_end ? exp2f(fmaf(__uint_as_float(s[2 * i + 1]), p.scale_log2, -moff)) : 0.0f;
-          l += p0 + p1;
-          __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
-          pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+          for (int i = 0; i < 16; ++i) {
+            const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff));
+            const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff));
+            lsum0 += p0; lsum1 += p1;
+            __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+            pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int kk = kbase + c * 32 + 2 * i;
+            const float p0 = kk < my_end ? fast_exp2(fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff)) : 0.0f;
+            const float p1 = kk + 1 < my_end ? fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff)) : 0.0f;
+            lsum0 += p0; lsum1 += p1;
+            __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+            pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+          }
         }
         uint8_t* base = (c < 2 ? p_lo : p_hi) + row_off;
 #pragma unroll
@@ -190,6 +212,7 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
           *reinterpret_cast<uint4*>(base + ((chunk ^ sw) << 4)) = make_uint4(pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2], pk[4 * q4 + 3]);
         }
       }
+      l += lsum0 + lsum1;
       m = m_new;
       ptx::fence_proxy_async_smem();   // make the generic-proxy smem writes visible to the tensor core
       ptx::tc_fence_before();

@@ -30,7 +30,8 @@ struct Epi {
 
 template <int BN> constexpr int stages() { return BN >= 256 ? 4 : (BN >= 128 ? 6 : 8); }
 template <int BN> constexpr size_t smem_bytes() {
-  return (size_t)stages<BN>() * (BM * BK * 2 + BN * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
+  return (size_t)stages<BN>() * (BM * BK * 2 + BN * BK * 2) + EPI_WARPS * 4096 /*epilogue staging*/ +
+         1024 /*align slack*/ + 256 /*barriers*/;
 }
 }  // namespace g5
 
@@ -90,6 +91,83 @@ __device__ __forceinline__ void epi_store_chunk(const Epi& ep, const uint32_t (&
   }
 }
 
+// exact-erf GELU with erf from Abramowitz-Stegun 7.1.26 (|abs err| < 1.5e-7): 2 MUFU + ~12 FMA-pipe ops per element
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  float poly = fmaf(t, 1.061405429f, -1.453152027f);
+  poly = fmaf(t, poly, 1.421413741f);
+  poly = fmaf(t, poly, -0.284496736f);
+  poly = fmaf(t, poly, 0.254829592f);
+  const float e = fast_exp2(-z * z * 1.4426950408889634f);
+  const float erf_abs = fmaf(-poly * t, e, 1.0f);
+  return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+}
+
+// Coalesced epilogue for one 32-row x 32-column accumulator block owned by a warp (thread = row):
+// bias/GELU in registers -> fp32 staging tile in shared memory (16B chunks XOR-swizzled by row) -> re-read with
+// 4 lanes per row so that every global access is a 64..128-byte row segment; the residual is added at that point,
+// with the same coalesced pattern.  Requires N % 8 == 0 and 16-byte aligned rows (checked by the caller).
+__device__ __forceinline__ void epi_block_coalesced(const Epi& ep, const uint32_t (&acc)[32], float* stage, int lane,
+                                                    int row0, int col0, int M, int N) {
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
+  if (ep.bias) {
+    if (col0 + 32 <= N) {
+      const float4* bp = reinterpret_cast<const float4*>(ep.bias + col0);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) { const float4 b4 = __ldg(bp + q); v[4 * q] += b4.x; v[4 * q + 1] += b4.y; v[4 * q + 2] += b4.z; v[4 * q + 3] += b4.w; }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (col0 + j < N) v[j] += __ldg(ep.bias + col0 + j);
+    }
+  }
+  if (ep.act == ACAI_ACT_GELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
+  }
+  __syncwarp();   // the previous block's readers are done with the staging tile
+  {
+    float4* srow = reinterpret_cast<float4*>(stage + lane * 32);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) srow[q ^ (lane & 7)] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+  }
+  __syncwarp();
+  const int sub = lane & 3, c8 = sub * 8;
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int r = it * 8 + (lane >> 2);
+    const int grow = row0 + r, gcol = col0 + c8;
+    const float4* srow = reinterpret_cast<const float4*>(stage + r * 32);
+    const float4 x0 = srow[(2 * sub) ^ (r & 7)], x1 = srow[(2 * sub + 1) ^ (r & 7)];
+    if (grow < M && gcol < N) {
+      float y[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+      if (ep.res) {
+        if (ep.res_dt == ACAI_BF16) {
+          const uint4 raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(ep.res) + (int64_t)grow * ep.ldr + gcol));
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); y[2 * i] += f.x; y[2 * i + 1] += f.y; }
+        } else {
+          const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(ep.res) + (int64_t)grow * ep.ldr + gcol);
+          const float4 a = __ldg(rp), b = __ldg(rp + 1);
+          y[0] += a.x; y[1] += a.y; y[2] += a.z; y[3] += a.w; y[4] += b.x; y[5] += b.y; y[6] += b.z; y[7] += b.w;
+        }
+      }
+      if (ep.out_dt == ACAI_BF16) {
+        uint4 pk; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(y[2 * i], y[2 * i + 1]);
+        *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + (int64_t)grow * ep.ldo + gcol) = pk;
+      } else {
+        float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + (int64_t)grow * ep.ldo + gcol);
+        op[0] = make_float4(y[0], y[1], y[2], y[3]); op[1] = make_float4(y[4], y[5], y[6], y[7]);
+      }
+    }
+  }
+}
+
 template <int BN>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, Epi ep,
@@ -106,6 +184,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  float* staging = reinterpret_cast<float*>(smem + STAGES * (A_BYTES + B_BYTES) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN, num_tiles = num_m * num_n, num_k = K / BK;
@@ -167,8 +246,10 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     const int lane_grp = warp & 3;       // TMEM lanes this warp may touch: 32*(warp%4) ..
     const int half = ew >> 2;            // which half of the BN columns
     constexpr int COLS_PER_WARP = BN / 2;
-    const bool vec_ok = (ep.ldo % 8 == 0) && ((reinterpret_cast<uintptr_t>(ep.out) & 15) == 0) &&
-                        (!ep.res || ((ep.ldr % 8 == 0) && ((reinterpret_cast<uintptr_t>(ep.res) & 15) == 0)));
+    const bool vec_ok = (N % 8 == 0) && (ep.ldo % 8 == 0) && ((reinterpret_cast<uintptr_t>(ep.out) & 15) == 0) &&
+                        (!ep.res || ((ep.ldr % 8 == 0) && ((reinterpret_cast<uintptr_t>(ep.res) & 15) == 0))) &&
+                        (!ep.bias || ((reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0));
+    float* stage = staging + ew * 1024;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
@@ -183,7 +264,11 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
         ptx::tmem_ld_32x32(taddr + c, acc);
         ptx::tmem_ld_wait();
         const int col0 = n0 + half * COLS_PER_WARP + c;
-        if (row < M && col0 < N) epi_store_chunk(ep, acc, row, col0, N, vec_ok);
+        if (vec_ok) {
+          if (col0 < N && m0 + lane_grp * 32 < M) epi_block_coalesced(ep, acc, stage, lane, m0 + lane_grp * 32, col0, M, N);
+        } else if (row < M && col0 < N) {
+          epi_store_chunk(ep, acc, row, col0, N, false);
+        }
       }
       ptx::tc_fence_before();
       __syncwarp();

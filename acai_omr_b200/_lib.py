@@ -42,6 +42,12 @@ SIGNATURES = {
     "acai_decode_attn": [_p, _i32, _i64, _p, _p, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i64, _f32, _p,
                          _i32, _i64, _p, _sz, _p],
     "acai_kv_append": [_p, _p, _i32, _i64, _i64, _i64, _i32, _p, _p, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p],
+    "acai_decode_workspace_bytes": [_i32, _i32, _i32],
+    "acai_decode_attn_paged": [_p, _i64, _p, _i64, _p, _i32, _p, _i32, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _f32, _p,
+                               _i32, _i64, _p, _sz, _p],
+    "acai_decode_embed": [_p, _i64, _p, _i32, _p, _p, _p, _i32, _i32, _p],
+    "acai_greedy_update": [_p, _i32, _i64, _i32, _i32, _p, _p, _i64, _p, _p, _i32, _p],
+    "acai_advance_step": [_p, _p],
     "acai_embed_tokens": [_p, _i32, _p, _p, _p, _i32, _i32, _p, _i32, _i32, _p],
     "acai_argmax_logprob": [_p, _i32, _i64, _i32, _i32, _p, _p, _p],
     "acai_unpack_padded": [_p, _i32, _p, _i32, _i32, _i32, _p, _p, _i32, _p],
@@ -69,7 +75,8 @@ def load():
     for name, argtypes in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.argtypes = argtypes
-        fn.restype = C.c_char_p if name == "acai_last_error" else C.c_int
+        fn.restype = (C.c_char_p if name == "acai_last_error" else
+                      C.c_size_t if name == "acai_decode_workspace_bytes" else C.c_int)
     _lib = lib
     return lib
 

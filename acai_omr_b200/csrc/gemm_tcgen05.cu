@@ -91,17 +91,36 @@ __device__ __forceinline__ void epi_store_chunk(const Epi& ep, const uint32_t (&
   }
 }
 
-// exact-erf GELU with erf from Abramowitz-Stegun 7.1.26 (|abs err| < 1.5e-7): 2 MUFU + ~12 FMA-pipe ops per element
+// exact-erf GELU: x * Phi(x) with erfc from Abramowitz-Stegun 7.1.26 (|abs err of erf| < 1.5e-7).
+// 2 MUFU (rcp, ex2) + ~11 FMA-pipe ops per element; the negative branch keeps full relative accuracy.
 __device__ __forceinline__ float gelu_fast(float x) {
   const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
   float poly = fmaf(t, 1.061405429f, -1.453152027f);
   poly = fmaf(t, poly, 1.421413741f);
   poly = fmaf(t, poly, -0.284496736f);
   poly = fmaf(t, poly, 0.254829592f);
-  const float e = fast_exp2(-z * z * 1.4426950408889634f);
-  const float erf_abs = fmaf(-poly * t, e, 1.0f);
-  return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+  const float zs = z * 1.2011224087864498f;                 // sqrt(log2 e) * z  ->  exp(-z^2) = 2^(-zs^2)
+  const float h = 0.5f * poly * t * fast_exp2(-zs * zs);    // 0.5 * erfc(z)
+  return x * (x >= 0.0f ? 1.0f - h : h);
+}
+
+// Residual prefetch for one 32x32 block: the 16-byte pieces this lane will add in epi_block_coalesced.
+__device__ __forceinline__ void epi_prefetch_res(const Epi& ep, int lane, int row0, int col0, int M, int N, uint4 (&r)[8]) {
+  const int c8 = (lane & 3) * 8;
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int grow = row0 + it * 8 + (lane >> 2), gcol = col0 + c8;
+    if (grow < M && gcol < N) {
+      if (ep.res_dt == ACAI_BF16) {
+        r[it] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(ep.res) + (int64_t)grow * ep.ldr + gcol));
+      } else {
+        const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(ep.res) + (int64_t)grow * ep.ldr + gcol);
+        r[it] = __ldg(rp); r[4 + it] = __ldg(rp + 1);
+      }
+    }
+  }
 }
 
 // Coalesced epilogue for one 32-row x 32-column accumulator block owned by a warp (thread = row):
@@ -109,7 +128,7 @@ __device__ __forceinline__ float gelu_fast(float x) {
 // 4 lanes per row so that every global access is a 64..128-byte row segment; the residual is added at that point,
 // with the same coalesced pattern.  Requires N % 8 == 0 and 16-byte aligned rows (checked by the caller).
 __device__ __forceinline__ void epi_block_coalesced(const Epi& ep, const uint32_t (&acc)[32], float* stage, int lane,
-                                                    int row0, int col0, int M, int N) {
+                                                    int row0, int col0, int M, int N, const uint4 (&rpre)[8]) {
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
@@ -145,13 +164,11 @@ __device__ __forceinline__ void epi_block_coalesced(const Epi& ep, const uint32_
       float y[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
       if (ep.res) {
         if (ep.res_dt == ACAI_BF16) {
-          const uint4 raw = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(ep.res) + (int64_t)grow * ep.ldr + gcol));
-          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rpre[it]);
 #pragma unroll
           for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); y[2 * i] += f.x; y[2 * i + 1] += f.y; }
         } else {
-          const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(ep.res) + (int64_t)grow * ep.ldr + gcol);
-          const float4 a = __ldg(rp), b = __ldg(rp + 1);
+          const float4 a = *reinterpret_cast<const float4*>(&rpre[it]), b = *reinterpret_cast<const float4*>(&rpre[4 + it]);
           y[0] += a.x; y[1] += a.y; y[2] += a.z; y[3] += a.w; y[4] += b.x; y[5] += b.y; y[6] += b.z; y[7] += b.w;
         }
       }
@@ -258,17 +275,25 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
       ptx::tc_fence_after();
       const int row = m0 + lane_grp * 32 + lane;
       const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + as * BN + half * COLS_PER_WARP;
+      const int brow0 = m0 + lane_grp * 32, bcol0 = n0 + half * COLS_PER_WARP;
+      const bool active = vec_ok && brow0 < M;
+      uint4 rcur[8], rnext[8];
+      if (active && ep.res && bcol0 < N) epi_prefetch_res(ep, lane, brow0, bcol0, M, N, rcur);
 #pragma unroll 1
       for (int c = 0; c < COLS_PER_WARP; c += 32) {
+        const int col0 = bcol0 + c;
+        if (active && ep.res && c + 32 < COLS_PER_WARP && col0 + 32 < N)
+          epi_prefetch_res(ep, lane, brow0, col0 + 32, M, N, rnext);   // one block ahead: hides the L2/HBM latency
         uint32_t acc[32];
         ptx::tmem_ld_32x32(taddr + c, acc);
         ptx::tmem_ld_wait();
-        const int col0 = n0 + half * COLS_PER_WARP + c;
         if (vec_ok) {
-          if (col0 < N && m0 + lane_grp * 32 < M) epi_block_coalesced(ep, acc, stage, lane, m0 + lane_grp * 32, col0, M, N);
+          if (col0 < N && brow0 < M) epi_block_coalesced(ep, acc, stage, lane, brow0, col0, M, N, rcur);
         } else if (row < M && col0 < N) {
           epi_store_chunk(ep, acc, row, col0, N, false);
         }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) rcur[i] = rnext[i];
       }
       ptx::tc_fence_before();
       __syncwarp();

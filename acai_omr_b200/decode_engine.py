@@ -1,0 +1,147 @@
+"""KV-cached greedy decode engine: ViTOMR.cached_greedy_generate's loop (models.py:562-615) with every step
+captured ONCE as a CUDA graph and replayed, no host sync per step.
+
+Layout in HBM (dtype = compute dtype, bf16 under autocast / fp32 otherwise):
+  self cache   pool[layer]  : [B * pages_per_seq * 64 rows, 2*D]  token-major rows [K | V], 64-token pages, page table [B, pages]
+  memory cache cross[layer] : [sum S_b rows, 2*D]  = the cross-KV projection GEMM's output, packed (no padding rows)
+  per step     x [B, D], qkv [B, 3D], mlp hidden [B, M], logits [B, V]
+Per step and layer: qkv GEMM -> paged split-KV attention (appends this step's K|V row) -> out-proj GEMM (+residual)
+-> LN -> cross-q GEMM -> attention over the memory cache -> out-proj GEMM (+residual) -> LN -> MLP GEMMs -> LN.
+The step index lives in device memory; the embedding, attention and greedy-update kernels read it, so the same
+graph serves every step.  `finished` is polled every POLL steps; extra steps past the all-finished point only write
+positions that mask_and_clip_seqs discards, so outputs are identical to the reference loop.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .layers import Packed, compute_dtype, lens_from_mask, w_
+
+PAGE = 64
+POLL = 32
+
+
+def eligible(decoder, dt) -> bool:
+    from .models.kv_caching import CachedTransformerDecoder
+    blocks = decoder.decoder_blocks
+    if not isinstance(blocks, CachedTransformerDecoder):
+        return False
+    layer = blocks.layers[0]
+    cache_dt = blocks.self_attn_caches[0].k_cache.dtype
+    return layer.head_dim == 64 and cache_dt == dt and decoder.hidden_dim % 8 == 0
+
+
+class GreedyDecodeEngine:
+    def __init__(self, decoder, batch, max_len, mem_rows, dt, device):
+        self.dec, self.B, self.max_len, self.mem_rows, self.dt, self.device = decoder, batch, max_len, mem_rows, dt, device
+        blocks = decoder.decoder_blocks
+        self.L, self.D, self.H = len(blocks.layers), decoder.hidden_dim, blocks.layers[0].num_heads
+        D, B = self.D, batch
+        self.pages_per_seq = (max_len + PAGE - 1) // PAGE
+        rows = B * self.pages_per_seq * PAGE
+        self.pool = [torch.empty((rows, 2 * D), dtype=dt, device=device) for _ in range(self.L)]
+        self.page_table = torch.arange(B * self.pages_per_seq, dtype=torch.int32, device=device).view(B, self.pages_per_seq)
+        self.cross = [torch.empty((mem_rows, 2 * D), dtype=dt, device=device) for _ in range(self.L)]
+        self.seq_start = torch.zeros(B, dtype=torch.int32, device=device)
+        self.kv_lens = torch.zeros(B, dtype=torch.int32, device=device)
+        self.step = torch.ones(1, dtype=torch.int32, device=device)
+        self.seqs = torch.empty((B, max_len), dtype=torch.long, device=device)
+        self.logp = torch.empty((B, max_len), dtype=torch.float32, device=device)
+        self.finished = torch.empty(B, dtype=torch.uint8, device=device)
+        self.max_mem_len = 0
+        self.ws_self = ops.decode_workspace(B, self.H, max_len, device)
+        self.ws_cross = None
+        self.graph = None
+
+    # ---- one decode step (what the graph captures) ------------------------------------------------------------
+    def _step(self):
+        dec, dt, D, H = self.dec, self.dt, self.D, self.H
+        x = ops.decode_embed(self.seqs, self.step, dec.vocab_embedding.weight, dec.pos_embedding, dt)
+        for i, layer in enumerate(dec.decoder_blocks.layers):
+            sa, ca = layer.self_attn, layer.multihead_attn
+            qkv = ops.linear(x, w_(sa.in_proj_weight, dt), sa.in_proj_bias, out_dtype=dt)
+            a = ops.decode_attn_paged(qkv[:, :D], qkv[:, D:], self.pool[i], H, 64, self.max_len, self.ws_self, dt,
+                                      page_table=self.page_table, step=self.step, len_offset=-1)
+            y = ops.linear(a, w_(sa.out_proj.weight, dt), sa.out_proj.bias, residual=x, out_dtype=dt)
+            x = layer.norm1(y, out_dtype=dt)
+            qc = ops.linear(x, w_(ca.in_proj_weight, dt, rows=(0, D)), ca.in_proj_bias[:D], out_dtype=dt)
+            c = ops.decode_attn_paged(qc, None, self.cross[i], H, 64, self.max_mem_len, self.ws_cross, dt,
+                                      seq_start=self.seq_start, kv_lens=self.kv_lens)
+            y = ops.linear(c, w_(ca.out_proj.weight, dt), ca.out_proj.bias, residual=x, out_dtype=dt)
+            x = layer.norm2(y, out_dtype=dt)
+            x = layer.mlp_packed(x)
+        if dec.decoder_blocks.norm is not None:
+            x = dec.decoder_blocks.norm(x, out_dtype=dt)
+        logits = ops.linear(x, w_(dec.unembed.weight, dt), dec.unembed.bias, out_dtype=dt)
+        ops.greedy_update(logits, self.step, self.seqs, self.logp, self.finished, dec.eos_idx)
+        ops.advance_step(self.step)
+
+    def _reset(self):
+        self.seqs.fill_(self.dec.pad_idx)
+        self.seqs[:, 0] = self.dec.bos_idx
+        self.logp.zero_()
+        self.finished.zero_()
+        self.step.fill_(1)
+
+    # ---- prefill: cross K/V of the encoder memory straight into the memory cache ----------------------------------
+    def prefill(self, mem_packed, mp: Packed):
+        dt, D = self.dt, self.D
+        if mem_packed.dtype != dt:
+            mem_packed = mem_packed.to(dt)
+        for i, layer in enumerate(self.dec.decoder_blocks.layers):
+            ca = layer.multihead_attn
+            ops.linear(mem_packed, w_(ca.in_proj_weight, dt, rows=(D, 3 * D)), ca.in_proj_bias[D:],
+                       out=self.cross[i][: mp.total])
+        self.seq_start.copy_(mp.cu[:-1], non_blocking=True)
+        self.kv_lens.copy_(mp.cu[1:] - mp.cu[:-1], non_blocking=True)
+        if mp.max_len > self.max_mem_len or self.ws_cross is None:     # grid of the cross pass grows: re-capture
+            self.max_mem_len = max(mp.max_len, self.max_mem_len)
+            self.ws_cross = ops.decode_workspace(self.B, self.H, self.max_mem_len, self.device)
+            self.graph = None
+
+    def generate(self, stop_early=True):
+        """Run steps t = 1 .. max_len-1 (or until every row has emitted <eos>); returns raw (seqs, log_probs)."""
+        if self.graph is None:
+            self._reset()
+            self._step()                      # eager warm-up: bf16 weight copies, tensor maps, function attributes
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            self._reset()
+            with torch.cuda.graph(g):
+                self._step()
+            self.graph = g
+        self._reset()
+        for t in range(1, self.max_len):
+            self.graph.replay()
+            if stop_early and t % POLL == 0 and bool(self.finished.all()):
+                break
+        return self.seqs, self.logp
+
+
+def get_engine(vitomr, decoder, batch, max_len, mem_rows, dt, device):
+    cache = vitomr.__dict__.setdefault("_acai_engines", {})
+    key = (id(decoder), batch, max_len, dt, str(device))
+    eng = cache.get(key)
+    if eng is None or eng.mem_rows < mem_rows:
+        cache.clear()                          # one engine at a time: the caches are large
+        eng = GreedyDecodeEngine(decoder, batch, max_len, max(mem_rows, 1), dt, device)
+        cache[key] = eng
+    return eng
+
+
+def greedy_generate(vitomr, img_latent, latent_attention_mask, max_len, stop_early=True):
+    """Fast path of ViTOMR.cached_greedy_generate; returns None when the decoder does not qualify."""
+    dec = vitomr.decoder
+    dt = compute_dtype()
+    if not img_latent.is_cuda or not eligible(dec, dt) or max_len > dec.max_lmx_seq_len or max_len < 2:
+        return None
+    B, S = img_latent.shape[0], img_latent.shape[1]
+    if B > dec.decoder_blocks.self_attn_caches[0].max_batch_size:
+        raise ValueError(f"The current cache has been setup with a max batch size of "
+                         f"{dec.decoder_blocks.self_attn_caches[0].max_batch_size}, but found batch size {B}!")
+    mem, mp = dec._memory_packed(img_latent, latent_attention_mask, dt)
+    eng = get_engine(vitomr, dec, B, max_len, mp.total, dt, img_latent.device)
+    eng.prefill(mem, mp)
+    seqs, logp = eng.generate(stop_early=stop_early)
+    return seqs.clone(), logp.clone()

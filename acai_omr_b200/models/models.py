@@ -348,6 +348,11 @@ class ViTOMR(nn.Module):
         """models.py:600-615.  The all-finished test is polled every EOS_POLL_INTERVAL steps instead of
         every step; the extra steps only write positions after every row's first <eos>, which
         mask_and_clip_seqs discards, so the returned tensors are identical."""
+        from ..decode_engine import greedy_generate
+        fast = greedy_generate(self, img_latent, latent_attention_mask, max_len)   # CUDA-graphed paged-KV engine
+        if fast is not None:
+            return self.mask_and_clip_seqs(*fast)
+        # generic path (any head_dim / cache dtype): the module-level cached API, one launch per op
         seqs, seq_log_probs, finished = self.cached_set_up_inference(img_latent, max_len)
         for t in range(1, max_len):
             nxt, lp = self.cached_get_next_token(seqs, t, latent_attention_mask)

@@ -114,7 +114,7 @@ def _rows2d(x):
 
 
 # ------------------------------------------------------------------------------------------
-def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None):
+def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None, out=None):
     """act(x @ weight.T + bias) + residual over the last dim (acai_linear_fwd)."""
     _cuda(x, weight, bias, residual)
     x2, M, K, lda = _rows2d(x)
@@ -124,8 +124,13 @@ def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None):
     N = w.shape[0]
     if w.shape[1] != K:
         raise AcaiError(f"linear: x has {K} features, weight expects {w.shape[1]}")
-    out_dtype = out_dtype or x.dtype
-    out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    if out is not None:
+        if out.shape != (M, N) or out.stride(1) != 1:
+            raise AcaiError("linear: `out` must be [M, N] with a unit inner stride")
+        out_dtype = out.dtype
+    else:
+        out_dtype = out_dtype or x.dtype
+        out = torch.empty((M, N), dtype=out_dtype, device=x.device)
     if M == 0:
         return out.view(*x.shape[:-1], N)
     r2, ldr, rdt = None, 0, 0
@@ -139,7 +144,7 @@ def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None):
     name = "acai_linear_fwd" if Profile.active is None else \
         f"acai_linear_fwd[{M}x{N}x{K}{',gelu' if act else ''}{',res' if r2 is not None else ''}]"
     _call(name, lib.acai_linear_fwd, _p(x2), _dt(x2), lda, _p(w), _dt(w), w.stride(0), _p(b), _p(r2), rdt, ldr,
-                                   _p(out), _DT[out_dtype], N, M, N, K, act, _stream(),
+                                   _p(out), _DT[out_dtype], out.stride(0), M, N, K, act, _stream(),
           flops=2.0 * M * N * K, nbytes=float(x2.element_size() * M * K + w.element_size() * N * K + out.element_size() * M * N))
     return out.view(*x.shape[:-1], N)
 
@@ -297,3 +302,51 @@ def pack_padded(padded, cu_seqlens, total, out_dtype=None):
     _call("acai_pack_padded", lib.acai_pack_padded, _p(padded), _dt(padded), _p(cu_seqlens), B, L, dim, _p(out), _DT[out_dtype],
                                     _stream())
     return out
+
+
+# ------------------------------------------------------------------------------------------ decode engine ops
+def decode_workspace(batch, heads, max_kv_len, device):
+    n = _lib.load().acai_decode_workspace_bytes(batch, heads, max_kv_len)
+    return torch.empty(n, dtype=torch.uint8, device=device)
+
+
+def decode_attn_paged(q, new_kv, kv_rows, heads, head_dim, max_kv_len, workspace, out_dtype, page_table=None,
+                      seq_start=None, kv_lens=None, step=None, len_offset=0, scale=None):
+    """Token-major (paged) decode attention (acai_decode_attn_paged).  q:[B, >=H*d] view, new_kv:[B, >=2*H*d] view or None,
+    kv_rows:[rows, 2*H*d] cache."""
+    _cuda(q, new_kv, kv_rows, page_table, seq_start, kv_lens, step, workspace)
+    B = q.shape[0]
+    out = torch.empty((B, heads * head_dim), dtype=out_dtype, device=q.device)
+    lib = _lib.load()
+    nbytes = float(kv_rows.element_size()) * 2 * heads * head_dim * B * max_kv_len  # upper bound; bench.py passes exact
+    _call("acai_decode_attn_paged", lib.acai_decode_attn_paged, _p(q), q.stride(0), _p(new_kv),
+          new_kv.stride(0) if new_kv is not None else 0, _p(kv_rows), _dt(kv_rows), _p(page_table),
+          page_table.stride(0) if page_table is not None else 0, _p(seq_start), _p(kv_lens), _p(step), int(len_offset),
+          int(max_kv_len), B, heads, head_dim, float(scale or 1.0 / math.sqrt(head_dim)), _p(out), _DT[out_dtype],
+          out.stride(0), _p(workspace), workspace.numel(), _stream(), nbytes=nbytes)
+    _bump()  # two kernels per call (split-KV pass + combine)
+    return out
+
+
+def decode_embed(seqs, step, table, pos, out_dtype):
+    _cuda(seqs, step, table, pos)
+    B, dim = seqs.shape[0], table.shape[1]
+    out = torch.empty((B, dim), dtype=out_dtype, device=seqs.device)
+    lib = _lib.load()
+    _call("acai_decode_embed", lib.acai_decode_embed, _p(seqs), seqs.stride(0), _p(step), B, _p(_f32c(table)),
+          _p(_f32c(pos)), _p(out), _DT[out_dtype], dim, _stream())
+    return out
+
+
+def greedy_update(logits, step, seqs, log_probs, finished, eos_idx):
+    _cuda(logits, step, seqs, log_probs, finished)
+    l2, rows, vocab, ld = _rows2d(logits)
+    lib = _lib.load()
+    _call("acai_greedy_update", lib.acai_greedy_update, _p(l2), _dt(l2), ld, rows, vocab, _p(step), _p(seqs),
+          seqs.stride(0), _p(log_probs), _p(finished), int(eos_idx), _stream())
+
+
+def advance_step(step):
+    _cuda(step)
+    lib = _lib.load()
+    _call("acai_advance_step", lib.acai_advance_step, _p(step), _stream())

@@ -126,6 +126,33 @@ int acai_kv_append(const void* k_new, const void* v_new, int32_t src_dtype, int6
                    int64_t kv_batch_stride, int64_t kv_head_stride, int64_t kv_tok_stride,
                    int32_t batch, int32_t heads, int32_t head_dim, int32_t pos, void* stream);
 
+/* acai_decode_attn_paged: the same attention over a TOKEN-MAJOR cache whose rows are [K(H*64) | V(H*64)] - the
+ * layout the fused QKV / cross-KV projections emit - addressed through a page table (64 tokens per page; the
+ * self-attention pool) or as seq_start[b] + t (the packed encoder-memory cache, no padding rows).  If `new_kv` is
+ * given, this step's [K|V] row of every sequence is appended at position len (KVCache.update, kv_caching.py:57-109)
+ * and attended to.  len = kv_lens[b], or *step_ptr + len_offset (device-side step counter, so that one captured
+ * CUDA graph serves every step).  head_dim must be 64; q/new_kv/cache share `dtype`.  Split-KV over 256-token chunks
+ * with a combine pass; `workspace` holds the partials (acai_decode_workspace_bytes). */
+size_t acai_decode_workspace_bytes(int32_t batch, int32_t heads, int32_t max_kv_len);
+int acai_decode_attn_paged(const void* q, int64_t q_stride, const void* new_kv, int64_t new_kv_stride,
+                           void* kv_rows, int32_t dtype, const int32_t* page_table, int32_t table_stride,
+                           const int32_t* seq_start, const int32_t* kv_lens, const int32_t* step_ptr,
+                           int32_t len_offset, int32_t max_kv_len, int32_t batch, int32_t heads, int32_t head_dim,
+                           float scale, void* out, int32_t out_dtype, int64_t o_stride,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* Greedy-loop bookkeeping driven by the device-side step counter t = *step_ptr (models.py:575-583, 603-610):
+ *   acai_decode_embed : out[b] = table[seqs[b, t-1]] + pos[t]   (time_step = t for the token at t-1, models.py:576)
+ *   acai_greedy_update: seqs[b, t] = argmax(logits[b]); log_probs[b, t] = log_softmax(logits[b])[argmax];
+ *                       finished[b] |= (argmax == eos)
+ *   acai_advance_step : *step_ptr += 1 */
+int acai_decode_embed(const int64_t* seqs, int64_t seq_stride, const int32_t* step_ptr, int32_t batch,
+                      const float* table, const float* pos, void* out, int32_t out_dtype, int32_t dim, void* stream);
+int acai_greedy_update(const void* logits, int32_t dtype, int64_t ld, int32_t rows, int32_t vocab,
+                       const int32_t* step_ptr, int64_t* seqs, int64_t seq_stride, float* log_probs,
+                       uint8_t* finished, int32_t eos_idx, void* stream);
+int acai_advance_step(int32_t* step_ptr, void* stream);
+
 /* Token embedding + learned 1-D position (models.py:460-466, 492-495, 522-524):
  * out[r,:] = table[ids[r],:] + pos[pos_ids ? pos_ids[r] : pos_offset + (r % period), :]. */
 int acai_embed_tokens(const int64_t* ids, int32_t rows, const float* table, const float* pos,

@@ -239,3 +239,55 @@ def test_attn_varlen_tcgen05_cross():
     y = ops.attn_varlen(q, kv[:, :H * d], kv[:, H * d:], pq.cu, pk.cu, pq.max_len, H, d)
     ref = ref_varlen(q.float(), kv[:, :H * d].float().contiguous(), kv[:, H * d:].float().contiguous(), lq, lk, H, d, False)
     close(y, ref, 2e-2, 2e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_decode_attn_paged_self_and_cross(dtype):
+    """acai_decode_attn_paged: paged self cache with append driven by a device step counter, and the packed memory
+    cache with per-sequence lengths; vs fp32 math on the same (rounded) values."""
+    B, H, d, max_len = 3, 4, 64, 700
+    D = H * d
+    pps = (max_len + 63) // 64
+    g = torch.Generator().manual_seed(0)
+    perm = torch.randperm(B * pps, generator=g).int().view(B, pps).to(DEV)      # scattered pages
+    pool = torch.zeros(B * pps * 64, 2 * D, dtype=dtype, device=DEV)
+    ws = ops.decode_workspace(B, H, max_len, DEV)
+    step = torch.ones(1, dtype=torch.int32, device=DEV)
+    hist = []
+    tol = (1e-4, 2e-5) if dtype == torch.float32 else (2e-2, 2e-2)
+    for t in list(range(1, 6)) + [255, 256, 257, 600]:
+        # fill history up to t-1 cached tokens directly, then run one step that appends token t-1
+        while len(hist) < t - 1:
+            row = rnd(B, 2 * D, seed=100 + len(hist)).to(dtype)
+            pos = len(hist)
+            rows = perm[:, pos // 64].long() * 64 + pos % 64
+            pool[rows] = row
+            hist.append(row)
+        step.fill_(t)
+        qkv = rnd(B, 3 * D, seed=500 + t).to(dtype)
+        out = ops.decode_attn_paged(qkv[:, :D], qkv[:, D:], pool, H, d, max_len, ws, torch.float32,
+                                    page_table=perm, step=step, len_offset=-1)
+        hist.append(qkv[:, D:].clone())
+        kv = torch.stack(hist, dim=1).float()                                        # (B, t, 2D)
+        k, v = kv[..., :D].view(B, t, H, d).transpose(1, 2), kv[..., D:].view(B, t, H, d).transpose(1, 2)
+        s = (qkv[:, :D].float().view(B, H, 1, d).double() @ k.double().transpose(-1, -2)) / math.sqrt(d)
+        ref = (torch.softmax(s, -1) @ v.double()).transpose(1, 2).reshape(B, D).float()
+        close(out, ref, *tol)
+        rows = perm[:, (t - 1) // 64].long() * 64 + (t - 1) % 64
+        assert torch.equal(pool[rows], qkv[:, D:])                                   # the append landed in its page
+    # packed memory cache, ragged lengths, no append
+    lens = [300, 1, 257]
+    mp = Packed(lens, DEV)
+    mem = rnd(sum(lens), 2 * D, seed=9).to(dtype)
+    q = rnd(B, D, seed=10).to(dtype)
+    wsc = ops.decode_workspace(B, H, max(lens), DEV)
+    out = ops.decode_attn_paged(q, None, mem, H, d, max(lens), wsc, torch.float32, seq_start=mp.cu[:-1].contiguous(),
+                                kv_lens=torch.tensor(lens, dtype=torch.int32, device=DEV))
+    o = 0
+    for b, L in enumerate(lens):
+        kv = mem[o:o + L].float()
+        k, v = kv[:, :D].view(L, H, d).transpose(0, 1), kv[:, D:].view(L, H, d).transpose(0, 1)
+        s = (q[b].float().view(H, 1, d).double() @ k.double().transpose(-1, -2)) / math.sqrt(d)
+        ref = (torch.softmax(s, -1) @ v.double()).reshape(D).float()
+        close(out[b], ref, *tol)
+        o += L

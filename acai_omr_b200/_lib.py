@@ -34,7 +34,8 @@ SIGNATURES = {
     "acai_version": [],
     "acai_last_error": [],
     "acai_device_ok": [],
-    "acai_patch_embed_fwd": [_p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _i32, _i32, _p],
+    "acai_patch_embed_workspace_bytes": [_i32, _i32, _i32, _i32],
+    "acai_patch_embed_fwd": [_p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _i32, _i32, _p, _sz, _p],
     "acai_linear_fwd": [_p, _i32, _i64, _p, _i32, _i64, _p, _p, _i32, _i64, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p],
     "acai_layernorm_fwd": [_p, _i32, _p, _i32, _p, _p, _f32, _p, _i32, _p, _i32, _i32, _i32, _p],
     "acai_attn_varlen_fwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32,
@@ -76,7 +77,7 @@ def load():
         fn = getattr(lib, name)
         fn.argtypes = argtypes
         fn.restype = (C.c_char_p if name == "acai_last_error" else
-                      C.c_size_t if name == "acai_decode_workspace_bytes" else C.c_int)
+                      C.c_size_t if name.endswith("_workspace_bytes") else C.c_int)
     _lib = lib
     return lib
 

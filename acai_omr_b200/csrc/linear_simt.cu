@@ -229,24 +229,102 @@ int linear_simt(const void* a, int a_dt, int64_t lda, const void* w, int w_dt, i
 
 }  // namespace acai
 
+namespace acai {
+
+int linear_tcgen05_ex(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res,
+                      int res_dt, int64_t ldr, const int32_t* res_rows, void* out, int out_dt, int64_t ldo, int M, int N,
+                      int K, int act, cudaStream_t st);
+
+// im2col for the tensor-core patch embedding: token t -> its C*P*P pixels as one bf16 row (feature order channel,
+// row-in-patch, col-in-patch = nn.Unfold's), plus the row of the position grid it will add.  One thread moves 8
+// consecutive pixels of one patch row (2 x 16-byte loads when the image rows allow it, one 16-byte store); a warp
+// covers whole 32/64-byte pixel runs, so every sector fetched is used.
+__global__ void __launch_bounds__(256)
+patch_im2col_kernel(const acai_image_desc* __restrict__ images, int num_images, const int32_t* __restrict__ cu,
+                    const int32_t* __restrict__ patch_index, int total, int P, int C, int K, int pe_w,
+                    __nv_bfloat16* __restrict__ patches, int32_t* __restrict__ pe_rows) {
+  const int pieces = K / 8;                                    // 16-byte output pieces per token
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (int64_t)total * pieces) return;
+  const int tok = (int)(gid / pieces), piece = (int)(gid - (int64_t)tok * pieces);
+  const int b = find_sequence(cu, num_images, tok);
+  const acai_image_desc d = images[b];
+  const int pid = patch_index ? patch_index[tok] : tok - cu[b];
+  const int prow = pid / d.wp, pcol = pid - prow * d.wp;
+  if (piece == 0) pe_rows[tok] = prow * pe_w + pcol;
+  const int k = piece * 8, pp = P * P;
+  const int ch = k / pp, rem = k - ch * pp, i = rem / P, j = rem - i * P;      // P % 8 == 0: the 8 pixels share a row
+  const float* src = d.pixels + (int64_t)ch * d.height * d.width + (int64_t)(prow * P + i) * d.width + pcol * P + j;
+  float v[8];
+  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src)), c = __ldg(reinterpret_cast<const float4*>(src) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = __ldg(src + e);
+  }
+  uint4 pk; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+  for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+  *reinterpret_cast<uint4*>(patches + (int64_t)tok * K + k) = pk;
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = __float2bfloat16_rn(in[i]);
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+}  // namespace acai
+
 using namespace acai;
+
+extern "C" size_t acai_patch_embed_workspace_bytes(int32_t total_tokens, int32_t patch_size, int32_t channels,
+                                                   int32_t embed_dim) {
+  const size_t K = (size_t)channels * patch_size * patch_size;
+  return align256((size_t)total_tokens * K * 2) + align256((size_t)total_tokens * 4) + align256((size_t)embed_dim * K * 2);
+}
 
 extern "C" int acai_patch_embed_fwd(const acai_image_desc* images, int32_t num_images, const int32_t* cu_seqlens,
                                     const int32_t* patch_index, int32_t total_tokens, int32_t patch_size,
                                     int32_t channels, const float* weight, const float* bias,
                                     const float* pos_embedding, int32_t pe_h, int32_t pe_w, int32_t interpolate,
-                                    void* out, int32_t out_dtype, int32_t embed_dim, void* stream) {
+                                    void* out, int32_t out_dtype, int32_t embed_dim, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
   ACAI_CHECK_ARG(images && cu_seqlens && weight && pos_embedding && out, "acai_patch_embed_fwd: null pointer");
   ACAI_CHECK_ARG(num_images > 0 && total_tokens >= 0 && patch_size > 0 && channels > 0 && embed_dim > 0,
                  "acai_patch_embed_fwd: bad sizes");
   ACAI_CHECK_ARG(dtype_valid(out_dtype), "acai_patch_embed_fwd: bad out dtype %d", out_dtype);
   if (total_tokens == 0) return ACAI_OK;
   const int K = channels * patch_size * patch_size;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (workspace && out_dtype == ACAI_BF16 && !interpolate && K % 64 == 0 && patch_size % 8 == 0 && embed_dim % 8 == 0 &&
+      !((uintptr_t)workspace & 255) && !((uintptr_t)out & 15) && !((uintptr_t)pos_embedding & 15) &&
+      workspace_bytes >= acai_patch_embed_workspace_bytes(total_tokens, patch_size, channels, embed_dim)) {
+    char* ws = reinterpret_cast<char*>(workspace);
+    __nv_bfloat16* patches = reinterpret_cast<__nv_bfloat16*>(ws);
+    int32_t* pe_rows = reinterpret_cast<int32_t*>(ws + align256((size_t)total_tokens * K * 2));
+    __nv_bfloat16* wb = reinterpret_cast<__nv_bfloat16*>(ws + align256((size_t)total_tokens * K * 2) + align256((size_t)total_tokens * 4));
+    const int64_t n_pieces = (int64_t)total_tokens * (K / 8);
+    patch_im2col_kernel<<<(unsigned)((n_pieces + 255) / 256), 256, 0, st>>>(images, num_images, cu_seqlens, patch_index,
+                                                                          total_tokens, patch_size, channels, K, pe_w,
+                                                                          patches, pe_rows);
+    int rc = launch_status("patch_im2col");
+    if (rc) return rc;
+    const int64_t nw = (int64_t)embed_dim * K;
+    cast_f32_bf16_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, st>>>(weight, wb, nw);
+    rc = launch_status("cast_f32_bf16");
+    if (rc) return rc;
+    rc = linear_tcgen05_ex(patches, K, wb, K, bias, pos_embedding, ACAI_F32, embed_dim, pe_rows, out, ACAI_BF16, embed_dim,
+                           total_tokens, embed_dim, K, ACAI_ACT_NONE, st);
+    if (rc != ACAI_ERR_UNSUPPORTED) return rc;
+  }
   PatchCtx c{images, num_images, cu_seqlens, patch_index, total_tokens, patch_size, channels, K,
              bias, pos_embedding, pe_h, pe_w, interpolate, out, out_dtype, embed_dim};
   PatchA al{c}; PatchEpi ep{c};
   dim3 grid((total_tokens + BM - 1) / BM, (embed_dim + BN - 1) / BN);
-  gemm_nt_simt<PatchA, PatchEpi, true><<<grid, 256, 0, (cudaStream_t)stream>>>(
+  gemm_nt_simt<PatchA, PatchEpi, true><<<grid, 256, 0, st>>>(
       al, weight, ACAI_F32, (int64_t)K, ep, total_tokens, embed_dim, K);
   return launch_status("patch_embed");
 }

@@ -67,10 +67,11 @@ class Encoder(nn.Module):
         """K1: ragged images -> (packed rows [sum L, E], Packed).  `keep`: optional (lens, patch_index) for MAE."""
         imgs = self._image_list(x)
         P = self.patch_size
-        lens = []
+        lens, oversize = [], False
         for t in imgs:
             h_p, w_p = t.shape[-2] // P, t.shape[-1] // P
             self._grid_check(h_p, w_p)
+            oversize |= h_p > self.pe_max_height or w_p > self.pe_max_width
             lens.append(h_p * w_p)
         dev = self.pos_embedding.device
         patch_index = None
@@ -79,7 +80,7 @@ class Encoder(nn.Module):
         pk = Packed(lens, dev)
         descs = ops.make_image_descs(imgs, P, dev)
         out = ops.patch_embed(imgs, descs, pk.cu, pk.total, P, imgs[0].shape[0], self.projection.weight,
-                              self.projection.bias, self.pos_embedding, self._interpolate_pe,
+                              self.projection.bias, self.pos_embedding, self._interpolate_pe and oversize,
                               out_dtype or compute_dtype(), patch_index=patch_index)
         return out, pk
 

@@ -201,9 +201,18 @@ def patch_embed(images, descs_dev, cu_seqlens, total_tokens, patch_size, channel
     out = torch.empty((total_tokens, E), dtype=out_dtype, device=weight.device)
     w, b, pe = _f32c(weight), _f32c(bias), _f32c(pos_embedding)
     lib = _lib.load()
+    ws = None
+    if out_dtype == torch.bfloat16 and not interpolate:     # tensor-core path: im2col + tcgen05 GEMM
+        ws = torch.empty(lib.acai_patch_embed_workspace_bytes(total_tokens, patch_size, channels, E), dtype=torch.uint8,
+                         device=weight.device)
+    K = channels * patch_size * patch_size
     _call("acai_patch_embed_fwd", lib.acai_patch_embed_fwd, _p(descs_dev), len(images), _p(cu_seqlens), _p(patch_index), total_tokens,
                                         patch_size, channels, _p(w), _p(b), _p(pe), pe.shape[0], pe.shape[1],
-                                        1 if interpolate else 0, _p(out), _DT[out_dtype], E, _stream())
+                                        1 if interpolate else 0, _p(out), _DT[out_dtype], E, _p(ws),
+                                        ws.numel() if ws is not None else 0, _stream(),
+          flops=2.0 * total_tokens * K * E, nbytes=float(total_tokens) * (4 * K + 4 * E + out.element_size() * E))
+    if ws is not None:
+        _bump(2)  # im2col + weight cast + GEMM
     return out
 
 

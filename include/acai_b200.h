@@ -52,6 +52,11 @@ typedef struct {
   int32_t hp, wp;      /* patches per column / row = H / P, W / P                     */
 } acai_image_desc;
 
+/* `workspace` (device, >= acai_patch_embed_workspace_bytes, or NULL): with a workspace, bf16 output, interpolate == 0
+ * and C*P*P % 64 == 0 the projection runs on the tensor cores: an im2col pass writes the patches as bf16 rows plus each
+ * token's position-grid row, then the tcgen05 GEMM adds bias and the gathered position embedding in its epilogue.
+ * Otherwise (fp32 output = the token-exact mode, interpolated grids, no workspace) one fp32 SIMT kernel does it all. */
+size_t acai_patch_embed_workspace_bytes(int32_t total_tokens, int32_t patch_size, int32_t channels, int32_t embed_dim);
 int acai_patch_embed_fwd(const acai_image_desc* images, /* device array [num_images]             */
                          int32_t num_images,
                          const int32_t* cu_seqlens,      /* [num_images+1] packed token offsets   */
@@ -62,7 +67,8 @@ int acai_patch_embed_fwd(const acai_image_desc* images, /* device array [num_ima
                          const float* bias,              /* [E] or NULL                            */
                          const float* pos_embedding,     /* [pe_h, pe_w, E] fp32                   */
                          int32_t pe_h, int32_t pe_w, int32_t interpolate,
-                         void* out, int32_t out_dtype, int32_t embed_dim, void* stream);
+                         void* out, int32_t out_dtype, int32_t embed_dim,
+                         void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- K2: dense projections ----------------------------------------------------------------
  * out[M,N] = act(a[M,K] . w[N,K]^T + bias) + residual.   Replaces every nn.Linear / F.linear on

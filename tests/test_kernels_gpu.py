@@ -200,6 +200,33 @@ def test_patch_embed_ragged(out_dtype):
     close(y2.cpu(), ref2, 1e-5, 1e-5)
 
 
+def test_patch_embed_tensor_core_path():
+    """bf16 output + no interpolation -> im2col + tcgen05 GEMM with the position grid gathered in the epilogue."""
+    P, E = 16, 192
+    shapes = [(32, 64), (48, 160), (16, 16), (35, 50), (64, 33)]   # the last two have unaligned rows / dropped borders
+    g = torch.Generator().manual_seed(5)
+    imgs = [torch.rand(1, h, w, generator=g).to(DEV) for h, w in shapes]
+    sd = {"projection.weight": rnd(E, P * P, seed=1, scale=0.06), "projection.bias": rnd(E, seed=2),
+          "pos_embedding": rnd(5, 12, E, seed=3)}
+    lens = [(h // P) * (w // P) for h, w in shapes]
+    pk = Packed(lens, DEV)
+    descs = ops.make_image_descs(imgs, P, DEV)
+    n0 = ops.launch_count()
+    y = ops.patch_embed(imgs, descs, pk.cu, pk.total, P, 1, sd["projection.weight"], sd["projection.bias"],
+                        sd["pos_embedding"], False, torch.bfloat16)
+    assert ops.launch_count() - n0 == 3
+    cpu_sd = {k: v.cpu() for k, v in sd.items()}
+    emb, mask = O.encoder_batchify([i.cpu() for i in imgs], cpu_sd, P, 5, 12)
+    close(y.float().cpu(), emb[~mask], 2e-2, 2e-2)
+    keep = [torch.tensor([7, 0, 5]), torch.tensor([20, 1, 29]), torch.tensor([0]), torch.tensor([0, 5, 4]), torch.tensor([2, 7])]
+    pk2 = Packed([len(k) for k in keep], DEV)
+    idx = torch.cat(keep).int().to(DEV)
+    y2 = ops.patch_embed(imgs, descs, pk2.cu, pk2.total, P, 1, sd["projection.weight"], sd["projection.bias"],
+                         sd["pos_embedding"], False, torch.bfloat16, patch_index=idx)
+    ref2 = torch.cat([emb[i, k] for i, k in enumerate(keep)])
+    close(y2.float().cpu(), ref2, 2e-2, 2e-2)
+
+
 def test_patch_embed_interpolated_pe():
     P, E = 2, 8
     pe = rnd(4, 6, E, seed=1)

@@ -1,13 +1,21 @@
 // K3 (tensor-core path): packed variable-length flash attention for head_dim 64, bf16 operands.
 //
-// One CTA = one (sequence, head, 128-query block); 2 CTAs are resident per SM so that one CTA's softmax
-// overlaps the other's MMAs.  Per 128-key block j:
-//     S_j = Q K_j^T            tcgen05.mma 128x128x16 x4, accumulator in TMEM (128 columns)
-//     P_j = exp2(S_j - m)      4 softmax warps, thread = query row: tcgen05.ld -> registers -> bf16 -> swizzled smem
-//     O_j = P_j V_j            tcgen05.mma 128x64x16 x8 (V is the MN-major B operand), TMEM (64 columns)
-//     acc = acc * corr + O_j   in registers (fp32), so TMEM never needs a read-modify-write
-// Q/K/V tiles come in by TMA straight out of the fused [T, 3*H*64] QKV buffer (or separate Q and KV buffers for
-// cross attention); ragged sequence ends are masked in the softmax, never padded.
+// One CTA = one (sequence, head, 128-query tile); two CTAs are resident per SM (256 of the SM's 512 TMEM columns
+// each), so one CTA's prologue / output store overlaps the other's steady state and the MUFU pipe - the real bound
+// here: 64 exp2 per row per 64-key block against 256 MMA cycles - always has a softmax warp with work.
+// Per 64-key block j:
+//     S_j = Q K_j^T            tcgen05.mma 128x64x16 x4 (SS), fp32 accumulator in TMEM, DOUBLE-buffered (2 x 64 columns):
+//                              S_{j+1} is already finished when the softmax of block j ends, no MMA round trip in between
+//     P_j = exp2(S_j - m)      4 softmax warps, thread = query row: one tcgen05.ld pass (64 values in registers),
+//                              bf16 pairs written back OVER S_j with tcgen05.st (32 columns) - P never touches smem
+//     O  += P_j V_j            tcgen05.mma 128x64x16 x4 with A = P from TMEM (TS), B = V MN-major from smem;
+//                              O (64 columns) stays in TMEM for the whole sequence
+// Online-softmax rescaling of O is lazy: m is only advanced (and O multiplied by 2^(m_old-m_new) through a
+// tcgen05.ld/st round trip) when some row of the warp saw its maximum grow by more than 2^8; otherwise the stale
+// maximum keeps being used, which is exact after the final division by l.  The rescale needs O to hold P_{j-1} V_{j-1}:
+// the issuer commits every PV to an `o_step` barrier that the softmax warps consult only on that (rare) path.
+// Q/K/V tiles arrive by TMA straight out of the fused [T, 3*H*64] QKV buffer (or separate Q and KV buffers for cross
+// attention); ragged sequence ends are masked in the softmax, never padded.
 //   warps 0-3: softmax + output     warp 4: TMA producer (+TMEM alloc)     warp 5: MMA issuer
 #include "common.cuh"
 #include "ptx_sm100.cuh"
@@ -18,12 +26,14 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t 
                      uint32_t box_cols);
 
 namespace fa {
-constexpr int BQ = 128, BKV = 128, D = 64;
+constexpr int BQ = 128, BKV = 64, D = 64, KV_STAGES = 4;
 constexpr int THREADS = 192;
-constexpr uint32_t TILE = 128 * 64 * 2;           // 16 KB: one 128-row x 64-col bf16 tile
-constexpr uint32_t OFF_Q = 0, OFF_K = TILE, OFF_V = 3 * TILE, OFF_PHI = 5 * TILE, OFF_BAR = 6 * TILE;
-constexpr size_t SMEM = 6 * TILE + 1024 + 128;
-constexpr uint32_t TMEM_COLS = 256;               // S: 128 columns, O: 64 columns
+constexpr uint32_t QTILE = BQ * D * 2;            // 16 KB
+constexpr uint32_t KTILE = BKV * D * 2;           // 8 KB
+constexpr uint32_t OFF_Q = 0, OFF_K = QTILE, OFF_V = OFF_K + KV_STAGES * KTILE, OFF_BAR = OFF_V + KV_STAGES * KTILE;
+constexpr size_t SMEM = OFF_BAR + 256;
+constexpr uint32_t TMEM_COLS = 256;               // S[0] 0..63, S[1] 64..127, O 128..191
+constexpr float RESCALE_LOG2 = 8.0f;
 }  // namespace fa
 using namespace fa;
 
@@ -36,16 +46,16 @@ struct AttnParams {
 __global__ void __launch_bounds__(THREADS, 2)
 attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
-  uint64_t* q_full = bars;            // 1
-  uint64_t* kv_full = bars + 1;       // 2
-  uint64_t* kv_empty = bars + 3;      // 2
-  uint64_t* s_full = bars + 5;
-  uint64_t* p_full = bars + 6;
-  uint64_t* o_full = bars + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* q_full = bars;                          // 1
+  uint64_t* kv_full = bars + 1;                     // KV_STAGES
+  uint64_t* kv_empty = kv_full + KV_STAGES;         // KV_STAGES
+  uint64_t* s_full = kv_empty + KV_STAGES;          // 2 (per S buffer)
+  uint64_t* p_full = s_full + 2;                    // 2
+  uint64_t* o_step = p_full + 2;                    // 1: one phase per finished PV (consulted on the rescale path)
+  uint64_t* o_full = o_step + 1;                    // 1: the last PV has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z, h = blockIdx.y, qb = blockIdx.x;
@@ -58,8 +68,9 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
 
   if (warp == 5 && lane == 0) {
     ptx::mbar_init(q_full, 1);
-    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&kv_full[s], 1); ptx::mbar_init(&kv_empty[s], 1); }
-    ptx::mbar_init(s_full, 1); ptx::mbar_init(p_full, 128); ptx::mbar_init(o_full, 1);
+    for (int s = 0; s < KV_STAGES; ++s) { ptx::mbar_init(&kv_full[s], 1); ptx::mbar_init(&kv_empty[s], 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 128); }
+    ptx::mbar_init(o_step, 1); ptx::mbar_init(o_full, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 4) {
@@ -70,19 +81,19 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 128;
 
   if (warp == 4) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && n_kv > 0) {
-      ptx::mbar_arrive_expect_tx(q_full, TILE);
+      ptx::mbar_arrive_expect_tx(q_full, QTILE);
       ptx::tma_load_2d(smem + OFF_Q, &tma_q, q_full, h * D, q0 + qb * BQ);
+      int s = 0; uint32_t ph = 0;
       for (int j = 0; j < n_kv; ++j) {
-        const int s = j & 1;
-        ptx::mbar_wait(&kv_empty[s], ((j >> 1) & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(&kv_full[s], 2 * TILE);
-        ptx::tma_load_2d(smem + OFF_K + s * TILE, &tma_k, &kv_full[s], h * D, k0 + j * BKV);
-        ptx::tma_load_2d(smem + OFF_V + s * TILE, &tma_v, &kv_full[s], h * D, k0 + j * BKV);
+        ptx::mbar_wait(&kv_empty[s], ph ^ 1);
+        ptx::mbar_arrive_expect_tx(&kv_full[s], 2 * KTILE);
+        ptx::tma_load_2d(smem + OFF_K + s * KTILE, &tma_k, &kv_full[s], h * D, k0 + j * BKV);
+        ptx::tma_load_2d(smem + OFF_V + s * KTILE, &tma_v, &kv_full[s], h * D, k0 + j * BKV);
+        if (++s == KV_STAGES) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 5) {
@@ -91,162 +102,137 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BQ, BKV);
       constexpr uint32_t IDESC_O = ptx::idesc_bf16_f32(BQ, D, false, true);   // B = V is MN-major
       const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_Q), 1024);
-      const uint64_t phidesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_PHI), 1024);
-      auto issue_s = [&](int j) {
-        const int s = j & 1;
-        ptx::mbar_wait(&kv_full[s], (j >> 1) & 1);
+      auto issue_s = [&](int j) {                    // S_j into buffer j & 1; K_j sits in stage j % KV_STAGES
+        const int st = j % KV_STAGES;
+        ptx::mbar_wait(&kv_full[st], (j / KV_STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + s * TILE), 1024);
+        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024);
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_s, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
-        ptx::umma_commit(s_full);
+        for (int k = 0; k < D / 16; ++k)
+          ptx::umma_f16_ss(tmem_base + (j & 1) * 64, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+        ptx::umma_commit(&s_full[j & 1]);
       };
       ptx::mbar_wait(q_full, 0);
       issue_s(0);
+      if (n_kv > 1) issue_s(1);
       for (int j = 0; j < n_kv; ++j) {
-        const int s = j & 1;
-        ptx::mbar_wait(p_full, j & 1);
+        const int st = j % KV_STAGES;
+        ptx::mbar_wait(&p_full[j & 1], (j >> 1) & 1);
         ptx::tc_fence_after();
-        const uint64_t plodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + s * TILE), 1024);  // P[:, 0:64] aliases K_j
-        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + s * TILE), 1024);
+        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + st * KTILE), 1024);
 #pragma unroll
-        for (int kk = 0; kk < BKV / 16; ++kk) {
-          const uint64_t adesc = (kk < 4 ? plodesc : phidesc) + 2 * (kk & 3);
-          ptx::umma_f16_ss(tmem_o, adesc, vdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_O, kk != 0);
-        }
-        ptx::umma_commit(o_full);
-        ptx::umma_commit(&kv_empty[s]);
-        if (j + 1 < n_kv) issue_s(j + 1);
+        for (int kk = 0; kk < BKV / 16; ++kk)       // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
+          ptx::umma_f16_ts(tmem_base + 128, tmem_base + (j & 1) * 64 + kk * 8, vdesc + (uint64_t)kk * (16 * 128 >> 4),
+                           IDESC_O, (j | kk) != 0);
+        ptx::umma_commit(&kv_empty[st]);
+        ptx::umma_commit(o_step);
+        if (j == n_kv - 1) ptx::umma_commit(o_full);
+        if (j + 2 < n_kv) issue_s(j + 2);            // overwrites P_j: tcgen05 ops execute in issue order
       }
     }
   } else {
-    // ------------------------------------------------------------------ softmax + output (thread = query row)
+    // ------------------------------------------------------------------ softmax warps (thread = query row)
     const int r = warp * 32 + lane;
     const int qi = qb * BQ + r;
     const bool valid = qi < lq;
-    const int my_end = p.causal ? min(lk, qi + shift + 1) : lk;     // exclusive key bound of this row
+    const int my_end = p.causal ? max(0, min(lk, qi + shift + 1)) : lk;     // exclusive key bound of this row
+    const int warp_min_end = __shfl_sync(0xffffffffu, my_end, 0);          // rows ascend inside a warp
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
-    float acc[D];
-#pragma unroll
-    for (int e = 0; e < D; ++e) acc[e] = 0.0f;
-    float m = -INFINITY, l = 0.0f;
+    const uint32_t tmem_o = tmem_base + lane_addr + 128;
     const float scale_log2 = p.scale_log2;
-    const uint32_t row_off = (uint32_t)(r >> 3) * 1024 + (uint32_t)(r & 7) * 128;
-    const uint32_t sw = (uint32_t)(r & 7);
+    float m = -INFINITY, l = 0.0f;
 
     for (int j = 0; j < n_kv; ++j) {
-      if (j > 0) {                      // fold O_{j-1} (scale m_{j-1}) into the running accumulator
-        ptx::mbar_wait(o_full, (j - 1) & 1);
-        ptx::tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t o[32];
-          ptx::tmem_ld_32x32(tmem_o + lane_addr + c * 32, o);
-          ptx::tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) acc[c * 32 + i] += __uint_as_float(o[i]);
-        }
-      }
-      ptx::mbar_wait(s_full, j & 1);
+      const uint32_t tmem_s = tmem_base + lane_addr + (j & 1) * 64;
+      ptx::mbar_wait(&s_full[j & 1], (j >> 1) & 1);
       ptx::tc_fence_after();
+      uint32_t s[64];
+      ptx::tmem_ld_32x32(tmem_s, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+      ptx::tmem_ld_32x32(tmem_s + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
+      ptx::tmem_ld_wait();
       const int kbase = j * BKV;
-      const bool full = kbase + BKV <= my_end;      // no key of this block is masked for this row
-      float rmax = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; c += 2) {
-        uint32_t s0[32], s1[32];
-        ptx::tmem_ld_32x32(tmem_s + lane_addr + c * 32, s0);
-        ptx::tmem_ld_32x32(tmem_s + lane_addr + c * 32 + 32, s1);
-        ptx::tmem_ld_wait();
-        if (full) {
+      if (kbase + BKV > warp_min_end) {             // ragged end / causal diagonal: mask keys >= my_end
 #pragma unroll
-          for (int i = 0; i < 32; ++i) rmax = fmaxf(rmax, fmaxf(__uint_as_float(s0[i]), __uint_as_float(s1[i])));
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            if (kbase + c * 32 + i < my_end) rmax = fmaxf(rmax, __uint_as_float(s0[i]));
-            if (kbase + c * 32 + 32 + i < my_end) rmax = fmaxf(rmax, __uint_as_float(s1[i]));
-          }
-        }
+        for (int i = 0; i < 64; ++i) if (kbase + i >= my_end) s[i] = 0xff800000u;   // -inf
       }
-      const float m_new = fmaxf(m, rmax);
-      const float m_use = m_new == -INFINITY ? 0.0f : m_new;
-      const float corr = fast_exp2((m - m_use) * scale_log2);        // m = -inf -> 0
-      l *= corr;
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-      for (int e = 0; e < D; ++e) acc[e] *= corr;
-      const float moff = m_use * scale_log2;
-      uint8_t* const p_lo = smem + OFF_K + (j & 1) * TILE;
-      uint8_t* const p_hi = smem + OFF_PHI;
-      float lsum0 = 0.0f, lsum1 = 0.0f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t s[32];
-        ptx::tmem_ld_32x32(tmem_s + lane_addr + c * 32, s);
-        ptx::tmem_ld_wait();
-        uint32_t pk[16];
-        if (full) {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff));
-            const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff));
-            lsum0 += p0; lsum1 += p1;
-            __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
-            pk[i] = *reinterpret_cast<uint32_t*>(&hh);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int kk = kbase + c * 32 + 2 * i;
-            const float p0 = kk < my_end ? fast_exp2(fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff)) : 0.0f;
-            const float p1 = kk + 1 < my_end ? fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff)) : 0.0f;
-            lsum0 += p0; lsum1 += p1;
-            __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
-            pk[i] = *reinterpret_cast<uint32_t*>(&hh);
-          }
-        }
-        uint8_t* base = (c < 2 ? p_lo : p_hi) + row_off;
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          const uint32_t chunk = (uint32_t)((c & 1) * 4 + q4);
-          *reinterpret_cast<uint4*>(base + ((chunk ^ sw) << 4)) = make_uint4(pk[4 * q4], pk[4 * q4 + 1], pk[4 * q4 + 2], pk[4 * q4 + 3]);
-        }
+      for (int i = 0; i < 64; i += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(s[i])); mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(s[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
       }
-      l += lsum0 + lsum1;
-      m = m_new;
-      ptx::fence_proxy_async_smem();   // make the generic-proxy smem writes visible to the tensor core
+      const float m_new = fmaxf(m, fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)));
+      const bool grow = (m_new - m) * scale_log2 > RESCALE_LOG2 || (m == -INFINITY && m_new > -INFINITY);
+      if (__any_sync(0xffffffffu, grow)) {          // advance the reference maximum (warp-uniform: TMEM ops are collective)
+        const float m_use = m_new == -INFINITY ? 0.0f : m_new;
+        const float corr = m == -INFINITY ? 0.0f : fast_exp2((m - m_use) * scale_log2);
+        l *= corr;
+        if (j > 0) {
+          ptx::mbar_wait(o_step, (j - 1) & 1);      // O holds P_{j-1} V_{j-1}
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld_32x32(tmem_o + c * 32, o);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+            ptx::tmem_st_32x32(tmem_o + c * 32, o);
+          }
+        }
+        m = m_new;
+      }
+      const float moff = (m == -INFINITY ? 0.0f : m) * scale_log2;
+      float l0 = 0.0f, l1 = 0.0f;
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff));
+        const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff));
+        l0 += p0; l1 += p1;
+        const __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+        pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+      }
+      l += l0 + l1;
+      ptx::tmem_st_32x32(tmem_s, pk);
+      ptx::tmem_st_wait();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(p_full);
+      ptx::mbar_arrive(&p_full[j & 1]);
     }
     if (n_kv > 0) {
-      ptx::mbar_wait(o_full, (n_kv - 1) & 1);
+      ptx::mbar_wait(o_full, 0);
       ptx::tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t o[32];
-        ptx::tmem_ld_32x32(tmem_o + lane_addr + c * 32, o);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc[c * 32 + i] += __uint_as_float(o[i]);
-      }
     }
-    if (valid) {
-      const float inv = l > 0.0f ? 1.0f / l : 0.0f;
-      const int64_t off = (int64_t)(q0 + qi) * p.o_stride + (int64_t)h * D;
-      if (p.out_dt == ACAI_BF16) {
-        uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
+    const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+    const int64_t off = (int64_t)(q0 + qi) * p.o_stride + (int64_t)h * D;
 #pragma unroll
-        for (int q4 = 0; q4 < 8; ++q4) {
-          uint4 v4; __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&v4);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) hh[i] = __floats2bfloat162_rn(acc[q4 * 8 + 2 * i] * inv, acc[q4 * 8 + 2 * i + 1] * inv);
-          op[q4] = v4;
-        }
+    for (int c = 0; c < 2; ++c) {
+      uint32_t o[32];
+      if (n_kv > 0) {
+        ptx::tmem_ld_32x32(tmem_o + c * 32, o);
+        ptx::tmem_ld_wait();
       } else {
-        float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off);
 #pragma unroll
-        for (int q4 = 0; q4 < 16; ++q4)
-          op[q4] = make_float4(acc[4 * q4] * inv, acc[4 * q4 + 1] * inv, acc[4 * q4 + 2] * inv, acc[4 * q4 + 3] * inv);
+        for (int i = 0; i < 32; ++i) o[i] = 0u;
+      }
+      if (valid) {
+        if (p.out_dt == ACAI_BF16) {
+          uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off + c * 32);
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            uint4 v4; __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&v4);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              hh[i] = __floats2bfloat162_rn(__uint_as_float(o[q4 * 8 + 2 * i]) * inv, __uint_as_float(o[q4 * 8 + 2 * i + 1]) * inv);
+            op[q4] = v4;
+          }
+        } else {
+          float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off + c * 32);
+#pragma unroll
+          for (int q4 = 0; q4 < 8; ++q4)
+            op[q4] = make_float4(__uint_as_float(o[4 * q4]) * inv, __uint_as_float(o[4 * q4 + 1]) * inv,
+                                 __uint_as_float(o[4 * q4 + 2]) * inv, __uint_as_float(o[4 * q4 + 3]) * inv);
+        }
       }
     }
   }

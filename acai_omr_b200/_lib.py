@@ -45,7 +45,7 @@ SIGNATURES = {
     "acai_kv_append": [_p, _p, _i32, _i64, _i64, _i64, _i32, _p, _p, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p],
     "acai_decode_workspace_bytes": [_i32, _i32, _i32],
     "acai_decode_attn_paged": [_p, _i64, _p, _i64, _p, _i32, _p, _i32, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _f32, _p,
-                               _i32, _i64, _p, _sz, _p],
+                               _i32, _i64, _p, _sz, _i64, _p],
     "acai_decode_embed": [_p, _i64, _p, _i32, _p, _p, _p, _i32, _i32, _p],
     "acai_greedy_update": [_p, _i32, _i64, _i32, _i32, _p, _p, _i64, _p, _p, _i32, _p],
     "acai_advance_step": [_p, _p],

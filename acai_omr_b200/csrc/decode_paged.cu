@@ -160,12 +160,12 @@ decode_attn_paged_kernel(DecodeArgs a) {
 
 // Fold the per-chunk partials: out[b, h*64+e] = sum_c acc_c * 2^(m_c - M) / sum_c l_c * 2^(m_c - M).
 __global__ void __launch_bounds__(256)
-decode_combine_kernel(const float* __restrict__ ws, int max_chunks, int heads, const int32_t* __restrict__ kv_lens,
-                      const int32_t* __restrict__ step_ptr, int len_offset, int has_new, void* __restrict__ out,
-                      int out_dt, int64_t o_stride) {
+decode_combine_kernel(const float* __restrict__ ws, int max_chunks, int chunk_tokens, int heads,
+                      const int32_t* __restrict__ kv_lens, const int32_t* __restrict__ step_ptr, int len_offset,
+                      int has_new, void* __restrict__ out, int out_dt, int64_t o_stride) {
   const int b = blockIdx.x;
   const int len = (kv_lens ? kv_lens[b] : (*step_ptr + len_offset)) + has_new;
-  const int n_chunks = min(max_chunks, (len + DCH - 1) / DCH);
+  const int n_chunks = min(max_chunks, (len + chunk_tokens - 1) / chunk_tokens);
   for (int i = threadIdx.x; i < heads * DHD; i += blockDim.x) {
     const int h = i / DHD, e = i - h * DHD;
     const float* w = ws + ((int64_t)b * max_chunks * heads + h) * (DHD + 2);
@@ -228,8 +228,16 @@ __global__ void advance_step_kernel(int32_t* step_ptr) { *step_ptr += 1; }
 
 using namespace acai;
 
+namespace acai {
+int decode_attn_tma(const void* q, int64_t q_stride, const void* new_kv, int64_t new_kv_stride, void* kv_rows,
+                    int64_t kv_rows_total, const int32_t* page_table, int table_stride, const int32_t* seq_start,
+                    const int32_t* kv_lens, const int32_t* step_ptr, int len_offset, int max_kv_len, int batch, int heads,
+                    float scale, float* ws, int max_chunks, int chunk_tokens, cudaStream_t st);
+constexpr int DCH_MIN = 64;   // smallest split-KV chunk (small batches: more CTAs)
+}
+
 extern "C" size_t acai_decode_workspace_bytes(int32_t batch, int32_t heads, int32_t max_kv_len) {
-  const size_t chunks = (size_t)(max_kv_len + DCH - 1) / DCH;
+  const size_t chunks = (size_t)(max_kv_len + DCH_MIN - 1) / DCH_MIN;
   return (size_t)batch * chunks * heads * (DHD + 2) * sizeof(float);
 }
 
@@ -238,7 +246,7 @@ extern "C" int acai_decode_attn_paged(const void* q, int64_t q_stride, const voi
                                       const int32_t* seq_start, const int32_t* kv_lens, const int32_t* step_ptr,
                                       int32_t len_offset, int32_t max_kv_len, int32_t batch, int32_t heads,
                                       int32_t head_dim, float scale, void* out, int32_t out_dtype, int64_t o_stride,
-                                      void* workspace, size_t workspace_bytes, void* stream) {
+                                      void* workspace, size_t workspace_bytes, int64_t kv_rows_total, void* stream) {
   ACAI_CHECK_ARG(q && kv_rows && out && workspace, "acai_decode_attn_paged: null pointer");
   ACAI_CHECK_ARG((page_table != nullptr) != (seq_start != nullptr), "acai_decode_attn_paged: give a page table or seq_start");
   ACAI_CHECK_ARG((kv_lens != nullptr) != (step_ptr != nullptr), "acai_decode_attn_paged: give kv_lens or step_ptr");
@@ -248,18 +256,32 @@ extern "C" int acai_decode_attn_paged(const void* q, int64_t q_stride, const voi
   const int al = dtype == ACAI_BF16 ? 8 : 4;
   ACAI_CHECK_ARG(q_stride % al == 0 && (!new_kv || new_kv_stride % al == 0) && !((uintptr_t)q & 15) &&
                  !((uintptr_t)kv_rows & 15) && !((uintptr_t)new_kv & 15), "acai_decode_attn_paged: operands must be 16-byte aligned");
-  const int chunks = (max_kv_len + DCH - 1) / DCH;
   ACAI_CHECK_ARG(workspace_bytes >= acai_decode_workspace_bytes(batch, heads, max_kv_len), "acai_decode_attn_paged: workspace too small");
-  DecodeArgs a{q, q_stride, new_kv, new_kv_stride, kv_rows, page_table, table_stride, seq_start, kv_lens, step_ptr,
-               len_offset, heads, scale * 1.4426950408889634f, reinterpret_cast<float*>(workspace), chunks};
-  const int threads = 32 * (heads < 16 ? heads : 16);
   cudaStream_t st = (cudaStream_t)stream;
-  if (dtype == ACAI_BF16) decode_attn_paged_kernel<__nv_bfloat16><<<dim3(chunks, batch), threads, 0, st>>>(a);
-  else decode_attn_paged_kernel<float><<<dim3(chunks, batch), threads, 0, st>>>(a);
-  int rc = launch_status("decode_attn_paged");
-  if (rc) return rc;
-  decode_combine_kernel<<<batch, 256, 0, st>>>(a.ws, chunks, heads, kv_lens, step_ptr, len_offset, new_kv ? 1 : 0, out,
-                                               out_dtype, o_stride);
+  float* ws = reinterpret_cast<float*>(workspace);
+  int chunk_tokens = DCH, rc = ACAI_ERR_UNSUPPORTED;
+  if (dtype == ACAI_BF16 && kv_rows_total > 0) {
+    // TMA-streaming kernel; chunk length: the longest of 256/128/64 that still gives every SM a few CTAs
+    const int hg = (heads + 3) / 4;
+    int ct = 256;
+    while (ct > DCH_MIN && (int64_t)((max_kv_len + ct - 1) / ct) * hg * batch < 4 * num_sms()) ct >>= 1;
+    rc = decode_attn_tma(q, q_stride, new_kv, new_kv_stride, kv_rows, kv_rows_total, page_table, table_stride, seq_start,
+                         kv_lens, step_ptr, len_offset, max_kv_len, batch, heads, scale, ws, (max_kv_len + ct - 1) / ct, ct, st);
+    if (rc == ACAI_OK) chunk_tokens = ct;
+    else if (rc != ACAI_ERR_UNSUPPORTED) return rc;
+  }
+  const int chunks = (max_kv_len + chunk_tokens - 1) / chunk_tokens;
+  if (rc == ACAI_ERR_UNSUPPORTED) {
+    DecodeArgs a{q, q_stride, new_kv, new_kv_stride, kv_rows, page_table, table_stride, seq_start, kv_lens, step_ptr,
+                 len_offset, heads, scale * 1.4426950408889634f, ws, chunks};
+    const int threads = 32 * (heads < 16 ? heads : 16);
+    if (dtype == ACAI_BF16) decode_attn_paged_kernel<__nv_bfloat16><<<dim3(chunks, batch), threads, 0, st>>>(a);
+    else decode_attn_paged_kernel<float><<<dim3(chunks, batch), threads, 0, st>>>(a);
+    rc = launch_status("decode_attn_paged");
+    if (rc) return rc;
+  }
+  decode_combine_kernel<<<batch, 256, 0, st>>>(ws, chunks, chunk_tokens, heads, kv_lens, step_ptr, len_offset,
+                                               new_kv ? 1 : 0, out, out_dtype, o_stride);
   return launch_status("decode_combine");
 }
 

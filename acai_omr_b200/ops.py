@@ -332,7 +332,7 @@ def decode_attn_paged(q, new_kv, kv_rows, heads, head_dim, max_kv_len, workspace
           new_kv.stride(0) if new_kv is not None else 0, _p(kv_rows), _dt(kv_rows), _p(page_table),
           page_table.stride(0) if page_table is not None else 0, _p(seq_start), _p(kv_lens), _p(step), int(len_offset),
           int(max_kv_len), B, heads, head_dim, float(scale or 1.0 / math.sqrt(head_dim)), _p(out), _DT[out_dtype],
-          out.stride(0), _p(workspace), workspace.numel(), _stream(), nbytes=nbytes)
+          out.stride(0), _p(workspace), workspace.numel(), kv_rows.shape[0], _stream(), nbytes=nbytes)
     _bump()  # two kernels per call (split-KV pass + combine)
     return out
 

@@ -145,7 +145,10 @@ int acai_decode_attn_paged(const void* q, int64_t q_stride, const void* new_kv, 
                            const int32_t* seq_start, const int32_t* kv_lens, const int32_t* step_ptr,
                            int32_t len_offset, int32_t max_kv_len, int32_t batch, int32_t heads, int32_t head_dim,
                            float scale, void* out, int32_t out_dtype, int64_t o_stride,
-                           void* workspace, size_t workspace_bytes, void* stream);
+                           void* workspace, size_t workspace_bytes,
+                           int64_t kv_rows_total, /* rows allocated behind kv_rows (bounds the TMA descriptor of the
+                                                     bf16 streaming kernel); 0 = unknown -> register kernel */
+                           void* stream);
 
 /* Greedy-loop bookkeeping driven by the device-side step counter t = *step_ptr (models.py:575-583, 603-610):
  *   acai_decode_embed : out[b] = table[seqs[b, t-1]] + pos[t]   (time_step = t for the token at t-1, models.py:576)

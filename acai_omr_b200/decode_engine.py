@@ -53,6 +53,7 @@ class GreedyDecodeEngine:
         self.ws_self = ops.decode_workspace(B, self.H, max_len, device)
         self.ws_cross = None
         self.graph = None
+        self.launches_per_step = 0
 
     # ---- one decode step (what the graph captures) ------------------------------------------------------------
     def _step(self):
@@ -104,7 +105,9 @@ class GreedyDecodeEngine:
         """Run steps t = 1 .. max_len-1 (or until every row has emitted <eos>); returns raw (seqs, log_probs)."""
         if self.graph is None:
             self._reset()
+            n0 = ops.launch_count()
             self._step()                      # eager warm-up: bf16 weight copies, tensor maps, function attributes
+            self.launches_per_step = ops.launch_count() - n0
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             self._reset()

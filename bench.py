@@ -117,11 +117,18 @@ def run_ours(args, rank, world, device):
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
             return enc.encode_packed(imgs_dev)[0]
 
+    out_host = torch.empty((NUM_SYSTEMS, max(lens), 768), dtype=torch.float32).pin_memory()
+    mask_host = torch.empty((NUM_SYSTEMS, max(lens)), dtype=torch.bool).pin_memory()
+
     def step_e2e():
+        """The public module API (Encoder.forward: padded fp32 latent + mask) from pinned host images to pinned host results."""
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
             dev = [t.to(device, non_blocking=True) for t in imgs_host]
             out, mask = enc(dev)
-        return out.cpu(), mask.cpu()
+        out_host.copy_(out, non_blocking=True)
+        mask_host.copy_(mask, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return out_host, mask_host
 
     def barrier():
         if world > 1:
@@ -209,6 +216,97 @@ def run_ours(args, rank, world, device):
     return line
 
 
+# ------------------------------------------------------------------------------------------ decode leg (configs[2])
+DECODE_BATCH, DECODE_MAX_LEN = 256, 1024
+DEC_D, DEC_H, DEC_LAYERS, DEC_MLP, DEC_VOCAB = 1024, 16, 12, 4096, 227
+
+
+def decode_step_bytes(B, mem_lens, t):
+    """Algorithmic HBM bytes of decode step t: every weight once (bf16; cross-KV projections excluded, they
+    are precomputed), K and V of t self tokens + S_b memory tokens per sequence per layer, plus the appended row."""
+    per_layer_w = 3 * DEC_D * DEC_D + DEC_D * DEC_D + DEC_D * DEC_D + DEC_D * DEC_D + 2 * DEC_D * DEC_MLP
+    weights = 2 * (DEC_LAYERS * per_layer_w + DEC_VOCAB * DEC_D)
+    row = DEC_LAYERS * 2 * DEC_D * 2                       # 49 152 B: K and V of one position in all layers
+    return weights + row * (B * t + sum(mem_lens)) + row * B
+
+
+def run_decode(args, rank, world, device):
+    """Batched KV-cached greedy decode: 256 systems/GPU, encoder memory of the config-2 length mix, 1023 steps
+    (early stop disabled for timing), bf16 weights and caches; the step is one replayed CUDA graph."""
+    from acai_omr_b200 import decode_engine, ops, synth
+    from acai_omr_b200.layers import Packed
+    from acai_omr_b200.models import models as M
+    B, max_len = DECODE_BATCH, DECODE_MAX_LEN
+    torch.manual_seed(0)
+    dec = M.OMRDecoder(1536, M.default_vocab_path(), num_layers=DEC_LAYERS, hidden_dim=DEC_D, num_heads=DEC_H,
+                       mlp_dim=DEC_MLP, use_caching=True, max_batch_size=1, cache_dtype=torch.bfloat16)
+    synth.rerandomise_(dec, 2)
+    dec = dec.to(device).eval()
+    lens = [(h // 16) * (w // 16) for h, w in synth.system_shapes(B)]
+    mp = Packed(lens, device)
+    g = torch.Generator(device=device).manual_seed(3 + rank)
+    mem = torch.randn(mp.total, DEC_D, device=device, generator=g).bfloat16()
+    steps = max_len - 1
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        eng = decode_engine.GreedyDecodeEngine(dec, B, max_len, mp.total, torch.bfloat16, device)
+        eng.prefill(mem, mp)
+        eng.generate(stop_early=False)                      # graph capture + one full warm-up pass
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+        n0 = ops.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.prefill(mem, mp)
+        t_pref = torch.cuda.Event(enable_timing=True)
+        t_pref.record()
+        eng.generate(stop_early=False)
+        e1.record()
+        torch.cuda.synchronize()
+        ms_total, ms_prefill = e0.elapsed_time(e1), e0.elapsed_time(t_pref)
+        # the dominant kernel alone (cross-attention over the 1 GB memory cache of one layer), CUDA events per launch
+        qc = torch.randn(B, DEC_D, device=device, generator=g).bfloat16()
+        reps, kern_ms = 20, 0.0
+        for i in range(reps + 3):
+            k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            k0.record()
+            ops.decode_attn_paged(qc, None, eng.cross[i % DEC_LAYERS], DEC_H, 64, eng.max_mem_len, eng.ws_cross,
+                                  torch.bfloat16, seq_start=eng.seq_start, kv_lens=eng.kv_lens)
+            k1.record()
+            k1.synchronize()
+            if i >= 3:
+                kern_ms += k0.elapsed_time(k1)
+        kern_ms /= reps
+    launches_per_step = eng.launches_per_step
+    t = torch.tensor([ms_total, ms_prefill, kern_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms_total, ms_prefill, kern_ms = (float(v) for v in t)
+    if rank != 0:
+        return None
+    peaks = load_peaks()
+    ms_step = (ms_total - ms_prefill) / steps
+    step_bytes = sum(decode_step_bytes(B, lens, tt) for tt in range(1, max_len)) / steps
+    kern_bytes = sum(lens) * 2 * DEC_D * 2 + 2 * B * DEC_D * 2          # K|V rows of every memory token + q + out
+    return {
+        "metric": "batched KV-cached LMX greedy decode tokens/sec", "value": world * B * steps / (ms_total * 1e-3),
+        "unit": "tokens/s", "ms_per_step": ms_step, "prefill_ms": ms_prefill,
+        "config": {"workload": "configs[2]: %d systems/GPU, memory lengths of the config-2 mix (sum S = %d), %d greedy steps "
+                               "incl. cross-KV prefill, early stop disabled, full-size OMRDecoder (12 x 1024d, 16 heads, vocab 227), "
+                               "bf16 weights and KV caches, CUDA-graphed step" % (B, sum(lens), steps),
+                   "kv_cache_gb": round((DEC_LAYERS * (B * eng.pages_per_seq * 64 + mp.total) * 2 * DEC_D * 2) / 1e9, 1)},
+        "gpu_launches_per_step": launches_per_step,
+        "step_roofline": {"bound": "hbm", "achieved": step_bytes / (ms_step * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
+                          "unit": "GB/s", "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                          "algorithmic_bytes_per_step": step_bytes},
+        "roofline": {"bound": "hbm", "kernel": "decode_attn_tma_kernel (+combine), cross-attention over one layer's memory cache",
+                     "achieved": kern_bytes / (kern_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": kern_bytes / (kern_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                     "algorithmic_bytes_per_launch": kern_bytes, "ms_per_launch": kern_ms,
+                     "peak_source": peaks["source"] + " (HBM copy, MEASURED_PEAKS.json)"},
+    }
+
+
 # ------------------------------------------------------------------------------------------ CPU arms
 def oracle_encoder_step(imgs, sd, threads):
     """The reference algorithm (oracle port, fp32, CPU) for the encoder forward on `imgs`."""
@@ -281,6 +379,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-decode", action="store_true", help="skip the configs[2] decode leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -298,7 +397,11 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.distributed.init_process_group("nccl", device_id=device)
     line = run_ours(args, rank, world, device)
+    torch.cuda.empty_cache()
+    dec = None if args.no_decode else run_decode(args, rank, world, device)
     if line is not None:
+        if dec is not None:
+            line["decode"] = dec
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line), flush=True)

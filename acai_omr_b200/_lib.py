@@ -52,6 +52,9 @@ SIGNATURES = {
     "acai_embed_tokens": [_p, _i32, _p, _p, _p, _i32, _i32, _p, _i32, _i32, _p],
     "acai_argmax_logprob": [_p, _i32, _i64, _i32, _i32, _p, _p, _p],
     "acai_unpack_padded": [_p, _i32, _p, _i32, _i32, _i32, _p, _p, _i32, _p],
+    "acai_patchify": [_p, _i32, _p, _i32, _i32, _i32, _p, _i32, _p],
+    "acai_mae_restore": [_p, _i32, _p, _p, _p, _p, _i32, _i32, _p, _p, _i32, _p, _i32, _i32, _p],
+    "acai_mae_loss_fwd": [_p, _i32, _p, _p, _i32, _i32, _p, _p, _p],
     "acai_pack_padded": [_p, _i32, _p, _i32, _i32, _i32, _p, _i32, _p],
 }
 

@@ -174,9 +174,122 @@ __global__ void kv_append_kernel(const void* __restrict__ k_new, const void* __r
   }
 }
 
+
+// ---- MAE glue (models.py:219-241, 265-267, 271-288) ------------------------------------------------------------
+// nn.Unfold patches of a ragged image list as packed rows [total, C*P*P] (feature order channel, row, col).
+__global__ void patchify_kernel(const acai_image_desc* __restrict__ images, int num_images, const int32_t* __restrict__ cu,
+                                int total, int P, int C, void* __restrict__ out, int out_dt) {
+  const int K = C * P * P;
+  const int64_t n = (int64_t)total * K;
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < n; g += (int64_t)gridDim.x * blockDim.x) {
+    const int tok = (int)(g / K), k = (int)(g - (int64_t)tok * K);
+    const int b = find_sequence(cu, num_images, tok);
+    const acai_image_desc d = images[b];
+    const int pid = tok - cu[b], prow = pid / d.wp, pcol = pid - prow * d.wp;
+    const int ch = k / (P * P), rem = k - ch * P * P, i = rem / P, j = rem - i * P;
+    const float v = __ldg(d.pixels + (int64_t)ch * d.height * d.width + (int64_t)(prow * P + i) * d.width + pcol * P + j);
+    st_from_float(out, g, out_dt, v);
+  }
+}
+
+// prepare_for_decoder: row i of sequence b = (r < keep_b ? latent[cu_keep[b] + r] : mask_token) + dec_pe[i / wp, i % wp]
+// with r = ids_restore[cu_full[b] + i].  One CTA per output row.
+__global__ void mae_restore_kernel(const void* __restrict__ latent, int lat_dt, const int32_t* __restrict__ cu_keep,
+                                   const int32_t* __restrict__ cu_full, const int64_t* __restrict__ ids_restore,
+                                   const int32_t* __restrict__ wps, int batch, const float* __restrict__ mask_token,
+                                   const float* __restrict__ dec_pe, int pe_w, void* __restrict__ out, int out_dt, int dim) {
+  const int row = blockIdx.x;
+  const int b = find_sequence(cu_full, batch, row);
+  const int i = row - cu_full[b];
+  const int r = (int)ids_restore[row];
+  const int keep = cu_keep[b + 1] - cu_keep[b];
+  const int wp = wps[b];
+  const float* pe = dec_pe + ((int64_t)(i / wp) * pe_w + (i % wp)) * dim;
+  const int64_t src = (int64_t)(cu_keep[b] + r) * dim;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) {
+    const float v = r < keep ? ld_as_float(latent, src + c, lat_dt) : __ldg(mask_token + c);
+    st_from_float(out, (int64_t)row * dim + c, out_dt, v + __ldg(pe + c));
+  }
+}
+
+// MAELoss per patch: target normalised by its own mean / unbiased variance (eps 1e-6), mean squared error vs pred.
+__global__ void mae_row_loss_kernel(const void* __restrict__ pred, int pred_dt, const float* __restrict__ target,
+                                    const uint8_t* __restrict__ mask, int feats, float* __restrict__ row_loss) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  if (!mask[row]) { if (threadIdx.x == 0) row_loss[row] = 0.0f; return; }
+  const int64_t base = (int64_t)row * feats;
+  float s = 0.0f;
+  for (int c = threadIdx.x; c < feats; c += blockDim.x) s += target[base + c];
+  const float mean = block_sum(s, red) / (float)feats;
+  float q = 0.0f;
+  for (int c = threadIdx.x; c < feats; c += blockDim.x) { const float d = target[base + c] - mean; q += d * d; }
+  const float var = block_sum(q, red) / (float)(feats - 1);
+  const float rstd = 1.0f / sqrtf(var + 1.0e-6f);
+  float e = 0.0f;
+  for (int c = threadIdx.x; c < feats; c += blockDim.x) {
+    const float d = ld_as_float(pred, base + c, pred_dt) - (target[base + c] - mean) * rstd;
+    e += d * d;
+  }
+  e = block_sum(e, red);
+  if (threadIdx.x == 0) row_loss[row] = e / (float)feats;
+}
+
+// Deterministic masked sum: out[0] = sum row_loss[mask], out[1] = count(mask).  One CTA, fixed reduction order.
+__global__ void __launch_bounds__(1024)
+masked_sum_kernel(const float* __restrict__ row_loss, const uint8_t* __restrict__ mask, int rows, float* __restrict__ out) {
+  __shared__ float red[32];
+  float s = 0.0f, n = 0.0f;
+  for (int r = threadIdx.x; r < rows; r += blockDim.x) if (mask[r]) { s += row_loss[r]; n += 1.0f; }
+  s = block_sum(s, red);
+  n = block_sum(n, red);
+  if (threadIdx.x == 0) { out[0] = s; out[1] = n; }
+}
+
 }  // namespace acai
 
 using namespace acai;
+
+extern "C" int acai_patchify(const acai_image_desc* images, int32_t num_images, const int32_t* cu_seqlens,
+                             int32_t total_tokens, int32_t patch_size, int32_t channels, void* out, int32_t out_dtype,
+                             void* stream) {
+  ACAI_CHECK_ARG(images && cu_seqlens && out && num_images > 0 && total_tokens >= 0 && patch_size > 0 && channels > 0 &&
+                 dtype_valid(out_dtype), "acai_patchify: bad argument");
+  if (total_tokens == 0) return ACAI_OK;
+  const int64_t n = (int64_t)total_tokens * channels * patch_size * patch_size;
+  const int64_t blocks = (n + 255) / 256;
+  patchify_kernel<<<(unsigned)(blocks < 65535 * 16 ? blocks : 65535 * 16), 256, 0, (cudaStream_t)stream>>>(
+      images, num_images, cu_seqlens, total_tokens, patch_size, channels, out, out_dtype);
+  return launch_status("patchify");
+}
+
+extern "C" int acai_mae_restore(const void* latent, int32_t latent_dtype, const int32_t* cu_keep, const int32_t* cu_full,
+                                const int64_t* ids_restore, const int32_t* patches_per_row, int32_t batch,
+                                int32_t total_rows, const float* mask_token, const float* dec_pos_embedding, int32_t pe_w,
+                                void* out, int32_t out_dtype, int32_t dim, void* stream) {
+  ACAI_CHECK_ARG(latent && cu_keep && cu_full && ids_restore && patches_per_row && mask_token && dec_pos_embedding && out,
+                 "acai_mae_restore: null pointer");
+  ACAI_CHECK_ARG(batch > 0 && total_rows >= 0 && dim > 0 && dtype_valid(latent_dtype) && dtype_valid(out_dtype),
+                 "acai_mae_restore: bad argument");
+  if (total_rows == 0) return ACAI_OK;
+  mae_restore_kernel<<<total_rows, dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(
+      latent, latent_dtype, cu_keep, cu_full, ids_restore, patches_per_row, batch, mask_token, dec_pos_embedding, pe_w, out,
+      out_dtype, dim);
+  return launch_status("mae_restore");
+}
+
+extern "C" int acai_mae_loss_fwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask,
+                                 int32_t rows, int32_t feats, float* row_loss, float* sums, void* stream) {
+  ACAI_CHECK_ARG(pred && target && loss_mask && row_loss && sums && rows > 0 && feats > 1 && dtype_valid(pred_dtype),
+                 "acai_mae_loss_fwd: bad argument");
+  mae_row_loss_kernel<<<rows, feats >= 256 ? 128 : 64, 0, (cudaStream_t)stream>>>(pred, pred_dtype, target, loss_mask, feats,
+                                                                                row_loss);
+  int rc = launch_status("mae_row_loss");
+  if (rc) return rc;
+  masked_sum_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(row_loss, loss_mask, rows, sums);
+  return launch_status("masked_sum");
+}
+
 
 extern "C" int acai_layernorm_fwd(const void* x, int32_t x_dtype, const void* residual, int32_t res_dtype,
                                   const float* gamma, const float* beta, float eps, void* out, int32_t out_dtype,

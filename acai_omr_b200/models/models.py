@@ -132,6 +132,147 @@ class Encoder(nn.Module):
         return h.view(1, pk.total, self.hidden_dim)
 
 
+class MAEEncoder(Encoder):
+    """models.py:100-180: the Encoder with MAE shuffling/masking; only the kept 25 % of the patches are embedded
+    (K1 gathers them through a patch index) and encoded."""
+
+    def __init__(self, mask_ratio, patch_size, pe_max_height, pe_max_width, num_layers=12, num_heads=12, hidden_dim=768,
+                 mlp_dim=3072):
+        super().__init__(patch_size, pe_max_height, pe_max_width, num_layers, hidden_dim, num_heads, mlp_dim,
+                         transformer_dropout=0.0)
+        self.mask_ratio = mask_ratio
+
+    def mask_indices(self, seq_len, device, noise=None):
+        """Index bookkeeping of mask_sequence (models.py:106-125): (ids_keep, ids_restore, seq_mask, len_keep).
+        `noise` replaces the per-image torch.rand draw (parity tests inject the reference's draw)."""
+        len_keep = int(seq_len * (1 - self.mask_ratio))
+        if noise is None:
+            noise = torch.rand(seq_len, device=device)
+        ids_shuffle = torch.argsort(noise.to(device))
+        ids_restore = torch.argsort(ids_shuffle)
+        seq_mask = torch.ones(seq_len, device=device, dtype=torch.int)
+        seq_mask[:len_keep] = 0
+        return ids_shuffle[:len_keep], ids_restore, seq_mask.index_select(0, ids_restore), len_keep
+
+    def embed_masked_packed(self, x, noises=None):
+        """-> (packed kept-patch embeddings, Packed(kept), info dict for the decoder side)."""
+        imgs = self._image_list(x)
+        P, dev = self.patch_size, self.pos_embedding.device
+        keep, restore, masks, keep_lens, full_lens, dims = [], [], [], [], [], []
+        for i, t in enumerate(imgs):
+            h_p, w_p = t.shape[-2] // P, t.shape[-1] // P
+            self._grid_check(h_p, w_p)
+            ids_keep, ids_restore, seq_mask, len_keep = self.mask_indices(h_p * w_p, dev, None if noises is None else noises[i])
+            keep.append(ids_keep); restore.append(ids_restore); masks.append(seq_mask)
+            keep_lens.append(len_keep); full_lens.append(h_p * w_p); dims.append((h_p, w_p))
+        patch_index = torch.cat(keep).to(torch.int32)
+        h, pk = self.embed_packed(imgs, keep=(keep_lens, patch_index))
+        info = dict(imgs=imgs, kept_seq_lens=keep_lens, unmasked_seq_lens=full_lens, seq_masks=masks, ids_restore=restore,
+                    patchified_dims=dims)
+        return h, pk, info
+
+    def batchify(self, x, noises=None):
+        """models.py:128-173 (padded API; same 8-tuple)."""
+        h, pk, info = self.embed_masked_packed(x, noises)
+        emb = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self.projection.bias)
+        full = Packed(info["unmasked_seq_lens"], emb.device)
+        return (emb, pk.mask(emb.device), full.mask(emb.device), info["kept_seq_lens"], info["unmasked_seq_lens"],
+                torch.nested.as_nested_tensor(info["seq_masks"], layout=torch.jagged),
+                torch.nested.as_nested_tensor(info["ids_restore"], layout=torch.jagged), info["patchified_dims"])
+
+    def encode_masked_packed(self, x, noises=None):
+        h, pk, info = self.embed_masked_packed(x, noises)
+        h = self.encoder_blocks.forward_packed(h, pk, final_dtype=torch.float32)
+        return h, pk, info
+
+    def forward(self, x, noises=None):
+        """models.py:176-180."""
+        h, pk, info = self.encode_masked_packed(x, noises)
+        out = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
+        out._acai_packed = (h, pk, info)
+        full = Packed(info["unmasked_seq_lens"], out.device)
+        return (out, full.mask(out.device), info["kept_seq_lens"], info["unmasked_seq_lens"],
+                torch.nested.as_nested_tensor(info["seq_masks"], layout=torch.jagged),
+                torch.nested.as_nested_tensor(info["ids_restore"], layout=torch.jagged), info["patchified_dims"])
+
+
+class MAEDecoder(nn.Module):
+    """models.py:182-195."""
+
+    def __init__(self, num_layers=8, hidden_dim=512, num_heads=16, mlp_dim=3072, transformer_dropout=0.0):
+        super().__init__()
+        self.decoder_blocks = _encoder_stack(hidden_dim, num_heads, mlp_dim, transformer_dropout, num_layers, True)
+
+    def forward(self, x, attention_mask):
+        return self.decoder_blocks(x, src_key_padding_mask=attention_mask)
+
+
+class MAE(nn.Module):
+    """models.py:197-269."""
+
+    def __init__(self, mask_ratio, patch_size, pe_max_height, pe_max_width, encoder_hidden_dim=768, decoder_hidden_dim=512,
+                 encoder_kwargs={}, decoder_kwargs={}):
+        super().__init__()
+        self.patch_size = patch_size
+        self.encoder = MAEEncoder(mask_ratio, self.patch_size, pe_max_height, pe_max_width, hidden_dim=encoder_hidden_dim,
+                                  **encoder_kwargs)
+        self.decoder_hidden_dim = decoder_hidden_dim
+        self.decoder = MAEDecoder(hidden_dim=self.decoder_hidden_dim, **decoder_kwargs)
+        self.decoder_embed = Linear(encoder_hidden_dim, self.decoder_hidden_dim)
+        self.decoder_unembed = Linear(self.decoder_hidden_dim, NUM_CHANNELS * patch_size ** 2)
+        self.mask_token = nn.Parameter(torch.zeros(1, 1, self.decoder_hidden_dim))
+        self.decoder_pos_embedding = nn.Parameter(torch.zeros(pe_max_height, pe_max_width, self.decoder_hidden_dim))
+        nn.init.trunc_normal_(self.mask_token, std=0.1)
+        nn.init.trunc_normal_(self.decoder_pos_embedding, std=0.1)
+
+    def _restore_packed(self, latent_packed, pk_keep, info, out_dtype):
+        dev = latent_packed.device
+        full = Packed(info["unmasked_seq_lens"], dev)
+        ids = torch.cat([r.to(dev) for r in info["ids_restore"]]).to(torch.int64).contiguous()
+        wps = torch.tensor([w for _, w in info["patchified_dims"]], dtype=torch.int32).to(dev)
+        rows = ops.mae_restore(latent_packed, pk_keep.cu, full.cu, ids, wps, full.total, self.mask_token,
+                               self.decoder_pos_embedding, out_dtype)
+        return rows, full
+
+    def prepare_for_decoder(self, latent, kept_seq_lens, unmasked_seq_lens, batch_ids_restore, patchified_dims):
+        """models.py:219-241 (padded API): latent (N, L_keep_max, D) -> (N, L_max, D) with mask tokens, unshuffled, + PE."""
+        dev = latent.device
+        pk = Packed(kept_seq_lens, dev)
+        restore = batch_ids_restore.unbind() if hasattr(batch_ids_restore, "unbind") else list(batch_ids_restore)
+        info = dict(unmasked_seq_lens=unmasked_seq_lens, ids_restore=list(restore), patchified_dims=patchified_dims)
+        packed = ops.pack_padded(latent, pk.cu, pk.total)
+        rows, full = self._restore_packed(packed, pk, info, latent.dtype)
+        return ops.unpack_padded(rows, full.cu, full.batch, full.max_len)
+
+    def forward(self, batch, noises=None):
+        """models.py:249-269 -> (pred (N, L_m, C*P*P), loss_mask (N, L_m) bool, target (N, L_m, C*P*P))."""
+        x, y = zip(*batch)
+        dt = compute_dtype()
+        h, pk, info = self.encoder.encode_masked_packed(list(x), noises)
+        lat = self.decoder_embed(h, out_dtype=dt)
+        rows, full = self._restore_packed(lat, pk, info, dt)
+        hid = self.decoder.decoder_blocks.forward_packed(rows, full, final_dtype=torch.float32)
+        pred = self.decoder_unembed(hid, out_dtype=dt)
+        dev = pred.device
+        P = self.patch_size
+        tgts = self.encoder._image_list(list(y))
+        tgt_rows = ops.patchify(tgts, ops.make_image_descs(tgts, P, dev), full.cu, full.total, P, tgts[0].shape[0])
+        pred_p = ops.unpack_padded(pred, full.cu, full.batch, full.max_len)
+        target_p = ops.unpack_padded(tgt_rows, full.cu, full.batch, full.max_len)
+        loss_mask = torch.zeros((full.batch, full.max_len), dtype=torch.bool, device=dev)
+        for i, m in enumerate(info["seq_masks"]):
+            loss_mask[i, : m.shape[0]] = m.bool()
+        return pred_p, loss_mask, target_p
+
+
+class MAELoss(nn.Module):
+    """models.py:271-288."""
+
+    def forward(self, pred, loss_mask, target):
+        sums, _ = ops.mae_loss(pred, loss_mask, target)
+        return sums[0] / sums[1]
+
+
 class OMREncoder(Encoder):
     """models.py:290-332: as Encoder, but oversize images get a bilinearly resized PE grid."""
     _interpolate_pe = True

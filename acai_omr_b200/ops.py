@@ -359,3 +359,42 @@ def advance_step(step):
     _cuda(step)
     lib = _lib.load()
     _call("acai_advance_step", lib.acai_advance_step, _p(step), _stream())
+
+
+# ------------------------------------------------------------------------------------------ MAE glue
+def patchify(images, descs_dev, cu_seqlens, total_tokens, patch_size, channels, out_dtype=torch.float32):
+    """nn.Unfold patches of a ragged image list as packed rows [total, C*P*P] (acai_patchify)."""
+    _cuda(descs_dev, cu_seqlens, *images)
+    out = torch.empty((total_tokens, channels * patch_size * patch_size), dtype=out_dtype, device=cu_seqlens.device)
+    _call("acai_patchify", _lib.load().acai_patchify, _p(descs_dev), len(images), _p(cu_seqlens), total_tokens, patch_size,
+          channels, _p(out), _DT[out_dtype], _stream())
+    return out
+
+
+def mae_restore(latent, cu_keep, cu_full, ids_restore, patches_per_row, total_rows, mask_token, dec_pos_embedding, out_dtype):
+    """MAE.prepare_for_decoder on packed rows (acai_mae_restore)."""
+    _cuda(latent, cu_keep, cu_full, ids_restore, patches_per_row, mask_token, dec_pos_embedding)
+    dim = latent.shape[-1]
+    latent = latent.contiguous()
+    out = torch.empty((total_rows, dim), dtype=out_dtype, device=latent.device)
+    mt, pe = _f32c(mask_token).reshape(-1), _f32c(dec_pos_embedding)
+    _call("acai_mae_restore", _lib.load().acai_mae_restore, _p(latent), _dt(latent), _p(cu_keep), _p(cu_full), _p(ids_restore),
+          _p(patches_per_row), cu_full.numel() - 1, total_rows, _p(mt), _p(pe), pe.shape[1], _p(out), _DT[out_dtype], dim,
+          _stream())
+    return out
+
+
+def mae_loss(pred, loss_mask, target):
+    """(sum of per-patch losses over loss_mask, count) as a 2-element fp32 tensor, plus the per-row losses."""
+    _cuda(pred, loss_mask, target)
+    feats = pred.shape[-1]
+    p2 = pred.reshape(-1, feats).contiguous()
+    t2 = target.reshape(-1, feats).float().contiguous()
+    m2 = loss_mask.reshape(-1).to(torch.uint8).contiguous()
+    rows = p2.shape[0]
+    row_loss = torch.empty(rows, dtype=torch.float32, device=pred.device)
+    sums = torch.empty(2, dtype=torch.float32, device=pred.device)
+    _call("acai_mae_loss_fwd", _lib.load().acai_mae_loss_fwd, _p(p2), _dt(p2), _p(t2), _p(m2), rows, feats, _p(row_loss),
+          _p(sums), _stream())
+    _bump()
+    return sums, row_loss

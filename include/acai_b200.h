@@ -183,6 +183,24 @@ int acai_unpack_padded(const void* packed, int32_t in_dtype, const int32_t* cu_s
 int acai_pack_padded(const void* padded, int32_t in_dtype, const int32_t* cu_seqlens, int32_t batch,
                      int32_t max_len, int32_t dim, void* out, int32_t out_dtype, void* stream);
 
+/* ---- MAE glue ----------------------------------------------------------------------------------------------------
+ * acai_patchify: nn.Unfold(P, P) patches of a ragged image list as packed rows [total, C*P*P] (the reconstruction
+ *   targets, models.py:265-267).
+ * acai_mae_restore: MAE.prepare_for_decoder (models.py:219-241) on packed rows: row i of sequence b is
+ *   latent[cu_keep[b] + r] if r = ids_restore[cu_full[b] + i] < keep_b else mask_token, plus the decoder position
+ *   embedding of patch i (grid row i / patches_per_row[b], column i % patches_per_row[b]).
+ * acai_mae_loss_fwd: MAELoss (models.py:271-288): row_loss[r] = mean_f (pred - (target - mean_r) / sqrt(var_r + 1e-6))^2
+ *   with the unbiased per-patch variance, for rows with loss_mask != 0; sums = {sum of those, their count} reduced in a
+ *   fixed order (the loss is sums[0] / sums[1]). */
+int acai_patchify(const acai_image_desc* images, int32_t num_images, const int32_t* cu_seqlens, int32_t total_tokens,
+                  int32_t patch_size, int32_t channels, void* out, int32_t out_dtype, void* stream);
+int acai_mae_restore(const void* latent, int32_t latent_dtype, const int32_t* cu_keep, const int32_t* cu_full,
+                     const int64_t* ids_restore, const int32_t* patches_per_row, int32_t batch, int32_t total_rows,
+                     const float* mask_token, const float* dec_pos_embedding, int32_t pe_w,
+                     void* out, int32_t out_dtype, int32_t dim, void* stream);
+int acai_mae_loss_fwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask,
+                      int32_t rows, int32_t feats, float* row_loss, float* sums, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

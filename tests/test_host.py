@@ -119,3 +119,24 @@ def test_split_lmx_and_inference_mask():
     assert vit.create_inference_mask(s).tolist() == [[True, True, True, False, False], [True] * 5]
     a, b, c = vit.mask_and_clip_seqs(s, torch.ones(2, 5))
     assert a.tolist() == [[0, 5, 2, 1, 1], [0, 5, 6, 7, 8]] and b[0].tolist() == [1, 1, 1, 0, 0]
+
+
+def test_mae_state_dict_matches_reference_fixture(golden):
+    """debug_pretrained_mae.pth (the reference's tiny MAE fixture, tests/test_pre_train.py:29): same keys and shapes."""
+    keys = golden["debug_mae_keys"]
+    mae = M.MAE(0.75, 16, 60, 200, encoder_hidden_dim=10, decoder_hidden_dim=10,
+                encoder_kwargs=dict(num_layers=2, num_heads=1, mlp_dim=1), decoder_kwargs=dict(num_layers=2, num_heads=1, mlp_dim=1))
+    ours = {k: tuple(v.shape) for k, v in mae.state_dict().items()}
+    assert set(ours) == set(keys)
+    mismatched = {k: (ours[k], keys[k]) for k in keys if ours[k] != keys[k] and "linear" not in k}
+    assert not mismatched, mismatched
+
+
+def test_mae_mask_indices_roundtrip():
+    """tests/test_mae.py:36-55: unshuffling the shuffled order restores the sequence; 25 % kept."""
+    enc = M.MAEEncoder(0.75, 4, 6, 10, num_layers=1, num_heads=1, hidden_dim=8, mlp_dim=8)
+    keep, restore, seq_mask, n = enc.mask_indices(40, "cpu")
+    assert n == 10 and keep.shape == (10,) and int(seq_mask.sum()) == 30
+    shuffled = torch.argsort(restore)
+    assert torch.equal(shuffled[:n], keep) and torch.equal(shuffled[restore], torch.arange(40))
+    assert torch.equal(seq_mask[keep], torch.zeros(10, dtype=torch.int))

@@ -207,3 +207,60 @@ def test_bf16_autocast_mode_within_tolerance():
     assert logits.dtype == torch.bfloat16
     assert rel_err(logits, ref) < 2e-2
     assert rel_err(steps, ref) < 2e-2
+
+
+def test_mae_forward_and_loss_golden(golden):
+    """MAE.forward + MAELoss (models.py:249-288) with the reference's own torch.rand draws injected."""
+    g = golden["mae"]
+    c = g["cfg"]
+    mae = M.MAE(c["mask_ratio"], c["patch_size"], c["pe_max_height"], c["pe_max_width"], c["encoder_hidden_dim"],
+                c["decoder_hidden_dim"], c["encoder_kwargs"], c["decoder_kwargs"])
+    mae.load_state_dict(g["sd"])
+    mae = mae.to(DEV).eval()
+    batch = list(zip(cuda_list(g["imgs"]), cuda_list(g["targets"])))
+    with torch.no_grad():
+        pred, lmask, target = mae(batch, noises=g["noises"])
+        loss = M.MAELoss()(pred, lmask, target)
+    assert torch.equal(lmask.cpu(), g["loss_mask"])
+    assert torch.equal(target.cpu(), g["target"])
+    valid = g["loss_mask"]
+    assert torch.allclose(pred.cpu()[valid], g["pred"][valid], **TOL)
+    assert torch.allclose(loss.cpu(), g["loss"], **TOL)
+    # padded-API pieces the reference's tests exercise (tests/test_mae.py:57-122)
+    with torch.no_grad():
+        emb, enc_mask, dec_mask, keep, full, seq_masks, restore, dims = mae.encoder.batchify(cuda_list(g["imgs"]), noises=g["noises"])
+    assert keep == [int(L * 0.25) for L in full] and dec_mask.shape[1] == max(full)
+    assert [tuple(m.shape) for m in seq_masks.unbind()] == [(L,) for L in full]
+
+
+def test_mae_loss_known_answer_gpu():
+    """Reference tests/test_mae.py:169-180: MAELoss == 10.583329200744629."""
+    target = torch.cat([
+        torch.tensor([[1, 1, 1], [2, 2, 2]], dtype=torch.float).unsqueeze(-1).repeat(1, 1, 6),
+        torch.tensor([[2, 2, 2], [3, 3, 3]], dtype=torch.float).unsqueeze(-1).repeat(1, 1, 6)], dim=-1).to(DEV)
+    pred = torch.tensor([[2, 2, 2], [3, 3, 4]], dtype=torch.float).unsqueeze(-1).repeat(1, 1, 12).to(DEV)
+    loss_mask = torch.tensor([[1, 0, 0], [1, 0, 1]], dtype=torch.float).to(DEV)
+    loss = M.MAELoss()(pred, loss_mask, target)
+    assert abs(loss.item() - 10.583329200744629) < 2e-5
+
+
+def test_mae_bf16_full_head_dims():
+    """MAE decoder shape class of the real model: 16 heads of 32 (SIMT attention path), bf16 autocast vs the fp32 oracle."""
+    torch.manual_seed(0)
+    from acai_omr_b200 import synth
+    mae = M.MAE(0.75, 16, 12, 40, encoder_hidden_dim=128, decoder_hidden_dim=64,
+                encoder_kwargs=dict(num_layers=2, num_heads=2, mlp_dim=256), decoder_kwargs=dict(num_layers=2, num_heads=2, mlp_dim=128))
+    synth.rerandomise_(mae, 3)
+    sd = {k: v.detach().clone() for k, v in mae.state_dict().items()}
+    g = torch.Generator().manual_seed(1)
+    imgs = [torch.rand(1, 64, 160, generator=g), torch.rand(1, 32, 320, generator=g), torch.rand(1, 48, 48, generator=g)]
+    noises = [torch.rand((t.shape[1] // 16) * (t.shape[2] // 16), generator=g) for t in imgs]
+    cfg = dict(mask_ratio=0.75, patch_size=16, pe_max_height=12, pe_max_width=40, encoder_heads=2, decoder_heads=2)
+    pred_o, lmask_o, target_o = O.mae_forward(list(zip(imgs, imgs)), sd, cfg, noises)
+    mae = mae.to(DEV).eval()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        pred, lmask, target = mae(list(zip(cuda_list(imgs), cuda_list(imgs))), noises=noises)
+        loss = M.MAELoss()(pred, lmask, target)
+    assert torch.equal(lmask.cpu(), lmask_o) and torch.allclose(target.cpu(), target_o)
+    assert rel_err(pred[lmask], pred_o[lmask_o]) < 2e-2
+    assert abs(loss.item() - O.mae_loss(pred_o, lmask_o, target_o).item()) < 2e-2 * max(1.0, loss.item())

@@ -17,7 +17,7 @@ __global__ void __launch_bounds__(QB)
 attn_varlen_simt(const void* __restrict__ q, const void* __restrict__ k, const void* __restrict__ v, int dt,
                  int64_t qs, int64_t ks, int64_t vs, const int32_t* __restrict__ cu_q,
                  const int32_t* __restrict__ cu_k, int d, int causal, float scale,
-                 void* __restrict__ out, int out_dt, int64_t os) {
+                 void* __restrict__ out, int out_dt, int64_t os, float* __restrict__ lse, int total_q) {
   __shared__ float Ks[KT][DMAX];
   __shared__ float Vs[KT][DMAX];
   const int b = blockIdx.z, h = blockIdx.y, qb = blockIdx.x, tid = threadIdx.x;
@@ -86,6 +86,7 @@ attn_varlen_simt(const void* __restrict__ q, const void* __restrict__ k, const v
 #pragma unroll
     for (int e = 0; e < DMAX; ++e)
       if (e < d) st_from_float(out, (int64_t)(q0 + row) * os + (int64_t)h * d + e, out_dt, acc[e] * inv);
+    if (lse) lse[(int64_t)h * total_q + q0 + row] = l > 0.0f ? (m + logf(l)) * 1.4426950408889634f : INFINITY;   // log2 domain
   }
 }
 
@@ -136,7 +137,8 @@ decode_attn_simt(const void* __restrict__ q, int q_dt, int64_t q_bs, const void*
 
 int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs,
                    const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
-                   int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, cudaStream_t st);
+                   int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, float* lse,
+                   cudaStream_t st);
 
 }  // namespace acai
 
@@ -146,7 +148,7 @@ extern "C" int acai_attn_varlen_fwd(const void* q, const void* k, const void* v,
                                     int64_t k_stride, int64_t v_stride, const int32_t* cu_seqlens_q,
                                     const int32_t* cu_seqlens_k, int32_t batch, int32_t max_seqlen_q, int32_t total_q,
                                     int32_t total_k, int32_t heads, int32_t head_dim, int32_t causal, float scale,
-                                    void* out, int32_t out_dtype, int64_t o_stride, void* stream) {
+                                    void* out, int32_t out_dtype, int64_t o_stride, float* lse, void* stream) {
   ACAI_CHECK_ARG(q && k && v && cu_seqlens_q && cu_seqlens_k && out, "acai_attn_varlen_fwd: null pointer");
   ACAI_CHECK_ARG(batch > 0 && heads > 0 && head_dim > 0 && max_seqlen_q >= 0, "acai_attn_varlen_fwd: bad sizes");
   ACAI_CHECK_ARG(dtype_valid(dtype) && dtype_valid(out_dtype), "acai_attn_varlen_fwd: bad dtype");
@@ -156,12 +158,12 @@ extern "C" int acai_attn_varlen_fwd(const void* q, const void* k, const void* v,
   cudaStream_t st = (cudaStream_t)stream;
   {
     int rc = attn_varlen_tc(q, k, v, dtype, q_stride, k_stride, v_stride, cu_seqlens_q, cu_seqlens_k, batch,
-                            max_seqlen_q, total_q, total_k, heads, head_dim, causal, scale, out, out_dtype, o_stride, st);
+                            max_seqlen_q, total_q, total_k, heads, head_dim, causal, scale, out, out_dtype, o_stride, lse, st);
     if (rc != ACAI_ERR_UNSUPPORTED) return rc;
   }
   dim3 grid((max_seqlen_q + QB - 1) / QB, heads, batch);
 #define LAUNCH(D) attn_varlen_simt<D><<<grid, QB, 0, st>>>(q, k, v, dtype, q_stride, k_stride, v_stride, cu_seqlens_q, \
-                                                           cu_seqlens_k, head_dim, causal, scale, out, out_dtype, o_stride)
+                                                           cu_seqlens_k, head_dim, causal, scale, out, out_dtype, o_stride, lse, total_q)
   if (head_dim <= 16) LAUNCH(16);
   else if (head_dim <= 32) LAUNCH(32);
   else if (head_dim <= 64) LAUNCH(64);

@@ -41,6 +41,7 @@ struct AttnParams {
   const int32_t* cu_q; const int32_t* cu_k;
   void* out; int out_dt; int64_t o_stride;
   int causal; float scale_log2;
+  float* lse; int total_q;      // optional [heads, total_q] log2-domain log-sum-exp of every query row (for the backward)
 };
 
 __global__ void __launch_bounds__(THREADS, 2)
@@ -204,6 +205,7 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
       ptx::tc_fence_after();
     }
     const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+    if (p.lse && valid) p.lse[(int64_t)h * p.total_q + q0 + qi] = l > 0.0f ? m * scale_log2 + log2f(l) : INFINITY;
     const int64_t off = (int64_t)(q0 + qi) * p.o_stride + (int64_t)h * D;
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
@@ -244,7 +246,8 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
 // returns ACAI_ERR_UNSUPPORTED when the problem does not qualify
 int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs,
                    const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
-                   int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, cudaStream_t st) {
+                   int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, float* lse,
+                   cudaStream_t st) {
   if (dtype != ACAI_BF16 || head_dim != D || qs % 8 || ks % 8 || vs % 8 || os % 8 || total_q <= 0 || total_k <= 0 ||
       (reinterpret_cast<uintptr_t>(q) & 15) || (reinterpret_cast<uintptr_t>(k) & 15) ||
       (reinterpret_cast<uintptr_t>(v) & 15) || (reinterpret_cast<uintptr_t>(out) & 15))
@@ -261,7 +264,7 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
     ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     attr_set = true;
   }
-  AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f};
+  AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
   attn_fwd_tc64<<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
   return launch_status("attn_fwd_tc64");

@@ -1,0 +1,323 @@
+// Backward-pass building blocks of the teacher-forced / MAE training step.  The dense
+// contractions of the backward (dX = dY W, dW = dY^T X) run on the same tcgen05 GEMM as the forward: this file supplies
+// the operand transposes they need plus the memory-bound pieces (bias gradients, GELU, LayerNorm, cross-entropy,
+// embedding / position scatter-adds, MAE glue).  All reductions that feed parameters have a fixed order or use fp32
+// atomics on distinct rows only where the reference's own autograd is non-deterministic too (index_add).
+#include "common.cuh"
+
+namespace acai {
+
+// out[c, r] = in[r, c] for r < rows, 0 for rows <= r < ld_out (zero padding so that the transposed matrix can be a
+// K-major GEMM operand with K % 64 == 0).  32x32 tiles through padded shared memory: coalesced both ways.
+template <typename T>
+__global__ void __launch_bounds__(256)
+transpose_pad_kernel(const T* __restrict__ in, int64_t ld_in, int rows, int cols, T* __restrict__ out, int64_t ld_out) {
+  __shared__ T tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int r = r0 + ty + i, c = c0 + tx;
+    tile[ty + i][tx] = (r < rows && c < cols) ? in[(int64_t)r * ld_in + c] : T(0);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    const int c = c0 + ty + i, r = r0 + tx;
+    if (c < cols && r < ld_out) out[(int64_t)c * ld_out + r] = tile[tx][ty + i];
+  }
+}
+
+// Column sums in a fixed order: stage 1 sums 128-row slabs per column, stage 2 folds the slabs.
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const void* __restrict__ x, int dt, int64_t ld, int rows, int cols, float* __restrict__ part) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r0 = blockIdx.y * 128, r1 = min(rows, r0 + 128);
+  if (c >= cols) return;
+  float s = 0.0f;
+  for (int r = r0; r < r1; ++r) s += ld_as_float(x, (int64_t)r * ld + c, dt);
+  part[(int64_t)blockIdx.y * cols + c] = s;
+}
+__global__ void colsum_final_kernel(const float* __restrict__ part, int slabs, int cols, float* __restrict__ out, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.0f;
+  for (int i = 0; i < slabs; ++i) s += part[(int64_t)i * cols + c];
+  out[c] = accumulate ? out[c] + s : s;
+}
+
+// exact-erf GELU and its derivative  d/dz [z Phi(z)] = Phi(z) + z phi(z)
+__global__ void gelu_fwd_kernel(const void* __restrict__ z, int dt, void* __restrict__ out, int out_dt, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    st_from_float(out, i, out_dt, gelu_erf(ld_as_float(z, i, dt)));
+}
+__global__ void gelu_bwd_kernel(const void* __restrict__ dy, int dy_dt, const void* __restrict__ z, int z_dt,
+                                void* __restrict__ dz, int dz_dt, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = ld_as_float(z, i, z_dt);
+    const float cdf = 0.5f * (1.0f + erff(v * 0.70710678118654752440f));
+    const float pdf = 0.39894228040143267794f * expf(-0.5f * v * v);
+    st_from_float(dz, i, dz_dt, ld_as_float(dy, i, dy_dt) * (cdf + v * pdf));
+  }
+}
+
+// LayerNorm backward for y = (v - mu) * rstd * gamma + beta with v = x (+ residual):
+//   dv = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma ;  dgamma = sum_rows dy * xhat ;  dbeta = sum_rows dy
+// One warp per row; each CTA (8 rows per pass, grid-stride) keeps per-column partial sums in registers and writes one
+// slab of partials, folded by colsum_final_kernel (fixed order).
+template <int NV>   // cols <= NV * 32; lane owns columns lane + 32 * i
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(const void* __restrict__ dy, int dy_dt, const void* __restrict__ x, int x_dt,
+                     const void* __restrict__ res, int res_dt, const float* __restrict__ gamma, float eps,
+                     void* __restrict__ dv, int dv_dt, float* __restrict__ part_g, float* __restrict__ part_b,
+                     int rows, int cols) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float ag[NV], ab[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) { ag[i] = 0.0f; ab[i] = 0.0f; }
+  for (int row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
+    const int64_t base = (int64_t)row * cols;
+    float v[NV], d[NV];
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      v[i] = 0.0f; d[i] = 0.0f;
+      if (c < cols) {
+        v[i] = ld_as_float(x, base + c, x_dt) + (res ? ld_as_float(res, base + c, res_dt) : 0.0f);
+        d[i] = ld_as_float(dy, base + c, dy_dt);
+        s += v[i];
+      }
+    }
+    const float mu = warp_sum(s) / (float)cols;
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) if (lane + 32 * i < cols) { const float t = v[i] - mu; q += t * t; }
+    const float rstd = rsqrtf(warp_sum(q) / (float)cols + eps);
+    float m1 = 0.0f, m2 = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < cols) {
+        const float xh = (v[i] - mu) * rstd, g = d[i] * __ldg(gamma + c);
+        m1 += g; m2 += g * xh;
+        ag[i] += d[i] * xh; ab[i] += d[i];
+        v[i] = xh; d[i] = g;
+      }
+    }
+    m1 = warp_sum(m1) / (float)cols; m2 = warp_sum(m2) / (float)cols;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < cols) st_from_float(dv, base + c, dv_dt, rstd * (d[i] - m1 - v[i] * m2));
+    }
+  }
+  const int64_t slab = (int64_t)(blockIdx.x * 8 + warp) * cols;     // one slab of partials per warp
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = lane + 32 * i;
+    if (c < cols) { part_g[slab + c] = ag[i]; part_b[slab + c] = ab[i]; }
+  }
+}
+
+// Cross-entropy with ignore_index (OMRCELoss, models.py:784-796), one warp per row:
+//   row_loss = logsumexp(z) - z[target]   (0 for ignored rows);  dlogits = softmax(z) - onehot(target)  (0 for ignored rows)
+// dlogits is scaled by *scale_ptr (= upstream gradient / count, a device scalar).  `valid[row]` = 1 for counted rows.
+__global__ void ce_fwd_bwd_kernel(const void* __restrict__ logits, int dt, int64_t ld, const int64_t* __restrict__ targets,
+                                  int rows, int vocab, int ignore_index, float* __restrict__ row_loss,
+                                  uint8_t* __restrict__ valid, void* __restrict__ dlogits, int dl_dt, int64_t ldd,
+                                  const float* __restrict__ scale_ptr) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int64_t tgt = targets[row];
+  const bool ok = tgt != ignore_index;
+  float mx = -INFINITY;
+  for (int c = lane; c < vocab; c += 32) mx = fmaxf(mx, ld_as_float(logits, (int64_t)row * ld + c, dt));
+  mx = warp_max(mx);
+  float s = 0.0f;
+  for (int c = lane; c < vocab; c += 32) s += expf(ld_as_float(logits, (int64_t)row * ld + c, dt) - mx);
+  s = warp_sum(s);
+  const float lse = mx + logf(s);
+  if (lane == 0 && row_loss) {
+    row_loss[row] = ok ? lse - ld_as_float(logits, (int64_t)row * ld + tgt, dt) : 0.0f;
+    valid[row] = ok ? 1 : 0;
+  }
+  if (dlogits) {
+    const float sc = *scale_ptr;
+    for (int c = lane; c < vocab; c += 32) {
+      float g = 0.0f;
+      if (ok) g = sc * (expf(ld_as_float(logits, (int64_t)row * ld + c, dt) - lse) - (c == tgt ? 1.0f : 0.0f));
+      st_from_float(dlogits, (int64_t)row * ldd + c, dl_dt, g);
+    }
+  }
+}
+
+// dst[index[r], :] += src[r, :]  (fp32 atomics; rows with index < 0 are skipped).  Embedding / position-table
+// gradients: the reference's index_add / embedding_dense_backward are atomic adds as well.
+__global__ void scatter_add_rows_kernel(const void* __restrict__ src, int dt, int64_t ld, const int64_t* __restrict__ index,
+                                        int rows, int dim, float* __restrict__ dst, float scale) {
+  const int r = blockIdx.x;
+  const int64_t d = index[r];
+  if (d < 0) return;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x)
+    atomicAdd(dst + d * dim + c, scale * ld_as_float(src, (int64_t)r * ld + c, dt));
+}
+
+// out[r, :] = index[r] >= 0 ? src[index[r], :] : 0   (gather of gradient rows, e.g. MAE restore backward)
+__global__ void gather_rows_kernel(const void* __restrict__ src, int dt, const int64_t* __restrict__ index, int rows, int dim,
+                                   void* __restrict__ out, int out_dt) {
+  const int r = blockIdx.x;
+  const int64_t s = index[r];
+  for (int c = threadIdx.x; c < dim; c += blockDim.x)
+    st_from_float(out, (int64_t)r * dim + c, out_dt, s >= 0 ? ld_as_float(src, s * dim + c, dt) : 0.0f);
+}
+
+// MAELoss backward: dpred = mask * scale * 2 (pred - tn) / F with tn the per-patch normalised target.
+__global__ void mae_loss_bwd_kernel(const void* __restrict__ pred, int pred_dt, const float* __restrict__ target,
+                                    const uint8_t* __restrict__ mask, int feats, const float* __restrict__ scale_ptr,
+                                    void* __restrict__ dpred, int dp_dt) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  const int64_t base = (int64_t)row * feats;
+  if (!mask[row]) { for (int c = threadIdx.x; c < feats; c += blockDim.x) st_from_float(dpred, base + c, dp_dt, 0.0f); return; }
+  float s = 0.0f;
+  for (int c = threadIdx.x; c < feats; c += blockDim.x) s += target[base + c];
+  const float mean = block_sum(s, red) / (float)feats;
+  float q = 0.0f;
+  for (int c = threadIdx.x; c < feats; c += blockDim.x) { const float d = target[base + c] - mean; q += d * d; }
+  const float rstd = 1.0f / sqrtf(block_sum(q, red) / (float)(feats - 1) + 1.0e-6f);
+  const float k = 2.0f * (*scale_ptr) / (float)feats;
+  for (int c = threadIdx.x; c < feats; c += blockDim.x)
+    st_from_float(dpred, base + c, dp_dt, k * (ld_as_float(pred, base + c, pred_dt) - (target[base + c] - mean) * rstd));
+}
+
+}  // namespace acai
+
+namespace acai {
+__global__ void masked_sum_kernel(const float* __restrict__ row_loss, const uint8_t* __restrict__ mask, int rows, float* __restrict__ out);
+}
+using namespace acai;
+
+static unsigned grid_for(int64_t n, int threads = 256) {
+  const int64_t b = (n + threads - 1) / threads;
+  return (unsigned)(b < 148 * 32 ? (b < 1 ? 1 : b) : 148 * 32);
+}
+
+extern "C" int acai_transpose(const void* in, int32_t dtype, int64_t ld_in, int32_t rows, int32_t cols, void* out,
+                              int64_t ld_out, void* stream) {
+  ACAI_CHECK_ARG(in && out && rows > 0 && cols > 0 && ld_in >= cols && ld_out >= rows && dtype_valid(dtype),
+                 "acai_transpose: bad argument");
+  dim3 grid((cols + 31) / 32, (unsigned)((ld_out + 31) / 32));
+  if (dtype == ACAI_BF16)
+    transpose_pad_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const __nv_bfloat16*>(in), ld_in, rows, cols, reinterpret_cast<__nv_bfloat16*>(out), ld_out);
+  else
+    transpose_pad_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float*>(in), ld_in, rows, cols,
+                                                                     reinterpret_cast<float*>(out), ld_out);
+  return launch_status("transpose_pad");
+}
+
+extern "C" size_t acai_colsum_workspace_bytes(int32_t rows, int32_t cols) {
+  return (size_t)((rows + 127) / 128) * cols * sizeof(float);
+}
+
+extern "C" int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t rows, int32_t cols, float* out,
+                           int32_t accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+  ACAI_CHECK_ARG(x && out && workspace && rows > 0 && cols > 0 && dtype_valid(dtype), "acai_colsum: bad argument");
+  ACAI_CHECK_ARG(workspace_bytes >= acai_colsum_workspace_bytes(rows, cols), "acai_colsum: workspace too small");
+  const int slabs = (rows + 127) / 128;
+  colsum_partial_kernel<<<dim3((cols + 255) / 256, slabs), 256, 0, (cudaStream_t)stream>>>(x, dtype, ld, rows, cols,
+                                                                                        reinterpret_cast<float*>(workspace));
+  int rc = launch_status("colsum_partial");
+  if (rc) return rc;
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float*>(workspace), slabs, cols,
+                                                                           out, accumulate);
+  return launch_status("colsum_final");
+}
+
+extern "C" int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, void* stream) {
+  ACAI_CHECK_ARG(z && out && n >= 0 && dtype_valid(z_dtype) && dtype_valid(out_dtype), "acai_gelu_fwd: bad argument");
+  if (n == 0) return ACAI_OK;
+  gelu_fwd_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(z, z_dtype, out, out_dtype, n);
+  return launch_status("gelu_fwd");
+}
+
+extern "C" int acai_gelu_bwd(const void* dy, int32_t dy_dtype, const void* z, int32_t z_dtype, void* dz, int32_t dz_dtype,
+                             int64_t n, void* stream) {
+  ACAI_CHECK_ARG(dy && z && dz && n >= 0 && dtype_valid(dy_dtype) && dtype_valid(z_dtype) && dtype_valid(dz_dtype),
+                 "acai_gelu_bwd: bad argument");
+  if (n == 0) return ACAI_OK;
+  gelu_bwd_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(dy, dy_dtype, z, z_dtype, dz, dz_dtype, n);
+  return launch_status("gelu_bwd");
+}
+
+static int ln_bwd_grid(int rows) { const int g = (rows + 7) / 8; return g < 296 ? g : 296; }
+
+extern "C" size_t acai_layernorm_bwd_workspace_bytes(int32_t rows, int32_t cols) {
+  return (size_t)2 * ln_bwd_grid(rows) * 8 * cols * sizeof(float);
+}
+
+extern "C" int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* x, int32_t x_dtype, const void* residual,
+                                  int32_t res_dtype, const float* gamma, float eps, void* dv, int32_t dv_dtype,
+                                  float* dgamma, float* dbeta, int32_t accumulate, int32_t rows, int32_t cols,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
+  ACAI_CHECK_ARG(dy && x && gamma && dv && dgamma && dbeta && workspace, "acai_layernorm_bwd: null pointer");
+  ACAI_CHECK_ARG(rows > 0 && cols > 0 && cols <= 1024, "acai_layernorm_bwd: rows=%d cols=%d out of range (cols <= 1024)", rows, cols);
+  ACAI_CHECK_ARG(dtype_valid(dy_dtype) && dtype_valid(x_dtype) && dtype_valid(dv_dtype) && (!residual || dtype_valid(res_dtype)),
+                 "acai_layernorm_bwd: bad dtype");
+  ACAI_CHECK_ARG(workspace_bytes >= acai_layernorm_bwd_workspace_bytes(rows, cols), "acai_layernorm_bwd: workspace too small");
+  const int grid = ln_bwd_grid(rows), slabs = grid * 8;
+  float* pg = reinterpret_cast<float*>(workspace);
+  float* pb = pg + (size_t)slabs * cols;
+  cudaStream_t st = (cudaStream_t)stream;
+#define LNB(NV) layernorm_bwd_kernel<NV><<<grid, 256, 0, st>>>(dy, dy_dtype, x, x_dtype, residual, res_dtype, gamma, eps, dv, \
+                                                               dv_dtype, pg, pb, rows, cols)
+  if (cols <= 128) LNB(4); else if (cols <= 256) LNB(8); else if (cols <= 512) LNB(16); else if (cols <= 768) LNB(24); else LNB(32);
+#undef LNB
+  int rc = launch_status("layernorm_bwd");
+  if (rc) return rc;
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pg, slabs, cols, dgamma, accumulate);
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pb, slabs, cols, dbeta, accumulate);
+  return launch_status("layernorm_bwd_reduce");
+}
+
+extern "C" int acai_ce_loss(const void* logits, int32_t dtype, int64_t ld, const int64_t* targets, int32_t rows,
+                            int32_t vocab, int32_t ignore_index, float* row_loss, uint8_t* valid, float* sums,
+                            void* dlogits, int32_t dlogits_dtype, int64_t ldd, const float* scale, void* stream) {
+  ACAI_CHECK_ARG(logits && targets && rows > 0 && vocab > 0 && dtype_valid(dtype), "acai_ce_loss: bad argument");
+  ACAI_CHECK_ARG((row_loss && valid && sums) || (dlogits && scale && dtype_valid(dlogits_dtype)), "acai_ce_loss: nothing to compute");
+  cudaStream_t st = (cudaStream_t)stream;
+  ce_fwd_bwd_kernel<<<(rows + 3) / 4, 128, 0, st>>>(logits, dtype, ld, targets, rows, vocab, ignore_index, row_loss, valid,
+                                                    dlogits, dlogits_dtype, ldd, scale);
+  int rc = launch_status("ce_loss");
+  if (rc || !row_loss) return rc;
+  masked_sum_kernel<<<1, 1024, 0, st>>>(row_loss, valid, rows, sums);
+  return launch_status("masked_sum");
+}
+
+extern "C" int acai_scatter_add_rows(const void* src, int32_t dtype, int64_t ld, const int64_t* index, int32_t rows,
+                                     int32_t dim, float* dst, float scale, void* stream) {
+  ACAI_CHECK_ARG(src && index && dst && rows >= 0 && dim > 0 && dtype_valid(dtype), "acai_scatter_add_rows: bad argument");
+  if (rows == 0) return ACAI_OK;
+  scatter_add_rows_kernel<<<rows, dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(src, dtype, ld, index, rows, dim, dst, scale);
+  return launch_status("scatter_add_rows");
+}
+
+extern "C" int acai_gather_rows(const void* src, int32_t dtype, const int64_t* index, int32_t rows, int32_t dim, void* out,
+                                int32_t out_dtype, void* stream) {
+  ACAI_CHECK_ARG(src && index && out && rows >= 0 && dim > 0 && dtype_valid(dtype) && dtype_valid(out_dtype),
+                 "acai_gather_rows: bad argument");
+  if (rows == 0) return ACAI_OK;
+  gather_rows_kernel<<<rows, dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(src, dtype, index, rows, dim, out, out_dtype);
+  return launch_status("gather_rows");
+}
+
+extern "C" int acai_mae_loss_bwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask,
+                                 int32_t rows, int32_t feats, const float* scale, void* dpred, int32_t dpred_dtype,
+                                 void* stream) {
+  ACAI_CHECK_ARG(pred && target && loss_mask && scale && dpred && rows > 0 && feats > 1 && dtype_valid(pred_dtype) &&
+                 dtype_valid(dpred_dtype), "acai_mae_loss_bwd: bad argument");
+  mae_loss_bwd_kernel<<<rows, feats >= 256 ? 128 : 64, 0, (cudaStream_t)stream>>>(pred, pred_dtype, target, loss_mask, feats,
+                                                                                scale, dpred, dpred_dtype);
+  return launch_status("mae_loss_bwd");
+}

@@ -1,0 +1,444 @@
+"""Differentiable front of `ops`: each function runs the forward kernel and, when a gradient is wanted,
+records a `torch.autograd.Function` whose backward is again only sm_100a kernels (GEMMs for dX / dW on the
+tcgen05 path, acai_layernorm_bwd, acai_attn_varlen_bwd, acai_ce_loss ...).  torch.autograd is used as the
+tape and for gradient accumulation into `.grad`; it never computes a gradient itself.
+
+Covers the training rows of SURVEY §8: teacher-forced ViTOMR (models.py:649-737 + OMRCELoss 784-796) and MAE
+pre-training (models.py:197-288).  With gradients disabled every function is a plain `ops` call, so the
+inference path is unchanged.
+
+Not differentiable here (raise instead of silently detaching): interpolated position embeddings (oversize
+images) and the second LayerNorm output used by the cached decoder.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+
+
+def needs_grad(*tensors) -> bool:
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)
+
+
+def _weights():
+    from .layers import WEIGHTS
+    return WEIGHTS
+
+
+def _slice(p, rows):
+    return p if (p is None or rows is None) else p[rows[0]:rows[1]]
+
+
+def _full_rows(grad_rows, like, rows):
+    """Gradient of a row slice -> gradient of the whole parameter."""
+    if rows is None:
+        return grad_rows
+    full = torch.zeros(like.shape, dtype=grad_rows.dtype, device=grad_rows.device)
+    full[rows[0]:rows[1]] = grad_rows
+    return full
+
+
+# ------------------------------------------------------------------------------------------ linear (+GELU, +residual)
+class _Linear(torch.autograd.Function):
+    """y = act(x W^T + b) + residual.   dX = dZ W,  dW = dZ^T X (fp32 out),  db = colsum(dZ),  dres = dY.
+    In training the GELU is not fused into the GEMM epilogue: the pre-activation z is kept for the backward."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, act, out_dtype, rows):
+        dt = x.dtype
+        K = x.shape[-1]
+        x2 = x.reshape(-1, K)
+        if x2.stride(-1) != 1:
+            x2 = x2.contiguous()
+        w = _weights().get(weight, dt, rows)
+        b = _slice(bias, rows)
+        b = b.detach() if b is not None else None
+        z = None
+        if act == ops.ACT_GELU:
+            if residual is not None:
+                raise ops.AcaiError("linear: GELU + residual is not used by the model")
+            z = ops.linear(x2, w, b, out_dtype=dt)
+            y = ops.gelu(z, out_dtype=out_dtype)
+        else:
+            y = ops.linear(x2, w, b, residual=residual.detach() if residual is not None else None, out_dtype=out_dtype)
+        ctx.save_for_backward(x2, weight, z)
+        ctx.rows, ctx.x_shape, ctx.has_bias = rows, x.shape, bias is not None
+        ctx.res_meta = (residual.shape, residual.dtype) if residual is not None else None
+        return y.view(*x.shape[:-1], y.shape[-1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, z = ctx.saved_tensors
+        dt, rows = x2.dtype, ctx.rows
+        N = dy.shape[-1]
+        dy2 = dy.reshape(-1, N)
+        if z is not None:
+            dz = ops.gelu_bwd(dy2, z, out_dtype=dt)
+        else:
+            dz = dy2 if dy2.dtype == dt else dy2.to(dt)
+            if not dz.is_contiguous():
+                dz = dz.contiguous()
+        dx = dw = db = dres = None
+        if ctx.needs_input_grad[0]:
+            wt = _weights().get_t(weight, dt, rows)                      # [K, N]
+            dx = ops.linear(dz, wt, out_dtype=dt).view(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            dzt, xt = ops.transpose_pad(dz), ops.transpose_pad(x2)       # [N, Mp], [K, Mp]: the token dim becomes K
+            dw = _full_rows(ops.linear(dzt, xt, out_dtype=torch.float32), weight, rows)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = ops.colsum(dz)
+            if rows is not None:
+                full = torch.zeros(weight.shape[0], dtype=torch.float32, device=db.device)
+                full[rows[0]:rows[1]] = db
+                db = full
+        if ctx.res_meta is not None and ctx.needs_input_grad[3]:
+            shape, rdt = ctx.res_meta
+            dres = dy.reshape(shape)
+            if dres.dtype != rdt:
+                dres = dres.to(rdt)
+        return dx, dw, db, dres, None, None, None
+
+
+def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None, rows=None):
+    """act(x @ weight[rows].T + bias[rows]) + residual; `weight` / `bias` are the (fp32 master) parameters."""
+    dt = x.dtype
+    if not needs_grad(x, weight, bias, residual):
+        return ops.linear(x, _weights().get(weight, dt, rows), _slice(bias, rows), act=act, residual=residual,
+                          out_dtype=out_dtype or dt)
+    return _Linear.apply(x, weight, bias, residual, act, out_dtype or dt, rows)
+
+
+# ------------------------------------------------------------------------------------------ LayerNorm
+class _LayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, eps, out_dtype):
+        y = ops.layernorm(x, gamma.detach(), beta.detach(), eps, residual=residual, out_dtype=out_dtype)
+        ctx.save_for_backward(x, residual, gamma)
+        ctx.eps = eps
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, residual, gamma = ctx.saved_tensors
+        dv, dg, db = ops.layernorm_bwd(dy, x, residual, gamma.detach(), ctx.eps, dv_dtype=x.dtype)
+        dres = None
+        if residual is not None and ctx.needs_input_grad[1]:
+            dres = dv if residual.dtype == dv.dtype else dv.to(residual.dtype)
+        return dv, dres, dg, db, None, None
+
+
+def layernorm(x, gamma, beta, eps, residual=None, out_dtype=None, out2_dtype=None):
+    if not needs_grad(x, residual, gamma, beta):
+        return ops.layernorm(x, gamma, beta, eps, residual=residual, out_dtype=out_dtype, out2_dtype=out2_dtype)
+    if out2_dtype is not None:
+        raise ops.AcaiError("layernorm: the two-output form is inference-only")
+    return _LayerNorm.apply(x, residual, gamma, beta, eps, out_dtype or x.dtype)
+
+
+# ------------------------------------------------------------------------------------------ attention
+class _SelfAttention(torch.autograd.Function):
+    """Packed ragged self-attention over a fused [T, 3D] QKV buffer; backward fills one d(QKV) buffer."""
+
+    @staticmethod
+    def forward(ctx, qkv, cu, max_len, heads, head_dim, causal, flops):
+        D = heads * head_dim
+        out, lse = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], cu, cu, max_len, heads, head_dim,
+                                   causal=causal, out_dtype=qkv.dtype, flops=flops, return_lse=True)
+        ctx.save_for_backward(qkv, out, lse, cu)
+        ctx.meta = (max_len, heads, head_dim, causal)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse, cu = ctx.saved_tensors
+        max_len, heads, head_dim, causal = ctx.meta
+        D = heads * head_dim
+        dqkv = torch.empty_like(qkv)
+        ops.attn_varlen_bwd(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], out, dout, lse, cu, cu, max_len, max_len, heads,
+                            head_dim, causal, dqkv[:, :D], dqkv[:, D:2 * D], dqkv[:, 2 * D:])
+        return dqkv, None, None, None, None, None, None
+
+
+class _CrossAttention(torch.autograd.Function):
+    """q:[Tq, D] against a fused [Tk, 2D] K|V buffer (kv_caching.py:241-245 layout)."""
+
+    @staticmethod
+    def forward(ctx, q, kv, cu_q, cu_k, max_q, max_k, heads, head_dim, flops):
+        D = heads * head_dim
+        out, lse = ops.attn_varlen(q, kv[:, :D], kv[:, D:], cu_q, cu_k, max_q, heads, head_dim, causal=False,
+                                   out_dtype=q.dtype, flops=flops, return_lse=True)
+        ctx.save_for_backward(q, kv, out, lse, cu_q, cu_k)
+        ctx.meta = (max_q, max_k, heads, head_dim)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q, kv, out, lse, cu_q, cu_k = ctx.saved_tensors
+        max_q, max_k, heads, head_dim = ctx.meta
+        D = heads * head_dim
+        dq, dkv = torch.empty_like(q), torch.empty_like(kv)
+        ops.attn_varlen_bwd(q, kv[:, :D], kv[:, D:], out, dout, lse, cu_q, cu_k, max_q, max_k, heads, head_dim, False,
+                            dq, dkv[:, :D], dkv[:, D:])
+        return dq, dkv, None, None, None, None, None, None, None
+
+
+def self_attention(qkv, pk, heads, head_dim, causal, flops=0.0):
+    D = heads * head_dim
+    if not needs_grad(qkv):
+        return ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pk.cu, pk.cu, pk.max_len, heads, head_dim,
+                               causal=causal, out_dtype=qkv.dtype, flops=flops)
+    return _SelfAttention.apply(qkv, pk.cu, pk.max_len, heads, head_dim, causal, flops)
+
+
+def cross_attention(q, kv, pq, pk, heads, head_dim, flops=0.0):
+    D = heads * head_dim
+    if not needs_grad(q, kv):
+        return ops.attn_varlen(q, kv[:, :D], kv[:, D:], pq.cu, pk.cu, pq.max_len, heads, head_dim, causal=False,
+                               out_dtype=q.dtype, flops=flops)
+    return _CrossAttention.apply(q, kv, pq.cu, pk.cu, pq.max_len, pk.max_len, heads, head_dim, flops)
+
+
+# ------------------------------------------------------------------------------------------ packed <-> padded
+class _Unpack(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, packed, cu, batch, max_len, fill, out_dtype):
+        ctx.save_for_backward(cu)
+        ctx.meta = (packed.shape[0], packed.dtype)
+        return ops.unpack_padded(packed, cu, batch, max_len, fill=fill, out_dtype=out_dtype)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (cu,) = ctx.saved_tensors
+        total, dt = ctx.meta
+        return ops.pack_padded(dout, cu, total, out_dtype=dt), None, None, None, None, None
+
+
+class _Pack(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, padded, cu, total, out_dtype):
+        ctx.save_for_backward(cu)
+        ctx.meta = (padded.shape[0], padded.shape[1], padded.dtype)
+        return ops.pack_padded(padded, cu, total, out_dtype=out_dtype)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (cu,) = ctx.saved_tensors
+        B, L, dt = ctx.meta
+        return ops.unpack_padded(dout, cu, B, L, out_dtype=dt), None, None, None
+
+
+def unpack_padded(packed, cu, batch, max_len, fill=None, out_dtype=None):
+    """Padding rows are constants (`fill`) of the forward: they carry no gradient, as in the reference where
+    they are masked out of every attention and of the loss."""
+    if not needs_grad(packed):
+        return ops.unpack_padded(packed, cu, batch, max_len, fill=fill, out_dtype=out_dtype)
+    return _Unpack.apply(packed, cu, batch, max_len, fill.detach() if fill is not None else None, out_dtype)
+
+
+def pack_padded(padded, cu, total, out_dtype=None):
+    if not needs_grad(padded):
+        return ops.pack_padded(padded, cu, total, out_dtype=out_dtype)
+    return _Pack.apply(padded, cu, total, out_dtype)
+
+
+# ------------------------------------------------------------------------------------------ token embedding
+class _EmbedTokens(torch.autograd.Function):
+    """table[ids] + pos[t] for (B, T) ids (models.py:466-470).  d(table) by row scatter-add (padding_idx rows get
+    none, as nn.Embedding); d(pos[:T]) is the fixed-order sum over the batch."""
+
+    @staticmethod
+    def forward(ctx, ids, table, pos, out_dtype, padding_idx):
+        B, T = ids.shape
+        out = ops.embed_tokens(ids, table.detach(), pos.detach(), out_dtype, period=T)
+        ctx.save_for_backward(ids)
+        ctx.meta = (table.shape, pos.shape, padding_idx)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        tshape, pshape, padding_idx = ctx.meta
+        B, T = ids.shape
+        dim = tshape[1]
+        dtab = dpos = None
+        if ctx.needs_input_grad[1]:
+            idx = ids.reshape(-1).long()
+            if padding_idx is not None:
+                idx = torch.where(idx == padding_idx, torch.full_like(idx, -1), idx)
+            dtab = ops.scatter_add_rows(dout.reshape(-1, dim), idx, torch.zeros(tshape, dtype=torch.float32, device=dout.device))
+        if ctx.needs_input_grad[2]:
+            dpos = torch.zeros(pshape, dtype=torch.float32, device=dout.device)
+            ops.colsum(dout.reshape(B, T * dim), out=dpos.view(-1)[: T * dim])
+        return None, dtab, dpos, None, None
+
+
+def embed_tokens(ids, table, pos, out_dtype, padding_idx=None):
+    if not needs_grad(table, pos):
+        return ops.embed_tokens(ids, table, pos, out_dtype, period=ids.shape[1])
+    return _EmbedTokens.apply(ids, table, pos, out_dtype, padding_idx)
+
+
+# ------------------------------------------------------------------------------------------ patch embedding
+class PatchGeometry:
+    """Everything the patch-embedding kernels need about one ragged image batch (no arithmetic)."""
+
+    def __init__(self, imgs, descs, pk, patch_size, channels, dims, patch_index=None):
+        self.imgs, self.descs, self.pk, self.P, self.C, self.dims, self.patch_index = imgs, descs, pk, patch_size, channels, dims, patch_index
+
+    def row_tables(self, pe_w, device):
+        """Per output row: (row of the un-gathered patch matrix, row of the flattened position table)."""
+        from .layers import Packed
+        full_lens = [h * w for h, w in self.dims]
+        full = Packed(full_lens, device)
+        lens = torch.tensor(self.pk.lens, device=device)
+        img = torch.repeat_interleave(torch.arange(len(self.dims), device=device), lens)
+        if self.patch_index is not None:
+            p = self.patch_index.to(device=device, dtype=torch.int64)
+        else:
+            p = torch.arange(self.pk.total, device=device) - self.pk.cu.long()[img]
+        wp = torch.tensor([w for _, w in self.dims], device=device)[img]
+        return full, full.cu.long()[img] + p, (p // wp) * pe_w + p % wp
+
+
+class _PatchEmbed(torch.autograd.Function):
+    """K1: rows = patches W^T + b + PE[row, col] (models.py:36-66).  Backward: dW = dY^T patches (GEMM),
+    db = colsum(dY), dPE by row scatter-add.  Images carry no gradient."""
+
+    @staticmethod
+    def forward(ctx, weight, bias, pos_embedding, geom, out_dtype):
+        out = ops.patch_embed(geom.imgs, geom.descs, geom.pk.cu, geom.pk.total, geom.P, geom.C, weight.detach(),
+                              bias.detach() if bias is not None else None, pos_embedding.detach(), False, out_dtype,
+                              patch_index=geom.patch_index)
+        ctx.geom, ctx.shapes = geom, (weight.shape, pos_embedding.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        geom = ctx.geom
+        wshape, pshape = ctx.shapes
+        dev, dt = dy.device, dy.dtype
+        dy = dy.contiguous()
+        dw = db = dpe = None
+        full, patch_row, pe_row = geom.row_tables(pshape[1], dev)
+        if ctx.needs_input_grad[0]:
+            patches = ops.patchify(geom.imgs, geom.descs, full.cu, full.total, geom.P, geom.C, out_dtype=dt)
+            if geom.patch_index is not None:
+                patches = ops.gather_rows(patches, patch_row)
+            dw = ops.linear(ops.transpose_pad(dy), ops.transpose_pad(patches), out_dtype=torch.float32)
+        if ctx.needs_input_grad[1]:
+            db = ops.colsum(dy)
+        if ctx.needs_input_grad[2]:
+            dpe = torch.zeros(pshape, dtype=torch.float32, device=dev)
+            ops.scatter_add_rows(dy, pe_row, dpe.view(-1, pshape[-1]))
+        return dw, db, dpe, None, None
+
+
+def patch_embed(geom: PatchGeometry, weight, bias, pos_embedding, interpolate, out_dtype):
+    if not needs_grad(weight, bias, pos_embedding):
+        return ops.patch_embed(geom.imgs, geom.descs, geom.pk.cu, geom.pk.total, geom.P, geom.C, weight, bias, pos_embedding,
+                               interpolate, out_dtype, patch_index=geom.patch_index)
+    if interpolate:
+        raise ops.AcaiError("patch_embed: training through an interpolated position grid (oversize image) is not implemented")
+    return _PatchEmbed.apply(weight, bias, pos_embedding, geom, out_dtype)
+
+
+# ------------------------------------------------------------------------------------------ MAE restore
+class _MaeRestore(torch.autograd.Function):
+    """MAE.prepare_for_decoder on packed rows (models.py:219-241): out[b, i] = (r < keep_b ? latent[b, r] : mask_token)
+    + dec_PE[i // w, i % w] with r = ids_restore[b][i]."""
+
+    @staticmethod
+    def forward(ctx, latent, mask_token, dec_pe, cu_keep, cu_full, ids_restore, wps, total_rows, out_dtype):
+        out = ops.mae_restore(latent, cu_keep, cu_full, ids_restore, wps, total_rows, mask_token.detach(), dec_pe.detach(),
+                              out_dtype)
+        ctx.save_for_backward(cu_keep, cu_full, ids_restore, wps)
+        ctx.meta = (latent.shape, latent.dtype, mask_token.shape, dec_pe.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        cu_keep, cu_full, ids_restore, wps = ctx.saved_tensors
+        lshape, ldt, mshape, pshape = ctx.meta
+        dev = dout.device
+        dout = dout.contiguous()
+        total = dout.shape[0]
+        cuk, cuf = cu_keep.long(), cu_full.long()
+        img = torch.repeat_interleave(torch.arange(cuf.numel() - 1, device=dev), cuf[1:] - cuf[:-1])
+        i = torch.arange(total, device=dev) - cuf[img]
+        r = ids_restore.long()
+        kept = r < (cuk[1:] - cuk[:-1])[img]
+        src = torch.full((lshape[0] + 1,), -1, dtype=torch.int64, device=dev)      # last slot swallows the masked rows
+        src[torch.where(kept, cuk[img] + r, torch.full_like(r, lshape[0]))] = torch.arange(total, device=dev)
+        src = src[:-1]
+        dlat = dmask = dpe = None
+        d_kept = ops.gather_rows(dout, src, out_dtype=ldt)                  # also the kept share of sum(dout)
+        if ctx.needs_input_grad[0]:
+            dlat = d_kept
+        if ctx.needs_input_grad[1]:
+            dmask = (ops.colsum(dout) - ops.colsum(d_kept)).view(mshape)
+        if ctx.needs_input_grad[2]:
+            wp = wps.long()[img]
+            dpe = torch.zeros(pshape, dtype=torch.float32, device=dev)
+            ops.scatter_add_rows(dout, (i // wp) * pshape[1] + i % wp, dpe.view(-1, pshape[-1]))
+        return dlat, dmask, dpe, None, None, None, None, None, None
+
+
+def mae_restore(latent, cu_keep, cu_full, ids_restore, wps, total_rows, mask_token, dec_pe, out_dtype):
+    if not needs_grad(latent, mask_token, dec_pe):
+        return ops.mae_restore(latent, cu_keep, cu_full, ids_restore, wps, total_rows, mask_token, dec_pe, out_dtype)
+    return _MaeRestore.apply(latent, mask_token, dec_pe, cu_keep, cu_full, ids_restore, wps, total_rows, out_dtype)
+
+
+# ------------------------------------------------------------------------------------------ losses
+class _CELoss(torch.autograd.Function):
+    """OMRCELoss (models.py:784-796), label_smoothing 0: mean over non-pad targets of -log softmax(logits)[target]."""
+
+    @staticmethod
+    def forward(ctx, logits, targets, ignore_index, normaliser):
+        sums = ops.ce_loss(logits, targets, ignore_index)
+        denom = sums[1] if normaliser is None else normaliser
+        ctx.save_for_backward(logits, targets, denom)
+        ctx.ignore_index = ignore_index
+        ctx.mark_non_differentiable(sums)
+        return sums[0] / denom, sums
+
+    @staticmethod
+    def backward(ctx, g, _gs):
+        logits, targets, denom = ctx.saved_tensors
+        scale = (g.float() / denom).reshape(1).contiguous()
+        return ops.ce_loss(logits, targets, ctx.ignore_index, dlogits_scale=scale, dlogits_dtype=logits.dtype), None, None, None
+
+
+def ce_loss(logits, targets, ignore_index, normaliser=None):
+    """-> (loss, sums = [sum of token losses, token count]).  `normaliser` (1-element device tensor) replaces the local
+    count, e.g. the global token count divided by the world size under data parallelism."""
+    if not needs_grad(logits):
+        sums = ops.ce_loss(logits, targets, ignore_index)
+        return sums[0] / (sums[1] if normaliser is None else normaliser), sums
+    return _CELoss.apply(logits, targets, ignore_index, normaliser)
+
+
+class _MAELoss(torch.autograd.Function):
+    """MAELoss (models.py:271-288): mean over masked patches of mean_f (pred - normalised target)^2."""
+
+    @staticmethod
+    def forward(ctx, pred, loss_mask, target, normaliser):
+        sums, _ = ops.mae_loss(pred, loss_mask, target)
+        denom = sums[1] if normaliser is None else normaliser
+        ctx.save_for_backward(pred, loss_mask, target, denom)
+        ctx.mark_non_differentiable(sums)
+        return sums[0] / denom, sums
+
+    @staticmethod
+    def backward(ctx, g, _gs):
+        pred, loss_mask, target, denom = ctx.saved_tensors
+        scale = (g.float() / denom).reshape(1).contiguous()
+        return ops.mae_loss_bwd(pred, loss_mask, target, scale, dpred_dtype=pred.dtype), None, None, None
+
+
+def mae_loss(pred, loss_mask, target, normaliser=None):
+    if not needs_grad(pred):
+        sums, _ = ops.mae_loss(pred, loss_mask, target)
+        return sums[0] / (sums[1] if normaliser is None else normaliser), sums
+    return _MAELoss.apply(pred, loss_mask, target, normaliser)

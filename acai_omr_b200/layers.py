@@ -16,6 +16,7 @@ import math
 import torch
 from torch import nn
 
+from . import functional as F
 from . import ops
 
 
@@ -46,6 +47,17 @@ class _WeightCache:
         self._store[key] = (ver, t)
         return t
 
+    def get_t(self, p: torch.Tensor, dtype: torch.dtype, rows=None):
+        """Transposed copy [in, out] of (a row slice of) `p` in `dtype`: the B operand of dX = dY W."""
+        key = (id(p), dtype, rows, "T")
+        hit = self._store.get(key)
+        ver = (p._version, p.data_ptr())
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        t = ops.transpose_pad(self.get(p, dtype, rows), pad_to=1)
+        self._store[key] = (ver, t)
+        return t
+
     def clear(self):
         self._store.clear()
 
@@ -65,15 +77,15 @@ class Linear(nn.Linear):
         dt = compute_dtype()
         if x.dtype != dt:
             x = x.to(dt)
-        return ops.linear(x, w_(self.weight, dt), self.bias, act=act, residual=residual, out_dtype=out_dtype or dt)
+        return F.linear(x, self.weight, self.bias, act=act, residual=residual, out_dtype=out_dtype or dt)
 
 
 class LayerNorm(nn.LayerNorm):
     """nn.LayerNorm parameters; forward = acai_layernorm_fwd (optionally fused residual add)."""
 
     def forward(self, x, residual=None, out_dtype=None, out2_dtype=None):
-        return ops.layernorm(x, self.weight, self.bias, self.eps, residual=residual,
-                             out_dtype=out_dtype or x.dtype, out2_dtype=out2_dtype)
+        return F.layernorm(x, self.weight, self.bias, self.eps, residual=residual,
+                           out_dtype=out_dtype or x.dtype, out2_dtype=out2_dtype)
 
 
 class MultiheadAttention(nn.Module):
@@ -100,24 +112,22 @@ class MultiheadAttention(nn.Module):
     def self_attention_packed(self, x, pk, causal, residual):
         """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D]."""
         dt, D = x.dtype, self.embed_dim
-        qkv = ops.linear(x, w_(self.in_proj_weight, dt), self.in_proj_bias, out_dtype=dt)
-        a = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pk.cu, pk.cu, pk.max_len, self.num_heads,
-                            self.head_dim, causal=causal, out_dtype=dt,
-                            flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0))
-        return ops.linear(a, w_(self.out_proj.weight, dt), self.out_proj.bias, residual=residual, out_dtype=dt)
+        qkv = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt)
+        a = F.self_attention(qkv, pk, self.num_heads, self.head_dim, causal,
+                             flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0))
+        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt)
 
     def project_memory_packed(self, mem):
         """[K | V] = mem . W_kv^T + b_kv  (kv_caching.py:241-245) over packed memory rows."""
         dt, D = mem.dtype, self.embed_dim
-        return ops.linear(mem, w_(self.in_proj_weight, dt, rows=(D, 3 * D)), self.in_proj_bias[D:], out_dtype=dt)
+        return F.linear(mem, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(D, 3 * D))
 
     def cross_attention_packed(self, x, kv, pq, pk, residual):
         dt, D = x.dtype, self.embed_dim
-        q = ops.linear(x, w_(self.in_proj_weight, dt, rows=(0, D)), self.in_proj_bias[:D], out_dtype=dt)
-        a = ops.attn_varlen(q, kv[:, :D], kv[:, D:], pq.cu, pk.cu, pq.max_len, self.num_heads, self.head_dim,
-                            causal=False, out_dtype=dt,
-                            flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)))
-        return ops.linear(a, w_(self.out_proj.weight, dt), self.out_proj.bias, residual=residual, out_dtype=dt)
+        q = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(0, D))
+        a = F.cross_attention(q, kv, pq, pk, self.num_heads, self.head_dim,
+                              flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)))
+        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt)
 
 
 class Packed:
@@ -182,8 +192,8 @@ class TransformerEncoderLayer(nn.Module):
         dt = x.dtype
         y = self.self_attn.self_attention_packed(x, pk, False, residual=x)
         x = self.norm1(y, out_dtype=dt)
-        h = ops.linear(x, w_(self.linear1.weight, dt), self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
-        y = ops.linear(h, w_(self.linear2.weight, dt), self.linear2.bias, residual=x, out_dtype=dt)
+        h = F.linear(x, self.linear1.weight, self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+        y = F.linear(h, self.linear2.weight, self.linear2.bias, residual=x, out_dtype=dt)
         return self.norm2(y, out_dtype=dt)
 
 
@@ -221,10 +231,10 @@ class TransformerEncoder(nn.Module):
         B, L, D = src.shape
         pk = Packed(lens_from_mask(src_key_padding_mask, B, L), src.device)
         dt = compute_dtype()
-        x = ops.pack_padded(src, pk.cu, pk.total, out_dtype=dt)
+        x = F.pack_padded(src, pk.cu, pk.total, out_dtype=dt)
         x = self.forward_packed(x, pk, final_dtype=torch.float32 if self.norm is not None else None)
         fill = self.norm.bias if (self.norm is not None and not self.training) else None
-        return ops.unpack_padded(x, pk.cu, B, L, fill=fill)
+        return F.unpack_padded(x, pk.cu, B, L, fill=fill)
 
 
 class TransformerDecoderLayer(nn.Module):
@@ -252,8 +262,8 @@ class TransformerDecoderLayer(nn.Module):
 
     def mlp_packed(self, x):
         dt = x.dtype
-        h = ops.linear(x, w_(self.linear1.weight, dt), self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
-        y = ops.linear(h, w_(self.linear2.weight, dt), self.linear2.bias, residual=x, out_dtype=dt)
+        h = F.linear(x, self.linear1.weight, self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+        y = F.linear(h, self.linear2.weight, self.linear2.bias, residual=x, out_dtype=dt)
         return self.norm3(y, out_dtype=dt)
 
     def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True):
@@ -296,11 +306,11 @@ class TransformerDecoder(nn.Module):
         tp = Packed(lens_from_mask(tgt_key_padding_mask, B, T), tgt.device)
         mp = Packed(lens_from_mask(memory_key_padding_mask, B, S), tgt.device)
         dt = compute_dtype()
-        x = ops.pack_padded(tgt, tp.cu, tp.total, out_dtype=dt)
-        mem = ops.pack_padded(memory, mp.cu, mp.total, out_dtype=dt)
+        x = F.pack_padded(tgt, tp.cu, tp.total, out_dtype=dt)
+        mem = F.pack_padded(memory, mp.cu, mp.total, out_dtype=dt)
         x = self.forward_packed(x, tp, mem, mp, causal=tgt_mask is not None or bool(tgt_is_causal),
                                 final_dtype=torch.float32 if self.norm is not None else None)
-        return ops.unpack_padded(x, tp.cu, B, T)
+        return F.unpack_padded(x, tp.cu, B, T)
 
 
 def gelu_mlp_head(x, lin_a: Linear, lin_b: Linear, out_dtype=None):
@@ -308,8 +318,8 @@ def gelu_mlp_head(x, lin_a: Linear, lin_b: Linear, out_dtype=None):
     dt = compute_dtype()
     if x.dtype != dt:
         x = x.to(dt)
-    h = ops.linear(x, w_(lin_a.weight, dt), lin_a.bias, act=ops.ACT_GELU, out_dtype=dt)
-    return ops.linear(h, w_(lin_b.weight, dt), lin_b.bias, out_dtype=out_dtype or dt)
+    h = F.linear(x, lin_a.weight, lin_a.bias, act=ops.ACT_GELU, out_dtype=dt)
+    return F.linear(h, lin_b.weight, lin_b.bias, out_dtype=out_dtype or dt)
 
 
 SQRT_HALF = 1.0 / math.sqrt(2.0)

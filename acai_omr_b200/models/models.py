@@ -14,6 +14,7 @@ import re
 import torch
 from torch import nn
 
+from .. import functional as F
 from .. import ops
 from ..config import LMX_BOS_TOKEN, LMX_EOS_TOKEN, LMX_PAD_TOKEN
 from ..layers import (LayerNorm, Linear, Packed, TransformerDecoder, TransformerDecoderLayer, TransformerEncoder,
@@ -67,21 +68,21 @@ class Encoder(nn.Module):
         """K1: ragged images -> (packed rows [sum L, E], Packed).  `keep`: optional (lens, patch_index) for MAE."""
         imgs = self._image_list(x)
         P = self.patch_size
-        lens, oversize = [], False
+        lens, dims, oversize = [], [], False
         for t in imgs:
             h_p, w_p = t.shape[-2] // P, t.shape[-1] // P
             self._grid_check(h_p, w_p)
             oversize |= h_p > self.pe_max_height or w_p > self.pe_max_width
             lens.append(h_p * w_p)
+            dims.append((h_p, w_p))
         dev = self.pos_embedding.device
         patch_index = None
         if keep is not None:
             lens, patch_index = keep
         pk = Packed(lens, dev)
-        descs = ops.make_image_descs(imgs, P, dev)
-        out = ops.patch_embed(imgs, descs, pk.cu, pk.total, P, imgs[0].shape[0], self.projection.weight,
-                              self.projection.bias, self.pos_embedding, self._interpolate_pe and oversize,
-                              out_dtype or compute_dtype(), patch_index=patch_index)
+        geom = F.PatchGeometry(imgs, ops.make_image_descs(imgs, P, dev), pk, P, imgs[0].shape[0], dims, patch_index)
+        out = F.patch_embed(geom, self.projection.weight, self.projection.bias, self.pos_embedding,
+                            self._interpolate_pe and oversize, out_dtype or compute_dtype())
         return out, pk
 
     def _stacks(self):
@@ -100,7 +101,7 @@ class Encoder(nn.Module):
         """models.py:36-66: (B, L_m, E) embeddings (+PE) and the (B, L_m) True=padding mask.  Padding rows
         hold projection(0) = the projection bias, as in the reference."""
         h, pk = self.embed_packed(x)
-        emb = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self.projection.bias)
+        emb = F.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self.projection.bias)
         return emb, pk.mask(emb.device)
 
     def create_attention_mask(self, seq_lens, max_len):
@@ -116,7 +117,7 @@ class Encoder(nn.Module):
     def forward(self, x):
         """models.py:76-79 -> (x:(B,L_m,E), src_key_padding_mask:(B,L_m) True=padding)."""
         h, pk = self.encode_packed(x)
-        out = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
+        out = F.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
         mask = pk.mask(out.device)
         out._acai_packed = (h, pk)  # lets ViTOMR feed the decoder without re-packing
         return out, mask
@@ -174,7 +175,7 @@ class MAEEncoder(Encoder):
     def batchify(self, x, noises=None):
         """models.py:128-173 (padded API; same 8-tuple)."""
         h, pk, info = self.embed_masked_packed(x, noises)
-        emb = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self.projection.bias)
+        emb = F.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self.projection.bias)
         full = Packed(info["unmasked_seq_lens"], emb.device)
         return (emb, pk.mask(emb.device), full.mask(emb.device), info["kept_seq_lens"], info["unmasked_seq_lens"],
                 torch.nested.as_nested_tensor(info["seq_masks"], layout=torch.jagged),
@@ -188,7 +189,7 @@ class MAEEncoder(Encoder):
     def forward(self, x, noises=None):
         """models.py:176-180."""
         h, pk, info = self.encode_masked_packed(x, noises)
-        out = ops.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
+        out = F.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
         out._acai_packed = (h, pk, info)
         full = Packed(info["unmasked_seq_lens"], out.device)
         return (out, full.mask(out.device), info["kept_seq_lens"], info["unmasked_seq_lens"],
@@ -230,8 +231,8 @@ class MAE(nn.Module):
         full = Packed(info["unmasked_seq_lens"], dev)
         ids = torch.cat([r.to(dev) for r in info["ids_restore"]]).to(torch.int64).contiguous()
         wps = torch.tensor([w for _, w in info["patchified_dims"]], dtype=torch.int32).to(dev)
-        rows = ops.mae_restore(latent_packed, pk_keep.cu, full.cu, ids, wps, full.total, self.mask_token,
-                               self.decoder_pos_embedding, out_dtype)
+        rows = F.mae_restore(latent_packed, pk_keep.cu, full.cu, ids, wps, full.total, self.mask_token,
+                             self.decoder_pos_embedding, out_dtype)
         return rows, full
 
     def prepare_for_decoder(self, latent, kept_seq_lens, unmasked_seq_lens, batch_ids_restore, patchified_dims):
@@ -240,9 +241,9 @@ class MAE(nn.Module):
         pk = Packed(kept_seq_lens, dev)
         restore = batch_ids_restore.unbind() if hasattr(batch_ids_restore, "unbind") else list(batch_ids_restore)
         info = dict(unmasked_seq_lens=unmasked_seq_lens, ids_restore=list(restore), patchified_dims=patchified_dims)
-        packed = ops.pack_padded(latent, pk.cu, pk.total)
+        packed = F.pack_padded(latent, pk.cu, pk.total)
         rows, full = self._restore_packed(packed, pk, info, latent.dtype)
-        return ops.unpack_padded(rows, full.cu, full.batch, full.max_len)
+        return F.unpack_padded(rows, full.cu, full.batch, full.max_len)
 
     def forward(self, batch, noises=None):
         """models.py:249-269 -> (pred (N, L_m, C*P*P), loss_mask (N, L_m) bool, target (N, L_m, C*P*P))."""
@@ -257,7 +258,7 @@ class MAE(nn.Module):
         P = self.patch_size
         tgts = self.encoder._image_list(list(y))
         tgt_rows = ops.patchify(tgts, ops.make_image_descs(tgts, P, dev), full.cu, full.total, P, tgts[0].shape[0])
-        pred_p = ops.unpack_padded(pred, full.cu, full.batch, full.max_len)
+        pred_p = F.unpack_padded(pred, full.cu, full.batch, full.max_len)
         target_p = ops.unpack_padded(tgt_rows, full.cu, full.batch, full.max_len)
         loss_mask = torch.zeros((full.batch, full.max_len), dtype=torch.bool, device=dev)
         for i, m in enumerate(info["seq_masks"]):
@@ -269,8 +270,7 @@ class MAELoss(nn.Module):
     """models.py:271-288."""
 
     def forward(self, pred, loss_mask, target):
-        sums, _ = ops.mae_loss(pred, loss_mask, target)
-        return sums[0] / sums[1]
+        return F.mae_loss(pred, loss_mask, target)[0]
 
 
 class OMREncoder(Encoder):
@@ -325,7 +325,7 @@ class TransitionHead(nn.Sequential):
         # (the reference computes head(padding row) there; those rows are masked everywhere downstream)
         h, pk = packed
         hp = gelu_mlp_head(h, self[0], self[3])
-        out = ops.unpack_padded(hp, pk.cu, pk.batch, x.shape[1])
+        out = F.unpack_padded(hp, pk.cu, pk.batch, x.shape[1])
         out._acai_packed = (hp, pk)
         return out
 
@@ -382,7 +382,7 @@ class OMRDecoder(nn.Module):
             mem, mp = packed
             return (mem if mem.dtype == dt else mem.to(dt)), mp
         mp = Packed(lens, img_latent.device)
-        return ops.pack_padded(img_latent, mp.cu, mp.total, out_dtype=dt), mp
+        return F.pack_padded(img_latent, mp.cu, mp.total, out_dtype=dt), mp
 
     def _decode_packed(self, input_seqs, img_latent, tgt_lens, latent_attention_mask, token_idxs_input):
         B, T = input_seqs.shape[0], input_seqs.shape[1]
@@ -390,14 +390,15 @@ class OMRDecoder(nn.Module):
         dev = self.pos_embedding.device
         tp = Packed(tgt_lens, dev)
         if token_idxs_input:
-            x = ops.embed_tokens(input_seqs, self.vocab_embedding.weight, self.pos_embedding, dt, period=T)  # (B,T,D)
-            x = ops.pack_padded(x, tp.cu, tp.total)
+            x = F.embed_tokens(input_seqs, self.vocab_embedding.weight, self.pos_embedding, dt,
+                               padding_idx=self.vocab_embedding.padding_idx)  # (B,T,D)
+            x = F.pack_padded(x, tp.cu, tp.total)
         else:
             raise NotImplementedError("embedding-space inputs (scheduled sampling, models.py:833) are not implemented yet")
         mem, mp = self._memory_packed(img_latent, latent_attention_mask, dt)
         h = self.decoder_blocks.forward_packed(x, tp, mem, mp, causal=True)
-        logits = ops.linear(h, w_(self.unembed.weight, dt), self.unembed.bias, out_dtype=dt)
-        return ops.unpack_padded(logits, tp.cu, B, T)
+        logits = F.linear(h, self.unembed.weight, self.unembed.bias, out_dtype=dt)
+        return F.unpack_padded(logits, tp.cu, B, T)
 
     def forward(self, input_seqs, img_latent, lmx_attention_mask, latent_attention_mask, token_idxs_input=True,
                 checkpoint_grads=False):
@@ -597,6 +598,20 @@ class TeacherForcedViTOMR(ViTOMR):
         param_groups.append({"params": (p for p in [self.encoder.pos_embedding]), "lr": min_layer_lr})
         param_groups.append({"params": self.encoder.projection.parameters(), "lr": min_layer_lr})
         return param_groups, layer_lrs
+
+
+class OMRCELoss(nn.Module):
+    """models.py:784-796: token-level cross entropy over non-pad targets (acai_ce_loss forward + backward)."""
+
+    def __init__(self, pad_idx, label_smoothing=0.0):
+        super().__init__()
+        if label_smoothing != 0.0:
+            raise NotImplementedError("label_smoothing != 0 is not implemented (the reference trains with 0.0, "
+                                      "omr_teacher_force_train.py:48)")
+        self.pad_idx, self.label_smoothing = pad_idx, label_smoothing
+
+    def forward(self, pred, target_seqs):
+        return F.ce_loss(pred, target_seqs.to(pred.device), self.pad_idx)[0]
 
 
 def default_vocab_path():

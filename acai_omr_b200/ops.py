@@ -174,7 +174,8 @@ def layernorm(x, gamma, beta, eps, residual=None, out_dtype=None, out2_dtype=Non
     return out if out2 is None else (out, out2.view(x.shape))
 
 
-def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_dtype=None, scale=None, flops=0.0):
+def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_dtype=None, scale=None, flops=0.0,
+                return_lse=False):
     """Packed ragged attention.  q:[Tq, >=H*d] k,v:[Tk, >=H*d] row-strided views (acai_attn_varlen_fwd)."""
     _cuda(q, k, v, cu_q, cu_k)
     if not (q.dtype == k.dtype == v.dtype):
@@ -185,12 +186,13 @@ def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_d
     out_dtype = out_dtype or q.dtype
     D = heads * head_dim
     out = torch.empty((q.shape[0], D), dtype=out_dtype, device=q.device)
+    lse = torch.empty((heads, q.shape[0]), dtype=torch.float32, device=q.device) if return_lse else None
     lib = _lib.load()
     _call("acai_attn_varlen_fwd", lib.acai_attn_varlen_fwd, _p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0), v.stride(0),
                                         _p(cu_q), _p(cu_k), cu_q.numel() - 1, int(max_q), q.shape[0], k.shape[0], heads, head_dim,
                                         1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
-                                        _p(out), _DT[out_dtype], D, _stream(), flops=flops)
-    return out
+                                        _p(out), _DT[out_dtype], D, _p(lse), _stream(), flops=flops)
+    return (out, lse) if return_lse else out
 
 
 def patch_embed(images, descs_dev, cu_seqlens, total_tokens, patch_size, channels, weight, bias, pos_embedding,
@@ -398,3 +400,147 @@ def mae_loss(pred, loss_mask, target):
           _p(sums), _stream())
     _bump()
     return sums, row_loss
+
+
+# ------------------------------------------------------------------------------------------ training building blocks
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+
+
+def transpose_pad(x, pad_to=64):
+    """[R, C] -> [C, ceil(R / pad_to) * pad_to] with zero padding (acai_transpose): the K-major operand of dW = dY^T X."""
+    _cuda(x)
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    R, Cc = x.shape
+    Rp = (R + pad_to - 1) // pad_to * pad_to
+    out = torch.empty((Cc, Rp), dtype=x.dtype, device=x.device)
+    _call("acai_transpose", _lib.load().acai_transpose, _p(x), _dt(x), x.stride(0), R, Cc, _p(out), Rp, _stream(),
+          nbytes=2.0 * x.element_size() * R * Cc)
+    return out
+
+
+def colsum(x, out=None, accumulate=False):
+    """fp32 column sums of a 2-D tensor in a fixed order (acai_colsum)."""
+    _cuda(x, out)
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    R, Cc = x.shape
+    if out is None:
+        out = torch.empty(Cc, dtype=torch.float32, device=x.device)
+    lib = _lib.load()
+    ws = _ws(lib.acai_colsum_workspace_bytes(R, Cc), x.device)
+    _call("acai_colsum", lib.acai_colsum, _p(x), _dt(x), x.stride(0), R, Cc, _p(out), 1 if accumulate else 0, _p(ws),
+          ws.numel(), _stream())
+    _bump()
+    return out
+
+
+def gelu(z, out_dtype=None):
+    _cuda(z)
+    z = z.contiguous()
+    out = torch.empty(z.shape, dtype=out_dtype or z.dtype, device=z.device)
+    _call("acai_gelu_fwd", _lib.load().acai_gelu_fwd, _p(z), _dt(z), _p(out), _dt(out), z.numel(), _stream())
+    return out
+
+
+def gelu_bwd(dy, z, out_dtype=None):
+    _cuda(dy, z)
+    dy, z = dy.contiguous(), z.contiguous()
+    dz = torch.empty(z.shape, dtype=out_dtype or z.dtype, device=z.device)
+    _call("acai_gelu_bwd", _lib.load().acai_gelu_bwd, _p(dy), _dt(dy), _p(z), _dt(z), _p(dz), _dt(dz), z.numel(), _stream())
+    return dz
+
+
+def layernorm_bwd(dy, x, residual, gamma, eps, dv_dtype=None):
+    """-> (dv [rows, cols], dgamma fp32, dbeta fp32) for y = LN(x + residual) * gamma + beta."""
+    _cuda(dy, x, residual, gamma)
+    cols = x.shape[-1]
+    x2, dy2 = x.reshape(-1, cols).contiguous(), dy.reshape(-1, cols).contiguous()
+    r2 = residual.reshape(-1, cols).contiguous() if residual is not None else None
+    rows = x2.shape[0]
+    dv = torch.empty((rows, cols), dtype=dv_dtype or x.dtype, device=x.device)
+    dg = torch.empty(cols, dtype=torch.float32, device=x.device)
+    db = torch.empty(cols, dtype=torch.float32, device=x.device)
+    lib = _lib.load()
+    ws = _ws(lib.acai_layernorm_bwd_workspace_bytes(rows, cols), x.device)
+    _call("acai_layernorm_bwd", lib.acai_layernorm_bwd, _p(dy2), _dt(dy2), _p(x2), _dt(x2), _p(r2),
+          _dt(r2) if r2 is not None else 0, _p(_f32c(gamma)), float(eps), _p(dv), _dt(dv), _p(dg), _p(db), 0, rows, cols,
+          _p(ws), ws.numel(), _stream())
+    _bump(2)
+    return dv.view(x.shape), dg, db
+
+
+def attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, max_q, max_k, heads, head_dim, causal, dq, dk, dv, scale=None):
+    """Writes dq/dk/dv (row-strided 2-D views, e.g. slices of a fused d(QKV) buffer) - acai_attn_varlen_bwd."""
+    _cuda(q, k, v, out, dout, lse, cu_q, cu_k, dq, dk, dv)
+    dout = dout if dout.stride(1) == 1 else dout.contiguous()
+    if dout.dtype != q.dtype:
+        dout = dout.to(q.dtype)
+    delta = torch.empty(heads * q.shape[0], dtype=torch.float32, device=q.device)
+    _call("acai_attn_varlen_bwd", _lib.load().acai_attn_varlen_bwd, _p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0),
+          v.stride(0), _p(out), out.stride(0), _p(dout), dout.stride(0), _p(lse), _p(cu_q), _p(cu_k), cu_q.numel() - 1,
+          int(max_q), int(max_k), q.shape[0], heads, head_dim, 1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
+          _p(dq), _p(dk), _p(dv), _dt(dq), dq.stride(0), dk.stride(0), dv.stride(0), _p(delta), _stream())
+    _bump(2)
+
+
+def ce_loss(logits, targets, ignore_index, dlogits_scale=None, dlogits_dtype=None):
+    """OMRCELoss pieces (acai_ce_loss).  Forward (dlogits_scale None): returns sums[2] = {sum, count}.
+    Backward (dlogits_scale = 1-element fp32 device tensor): returns dlogits = scale * (softmax - onehot)."""
+    _cuda(logits, targets, dlogits_scale)
+    V = logits.shape[-1]
+    l2 = logits.reshape(-1, V)
+    if l2.stride(1) != 1:
+        l2 = l2.contiguous()
+    t = targets.reshape(-1).to(torch.int64).contiguous()
+    rows = l2.shape[0]
+    lib = _lib.load()
+    if dlogits_scale is None:
+        row_loss = torch.empty(rows, dtype=torch.float32, device=logits.device)
+        valid = torch.empty(rows, dtype=torch.uint8, device=logits.device)
+        sums = torch.empty(2, dtype=torch.float32, device=logits.device)
+        _call("acai_ce_loss", lib.acai_ce_loss, _p(l2), _dt(l2), l2.stride(0), _p(t), rows, V, int(ignore_index), _p(row_loss),
+              _p(valid), _p(sums), None, 0, 0, None, _stream())
+        _bump()
+        return sums
+    dl = torch.empty((rows, V), dtype=dlogits_dtype or logits.dtype, device=logits.device)
+    _call("acai_ce_loss", lib.acai_ce_loss, _p(l2), _dt(l2), l2.stride(0), _p(t), rows, V, int(ignore_index), None, None, None,
+          _p(dl), _dt(dl), V, _p(dlogits_scale), _stream())
+    return dl.view(logits.shape)
+
+
+def scatter_add_rows(src, index, dst, scale=1.0):
+    """dst[index[r]] += scale * src[r] (fp32 dst, rows with index < 0 skipped) - acai_scatter_add_rows."""
+    _cuda(src, index, dst)
+    dim = src.shape[-1]
+    s2 = src.reshape(-1, dim)
+    if s2.stride(1) != 1:
+        s2 = s2.contiguous()
+    idx = index.reshape(-1).to(torch.int64).contiguous()
+    _call("acai_scatter_add_rows", _lib.load().acai_scatter_add_rows, _p(s2), _dt(s2), s2.stride(0), _p(idx), s2.shape[0], dim,
+          _p(dst), float(scale), _stream())
+    return dst
+
+
+def gather_rows(src, index, out_dtype=None):
+    """out[r] = src[index[r]] (0 where index < 0) - acai_gather_rows."""
+    _cuda(src, index)
+    dim = src.shape[-1]
+    s2 = src.reshape(-1, dim).contiguous()
+    idx = index.reshape(-1).to(torch.int64).contiguous()
+    out = torch.empty((idx.numel(), dim), dtype=out_dtype or src.dtype, device=src.device)
+    _call("acai_gather_rows", _lib.load().acai_gather_rows, _p(s2), _dt(s2), _p(idx), idx.numel(), dim, _p(out), _dt(out), _stream())
+    return out
+
+
+def mae_loss_bwd(pred, loss_mask, target, scale, dpred_dtype=None):
+    _cuda(pred, loss_mask, target, scale)
+    feats = pred.shape[-1]
+    p2 = pred.reshape(-1, feats).contiguous()
+    t2 = target.reshape(-1, feats).float().contiguous()
+    m2 = loss_mask.reshape(-1).to(torch.uint8).contiguous()
+    dp = torch.empty(p2.shape, dtype=dpred_dtype or pred.dtype, device=pred.device)
+    _call("acai_mae_loss_bwd", _lib.load().acai_mae_loss_bwd, _p(p2), _dt(p2), _p(t2), _p(m2), p2.shape[0], feats, _p(scale),
+          _p(dp), _dt(dp), _stream())
+    return dp.view(pred.shape)

@@ -106,7 +106,23 @@ int acai_attn_varlen_fwd(const void* q, const void* k, const void* v, int32_t dt
                          int32_t batch, int32_t max_seqlen_q, int32_t total_q, int32_t total_k,
                          int32_t heads, int32_t head_dim,
                          int32_t causal, float scale,
-                         void* out, int32_t out_dtype, int64_t o_stride, void* stream);
+                         void* out, int32_t out_dtype, int64_t o_stride,
+                         float* lse, /* optional [heads, total_q]: log2-domain log-sum-exp per query row (saved for
+                                        acai_attn_varlen_bwd); NULL in inference */
+                         void* stream);
+
+/* Backward of the above (autograd of nn.MultiheadAttention / SDPA in the teacher-forced and MAE training steps,
+ * omr_teacher_force_train.py:120, pre_train.py:60): flash-style recomputation from `lse`; dq/dk/dv are written (not
+ * accumulated) as [heads*head_dim] slices of rows with the given strides, e.g. straight into a fused d(QKV) buffer.
+ * `delta_ws`: [heads * total_q] floats of scratch. */
+int acai_attn_varlen_bwd(const void* q, const void* k, const void* v, int32_t dtype,
+                         int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                         const void* out, int64_t o_stride, const void* dout, int64_t do_stride, const float* lse,
+                         const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                         int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k, int32_t total_q,
+                         int32_t heads, int32_t head_dim, int32_t causal, float scale,
+                         void* dq, void* dk, void* dv, int32_t grad_dtype,
+                         int64_t dq_stride, int64_t dk_stride, int64_t dv_stride, float* delta_ws, void* stream);
 
 /* ---- K4: decode step ---------------------------------------------------------------------------
  * One query row per (sequence, head) against a KV cache.  Replaces
@@ -200,6 +216,41 @@ int acai_mae_restore(const void* latent, int32_t latent_dtype, const int32_t* cu
                      void* out, int32_t out_dtype, int32_t dim, void* stream);
 int acai_mae_loss_fwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask,
                       int32_t rows, int32_t feats, float* row_loss, float* sums, void* stream);
+
+/* ---- training step: backward building blocks --------------------------------------------------------------------
+ * The reference trains through torch autograd (loss.backward(), omr_teacher_force_train.py:120, pre_train.py:60); these
+ * are the kernels behind the autograd Functions of acai_omr_b200/autograd.py.  Linear backward = two acai_linear_fwd
+ * calls on transposed operands (dX = dY . W,  dW = dY^T . X) + acai_colsum for the bias.
+ *   acai_transpose : out[c, r] = in[r, c], zero-padded up to ld_out columns (K % 64 for the tensor-core GEMM)
+ *   acai_colsum    : out[c] (+)= sum_r x[r, c] in a fixed order (bias gradients)
+ *   acai_gelu_fwd / acai_gelu_bwd : exact-erf GELU on a saved pre-activation (training keeps z)
+ *   acai_layernorm_bwd : dv for v = x + residual, dgamma / dbeta (+)= column reductions (fixed order)
+ *   acai_ce_loss   : OMRCELoss (models.py:784-796): row_loss / valid / sums = {sum, count} and/or
+ *                    dlogits = *scale * (softmax - onehot) for non-ignored rows
+ *   acai_scatter_add_rows / acai_gather_rows : embedding, position-table and MAE-restore gradients
+ *   acai_mae_loss_bwd : dpred = mask * *scale * 2 (pred - normalised target) / feats */
+int acai_transpose(const void* in, int32_t dtype, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,
+                   void* stream);
+size_t acai_colsum_workspace_bytes(int32_t rows, int32_t cols);
+int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t rows, int32_t cols, float* out, int32_t accumulate,
+                void* workspace, size_t workspace_bytes, void* stream);
+int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, void* stream);
+int acai_gelu_bwd(const void* dy, int32_t dy_dtype, const void* z, int32_t z_dtype, void* dz, int32_t dz_dtype, int64_t n,
+                  void* stream);
+size_t acai_layernorm_bwd_workspace_bytes(int32_t rows, int32_t cols);
+int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* x, int32_t x_dtype, const void* residual,
+                       int32_t res_dtype, const float* gamma, float eps, void* dv, int32_t dv_dtype,
+                       float* dgamma, float* dbeta, int32_t accumulate, int32_t rows, int32_t cols,
+                       void* workspace, size_t workspace_bytes, void* stream);
+int acai_ce_loss(const void* logits, int32_t dtype, int64_t ld, const int64_t* targets, int32_t rows, int32_t vocab,
+                 int32_t ignore_index, float* row_loss, uint8_t* valid, float* sums,
+                 void* dlogits, int32_t dlogits_dtype, int64_t ldd, const float* scale, void* stream);
+int acai_scatter_add_rows(const void* src, int32_t dtype, int64_t ld, const int64_t* index, int32_t rows, int32_t dim,
+                          float* dst, float scale, void* stream);
+int acai_gather_rows(const void* src, int32_t dtype, const int64_t* index, int32_t rows, int32_t dim, void* out,
+                     int32_t out_dtype, void* stream);
+int acai_mae_loss_bwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask, int32_t rows,
+                      int32_t feats, const float* scale, void* dpred, int32_t dpred_dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -27,3 +27,10 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope="session")
 def golden():
     return torch.load(GOLDEN, map_location="cpu", weights_only=False)
+
+
+@pytest.fixture(scope="session")
+def golden_grads():
+    """Parameter gradients of the unmodified reference for the golden_small.pt training steps
+    (tests/golden/make_golden_grads.py)."""
+    return torch.load(os.path.join(ROOT, "tests", "golden", "golden_grads.pt"), map_location="cpu", weights_only=False)

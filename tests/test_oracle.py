@@ -125,3 +125,37 @@ def test_split_lmx_known_answer():
     assert torch.equal(inp, torch.tensor([[0, 2, 3, 226, 1], [0, 2, 2, 3, 4]]))
     assert torch.equal(tgt, torch.tensor([[2, 3, 226, 1, 1], [2, 2, 3, 4, 226]]))
     assert torch.equal(mask, torch.tensor([[False, False, False, False, True], [False] * 5]))
+
+
+def _leaf_sd(sd):
+    return {k: v.clone().requires_grad_(True) if v.is_floating_point() else v for k, v in sd.items()}
+
+
+def _check_grads(sd, ref, tol):
+    for k, g_ref in ref.items():
+        got = sd[k].grad
+        assert got is not None, k
+        assert torch.allclose(got, g_ref, **tol), (k, float((got - g_ref).abs().max()))
+
+
+def test_teacher_forced_gradients_match_reference(golden, golden_grads):
+    """d(OMRCELoss)/d(every parameter) of the oracle's autograd vs the reference's (train mode, dropout 0)."""
+    g, gg = golden["vitomr"], golden_grads["vitomr"]
+    sd = _leaf_sd(g["sd"])
+    enc_cfg = dict(patch_size=4, pe_max_height=6, pe_max_width=10, num_heads=4, interpolate=True, stacks=["fine_tune_blocks"])
+    pred, tgt = O.teacher_forced_forward(list(zip(g["imgs"], g["lmx"])), sd, dict(encoder=enc_cfg, decoder_heads=4, pad_idx=1))
+    loss = O.ce_loss(pred, tgt, 1)
+    assert torch.allclose(loss.detach(), gg["loss"], **TOL)
+    loss.backward()
+    _check_grads(sd, gg["grads"], dict(atol=2e-5, rtol=1e-3))
+
+
+def test_mae_gradients_match_reference(golden, golden_grads):
+    g, gg = golden["mae"], golden_grads["mae"]
+    sd = _leaf_sd(g["sd"])
+    cfg = dict(mask_ratio=0.75, patch_size=4, pe_max_height=6, pe_max_width=10, encoder_heads=4, decoder_heads=2)
+    pred, lmask, target = O.mae_forward(list(zip(g["imgs"], g["targets"])), sd, cfg, g["noises"])
+    loss = O.mae_loss(pred, lmask, target)
+    assert torch.allclose(loss.detach(), gg["loss"], **TOL)
+    loss.backward()
+    _check_grads(sd, gg["grads"], dict(atol=2e-5, rtol=1e-3))

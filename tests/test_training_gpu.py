@@ -1,0 +1,349 @@
+"""Backward kernels and the training steps (teacher-forced ViTOMR + OMRCELoss, MAE + MAELoss) against
+(1) torch autograd on the same inputs (kernel level), (2) the reference's own parameter gradients stored in
+tests/golden/golden_grads.pt (model level, fp32), (3) the CPU oracle's autograd at a mid size in bf16 mode."""
+import math
+import os
+
+import pytest
+import torch
+
+from acai_omr_b200 import functional as F
+from acai_omr_b200 import ops
+from acai_omr_b200.layers import Packed
+from acai_omr_b200.models import models as M
+from oracle import vitomr_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+VOCAB = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "acai_omr_b200", "data", "lmx_vocab.txt")
+
+
+def rel_err(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+def rnd(*shape, seed=0, dtype=torch.float32, scale=1.0):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    return (scale * torch.randn(*shape, device=DEV, generator=g)).to(dtype)
+
+
+# ------------------------------------------------------------------------------------------ kernels
+@pytest.mark.parametrize("shape", [(1, 1), (70, 33), (257, 768), (1000, 64)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_transpose_pad_and_colsum(shape, dtype):
+    x = rnd(*shape, seed=1, dtype=dtype)
+    t = ops.transpose_pad(x)
+    R, Cc = shape
+    Rp = (R + 63) // 64 * 64
+    assert t.shape == (Cc, Rp)
+    assert torch.equal(t[:, :R], x.t())
+    assert not bool(t[:, R:].any())
+    assert torch.equal(ops.transpose_pad(x, pad_to=1), x.t().contiguous())
+    s = ops.colsum(x)
+    assert torch.allclose(s, x.double().sum(0).float(), atol=1e-3 * math.sqrt(R), rtol=1e-4)
+    s2 = ops.colsum(x)
+    assert torch.equal(s, s2)          # fixed summation order
+    acc = torch.ones(Cc, device=DEV)
+    ops.colsum(x, out=acc, accumulate=True)
+    assert torch.allclose(acc, 1.0 + s, atol=1e-5, rtol=1e-5)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-6), (torch.bfloat16, 1e-2)])
+def test_gelu_fwd_bwd(dtype, tol):
+    z = rnd(333, 96, seed=2, dtype=dtype, scale=2.0)
+    dy = rnd(333, 96, seed=3, dtype=dtype)
+    zr = z.float().requires_grad_(True)
+    yr = torch.nn.functional.gelu(zr)
+    yr.backward(dy.float())
+    assert rel_err(ops.gelu(z), yr) < tol
+    assert rel_err(ops.gelu_bwd(dy, z), zr.grad) < tol
+
+
+@pytest.mark.parametrize("rows,cols", [(5, 32), (300, 48), (1000, 768), (513, 1024), (64, 512)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_layernorm_bwd(rows, cols, dtype, with_res):
+    x = rnd(rows, cols, seed=4, dtype=dtype)
+    res = rnd(rows, cols, seed=5, dtype=dtype) if with_res else None
+    gamma, beta = 1.0 + 0.1 * rnd(cols, seed=6), 0.1 * rnd(cols, seed=7)
+    dy = rnd(rows, cols, seed=8)
+    v = (x.float() + (res.float() if with_res else 0.0)).requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    torch.nn.functional.layer_norm(v, (cols,), gr, br, 1e-6).backward(dy)
+    dv, dg, db = ops.layernorm_bwd(dy, x, res, gamma, 1e-6)
+    tol = 2e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(dv, v.grad) < tol
+    assert rel_err(dg, gr.grad) < tol and rel_err(db, br.grad) < 1e-5
+    dv2, dg2, _ = ops.layernorm_bwd(dy, x, res, gamma, 1e-6)
+    assert torch.equal(dg, dg2) and torch.equal(dv, dv2)
+
+
+def torch_attention(q, k, v, lens_q, lens_k, H, causal):
+    """fp32 reference over packed rows: per-sequence softmax(q k^T / sqrt(d)) v."""
+    outs, oq, ok = [], 0, 0
+    d = q.shape[1] // H
+    for lq, lk in zip(lens_q, lens_k):
+        qs = q[oq:oq + lq].view(lq, H, d).transpose(0, 1)
+        ks = k[ok:ok + lk].view(lk, H, d).transpose(0, 1)
+        vs = v[ok:ok + lk].view(lk, H, d).transpose(0, 1)
+        s = qs @ ks.transpose(1, 2) / math.sqrt(d)
+        if causal:
+            s = s.masked_fill(torch.ones(lq, lk, dtype=torch.bool, device=s.device).triu(1), float("-inf"))
+        outs.append((torch.softmax(s, -1) @ vs).transpose(0, 1).reshape(lq, H * d))
+        oq, ok = oq + lq, ok + lk
+    return torch.cat(outs)
+
+
+@pytest.mark.parametrize("H,d", [(4, 8), (3, 12), (2, 32), (2, 64), (12, 64), (1, 128)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("causal", [False, True])
+def test_self_attention_backward(H, d, dtype, causal):
+    lens = [1, 70, 129, 33, 200]
+    pk = Packed(lens, DEV)
+    D = H * d
+    qkv = rnd(pk.total, 3 * D, seed=9, dtype=dtype, scale=0.7).requires_grad_(True)
+    dout = rnd(pk.total, D, seed=10, dtype=dtype)
+    out = F.self_attention(qkv, pk, H, d, causal)
+    out.backward(dout)
+    ref_in = qkv.detach().float().requires_grad_(True)
+    ref = torch_attention(ref_in[:, :D], ref_in[:, D:2 * D], ref_in[:, 2 * D:], lens, lens, H, causal)
+    ref.backward(dout.float())
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    assert rel_err(out, ref) < tol
+    for i, name in enumerate("qkv"):
+        assert rel_err(qkv.grad[:, i * D:(i + 1) * D], ref_in.grad[:, i * D:(i + 1) * D]) < tol, name
+
+
+@pytest.mark.parametrize("H,d", [(4, 12), (2, 64), (16, 64)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_cross_attention_backward(H, d, dtype):
+    lens_q, lens_k = [5, 64, 1, 100], [130, 7, 300, 64]
+    pq, pk = Packed(lens_q, DEV), Packed(lens_k, DEV)
+    D = H * d
+    q = rnd(pq.total, D, seed=11, dtype=dtype, scale=0.7).requires_grad_(True)
+    kv = rnd(pk.total, 2 * D, seed=12, dtype=dtype, scale=0.7).requires_grad_(True)
+    dout = rnd(pq.total, D, seed=13, dtype=dtype)
+    out = F.cross_attention(q, kv, pq, pk, H, d)
+    out.backward(dout)
+    qr, kvr = q.detach().float().requires_grad_(True), kv.detach().float().requires_grad_(True)
+    ref = torch_attention(qr, kvr[:, :D], kvr[:, D:], lens_q, lens_k, H, False)
+    ref.backward(dout.float())
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    assert rel_err(out, ref) < tol
+    assert rel_err(q.grad, qr.grad) < tol and rel_err(kv.grad, kvr.grad) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+def test_ce_loss_fwd_bwd(dtype, tol):
+    B, T, V, pad = 5, 37, 227, 1
+    logits = rnd(B, T, V, seed=14, dtype=dtype, scale=3.0).requires_grad_(True)
+    g = torch.Generator().manual_seed(15)
+    tgt = torch.randint(0, V, (B, T), generator=g)
+    tgt[0, 20:] = pad
+    tgt[3] = pad
+    tgt = tgt.to(DEV)
+    loss, sums = F.ce_loss(logits, tgt, pad)
+    (loss * 1.7).backward()
+    lr = logits.detach().float().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(lr.reshape(-1, V), tgt.reshape(-1), ignore_index=pad)
+    (ref * 1.7).backward()
+    assert abs(float(loss.detach()) - float(ref.detach())) < tol * abs(float(ref.detach()))
+    assert float(sums[1]) == float((tgt != pad).sum())
+    assert rel_err(logits.grad, lr.grad) < tol
+    assert not bool(logits.grad[3].any())
+    loss_g, _ = F.ce_loss(logits.detach(), tgt, pad, normaliser=torch.tensor([10.0], device=DEV))
+    assert abs(float(loss_g) - float(sums[0]) / 10.0) < 1e-5 * abs(float(loss_g))
+
+
+def test_scatter_gather_rows():
+    src = rnd(300, 48, seed=16)
+    g = torch.Generator().manual_seed(17)
+    idx = torch.randint(-1, 20, (300,), generator=g).to(DEV)
+    dst = ops.scatter_add_rows(src, idx, torch.zeros(20, 48, device=DEV))
+    ref = torch.zeros(21, 48, device=DEV).index_add_(0, torch.where(idx < 0, torch.full_like(idx, 20), idx), src)[:20]
+    assert torch.allclose(dst, ref, atol=1e-4, rtol=1e-5)
+    got = ops.gather_rows(src, idx)
+    assert torch.equal(got[idx >= 0], src[idx[idx >= 0]]) and not bool(got[idx < 0].any())
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+def test_mae_loss_backward(dtype, tol):
+    pred = rnd(3, 40, 256, seed=18, dtype=dtype).requires_grad_(True)
+    target = torch.rand(3, 40, 256, device=DEV)
+    mask = (torch.rand(3, 40, device=DEV) > 0.3)
+    loss, _ = F.mae_loss(pred, mask, target)
+    loss.backward()
+    pr = pred.detach().float().cpu().requires_grad_(True)
+    ref = O.mae_loss(pr, mask.cpu(), target.cpu())
+    ref.backward()
+    assert abs(float(loss.detach()) - float(ref.detach())) < tol * abs(float(ref.detach()))
+    assert rel_err(pred.grad, pr.grad) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1.5e-2)])
+@pytest.mark.parametrize("M_,N,K,rows,act,res", [
+    (300, 96, 64, None, 0, False), (129, 768, 768, None, 0, True), (500, 3072, 768, None, 1, False),
+    (77, 227, 128, None, 0, False), (260, 128, 128, (0, 128), 0, False), (260, 256, 128, (128, 384), 0, False)])
+def test_linear_backward(dtype, tol, M_, N, K, rows, act, res):
+    Nw = N if rows is None else 384
+    w = (rnd(Nw, K, seed=19) / math.sqrt(K)).requires_grad_(True)
+    b = (0.1 * rnd(Nw, seed=20)).requires_grad_(True)
+    x = rnd(M_, K, seed=21, dtype=dtype).requires_grad_(True)
+    r = rnd(M_, N, seed=22, dtype=dtype).requires_grad_(True) if res else None
+    dy = rnd(M_, N, seed=23, dtype=dtype)
+    y = F.linear(x, w, b, act=act, residual=r, rows=rows)
+    y.backward(dy)
+    xr, wr, br = x.detach().float().requires_grad_(True), w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    ws, bs = (wr, br) if rows is None else (wr[rows[0]:rows[1]], br[rows[0]:rows[1]])
+    if dtype == torch.bfloat16:
+        ws = ws.detach().bfloat16().float() + (ws - ws.detach())        # forward with the bf16-rounded weight, gradient to the master
+    yr = xr @ ws.t() + bs
+    if act:
+        yr = torch.nn.functional.gelu(yr)
+    rr = None
+    if res:
+        rr = r.detach().float().requires_grad_(True)
+        yr = yr + rr
+    yr.backward(dy.float())
+    assert rel_err(y, yr) < tol
+    assert rel_err(x.grad, xr.grad) < tol and rel_err(w.grad, wr.grad) < tol and rel_err(b.grad, br.grad) < tol
+    if res:
+        assert rel_err(r.grad, rr.grad) < tol
+
+
+# ------------------------------------------------------------------------------------------ model level
+def cuda_list(ts):
+    return [t.to(DEV) for t in ts]
+
+
+def check_param_grads(module, ref_grads, atol, rtol, min_cos=None):
+    bad = []
+    for name, p in module.named_parameters():
+        ref = ref_grads[name]
+        assert p.grad is not None, name
+        got = p.grad.detach().float().cpu()
+        if min_cos is not None:
+            if float(ref.norm()) < 1e-7:
+                continue
+            cos = float((got * ref).sum() / (got.norm() * ref.norm() + 1e-30))
+            nr = float(got.norm() / ref.norm())
+            if cos < min_cos or abs(nr - 1.0) > 1.0 - min_cos + 0.03:
+                bad.append((name, cos, nr))
+        elif not torch.allclose(got, ref, atol=atol, rtol=rtol):
+            bad.append((name, float((got - ref).abs().max()), float(ref.abs().max())))
+    assert not bad, bad
+
+
+def test_teacher_forced_step_gradients_golden(golden, golden_grads):
+    """One fp32 training step of TeacherForcedViTOMR + OMRCELoss: every parameter gradient vs the reference's."""
+    g, gg = golden["vitomr"], golden_grads["vitomr"]
+    c = g["cfg"]
+    enc = M.FineTuneOMREncoder(4, 6, 10, 2, num_layers=2, hidden_dim=32, num_heads=4, mlp_dim=64, transformer_dropout=0.0)
+    dec = M.OMRDecoder(20, VOCAB, num_layers=2, hidden_dim=48, num_heads=4, mlp_dim=96, transformer_dropout=0.0)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=c["transition_head_dim"], transition_head_dropout=0.0)
+    vit.load_state_dict(g["sd"])
+    for p in vit.parameters():
+        p.requires_grad_(True)
+    vit = vit.to(DEV).train()
+    pred, tgt = vit(list(zip(cuda_list(g["imgs"]), cuda_list(g["lmx"]))))
+    loss = M.OMRCELoss(vit.decoder.pad_idx)(pred, tgt)
+    assert torch.allclose(loss.detach().cpu(), gg["loss"], atol=2e-5, rtol=1e-4)
+    loss.backward()
+    check_param_grads(vit, gg["grads"], atol=3e-5, rtol=2e-3)
+
+
+def test_mae_step_gradients_golden(golden, golden_grads):
+    g, gg = golden["mae"], golden_grads["mae"]
+    c = g["cfg"]
+    mae = M.MAE(c["mask_ratio"], c["patch_size"], c["pe_max_height"], c["pe_max_width"], c["encoder_hidden_dim"],
+                c["decoder_hidden_dim"], c["encoder_kwargs"], c["decoder_kwargs"])
+    mae.load_state_dict(g["sd"])
+    mae = mae.to(DEV).train()
+    pred, lmask, target = mae(list(zip(cuda_list(g["imgs"]), cuda_list(g["targets"]))), noises=g["noises"])
+    loss = M.MAELoss()(pred, lmask, target)
+    assert torch.allclose(loss.detach().cpu(), gg["loss"], atol=2e-5, rtol=1e-4)
+    loss.backward()
+    check_param_grads(mae, gg["grads"], atol=3e-5, rtol=2e-3)
+
+
+def test_frozen_encoder_gets_no_gradients(golden):
+    """The fine-tune recipe (models.py:663-677): frozen blocks / projection / PE stay without .grad."""
+    enc = M.FineTuneOMREncoder(16, 12, 40, 1, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.0)
+    dec = M.OMRDecoder(32, VOCAB, num_layers=1, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.0)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=128, transition_head_dropout=0.0).to(DEV).train()
+    g = torch.Generator().manual_seed(3)
+    imgs = [torch.rand(1, 64, 160, generator=g), torch.rand(1, 32, 320, generator=g)]
+    lmx = [torch.tensor([0, 5, 9, 33, 2]), torch.tensor([0, 7, 2])]
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        pred, tgt = vit(list(zip(cuda_list(imgs), cuda_list(lmx))))
+        loss = M.OMRCELoss(vit.decoder.pad_idx)(pred, tgt)
+    loss.backward()
+    for name, p in vit.named_parameters():
+        frozen = name.startswith("encoder.frozen_blocks") or name.startswith("encoder.projection") or name == "encoder.pos_embedding"
+        assert (p.grad is None) == frozen, name
+        if p.grad is not None:
+            assert p.grad.dtype == torch.float32 and bool(torch.isfinite(p.grad).all()), name
+
+
+def _oracle_grads(loss_fn, sd):
+    leaf = {k: v.clone().requires_grad_(True) if v.is_floating_point() else v for k, v in sd.items()}
+    loss = loss_fn(leaf)
+    loss.backward()
+    return float(loss.detach()), {k: v.grad for k, v in leaf.items() if v.is_floating_point()}
+
+
+def test_bf16_teacher_forced_step_vs_oracle_autograd():
+    """Mid-size model with the real head dim (64 -> tcgen05 attention forward), whole step under bf16 autocast as
+    omr_teacher_force_train.py runs it, against the fp32 CPU oracle differentiated by torch autograd."""
+    from acai_omr_b200 import synth
+    enc = M.FineTuneOMREncoder(16, 12, 40, 2, num_layers=3, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.0)
+    dec = M.OMRDecoder(48, VOCAB, num_layers=2, hidden_dim=192, num_heads=3, mlp_dim=384, transformer_dropout=0.0)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=160, transition_head_dropout=0.0)
+    synth.rerandomise_(vit, 41)
+    for p in vit.parameters():
+        p.requires_grad_(True)
+    sd = {k: v.detach().clone() for k, v in vit.state_dict().items()}
+    g = torch.Generator().manual_seed(42)
+    imgs = [torch.rand(1, h, w, generator=g) for h, w in [(64, 160), (32, 320), (96, 96), (16, 640)]]
+    lmx = [torch.cat([torch.tensor([0]), torch.randint(3, 227, (n,), generator=g), torch.tensor([2])]) for n in (30, 7, 45, 18)]
+    enc_cfg = dict(patch_size=16, pe_max_height=12, pe_max_width=40, num_heads=2, interpolate=True,
+                   stacks=["frozen_blocks", "fine_tune_blocks"])
+    cfg = dict(encoder=enc_cfg, decoder_heads=3, pad_idx=1)
+
+    def oracle_loss(leaf):
+        pred, tgt = O.teacher_forced_forward(list(zip(imgs, lmx)), leaf, cfg)
+        return O.ce_loss(pred, tgt, 1)
+
+    loss_o, grads_o = _oracle_grads(oracle_loss, sd)
+    vit = vit.to(DEV).train()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        pred, tgt = vit(list(zip(cuda_list(imgs), cuda_list(lmx))))
+        loss = M.OMRCELoss(vit.decoder.pad_idx)(pred, tgt)
+    loss.backward()
+    assert abs(float(loss) - loss_o) < 2e-2 * abs(loss_o)
+    check_param_grads(vit, grads_o, 0, 0, min_cos=0.97)
+
+
+def test_bf16_mae_step_vs_oracle_autograd():
+    from acai_omr_b200 import synth
+    mae = M.MAE(0.75, 16, 12, 40, encoder_hidden_dim=128, decoder_hidden_dim=64,
+                encoder_kwargs=dict(num_layers=2, num_heads=2, mlp_dim=256), decoder_kwargs=dict(num_layers=2, num_heads=2, mlp_dim=128))
+    synth.rerandomise_(mae, 43)
+    sd = {k: v.detach().clone() for k, v in mae.state_dict().items()}
+    g = torch.Generator().manual_seed(44)
+    imgs = [torch.rand(1, 64, 160, generator=g), torch.rand(1, 32, 320, generator=g), torch.rand(1, 48, 48, generator=g)]
+    noises = [torch.rand((t.shape[1] // 16) * (t.shape[2] // 16), generator=g) for t in imgs]
+    cfg = dict(mask_ratio=0.75, patch_size=16, pe_max_height=12, pe_max_width=40, encoder_heads=2, decoder_heads=2)
+
+    def oracle_loss(leaf):
+        return O.mae_loss(*O.mae_forward(list(zip(imgs, imgs)), leaf, cfg, noises))
+
+    loss_o, grads_o = _oracle_grads(oracle_loss, sd)
+    mae = mae.to(DEV).train()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        cu = cuda_list(imgs)
+        loss = M.MAELoss()(*mae(list(zip(cu, cu)), noises=noises))
+    loss.backward()
+    assert abs(float(loss) - loss_o) < 2e-2 * abs(loss_o)
+    check_param_grads(mae, grads_o, 0, 0, min_cos=0.97)

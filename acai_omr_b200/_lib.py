@@ -40,7 +40,7 @@ SIGNATURES = {
     "acai_layernorm_fwd": [_p, _i32, _p, _i32, _p, _p, _f32, _p, _i32, _p, _i32, _i32, _i32, _p],
     "acai_attn_varlen_fwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32,
                              _i64, _p, _p],
-    "acai_attn_varlen_bwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _p, _p, _i32, _i32, _i32, _i32, _i32,
+    "acai_attn_varlen_bwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32,
                              _i32, _i32, _f32, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _p],
     "acai_transpose": [_p, _i32, _i64, _i32, _i32, _p, _i64, _p],
     "acai_colsum_workspace_bytes": [_i32, _i32],
@@ -53,6 +53,7 @@ SIGNATURES = {
     "acai_scatter_add_rows": [_p, _i32, _i64, _p, _i32, _i32, _p, _f32, _p],
     "acai_gather_rows": [_p, _i32, _p, _i32, _i32, _p, _i32, _p],
     "acai_mae_loss_bwd": [_p, _i32, _p, _p, _i32, _i32, _p, _p, _i32, _p],
+    "acai_adamw_step": [_p, _p, _p, _p, _p, _i64, _f32, _f32, _f32, _f32, _f32, _i32, _f32, _p],
     "acai_decode_attn": [_p, _i32, _i64, _p, _p, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i64, _f32, _p,
                          _i32, _i64, _p, _sz, _p],
     "acai_kv_append": [_p, _p, _i32, _i64, _i64, _i64, _i32, _p, _p, _i32, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p],

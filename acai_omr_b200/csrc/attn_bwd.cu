@@ -164,6 +164,11 @@ attn_bwd_dkv_kernel(AttnBwdArgs a) {
   }
 }
 
+int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs, const void* dout,
+                int64_t dos, const float* lse, const float* delta, const int32_t* cu_q, const int32_t* cu_k, int batch,
+                int max_q, int max_k, int64_t total_q, int64_t total_k, int heads, int head_dim, int causal, float scale,
+                void* dq, void* dk, void* dv, int grad_dtype, int64_t dqs, int64_t dks, int64_t dvs, cudaStream_t st);
+
 }  // namespace acai
 
 using namespace acai;
@@ -172,7 +177,7 @@ extern "C" int acai_attn_varlen_bwd(const void* q, const void* k, const void* v,
                                     int64_t k_stride, int64_t v_stride, const void* out, int64_t o_stride,
                                     const void* dout, int64_t do_stride, const float* lse, const int32_t* cu_seqlens_q,
                                     const int32_t* cu_seqlens_k, int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k,
-                                    int32_t total_q, int32_t heads, int32_t head_dim, int32_t causal, float scale,
+                                    int32_t total_q, int32_t total_k, int32_t heads, int32_t head_dim, int32_t causal, float scale,
                                     void* dq, void* dk, void* dv, int32_t grad_dtype, int64_t dq_stride, int64_t dk_stride,
                                     int64_t dv_stride, float* delta_ws, void* stream) {
   ACAI_CHECK_ARG(q && k && v && out && dout && lse && cu_seqlens_q && cu_seqlens_k && dq && dk && dv && delta_ws,
@@ -189,6 +194,10 @@ extern "C" int acai_attn_varlen_bwd(const void* q, const void* k, const void* v,
   attn_delta_kernel<<<(unsigned)((nw + 7) / 8), 256, 0, st>>>(a);
   int rc = launch_status("attn_delta");
   if (rc) return rc;
+  rc = acai::attn_bwd_tc(q, k, v, dtype, q_stride, k_stride, v_stride, dout, do_stride, lse, delta_ws, cu_seqlens_q, cu_seqlens_k,
+                   batch, max_seqlen_q, max_seqlen_k, total_q, total_k, heads, head_dim, causal, scale, dq, dk, dv, grad_dtype,
+                   dq_stride, dk_stride, dv_stride, st);
+  if (rc != ACAI_ERR_UNSUPPORTED) return rc;
   dim3 gq((max_seqlen_q + BR - 1) / BR, heads, batch), gk((max_seqlen_k + BR - 1) / BR, heads, batch);
   if (head_dim <= 32) { attn_bwd_dq_kernel<32><<<gq, 2 * BR, 0, st>>>(a); attn_bwd_dkv_kernel<32><<<gk, 2 * BR, 0, st>>>(a); }
   else if (head_dim <= 64) { attn_bwd_dq_kernel<64><<<gq, 2 * BR, 0, st>>>(a); attn_bwd_dkv_kernel<64><<<gk, 2 * BR, 0, st>>>(a); }

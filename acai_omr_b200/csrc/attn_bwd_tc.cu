@@ -1,0 +1,394 @@
+// K3 backward (tensor-core path): packed variable-length attention gradients for head_dim 64, bf16 operands.
+//
+// The forward saved L = log2-domain log-sum-exp per (head, query) and `attn_delta_kernel` (attn_bwd.cu) gives
+// delta = rowsum(dO . O), so no online softmax is needed here: P = exp2(S * scale_log2 - L) is recomputed exactly.
+// Two kernels, both with the forward kernel's shape (warps 0-3 elementwise math on TMEM rows, warp 4 TMA producer,
+// warp 5 MMA issuer, 256 TMEM columns -> two CTAs per SM so one CTA's MMAs overlap the other's exp2/FMA phase):
+//
+//   dQ kernel   CTA = (sequence, head, 128 queries), loop over 64-key blocks j:
+//       S  = Q K_j^T , dP = dO V_j^T          tcgen05.mma SS -> TMEM columns 0..63 / 64..127
+//       dS = P . (dP - delta)                  thread = query row; bf16 written back over S (TS operand)
+//       dQ += dS K_j                           tcgen05.mma TS, B = K_j MN-major from the same smem tile
+//   dK/dV kernel CTA = (sequence, head, 128 keys), loop over 64-query blocks i (transposed problem, thread = key row):
+//       S^T = K Q_i^T , dP^T = V dO_i^T        SS
+//       P^T, dS^T                               bf16 over S^T / dP^T
+//       dV += P^T dO_i , dK += dS^T Q_i        TS, B = dO_i / Q_i MN-major
+// Seven GEMMs instead of the five of a fused single pass, but no atomics and no cross-CTA reduction: every output
+// element has exactly one writer and a fixed summation order (bitwise reproducible gradients).
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace acai {
+
+int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                     uint32_t box_cols);
+
+namespace fb {
+constexpr int BIG = 128, SMALL = 64, D = 64, STAGES = 3;
+constexpr int THREADS = 192;
+constexpr uint32_t BIGTILE = BIG * D * 2;           // 16 KB
+constexpr uint32_t SMALLTILE = SMALL * D * 2;       // 8 KB
+constexpr uint32_t OFF_A0 = 0, OFF_A1 = BIGTILE;    // the two resident 128-row tiles (Q,dO or K,V)
+constexpr uint32_t OFF_B0 = 2 * BIGTILE, OFF_B1 = OFF_B0 + STAGES * SMALLTILE;   // streamed 64-row tiles (K,V or Q,dO)
+constexpr uint32_t OFF_VEC = OFF_B1 + STAGES * SMALLTILE;                         // 2 x (64 L + 64 delta) floats
+constexpr uint32_t OFF_BAR = OFF_VEC + 2 * 128 * 4;
+constexpr size_t SMEM = OFF_BAR + 256;
+constexpr uint32_t TMEM_COLS = 256;                 // 0..63 S, 64..127 dP, 128..255 accumulators
+}  // namespace fb
+
+struct AttnBwdParams {
+  const int32_t* cu_q; const int32_t* cu_k;
+  const float* lse; const float* delta; int total_q;
+  int causal; float scale, scale_log2;
+  __nv_bfloat16* dq; __nv_bfloat16* dk; __nv_bfloat16* dv; int64_t dqs, dks, dvs;
+};
+
+__device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_t (&o)[32], float mul) {
+  uint4* op = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+  for (int q4 = 0; q4 < 4; ++q4) {
+    uint4 v4; __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&v4);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      hh[i] = __floats2bfloat162_rn(__uint_as_float(o[q4 * 8 + 2 * i]) * mul, __uint_as_float(o[q4 * 8 + 2 * i + 1]) * mul);
+    op[q4] = v4;
+  }
+}
+
+// ------------------------------------------------------------------------------------------ dQ
+__global__ void __launch_bounds__(fb::THREADS, 2)
+attn_bwd_dq_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do,
+                 const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v, AttnBwdParams p) {
+  using namespace fb;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* a_full = bars;                     // Q and dO tiles
+  uint64_t* b_full = bars + 1;                 // STAGES
+  uint64_t* b_empty = b_full + STAGES;         // STAGES
+  uint64_t* sp_full = b_empty + STAGES;        // S and dP of the current block are in TMEM
+  uint64_t* ds_full = sp_full + 1;             // 128 arrivals: dS written
+  uint64_t* acc_full = ds_full + 1;            // last dQ MMA landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z, h = blockIdx.y, qb = blockIdx.x;
+  const int q0 = p.cu_q[b], lq = p.cu_q[b + 1] - q0, k0 = p.cu_k[b], lk = p.cu_k[b + 1] - k0;
+  if (qb * BIG >= lq) return;
+  const int shift = lk - lq;
+  int kv_end = lk;
+  if (p.causal) { const int last = qb * BIG + BIG + shift; kv_end = last < lk ? (last < 0 ? 0 : last) : lk; }
+  const int n_kv = (kv_end + SMALL - 1) / SMALL;
+
+  if (warp == 5 && lane == 0) {
+    ptx::mbar_init(a_full, 1);
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
+    ptx::mbar_init(sp_full, 1); ptx::mbar_init(ds_full, 128); ptx::mbar_init(acc_full, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 4) {
+    if (lane == 0) {
+      ptx::prefetch_tensormap(&tma_q); ptx::prefetch_tensormap(&tma_do);
+      ptx::prefetch_tensormap(&tma_k); ptx::prefetch_tensormap(&tma_v);
+    }
+    ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    if (lane == 0 && n_kv > 0) {
+      ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
+      ptx::tma_load_2d(smem + OFF_A0, &tma_q, a_full, h * D, q0 + qb * BIG);
+      ptx::tma_load_2d(smem + OFF_A1, &tma_do, a_full, h * D, q0 + qb * BIG);
+      int s = 0; uint32_t ph = 0;
+      for (int j = 0; j < n_kv; ++j) {
+        ptx::mbar_wait(&b_empty[s], ph ^ 1);
+        ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
+        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_k, &b_full[s], h * D, k0 + j * SMALL);
+        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_v, &b_full[s], h * D, k0 + j * SMALL);
+        if (++s == STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 5) {
+    if (lane == 0 && n_kv > 0) {
+      constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
+      constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, D, false, true);      // B MN-major
+      const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024);
+      const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024);
+      ptx::mbar_wait(a_full, 0);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j % STAGES;
+        ptx::mbar_wait(&b_full[st], (j / STAGES) & 1);
+        ptx::tc_fence_after();
+        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024);
+        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, dodesc + 2 * k, vdesc + 2 * k, IDESC_S, k != 0);
+        ptx::umma_commit(sp_full);
+        ptx::mbar_wait(ds_full, j & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < SMALL / 16; ++kk)
+          ptx::umma_f16_ts(tmem_base + 128, tmem_base + kk * 8, kdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (j | kk) != 0);
+        ptx::umma_commit(&b_empty[st]);
+        if (j == n_kv - 1) ptx::umma_commit(acc_full);
+      }
+    }
+  } else {
+    const int r = warp * 32 + lane;
+    const int qi = qb * BIG + r;
+    const bool valid = qi < lq;
+    const int my_end = !valid ? 0 : (p.causal ? max(0, min(lk, qi + shift + 1)) : lk);
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const float sl2 = p.scale_log2;
+    const float L = valid ? p.lse[(int64_t)h * p.total_q + q0 + qi] : INFINITY;
+    const float dl = valid ? p.delta[(int64_t)h * p.total_q + q0 + qi] : 0.0f;
+    for (int j = 0; j < n_kv; ++j) {
+      ptx::mbar_wait(sp_full, j & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t s[32], dp[32], pk[16];
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + half * 32, s);
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + 64 + half * 32, dp);
+        ptx::tmem_ld_wait();
+        const int kbase = j * SMALL + half * 32;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
+          float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -L));
+          if (kbase + 2 * i >= my_end) p0 = 0.0f;
+          if (kbase + 2 * i + 1 >= my_end) p1 = 0.0f;
+          const __nv_bfloat162 hh = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[2 * i]) - dl),
+                                                          p1 * (__uint_as_float(dp[2 * i + 1]) - dl));
+          pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+        }
+        ptx::tmem_st_32x16(tmem_base + lane_addr + half * 16, pk);
+      }
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(ds_full);
+    }
+    if (n_kv > 0) {
+      ptx::mbar_wait(acc_full, 0);
+      ptx::tc_fence_after();
+    }
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t o[32];
+      if (n_kv > 0) {
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + 128 + c * 32, o);
+        ptx::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = 0u;
+      }
+      if (valid) store_row_bf16(p.dq + (int64_t)(q0 + qi) * p.dqs + (int64_t)h * D + c * 32, o, p.scale);
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------ dK / dV
+__global__ void __launch_bounds__(fb::THREADS, 2)
+attn_bwd_dkv_tc64(const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v,
+                  const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do, AttnBwdParams p) {
+  using namespace fb;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* a_full = bars;                     // K and V tiles
+  uint64_t* b_full = bars + 1;                 // STAGES: Q_i and dO_i
+  uint64_t* b_empty = b_full + STAGES;
+  uint64_t* sp_full = b_empty + STAGES;
+  uint64_t* ds_full = sp_full + 1;
+  uint64_t* acc_full = ds_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  float* vec = reinterpret_cast<float*>(smem + OFF_VEC);          // [2][128]: L of 64 queries, then delta of 64 queries
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z, h = blockIdx.y, kb = blockIdx.x;
+  const int q0 = p.cu_q[b], lq = p.cu_q[b + 1] - q0, k0 = p.cu_k[b], lk = p.cu_k[b + 1] - k0;
+  if (kb * BIG >= lk) return;
+  const int shift = lk - lq;
+  // causal: key kr is seen by queries q >= kr - shift; the first query block that can see this key tile
+  int i0 = 0;
+  if (p.causal) { const int first = kb * BIG - shift; i0 = first > 0 ? first / SMALL : 0; }
+  const int n_q = (lq + SMALL - 1) / SMALL;
+  const int n_it = n_q > i0 ? n_q - i0 : 0;
+
+  if (warp == 5 && lane == 0) {
+    ptx::mbar_init(a_full, 1);
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
+    ptx::mbar_init(sp_full, 1); ptx::mbar_init(ds_full, 128); ptx::mbar_init(acc_full, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 4) {
+    if (lane == 0) {
+      ptx::prefetch_tensormap(&tma_q); ptx::prefetch_tensormap(&tma_do);
+      ptx::prefetch_tensormap(&tma_k); ptx::prefetch_tensormap(&tma_v);
+    }
+    ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    if (lane == 0 && n_it > 0) {
+      ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
+      ptx::tma_load_2d(smem + OFF_A0, &tma_k, a_full, h * D, k0 + kb * BIG);
+      ptx::tma_load_2d(smem + OFF_A1, &tma_v, a_full, h * D, k0 + kb * BIG);
+      int s = 0; uint32_t ph = 0;
+      for (int it = 0; it < n_it; ++it) {
+        ptx::mbar_wait(&b_empty[s], ph ^ 1);
+        ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
+        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_q, &b_full[s], h * D, q0 + (i0 + it) * SMALL);
+        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_do, &b_full[s], h * D, q0 + (i0 + it) * SMALL);
+        if (++s == STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 5) {
+    if (lane == 0 && n_it > 0) {
+      constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
+      constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, D, false, true);
+      const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024);
+      const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024);
+      ptx::mbar_wait(a_full, 0);
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it % STAGES;
+        ptx::mbar_wait(&b_full[st], (it / STAGES) & 1);
+        ptx::tc_fence_after();
+        const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024);
+        const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base, kdesc + 2 * k, qdesc + 2 * k, IDESC_S, k != 0);       // S^T
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, vdesc + 2 * k, dodesc + 2 * k, IDESC_S, k != 0); // dP^T
+        ptx::umma_commit(sp_full);
+        ptx::mbar_wait(ds_full, it & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < SMALL / 16; ++kk)      // dV += P^T dO_i
+          ptx::umma_f16_ts(tmem_base + 128, tmem_base + kk * 8, dodesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+#pragma unroll
+        for (int kk = 0; kk < SMALL / 16; ++kk)      // dK += dS^T Q_i
+          ptx::umma_f16_ts(tmem_base + 192, tmem_base + 64 + kk * 8, qdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+        ptx::umma_commit(&b_empty[st]);
+        if (it == n_it - 1) ptx::umma_commit(acc_full);
+      }
+    }
+  } else {
+    const int r = warp * 32 + lane;
+    const int kr = kb * BIG + r;
+    const bool valid = kr < lk;
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const float sl2 = p.scale_log2;
+    for (int it = 0; it < n_it; ++it) {
+      const int qbase = (i0 + it) * SMALL;
+      float* vb = vec + (it & 1) * 128;
+      {                                            // stage L / delta of this query block (broadcast reads below)
+        const int q = qbase + (r & 63);
+        const float* src = r < 64 ? p.lse : p.delta;
+        vb[r] = q < lq ? src[(int64_t)h * p.total_q + q0 + q] : (r < 64 ? INFINITY : 0.0f);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      // first query column this key row may attend to (causal), all columns masked for rows past the sequence end
+      const int cmin = !valid ? SMALL : (p.causal ? kr - shift - qbase : 0);
+      ptx::mbar_wait(sp_full, it & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t s[32], dp[32], pk[16], dk[16];
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + half * 32, s);
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + 64 + half * 32, dp);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int c = half * 32 + 2 * i;
+          float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -vb[c]));
+          float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -vb[c + 1]));
+          if (c < cmin) p0 = 0.0f;
+          if (c + 1 < cmin) p1 = 0.0f;
+          const __nv_bfloat162 hp = __floats2bfloat162_rn(p0, p1);
+          const __nv_bfloat162 hd = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[2 * i]) - vb[64 + c]),
+                                                          p1 * (__uint_as_float(dp[2 * i + 1]) - vb[64 + c + 1]));
+          pk[i] = *reinterpret_cast<const uint32_t*>(&hp);
+          dk[i] = *reinterpret_cast<const uint32_t*>(&hd);
+        }
+        ptx::tmem_st_32x16(tmem_base + lane_addr + half * 16, pk);
+        ptx::tmem_st_32x16(tmem_base + lane_addr + 64 + half * 16, dk);
+      }
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(ds_full);
+    }
+    if (n_it > 0) {
+      ptx::mbar_wait(acc_full, 0);
+      ptx::tc_fence_after();
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {                  // c 0,1: dV columns 128..191; c 2,3: dK columns 192..255
+      uint32_t o[32];
+      if (n_it > 0) {
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + 128 + c * 32, o);
+        ptx::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = 0u;
+      }
+      if (valid) {
+        if (c < 2) store_row_bf16(p.dv + (int64_t)(k0 + kr) * p.dvs + (int64_t)h * D + c * 32, o, 1.0f);
+        else store_row_bf16(p.dk + (int64_t)(k0 + kr) * p.dks + (int64_t)h * D + (c - 2) * 32, o, p.scale);
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// returns ACAI_ERR_UNSUPPORTED when the problem does not qualify (the caller then runs the SIMT kernels)
+int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs, const void* dout,
+                int64_t dos, const float* lse, const float* delta, const int32_t* cu_q, const int32_t* cu_k, int batch,
+                int max_q, int max_k, int64_t total_q, int64_t total_k, int heads, int head_dim, int causal, float scale,
+                void* dq, void* dk, void* dv, int grad_dtype, int64_t dqs, int64_t dks, int64_t dvs, cudaStream_t st) {
+  using namespace fb;
+  auto misaligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; };
+  if (dtype != ACAI_BF16 || grad_dtype != ACAI_BF16 || head_dim != D || qs % 8 || ks % 8 || vs % 8 || dos % 8 || dqs % 8 ||
+      dks % 8 || dvs % 8 || total_q <= 0 || total_k <= 0 || misaligned(q) || misaligned(k) || misaligned(v) ||
+      misaligned(dout) || misaligned(dq) || misaligned(dk) || misaligned(dv))
+    return ACAI_ERR_UNSUPPORTED;
+  const uint64_t cols = (uint64_t)heads * D;
+  CUtensorMap q_big, do_big, k_small, v_small, k_big, v_big, q_small, do_small;
+  int rc = 0;
+  if ((rc = make_tma_2d_bf16(&q_big, q, (uint64_t)total_q, cols, (uint64_t)qs, BIG, D))) return rc;
+  if ((rc = make_tma_2d_bf16(&do_big, dout, (uint64_t)total_q, cols, (uint64_t)dos, BIG, D))) return rc;
+  if ((rc = make_tma_2d_bf16(&k_small, k, (uint64_t)total_k, cols, (uint64_t)ks, SMALL, D))) return rc;
+  if ((rc = make_tma_2d_bf16(&v_small, v, (uint64_t)total_k, cols, (uint64_t)vs, SMALL, D))) return rc;
+  if ((rc = make_tma_2d_bf16(&k_big, k, (uint64_t)total_k, cols, (uint64_t)ks, BIG, D))) return rc;
+  if ((rc = make_tma_2d_bf16(&v_big, v, (uint64_t)total_k, cols, (uint64_t)vs, BIG, D))) return rc;
+  if ((rc = make_tma_2d_bf16(&q_small, q, (uint64_t)total_q, cols, (uint64_t)qs, SMALL, D))) return rc;
+  if ((rc = make_tma_2d_bf16(&do_small, dout, (uint64_t)total_q, cols, (uint64_t)dos, SMALL, D))) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    attr_set = true;
+  }
+  AttnBwdParams p{cu_q, cu_k, lse, delta, (int)total_q, causal, scale, scale * 1.4426950408889634f,
+                  (__nv_bfloat16*)dq, (__nv_bfloat16*)dk, (__nv_bfloat16*)dv, dqs, dks, dvs};
+  attn_bwd_dq_tc64<<<dim3((max_q + BIG - 1) / BIG, heads, batch), THREADS, SMEM, st>>>(q_big, do_big, k_small, v_small, p);
+  rc = launch_status("attn_bwd_dq_tc64");
+  if (rc) return rc;
+  attn_bwd_dkv_tc64<<<dim3((max_k + BIG - 1) / BIG, heads, batch), THREADS, SMEM, st>>>(k_big, v_big, q_small, do_small, p);
+  return launch_status("attn_bwd_dkv_tc64");
+}
+
+}  // namespace acai

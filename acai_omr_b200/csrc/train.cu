@@ -321,3 +321,36 @@ extern "C" int acai_mae_loss_bwd(const void* pred, int32_t pred_dtype, const flo
                                                                                 scale, dpred, dpred_dtype);
   return launch_status("mae_loss_bwd");
 }
+
+// Fused AdamW over one flat fp32 segment (torch.optim.AdamW semantics, decoupled weight decay; the reference's
+// optimiser, omr_teacher_force_train.py:207).  Also refreshes the bf16 shadow copy the GEMMs read, so no per-weight
+// cast is launched after a step.  `grad_scale` folds the 1/world_size of a summed all-reduce into the update.
+__global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                             __nv_bfloat16* __restrict__ p_lp, int64_t n, float lr, float b1, float b2, float eps, float wd,
+                             float bc1, float bc2_rsqrt, float grad_scale) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float gi = g[i] * grad_scale;
+    float pi = p[i] * (1.0f - lr * wd);
+    const float mi = b1 * m[i] + (1.0f - b1) * gi;
+    const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    pi -= (lr / bc1) * mi / (sqrtf(vi) * bc2_rsqrt + eps);
+    p[i] = pi;
+    if (p_lp) p_lp[i] = __float2bfloat16(pi);
+  }
+}
+
+extern "C" int acai_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* param_bf16,
+                               int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay, int32_t step,
+                               float grad_scale, void* stream) {
+  ACAI_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && n >= 0 && step >= 1, "acai_adamw_step: bad argument");
+  if (n == 0) return ACAI_OK;
+  const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
+  const int64_t blocks = (n + 255) / 256;
+  adamw_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, (cudaStream_t)stream>>>(
+      param, grad, exp_avg, exp_avg_sq, (__nv_bfloat16*)param_bf16, n, lr, beta1, beta2, eps, weight_decay, bc1,
+      1.0f / sqrtf(bc2), grad_scale);
+  return launch_status("adamw_step");
+}

@@ -12,6 +12,7 @@ Precision policy (mirrors the reference's use of autocast, vitomr_inference.py:8
 from __future__ import annotations
 
 import math
+import weakref
 
 import torch
 from torch import nn
@@ -31,15 +32,34 @@ class _WeightCache:
 
     def __init__(self):
         self._store = {}
+        self._shadow = {}
+        self.generation = 0
+
+    def register_shadow(self, p: torch.Tensor, shadow: torch.Tensor):
+        """`shadow` is a low-precision copy of `p` that its owner (train.FlatTrainer's fused AdamW) keeps in sync."""
+        self._shadow[id(p)] = (p._version, p.data_ptr(), shadow, weakref.ref(p))
+
+    def bump_generation(self):
+        """Parameters were updated through raw pointers (no torch version bump): derived copies are stale."""
+        self.generation += 1
 
     def get(self, p: torch.Tensor, dtype: torch.dtype, rows=None):
         if p is None:
             return None
         if p.dtype == dtype and rows is None:
             return p.detach()
+        sh = self._shadow.get(id(p))
+        if sh is not None and sh[3]() is not p:                   # the registered parameter died and its id was reused
+            del self._shadow[id(p)]
+            sh = None
+        if sh is not None and sh[2].dtype == dtype:
+            if sh[0] != p._version or sh[1] != p.data_ptr():     # written through torch since (load_state_dict, copy_)
+                sh[2].copy_(p.detach())
+                self._shadow[id(p)] = (p._version, p.data_ptr(), sh[2], sh[3])
+            return sh[2] if rows is None else sh[2][rows[0]:rows[1]]
         key = (id(p), dtype, rows)
         hit = self._store.get(key)
-        ver = (p._version, p.data_ptr())
+        ver = (p._version, p.data_ptr(), self.generation)
         if hit is not None and hit[0] == ver:
             return hit[1]
         src = p.detach() if rows is None else p.detach()[rows[0]:rows[1]]
@@ -51,7 +71,7 @@ class _WeightCache:
         """Transposed copy [in, out] of (a row slice of) `p` in `dtype`: the B operand of dX = dY W."""
         key = (id(p), dtype, rows, "T")
         hit = self._store.get(key)
-        ver = (p._version, p.data_ptr())
+        ver = (p._version, p.data_ptr(), self.generation)
         if hit is not None and hit[0] == ver:
             return hit[1]
         t = ops.transpose_pad(self.get(p, dtype, rows), pad_to=1)
@@ -60,6 +80,7 @@ class _WeightCache:
 
     def clear(self):
         self._store.clear()
+        self._shadow.clear()
 
 
 WEIGHTS = _WeightCache()

@@ -480,7 +480,7 @@ def attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, max_q, max_k, heads, he
     delta = torch.empty(heads * q.shape[0], dtype=torch.float32, device=q.device)
     _call("acai_attn_varlen_bwd", _lib.load().acai_attn_varlen_bwd, _p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0),
           v.stride(0), _p(out), out.stride(0), _p(dout), dout.stride(0), _p(lse), _p(cu_q), _p(cu_k), cu_q.numel() - 1,
-          int(max_q), int(max_k), q.shape[0], heads, head_dim, 1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
+          int(max_q), int(max_k), q.shape[0], k.shape[0], heads, head_dim, 1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
           _p(dq), _p(dk), _p(dv), _dt(dq), dq.stride(0), dk.stride(0), dv.stride(0), _p(delta), _stream())
     _bump(2)
 

@@ -58,3 +58,15 @@ def encoder_flops(lens, layers=12, d=768, mlp=3072, patch_feats=256):
     lin = sum(lens) * (layers * per_tok_layer + 2.0 * patch_feats * d)
     attn = layers * 4.0 * d * sum(l * l for l in lens)
     return lin + attn
+
+
+def lmx_lengths(num_systems: int, cycle=(384, 512, 640, 768, 896, 1024, 448, 576)):
+    """Target LMX sequence lengths (tokens incl. <bos>/<eos>) for the teacher-forced workload: a fixed cycle with mean
+    656, inside the reference's MAX_LMX_SEQ_LEN = 1536 (omr_teacher_force_train.py:25)."""
+    return [cycle[i % len(cycle)] for i in range(num_systems)]
+
+
+def synth_lmx(length: int, seed: int, vocab: int = 227, bos: int = 0, eos: int = 2, first: int = 3) -> torch.Tensor:
+    g = torch.Generator().manual_seed(4321 + seed)
+    body = torch.randint(first, vocab, (length - 2,), generator=g)
+    return torch.cat([torch.tensor([bos]), body, torch.tensor([eos])])

@@ -119,7 +119,7 @@ int acai_attn_varlen_bwd(const void* q, const void* k, const void* v, int32_t dt
                          int64_t q_stride, int64_t k_stride, int64_t v_stride,
                          const void* out, int64_t o_stride, const void* dout, int64_t do_stride, const float* lse,
                          const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
-                         int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k, int32_t total_q,
+                         int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k, int32_t total_q, int32_t total_k,
                          int32_t heads, int32_t head_dim, int32_t causal, float scale,
                          void* dq, void* dk, void* dv, int32_t grad_dtype,
                          int64_t dq_stride, int64_t dk_stride, int64_t dv_stride, float* delta_ws, void* stream);
@@ -251,6 +251,13 @@ int acai_gather_rows(const void* src, int32_t dtype, const int64_t* index, int32
                      int32_t out_dtype, void* stream);
 int acai_mae_loss_bwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask, int32_t rows,
                       int32_t feats, const float* scale, void* dpred, int32_t dpred_dtype, void* stream);
+
+/* One AdamW update (torch.optim.AdamW semantics; omr_teacher_force_train.py:207, mae_pre_train.py) of a flat fp32
+ * parameter segment, `grad_scale` applied to the gradient first (1/world_size after a summed all-reduce).
+ * `param_bf16` (may be NULL) receives the bf16 copy of the updated parameters that the tensor-core GEMMs read. */
+int acai_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* param_bf16, int64_t n,
+                    float lr, float beta1, float beta2, float eps, float weight_decay, int32_t step, float grad_scale,
+                    void* stream);
 
 #ifdef __cplusplus
 }

@@ -347,3 +347,49 @@ def test_bf16_mae_step_vs_oracle_autograd():
     loss.backward()
     assert abs(float(loss) - loss_o) < 2e-2 * abs(loss_o)
     check_param_grads(mae, grads_o, 0, 0, min_cos=0.97)
+
+
+def test_adamw_kernel_matches_torch():
+    from acai_omr_b200 import train
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(300, 17).to(DEV)
+    ref = torch.nn.Linear(300, 17).to(DEV)
+    ref.load_state_dict(lin.state_dict())
+    opt = torch.optim.AdamW(ref.parameters(), lr=3e-3, betas=(0.9, 0.95), weight_decay=0.01)
+    tr = train.FlatTrainer(lin, lr=3e-3, betas=(0.9, 0.95), weight_decay=0.01)
+    for it in range(4):
+        gs = [rnd(*p.shape, seed=50 + it + i) for i, p in enumerate(lin.parameters())]
+        tr.zero_grad()
+        for p, r, g in zip(lin.parameters(), ref.parameters(), gs):
+            p.grad.copy_(g)
+            r.grad = g.clone()
+        tr.step()
+        opt.step()
+    for p, r in zip(lin.parameters(), ref.parameters()):
+        assert torch.allclose(p, r, atol=1e-6, rtol=1e-5)
+    assert torch.equal(tr.shadow[: lin.weight.numel()].view_as(lin.weight), lin.weight.detach().bfloat16())
+
+
+def test_trainer_steps_reduce_the_loss_and_refresh_weight_copies():
+    """Three fused steps on a fixed batch: loss falls, the bf16 shadow / transposed copies follow the parameters."""
+    from acai_omr_b200 import layers, synth, train
+    enc = M.FineTuneOMREncoder(16, 12, 40, 1, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.0)
+    dec = M.OMRDecoder(48, VOCAB, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.0)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=128, transition_head_dropout=0.0)
+    synth.rerandomise_(vit, 5)
+    vit = vit.to(DEV).train()
+    groups, lrs = vit.create_fine_tune_param_groups(2e-3, 1e-3, 0.9)
+    tr = train.FlatTrainer(vit, groups)
+    frozen_before = vit.encoder.frozen_blocks.layers[0].linear1.weight.detach().clone()
+    imgs = [synth.synth_system(h, w, i).to(DEV) for i, (h, w) in enumerate([(64, 160), (32, 320), (96, 96)])]
+    batch = list(zip(imgs, [synth.synth_lmx(L, i).to(DEV) for i, L in enumerate([20, 33, 12])]))
+    losses = []
+    for _ in range(4):
+        sums = train.teacher_forced_step(vit, batch, tr)
+        losses.append(float(sums[0] / sums[1]))
+    assert losses[-1] < losses[0] - 0.05, losses
+    w = vit.decoder.unembed.weight
+    assert torch.equal(layers.w_(w, torch.bfloat16), w.detach().bfloat16())
+    assert torch.equal(layers.WEIGHTS.get_t(w, torch.bfloat16), w.detach().bfloat16().t().contiguous())
+    assert torch.equal(vit.encoder.frozen_blocks.layers[0].linear1.weight, frozen_before)
+    layers.WEIGHTS.clear()

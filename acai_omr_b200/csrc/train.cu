@@ -120,6 +120,119 @@ layernorm_bwd_kernel(const void* __restrict__ dy, int dy_dt, const void* __restr
   }
 }
 
+// ---- vectorised LayerNorm backward: TPR threads (a multiple of 32) own one row, 8 consecutive columns each (16-byte
+// bf16 / 2 x 16-byte fp32 accesses); G = blockDim / TPR rows are in flight per CTA, each row group synchronising on its
+// own named barrier.  Column partial sums stay in 16 registers per thread, are folded over the G groups through shared
+// memory and leave the CTA as ONE slab (fixed order everywhere -> bitwise reproducible dgamma / dbeta).
+__device__ __forceinline__ void load8(const void* p, int dt, int64_t i, float (&v)[8]) {
+  if (dt == ACAI_BF16) {
+    const uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p) + i);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const float2 f = __bfloat1622float2(h[k]); v[2 * k] = f.x; v[2 * k + 1] = f.y; }
+  } else {
+    const float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p) + i);
+    const float4 b = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p) + i + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+}
+__device__ __forceinline__ void store8(void* p, int dt, int64_t i, const float (&v)[8]) {
+  if (dt == ACAI_BF16) {
+    uint4 u; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p) + i) = u;
+  } else {
+    *reinterpret_cast<float4*>(reinterpret_cast<float*>(p) + i) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(reinterpret_cast<float*>(p) + i + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+}
+
+template <int TPR>
+__global__ void __launch_bounds__(384)
+layernorm_bwd_vec_kernel(const void* __restrict__ dy, int dy_dt, const void* __restrict__ x, int x_dt,
+                         const void* __restrict__ res, int res_dt, const float* __restrict__ gamma, float eps,
+                         void* __restrict__ dv, int dv_dt, float* __restrict__ part_g, float* __restrict__ part_b,
+                         int rows, int cols) {
+  constexpr int NW = TPR / 32;                       // warps per row group
+  extern __shared__ float sm[];                      // [G][NW][6] reduction scratch, then [G][cols] x 2 for the final fold
+  const int G = blockDim.x / TPR;
+  const int g = threadIdx.x / TPR, t = threadIdx.x % TPR, wg = t >> 5, lane = threadIdx.x & 31;
+  const int c0 = t * 8;
+  const bool active = c0 < cols;
+  float* red = sm + g * NW * 6;
+  float gm[8], ag[8], ab[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { gm[k] = active ? __ldg(gamma + c0 + k) : 0.0f; ag[k] = 0.0f; ab[k] = 0.0f; }
+  auto group_sum2 = [&](float a, float b, int slot, float& ra, float& rb) {     // all TPR threads of the group take part
+    a = warp_sum(a); b = warp_sum(b);
+    if (NW == 1) { ra = a; rb = b; return; }
+    if (lane == 0) { red[wg * 6 + slot] = a; red[wg * 6 + slot + 1] = b; }
+    asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(TPR) : "memory");
+    ra = 0.0f; rb = 0.0f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) { ra += red[w * 6 + slot]; rb += red[w * 6 + slot + 1]; }
+  };
+  const float inv_n = 1.0f / (float)cols;
+  for (int row = blockIdx.x * G + g; row < rows; row += gridDim.x * G) {
+    const int64_t base = (int64_t)row * cols + c0;
+    float v[8], d[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { v[k] = 0.0f; d[k] = 0.0f; }
+    if (active) {
+      load8(x, x_dt, base, v);
+      if (res) { float r8[8]; load8(res, res_dt, base, r8);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] += r8[k]; }
+      load8(dy, dy_dt, base, d);
+    }
+    float s = 0.0f, dummy;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[k];
+    float mu;
+    group_sum2(s, 0.0f, 0, mu, dummy);
+    mu *= inv_n;
+    float q = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { const float tt = active ? v[k] - mu : 0.0f; q += tt * tt; }
+    float var;
+    group_sum2(q, 0.0f, 2, var, dummy);
+    const float rstd = rsqrtf(var * inv_n + eps);
+    float m1 = 0.0f, m2 = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xh = active ? (v[k] - mu) * rstd : 0.0f, gg = d[k] * gm[k];
+      m1 += gg; m2 += gg * xh;
+      ag[k] += d[k] * xh; ab[k] += d[k];
+      v[k] = xh; d[k] = gg;
+    }
+    // three slot pairs: a warp that races ahead into the next row writes pair 0 while a slower one may still read pair 4
+    group_sum2(m1, m2, 4, m1, m2);
+    m1 *= inv_n; m2 *= inv_n;
+    if (active) {
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = rstd * (d[k] - m1 - v[k] * m2);
+      store8(dv, dv_dt, base, o);
+    }
+  }
+  // fold the G groups (fixed order) and write this CTA's slab
+  __syncthreads();
+  float* fg = sm;
+  float* fbeta = sm + (size_t)G * cols;
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { fg[g * cols + c0 + k] = ag[k]; fbeta[g * cols + c0 + k] = ab[k]; }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    float a = 0.0f, b2 = 0.0f;
+    for (int gg = 0; gg < G; ++gg) { a += fg[gg * cols + c]; b2 += fbeta[gg * cols + c]; }
+    part_g[(int64_t)blockIdx.x * cols + c] = a;
+    part_b[(int64_t)blockIdx.x * cols + c] = b2;
+  }
+}
+
 // Cross-entropy with ignore_index (OMRCELoss, models.py:784-796), one warp per row:
 //   row_loss = logsumexp(z) - z[target]   (0 for ignored rows);  dlogits = softmax(z) - onehot(target)  (0 for ignored rows)
 // dlogits is scaled by *scale_ptr (= upstream gradient / count, a device scalar).  `valid[row]` = 1 for counted rows.
@@ -266,10 +379,27 @@ extern "C" int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* 
   ACAI_CHECK_ARG(dtype_valid(dy_dtype) && dtype_valid(x_dtype) && dtype_valid(dv_dtype) && (!residual || dtype_valid(res_dtype)),
                  "acai_layernorm_bwd: bad dtype");
   ACAI_CHECK_ARG(workspace_bytes >= acai_layernorm_bwd_workspace_bytes(rows, cols), "acai_layernorm_bwd: workspace too small");
-  const int grid = ln_bwd_grid(rows), slabs = grid * 8;
+  int grid = ln_bwd_grid(rows), slabs = grid * 8;
   float* pg = reinterpret_cast<float*>(workspace);
-  float* pb = pg + (size_t)slabs * cols;
   cudaStream_t st = (cudaStream_t)stream;
+  auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (cols % 8 == 0 && al16(dy) && al16(x) && al16(dv) && (!residual || al16(residual))) {
+    const int tpr = ((cols / 8) + 31) / 32 * 32;           // 32, 64, 96 or 128
+    const int G = 384 / tpr;
+    grid = (rows + G - 1) / G < 2 * num_sms() ? (rows + G - 1) / G : 2 * num_sms();
+    float* pb2 = pg + (size_t)grid * cols;
+    const size_t shm = sizeof(float) * (size_t)(2 * G * cols > G * 4 * 6 ? 2 * G * cols : G * 4 * 6);
+#define LNV(T) layernorm_bwd_vec_kernel<T><<<grid, G * T, shm, st>>>(dy, dy_dtype, x, x_dtype, residual, res_dtype, gamma, eps, \
+                                                                    dv, dv_dtype, pg, pb2, rows, cols)
+    if (tpr == 32) LNV(32); else if (tpr == 64) LNV(64); else if (tpr == 96) LNV(96); else LNV(128);
+#undef LNV
+    int rc2 = launch_status("layernorm_bwd_vec");
+    if (rc2) return rc2;
+    colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pg, grid, cols, dgamma, accumulate);
+    colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pb2, grid, cols, dbeta, accumulate);
+    return launch_status("layernorm_bwd_reduce");
+  }
+  float* pb = pg + (size_t)slabs * cols;
 #define LNB(NV) layernorm_bwd_kernel<NV><<<grid, 256, 0, st>>>(dy, dy_dtype, x, x_dtype, residual, res_dtype, gamma, eps, dv, \
                                                                dv_dtype, pg, pb, rows, cols)
   if (cols <= 128) LNB(4); else if (cols <= 256) LNB(8); else if (cols <= 512) LNB(16); else if (cols <= 768) LNB(24); else LNB(32);
@@ -353,4 +483,18 @@ extern "C" int acai_adamw_step(float* param, const float* grad, float* exp_avg, 
       param, grad, exp_avg, exp_avg_sq, (__nv_bfloat16*)param_bf16, n, lr, beta1, beta2, eps, weight_decay, bc1,
       1.0f / sqrtf(bc2), grad_scale);
   return launch_status("adamw_step");
+}
+
+namespace acai {
+int wgrad_tcgen05(const void* dz, int64_t ldz, const void* x, int64_t ldx, float* dw, int64_t ldo, int n_out, int k_in, int T,
+                  cudaStream_t st);
+}
+
+extern "C" int acai_wgrad_accumulate(const void* dz, int64_t ldz, const void* x, int64_t ldx, int32_t dtype, float* dw,
+                                     int64_t ldw, int32_t n_out, int32_t k_in, int32_t tokens, void* stream) {
+  ACAI_CHECK_ARG(dz && x && dw && n_out > 0 && k_in > 0 && tokens > 0, "acai_wgrad_accumulate: bad argument");
+  if (dtype != ACAI_BF16) { set_error("acai_wgrad_accumulate: only bf16 operands run on the tensor-core path"); return ACAI_ERR_UNSUPPORTED; }
+  int rc = acai::wgrad_tcgen05(dz, ldz, x, ldx, dw, ldw, n_out, k_in, tokens, (cudaStream_t)stream);
+  if (rc == ACAI_ERR_UNSUPPORTED) set_error("acai_wgrad_accumulate: operands are not TMA-addressable (16-byte aligned rows needed)");
+  return rc;
 }

@@ -30,6 +30,14 @@ def _slice(p, rows):
     return p if (p is None or rows is None) else p[rows[0]:rows[1]]
 
 
+def _owned_grad(p):
+    """The parameter's preallocated fp32 gradient buffer when a trainer owns it (train.FlatTrainer sets `_acai_grad_owned`):
+    backward kernels then accumulate into it directly and report no gradient to autograd."""
+    if p is not None and getattr(p, "_acai_grad_owned", False) and p.grad is not None and p.grad.dtype == torch.float32:
+        return p.grad
+    return None
+
+
 def _full_rows(grad_rows, like, rows):
     """Gradient of a row slice -> gradient of the whole parameter."""
     if rows is None:
@@ -63,7 +71,7 @@ class _Linear(torch.autograd.Function):
         else:
             y = ops.linear(x2, w, b, residual=residual.detach() if residual is not None else None, out_dtype=out_dtype)
         ctx.save_for_backward(x2, weight, z)
-        ctx.rows, ctx.x_shape, ctx.has_bias = rows, x.shape, bias is not None
+        ctx.rows, ctx.x_shape, ctx.has_bias, ctx.bias_ref = rows, x.shape, bias is not None, bias
         ctx.res_meta = (residual.shape, residual.dtype) if residual is not None else None
         return y.view(*x.shape[:-1], y.shape[-1])
 
@@ -84,14 +92,24 @@ class _Linear(torch.autograd.Function):
             wt = _weights().get_t(weight, dt, rows)                      # [K, N]
             dx = ops.linear(dz, wt, out_dtype=dt).view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
-            dzt, xt = ops.transpose_pad(dz), ops.transpose_pad(x2)       # [N, Mp], [K, Mp]: the token dim becomes K
-            dw = _full_rows(ops.linear(dzt, xt, out_dtype=torch.float32), weight, rows)
+            g = _owned_grad(weight)
+            if g is not None:            # accumulate straight into the (flat) gradient buffer: no temporary, no add kernel
+                ops.wgrad_accumulate(dz, x2, g if rows is None else g[rows[0]:rows[1]])
+            else:
+                dw = torch.zeros(weight.shape if rows is None else (rows[1] - rows[0], weight.shape[1]), dtype=torch.float32,
+                                 device=dz.device)
+                dw = _full_rows(ops.wgrad_accumulate(dz, x2, dw), weight, rows)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = ops.colsum(dz)
-            if rows is not None:
-                full = torch.zeros(weight.shape[0], dtype=torch.float32, device=db.device)
-                full[rows[0]:rows[1]] = db
-                db = full
+            bias = ctx.bias_ref
+            g = _owned_grad(bias)
+            if g is not None:
+                ops.colsum(dz, out=g if rows is None else g[rows[0]:rows[1]], accumulate=True)
+            else:
+                db = ops.colsum(dz)
+                if rows is not None:
+                    full = torch.zeros(weight.shape[0], dtype=torch.float32, device=db.device)
+                    full[rows[0]:rows[1]] = db
+                    db = full
         if ctx.res_meta is not None and ctx.needs_input_grad[3]:
             shape, rdt = ctx.res_meta
             dres = dy.reshape(shape)

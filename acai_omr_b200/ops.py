@@ -420,6 +420,32 @@ def transpose_pad(x, pad_to=64):
     return out
 
 
+def wgrad_supported(dz, x, dw):
+    return (dz.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and dw.dtype == torch.float32 and dz.dim() == 2 and
+            x.dim() == 2 and dz.stride(1) == 1 and x.stride(1) == 1 and dw.stride(-1) == 1 and dz.stride(0) % 8 == 0 and
+            x.stride(0) % 8 == 0 and dw.stride(0) % 4 == 0 and dz.data_ptr() % 16 == 0 and x.data_ptr() % 16 == 0 and
+            dw.data_ptr() % 16 == 0 and x.shape[1] >= 8)
+
+
+def wgrad_accumulate(dz, x, dw):
+    """dw[n_out, k_in] += dz[T, n_out]^T @ x[T, k_in] in place on the tensor cores (acai_wgrad_accumulate), reading both
+    operands token-major; falls back to explicit transposes + the forward GEMM when TMA cannot address the operands."""
+    _cuda(dz, x, dw)
+    T, n_out = dz.shape
+    k_in = x.shape[1]
+    if dw.shape != (n_out, k_in) or x.shape[0] != T:
+        raise AcaiError("wgrad_accumulate: shape mismatch")
+    if T == 0:
+        return dw
+    if wgrad_supported(dz, x, dw):
+        name = "acai_wgrad_accumulate" if Profile.active is None else f"acai_wgrad_accumulate[{n_out}x{k_in}x{T}]"
+        _call(name, _lib.load().acai_wgrad_accumulate, _p(dz), dz.stride(0), _p(x), x.stride(0), _dt(dz), _p(dw), dw.stride(0),
+              n_out, k_in, T, _stream(), flops=2.0 * T * n_out * k_in)
+    else:
+        dw += linear(transpose_pad(dz), transpose_pad(x), out_dtype=torch.float32)
+    return dw
+
+
 def colsum(x, out=None, accumulate=False):
     """fp32 column sums of a 2-D tensor in a fixed order (acai_colsum)."""
     _cuda(x, out)

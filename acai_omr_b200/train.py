@@ -74,6 +74,7 @@ class FlatTrainer:
                 view.copy_(p.data)
                 p.data = view
                 p.grad = self.flat_grad[o:o + p.numel()].view(p.shape)
+                p._acai_grad_owned = True      # backward GEMMs accumulate into .grad directly (functional._owned_grad)
         self.shadow = None
         if shadow_dtype is not None:
             self.shadow = self.flat_param.to(shadow_dtype)

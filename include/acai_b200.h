@@ -252,6 +252,14 @@ int acai_gather_rows(const void* src, int32_t dtype, const int64_t* index, int32
 int acai_mae_loss_bwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask, int32_t rows,
                       int32_t feats, const float* scale, void* dpred, int32_t dpred_dtype, void* stream);
 
+/* Weight gradient of a linear layer, accumulated in place:  dw[n_out, k_in] += dz[tokens, n_out]^T . x[tokens, k_in]
+ * (bf16 operands exactly as the forward/backward left them - no transposed copies; fp32 dw, typically the parameter's
+ * slice of the flat gradient buffer).  tcgen05 GEMM with both operands MN-major, split over token ranges, partial
+ * tiles combined by TMA reduce-add.  Returns ACAI_ERR_UNSUPPORTED (nothing written) for non-bf16 operands or rows that
+ * are not 16-byte aligned; the caller then uses acai_transpose + acai_linear_fwd. */
+int acai_wgrad_accumulate(const void* dz, int64_t ldz, const void* x, int64_t ldx, int32_t dtype, float* dw, int64_t ldw,
+                          int32_t n_out, int32_t k_in, int32_t tokens, void* stream);
+
 /* One AdamW update (torch.optim.AdamW semantics; omr_teacher_force_train.py:207, mae_pre_train.py) of a flat fp32
  * parameter segment, `grad_scale` applied to the gradient first (1/world_size after a summed all-reduce).
  * `param_bf16` (may be NULL) receives the bf16 copy of the updated parameters that the tensor-core GEMMs read. */

@@ -393,3 +393,24 @@ def test_trainer_steps_reduce_the_loss_and_refresh_weight_copies():
     assert torch.equal(layers.WEIGHTS.get_t(w, torch.bfloat16), w.detach().bfloat16().t().contiguous())
     assert torch.equal(vit.encoder.frozen_blocks.layers[0].linear1.weight, frozen_before)
     layers.WEIGHTS.clear()
+
+
+@pytest.mark.parametrize("T,n_out,k_in", [(1000, 768, 768), (63, 128, 256), (5000, 3072, 768), (777, 200, 136), (4096, 64, 64),
+                                          (20000, 1024, 4096), (130, 8, 1024)])
+def test_wgrad_accumulate_tensor_core(T, n_out, k_in):
+    """dW += dZ^T X straight from token-major operands (MN-major UMMA operands, split-K, TMA reduce-add)."""
+    dz = rnd(T, n_out, seed=60, dtype=torch.bfloat16)
+    x = rnd(T, k_in, seed=61, dtype=torch.bfloat16)
+    dw0 = rnd(n_out, k_in, seed=62)
+    dw = dw0.clone()
+    assert ops.wgrad_supported(dz, x, dw)
+    ops.wgrad_accumulate(dz, x, dw)
+    ref = dw0.double() + dz.double().t() @ x.double()
+    assert rel_err(dw, ref) < 1e-5
+    # strided views (a slice of a fused QKV gradient buffer) and a row slice of the destination
+    big = rnd(T, 3 * n_out, seed=63, dtype=torch.bfloat16)
+    if n_out % 8 == 0:
+        dwf = torch.zeros(3 * n_out, k_in, device=DEV)
+        ops.wgrad_accumulate(big[:, n_out:2 * n_out], x, dwf[n_out:2 * n_out])
+        assert rel_err(dwf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().t() @ x.double()) < 1e-5
+        assert not bool(dwf[:n_out].any()) and not bool(dwf[2 * n_out:].any())

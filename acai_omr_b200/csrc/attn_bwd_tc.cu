@@ -56,8 +56,9 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_
 }
 
 // ------------------------------------------------------------------------------------------ dQ
+template <int DH>
 __global__ void __launch_bounds__(fb::THREADS, 2)
-attn_bwd_dq_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do,
+attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do,
                  const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v, AttnBwdParams p) {
   using namespace fb;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -100,34 +101,36 @@ attn_bwd_dq_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constan
   if (warp == 4) {
     if (lane == 0 && n_kv > 0) {
       ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
-      ptx::tma_load_2d(smem + OFF_A0, &tma_q, a_full, h * D, q0 + qb * BIG);
-      ptx::tma_load_2d(smem + OFF_A1, &tma_do, a_full, h * D, q0 + qb * BIG);
+      const int hcol = (h * DH) & ~63;
+      ptx::tma_load_2d(smem + OFF_A0, &tma_q, a_full, hcol, q0 + qb * BIG);
+      ptx::tma_load_2d(smem + OFF_A1, &tma_do, a_full, hcol, q0 + qb * BIG);
       int s = 0; uint32_t ph = 0;
       for (int j = 0; j < n_kv; ++j) {
         ptx::mbar_wait(&b_empty[s], ph ^ 1);
         ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
-        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_k, &b_full[s], h * D, k0 + j * SMALL);
-        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_v, &b_full[s], h * D, k0 + j * SMALL);
+        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_k, &b_full[s], hcol, k0 + j * SMALL);
+        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_v, &b_full[s], hcol, k0 + j * SMALL);
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 5) {
     if (lane == 0 && n_kv > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
-      constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, D, false, true);      // B MN-major
-      const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024);
-      const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024);
+      constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, DH, false, true);     // B MN-major
+      const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);    // DH = 32: the tile holds a head pair, 64-byte start offset
+      const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024) + hoff;
+      const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024) + hoff;
       ptx::mbar_wait(a_full, 0);
       for (int j = 0; j < n_kv; ++j) {
         const int st = j % STAGES;
         ptx::mbar_wait(&b_full[st], (j / STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024);
-        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024);
+        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024) + hoff;
+        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024) + hoff;
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, dodesc + 2 * k, vdesc + 2 * k, IDESC_S, k != 0);
+        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, dodesc + 2 * k, vdesc + 2 * k, IDESC_S, k != 0);
         ptx::umma_commit(sp_full);
         ptx::mbar_wait(ds_full, j & 1);
         ptx::tc_fence_after();
@@ -178,7 +181,7 @@ attn_bwd_dq_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constan
       ptx::tc_fence_after();
     }
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
+    for (int c = 0; c < DH / 32; ++c) {
       uint32_t o[32];
       if (n_kv > 0) {
         ptx::tmem_ld_32x32(tmem_base + lane_addr + 128 + c * 32, o);
@@ -187,7 +190,7 @@ attn_bwd_dq_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constan
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[i] = 0u;
       }
-      if (valid) store_row_bf16(p.dq + (int64_t)(q0 + qi) * p.dqs + (int64_t)h * D + c * 32, o, p.scale);
+      if (valid) store_row_bf16(p.dq + (int64_t)(q0 + qi) * p.dqs + (int64_t)h * DH + c * 32, o, p.scale);
     }
   }
   ptx::tc_fence_before();
@@ -196,8 +199,9 @@ attn_bwd_dq_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------ dK / dV
+template <int DH>
 __global__ void __launch_bounds__(fb::THREADS, 2)
-attn_bwd_dkv_tc64(const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v,
+attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v,
                   const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do, AttnBwdParams p) {
   using namespace fb;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -243,34 +247,36 @@ attn_bwd_dkv_tc64(const __grid_constant__ CUtensorMap tma_k, const __grid_consta
   if (warp == 4) {
     if (lane == 0 && n_it > 0) {
       ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
-      ptx::tma_load_2d(smem + OFF_A0, &tma_k, a_full, h * D, k0 + kb * BIG);
-      ptx::tma_load_2d(smem + OFF_A1, &tma_v, a_full, h * D, k0 + kb * BIG);
+      const int hcol = (h * DH) & ~63;
+      ptx::tma_load_2d(smem + OFF_A0, &tma_k, a_full, hcol, k0 + kb * BIG);
+      ptx::tma_load_2d(smem + OFF_A1, &tma_v, a_full, hcol, k0 + kb * BIG);
       int s = 0; uint32_t ph = 0;
       for (int it = 0; it < n_it; ++it) {
         ptx::mbar_wait(&b_empty[s], ph ^ 1);
         ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
-        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_q, &b_full[s], h * D, q0 + (i0 + it) * SMALL);
-        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_do, &b_full[s], h * D, q0 + (i0 + it) * SMALL);
+        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_q, &b_full[s], hcol, q0 + (i0 + it) * SMALL);
+        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_do, &b_full[s], hcol, q0 + (i0 + it) * SMALL);
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 5) {
     if (lane == 0 && n_it > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
-      constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, D, false, true);
-      const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024);
-      const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024);
+      constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, DH, false, true);
+      const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);
+      const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024) + hoff;
+      const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024) + hoff;
       ptx::mbar_wait(a_full, 0);
       for (int it = 0; it < n_it; ++it) {
         const int st = it % STAGES;
         ptx::mbar_wait(&b_full[st], (it / STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024);
-        const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024);
+        const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024) + hoff;
+        const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024) + hoff;
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base, kdesc + 2 * k, qdesc + 2 * k, IDESC_S, k != 0);       // S^T
+        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base, kdesc + 2 * k, qdesc + 2 * k, IDESC_S, k != 0);       // S^T
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, vdesc + 2 * k, dodesc + 2 * k, IDESC_S, k != 0); // dP^T
+        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, vdesc + 2 * k, dodesc + 2 * k, IDESC_S, k != 0); // dP^T
         ptx::umma_commit(sp_full);
         ptx::mbar_wait(ds_full, it & 1);
         ptx::tc_fence_after();
@@ -334,18 +340,21 @@ attn_bwd_dkv_tc64(const __grid_constant__ CUtensorMap tma_k, const __grid_consta
       ptx::tc_fence_after();
     }
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {                  // c 0,1: dV columns 128..191; c 2,3: dK columns 192..255
+    for (int c = 0; c < 2 * (DH / 32); ++c) {      // dV lives in TMEM columns 128.., dK in 192..
+      constexpr int HC = DH / 32;
+      const bool is_k = c >= HC;
+      const int cc = is_k ? c - HC : c;
       uint32_t o[32];
       if (n_it > 0) {
-        ptx::tmem_ld_32x32(tmem_base + lane_addr + 128 + c * 32, o);
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + (is_k ? 192 : 128) + cc * 32, o);
         ptx::tmem_ld_wait();
       } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[i] = 0u;
       }
       if (valid) {
-        if (c < 2) store_row_bf16(p.dv + (int64_t)(k0 + kr) * p.dvs + (int64_t)h * D + c * 32, o, 1.0f);
-        else store_row_bf16(p.dk + (int64_t)(k0 + kr) * p.dks + (int64_t)h * D + (c - 2) * 32, o, p.scale);
+        if (!is_k) store_row_bf16(p.dv + (int64_t)(k0 + kr) * p.dvs + (int64_t)h * DH + cc * 32, o, 1.0f);
+        else store_row_bf16(p.dk + (int64_t)(k0 + kr) * p.dks + (int64_t)h * DH + cc * 32, o, p.scale);
       }
     }
   }
@@ -361,11 +370,11 @@ int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t 
                 void* dq, void* dk, void* dv, int grad_dtype, int64_t dqs, int64_t dks, int64_t dvs, cudaStream_t st) {
   using namespace fb;
   auto misaligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; };
-  if (dtype != ACAI_BF16 || grad_dtype != ACAI_BF16 || head_dim != D || qs % 8 || ks % 8 || vs % 8 || dos % 8 || dqs % 8 ||
+  if (dtype != ACAI_BF16 || grad_dtype != ACAI_BF16 || (head_dim != 64 && head_dim != 32) || qs % 8 || ks % 8 || vs % 8 || dos % 8 || dqs % 8 ||
       dks % 8 || dvs % 8 || total_q <= 0 || total_k <= 0 || misaligned(q) || misaligned(k) || misaligned(v) ||
       misaligned(dout) || misaligned(dq) || misaligned(dk) || misaligned(dv))
     return ACAI_ERR_UNSUPPORTED;
-  const uint64_t cols = (uint64_t)heads * D;
+  const uint64_t cols = (uint64_t)heads * head_dim;
   CUtensorMap q_big, do_big, k_small, v_small, k_big, v_big, q_small, do_small;
   int rc = 0;
   if ((rc = make_tma_2d_bf16(&q_big, q, (uint64_t)total_q, cols, (uint64_t)qs, BIG, D))) return rc;
@@ -378,17 +387,22 @@ int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t 
   if ((rc = make_tma_2d_bf16(&do_small, dout, (uint64_t)total_q, cols, (uint64_t)dos, SMALL, D))) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     attr_set = true;
   }
   AttnBwdParams p{cu_q, cu_k, lse, delta, (int)total_q, causal, scale, scale * 1.4426950408889634f,
                   (__nv_bfloat16*)dq, (__nv_bfloat16*)dk, (__nv_bfloat16*)dv, dqs, dks, dvs};
-  attn_bwd_dq_tc64<<<dim3((max_q + BIG - 1) / BIG, heads, batch), THREADS, SMEM, st>>>(q_big, do_big, k_small, v_small, p);
-  rc = launch_status("attn_bwd_dq_tc64");
+  const dim3 gq((max_q + BIG - 1) / BIG, heads, batch), gk((max_k + BIG - 1) / BIG, heads, batch);
+  if (head_dim == 64) attn_bwd_dq_tc<64><<<gq, THREADS, SMEM, st>>>(q_big, do_big, k_small, v_small, p);
+  else attn_bwd_dq_tc<32><<<gq, THREADS, SMEM, st>>>(q_big, do_big, k_small, v_small, p);
+  rc = launch_status("attn_bwd_dq_tc");
   if (rc) return rc;
-  attn_bwd_dkv_tc64<<<dim3((max_k + BIG - 1) / BIG, heads, batch), THREADS, SMEM, st>>>(k_big, v_big, q_small, do_small, p);
-  return launch_status("attn_bwd_dkv_tc64");
+  if (head_dim == 64) attn_bwd_dkv_tc<64><<<gk, THREADS, SMEM, st>>>(k_big, v_big, q_small, do_small, p);
+  else attn_bwd_dkv_tc<32><<<gk, THREADS, SMEM, st>>>(k_big, v_big, q_small, do_small, p);
+  return launch_status("attn_bwd_dkv_tc");
 }
 
 }  // namespace acai

@@ -44,8 +44,11 @@ struct AttnParams {
   float* lse; int total_q;      // optional [heads, total_q] log2-domain log-sum-exp of every query row (for the backward)
 };
 
+// DH = head_dim (64 or 32).  Shared-memory tiles are always 64 columns (one 128-byte swizzle row) wide: for DH = 32 a
+// tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
+template <int DH>
 __global__ void __launch_bounds__(THREADS, 2)
-attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
+attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
@@ -87,13 +90,14 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && n_kv > 0) {
       ptx::mbar_arrive_expect_tx(q_full, QTILE);
-      ptx::tma_load_2d(smem + OFF_Q, &tma_q, q_full, h * D, q0 + qb * BQ);
+      const int hcol = (h * DH) & ~63;
+      ptx::tma_load_2d(smem + OFF_Q, &tma_q, q_full, hcol, q0 + qb * BQ);
       int s = 0; uint32_t ph = 0;
       for (int j = 0; j < n_kv; ++j) {
         ptx::mbar_wait(&kv_empty[s], ph ^ 1);
         ptx::mbar_arrive_expect_tx(&kv_full[s], 2 * KTILE);
-        ptx::tma_load_2d(smem + OFF_K + s * KTILE, &tma_k, &kv_full[s], h * D, k0 + j * BKV);
-        ptx::tma_load_2d(smem + OFF_V + s * KTILE, &tma_v, &kv_full[s], h * D, k0 + j * BKV);
+        ptx::tma_load_2d(smem + OFF_K + s * KTILE, &tma_k, &kv_full[s], hcol, k0 + j * BKV);
+        ptx::tma_load_2d(smem + OFF_V + s * KTILE, &tma_v, &kv_full[s], hcol, k0 + j * BKV);
         if (++s == KV_STAGES) { s = 0; ph ^= 1; }
       }
     }
@@ -101,15 +105,16 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0 && n_kv > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BQ, BKV);
-      constexpr uint32_t IDESC_O = ptx::idesc_bf16_f32(BQ, D, false, true);   // B = V is MN-major
-      const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_Q), 1024);
+      constexpr uint32_t IDESC_O = ptx::idesc_bf16_f32(BQ, DH, false, true);  // B = V is MN-major
+      const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);                 // this head's 16-byte units inside the 128 B row
+      const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_Q), 1024) + hoff;
       auto issue_s = [&](int j) {                    // S_j into buffer j & 1; K_j sits in stage j % KV_STAGES
         const int st = j % KV_STAGES;
         ptx::mbar_wait(&kv_full[st], (j / KV_STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024);
+        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024) + hoff;
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k)
+        for (int k = 0; k < DH / 16; ++k)
           ptx::umma_f16_ss(tmem_base + (j & 1) * 64, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
         ptx::umma_commit(&s_full[j & 1]);
       };
@@ -120,7 +125,7 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
         const int st = j % KV_STAGES;
         ptx::mbar_wait(&p_full[j & 1], (j >> 1) & 1);
         ptx::tc_fence_after();
-        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + st * KTILE), 1024);
+        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + st * KTILE), 1024) + hoff;
 #pragma unroll
         for (int kk = 0; kk < BKV / 16; ++kk)       // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
           ptx::umma_f16_ts(tmem_base + 128, tmem_base + (j & 1) * 64 + kk * 8, vdesc + (uint64_t)kk * (16 * 128 >> 4),
@@ -172,7 +177,7 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
           ptx::mbar_wait(o_step, (j - 1) & 1);      // O holds P_{j-1} V_{j-1}
           ptx::tc_fence_after();
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
+          for (int c = 0; c < DH / 32; ++c) {
             uint32_t o[32];
             ptx::tmem_ld_32x32(tmem_o + c * 32, o);
             ptx::tmem_ld_wait();
@@ -206,9 +211,9 @@ attn_fwd_tc64(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__
     }
     const float inv = l > 0.0f ? 1.0f / l : 0.0f;
     if (p.lse && valid) p.lse[(int64_t)h * p.total_q + q0 + qi] = l > 0.0f ? m * scale_log2 + log2f(l) : INFINITY;
-    const int64_t off = (int64_t)(q0 + qi) * p.o_stride + (int64_t)h * D;
+    const int64_t off = (int64_t)(q0 + qi) * p.o_stride + (int64_t)h * DH;
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
+    for (int c = 0; c < DH / 32; ++c) {
       uint32_t o[32];
       if (n_kv > 0) {
         ptx::tmem_ld_32x32(tmem_o + c * 32, o);
@@ -248,26 +253,29 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
                    const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
                    int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, float* lse,
                    cudaStream_t st) {
-  if (dtype != ACAI_BF16 || head_dim != D || qs % 8 || ks % 8 || vs % 8 || os % 8 || total_q <= 0 || total_k <= 0 ||
+  if (dtype != ACAI_BF16 || (head_dim != 64 && head_dim != 32) || qs % 8 || ks % 8 || vs % 8 || os % 8 || total_q <= 0 || total_k <= 0 ||
       (reinterpret_cast<uintptr_t>(q) & 15) || (reinterpret_cast<uintptr_t>(k) & 15) ||
       (reinterpret_cast<uintptr_t>(v) & 15) || (reinterpret_cast<uintptr_t>(out) & 15))
     return ACAI_ERR_UNSUPPORTED;
   CUtensorMap tq, tk, tv;
-  int rc = make_tma_2d_bf16(&tq, q, (uint64_t)total_q, (uint64_t)heads * D, (uint64_t)qs, BQ, D);
+  const uint64_t cols = (uint64_t)heads * head_dim;
+  int rc = make_tma_2d_bf16(&tq, q, (uint64_t)total_q, cols, (uint64_t)qs, BQ, D);
   if (rc) return rc;
-  rc = make_tma_2d_bf16(&tk, k, (uint64_t)total_k, (uint64_t)heads * D, (uint64_t)ks, BKV, D);
+  rc = make_tma_2d_bf16(&tk, k, (uint64_t)total_k, cols, (uint64_t)ks, BKV, D);
   if (rc) return rc;
-  rc = make_tma_2d_bf16(&tv, v, (uint64_t)total_k, (uint64_t)heads * D, (uint64_t)vs, BKV, D);
+  rc = make_tma_2d_bf16(&tv, v, (uint64_t)total_k, cols, (uint64_t)vs, BKV, D);
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     attr_set = true;
   }
   AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
-  attn_fwd_tc64<<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
-  return launch_status("attn_fwd_tc64");
+  if (head_dim == 64) attn_fwd_tc<64><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+  else attn_fwd_tc<32><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+  return launch_status("attn_fwd_tc");
 }
 
 }  // namespace acai

@@ -70,3 +70,13 @@ def synth_lmx(length: int, seed: int, vocab: int = 227, bos: int = 0, eos: int =
     g = torch.Generator().manual_seed(4321 + seed)
     body = torch.randint(first, vocab, (length - 2,), generator=g)
     return torch.cat([torch.tensor([bos]), body, torch.tensor([eos])])
+
+
+def decoder_flops(tgt_lens, mem_lens, layers=12, d=1024, mlp=4096, vocab=227):
+    """Algorithmic forward FLOPs of the teacher-forced LMX decoder: per target token and layer 2*(4d^2 self + 2d^2 cross q/o
+    + 2*d*mlp); per memory token and layer 2*(2d^2) for the cross K/V projection; causal self-attention 2*T^2*d and
+    cross-attention 4*T*S*d per layer per system; vocabulary projection 2*d*vocab per token."""
+    T, S = sum(tgt_lens), sum(mem_lens)
+    lin = layers * (T * 2.0 * (6 * d * d + 2 * d * mlp) + S * 2.0 * 2 * d * d) + T * 2.0 * d * vocab
+    attn = layers * sum(2.0 * t * t * d + 4.0 * t * s * d for t, s in zip(tgt_lens, mem_lens))
+    return lin + attn

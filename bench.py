@@ -307,6 +307,106 @@ def run_decode(args, rank, world, device):
     }
 
 
+# ------------------------------------------------------------------------------------------ training legs (configs[3], configs[4])
+TRAIN_SYSTEMS = 64
+
+
+def run_train(args, rank, world, device, kind):
+    """One data-parallel optimisation step per timed iteration: forward + loss + backward on this rank's shard
+    (TRAIN_SYSTEMS systems, bf16 autocast), ONE NCCL all-reduce of the flat fp32 gradient buffer, fused AdamW.
+    kind = "tf": TeacherForcedViTOMR (12-layer 768d encoder fully fine-tuned + 12-layer 1024d decoder) + OMRCELoss;
+    kind = "mae": MAE (mask ratio 0.75, 12-layer encoder + 8-layer 512d pixel decoder) + MAELoss.  Dropout 0 (the kernels
+    implement the deterministic path)."""
+    from acai_omr_b200 import layers, ops, synth, train
+    from acai_omr_b200.models import models as M
+    n = TRAIN_SYSTEMS
+    torch.manual_seed(0)
+    imgs = [synth.synth_system(h, w, rank * n + i).to(device) for i, (h, w) in enumerate(synth.system_shapes(n))]
+    lens = [(t.shape[-2] // 16) * (t.shape[-1] // 16) for t in imgs]
+    if kind == "tf":
+        enc = M.FineTuneOMREncoder(**encoder_kwargs(), transformer_dropout=0.0)
+        dec = M.OMRDecoder(1536, M.default_vocab_path(), num_layers=DEC_LAYERS, hidden_dim=DEC_D, num_heads=DEC_H,
+                           mlp_dim=DEC_MLP, transformer_dropout=0.0)
+        model = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dropout=0.0)
+        synth.rerandomise_(model, 1)
+        model = model.to(device).train()
+        tgt_lens = synth.lmx_lengths(n)
+        batch = list(zip(imgs, [synth.synth_lmx(L, rank * n + i).to(device) for i, L in enumerate(tgt_lens)]))
+        groups, _ = model.create_fine_tune_param_groups(1e-4, 1e-5, 0.9)
+        tr = train.FlatTrainer(model, groups)
+        step = lambda: train.teacher_forced_step(model, batch, tr)
+        work = {"lmx_tokens_per_gpu": sum(tgt_lens) - n}
+        flops = 3.0 * (synth.encoder_flops(lens) + synth.decoder_flops([t - 1 for t in tgt_lens], lens)
+                       + 2.0 * sum(lens) * (768 * 4096 + 4096 * 1024))
+        name = "configs[3]: teacher-forced ViTOMR fwd/bwd + grad all-reduce + AdamW"
+    else:
+        model = M.MAE(0.75, 16, 60, 200)
+        synth.rerandomise_(model, 2)
+        model = model.to(device).train()
+        batch = list(zip(imgs, imgs))
+        tr = train.FlatTrainer(model, lr=1.5e-4)
+        step = lambda: train.mae_step(model, batch, tr)
+        work = {}
+        flops = None
+        name = "configs[4]: MAE pre-training fwd/bwd + grad all-reduce + AdamW"
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+    for _ in range(3):
+        sums = step()
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    k = max(3, min(args.steps, 10))
+    n0 = ops.launch_count()
+    total = 0.0
+    for _ in range(k):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sums = step()
+        e1.record()
+        e1.synchronize()
+        total += e0.elapsed_time(e1)
+    launches = (ops.launch_count() - n0) // k
+    with ops.Profile() as prof:
+        step()
+    kern = prof.summary()
+    loss = float(sums[0] / sums[1])
+    t = torch.tensor([total / k], dtype=torch.float64, device=device)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms = float(t[0])
+    peak_mem = torch.cuda.max_memory_allocated() / 2 ** 30
+    numel = tr.numel
+    del tr, model, batch
+    layers.WEIGHTS.clear()
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    peaks = load_peaks()
+    merged = {}
+    for k_, v_ in kern.items():
+        merged.setdefault(k_.split("[")[0], dict(ms=0.0))["ms"] += v_["ms"]
+    gemm = [v_ for k_, v_ in kern.items() if k_.startswith("acai_linear_fwd") or k_.startswith("acai_wgrad")]
+    g_ms, g_fl = sum(v_["ms"] for v_ in gemm), sum(v_["flops"] for v_ in gemm)
+    out = {
+        "metric": "training systems/sec (fwd + bwd + gradient all-reduce + AdamW)", "value": world * n / (ms * 1e-3),
+        "unit": UNIT, "ms_per_step": ms, "n_gpus": world, "scaling": "weak", "dtype": "bf16 autocast, fp32 master weights/grads",
+        "config": dict({"workload": name, "systems_per_gpu": n, "patch_tokens_per_gpu": sum(lens),
+                        "trainable_parameters": numel, "l2": "flushed between steps",
+                        "collective": "one NCCL all-reduce of the flat fp32 gradient buffer per step" if world > 1 else "none (1 GPU)"},
+                       **work),
+        "loss_last_step": loss, "gpu_launches_per_step": launches, "peak_mem_gib": round(peak_mem, 1),
+        "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05 + gemm_wgrad_tcgen05", "achieved": g_fl / (g_ms * 1e-3) / 1e12,
+                     "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                     "frac": g_fl / (g_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"],
+                     "kernel_share_of_step": g_ms / sum(v["ms"] for v in kern.values())},
+        "kernels_ms_per_step": {k_: round(v_["ms"], 3) for k_, v_ in sorted(merged.items(), key=lambda kv: -kv[1]["ms"])},
+    }
+    if flops is not None:
+        out["roofline"]["whole_step_tflops"] = flops / (ms * 1e-3) / 1e12
+    return out
+
+
 # ------------------------------------------------------------------------------------------ CPU arms
 def oracle_encoder_step(imgs, sd, threads):
     """The reference algorithm (oracle port, fp32, CPU) for the encoder forward on `imgs`."""
@@ -380,6 +480,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-decode", action="store_true", help="skip the configs[2] decode leg")
+    ap.add_argument("--no-train", action="store_true", help="skip the configs[3]/[4] training legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -399,9 +500,16 @@ def main():
     line = run_ours(args, rank, world, device)
     torch.cuda.empty_cache()
     dec = None if args.no_decode else run_decode(args, rank, world, device)
+    torch.cuda.empty_cache()
+    tf = None if args.no_train else run_train(args, rank, world, device, "tf")
+    mae = None if args.no_train else run_train(args, rank, world, device, "mae")
     if line is not None:
         if dec is not None:
             line["decode"] = dec
+        if tf is not None:
+            line["train_teacher_forced"] = tf
+        if mae is not None:
+            line["train_mae"] = mae
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line), flush=True)

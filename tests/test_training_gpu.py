@@ -95,7 +95,7 @@ def torch_attention(q, k, v, lens_q, lens_k, H, causal):
     return torch.cat(outs)
 
 
-@pytest.mark.parametrize("H,d", [(4, 8), (3, 12), (2, 32), (2, 64), (12, 64), (1, 128)])
+@pytest.mark.parametrize("H,d", [(4, 8), (3, 12), (2, 32), (16, 32), (2, 64), (12, 64), (1, 128)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("causal", [False, True])
 def test_self_attention_backward(H, d, dtype, causal):
@@ -115,7 +115,7 @@ def test_self_attention_backward(H, d, dtype, causal):
         assert rel_err(qkv.grad[:, i * D:(i + 1) * D], ref_in.grad[:, i * D:(i + 1) * D]) < tol, name
 
 
-@pytest.mark.parametrize("H,d", [(4, 12), (2, 64), (16, 64)])
+@pytest.mark.parametrize("H,d", [(4, 12), (3, 32), (2, 64), (16, 64)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_cross_attention_backward(H, d, dtype):
     lens_q, lens_k = [5, 64, 1, 100], [130, 7, 300, 64]

@@ -24,8 +24,8 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t 
                      uint32_t box_cols);
 
 namespace fb {
-constexpr int BIG = 128, SMALL = 64, D = 64, STAGES = 3;
-constexpr int THREADS = 192;
+constexpr int BIG = 128, SMALL = 64, D = 64, STAGES = 4;
+constexpr int THREADS = 320;           // warps 0-7 elementwise (4 lane quarters x 2 column halves), 8 TMA, 9 MMA
 constexpr uint32_t BIGTILE = BIG * D * 2;           // 16 KB
 constexpr uint32_t SMALLTILE = SMALL * D * 2;       // 8 KB
 constexpr uint32_t OFF_A0 = 0, OFF_A1 = BIGTILE;    // the two resident 128-row tiles (Q,dO or K,V)
@@ -56,19 +56,22 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_
 }
 
 // ------------------------------------------------------------------------------------------ dQ
+// TMEM: S[0] 0..63, S[1] 64..127 (double-buffered: S_{j+1} is computed while block j is in the elementwise phase),
+// dP 128..191 (single buffer, handed back as soon as the elementwise warps have it in registers), dQ 192..255.
 template <int DH>
 __global__ void __launch_bounds__(fb::THREADS, 2)
 attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do,
-                 const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v, AttnBwdParams p) {
+               const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v, AttnBwdParams p) {
   using namespace fb;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* a_full = bars;                     // Q and dO tiles
   uint64_t* b_full = bars + 1;                 // STAGES
   uint64_t* b_empty = b_full + STAGES;         // STAGES
-  uint64_t* sp_full = b_empty + STAGES;        // S and dP of the current block are in TMEM
-  uint64_t* ds_full = sp_full + 1;             // 128 arrivals: dS written
-  uint64_t* acc_full = ds_full + 1;            // last dQ MMA landed
+  uint64_t* sp_full = b_empty + STAGES;        // 2: S (buffer j&1) and dP of block j are in TMEM
+  uint64_t* ds_full = sp_full + 2;             // 2 x 256 arrivals: dS of block j written over S buffer j&1
+  uint64_t* dp_free = ds_full + 2;             // 256 arrivals: dP of block j is in registers
+  uint64_t* acc_full = dp_free + 1;            // last dQ MMA landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -80,13 +83,14 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
   if (p.causal) { const int last = qb * BIG + BIG + shift; kv_end = last < lk ? (last < 0 ? 0 : last) : lk; }
   const int n_kv = (kv_end + SMALL - 1) / SMALL;
 
-  if (warp == 5 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     ptx::mbar_init(a_full, 1);
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
-    ptx::mbar_init(sp_full, 1); ptx::mbar_init(ds_full, 128); ptx::mbar_init(acc_full, 1);
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&sp_full[i], 1); ptx::mbar_init(&ds_full[i], 256); }
+    ptx::mbar_init(dp_free, 256); ptx::mbar_init(acc_full, 1);
     ptx::fence_barrier_init();
   }
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
       ptx::prefetch_tensormap(&tma_q); ptx::prefetch_tensormap(&tma_do);
       ptx::prefetch_tensormap(&tma_k); ptx::prefetch_tensormap(&tma_v);
@@ -98,10 +102,10 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0 && n_kv > 0) {
-      ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
       const int hcol = (h * DH) & ~63;
+      ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
       ptx::tma_load_2d(smem + OFF_A0, &tma_q, a_full, hcol, q0 + qb * BIG);
       ptx::tma_load_2d(smem + OFF_A1, &tma_do, a_full, hcol, q0 + qb * BIG);
       int s = 0; uint32_t ph = 0;
@@ -113,53 +117,80 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     if (lane == 0 && n_kv > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
       constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, DH, false, true);     // B MN-major
       const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);    // DH = 32: the tile holds a head pair, 64-byte start offset
       const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024) + hoff;
       const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024) + hoff;
+      auto kdesc_of = [&](int j) { return ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + (j % STAGES) * SMALLTILE), 1024) + hoff; };
+      auto vdesc_of = [&](int j) { return ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + (j % STAGES) * SMALLTILE), 1024) + hoff; };
+      auto issue_s = [&](int j) {                  // S_j into buffer j & 1 (waits for K_j / V_j to land)
+        ptx::mbar_wait(&b_full[j % STAGES], (j / STAGES) & 1);
+        ptx::tc_fence_after();
+        const uint64_t kd = kdesc_of(j);
+#pragma unroll
+        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + (j & 1) * 64, qdesc + 2 * k, kd + 2 * k, IDESC_S, k != 0);
+      };
+      auto issue_dp = [&](int j) {                 // dP_j, then S_j and dP_j are announced together
+        const uint64_t vd = vdesc_of(j);
+#pragma unroll
+        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + 128, dodesc + 2 * k, vd + 2 * k, IDESC_S, k != 0);
+        ptx::umma_commit(&sp_full[j & 1]);
+      };
       ptx::mbar_wait(a_full, 0);
+      issue_s(0);
+      issue_dp(0);
+      if (n_kv > 1) issue_s(1);
       for (int j = 0; j < n_kv; ++j) {
-        const int st = j % STAGES;
-        ptx::mbar_wait(&b_full[st], (j / STAGES) & 1);
+        if (j + 1 < n_kv) {
+          ptx::mbar_wait(dp_free, j & 1);          // block j's dP is in registers: the buffer can take dP_{j+1}
+          ptx::tc_fence_after();
+          issue_dp(j + 1);
+        }
+        ptx::mbar_wait(&ds_full[j & 1], (j >> 1) & 1);
         ptx::tc_fence_after();
-        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024) + hoff;
-        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024) + hoff;
-#pragma unroll
-        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
-#pragma unroll
-        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, dodesc + 2 * k, vdesc + 2 * k, IDESC_S, k != 0);
-        ptx::umma_commit(sp_full);
-        ptx::mbar_wait(ds_full, j & 1);
-        ptx::tc_fence_after();
+        const uint64_t kd = kdesc_of(j);
 #pragma unroll
         for (int kk = 0; kk < SMALL / 16; ++kk)
-          ptx::umma_f16_ts(tmem_base + 128, tmem_base + kk * 8, kdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (j | kk) != 0);
-        ptx::umma_commit(&b_empty[st]);
+          ptx::umma_f16_ts(tmem_base + 192, tmem_base + (j & 1) * 64 + (kk >> 1) * 32 + (kk & 1) * 8,
+                           kd + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (j | kk) != 0);
+        ptx::umma_commit(&b_empty[j % STAGES]);
         if (j == n_kv - 1) ptx::umma_commit(acc_full);
+        if (j + 2 < n_kv) issue_s(j + 2);          // overwrites dS_j: tcgen05 ops execute in issue order
       }
     }
   } else {
-    const int r = warp * 32 + lane;
+    const int r = (warp & 3) * 32 + lane, half = warp >> 2;       // this thread: query row r, key columns half*32..+31 of a block
     const int qi = qb * BIG + r;
     const bool valid = qi < lq;
     const int my_end = !valid ? 0 : (p.causal ? max(0, min(lk, qi + shift + 1)) : lk);
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
     const float sl2 = p.scale_log2;
     const float L = valid ? p.lse[(int64_t)h * p.total_q + q0 + qi] : INFINITY;
     const float dl = valid ? p.delta[(int64_t)h * p.total_q + q0 + qi] : 0.0f;
     for (int j = 0; j < n_kv; ++j) {
-      ptx::mbar_wait(sp_full, j & 1);
+      const uint32_t tmem_s = tmem_base + lane_addr + (j & 1) * 64 + half * 32;
+      ptx::mbar_wait(&sp_full[j & 1], (j >> 1) & 1);
       ptx::tc_fence_after();
+      uint32_t s[32], dp[32], pk[16];
+      ptx::tmem_ld_32x32(tmem_base + lane_addr + 128 + half * 32, dp);
+      ptx::tmem_ld_32x32(tmem_s, s);
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(dp_free);
+      const int kbase = j * SMALL + half * 32;
+      if (kbase + 32 <= my_end) {                  // whole half visible (the common case): no masking instructions
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t s[32], dp[32], pk[16];
-        ptx::tmem_ld_32x32(tmem_base + lane_addr + half * 32, s);
-        ptx::tmem_ld_32x32(tmem_base + lane_addr + 64 + half * 32, dp);
-        ptx::tmem_ld_wait();
-        const int kbase = j * SMALL + half * 32;
+        for (int i = 0; i < 16; ++i) {
+          const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -L));
+          const __nv_bfloat162 hh = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[2 * i]) - dl),
+                                                          p1 * (__uint_as_float(dp[2 * i + 1]) - dl));
+          pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+        }
+      } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
@@ -170,21 +201,22 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
                                                           p1 * (__uint_as_float(dp[2 * i + 1]) - dl));
           pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
         }
-        ptx::tmem_st_32x16(tmem_base + lane_addr + half * 16, pk);
       }
+      // dS (bf16, 16 columns) goes over the START of this warp's own S half, never over the half the sibling warp reads
+      ptx::tmem_st_32x16(tmem_s, pk);
       ptx::tmem_st_wait();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(ds_full);
+      ptx::mbar_arrive(&ds_full[j & 1]);
     }
     if (n_kv > 0) {
       ptx::mbar_wait(acc_full, 0);
       ptx::tc_fence_after();
     }
-#pragma unroll
-    for (int c = 0; c < DH / 32; ++c) {
+    if (half < DH / 32) {
+      const int c = half;
       uint32_t o[32];
       if (n_kv > 0) {
-        ptx::tmem_ld_32x32(tmem_base + lane_addr + 128 + c * 32, o);
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + 192 + c * 32, o);
         ptx::tmem_ld_wait();
       } else {
 #pragma unroll
@@ -195,7 +227,7 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  if (warp == 8) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------ dK / dV
@@ -226,13 +258,13 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
   const int n_q = (lq + SMALL - 1) / SMALL;
   const int n_it = n_q > i0 ? n_q - i0 : 0;
 
-  if (warp == 5 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     ptx::mbar_init(a_full, 1);
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
-    ptx::mbar_init(sp_full, 1); ptx::mbar_init(ds_full, 128); ptx::mbar_init(acc_full, 1);
+    ptx::mbar_init(sp_full, 1); ptx::mbar_init(ds_full, 256); ptx::mbar_init(acc_full, 1);
     ptx::fence_barrier_init();
   }
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
       ptx::prefetch_tensormap(&tma_q); ptx::prefetch_tensormap(&tma_do);
       ptx::prefetch_tensormap(&tma_k); ptx::prefetch_tensormap(&tma_v);
@@ -244,7 +276,7 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0 && n_it > 0) {
       ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
       const int hcol = (h * DH) & ~63;
@@ -259,7 +291,7 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     if (lane == 0 && n_it > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
       constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, DH, false, true);
@@ -282,55 +314,63 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
         ptx::tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < SMALL / 16; ++kk)      // dV += P^T dO_i
-          ptx::umma_f16_ts(tmem_base + 128, tmem_base + kk * 8, dodesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+          ptx::umma_f16_ts(tmem_base + 128, tmem_base + (kk >> 1) * 32 + (kk & 1) * 8, dodesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
 #pragma unroll
         for (int kk = 0; kk < SMALL / 16; ++kk)      // dK += dS^T Q_i
-          ptx::umma_f16_ts(tmem_base + 192, tmem_base + 64 + kk * 8, qdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+          ptx::umma_f16_ts(tmem_base + 192, tmem_base + 64 + (kk >> 1) * 32 + (kk & 1) * 8, qdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
         ptx::umma_commit(&b_empty[st]);
         if (it == n_it - 1) ptx::umma_commit(acc_full);
       }
     }
   } else {
-    const int r = warp * 32 + lane;
+    const int r = (warp & 3) * 32 + lane, half = warp >> 2;       // key row r, query columns half*32..+31 of a block
+    const int tid = threadIdx.x;                                   // 0..255 here
     const int kr = kb * BIG + r;
     const bool valid = kr < lk;
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
     const float sl2 = p.scale_log2;
     for (int it = 0; it < n_it; ++it) {
       const int qbase = (i0 + it) * SMALL;
       float* vb = vec + (it & 1) * 128;
-      {                                            // stage L / delta of this query block (broadcast reads below)
-        const int q = qbase + (r & 63);
-        const float* src = r < 64 ? p.lse : p.delta;
-        vb[r] = q < lq ? src[(int64_t)h * p.total_q + q0 + q] : (r < 64 ? INFINITY : 0.0f);
+      if (tid < 128) {                             // stage L / delta of this query block (broadcast reads below)
+        const int q = qbase + (tid & 63);
+        const float* src = tid < 64 ? p.lse : p.delta;
+        vb[tid] = q < lq ? src[(int64_t)h * p.total_q + q0 + q] : (tid < 64 ? INFINITY : 0.0f);
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       // first query column this key row may attend to (causal), all columns masked for rows past the sequence end
       const int cmin = !valid ? SMALL : (p.causal ? kr - shift - qbase : 0);
       ptx::mbar_wait(sp_full, it & 1);
       ptx::tc_fence_after();
+      uint32_t s[32], dp[32], pk[16], dk[16];
+      ptx::tmem_ld_32x32(tmem_base + lane_addr + half * 32, s);
+      ptx::tmem_ld_32x32(tmem_base + lane_addr + 64 + half * 32, dp);
+      ptx::tmem_ld_wait();
+      const float4* vl = reinterpret_cast<const float4*>(vb + half * 32);
+      const float4* vd = reinterpret_cast<const float4*>(vb + 64 + half * 32);
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t s[32], dp[32], pk[16], dk[16];
-        ptx::tmem_ld_32x32(tmem_base + lane_addr + half * 32, s);
-        ptx::tmem_ld_32x32(tmem_base + lane_addr + 64 + half * 32, dp);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int c = half * 32 + 2 * i;
-          float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -vb[c]));
-          float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -vb[c + 1]));
-          if (c < cmin) p0 = 0.0f;
-          if (c + 1 < cmin) p1 = 0.0f;
-          const __nv_bfloat162 hp = __floats2bfloat162_rn(p0, p1);
-          const __nv_bfloat162 hd = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[2 * i]) - vb[64 + c]),
-                                                          p1 * (__uint_as_float(dp[2 * i + 1]) - vb[64 + c + 1]));
-          pk[i] = *reinterpret_cast<const uint32_t*>(&hp);
-          dk[i] = *reinterpret_cast<const uint32_t*>(&hd);
-        }
-        ptx::tmem_st_32x16(tmem_base + lane_addr + half * 16, pk);
-        ptx::tmem_st_32x16(tmem_base + lane_addr + 64 + half * 16, dk);
+      for (int i4 = 0; i4 < 8; ++i4) {
+        const float4 l4 = vl[i4], d4 = vd[i4];
+        const int c = half * 32 + 4 * i4;
+        float p0 = fast_exp2(fmaf(__uint_as_float(s[4 * i4]), sl2, -l4.x));
+        float p1 = fast_exp2(fmaf(__uint_as_float(s[4 * i4 + 1]), sl2, -l4.y));
+        float p2 = fast_exp2(fmaf(__uint_as_float(s[4 * i4 + 2]), sl2, -l4.z));
+        float p3 = fast_exp2(fmaf(__uint_as_float(s[4 * i4 + 3]), sl2, -l4.w));
+        if (c < cmin) p0 = 0.0f;
+        if (c + 1 < cmin) p1 = 0.0f;
+        if (c + 2 < cmin) p2 = 0.0f;
+        if (c + 3 < cmin) p3 = 0.0f;
+        const __nv_bfloat162 hp0 = __floats2bfloat162_rn(p0, p1), hp1 = __floats2bfloat162_rn(p2, p3);
+        const __nv_bfloat162 hd0 = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[4 * i4]) - d4.x),
+                                                         p1 * (__uint_as_float(dp[4 * i4 + 1]) - d4.y));
+        const __nv_bfloat162 hd1 = __floats2bfloat162_rn(p2 * (__uint_as_float(dp[4 * i4 + 2]) - d4.z),
+                                                         p3 * (__uint_as_float(dp[4 * i4 + 3]) - d4.w));
+        pk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hp0); pk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hp1);
+        dk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hd0); dk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hd1);
       }
+      // P^T / dS^T go over the start of this warp's own halves of S^T / dP^T (columns 0..15 or 32..47, +64)
+      ptx::tmem_st_32x16(tmem_base + lane_addr + half * 32, pk);
+      ptx::tmem_st_32x16(tmem_base + lane_addr + 64 + half * 32, dk);
       ptx::tmem_st_wait();
       ptx::tc_fence_before();
       ptx::mbar_arrive(ds_full);
@@ -339,11 +379,10 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
       ptx::mbar_wait(acc_full, 0);
       ptx::tc_fence_after();
     }
+    // half 0 stores dV (TMEM columns 128..), half 1 stores dK (192..)
 #pragma unroll
-    for (int c = 0; c < 2 * (DH / 32); ++c) {      // dV lives in TMEM columns 128.., dK in 192..
-      constexpr int HC = DH / 32;
-      const bool is_k = c >= HC;
-      const int cc = is_k ? c - HC : c;
+    for (int cc = 0; cc < DH / 32; ++cc) {
+      const bool is_k = half == 1;
       uint32_t o[32];
       if (n_it > 0) {
         ptx::tmem_ld_32x32(tmem_base + lane_addr + (is_k ? 192 : 128) + cc * 32, o);
@@ -360,7 +399,7 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  if (warp == 8) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // returns ACAI_ERR_UNSUPPORTED when the problem does not qualify (the caller then runs the SIMT kernels)

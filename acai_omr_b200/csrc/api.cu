@@ -2,6 +2,8 @@
 // acai_linear_fwd dispatcher (tcgen05 tensor-core GEMM when the problem qualifies, SIMT otherwise).
 #include <stdarg.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace acai {
@@ -32,6 +34,8 @@ int linear_simt(const void* a, int a_dt, int64_t lda, const void* w, int w_dt, i
                 const void* res, int res_dt, int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K,
                 int act, cudaStream_t st);
 // returns ACAI_ERR_UNSUPPORTED when the problem does not qualify for the tensor-core path
+int linear_gemv_bf16(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
+                     int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K, int act, cudaStream_t st);
 int linear_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res,
                    int res_dt, int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K, int act,
                    cudaStream_t st);
@@ -65,6 +69,13 @@ extern "C" int acai_linear_fwd(const void* a, int32_t a_dtype, int64_t lda, cons
   if (M == 0) return ACAI_OK;
   cudaStream_t st = (cudaStream_t)stream;
   if (a_dtype == ACAI_BF16 && w_dtype == ACAI_BF16) {
+    // decode steps at very small batch: stream the weights once through all SMs instead of one 128-row tile column
+    // (measured cross-over against the tcgen05 path: M = 4; ACAI_GEMV_MAX_M overrides it for benchmarking)
+    static const int gemv_max_m = [] { const char* e = getenv("ACAI_GEMV_MAX_M"); return e ? atoi(e) : 4; }();
+    if (M <= gemv_max_m) {
+      int rc = linear_gemv_bf16(a, lda, w, ldw, bias, residual, res_dtype, ldr, out, out_dtype, ldo, M, N, K, act, st);
+      if (rc != ACAI_ERR_UNSUPPORTED) return rc;
+    }
     int rc = linear_tcgen05(a, lda, w, ldw, bias, residual, res_dtype, ldr, out, out_dtype, ldo, M, N, K, act, st);
     if (rc != ACAI_ERR_UNSUPPORTED) return rc;
   }

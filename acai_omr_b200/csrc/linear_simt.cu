@@ -212,6 +212,78 @@ gemv_small_m(const void* __restrict__ a, int a_dt, int64_t lda, const void* __re
   }
 }
 
+// bf16 decode-step GEMV for M <= 32 rows (greedy decode at small batch): one warp per output column n, the weight row
+// streamed exactly once with 16-byte loads that bypass L1 allocation, FOUR loads in flight per lane before the first
+// FMA (a 2 KB weight row is otherwise a chain of dependent DRAM round trips); the M activation rows come from L1.
+// All SMs take part (N / 8 CTAs), so a [1024 x 1024] projection costs one DRAM latency instead of the 16-CTA tensor-core
+// launch it replaces (the tcgen05 tile is 128 rows tall: at M = 1 it moves 2 MB of weights through 16 SMs).
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float dot8_bf16(const uint4& a, const uint4& b, float acc) {
+  const __nv_bfloat162* x = reinterpret_cast<const __nv_bfloat162*>(&a);
+  const __nv_bfloat162* y = reinterpret_cast<const __nv_bfloat162*>(&b);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 fx = __bfloat1622float2(x[i]), fy = __bfloat1622float2(y[i]);
+    acc = fmaf(fx.x, fy.x, acc);
+    acc = fmaf(fx.y, fy.y, acc);
+  }
+  return acc;
+}
+template <int MAXM>
+__global__ void __launch_bounds__(256)
+gemv_bf16_small_m(const __nv_bfloat16* __restrict__ a, int64_t lda, const __nv_bfloat16* __restrict__ w, int64_t ldw,
+                  LinearEpi epi, int M, int N, int K) {
+  const int lane = threadIdx.x & 31;
+  const int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (n >= N) return;
+  float acc[MAXM];
+#pragma unroll
+  for (int m = 0; m < MAXM; ++m) acc[m] = 0.0f;
+  const uint4* wp = reinterpret_cast<const uint4*>(w + (int64_t)n * ldw);
+  const int nv = K >> 3;
+  for (int v0 = lane; v0 < nv; v0 += 128) {
+    uint4 wr[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) wr[u] = v0 + 32 * u < nv ? ldg_stream(wp + v0 + 32 * u) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = v0 + 32 * u;
+      if (idx < nv) {
+#pragma unroll
+        for (int m = 0; m < MAXM; ++m)
+          if (m < M) acc[m] = dot8_bf16(__ldg(reinterpret_cast<const uint4*>(a + (int64_t)m * lda) + idx), wr[u], acc[m]);
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < MAXM; ++m) {
+    if (m < M) {                                   // M is uniform: no divergence around the shuffles
+      const float v = warp_sum(acc[m]);
+      if (lane == 0) epi.store(m, n, 0, v);
+    }
+  }
+}
+
+// bf16 x bf16, M <= 32, 16-byte addressable rows: the decode-step projections at small batch.  ACAI_ERR_UNSUPPORTED otherwise.
+int linear_gemv_bf16(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
+                     int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K, int act, cudaStream_t st) {
+  if (M > 32 || K % 8 || lda % 8 || ldw % 8 || (reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(w) & 15))
+    return ACAI_ERR_UNSUPPORTED;
+  LinearEpi epi{bias, res, res_dt, ldr, out, out_dt, ldo, act};
+  const __nv_bfloat16* ab = reinterpret_cast<const __nv_bfloat16*>(a);
+  const __nv_bfloat16* wb = reinterpret_cast<const __nv_bfloat16*>(w);
+  const dim3 grid((N + 7) / 8);
+  if (M <= 2) gemv_bf16_small_m<2><<<grid, 256, 0, st>>>(ab, lda, wb, ldw, epi, M, N, K);
+  else if (M <= 8) gemv_bf16_small_m<8><<<grid, 256, 0, st>>>(ab, lda, wb, ldw, epi, M, N, K);
+  else if (M <= 16) gemv_bf16_small_m<16><<<grid, 256, 0, st>>>(ab, lda, wb, ldw, epi, M, N, K);
+  else gemv_bf16_small_m<32><<<grid, 256, 0, st>>>(ab, lda, wb, ldw, epi, M, N, K);
+  return launch_status("gemv_bf16_small_m");
+}
+
 int linear_simt(const void* a, int a_dt, int64_t lda, const void* w, int w_dt, int64_t ldw, const float* bias,
                 const void* res, int res_dt, int64_t ldr, void* out, int out_dt, int64_t ldo,
                 int M, int N, int K, int act, cudaStream_t st) {

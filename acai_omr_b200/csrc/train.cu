@@ -534,3 +534,94 @@ extern "C" int acai_wgrad_accumulate(const void* dz, int64_t ldz, const void* x,
   if (rc == ACAI_ERR_UNSUPPORTED) set_error("acai_wgrad_accumulate: operands are not TMA-addressable (16-byte aligned rows needed)");
   return rc;
 }
+
+// ------------------------------------------------------------------------------------------ scheduled sampling (models.py:798-838)
+namespace acai {
+
+// F.gumbel_softmax(logits, tau, hard) per row with the Gumbel noise supplied by the caller (so that a run can be replayed):
+//   y_soft = softmax((logits + g) / tau);  y = hard ? onehot(argmax y_soft) : y_soft   (first maximum wins, as torch.max)
+// y_soft is always written (the backward of both modes is that of y_soft: straight-through estimator).  One warp per row.
+__global__ void gumbel_softmax_fwd_kernel(const void* __restrict__ logits, int dt, int64_t ld, const float* __restrict__ noise,
+                                          int rows, int vocab, float inv_tau, int hard, float* __restrict__ y_soft,
+                                          void* __restrict__ y, int y_dt) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int64_t base = (int64_t)row * vocab;
+  float mx = -INFINITY; int arg = 0x7fffffff;
+  for (int c = lane; c < vocab; c += 32) {
+    const float v = (ld_as_float(logits, (int64_t)row * ld + c, dt) + noise[base + c]) * inv_tau;
+    if (v > mx) { mx = v; arg = c; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+  }
+  float s = 0.0f;
+  for (int c = lane; c < vocab; c += 32)
+    s += expf((ld_as_float(logits, (int64_t)row * ld + c, dt) + noise[base + c]) * inv_tau - mx);
+  s = warp_sum(s);
+  const float inv = 1.0f / s;
+  for (int c = lane; c < vocab; c += 32) {
+    const float p = expf((ld_as_float(logits, (int64_t)row * ld + c, dt) + noise[base + c]) * inv_tau - mx) * inv;
+    y_soft[base + c] = p;
+    st_from_float(y, base + c, y_dt, hard ? (c == arg ? 1.0f : 0.0f) : p);
+  }
+}
+
+// dlogits = (1 / tau) * y_soft * (dy - sum_c y_soft * dy)
+__global__ void gumbel_softmax_bwd_kernel(const void* __restrict__ dy, int dy_dt, const float* __restrict__ y_soft, int rows,
+                                          int vocab, float inv_tau, void* __restrict__ dlogits, int dl_dt) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int64_t base = (int64_t)row * vocab;
+  float dot = 0.0f;
+  for (int c = lane; c < vocab; c += 32) dot += y_soft[base + c] * ld_as_float(dy, base + c, dy_dt);
+  dot = warp_sum(dot);
+  for (int c = lane; c < vocab; c += 32)
+    st_from_float(dlogits, base + c, dl_dt, inv_tau * y_soft[base + c] * (ld_as_float(dy, base + c, dy_dt) - dot));
+}
+
+// out[r, :] = (sel && sel[r] >= 0 ? a[sel[r], :] : b[r, :]) + (pos ? pos[r % period, :] : 0)
+// (mixing expected and gold embeddings; adding the position table to embedding-space decoder inputs)
+__global__ void mix_rows_kernel(const void* __restrict__ a, int a_dt, const int64_t* __restrict__ sel, const void* __restrict__ b,
+                                int b_dt, const float* __restrict__ pos, int period, int dim, void* __restrict__ out, int out_dt) {
+  const int r = blockIdx.x;
+  const int64_t s = sel ? sel[r] : -1;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) {
+    float v = s >= 0 ? ld_as_float(a, s * dim + c, a_dt) : ld_as_float(b, (int64_t)r * dim + c, b_dt);
+    if (pos) v += pos[(int64_t)(r % period) * dim + c];
+    st_from_float(out, (int64_t)r * dim + c, out_dt, v);
+  }
+}
+
+}  // namespace acai
+
+extern "C" int acai_gumbel_softmax_fwd(const void* logits, int32_t dtype, int64_t ld, const float* noise, int32_t rows,
+                                       int32_t vocab, float tau, int32_t hard, float* y_soft, void* y, int32_t y_dtype,
+                                       void* stream) {
+  ACAI_CHECK_ARG(logits && noise && y_soft && y && rows > 0 && vocab > 0 && tau > 0.0f && dtype_valid(dtype) && dtype_valid(y_dtype),
+                 "acai_gumbel_softmax_fwd: bad argument");
+  acai::gumbel_softmax_fwd_kernel<<<(rows + 3) / 4, 128, 0, (cudaStream_t)stream>>>(logits, dtype, ld, noise, rows, vocab,
+                                                                                  1.0f / tau, hard, y_soft, y, y_dtype);
+  return launch_status("gumbel_softmax_fwd");
+}
+
+extern "C" int acai_gumbel_softmax_bwd(const void* dy, int32_t dy_dtype, const float* y_soft, int32_t rows, int32_t vocab,
+                                       float tau, void* dlogits, int32_t dlogits_dtype, void* stream) {
+  ACAI_CHECK_ARG(dy && y_soft && dlogits && rows > 0 && vocab > 0 && tau > 0.0f && dtype_valid(dy_dtype) && dtype_valid(dlogits_dtype),
+                 "acai_gumbel_softmax_bwd: bad argument");
+  acai::gumbel_softmax_bwd_kernel<<<(rows + 3) / 4, 128, 0, (cudaStream_t)stream>>>(dy, dy_dtype, y_soft, rows, vocab, 1.0f / tau,
+                                                                                  dlogits, dlogits_dtype);
+  return launch_status("gumbel_softmax_bwd");
+}
+
+extern "C" int acai_mix_rows(const void* a, int32_t a_dtype, const int64_t* sel, const void* b, int32_t b_dtype, const float* pos,
+                             int32_t period, int32_t rows, int32_t dim, void* out, int32_t out_dtype, void* stream) {
+  ACAI_CHECK_ARG(b && out && rows >= 0 && dim > 0 && dtype_valid(b_dtype) && dtype_valid(out_dtype) && (!sel || (a && dtype_valid(a_dtype))) &&
+                 (!pos || period > 0), "acai_mix_rows: bad argument");
+  if (rows == 0) return ACAI_OK;
+  acai::mix_rows_kernel<<<rows, dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(a, a_dtype, sel, b, b_dtype, pos, period, dim, out, out_dtype);
+  return launch_status("mix_rows");
+}

@@ -460,3 +460,133 @@ def mae_loss(pred, loss_mask, target, normaliser=None):
         sums, _ = ops.mae_loss(pred, loss_mask, target)
         return sums[0] / (sums[1] if normaliser is None else normaliser), sums
     return _MAELoss.apply(pred, loss_mask, target, normaliser)
+
+
+# ------------------------------------------------------------------------------------------ scheduled sampling (models.py:798-838)
+class _GumbelSoftmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, noise, tau, hard):
+        y, y_soft = ops.gumbel_softmax(logits, noise, tau, hard)
+        ctx.save_for_backward(y_soft)
+        ctx.meta = (tau, logits.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y_soft,) = ctx.saved_tensors
+        tau, dt = ctx.meta
+        return ops.gumbel_softmax_bwd(dy, y_soft, tau, dt), None, None, None
+
+
+def gumbel_softmax(logits, noise, tau, hard):
+    """F.gumbel_softmax with the Gumbel noise supplied (straight-through gradient when `hard`)."""
+    if not needs_grad(logits):
+        return ops.gumbel_softmax(logits, noise, tau, hard)[0]
+    return _GumbelSoftmax.apply(logits, noise, tau, hard)
+
+
+class _ExpectedEmbedding(torch.autograd.Function):
+    """probs[rows, V] @ table[V, D]  (models.py:811).  d probs = dout table^T,  d table += probs^T dout (wgrad GEMM)."""
+
+    @staticmethod
+    def forward(ctx, probs, table):
+        dt = probs.dtype
+        V = probs.shape[-1]
+        p2 = probs.reshape(-1, V)
+        out = ops.linear(p2, _weights().get_t(table, dt), out_dtype=dt)          # weight [D, V] = table^T
+        ctx.save_for_backward(p2, table)
+        ctx.shape = probs.shape
+        return out.view(*probs.shape[:-1], table.shape[1])
+
+    @staticmethod
+    def backward(ctx, dout):
+        p2, table = ctx.saved_tensors
+        dt = p2.dtype
+        d2 = dout.reshape(-1, table.shape[1])
+        d2 = (d2 if d2.dtype == dt else d2.to(dt)).contiguous()
+        dprobs = dtab = None
+        if ctx.needs_input_grad[0]:
+            dprobs = ops.linear(d2, _weights().get(table, dt), out_dtype=dt).view(ctx.shape)     # [rows, D] x [V, D]^T
+        if ctx.needs_input_grad[1]:
+            g = _owned_grad(table)
+            if g is not None:
+                ops.wgrad_accumulate(p2, d2, g)
+            else:
+                dtab = ops.wgrad_accumulate(p2, d2, torch.zeros(table.shape, dtype=torch.float32, device=d2.device))
+        return dprobs, dtab
+
+
+def expected_embedding(probs, table):
+    if not needs_grad(probs, table):
+        return ops.linear(probs, _weights().get_t(table, probs.dtype), out_dtype=probs.dtype)
+    return _ExpectedEmbedding.apply(probs, table)
+
+
+class _MixRows(torch.autograd.Function):
+    """out[r] = (sel[r] >= 0 ? a[sel[r]] : b[r]) + pos[r % period]; every row of `a` is selected at most once."""
+
+    @staticmethod
+    def forward(ctx, b, a, sel, pos, period):
+        out = ops.mix_rows(b, a, sel, pos.detach() if pos is not None else None, period)
+        ctx.save_for_backward(sel)
+        ctx.meta = (b.shape, b.dtype, a.shape if a is not None else None, a.dtype if a is not None else None,
+                    pos.shape if pos is not None else None, period)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (sel,) = ctx.saved_tensors
+        bshape, bdt, ashape, adt, pshape, period = ctx.meta
+        dim = bshape[-1]
+        d2 = dout.reshape(-1, dim).contiguous()
+        rows = d2.shape[0]
+        db = da = dpos = None
+        ar = torch.arange(rows, device=d2.device)
+        if ctx.needs_input_grad[0]:
+            db = (d2 if sel is None else ops.gather_rows(d2, torch.where(sel.reshape(-1) < 0, ar, torch.full_like(ar, -1)))).view(bshape)
+            if db.dtype != bdt:
+                db = db.to(bdt)
+        if ashape is not None and ctx.needs_input_grad[1]:
+            n_a = 1
+            for v in ashape[:-1]:
+                n_a *= v
+            inv = torch.full((n_a + 1,), -1, dtype=torch.int64, device=d2.device)
+            s = sel.reshape(-1)
+            inv[torch.where(s >= 0, s, torch.full_like(s, n_a))] = ar
+            da = ops.gather_rows(d2, inv[:-1], out_dtype=adt).view(ashape)
+        if pshape is not None and ctx.needs_input_grad[3]:
+            dpos = torch.zeros(pshape, dtype=torch.float32, device=d2.device)
+            ops.colsum(d2.view(rows // period, period * dim), out=dpos.view(-1)[: period * dim])
+        return db, da, None, dpos, None
+
+
+def mix_rows(b, a=None, sel=None, pos=None, period=0):
+    if not needs_grad(b, a, pos):
+        return ops.mix_rows(b, a, sel, pos, period)
+    return _MixRows.apply(b, a, sel, pos, period)
+
+
+class _EmbedRows(torch.autograd.Function):
+    """table[ids] without positions (nn.Embedding with padding_idx: that row receives no gradient)."""
+
+    @staticmethod
+    def forward(ctx, ids, table, out_dtype, padding_idx):
+        ctx.save_for_backward(ids)
+        ctx.meta = (table.shape, padding_idx)
+        return ops.gather_rows(table.detach(), ids, out_dtype=out_dtype).view(*ids.shape, table.shape[1])
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        tshape, padding_idx = ctx.meta
+        idx = ids.reshape(-1).long()
+        if padding_idx is not None:
+            idx = torch.where(idx == padding_idx, torch.full_like(idx, -1), idx)
+        dtab = ops.scatter_add_rows(dout.reshape(-1, tshape[1]), idx, torch.zeros(tshape, dtype=torch.float32, device=dout.device))
+        return None, dtab, None, None
+
+
+def embed_rows(ids, table, out_dtype, padding_idx=None):
+    if not needs_grad(table):
+        return ops.gather_rows(table, ids, out_dtype=out_dtype).view(*ids.shape, table.shape[1])
+    return _EmbedRows.apply(ids, table, out_dtype, padding_idx)

@@ -393,8 +393,10 @@ class OMRDecoder(nn.Module):
             x = F.embed_tokens(input_seqs, self.vocab_embedding.weight, self.pos_embedding, dt,
                                padding_idx=self.vocab_embedding.padding_idx)  # (B,T,D)
             x = F.pack_padded(x, tp.cu, tp.total)
-        else:
-            raise NotImplementedError("embedding-space inputs (scheduled sampling, models.py:833) are not implemented yet")
+        else:   # embedding-space inputs (scheduled sampling, models.py:463-470): add the position table, then pack
+            x = input_seqs if input_seqs.dtype == dt else input_seqs.to(dt)
+            x = F.mix_rows(x, pos=self.pos_embedding, period=T)
+            x = F.pack_padded(x, tp.cu, tp.total)
         mem, mp = self._memory_packed(img_latent, latent_attention_mask, dt)
         h = self.decoder_blocks.forward_packed(x, tp, mem, mp, causal=True)
         logits = F.linear(h, self.unembed.weight, self.unembed.bias, out_dtype=dt)
@@ -598,6 +600,53 @@ class TeacherForcedViTOMR(ViTOMR):
         param_groups.append({"params": (p for p in [self.encoder.pos_embedding]), "lr": min_layer_lr})
         param_groups.append({"params": self.encoder.projection.parameters(), "lr": min_layer_lr})
         return param_groups, layer_lrs
+
+
+class ScheduledSamplingViTOMR(TeacherForcedViTOMR):
+    """models.py:798-838: a second decoder pass on inputs mixed from gold embeddings and the first pass' expected
+    embeddings (Gumbel-softmax of its logits, right-shifted)."""
+
+    def sample_and_mix_seqs(self, teacher_forcing_prob, tf_input_seqs, tf_pred_logits, sample_tau, use_hard_sampling, device,
+                            sample_rand=None, gumbel_noise=None):
+        """models.py:801-817.  `sample_rand` (B,T) replaces the torch.rand draw and `gumbel_noise` (B,T,V) the Gumbel(0,1)
+        draw of F.gumbel_softmax (parity tests inject the reference's draws)."""
+        B, T = tf_input_seqs.shape
+        dec = self.decoder
+        sampling_ratio = 1 - teacher_forcing_prob
+        if sample_rand is None:
+            sample_rand = torch.rand((B, T), device=device)
+        sample_mask = sample_rand.to(device) < sampling_ratio
+        if gumbel_noise is None:
+            gumbel_noise = -torch.empty(tf_pred_logits.shape, dtype=torch.float32, device=device).exponential_().log()
+        dt = tf_pred_logits.dtype
+        ids = tf_input_seqs.to(device)
+        gold = F.embed_rows(ids, dec.vocab_embedding.weight, dt, padding_idx=dec.vocab_embedding.padding_idx)   # (B,T,E)
+        distrs = F.gumbel_softmax(tf_pred_logits, gumbel_noise.to(device), sample_tau, use_hard_sampling)        # (B,T,V)
+        expected = F.expected_embedding(distrs, dec.vocab_embedding.weight)                                       # (B,T,E)
+        # position t takes the expectation predicted at t-1 (right shift); position 0 always keeps the gold <bos> row
+        t = torch.arange(T, device=device)
+        row = torch.arange(B * T, device=device).view(B, T)
+        sel = torch.where(sample_mask & (t > 0)[None, :], row - 1, torch.full_like(row, -1))
+        return F.mix_rows(gold, a=expected, sel=sel)
+
+    def forward_train(self, x, teacher_forcing_prob, sample_tau, use_hard_sampling, sample_rand=None, gumbel_noise=None):
+        """models.py:819-834 -> (pred (B,T,V), target_seqs (B,T))."""
+        imgs, lmx_seqs = zip(*x)
+        img_latent, latent_attention_mask = self.encoder(imgs)
+        img_latent = self.transition_head(img_latent)
+        device = img_latent.device
+        tf_input_seqs, target_seqs, lmx_attention_mask = batchify_and_split_lmx_seqs(lmx_seqs, self.decoder.pad_idx, device)
+        T = tf_input_seqs.shape[1]
+        lmx_attention_mask._acai_lens = [min(int(s.shape[0]), T) for s in lmx_seqs]
+        tf_pred_logits = self.decoder(tf_input_seqs, img_latent, lmx_attention_mask, latent_attention_mask)
+        mixed = self.sample_and_mix_seqs(teacher_forcing_prob, tf_input_seqs, tf_pred_logits, sample_tau, use_hard_sampling,
+                                         device, sample_rand, gumbel_noise)
+        pred = self.decoder(mixed, img_latent, lmx_attention_mask, latent_attention_mask, token_idxs_input=False)
+        return pred, target_seqs
+
+    def forward_eval(self, x):
+        """models.py:836-838."""
+        return super().forward(x)
 
 
 class OMRCELoss(nn.Module):

@@ -570,3 +570,42 @@ def mae_loss_bwd(pred, loss_mask, target, scale, dpred_dtype=None):
     _call("acai_mae_loss_bwd", _lib.load().acai_mae_loss_bwd, _p(p2), _dt(p2), _p(t2), _p(m2), p2.shape[0], feats, _p(scale),
           _p(dp), _dt(dp), _stream())
     return dp.view(pred.shape)
+
+
+# ------------------------------------------------------------------------------------------ scheduled sampling
+def gumbel_softmax(logits, noise, tau, hard, out_dtype=None):
+    """-> (y, y_soft fp32) over the last dim; `noise` is the Gumbel(0,1) draw of the same shape (acai_gumbel_softmax_fwd)."""
+    _cuda(logits, noise)
+    V = logits.shape[-1]
+    l2 = logits.reshape(-1, V)
+    if l2.stride(1) != 1:
+        l2 = l2.contiguous()
+    n2 = noise.reshape(-1, V).float().contiguous()
+    y_soft = torch.empty(l2.shape, dtype=torch.float32, device=logits.device)
+    y = torch.empty(l2.shape, dtype=out_dtype or logits.dtype, device=logits.device)
+    _call("acai_gumbel_softmax_fwd", _lib.load().acai_gumbel_softmax_fwd, _p(l2), _dt(l2), l2.stride(0), _p(n2), l2.shape[0], V,
+          float(tau), 1 if hard else 0, _p(y_soft), _p(y), _dt(y), _stream())
+    return y.view(logits.shape), y_soft.view(logits.shape)
+
+
+def gumbel_softmax_bwd(dy, y_soft, tau, out_dtype):
+    _cuda(dy, y_soft)
+    V = y_soft.shape[-1]
+    d2 = dy.reshape(-1, V).contiguous()
+    dl = torch.empty(d2.shape, dtype=out_dtype, device=dy.device)
+    _call("acai_gumbel_softmax_bwd", _lib.load().acai_gumbel_softmax_bwd, _p(d2), _dt(d2), _p(y_soft), d2.shape[0], V, float(tau),
+          _p(dl), _dt(dl), _stream())
+    return dl.view(y_soft.shape)
+
+
+def mix_rows(b, a=None, sel=None, pos=None, period=0, out_dtype=None):
+    """out[r] = (sel[r] >= 0 ? a[sel[r]] : b[r]) + pos[r % period] over rows of the last dim (acai_mix_rows)."""
+    _cuda(a, sel, b, pos)
+    dim = b.shape[-1]
+    b2 = b.reshape(-1, dim).contiguous()
+    a2 = a.reshape(-1, dim).contiguous() if a is not None else None
+    s = sel.reshape(-1).to(torch.int64).contiguous() if sel is not None else None
+    out = torch.empty(b2.shape, dtype=out_dtype or b.dtype, device=b.device)
+    _call("acai_mix_rows", _lib.load().acai_mix_rows, _p(a2), _dt(a2) if a2 is not None else 0, _p(s), _p(b2), _dt(b2),
+          _p(_f32c(pos)), int(period), b2.shape[0], dim, _p(out), _dt(out), _stream())
+    return out.view(b.shape)

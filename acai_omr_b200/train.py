@@ -26,10 +26,23 @@ from . import functional as F
 ALIGN = 64  # elements: every parameter starts on a 256 B (fp32) / 128 B (bf16) boundary, as TMA wants
 
 
-def shard(items, rank, world):
-    """Stride sharding of a ragged batch: consecutive systems cycle through aspect ratios / lengths, so every rank
-    gets a similar sum of sequence lengths."""
-    return list(items)[rank::world]
+def shard(items, rank, world, cost=None):
+    """This rank's share of a ragged batch.  Without `cost`: stride sharding (consecutive systems cycle through aspect
+    ratios / lengths).  With `cost(item) -> number` (e.g. patch tokens + target tokens): greedy bin packing - items in
+    decreasing cost, each to the rank with the smallest running sum (ties to the lowest rank) - so that the per-rank
+    sums of sequence lengths are balanced.  Deterministic: every rank computes the same assignment."""
+    items = list(items)
+    if cost is None or world == 1:
+        return items[rank::world]
+    costs = [cost(it) for it in items]
+    order = sorted(range(len(items)), key=lambda i: (-costs[i], i))
+    load, mine = [0] * world, []
+    for i in order:
+        r = min(range(world), key=lambda k: (load[k], k))
+        load[r] += costs[i]
+        if r == rank:
+            mine.append(i)
+    return [items[i] for i in sorted(mine)]
 
 
 def _world(group):
@@ -142,6 +155,21 @@ def teacher_forced_step(vit, batch, trainer: FlatTrainer, autocast=True):
     trainer.zero_grad()
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
         pred, tgt = vit(batch)
+        tgt = tgt.to(pred.device)
+        norm = trainer.mean_count((tgt != vit.decoder.pad_idx).sum())
+        loss, sums = F.ce_loss(pred, tgt, vit.decoder.pad_idx, normaliser=norm)
+    loss.backward()
+    trainer.allreduce_gradients()
+    trainer.step()
+    return sums
+
+
+def scheduled_sampling_step(vit, batch, trainer: FlatTrainer, teacher_forcing_prob, sample_tau, use_hard_sampling, autocast=True):
+    """One data-parallel step of the reference's actual recipe (omr_teacher_force_train.py:113-127 with
+    ScheduledSamplingViTOMR.forward_train): two decoder passes, the second on Gumbel-softmax-mixed embeddings."""
+    trainer.zero_grad()
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+        pred, tgt = vit.forward_train(batch, teacher_forcing_prob, sample_tau, use_hard_sampling)
         tgt = tgt.to(pred.device)
         norm = trainer.mean_count((tgt != vit.decoder.pad_idx).sum())
         loss, sums = F.ce_loss(pred, tgt, vit.decoder.pad_idx, normaliser=norm)

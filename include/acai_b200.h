@@ -252,6 +252,19 @@ int acai_gather_rows(const void* src, int32_t dtype, const int64_t* index, int32
 int acai_mae_loss_bwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask, int32_t rows,
                       int32_t feats, const float* scale, void* dpred, int32_t dpred_dtype, void* stream);
 
+/* Scheduled sampling (ScheduledSamplingViTOMR.sample_and_mix_seqs, models.py:801-817).
+ *   acai_gumbel_softmax_fwd : F.gumbel_softmax(logits, tau, hard) with caller-supplied Gumbel noise [rows, vocab] fp32;
+ *                             writes y_soft (fp32, kept for the backward) and y (one-hot of the first maximum when hard)
+ *   acai_gumbel_softmax_bwd : dlogits = (1/tau) y_soft (dy - <y_soft, dy>)   (straight-through for hard)
+ *   acai_mix_rows           : out[r] = (sel && sel[r] >= 0 ? a[sel[r]] : b[r]) + (pos ? pos[r % period] : 0) - the
+ *                             torch.where / cat / right-shift of :809-816 and the position add of OMRDecoder.forward :469-470 */
+int acai_gumbel_softmax_fwd(const void* logits, int32_t dtype, int64_t ld, const float* noise, int32_t rows, int32_t vocab,
+                            float tau, int32_t hard, float* y_soft, void* y, int32_t y_dtype, void* stream);
+int acai_gumbel_softmax_bwd(const void* dy, int32_t dy_dtype, const float* y_soft, int32_t rows, int32_t vocab, float tau,
+                            void* dlogits, int32_t dlogits_dtype, void* stream);
+int acai_mix_rows(const void* a, int32_t a_dtype, const int64_t* sel, const void* b, int32_t b_dtype, const float* pos,
+                  int32_t period, int32_t rows, int32_t dim, void* out, int32_t out_dtype, void* stream);
+
 /* Weight gradient of a linear layer, accumulated in place:  dw[n_out, k_in] += dz[tokens, n_out]^T . x[tokens, k_in]
  * (bf16 operands exactly as the forward/backward left them - no transposed copies; fp32 dw, typically the parameter's
  * slice of the flat gradient buffer).  tcgen05 GEMM with both operands MN-major, split over token ranges, partial

@@ -422,3 +422,44 @@ def mae_loss(pred, loss_mask, target):
     tn = (target - mean) / (var + 1.0e-6) ** 0.5
     loss = ((pred - tn) ** 2).mean(dim=-1)
     return (loss * loss_mask).sum() / loss_mask.sum()
+
+
+# --------------------------------------------------------------------------- #
+# scheduled sampling  (models.py:798-838)
+# --------------------------------------------------------------------------- #
+def gumbel_softmax(logits, gumbel, tau, hard):
+    """F.gumbel_softmax with the Gumbel(0,1) draw supplied: softmax((logits + g) / tau); hard = straight-through one-hot."""
+    y_soft = torch.softmax((logits.float() + gumbel) / tau, dim=-1)
+    if not hard:
+        return y_soft
+    index = y_soft.max(dim=-1, keepdim=True)[1]
+    y_hard = torch.zeros_like(y_soft).scatter_(-1, index, 1.0)
+    return y_hard - y_soft.detach() + y_soft
+
+
+def decoder_forward_embeddings(emb, memory, sd, H, lmx_pad_mask=None, mem_pad_mask=None):
+    """OMRDecoder.forward(token_idxs_input=False) (models.py:463-483): embedding-space inputs + PE[:T]."""
+    T = emb.shape[1]
+    x = emb + sd["pos_embedding"][:T].unsqueeze(0)
+    x = decoder_stack(x, memory, sd, H, True, lmx_pad_mask, mem_pad_mask)
+    return linear(x, sd["unembed.weight"], sd["unembed.bias"])
+
+
+def scheduled_sampling_forward(batch, sd, cfg, tf_prob, tau, hard, rand, gumbel):
+    """ScheduledSamplingViTOMR.forward_train (models.py:819-834) with its two random draws supplied:
+    `rand` (B,T) for the sampling mask (:803) and `gumbel` (B,T,V) for F.gumbel_softmax (:808)."""
+    imgs, seqs = zip(*batch)
+    enc_sd = {k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")}
+    dec_sd = {k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}
+    lat, lat_mask = encoder_forward(list(imgs), enc_sd, cfg["encoder"], fast_path_pad_fill=False)
+    lat = transition_head(lat, sd)
+    inp, tgt, lmx_mask = batchify_and_split_lmx_seqs(list(seqs), cfg["pad_idx"])
+    logits = decoder_forward(inp, lat, dec_sd, cfg["decoder_heads"], lmx_mask, lat_mask)
+    table = dec_sd["vocab_embedding.weight"]
+    sample_mask = rand < (1 - tf_prob)
+    gold = table[inp]                                                   # padding_idx row is zero in a reference state_dict
+    expected = gumbel_softmax(logits, gumbel, tau, hard) @ table
+    expected = torch.cat([gold[:, 0:1], expected], dim=1)[:, :-1]       # right shift (:813-815)
+    mixed = torch.where(sample_mask.unsqueeze(-1), expected, gold)
+    pred = decoder_forward_embeddings(mixed, lat, dec_sd, cfg["decoder_heads"], lmx_mask, lat_mask)
+    return pred, tgt

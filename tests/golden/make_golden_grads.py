@@ -68,6 +68,41 @@ assert torch.equal(lmask, g["loss_mask"])
 loss = R.MAELoss()(pred, lmask, target)
 loss.backward()
 OUT["mae"] = dict(loss=loss.detach().clone(), grads=grads_of(mae))
+# ---- scheduled-sampling step (ScheduledSamplingViTOMR.forward_train, models.py:819-834) -----------------------
+g = G["vitomr"]
+c = g["cfg"]
+
+
+def build_ss():
+    enc = R.FineTuneOMREncoder(c["enc"]["patch_size"], c["enc"]["pe_max_height"], c["enc"]["pe_max_width"], c["enc"]["fine_tune_depth"],
+                               num_layers=c["enc"]["num_layers"], hidden_dim=c["enc"]["hidden_dim"], num_heads=c["enc"]["num_heads"],
+                               mlp_dim=c["enc"]["mlp_dim"], transformer_dropout=0.0)
+    dec = R.OMRDecoder(c["dec"]["max_lmx_seq_len"], "lmx_vocab.txt", num_layers=c["dec"]["num_layers"], hidden_dim=c["dec"]["hidden_dim"],
+                       num_heads=c["dec"]["num_heads"], mlp_dim=c["dec"]["mlp_dim"], transformer_dropout=0.0)
+    m = R.ScheduledSamplingViTOMR(enc, None, dec, transition_head_dim=c["transition_head_dim"], transition_head_dropout=0.0)
+    m.load_state_dict(g["sd"])
+    for p in m.parameters():
+        p.requires_grad_(True)
+    return m.train()
+
+
+OUT["scheduled_sampling"] = {}
+for hard in (False, True):
+    ss = build_ss()
+    B, T, V = len(g["lmx"]), max(int(s.shape[0]) for s in g["lmx"]) - 1, ss.decoder.vocab_size
+    torch.manual_seed(77)
+    # the two draws forward_train makes, in its order: torch.rand((B,T)) then empty_like(logits).exponential_() (F.gumbel_softmax)
+    rand = torch.rand((B, T))
+    gumbel = -torch.empty((B, T, V)).exponential_().log()
+    torch.manual_seed(77)
+    pred, tgt = ss.forward_train(list(zip(g["imgs"], g["lmx"])), 0.5, 1.5, hard)
+    loss = R.OMRCELoss(ss.decoder.pad_idx)(pred, tgt)
+    loss.backward()
+    OUT["scheduled_sampling"]["hard" if hard else "soft"] = dict(
+        tf_prob=0.5, tau=1.5, rand=rand, gumbel=gumbel, pred=pred.detach().clone(), target=tgt.clone(),
+        loss=loss.detach().clone(), grads=grads_of(ss))
+    print("scheduled sampling", "hard" if hard else "soft", "loss", float(loss), "sampled positions", int((rand < 0.5).sum()))
+
 OUT["meta"] = dict(torch=str(torch.__version__), reference="jsnchon/acai-omr@5819ae3")
 
 path = os.path.join(HERE, "golden_grads.pt")

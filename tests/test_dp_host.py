@@ -71,6 +71,17 @@ def test_shard_partitions_the_batch():
         assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
 
 
+def test_cost_balanced_sharding():
+    lens = [1024, 968, 972, 1000, 1015, 1008, 980, 1024, 120, 64, 500, 333, 90, 800, 640, 77]
+    for world in (2, 4, 8):
+        parts = [train.shard(lens, r, world, cost=lambda v: v) for r in range(world)]
+        assert sorted(sum(parts, [])) == sorted(lens)
+        sums = [sum(p) for p in parts]
+        assert max(sums) - min(sums) <= max(lens) // 2, sums          # greedy packing keeps the token sums close
+        naive = [sum(lens[r::world]) for r in range(world)]
+        assert max(sums) - min(sums) <= max(naive) - min(naive)
+
+
 def test_global_normaliser_gives_single_process_gradient():
     """sum_r (local_sum_r / (G / W)) / W == global_sum / G: the identity behind FlatTrainer.mean_count."""
     sums, counts = [3.0, 11.0, 0.5], [4.0, 9.0, 1.0]

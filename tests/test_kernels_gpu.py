@@ -318,3 +318,24 @@ def test_decode_attn_paged_self_and_cross(dtype):
         ref = (torch.softmax(s, -1) @ v.double()).reshape(D).float()
         close(out[b], ref, *tol)
         o += L
+
+
+@pytest.mark.parametrize("M", [1, 2, 5, 8, 13, 16, 32, 33])
+@pytest.mark.parametrize("N,K", [(1024, 1024), (227, 1024), (4096, 1024), (1024, 4096), (40, 72)])
+def test_linear_bf16_decode_step_shapes(M, N, K):
+    """M <= 32 takes the weight-streaming GEMV (one warp per output column), M = 33 the tensor-core tile: same results."""
+    x, w = rnd(M, K, seed=71).bfloat16(), rnd(N, K, seed=72, scale=0.05).bfloat16()
+    b, r = rnd(N, seed=73), rnd(M, N, seed=74).bfloat16()
+    for act in (ops.ACT_NONE, ops.ACT_GELU):
+        res = None if act else r
+        y = ops.linear(x, w, b, act=act, residual=res, out_dtype=torch.bfloat16)
+        ref = x.double() @ w.double().t() + b.double()
+        if act:
+            ref = torch.nn.functional.gelu(ref)
+        else:
+            ref = ref + r.double()
+        close(y, ref.float(), 1e-2, 2e-2)
+    # strided activation rows (a column slice of a fused QKV buffer)
+    big = rnd(M, 3 * K, seed=75).bfloat16()
+    y = ops.linear(big[:, K:2 * K], w, b, out_dtype=torch.float32)
+    close(y, (big[:, K:2 * K].double() @ w.double().t() + b.double()).float(), 1e-3, 2e-3)

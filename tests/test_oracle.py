@@ -159,3 +159,23 @@ def test_mae_gradients_match_reference(golden, golden_grads):
     assert torch.allclose(loss.detach(), gg["loss"], **TOL)
     loss.backward()
     _check_grads(sd, gg["grads"], dict(atol=2e-5, rtol=1e-3))
+
+
+def test_scheduled_sampling_forward_and_gradients_match_reference(golden, golden_grads):
+    """ScheduledSamplingViTOMR.forward_train + OMRCELoss + backward, soft and hard (straight-through) sampling, with the
+    reference's own random draws replayed (tests/golden/make_golden_grads.py)."""
+    g = golden["vitomr"]
+    enc_cfg = dict(patch_size=4, pe_max_height=6, pe_max_width=10, num_heads=4, interpolate=True, stacks=["fine_tune_blocks"])
+    cfg = dict(encoder=enc_cfg, decoder_heads=4, pad_idx=1)
+    for mode in ("soft", "hard"):
+        gg = golden_grads["scheduled_sampling"][mode]
+        sd = _leaf_sd(g["sd"])
+        pred, tgt = O.scheduled_sampling_forward(list(zip(g["imgs"], g["lmx"])), sd, cfg, gg["tf_prob"], gg["tau"], mode == "hard",
+                                                 gg["rand"], gg["gumbel"])
+        assert torch.equal(tgt, gg["target"])
+        valid = tgt != 1
+        assert torch.allclose(pred[valid], gg["pred"][valid], **TOL)
+        loss = O.ce_loss(pred, tgt, 1)
+        assert torch.allclose(loss.detach(), gg["loss"], **TOL)
+        loss.backward()
+        _check_grads(sd, gg["grads"], dict(atol=2e-5, rtol=1e-3))

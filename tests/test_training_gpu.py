@@ -414,3 +414,76 @@ def test_wgrad_accumulate_tensor_core(T, n_out, k_in):
         ops.wgrad_accumulate(big[:, n_out:2 * n_out], x, dwf[n_out:2 * n_out])
         assert rel_err(dwf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().t() @ x.double()) < 1e-5
         assert not bool(dwf[:n_out].any()) and not bool(dwf[2 * n_out:].any())
+
+
+@pytest.mark.parametrize("hard", [False, True])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1.5e-2)])
+def test_gumbel_softmax_fwd_bwd(hard, dtype, tol):
+    logits = rnd(3, 11, 227, seed=80, dtype=dtype, scale=2.0).requires_grad_(True)
+    noise = -torch.empty(3, 11, 227, device=DEV).exponential_(generator=torch.Generator(device=DEV).manual_seed(81)).log()
+    dy = rnd(3, 11, 227, seed=82, dtype=dtype)
+    y = F.gumbel_softmax(logits, noise, 1.5, hard)
+    y.backward(dy)
+    lr = logits.detach().float().requires_grad_(True)
+    ref = O.gumbel_softmax(lr, noise, 1.5, hard)
+    ref.backward(dy.float())
+    assert rel_err(y, ref) < tol
+    assert rel_err(logits.grad, lr.grad) < tol
+    if hard:
+        assert torch.equal(y.detach().float().sum(-1), torch.ones(3, 11, device=DEV)) and bool(((y == 0) | (y == 1)).all())
+
+
+def test_mix_rows_and_expected_embedding_backward():
+    B, T, D, V = 3, 7, 48, 227
+    gold = rnd(B, T, D, seed=83).requires_grad_(True)
+    exp = rnd(B, T, D, seed=84).requires_grad_(True)
+    pos = rnd(20, D, seed=85).requires_grad_(True)
+    mask = torch.rand(B, T, device=DEV, generator=torch.Generator(device=DEV).manual_seed(86)) < 0.5
+    row = torch.arange(B * T, device=DEV).view(B, T)
+    sel = torch.where(mask & (torch.arange(T, device=DEV) > 0)[None, :], row - 1, torch.full_like(row, -1))
+    out = F.mix_rows(F.mix_rows(gold, a=exp, sel=sel), pos=pos, period=T)
+    dy = rnd(B, T, D, seed=87)
+    out.backward(dy)
+    g2, e2, p2 = (t.detach().clone().requires_grad_(True) for t in (gold, exp, pos))
+    shifted = torch.cat([g2[:, :1], e2], dim=1)[:, :-1]
+    ref = torch.where(mask.unsqueeze(-1), shifted, g2) + p2[:T].unsqueeze(0)
+    ref.backward(dy)
+    assert torch.allclose(out, ref, atol=1e-6)
+    for a, b in ((gold, g2), (exp, e2), (pos, p2)):
+        assert torch.allclose(a.grad, b.grad, atol=1e-5), float((a.grad - b.grad).abs().max())
+    # probs @ table and its two gradients
+    probs = torch.softmax(rnd(B * T, V, seed=88), -1).requires_grad_(True)
+    table = rnd(V, D, seed=89).requires_grad_(True)
+    out = F.expected_embedding(probs, table)
+    dy2 = rnd(B * T, D, seed=90)
+    out.backward(dy2)
+    pr, tr = probs.detach().clone().requires_grad_(True), table.detach().clone().requires_grad_(True)
+    (pr @ tr).backward(dy2)
+    assert rel_err(out, pr @ tr) < 1e-5 and rel_err(probs.grad, pr.grad) < 1e-5 and rel_err(table.grad, tr.grad) < 1e-5
+
+
+@pytest.mark.parametrize("mode", ["soft", "hard"])
+def test_scheduled_sampling_step_golden(golden, golden_grads, mode):
+    """ScheduledSamplingViTOMR.forward_train + OMRCELoss + backward in fp32 with the reference's random draws replayed:
+    predictions, loss and every parameter gradient vs the reference's."""
+    g, gg = golden["vitomr"], golden_grads["scheduled_sampling"][mode]
+    c = g["cfg"]
+    enc = M.FineTuneOMREncoder(4, 6, 10, 2, num_layers=2, hidden_dim=32, num_heads=4, mlp_dim=64, transformer_dropout=0.0)
+    dec = M.OMRDecoder(20, VOCAB, num_layers=2, hidden_dim=48, num_heads=4, mlp_dim=96, transformer_dropout=0.0)
+    vit = M.ScheduledSamplingViTOMR(enc, None, dec, transition_head_dim=c["transition_head_dim"], transition_head_dropout=0.0)
+    vit.load_state_dict(g["sd"])
+    for p in vit.parameters():
+        p.requires_grad_(True)
+    vit = vit.to(DEV).train()
+    pred, tgt = vit.forward_train(list(zip(cuda_list(g["imgs"]), cuda_list(g["lmx"]))), gg["tf_prob"], gg["tau"], mode == "hard",
+                                  sample_rand=gg["rand"], gumbel_noise=gg["gumbel"])
+    assert torch.equal(tgt.cpu(), gg["target"])
+    valid = gg["target"] != 1
+    assert torch.allclose(pred.detach().cpu()[valid], gg["pred"][valid], atol=3e-5, rtol=1e-3)
+    loss = M.OMRCELoss(vit.decoder.pad_idx)(pred, tgt)
+    assert torch.allclose(loss.detach().cpu(), gg["loss"], atol=2e-5, rtol=1e-4)
+    loss.backward()
+    check_param_grads(vit, gg["grads"], atol=3e-5, rtol=2e-3)
+    with torch.no_grad():
+        p_eval, _ = vit.forward_eval(list(zip(cuda_list(g["imgs"]), cuda_list(g["lmx"]))))
+    assert p_eval.shape == pred.shape

@@ -77,9 +77,8 @@ def test_cost_balanced_sharding():
         parts = [train.shard(lens, r, world, cost=lambda v: v) for r in range(world)]
         assert sorted(sum(parts, [])) == sorted(lens)
         sums = [sum(p) for p in parts]
-        assert max(sums) - min(sums) <= max(lens) // 2, sums          # greedy packing keeps the token sums close
         naive = [sum(lens[r::world]) for r in range(world)]
-        assert max(sums) - min(sums) <= max(naive) - min(naive)
+        assert max(sums) - min(sums) <= max(naive) - min(naive) and max(sums) <= max(naive), (sums, naive)
 
 
 def test_global_normaliser_gives_single_process_gradient():

@@ -27,7 +27,7 @@ class ImageDesc(C.Structure):
                 ("hp", C.c_int32), ("wp", C.c_int32)]
 
 
-_p, _i32, _i64, _f32, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
+_p, _i32, _i64, _f32, _sz, _u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t, C.c_uint64
 
 # name -> argtypes, in header order
 SIGNATURES = {
@@ -39,9 +39,10 @@ SIGNATURES = {
     "acai_linear_fwd": [_p, _i32, _i64, _p, _i32, _i64, _p, _p, _i32, _i64, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p],
     "acai_layernorm_fwd": [_p, _i32, _p, _i32, _p, _p, _f32, _p, _i32, _p, _i32, _i32, _i32, _p],
     "acai_attn_varlen_fwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32,
-                             _i64, _p, _p],
+                             _i64, _p, _f32, _u64, _p],
+    "acai_attn_dropout_mask": [_f32, _u64, _i32, _i32, _i32, _p, _p],
     "acai_attn_varlen_bwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _p, _i64, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32,
-                             _i32, _i32, _f32, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _p],
+                             _i32, _i32, _f32, _p, _p, _p, _i32, _i64, _i64, _i64, _p, _f32, _u64, _p],
     "acai_transpose": [_p, _i32, _i64, _i32, _i32, _p, _i64, _p],
     "acai_colsum_workspace_bytes": [_i32, _i32],
     "acai_colsum": [_p, _i32, _i64, _i32, _i32, _p, _i32, _p, _sz, _p],
@@ -53,6 +54,8 @@ SIGNATURES = {
     "acai_scatter_add_rows": [_p, _i32, _i64, _p, _i32, _i32, _p, _f32, _p],
     "acai_gather_rows": [_p, _i32, _p, _i32, _i32, _p, _i32, _p],
     "acai_mae_loss_bwd": [_p, _i32, _p, _p, _i32, _i32, _p, _p, _i32, _p],
+    "acai_dropout": [_p, _i32, _p, _i32, _i64, _f32, _u64, _p, _i32, _p],
+    "acai_dropout_mask": [_i64, _f32, _u64, _p, _p],
     "acai_gumbel_softmax_fwd": [_p, _i32, _i64, _p, _i32, _i32, _f32, _i32, _p, _p, _i32, _p],
     "acai_gumbel_softmax_bwd": [_p, _i32, _p, _i32, _i32, _f32, _p, _i32, _p],
     "acai_mix_rows": [_p, _i32, _p, _p, _i32, _p, _i32, _i32, _i32, _p, _i32, _p],

@@ -19,6 +19,7 @@ struct AttnBwdArgs {
   const float* lse; const float* delta;
   const int32_t* cu_q; const int32_t* cu_k; int total_q; int heads; int d; int causal; float scale, scale_log2;
   void* dq; void* dk; void* dv; int gdt; int64_t dqs, dks, dvs;
+  AttnDropout drop;
 };
 
 // delta[h, row] = sum_e dO[row, h, e] * O[row, h, e]; one warp per (row, head)
@@ -85,7 +86,9 @@ attn_bwd_dq_kernel(AttnBwdArgs a) {
       const float s = pair_dot<DMAX>(q, &Ks[r][sub * HALF]);
       const float dp = pair_dot<DMAX>(g, &Vs[r][sub * HALF]);
       const float p = (t0 + r < my_end) ? fast_exp2(s * a.scale_log2 - lse) : 0.0f;
-      const float ds = p * (dp - delta) * a.scale;
+      float mk = 1.0f;
+      if (a.drop.thr) mk = attn_drop_keep(a.drop, (uint64_t)h * a.total_q + (uint64_t)(q0 + (valid ? row : 0)), t0 + r) ? a.drop.rp : 0.0f;
+      const float ds = p * (mk * dp - delta) * a.scale;
 #pragma unroll
       for (int e = 0; e < HALF; ++e) dq[e] = fmaf(ds, Ks[r][sub * HALF + e], dq[e]);
     }
@@ -144,10 +147,13 @@ attn_bwd_dkv_kernel(AttnBwdArgs a) {
       const float s = pair_dot<DMAX>(kk, &Qs[r][sub * HALF]);
       const float dp = pair_dot<DMAX>(vv, &Gs[r][sub * HALF]);
       const float p = (valid && t0 + r < lq && t0 + r >= my_first) ? fast_exp2(s * a.scale_log2 - Ls[r]) : 0.0f;
-      const float ds = p * (dp - Ds[r]) * a.scale;
+      float mk = 1.0f;
+      if (a.drop.thr) mk = attn_drop_keep(a.drop, (uint64_t)h * a.total_q + (uint64_t)(q0 + min(t0 + r, lq - 1)), valid ? key : 0) ? a.drop.rp : 0.0f;
+      const float ds = p * (mk * dp - Ds[r]) * a.scale;
+      const float pm = p * mk;
 #pragma unroll
       for (int e = 0; e < HALF; ++e) {
-        dv[e] = fmaf(p, Gs[r][sub * HALF + e], dv[e]);
+        dv[e] = fmaf(pm, Gs[r][sub * HALF + e], dv[e]);
         dk[e] = fmaf(ds, Qs[r][sub * HALF + e], dk[e]);
       }
     }
@@ -167,7 +173,8 @@ attn_bwd_dkv_kernel(AttnBwdArgs a) {
 int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs, const void* dout,
                 int64_t dos, const float* lse, const float* delta, const int32_t* cu_q, const int32_t* cu_k, int batch,
                 int max_q, int max_k, int64_t total_q, int64_t total_k, int heads, int head_dim, int causal, float scale,
-                void* dq, void* dk, void* dv, int grad_dtype, int64_t dqs, int64_t dks, int64_t dvs, cudaStream_t st);
+                void* dq, void* dk, void* dv, int grad_dtype, int64_t dqs, int64_t dks, int64_t dvs, AttnDropout drop,
+                cudaStream_t st);
 
 }  // namespace acai
 
@@ -179,24 +186,26 @@ extern "C" int acai_attn_varlen_bwd(const void* q, const void* k, const void* v,
                                     const int32_t* cu_seqlens_k, int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k,
                                     int32_t total_q, int32_t total_k, int32_t heads, int32_t head_dim, int32_t causal, float scale,
                                     void* dq, void* dk, void* dv, int32_t grad_dtype, int64_t dq_stride, int64_t dk_stride,
-                                    int64_t dv_stride, float* delta_ws, void* stream) {
+                                    int64_t dv_stride, float* delta_ws, float dropout_p, uint64_t dropout_seed, void* stream) {
   ACAI_CHECK_ARG(q && k && v && out && dout && lse && cu_seqlens_q && cu_seqlens_k && dq && dk && dv && delta_ws,
                  "acai_attn_varlen_bwd: null pointer");
   ACAI_CHECK_ARG(batch > 0 && heads > 0 && head_dim > 0 && total_q > 0 && batch <= 65535 && heads <= 65535,
                  "acai_attn_varlen_bwd: bad sizes");
   ACAI_CHECK_ARG(dtype_valid(dtype) && dtype_valid(grad_dtype), "acai_attn_varlen_bwd: bad dtype");
   if (head_dim > 128) { set_error("acai_attn_varlen_bwd: head_dim %d > 128 unsupported", head_dim); return ACAI_ERR_UNSUPPORTED; }
+  ACAI_CHECK_ARG(dropout_p >= 0.0f && dropout_p < 1.0f, "acai_attn_varlen_bwd: dropout_p out of range");
+  const AttnDropout drop{dropout_seed, dropout_threshold(dropout_p), 1.0f / (1.0f - dropout_p)};
   cudaStream_t st = (cudaStream_t)stream;
   AttnBwdArgs a{q, k, v, dtype, q_stride, k_stride, v_stride, out, o_stride, dout, do_stride, lse, delta_ws,
                 cu_seqlens_q, cu_seqlens_k, total_q, heads, head_dim, causal, scale, scale * 1.4426950408889634f,
-                dq, dk, dv, grad_dtype, dq_stride, dk_stride, dv_stride};
+                dq, dk, dv, grad_dtype, dq_stride, dk_stride, dv_stride, drop};
   const int64_t nw = (int64_t)total_q * heads;
   attn_delta_kernel<<<(unsigned)((nw + 7) / 8), 256, 0, st>>>(a);
   int rc = launch_status("attn_delta");
   if (rc) return rc;
   rc = acai::attn_bwd_tc(q, k, v, dtype, q_stride, k_stride, v_stride, dout, do_stride, lse, delta_ws, cu_seqlens_q, cu_seqlens_k,
                    batch, max_seqlen_q, max_seqlen_k, total_q, total_k, heads, head_dim, causal, scale, dq, dk, dv, grad_dtype,
-                   dq_stride, dk_stride, dv_stride, st);
+                   dq_stride, dk_stride, dv_stride, drop, st);
   if (rc != ACAI_ERR_UNSUPPORTED) return rc;
   dim3 gq((max_seqlen_q + BR - 1) / BR, heads, batch), gk((max_seqlen_k + BR - 1) / BR, heads, batch);
   if (head_dim <= 32) { attn_bwd_dq_kernel<32><<<gq, 2 * BR, 0, st>>>(a); attn_bwd_dkv_kernel<32><<<gk, 2 * BR, 0, st>>>(a); }

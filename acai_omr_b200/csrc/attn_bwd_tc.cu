@@ -30,8 +30,8 @@ constexpr uint32_t BIGTILE = BIG * D * 2;           // 16 KB
 constexpr uint32_t SMALLTILE = SMALL * D * 2;       // 8 KB
 constexpr uint32_t OFF_A0 = 0, OFF_A1 = BIGTILE;    // the two resident 128-row tiles (Q,dO or K,V)
 constexpr uint32_t OFF_B0 = 2 * BIGTILE, OFF_B1 = OFF_B0 + STAGES * SMALLTILE;   // streamed 64-row tiles (K,V or Q,dO)
-constexpr uint32_t OFF_VEC = OFF_B1 + STAGES * SMALLTILE;                         // 2 x (64 L + 64 delta) floats
-constexpr uint32_t OFF_BAR = OFF_VEC + 2 * 128 * 4;
+constexpr uint32_t OFF_VEC = OFF_B1 + STAGES * SMALLTILE;      // 2 x (64 L + 64 delta + 64 dropout row constants + 64 row bases)
+constexpr uint32_t OFF_BAR = OFF_VEC + 2 * 256 * 4;
 constexpr size_t SMEM = OFF_BAR + 256;
 constexpr uint32_t TMEM_COLS = 256;                 // 0..63 S, 64..127 dP, 128..255 accumulators
 }  // namespace fb
@@ -41,6 +41,7 @@ struct AttnBwdParams {
   const float* lse; const float* delta; int total_q;
   int causal; float scale, scale_log2;
   __nv_bfloat16* dq; __nv_bfloat16* dk; __nv_bfloat16* dv; int64_t dqs, dks, dvs;
+  AttnDropout drop;             // the forward's attention-probability dropout, regenerated here from (seed, head, row, key)
 };
 
 __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_t (&o)[32], float mul) {
@@ -58,7 +59,7 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* dst, const uint32_
 // ------------------------------------------------------------------------------------------ dQ
 // TMEM: S[0] 0..63, S[1] 64..127 (double-buffered: S_{j+1} is computed while block j is in the elementwise phase),
 // dP 128..191 (single buffer, handed back as soon as the elementwise warps have it in registers), dQ 192..255.
-template <int DH>
+template <int DH, bool DROP>
 __global__ void __launch_bounds__(fb::THREADS, 2)
 attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do,
                const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v, AttnBwdParams p) {
@@ -170,6 +171,9 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
     const float sl2 = p.scale_log2;
     const float L = valid ? p.lse[(int64_t)h * p.total_q + q0 + qi] : INFINITY;
     const float dl = valid ? p.delta[(int64_t)h * p.total_q + q0 + qi] : 0.0f;
+    const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? qi : 0));
+    const uint32_t rowconst = DROP ? attn_drop_rowconst(p.drop.seed, rowkey) : 0u;
+    const float rp = p.drop.rp;
     for (int j = 0; j < n_kv; ++j) {
       const uint32_t tmem_s = tmem_base + lane_addr + (j & 1) * 64 + half * 32;
       ptx::mbar_wait(&sp_full[j & 1], (j >> 1) & 1);
@@ -181,7 +185,20 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
       ptx::tc_fence_before();
       ptx::mbar_arrive(dp_free);
       const int kbase = j * SMALL + half * 32;
-      if (kbase + 32 <= my_end) {                  // whole half visible (the common case): no masking instructions
+      if (DROP) {                                  // dS = P . (M dP / (1 - p) - delta), M = the forward's keep mask
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
+          float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -L));
+          if (kbase + 2 * i >= my_end) p0 = 0.0f;
+          if (kbase + 2 * i + 1 >= my_end) p1 = 0.0f;
+          const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (SMALL / 2) + half * 16 + i));
+          const float t0 = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) * rp : 0.0f;
+          const float t1 = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) * rp : 0.0f;
+          const __nv_bfloat162 hh = __floats2bfloat162_rn(p0 * (t0 - dl), p1 * (t1 - dl));
+          pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+        }
+      } else if (kbase + 32 <= my_end) {           // whole half visible (the common case): no masking instructions
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
@@ -231,7 +248,7 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
 }
 
 // ------------------------------------------------------------------------------------------ dK / dV
-template <int DH>
+template <int DH, bool DROP>
 __global__ void __launch_bounds__(fb::THREADS, 2)
 attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v,
                   const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do, AttnBwdParams p) {
@@ -331,11 +348,14 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
     const float sl2 = p.scale_log2;
     for (int it = 0; it < n_it; ++it) {
       const int qbase = (i0 + it) * SMALL;
-      float* vb = vec + (it & 1) * 128;
+      float* vb = vec + (it & 1) * 256;
       if (tid < 128) {                             // stage L / delta of this query block (broadcast reads below)
         const int q = qbase + (tid & 63);
         const float* src = tid < 64 ? p.lse : p.delta;
         vb[tid] = q < lq ? src[(int64_t)h * p.total_q + q0 + q] : (tid < 64 ? INFINITY : 0.0f);
+      } else if (DROP) {                           // per query column: hash row constant (128..191) and low row base (192..255)
+        const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + qbase + (tid & 63));
+        reinterpret_cast<uint32_t*>(vb)[tid] = tid < 192 ? attn_drop_rowconst(p.drop.seed, rowkey) : (uint32_t)(rowkey << 15);
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       // first query column this key row may attend to (causal), all columns masked for rows past the sequence end
@@ -360,11 +380,22 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
         if (c + 1 < cmin) p1 = 0.0f;
         if (c + 2 < cmin) p2 = 0.0f;
         if (c + 3 < cmin) p3 = 0.0f;
-        const __nv_bfloat162 hp0 = __floats2bfloat162_rn(p0, p1), hp1 = __floats2bfloat162_rn(p2, p3);
-        const __nv_bfloat162 hd0 = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[4 * i4]) - d4.x),
-                                                         p1 * (__uint_as_float(dp[4 * i4 + 1]) - d4.y));
-        const __nv_bfloat162 hd1 = __floats2bfloat162_rn(p2 * (__uint_as_float(dp[4 * i4 + 2]) - d4.z),
-                                                         p3 * (__uint_as_float(dp[4 * i4 + 3]) - d4.w));
+        float m0 = 1.0f, m1 = 1.0f, m2 = 1.0f, m3 = 1.0f;         // M / (1 - p) of (query column, this key)
+        if (DROP) {
+          const uint4 rc = reinterpret_cast<const uint4*>(vb + 128 + half * 32)[i4];
+          const uint4 rb = reinterpret_cast<const uint4*>(vb + 192 + half * 32)[i4];
+          const uint32_t pair = (uint32_t)kr >> 1, sh = (kr & 1) * 16, thr = p.drop.thr;
+          const float rp = p.drop.rp;
+          m0 = ((mix32((rb.x + pair) ^ rc.x) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+          m1 = ((mix32((rb.y + pair) ^ rc.y) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+          m2 = ((mix32((rb.z + pair) ^ rc.z) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+          m3 = ((mix32((rb.w + pair) ^ rc.w) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+        }
+        const __nv_bfloat162 hp0 = __floats2bfloat162_rn(p0 * m0, p1 * m1), hp1 = __floats2bfloat162_rn(p2 * m2, p3 * m3);
+        const __nv_bfloat162 hd0 = __floats2bfloat162_rn(p0 * (m0 * __uint_as_float(dp[4 * i4]) - d4.x),
+                                                         p1 * (m1 * __uint_as_float(dp[4 * i4 + 1]) - d4.y));
+        const __nv_bfloat162 hd1 = __floats2bfloat162_rn(p2 * (m2 * __uint_as_float(dp[4 * i4 + 2]) - d4.z),
+                                                         p3 * (m3 * __uint_as_float(dp[4 * i4 + 3]) - d4.w));
         pk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hp0); pk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hp1);
         dk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hd0); dk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hd1);
       }
@@ -406,7 +437,8 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
 int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs, const void* dout,
                 int64_t dos, const float* lse, const float* delta, const int32_t* cu_q, const int32_t* cu_k, int batch,
                 int max_q, int max_k, int64_t total_q, int64_t total_k, int heads, int head_dim, int causal, float scale,
-                void* dq, void* dk, void* dv, int grad_dtype, int64_t dqs, int64_t dks, int64_t dvs, cudaStream_t st) {
+                void* dq, void* dk, void* dv, int grad_dtype, int64_t dqs, int64_t dks, int64_t dvs, AttnDropout drop,
+                cudaStream_t st) {
   using namespace fb;
   auto misaligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; };
   if (dtype != ACAI_BF16 || grad_dtype != ACAI_BF16 || (head_dim != 64 && head_dim != 32) || qs % 8 || ks % 8 || vs % 8 || dos % 8 || dqs % 8 ||
@@ -426,21 +458,25 @@ int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t 
   if ((rc = make_tma_2d_bf16(&do_small, dout, (uint64_t)total_q, cols, (uint64_t)dos, SMALL, D))) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+#define ACAI_SET(K) ACAI_CUDA(cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM))
+    ACAI_SET((attn_bwd_dq_tc<64, false>)); ACAI_SET((attn_bwd_dkv_tc<64, false>));
+    ACAI_SET((attn_bwd_dq_tc<32, false>)); ACAI_SET((attn_bwd_dkv_tc<32, false>));
+    ACAI_SET((attn_bwd_dq_tc<64, true>)); ACAI_SET((attn_bwd_dkv_tc<64, true>));
+    ACAI_SET((attn_bwd_dq_tc<32, true>)); ACAI_SET((attn_bwd_dkv_tc<32, true>));
+#undef ACAI_SET
     attr_set = true;
   }
   AttnBwdParams p{cu_q, cu_k, lse, delta, (int)total_q, causal, scale, scale * 1.4426950408889634f,
-                  (__nv_bfloat16*)dq, (__nv_bfloat16*)dk, (__nv_bfloat16*)dv, dqs, dks, dvs};
+                  (__nv_bfloat16*)dq, (__nv_bfloat16*)dk, (__nv_bfloat16*)dv, dqs, dks, dvs, drop};
   const dim3 gq((max_q + BIG - 1) / BIG, heads, batch), gk((max_k + BIG - 1) / BIG, heads, batch);
-  if (head_dim == 64) attn_bwd_dq_tc<64><<<gq, THREADS, SMEM, st>>>(q_big, do_big, k_small, v_small, p);
-  else attn_bwd_dq_tc<32><<<gq, THREADS, SMEM, st>>>(q_big, do_big, k_small, v_small, p);
+  const bool dr = drop.thr != 0;
+#define ACAI_LAUNCH(K, G, ...) do { if (head_dim == 64) { if (dr) K<64, true><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); else K<64, false><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); } \
+                                    else { if (dr) K<32, true><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); else K<32, false><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); } } while (0)
+  ACAI_LAUNCH(attn_bwd_dq_tc, gq, q_big, do_big, k_small, v_small, p);
   rc = launch_status("attn_bwd_dq_tc");
   if (rc) return rc;
-  if (head_dim == 64) attn_bwd_dkv_tc<64><<<gk, THREADS, SMEM, st>>>(k_big, v_big, q_small, do_small, p);
-  else attn_bwd_dkv_tc<32><<<gk, THREADS, SMEM, st>>>(k_big, v_big, q_small, do_small, p);
+  ACAI_LAUNCH(attn_bwd_dkv_tc, gk, k_big, v_big, q_small, do_small, p);
+#undef ACAI_LAUNCH
   return launch_status("attn_bwd_dkv_tc");
 }
 

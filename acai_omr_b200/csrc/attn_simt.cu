@@ -17,7 +17,7 @@ __global__ void __launch_bounds__(QB)
 attn_varlen_simt(const void* __restrict__ q, const void* __restrict__ k, const void* __restrict__ v, int dt,
                  int64_t qs, int64_t ks, int64_t vs, const int32_t* __restrict__ cu_q,
                  const int32_t* __restrict__ cu_k, int d, int causal, float scale,
-                 void* __restrict__ out, int out_dt, int64_t os, float* __restrict__ lse, int total_q) {
+                 void* __restrict__ out, int out_dt, int64_t os, float* __restrict__ lse, int total_q, AttnDropout drop) {
   __shared__ float Ks[KT][DMAX];
   __shared__ float Vs[KT][DMAX];
   const int b = blockIdx.z, h = blockIdx.y, qb = blockIdx.x, tid = threadIdx.x;
@@ -72,9 +72,11 @@ attn_varlen_simt(const void* __restrict__ q, const void* __restrict__ k, const v
         for (int c = 0; c < KC; ++c) {
           const int j = c0 + c;
           const float p = (s[c] > -INFINITY) ? expf(s[c] - m_new) : 0.0f;
-          l += p;
+          l += p;                                   // the normaliser sums the un-dropped probabilities
+          float pd = p;
+          if (drop.thr && p > 0.0f && !attn_drop_keep(drop, (uint64_t)h * total_q + (uint64_t)(q0 + (valid ? row : 0)), t0 + j)) pd = 0.0f;
 #pragma unroll
-          for (int e = 0; e < DMAX; ++e) acc[e] = fmaf(p, Vs[j < KT ? j : KT - 1][e], acc[e]);
+          for (int e = 0; e < DMAX; ++e) acc[e] = fmaf(pd, Vs[j < KT ? j : KT - 1][e], acc[e]);
         }
         m = m_new;
       }
@@ -82,7 +84,7 @@ attn_varlen_simt(const void* __restrict__ q, const void* __restrict__ k, const v
     __syncthreads();
   }
   if (valid) {
-    const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+    const float inv = l > 0.0f ? (drop.thr ? drop.rp : 1.0f) / l : 0.0f;
 #pragma unroll
     for (int e = 0; e < DMAX; ++e)
       if (e < d) st_from_float(out, (int64_t)(q0 + row) * os + (int64_t)h * d + e, out_dt, acc[e] * inv);
@@ -138,7 +140,7 @@ decode_attn_simt(const void* __restrict__ q, int q_dt, int64_t q_bs, const void*
 int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs,
                    const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
                    int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, float* lse,
-                   cudaStream_t st);
+                   AttnDropout drop, cudaStream_t st);
 
 }  // namespace acai
 
@@ -148,8 +150,11 @@ extern "C" int acai_attn_varlen_fwd(const void* q, const void* k, const void* v,
                                     int64_t k_stride, int64_t v_stride, const int32_t* cu_seqlens_q,
                                     const int32_t* cu_seqlens_k, int32_t batch, int32_t max_seqlen_q, int32_t total_q,
                                     int32_t total_k, int32_t heads, int32_t head_dim, int32_t causal, float scale,
-                                    void* out, int32_t out_dtype, int64_t o_stride, float* lse, void* stream) {
+                                    void* out, int32_t out_dtype, int64_t o_stride, float* lse, float dropout_p,
+                                    uint64_t dropout_seed, void* stream) {
   ACAI_CHECK_ARG(q && k && v && cu_seqlens_q && cu_seqlens_k && out, "acai_attn_varlen_fwd: null pointer");
+  ACAI_CHECK_ARG(dropout_p >= 0.0f && dropout_p < 1.0f, "acai_attn_varlen_fwd: dropout_p out of range");
+  const AttnDropout drop{dropout_seed, dropout_threshold(dropout_p), 1.0f / (1.0f - dropout_p)};
   ACAI_CHECK_ARG(batch > 0 && heads > 0 && head_dim > 0 && max_seqlen_q >= 0, "acai_attn_varlen_fwd: bad sizes");
   ACAI_CHECK_ARG(dtype_valid(dtype) && dtype_valid(out_dtype), "acai_attn_varlen_fwd: bad dtype");
   if (head_dim > 128) { set_error("acai_attn_varlen_fwd: head_dim %d > 128 unsupported", head_dim); return ACAI_ERR_UNSUPPORTED; }
@@ -158,12 +163,12 @@ extern "C" int acai_attn_varlen_fwd(const void* q, const void* k, const void* v,
   cudaStream_t st = (cudaStream_t)stream;
   {
     int rc = attn_varlen_tc(q, k, v, dtype, q_stride, k_stride, v_stride, cu_seqlens_q, cu_seqlens_k, batch,
-                            max_seqlen_q, total_q, total_k, heads, head_dim, causal, scale, out, out_dtype, o_stride, lse, st);
+                            max_seqlen_q, total_q, total_k, heads, head_dim, causal, scale, out, out_dtype, o_stride, lse, drop, st);
     if (rc != ACAI_ERR_UNSUPPORTED) return rc;
   }
   dim3 grid((max_seqlen_q + QB - 1) / QB, heads, batch);
 #define LAUNCH(D) attn_varlen_simt<D><<<grid, QB, 0, st>>>(q, k, v, dtype, q_stride, k_stride, v_stride, cu_seqlens_q, \
-                                                           cu_seqlens_k, head_dim, causal, scale, out, out_dtype, o_stride, lse, total_q)
+                                                           cu_seqlens_k, head_dim, causal, scale, out, out_dtype, o_stride, lse, total_q, drop)
   if (head_dim <= 16) LAUNCH(16);
   else if (head_dim <= 32) LAUNCH(32);
   else if (head_dim <= 64) LAUNCH(64);
@@ -193,4 +198,27 @@ extern "C" int acai_decode_attn(const void* q, int32_t q_dtype, int64_t q_batch_
       q, q_dtype, q_batch_stride, k, v, kv_dtype, kv_batch_stride, kv_head_stride, kv_tok_stride, head_dim, kv_len,
       key_padding_mask, mask_stride, scale, out, out_dtype, o_batch_stride);
   return launch_status("decode_attn_simt");
+}
+
+
+// Test / inspection aid: the keep decisions of the attention-probability dropout, keep[h, q, k] for global query rows q
+// and key positions k < max_k inside their sequence - exactly what every attention kernel regenerates.
+namespace acai {
+__global__ void attn_dropout_mask_kernel(AttnDropout drop, int heads, int total_q, int max_k, uint8_t* __restrict__ keep) {
+  const int64_t n = (int64_t)heads * total_q * max_k;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % max_k);
+    const int64_t rowkey = i / max_k;                 // = h * total_q + q
+    keep[i] = attn_drop_keep(drop, (uint64_t)rowkey, k) ? 1 : 0;
+  }
+}
+}  // namespace acai
+
+extern "C" int acai_attn_dropout_mask(float dropout_p, uint64_t dropout_seed, int32_t heads, int32_t total_q, int32_t max_k,
+                                      uint8_t* keep, void* stream) {
+  ACAI_CHECK_ARG(keep && heads > 0 && total_q > 0 && max_k > 0 && dropout_p >= 0.0f && dropout_p < 1.0f,
+                 "acai_attn_dropout_mask: bad argument");
+  const acai::AttnDropout drop{dropout_seed, acai::dropout_threshold(dropout_p), 1.0f / (1.0f - dropout_p)};
+  acai::attn_dropout_mask_kernel<<<1184, 256, 0, (cudaStream_t)stream>>>(drop, heads, total_q, max_k, keep);
+  return launch_status("attn_dropout_mask");
 }

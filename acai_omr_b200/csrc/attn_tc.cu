@@ -42,11 +42,12 @@ struct AttnParams {
   void* out; int out_dt; int64_t o_stride;
   int causal; float scale_log2;
   float* lse; int total_q;      // optional [heads, total_q] log2-domain log-sum-exp of every query row (for the backward)
+  AttnDropout drop;             // attention-probability dropout (training): P is masked before P V, l sums the unmasked P
 };
 
 // DH = head_dim (64 or 32).  Shared-memory tiles are always 64 columns (one 128-byte swizzle row) wide: for DH = 32 a
 // tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
-template <int DH>
+template <int DH, bool DROP>
 __global__ void __launch_bounds__(THREADS, 2)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
@@ -147,6 +148,8 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
     const uint32_t tmem_o = tmem_base + lane_addr + 128;
     const float scale_log2 = p.scale_log2;
     float m = -INFINITY, l = 0.0f;
+    const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? qi : 0));
+    const uint32_t rowconst = DROP ? attn_drop_rowconst(p.drop.seed, rowkey) : 0u;
 
     for (int j = 0; j < n_kv; ++j) {
       const uint32_t tmem_s = tmem_base + lane_addr + (j & 1) * 64;
@@ -196,7 +199,13 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
         const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff));
         const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff));
         l0 += p0; l1 += p1;
-        const __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+        float d0 = p0, d1 = p1;
+        if (DROP) {                                   // keys kbase + 2i, kbase + 2i + 1 = one hash pair
+          const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (BKV / 2) + i));
+          if ((bits & 0xffffu) < p.drop.thr) d0 = 0.0f;
+          if ((bits >> 16) < p.drop.thr) d1 = 0.0f;
+        }
+        const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
         pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
       }
       l += l0 + l1;
@@ -209,7 +218,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
       ptx::mbar_wait(o_full, 0);
       ptx::tc_fence_after();
     }
-    const float inv = l > 0.0f ? 1.0f / l : 0.0f;
+    const float inv = l > 0.0f ? (DROP ? p.drop.rp : 1.0f) / l : 0.0f;
     if (p.lse && valid) p.lse[(int64_t)h * p.total_q + q0 + qi] = l > 0.0f ? m * scale_log2 + log2f(l) : INFINITY;
     const int64_t off = (int64_t)(q0 + qi) * p.o_stride + (int64_t)h * DH;
 #pragma unroll
@@ -252,7 +261,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
 int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs,
                    const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
                    int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, float* lse,
-                   cudaStream_t st) {
+                   AttnDropout drop, cudaStream_t st) {
   if (dtype != ACAI_BF16 || (head_dim != 64 && head_dim != 32) || qs % 8 || ks % 8 || vs % 8 || os % 8 || total_q <= 0 || total_k <= 0 ||
       (reinterpret_cast<uintptr_t>(q) & 15) || (reinterpret_cast<uintptr_t>(k) & 15) ||
       (reinterpret_cast<uintptr_t>(v) & 15) || (reinterpret_cast<uintptr_t>(out) & 15))
@@ -267,14 +276,21 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
     attr_set = true;
   }
-  AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q};
+  AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q, drop};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
-  if (head_dim == 64) attn_fwd_tc<64><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
-  else attn_fwd_tc<32><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+  if (drop.thr == 0) {
+    if (head_dim == 64) attn_fwd_tc<64, false><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+    else attn_fwd_tc<32, false><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+  } else {
+    if (head_dim == 64) attn_fwd_tc<64, true><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+    else attn_fwd_tc<32, true><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+  }
   return launch_status("attn_fwd_tc");
 }
 

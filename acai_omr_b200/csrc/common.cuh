@@ -55,6 +55,41 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }
 
+// ---- counter-based dropout randomness ---------------------------------------------------------------------------
+// One 32-bit avalanche hash (two multiply / xor-shift rounds) of (seed, index of an element PAIR) yields two 16-bit
+// uniforms; an element is kept when its 16 bits are >= thr = round(p * 65536).  Stateless, so the backward kernels
+// regenerate exactly the forward's mask from (seed, index) - no mask tensor is stored.
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t dropout_bits(uint64_t seed, uint64_t pair) {
+  return mix32((uint32_t)pair ^ mix32((uint32_t)(pair >> 32) ^ (uint32_t)seed) ^ (uint32_t)(seed >> 32));
+}
+__host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, uint32_t thr) {
+  return ((dropout_bits(seed, idx >> 1) >> ((idx & 1) * 16)) & 0xffffu) >= thr;
+}
+__host__ __device__ __forceinline__ uint32_t dropout_threshold(float p) {
+  const float t = p * 65536.0f + 0.5f;
+  return t <= 0.0f ? 0u : (t >= 65536.0f ? 65536u : (uint32_t)t);
+}
+
+// Attention-probability dropout (nn.MultiheadAttention(dropout=p) in training mode): element (head h, global query row
+// q, key position k inside its sequence) belongs to pair (rowkey << 15) + (k >> 1) with rowkey = h * total_q + q, and
+// takes the low / high 16 bits of that pair's hash for even / odd k.  All attention kernels (tensor-core and SIMT,
+// forward and both backward passes) derive the mask from these three functions, so they agree bit for bit.
+struct AttnDropout { uint64_t seed; uint32_t thr; float rp; };        // thr = 0: no dropout; rp = 1 / (1 - p)
+__host__ __device__ __forceinline__ uint32_t attn_drop_rowconst(uint64_t seed, uint64_t rowkey) {
+  return mix32((uint32_t)((rowkey << 15) >> 32) ^ (uint32_t)seed) ^ (uint32_t)(seed >> 32);
+}
+__host__ __device__ __forceinline__ uint32_t attn_drop_bits(uint32_t rowconst, uint64_t rowkey, uint32_t pair_in_row) {
+  return mix32(((uint32_t)(rowkey << 15) + pair_in_row) ^ rowconst);
+}
+__host__ __device__ __forceinline__ bool attn_drop_keep(const AttnDropout& d, uint64_t rowkey, int k) {
+  const uint32_t bits = attn_drop_bits(attn_drop_rowconst(d.seed, rowkey), rowkey, (uint32_t)k >> 1);
+  return ((bits >> ((k & 1) * 16)) & 0xffffu) >= d.thr;
+}
+
 // 2^x on the MUFU pipe (ex2.approx.ftz): ~2 ulp, no denormal fix-up code around it
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;

@@ -625,3 +625,47 @@ extern "C" int acai_mix_rows(const void* a, int32_t a_dtype, const int64_t* sel,
   acai::mix_rows_kernel<<<rows, dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(a, a_dtype, sel, b, b_dtype, pos, period, dim, out, out_dtype);
   return launch_status("mix_rows");
 }
+
+// ------------------------------------------------------------------------------------------ dropout (hidden states)
+namespace acai {
+// out[i] = residual[i] + (keep(i) ? x[i] / (1 - p) : 0); the same call on dY (no residual) is the backward.
+__global__ void __launch_bounds__(256)
+dropout_kernel(const void* __restrict__ x, int dt, const void* __restrict__ res, int res_dt, int64_t n, uint32_t thr, float scale,
+               uint64_t seed, void* __restrict__ out, int out_dt) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t pr = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; 2 * pr < n; pr += stride) {
+    const uint32_t bits = dropout_bits(seed, (uint64_t)pr);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int64_t i = 2 * pr + j;
+      if (i < n) {
+        float v = ((bits >> (16 * j)) & 0xffffu) >= thr ? ld_as_float(x, i, dt) * scale : 0.0f;
+        if (res) v += ld_as_float(res, i, res_dt);
+        st_from_float(out, i, out_dt, v);
+      }
+    }
+  }
+}
+__global__ void dropout_mask_kernel(int64_t n, uint32_t thr, uint64_t seed, uint8_t* __restrict__ keep) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    keep[i] = dropout_keep(seed, (uint64_t)i, thr) ? 1 : 0;
+}
+}  // namespace acai
+
+extern "C" int acai_dropout(const void* x, int32_t dtype, const void* residual, int32_t res_dtype, int64_t n, float p,
+                            uint64_t seed, void* out, int32_t out_dtype, void* stream) {
+  ACAI_CHECK_ARG(x && out && n >= 0 && p >= 0.0f && p < 1.0f && dtype_valid(dtype) && dtype_valid(out_dtype) &&
+                 (!residual || dtype_valid(res_dtype)), "acai_dropout: bad argument");
+  if (n == 0) return ACAI_OK;
+  acai::dropout_kernel<<<grid_for((n + 1) / 2), 256, 0, (cudaStream_t)stream>>>(x, dtype, residual, res_dtype, n, dropout_threshold(p),
+                                                                               1.0f / (1.0f - p), seed, out, out_dtype);
+  return launch_status("dropout");
+}
+
+extern "C" int acai_dropout_mask(int64_t n, float p, uint64_t seed, uint8_t* keep, void* stream) {
+  ACAI_CHECK_ARG(keep && n >= 0 && p >= 0.0f && p < 1.0f, "acai_dropout_mask: bad argument");
+  if (n == 0) return ACAI_OK;
+  acai::dropout_mask_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(n, dropout_threshold(p), seed, keep);
+  return launch_status("dropout_mask");
+}

@@ -7,6 +7,9 @@ Covers the training rows of SURVEY §8: teacher-forced ViTOMR (models.py:649-737
 pre-training (models.py:197-288).  With gradients disabled every function is a plain `ops` call, so the
 inference path is unchanged.
 
+Dropout (training mode, p > 0) uses counter-based masks regenerated in the backward (`ops.DropoutState`): the keep
+rate and 1/(1-p) scaling are nn.Dropout's, the random stream is not torch's Philox (it cannot be reproduced).
+
 Not differentiable here (raise instead of silently detaching): interpolated position embeddings (oversize
 images) and the second LayerNorm output used by the cached decoder.
 """
@@ -159,62 +162,67 @@ class _SelfAttention(torch.autograd.Function):
     """Packed ragged self-attention over a fused [T, 3D] QKV buffer; backward fills one d(QKV) buffer."""
 
     @staticmethod
-    def forward(ctx, qkv, cu, max_len, heads, head_dim, causal, flops):
+    def forward(ctx, qkv, cu, max_len, heads, head_dim, causal, flops, dropout_p, seed):
         D = heads * head_dim
         out, lse = ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], cu, cu, max_len, heads, head_dim,
-                                   causal=causal, out_dtype=qkv.dtype, flops=flops, return_lse=True)
+                                   causal=causal, out_dtype=qkv.dtype, flops=flops, return_lse=True, dropout_p=dropout_p,
+                                   dropout_seed=seed)
         ctx.save_for_backward(qkv, out, lse, cu)
-        ctx.meta = (max_len, heads, head_dim, causal)
+        ctx.meta = (max_len, heads, head_dim, causal, dropout_p, seed)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         qkv, out, lse, cu = ctx.saved_tensors
-        max_len, heads, head_dim, causal = ctx.meta
+        max_len, heads, head_dim, causal, dropout_p, seed = ctx.meta
         D = heads * head_dim
         dqkv = torch.empty_like(qkv)
         ops.attn_varlen_bwd(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], out, dout, lse, cu, cu, max_len, max_len, heads,
-                            head_dim, causal, dqkv[:, :D], dqkv[:, D:2 * D], dqkv[:, 2 * D:])
-        return dqkv, None, None, None, None, None, None
+                            head_dim, causal, dqkv[:, :D], dqkv[:, D:2 * D], dqkv[:, 2 * D:], dropout_p=dropout_p,
+                            dropout_seed=seed)
+        return dqkv, None, None, None, None, None, None, None, None
 
 
 class _CrossAttention(torch.autograd.Function):
     """q:[Tq, D] against a fused [Tk, 2D] K|V buffer (kv_caching.py:241-245 layout)."""
 
     @staticmethod
-    def forward(ctx, q, kv, cu_q, cu_k, max_q, max_k, heads, head_dim, flops):
+    def forward(ctx, q, kv, cu_q, cu_k, max_q, max_k, heads, head_dim, flops, dropout_p, seed):
         D = heads * head_dim
         out, lse = ops.attn_varlen(q, kv[:, :D], kv[:, D:], cu_q, cu_k, max_q, heads, head_dim, causal=False,
-                                   out_dtype=q.dtype, flops=flops, return_lse=True)
+                                   out_dtype=q.dtype, flops=flops, return_lse=True, dropout_p=dropout_p, dropout_seed=seed)
         ctx.save_for_backward(q, kv, out, lse, cu_q, cu_k)
-        ctx.meta = (max_q, max_k, heads, head_dim)
+        ctx.meta = (max_q, max_k, heads, head_dim, dropout_p, seed)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, kv, out, lse, cu_q, cu_k = ctx.saved_tensors
-        max_q, max_k, heads, head_dim = ctx.meta
+        max_q, max_k, heads, head_dim, dropout_p, seed = ctx.meta
         D = heads * head_dim
         dq, dkv = torch.empty_like(q), torch.empty_like(kv)
         ops.attn_varlen_bwd(q, kv[:, :D], kv[:, D:], out, dout, lse, cu_q, cu_k, max_q, max_k, heads, head_dim, False,
-                            dq, dkv[:, :D], dkv[:, D:])
-        return dq, dkv, None, None, None, None, None, None, None
+                            dq, dkv[:, :D], dkv[:, D:], dropout_p=dropout_p, dropout_seed=seed)
+        return dq, dkv, None, None, None, None, None, None, None, None, None
 
 
-def self_attention(qkv, pk, heads, head_dim, causal, flops=0.0):
+def self_attention(qkv, pk, heads, head_dim, causal, flops=0.0, dropout_p=0.0, dropout_seed=None):
+    """`dropout_p` > 0: attention-probability dropout (training); a fresh seed is drawn unless one is given."""
     D = heads * head_dim
+    seed = 0 if dropout_p <= 0.0 else (ops.DropoutState.next_seed() if dropout_seed is None else dropout_seed)
     if not needs_grad(qkv):
         return ops.attn_varlen(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pk.cu, pk.cu, pk.max_len, heads, head_dim,
-                               causal=causal, out_dtype=qkv.dtype, flops=flops)
-    return _SelfAttention.apply(qkv, pk.cu, pk.max_len, heads, head_dim, causal, flops)
+                               causal=causal, out_dtype=qkv.dtype, flops=flops, dropout_p=dropout_p, dropout_seed=seed)
+    return _SelfAttention.apply(qkv, pk.cu, pk.max_len, heads, head_dim, causal, flops, dropout_p, seed)
 
 
-def cross_attention(q, kv, pq, pk, heads, head_dim, flops=0.0):
+def cross_attention(q, kv, pq, pk, heads, head_dim, flops=0.0, dropout_p=0.0, dropout_seed=None):
     D = heads * head_dim
+    seed = 0 if dropout_p <= 0.0 else (ops.DropoutState.next_seed() if dropout_seed is None else dropout_seed)
     if not needs_grad(q, kv):
         return ops.attn_varlen(q, kv[:, :D], kv[:, D:], pq.cu, pk.cu, pq.max_len, heads, head_dim, causal=False,
-                               out_dtype=q.dtype, flops=flops)
-    return _CrossAttention.apply(q, kv, pq.cu, pk.cu, pq.max_len, pk.max_len, heads, head_dim, flops)
+                               out_dtype=q.dtype, flops=flops, dropout_p=dropout_p, dropout_seed=seed)
+    return _CrossAttention.apply(q, kv, pq.cu, pk.cu, pq.max_len, pk.max_len, heads, head_dim, flops, dropout_p, seed)
 
 
 # ------------------------------------------------------------------------------------------ packed <-> padded
@@ -590,3 +598,32 @@ def embed_rows(ids, table, out_dtype, padding_idx=None):
     if not needs_grad(table):
         return ops.gather_rows(table, ids, out_dtype=out_dtype).view(*ids.shape, table.shape[1])
     return _EmbedRows.apply(ids, table, out_dtype, padding_idx)
+
+
+# ------------------------------------------------------------------------------------------ dropout
+class _Dropout(torch.autograd.Function):
+    """y = residual + dropout(x): nn.Dropout followed by the residual add of a post-norm block."""
+
+    @staticmethod
+    def forward(ctx, x, residual, p, seed):
+        ctx.meta = (p, seed, residual is not None and residual.dtype)
+        return ops.dropout(x, p, seed, residual=residual)
+
+    @staticmethod
+    def backward(ctx, dy):
+        p, seed, rdt = ctx.meta
+        dx = ops.dropout(dy, p, seed) if ctx.needs_input_grad[0] else None
+        dres = None
+        if rdt is not False and ctx.needs_input_grad[1]:
+            dres = dy if dy.dtype == rdt else dy.to(rdt)
+        return dx, dres, None, None
+
+
+def dropout(x, p, training, residual=None):
+    """nn.Dropout(p)(x) (+ residual).  Identity (or a plain add folded elsewhere by the caller) when not training or p == 0."""
+    if not training or p <= 0.0:
+        raise ops.AcaiError("functional.dropout: call only when a mask is needed (training and p > 0)")
+    seed = ops.DropoutState.next_seed()
+    if not needs_grad(x, residual):
+        return ops.dropout(x, p, seed, residual=residual)
+    return _Dropout.apply(x, residual, p, seed)

@@ -130,13 +130,24 @@ class MultiheadAttention(nn.Module):
         nn.init.constant_(self.out_proj.bias, 0.0)
 
     # ---- packed helpers -------------------------------------------------------------------
+    def _p(self):
+        """Dropout probability in force: nn.MultiheadAttention(dropout=p) drops attention probabilities in training mode;
+        the owning layer applies the same p to the block output before the residual add (dropout1/dropout2)."""
+        return self.dropout if self.training else 0.0
+
+    def _out(self, a, residual, dt):
+        p = self._p()
+        if p > 0.0:      # residual + dropout(out_proj(a)): the residual add moves out of the GEMM epilogue
+            return F.dropout(F.linear(a, self.out_proj.weight, self.out_proj.bias, out_dtype=dt), p, True, residual=residual)
+        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt)
+
     def self_attention_packed(self, x, pk, causal, residual):
         """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D]."""
         dt, D = x.dtype, self.embed_dim
         qkv = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt)
         a = F.self_attention(qkv, pk, self.num_heads, self.head_dim, causal,
-                             flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0))
-        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt)
+                             flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0), dropout_p=self._p())
+        return self._out(a, residual, dt)
 
     def project_memory_packed(self, mem):
         """[K | V] = mem . W_kv^T + b_kv  (kv_caching.py:241-245) over packed memory rows."""
@@ -147,8 +158,8 @@ class MultiheadAttention(nn.Module):
         dt, D = x.dtype, self.embed_dim
         q = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(0, D))
         a = F.cross_attention(q, kv, pq, pk, self.num_heads, self.head_dim,
-                              flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)))
-        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt)
+                              flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)), dropout_p=self._p())
+        return self._out(a, residual, dt)
 
 
 class Packed:
@@ -213,16 +224,22 @@ class TransformerEncoderLayer(nn.Module):
         dt = x.dtype
         y = self.self_attn.self_attention_packed(x, pk, False, residual=x)
         x = self.norm1(y, out_dtype=dt)
-        h = F.linear(x, self.linear1.weight, self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
-        y = F.linear(h, self.linear2.weight, self.linear2.bias, residual=x, out_dtype=dt)
-        return self.norm2(y, out_dtype=dt)
+        return self.norm2(_mlp_residual(self, x, dt), out_dtype=dt)
+
+
+def _mlp_residual(layer, x, dt):
+    """x + dropout2(linear2(dropout(gelu(linear1(x)))))  (the feed-forward block of nn.Transformer*Layer, post-norm)."""
+    p = layer.dropout_p if layer.training else 0.0
+    h = F.linear(x, layer.linear1.weight, layer.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+    if p > 0.0:
+        h = F.dropout(h, p, True)
+        return F.dropout(F.linear(h, layer.linear2.weight, layer.linear2.bias, out_dtype=dt), p, True, residual=x)
+    return F.linear(h, layer.linear2.weight, layer.linear2.bias, residual=x, out_dtype=dt)
 
 
 def _check_dropout(module, p):
-    if module.training and p > 0.0:
-        raise NotImplementedError(
-            "acai_omr_b200 implements the deterministic path (eval mode, or train mode with dropout 0); "
-            f"got training=True with dropout={p}")
+    """Dropout is implemented (counter-based masks, see functional.py); kept as a no-op hook for callers."""
+    return None
 
 
 class TransformerEncoder(nn.Module):
@@ -282,10 +299,7 @@ class TransformerDecoderLayer(nn.Module):
         return MultiheadAttention(d_model, nhead, dropout=dropout, **kw)
 
     def mlp_packed(self, x):
-        dt = x.dtype
-        h = F.linear(x, self.linear1.weight, self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
-        y = F.linear(h, self.linear2.weight, self.linear2.bias, residual=x, out_dtype=dt)
-        return self.norm3(y, out_dtype=dt)
+        return self.norm3(_mlp_residual(self, x, x.dtype), out_dtype=x.dtype)
 
     def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True):
         dt = x.dtype
@@ -334,12 +348,14 @@ class TransformerDecoder(nn.Module):
         return F.unpack_padded(x, tp.cu, B, T)
 
 
-def gelu_mlp_head(x, lin_a: Linear, lin_b: Linear, out_dtype=None):
-    """Linear -> exact GELU -> Linear with the activation fused into the first GEMM's epilogue."""
+def gelu_mlp_head(x, lin_a: Linear, lin_b: Linear, out_dtype=None, dropout_p=0.0):
+    """Linear -> exact GELU -> (Dropout) -> Linear with the activation fused into the first GEMM's epilogue."""
     dt = compute_dtype()
     if x.dtype != dt:
         x = x.to(dt)
     h = F.linear(x, lin_a.weight, lin_a.bias, act=ops.ACT_GELU, out_dtype=dt)
+    if dropout_p > 0.0:
+        h = F.dropout(h, dropout_p, True)
     return F.linear(h, lin_b.weight, lin_b.bias, out_dtype=out_dtype or dt)
 
 

@@ -316,15 +316,14 @@ class TransitionHead(nn.Sequential):
     models.py:655-660); forward fuses the GELU into the first projection's epilogue."""
 
     def forward(self, x):
-        if self.training and self[2].p > 0.0:
-            raise NotImplementedError("transition head dropout > 0 in training mode is not implemented")
+        p = self[2].p if self.training else 0.0
         packed = getattr(x, "_acai_packed", None)
         if packed is None:
-            return gelu_mlp_head(x, self[0], self[3])
+            return gelu_mlp_head(x, self[0], self[3], dropout_p=p)
         # came straight from the encoder: run on the packed rows of valid patches only and re-pad with zeros
         # (the reference computes head(padding row) there; those rows are masked everywhere downstream)
         h, pk = packed
-        hp = gelu_mlp_head(h, self[0], self[3])
+        hp = gelu_mlp_head(h, self[0], self[3], dropout_p=p)
         out = F.unpack_padded(hp, pk.cu, pk.batch, x.shape[1])
         out._acai_packed = (hp, pk)
         return out

@@ -175,7 +175,7 @@ def layernorm(x, gamma, beta, eps, residual=None, out_dtype=None, out2_dtype=Non
 
 
 def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_dtype=None, scale=None, flops=0.0,
-                return_lse=False):
+                return_lse=False, dropout_p=0.0, dropout_seed=0):
     """Packed ragged attention.  q:[Tq, >=H*d] k,v:[Tk, >=H*d] row-strided views (acai_attn_varlen_fwd)."""
     _cuda(q, k, v, cu_q, cu_k)
     if not (q.dtype == k.dtype == v.dtype):
@@ -191,7 +191,8 @@ def attn_varlen(q, k, v, cu_q, cu_k, max_q, heads, head_dim, causal=False, out_d
     _call("acai_attn_varlen_fwd", lib.acai_attn_varlen_fwd, _p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0), v.stride(0),
                                         _p(cu_q), _p(cu_k), cu_q.numel() - 1, int(max_q), q.shape[0], k.shape[0], heads, head_dim,
                                         1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
-                                        _p(out), _DT[out_dtype], D, _p(lse), _stream(), flops=flops)
+                                        _p(out), _DT[out_dtype], D, _p(lse), float(dropout_p), C.c_uint64(dropout_seed),
+                                        _stream(), flops=flops)
     return (out, lse) if return_lse else out
 
 
@@ -497,7 +498,8 @@ def layernorm_bwd(dy, x, residual, gamma, eps, dv_dtype=None):
     return dv.view(x.shape), dg, db
 
 
-def attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, max_q, max_k, heads, head_dim, causal, dq, dk, dv, scale=None):
+def attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, max_q, max_k, heads, head_dim, causal, dq, dk, dv, scale=None,
+                    dropout_p=0.0, dropout_seed=0):
     """Writes dq/dk/dv (row-strided 2-D views, e.g. slices of a fused d(QKV) buffer) - acai_attn_varlen_bwd."""
     _cuda(q, k, v, out, dout, lse, cu_q, cu_k, dq, dk, dv)
     dout = dout if dout.stride(1) == 1 else dout.contiguous()
@@ -507,7 +509,8 @@ def attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, max_q, max_k, heads, he
     _call("acai_attn_varlen_bwd", _lib.load().acai_attn_varlen_bwd, _p(q), _p(k), _p(v), _dt(q), q.stride(0), k.stride(0),
           v.stride(0), _p(out), out.stride(0), _p(dout), dout.stride(0), _p(lse), _p(cu_q), _p(cu_k), cu_q.numel() - 1,
           int(max_q), int(max_k), q.shape[0], k.shape[0], heads, head_dim, 1 if causal else 0, float(scale or 1.0 / math.sqrt(head_dim)),
-          _p(dq), _p(dk), _p(dv), _dt(dq), dq.stride(0), dk.stride(0), dv.stride(0), _p(delta), _stream())
+          _p(dq), _p(dk), _p(dv), _dt(dq), dq.stride(0), dk.stride(0), dv.stride(0), _p(delta), float(dropout_p),
+          C.c_uint64(dropout_seed), _stream())
     _bump(2)
 
 
@@ -609,3 +612,48 @@ def mix_rows(b, a=None, sel=None, pos=None, period=0, out_dtype=None):
     _call("acai_mix_rows", _lib.load().acai_mix_rows, _p(a2), _dt(a2) if a2 is not None else 0, _p(s), _p(b2), _dt(b2),
           _p(_f32c(pos)), int(period), b2.shape[0], dim, _p(out), _dt(out), _stream())
     return out.view(b.shape)
+
+
+# ------------------------------------------------------------------------------------------ dropout
+class DropoutState:
+    """Seeds for the counter-based dropout masks: one 64-bit seed per dropout call, derived on the host from a base
+    seed and a call counter (no device synchronisation).  `manual_seed` makes a run reproducible."""
+    base = 0x5EED_ACA1_0000_0001
+    counter = 0
+
+    @classmethod
+    def manual_seed(cls, seed: int):
+        cls.base, cls.counter = int(seed) & 0xFFFFFFFFFFFFFFFF, 0
+
+    @classmethod
+    def next_seed(cls) -> int:
+        cls.counter += 1
+        x = (cls.base + 0x9E3779B97F4A7C15 * cls.counter) & 0xFFFFFFFFFFFFFFFF      # splitmix64 step
+        x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+        x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+        return x ^ (x >> 31)
+
+
+def dropout(x, p, seed, residual=None, out_dtype=None):
+    """residual + keep(seed) * x / (1 - p)  (acai_dropout); the same call on a gradient is the backward."""
+    _cuda(x, residual)
+    x = x.contiguous()
+    r = residual.contiguous() if residual is not None else None
+    out = torch.empty(x.shape, dtype=out_dtype or x.dtype, device=x.device)
+    _call("acai_dropout", _lib.load().acai_dropout, _p(x), _dt(x), _p(r), _dt(r) if r is not None else 0, x.numel(), float(p),
+          C.c_uint64(seed), _p(out), _dt(out), _stream())
+    return out
+
+
+def dropout_mask(n, p, seed, device):
+    keep = torch.empty(n, dtype=torch.uint8, device=device)
+    _call("acai_dropout_mask", _lib.load().acai_dropout_mask, n, float(p), C.c_uint64(seed), _p(keep), _stream())
+    return keep.bool()
+
+
+def attn_dropout_mask(p, seed, heads, total_q, max_k, device):
+    """keep[h, q, k] (bool) of the attention-probability dropout for (p, seed) - what the attention kernels regenerate."""
+    keep = torch.empty((heads, total_q, max_k), dtype=torch.uint8, device=device)
+    _call("acai_attn_dropout_mask", _lib.load().acai_attn_dropout_mask, float(p), C.c_uint64(seed), heads, total_q, max_k,
+          _p(keep), _stream())
+    return keep.bool()

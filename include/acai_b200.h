@@ -109,6 +109,7 @@ int acai_attn_varlen_fwd(const void* q, const void* k, const void* v, int32_t dt
                          void* out, int32_t out_dtype, int64_t o_stride,
                          float* lse, /* optional [heads, total_q]: log2-domain log-sum-exp per query row (saved for
                                         acai_attn_varlen_bwd); NULL in inference */
+                         float dropout_p, uint64_t dropout_seed, /* attention-probability dropout, 0 = off (see below) */
                          void* stream);
 
 /* Backward of the above (autograd of nn.MultiheadAttention / SDPA in the teacher-forced and MAE training steps,
@@ -122,7 +123,8 @@ int acai_attn_varlen_bwd(const void* q, const void* k, const void* v, int32_t dt
                          int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k, int32_t total_q, int32_t total_k,
                          int32_t heads, int32_t head_dim, int32_t causal, float scale,
                          void* dq, void* dk, void* dv, int32_t grad_dtype,
-                         int64_t dq_stride, int64_t dk_stride, int64_t dv_stride, float* delta_ws, void* stream);
+                         int64_t dq_stride, int64_t dk_stride, int64_t dv_stride, float* delta_ws,
+                         float dropout_p, uint64_t dropout_seed, void* stream);
 
 /* ---- K4: decode step ---------------------------------------------------------------------------
  * One query row per (sequence, head) against a KV cache.  Replaces
@@ -251,6 +253,22 @@ int acai_gather_rows(const void* src, int32_t dtype, const int64_t* index, int32
                      int32_t out_dtype, void* stream);
 int acai_mae_loss_bwd(const void* pred, int32_t pred_dtype, const float* target, const uint8_t* loss_mask, int32_t rows,
                       int32_t feats, const float* scale, void* dpred, int32_t dpred_dtype, void* stream);
+
+/* Attention-probability dropout (nn.MultiheadAttention(dropout=p) in training mode): acai_attn_varlen_fwd / _bwd take
+ * (dropout_p, dropout_seed); P is masked and scaled by 1/(1-p) before P V, the softmax normaliser is unaffected.  The
+ * mask is a pure function of (seed, head, global query row, key position) that forward and backward regenerate;
+ * acai_attn_dropout_mask writes it out (uint8 keep[heads, total_q, max_k]) for tests. */
+int acai_attn_dropout_mask(float dropout_p, uint64_t dropout_seed, int32_t heads, int32_t total_q, int32_t max_k,
+                           uint8_t* keep, void* stream);
+
+/* Dropout on hidden states (nn.Dropout inside nn.TransformerEncoder/DecoderLayer and the transition head, training mode):
+ *   out[i] = residual[i] + (keep(seed, i) ? x[i] / (1 - p) : 0)      (residual may be NULL)
+ * keep() is a counter-based hash of (seed, element index) - torch's Philox stream cannot be reproduced, the keep rate
+ * and the 1/(1-p) scaling are nn.Dropout's.  The backward is the same call on dY with the same seed; no mask is stored.
+ * acai_dropout_mask writes the keep decisions (uint8) for tests. */
+int acai_dropout(const void* x, int32_t dtype, const void* residual, int32_t res_dtype, int64_t n, float p, uint64_t seed,
+                 void* out, int32_t out_dtype, void* stream);
+int acai_dropout_mask(int64_t n, float p, uint64_t seed, uint8_t* keep, void* stream);
 
 /* Scheduled sampling (ScheduledSamplingViTOMR.sample_and_mix_seqs, models.py:801-817).
  *   acai_gumbel_softmax_fwd : F.gumbel_softmax(logits, tau, hard) with caller-supplied Gumbel noise [rows, vocab] fp32;

@@ -487,3 +487,122 @@ def test_scheduled_sampling_step_golden(golden, golden_grads, mode):
     with torch.no_grad():
         p_eval, _ = vit.forward_eval(list(zip(cuda_list(g["imgs"]), cuda_list(g["lmx"]))))
     assert p_eval.shape == pred.shape
+
+
+# ------------------------------------------------------------------------------------------ dropout
+def test_hidden_dropout_matches_exported_mask_and_rate():
+    p, seed = 0.1, 0x1234_5678_9ABC_DEF0
+    x = rnd(1000, 771, seed=91).requires_grad_(True)            # odd element count: last hash pair is half used
+    res = rnd(1000, 771, seed=92).requires_grad_(True)
+    keep = ops.dropout_mask(x.numel(), p, seed, DEV).view(x.shape)
+    y = F._Dropout.apply(x, res, p, seed)
+    dy = rnd(1000, 771, seed=93)
+    y.backward(dy)
+    assert torch.allclose(y, res + keep * x / (1 - p), atol=1e-6)
+    assert torch.allclose(x.grad, keep * dy / (1 - p), atol=1e-6) and torch.equal(res.grad, dy)
+    rate = 1.0 - keep.float().mean().item()
+    assert abs(rate - p) < 4 * math.sqrt(p * (1 - p) / x.numel()) + 1e-5, rate        # 4 sigma + threshold quantisation
+    other = ops.dropout_mask(x.numel(), p, ops.DropoutState.next_seed(), DEV).view(x.shape)
+    agree = (other == keep).float().mean().item()
+    assert abs(agree - (p * p + (1 - p) ** 2)) < 0.01                                # independent masks for different seeds
+    # rows / columns are not correlated
+    assert abs(keep.float().mean(0).std().item() - math.sqrt(p * (1 - p) / 1000)) < 0.003
+    xb = rnd(64, 256, seed=94, dtype=torch.bfloat16)
+    kb = ops.dropout_mask(xb.numel(), 0.05, 7, DEV).view(xb.shape)
+    assert torch.equal(ops.dropout(xb, 0.05, 7), (kb * xb.float() / 0.95).bfloat16())
+
+
+def masked_attention_reference(q, k, v, lens_q, lens_k, H, causal, keep, p):
+    """fp32 torch attention with an explicit probability-dropout mask keep[h, q_global, k_local]."""
+    outs, oq, ok = [], 0, 0
+    d = q.shape[1] // H
+    for lq, lk in zip(lens_q, lens_k):
+        qs = q[oq:oq + lq].view(lq, H, d).transpose(0, 1)
+        ks = k[ok:ok + lk].view(lk, H, d).transpose(0, 1)
+        vs = v[ok:ok + lk].view(lk, H, d).transpose(0, 1)
+        s = qs @ ks.transpose(1, 2) / math.sqrt(d)
+        if causal:
+            s = s.masked_fill(torch.ones(lq, lk, dtype=torch.bool, device=s.device).triu(1 + lk - lq), float("-inf"))
+        pr = torch.softmax(s, -1) * keep[:, oq:oq + lq, :lk] / (1 - p)
+        outs.append((pr @ vs).transpose(0, 1).reshape(lq, H * d))
+        oq, ok = oq + lq, ok + lk
+    return torch.cat(outs)
+
+
+@pytest.mark.parametrize("H,d,dtype", [(4, 8, torch.float32), (3, 12, torch.float32), (2, 32, torch.bfloat16), (2, 64, torch.bfloat16),
+                                       (16, 64, torch.bfloat16), (2, 64, torch.float32)])
+@pytest.mark.parametrize("causal", [False, True])
+def test_attention_probability_dropout_fwd_bwd(H, d, dtype, causal):
+    """Forward and both backward passes regenerate the same mask (exported by acai_attn_dropout_mask): exact comparison
+    against masked fp32 attention, tensor-core (bf16, d 32/64) and SIMT kernels alike."""
+    p, seed = 0.1, 0xACA1_0000_0000_0042
+    lens = [1, 70, 129, 33, 200]
+    pk = Packed(lens, DEV)
+    D = H * d
+    qkv = rnd(pk.total, 3 * D, seed=95, dtype=dtype, scale=0.7).requires_grad_(True)
+    dout = rnd(pk.total, D, seed=96, dtype=dtype)
+    out = F.self_attention(qkv, pk, H, d, causal, dropout_p=p, dropout_seed=seed)
+    out.backward(dout)
+    keep = ops.attn_dropout_mask(p, seed, H, pk.total, pk.max_len, DEV).float()
+    rate = 1.0 - keep.mean().item()
+    assert abs(rate - p) < 0.005, rate
+    ref_in = qkv.detach().float().requires_grad_(True)
+    ref = masked_attention_reference(ref_in[:, :D], ref_in[:, D:2 * D], ref_in[:, 2 * D:], lens, lens, H, causal, keep, p)
+    ref.backward(dout.float())
+    tol = 3e-5 if dtype == torch.float32 else 2e-2
+    assert rel_err(out, ref) < tol
+    for i, name in enumerate("qkv"):
+        assert rel_err(qkv.grad[:, i * D:(i + 1) * D], ref_in.grad[:, i * D:(i + 1) * D]) < tol, name
+
+
+@pytest.mark.parametrize("H,d,dtype", [(4, 12, torch.float32), (3, 32, torch.bfloat16), (16, 64, torch.bfloat16)])
+def test_cross_attention_probability_dropout(H, d, dtype):
+    p, seed = 0.25, 99
+    lens_q, lens_k = [5, 64, 1, 100], [130, 7, 300, 64]
+    pq, pk = Packed(lens_q, DEV), Packed(lens_k, DEV)
+    D = H * d
+    q = rnd(pq.total, D, seed=97, dtype=dtype, scale=0.7).requires_grad_(True)
+    kv = rnd(pk.total, 2 * D, seed=98, dtype=dtype, scale=0.7).requires_grad_(True)
+    dout = rnd(pq.total, D, seed=99, dtype=dtype)
+    out = F.cross_attention(q, kv, pq, pk, H, d, dropout_p=p, dropout_seed=seed)
+    out.backward(dout)
+    keep = ops.attn_dropout_mask(p, seed, H, pq.total, pk.max_len, DEV).float()
+    qr, kvr = q.detach().float().requires_grad_(True), kv.detach().float().requires_grad_(True)
+    ref = masked_attention_reference(qr, kvr[:, :D], kvr[:, D:], lens_q, lens_k, H, False, keep, p)
+    ref.backward(dout.float())
+    tol = 3e-5 if dtype == torch.float32 else 2e-2
+    assert rel_err(out, ref) < tol and rel_err(q.grad, qr.grad) < tol and rel_err(kv.grad, kvr.grad) < tol
+
+
+def test_training_mode_with_reference_dropout_rates():
+    """The reference's recipe (encoder 0.05, transition head 0.05, decoder 0.1; omr_teacher_force_train.py:43-46) runs in
+    train mode: finite loss and gradients, a different mask every step, eval mode unaffected and deterministic."""
+    from acai_omr_b200 import synth
+    ops.DropoutState.manual_seed(1)
+    enc = M.FineTuneOMREncoder(16, 12, 40, 2, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.05)
+    dec = M.OMRDecoder(48, VOCAB, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.1)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=128, transition_head_dropout=0.05)
+    synth.rerandomise_(vit, 6)
+    vit = vit.to(DEV).train()
+    imgs = [synth.synth_system(h, w, i).to(DEV) for i, (h, w) in enumerate([(64, 160), (32, 320), (96, 96)])]
+    batch = list(zip(imgs, [synth.synth_lmx(L, i).to(DEV) for i, L in enumerate([20, 33, 12])]))
+    losses = []
+    for _ in range(3):
+        vit.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            pred, tgt = vit(batch)
+            loss = M.OMRCELoss(vit.decoder.pad_idx)(pred, tgt)
+        loss.backward()
+        losses.append(float(loss.detach()))
+        assert all(bool(torch.isfinite(p.grad).all()) for p in vit.parameters() if p.grad is not None)
+    assert len(set(losses)) == 3, losses                      # fresh masks per step
+    vit.eval()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        a, _ = vit(batch)
+        b, _ = vit(batch)
+    assert torch.equal(a, b)
+    ops.DropoutState.manual_seed(1)
+    vit.train()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        first = float(M.OMRCELoss(vit.decoder.pad_idx)(*vit(batch)).detach())
+    assert first == losses[0]                                  # manual_seed replays the run

@@ -52,38 +52,95 @@ __device__ __forceinline__ float gelu_grad(float v) {
   const float pdf = 0.39894228040143267794f * __expf(-0.5f * v * v);
   return cdf + v * pdf;
 }
-__global__ void gelu_fwd_kernel(const void* __restrict__ z, int dt, void* __restrict__ out, int out_dt, int64_t n) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    st_from_float(out, i, out_dt, gelu_erf(ld_as_float(z, i, dt)));
+// Both take an optional dropout (thr != 0) applied to the activation: out = keep(i) * gelu(z) / (1 - p), the mask being a
+// function of (seed, i) only, so the backward regenerates it (nn.Dropout after the activation of the feed-forward block).
+__global__ void gelu_fwd_kernel(const void* __restrict__ z, int dt, void* __restrict__ out, int out_dt, int64_t n, uint32_t thr,
+                                float rp, uint64_t seed) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float v = gelu_erf(ld_as_float(z, i, dt));
+    if (thr) v = dropout_keep(seed, (uint64_t)i, thr) ? v * rp : 0.0f;
+    st_from_float(out, i, out_dt, v);
+  }
 }
 __global__ void gelu_bwd_kernel(const void* __restrict__ dy, int dy_dt, const void* __restrict__ z, int z_dt,
-                                void* __restrict__ dz, int dz_dt, int64_t n) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    st_from_float(dz, i, dz_dt, ld_as_float(dy, i, dy_dt) * gelu_grad(ld_as_float(z, i, z_dt)));
+                                void* __restrict__ dz, int dz_dt, int64_t n, uint32_t thr, float rp, uint64_t seed) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float g = ld_as_float(dy, i, dy_dt) * gelu_grad(ld_as_float(z, i, z_dt));
+    if (thr) g = dropout_keep(seed, (uint64_t)i, thr) ? g * rp : 0.0f;
+    st_from_float(dz, i, dz_dt, g);
+  }
+}
+// keep factors (rp or 0) of the 8 consecutive elements 8*i8 .. 8*i8+7 = hash pairs 4*i8 .. 4*i8+3
+__device__ __forceinline__ void dropout_factors8(uint64_t seed, int64_t i8, uint32_t thr, float rp, float (&f)[8]) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t bits = dropout_bits(seed, (uint64_t)(4 * i8 + k));
+    f[2 * k] = (bits & 0xffffu) >= thr ? rp : 0.0f;
+    f[2 * k + 1] = (bits >> 16) >= thr ? rp : 0.0f;
+  }
 }
 // bf16 fast paths: 8 elements (16 bytes) per thread per step
 __global__ void __launch_bounds__(256)
-gelu_fwd_bf16x8_kernel(const uint4* __restrict__ z, uint4* __restrict__ out, int64_t n8) {
+gelu_fwd_bf16x8_kernel(const uint4* __restrict__ z, uint4* __restrict__ out, int64_t n8, uint32_t thr, float rp, uint64_t seed) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
     uint4 u = z[i];
     __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+    float m[8];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { const float2 f = __bfloat1622float2(h[k]); h[k] = __floats2bfloat162_rn(gelu_erf(f.x), gelu_erf(f.y)); }
+    for (int k = 0; k < 8; ++k) m[k] = 1.0f;
+    if (thr) dropout_factors8(seed, i, thr, rp, m);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = __bfloat1622float2(h[k]);
+      h[k] = __floats2bfloat162_rn(gelu_erf(f.x) * m[2 * k], gelu_erf(f.y) * m[2 * k + 1]);
+    }
     out[i] = u;
   }
 }
 __global__ void __launch_bounds__(256)
-gelu_bwd_bf16x8_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ z, uint4* __restrict__ dz, int64_t n8) {
+gelu_bwd_bf16x8_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ z, uint4* __restrict__ dz, int64_t n8, uint32_t thr,
+                       float rp, uint64_t seed) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
     uint4 u = z[i], g = dy[i];
     __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
     const __nv_bfloat162* gh = reinterpret_cast<const __nv_bfloat162*>(&g);
+    float m[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m[k] = 1.0f;
+    if (thr) dropout_factors8(seed, i, thr, rp, m);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float2 f = __bfloat1622float2(h[k]), d = __bfloat1622float2(gh[k]);
-      h[k] = __floats2bfloat162_rn(d.x * gelu_grad(f.x), d.y * gelu_grad(f.y));
+      h[k] = __floats2bfloat162_rn(d.x * gelu_grad(f.x) * m[2 * k], d.y * gelu_grad(f.y) * m[2 * k + 1]);
     }
     dz[i] = u;
+  }
+}
+// residual + dropout(x), bf16, 8 elements per thread
+__global__ void __launch_bounds__(256)
+dropout_bf16x8_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint4* __restrict__ out, int64_t n8, uint32_t thr,
+                      float rp, uint64_t seed) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    uint4 u = x[i];
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+    float m[8];
+    dropout_factors8(seed, i, thr, rp, m);
+    if (res) {
+      const uint4 r = res[i];
+      const __nv_bfloat162* rh = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = __bfloat1622float2(h[k]), g = __bfloat1622float2(rh[k]);
+        h[k] = __floats2bfloat162_rn(fmaf(f.x, m[2 * k], g.x), fmaf(f.y, m[2 * k + 1], g.y));
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = __bfloat1622float2(h[k]);
+        h[k] = __floats2bfloat162_rn(f.x * m[2 * k], f.y * m[2 * k + 1]);
+      }
+    }
+    out[i] = u;
   }
 }
 
@@ -374,29 +431,36 @@ extern "C" int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t row
   return launch_status("colsum_final");
 }
 
-extern "C" int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, void* stream) {
-  ACAI_CHECK_ARG(z && out && n >= 0 && dtype_valid(z_dtype) && dtype_valid(out_dtype), "acai_gelu_fwd: bad argument");
+extern "C" int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, float dropout_p,
+                             uint64_t dropout_seed, void* stream) {
+  ACAI_CHECK_ARG(z && out && n >= 0 && dtype_valid(z_dtype) && dtype_valid(out_dtype) && dropout_p >= 0.0f && dropout_p < 1.0f,
+                 "acai_gelu_fwd: bad argument");
   if (n == 0) return ACAI_OK;
+  const uint32_t thr = dropout_threshold(dropout_p);
+  const float rp = 1.0f / (1.0f - dropout_p);
   if (z_dtype == ACAI_BF16 && out_dtype == ACAI_BF16 && n % 8 == 0 && !((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(out)) & 15)) {
-    gelu_fwd_bf16x8_kernel<<<grid_for(n / 8), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const uint4*>(z), reinterpret_cast<uint4*>(out), n / 8);
+    gelu_fwd_bf16x8_kernel<<<grid_for(n / 8), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const uint4*>(z), reinterpret_cast<uint4*>(out), n / 8,
+                                                                            thr, rp, dropout_seed);
     return launch_status("gelu_fwd");
   }
-  gelu_fwd_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(z, z_dtype, out, out_dtype, n);
+  gelu_fwd_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(z, z_dtype, out, out_dtype, n, thr, rp, dropout_seed);
   return launch_status("gelu_fwd");
 }
 
 extern "C" int acai_gelu_bwd(const void* dy, int32_t dy_dtype, const void* z, int32_t z_dtype, void* dz, int32_t dz_dtype,
-                             int64_t n, void* stream) {
-  ACAI_CHECK_ARG(dy && z && dz && n >= 0 && dtype_valid(dy_dtype) && dtype_valid(z_dtype) && dtype_valid(dz_dtype),
-                 "acai_gelu_bwd: bad argument");
+                             int64_t n, float dropout_p, uint64_t dropout_seed, void* stream) {
+  ACAI_CHECK_ARG(dy && z && dz && n >= 0 && dtype_valid(dy_dtype) && dtype_valid(z_dtype) && dtype_valid(dz_dtype) &&
+                 dropout_p >= 0.0f && dropout_p < 1.0f, "acai_gelu_bwd: bad argument");
   if (n == 0) return ACAI_OK;
+  const uint32_t thr = dropout_threshold(dropout_p);
+  const float rp = 1.0f / (1.0f - dropout_p);
   if (dy_dtype == ACAI_BF16 && z_dtype == ACAI_BF16 && dz_dtype == ACAI_BF16 && n % 8 == 0 &&
       !((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(dz)) & 15)) {
     gelu_bwd_bf16x8_kernel<<<grid_for(n / 8), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(z),
-                                                                            reinterpret_cast<uint4*>(dz), n / 8);
+                                                                            reinterpret_cast<uint4*>(dz), n / 8, thr, rp, dropout_seed);
     return launch_status("gelu_bwd");
   }
-  gelu_bwd_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(dy, dy_dtype, z, z_dtype, dz, dz_dtype, n);
+  gelu_bwd_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(dy, dy_dtype, z, z_dtype, dz, dz_dtype, n, thr, rp, dropout_seed);
   return launch_status("gelu_bwd");
 }
 
@@ -658,6 +722,14 @@ extern "C" int acai_dropout(const void* x, int32_t dtype, const void* residual, 
   ACAI_CHECK_ARG(x && out && n >= 0 && p >= 0.0f && p < 1.0f && dtype_valid(dtype) && dtype_valid(out_dtype) &&
                  (!residual || dtype_valid(res_dtype)), "acai_dropout: bad argument");
   if (n == 0) return ACAI_OK;
+  auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (dtype == ACAI_BF16 && out_dtype == ACAI_BF16 && (!residual || res_dtype == ACAI_BF16) && n % 8 == 0 && al(x) && al(out) &&
+      (!residual || al(residual))) {
+    acai::dropout_bf16x8_kernel<<<grid_for(n / 8), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(residual), reinterpret_cast<uint4*>(out), n / 8,
+        dropout_threshold(p), 1.0f / (1.0f - p), seed);
+    return launch_status("dropout");
+  }
   acai::dropout_kernel<<<grid_for((n + 1) / 2), 256, 0, (cudaStream_t)stream>>>(x, dtype, residual, res_dtype, n, dropout_threshold(p),
                                                                                1.0f / (1.0f - p), seed, out, out_dtype);
   return launch_status("dropout");

@@ -56,7 +56,7 @@ class _Linear(torch.autograd.Function):
     In training the GELU is not fused into the GEMM epilogue: the pre-activation z is kept for the backward."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, act, out_dtype, rows):
+    def forward(ctx, x, weight, bias, residual, act, out_dtype, rows, dropout_p=0.0, dropout_seed=0):
         dt = x.dtype
         K = x.shape[-1]
         x2 = x.reshape(-1, K)
@@ -70,11 +70,12 @@ class _Linear(torch.autograd.Function):
             if residual is not None:
                 raise ops.AcaiError("linear: GELU + residual is not used by the model")
             z = ops.linear(x2, w, b, out_dtype=dt)
-            y = ops.gelu(z, out_dtype=out_dtype)
+            y = ops.gelu(z, out_dtype=out_dtype, dropout_p=dropout_p, dropout_seed=dropout_seed)
         else:
             y = ops.linear(x2, w, b, residual=residual.detach() if residual is not None else None, out_dtype=out_dtype)
         ctx.save_for_backward(x2, weight, z)
         ctx.rows, ctx.x_shape, ctx.has_bias, ctx.bias_ref = rows, x.shape, bias is not None, bias
+        ctx.drop = (dropout_p, dropout_seed)
         ctx.res_meta = (residual.shape, residual.dtype) if residual is not None else None
         return y.view(*x.shape[:-1], y.shape[-1])
 
@@ -85,7 +86,7 @@ class _Linear(torch.autograd.Function):
         N = dy.shape[-1]
         dy2 = dy.reshape(-1, N)
         if z is not None:
-            dz = ops.gelu_bwd(dy2, z, out_dtype=dt)
+            dz = ops.gelu_bwd(dy2, z, out_dtype=dt, dropout_p=ctx.drop[0], dropout_seed=ctx.drop[1])
         else:
             dz = dy2 if dy2.dtype == dt else dy2.to(dt)
             if not dz.is_contiguous():
@@ -118,16 +119,21 @@ class _Linear(torch.autograd.Function):
             dres = dy.reshape(shape)
             if dres.dtype != rdt:
                 dres = dres.to(rdt)
-        return dx, dw, db, dres, None, None, None
+        return dx, dw, db, dres, None, None, None, None, None
 
 
-def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None, rows=None):
-    """act(x @ weight[rows].T + bias[rows]) + residual; `weight` / `bias` are the (fp32 master) parameters."""
+def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None, rows=None, dropout_p=0.0):
+    """dropout(act(x @ weight[rows].T + bias[rows])) + residual; `weight` / `bias` are the (fp32 master) parameters.
+    `dropout_p` > 0 (only with the GELU activation: the feed-forward block's inner nn.Dropout) is fused into the GELU kernel."""
     dt = x.dtype
+    if dropout_p > 0.0 and act != ops.ACT_GELU:
+        raise ops.AcaiError("linear: fused dropout is the GELU path's; use functional.dropout for the others")
+    seed = ops.DropoutState.next_seed() if dropout_p > 0.0 else 0
     if not needs_grad(x, weight, bias, residual):
-        return ops.linear(x, _weights().get(weight, dt, rows), _slice(bias, rows), act=act, residual=residual,
-                          out_dtype=out_dtype or dt)
-    return _Linear.apply(x, weight, bias, residual, act, out_dtype or dt, rows)
+        y = ops.linear(x, _weights().get(weight, dt, rows), _slice(bias, rows), act=act, residual=residual,
+                       out_dtype=out_dtype or dt)
+        return ops.dropout(y, dropout_p, seed) if dropout_p > 0.0 else y
+    return _Linear.apply(x, weight, bias, residual, act, out_dtype or dt, rows, dropout_p, seed)
 
 
 # ------------------------------------------------------------------------------------------ LayerNorm

@@ -230,9 +230,8 @@ class TransformerEncoderLayer(nn.Module):
 def _mlp_residual(layer, x, dt):
     """x + dropout2(linear2(dropout(gelu(linear1(x)))))  (the feed-forward block of nn.Transformer*Layer, post-norm)."""
     p = layer.dropout_p if layer.training else 0.0
-    h = F.linear(x, layer.linear1.weight, layer.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+    h = F.linear(x, layer.linear1.weight, layer.linear1.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=p)
     if p > 0.0:
-        h = F.dropout(h, p, True)
         return F.dropout(F.linear(h, layer.linear2.weight, layer.linear2.bias, out_dtype=dt), p, True, residual=x)
     return F.linear(h, layer.linear2.weight, layer.linear2.bias, residual=x, out_dtype=dt)
 
@@ -353,9 +352,7 @@ def gelu_mlp_head(x, lin_a: Linear, lin_b: Linear, out_dtype=None, dropout_p=0.0
     dt = compute_dtype()
     if x.dtype != dt:
         x = x.to(dt)
-    h = F.linear(x, lin_a.weight, lin_a.bias, act=ops.ACT_GELU, out_dtype=dt)
-    if dropout_p > 0.0:
-        h = F.dropout(h, dropout_p, True)
+    h = F.linear(x, lin_a.weight, lin_a.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=dropout_p)
     return F.linear(h, lin_b.weight, lin_b.bias, out_dtype=out_dtype or dt)
 
 

@@ -463,19 +463,22 @@ def colsum(x, out=None, accumulate=False):
     return out
 
 
-def gelu(z, out_dtype=None):
+def gelu(z, out_dtype=None, dropout_p=0.0, dropout_seed=0):
+    """dropout(gelu(z)) - exact-erf GELU, optional fused nn.Dropout (acai_gelu_fwd)."""
     _cuda(z)
     z = z.contiguous()
     out = torch.empty(z.shape, dtype=out_dtype or z.dtype, device=z.device)
-    _call("acai_gelu_fwd", _lib.load().acai_gelu_fwd, _p(z), _dt(z), _p(out), _dt(out), z.numel(), _stream())
+    _call("acai_gelu_fwd", _lib.load().acai_gelu_fwd, _p(z), _dt(z), _p(out), _dt(out), z.numel(), float(dropout_p),
+          C.c_uint64(dropout_seed), _stream())
     return out
 
 
-def gelu_bwd(dy, z, out_dtype=None):
+def gelu_bwd(dy, z, out_dtype=None, dropout_p=0.0, dropout_seed=0):
     _cuda(dy, z)
     dy, z = dy.contiguous(), z.contiguous()
     dz = torch.empty(z.shape, dtype=out_dtype or z.dtype, device=z.device)
-    _call("acai_gelu_bwd", _lib.load().acai_gelu_bwd, _p(dy), _dt(dy), _p(z), _dt(z), _p(dz), _dt(dz), z.numel(), _stream())
+    _call("acai_gelu_bwd", _lib.load().acai_gelu_bwd, _p(dy), _dt(dy), _p(z), _dt(z), _p(dz), _dt(dz), z.numel(), float(dropout_p),
+          C.c_uint64(dropout_seed), _stream())
     return dz
 
 

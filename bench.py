@@ -315,8 +315,9 @@ def run_train(args, rank, world, device, kind):
     """One data-parallel optimisation step per timed iteration: forward + loss + backward on this rank's shard
     (TRAIN_SYSTEMS systems, bf16 autocast), ONE NCCL all-reduce of the flat fp32 gradient buffer, fused AdamW.
     kind = "tf": TeacherForcedViTOMR (12-layer 768d encoder fully fine-tuned + 12-layer 1024d decoder) + OMRCELoss;
-    kind = "mae": MAE (mask ratio 0.75, 12-layer encoder + 8-layer 512d pixel decoder) + MAELoss.  Dropout 0 (the kernels
-    implement the deterministic path)."""
+    kind = "mae": MAE (mask ratio 0.75, 12-layer encoder + 8-layer 512d pixel decoder) + MAELoss (the reference's MAE has no
+    dropout).  The teacher-forced model runs with the reference's dropout rates (encoder 0.05, transition head 0.05, decoder
+    0.1; omr_teacher_force_train.py:43-46), hidden-state and attention-probability dropout both active."""
     from acai_omr_b200 import layers, ops, synth, train
     from acai_omr_b200.models import models as M
     n = TRAIN_SYSTEMS
@@ -324,10 +325,10 @@ def run_train(args, rank, world, device, kind):
     imgs = [synth.synth_system(h, w, rank * n + i).to(device) for i, (h, w) in enumerate(synth.system_shapes(n))]
     lens = [(t.shape[-2] // 16) * (t.shape[-1] // 16) for t in imgs]
     if kind == "tf":
-        enc = M.FineTuneOMREncoder(**encoder_kwargs(), transformer_dropout=0.0)
+        enc = M.FineTuneOMREncoder(**encoder_kwargs(), transformer_dropout=0.05)
         dec = M.OMRDecoder(1536, M.default_vocab_path(), num_layers=DEC_LAYERS, hidden_dim=DEC_D, num_heads=DEC_H,
-                           mlp_dim=DEC_MLP, transformer_dropout=0.0)
-        model = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dropout=0.0)
+                           mlp_dim=DEC_MLP, transformer_dropout=0.1)
+        model = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dropout=0.05)
         synth.rerandomise_(model, 1)
         model = model.to(device).train()
         tgt_lens = synth.lmx_lengths(n)
@@ -338,7 +339,7 @@ def run_train(args, rank, world, device, kind):
         work = {"lmx_tokens_per_gpu": sum(tgt_lens) - n}
         flops = 3.0 * (synth.encoder_flops(lens) + synth.decoder_flops([t - 1 for t in tgt_lens], lens)
                        + 2.0 * sum(lens) * (768 * 4096 + 4096 * 1024))
-        name = "configs[3]: teacher-forced ViTOMR fwd/bwd + grad all-reduce + AdamW"
+        name = "configs[3]: teacher-forced ViTOMR fwd/bwd + grad all-reduce + AdamW, dropout 0.05 / 0.05 / 0.1 as the reference trains"
     else:
         model = M.MAE(0.75, 16, 60, 200)
         synth.rerandomise_(model, 2)

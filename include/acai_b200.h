@@ -236,9 +236,10 @@ int acai_transpose(const void* in, int32_t dtype, int64_t ld_in, int32_t rows, i
 size_t acai_colsum_workspace_bytes(int32_t rows, int32_t cols);
 int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t rows, int32_t cols, float* out, int32_t accumulate,
                 void* workspace, size_t workspace_bytes, void* stream);
-int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, void* stream);
+int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, float dropout_p,
+                  uint64_t dropout_seed, void* stream);     /* out = dropout(gelu(z)): the feed-forward block's nn.Dropout fused */
 int acai_gelu_bwd(const void* dy, int32_t dy_dtype, const void* z, int32_t z_dtype, void* dz, int32_t dz_dtype, int64_t n,
-                  void* stream);
+                  float dropout_p, uint64_t dropout_seed, void* stream);
 size_t acai_layernorm_bwd_workspace_bytes(int32_t rows, int32_t cols);
 int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* x, int32_t x_dtype, const void* residual,
                        int32_t res_dtype, const float* gamma, float eps, void* dv, int32_t dv_dtype,

@@ -1,5 +1,6 @@
 """Full-size training steps on one B200 (bf16 autocast, random-init weights, synthetic systems):
-    python profiles/prof_train.py tf  [systems]     teacher-forced ViTOMR (12+12 layers) + OMRCELoss + AdamW
+    python profiles/prof_train.py tf  [systems]     teacher-forced ViTOMR (12+12 layers) + OMRCELoss + AdamW, reference dropout rates
+    python profiles/prof_train.py tf0 [systems]     the same with every dropout 0 (the parity configuration)
     python profiles/prof_train.py mae [systems]     MAE pre-training (12-layer encoder on 25 % + 8-layer decoder) + AdamW
 Prints ms/step and a per-entry-point breakdown (CUDA events around every launch of the C-ABI)."""
 import os
@@ -13,10 +14,11 @@ from acai_omr_b200 import ops, synth, train  # noqa: E402
 from acai_omr_b200.models import models as M  # noqa: E402
 
 
-def build_tf():
-    enc = M.FineTuneOMREncoder(16, 60, 200, 12, transformer_dropout=0.0)
-    dec = M.OMRDecoder(1536, M.default_vocab_path(), num_layers=12, transformer_dropout=0.0)
-    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dropout=0.0)
+def build_tf(dropout=True):
+    pe, pd = (0.05, 0.1) if dropout else (0.0, 0.0)         # the reference's rates (omr_teacher_force_train.py:43-46)
+    enc = M.FineTuneOMREncoder(16, 60, 200, 12, transformer_dropout=pe)
+    dec = M.OMRDecoder(1536, M.default_vocab_path(), num_layers=12, transformer_dropout=pd)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dropout=pe)
     synth.rerandomise_(vit, 1)
     return vit.cuda().train()
 
@@ -31,8 +33,8 @@ def main():
     kind = sys.argv[1] if len(sys.argv) > 1 else "tf"
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 64
     imgs = [synth.synth_system(h, w, i).cuda() for i, (h, w) in enumerate(synth.system_shapes(n))]
-    if kind == "tf":
-        model = build_tf()
+    if kind in ("tf", "tf0"):
+        model = build_tf(dropout=kind == "tf")
         batch = list(zip(imgs, [synth.synth_lmx(L, i).cuda() for i, L in enumerate(synth.lmx_lengths(n))]))
         groups, _ = model.create_fine_tune_param_groups(1e-4, 1e-5, 0.9)
         tr = train.FlatTrainer(model, groups)

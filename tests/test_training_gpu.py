@@ -606,3 +606,27 @@ def test_training_mode_with_reference_dropout_rates():
     with torch.autocast("cuda", dtype=torch.bfloat16):
         first = float(M.OMRCELoss(vit.decoder.pad_idx)(*vit(batch)).detach())
     assert first == losses[0]                                  # manual_seed replays the run
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1.5e-2)])
+def test_gelu_linear_with_fused_dropout(dtype, tol):
+    """Linear -> GELU -> Dropout as one autograd node (dropout fused into the GELU kernels, mask regenerated in the backward)."""
+    ops.DropoutState.manual_seed(5)
+    seed = ops.DropoutState.next_seed()
+    ops.DropoutState.manual_seed(5)                      # F.linear will draw the same seed
+    M_, N, K, p = 300, 256, 128, 0.2
+    w = (rnd(N, K, seed=101) / math.sqrt(K)).requires_grad_(True)
+    b = (0.1 * rnd(N, seed=102)).requires_grad_(True)
+    x = rnd(M_, K, seed=103, dtype=dtype).requires_grad_(True)
+    dy = rnd(M_, N, seed=104, dtype=dtype)
+    y = F.linear(x, w, b, act=ops.ACT_GELU, dropout_p=p)
+    y.backward(dy)
+    keep = ops.dropout_mask(M_ * N, p, seed, DEV).view(M_, N).float()
+    xr, wr, br = x.detach().float().requires_grad_(True), w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    ws = wr if dtype == torch.float32 else wr.detach().bfloat16().float() + (wr - wr.detach())
+    z = xr @ ws.t() + br
+    if dtype == torch.bfloat16:
+        z = z.detach().bfloat16().float() + (z - z.detach())      # the kept pre-activation is bf16
+    yr = torch.nn.functional.gelu(z) * keep / (1 - p)
+    yr.backward(dy.float())
+    assert rel_err(y, yr) < tol and rel_err(x.grad, xr.grad) < tol and rel_err(w.grad, wr.grad) < tol and rel_err(b.grad, br.grad) < tol

@@ -39,6 +39,10 @@ int linear_gemv_bf16(const void* a, int64_t lda, const void* w, int64_t ldw, con
 int linear_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res,
                    int res_dt, int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K, int act,
                    cudaStream_t st);
+int linear_gelu_train_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* z, int64_t ldz,
+                              void* h, int64_t ldh, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
+int linear_gelu_bwd_tcgen05(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
+                            int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
 
 }  // namespace acai
 
@@ -80,4 +84,28 @@ extern "C" int acai_linear_fwd(const void* a, int32_t a_dtype, int64_t lda, cons
     if (rc != ACAI_ERR_UNSUPPORTED) return rc;
   }
   return linear_simt(a, a_dtype, lda, w, w_dtype, ldw, bias, residual, res_dtype, ldr, out, out_dtype, ldo, M, N, K, act, st);
+}
+
+// Feed-forward up-projection for training: z = a @ w^T + bias and h = dropout(gelu(z)), both bf16, one GEMM.
+extern "C" int acai_linear_gelu_train(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* z,
+                                      int64_t ldz, void* h, int64_t ldh, int32_t M, int32_t N, int32_t K, float dropout_p,
+                                      uint64_t dropout_seed, void* stream) {
+  ACAI_CHECK_ARG(a && w && z && h, "acai_linear_gelu_train: null pointer");
+  ACAI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && lda >= K && ldw >= K && ldz >= N && ldh >= N, "acai_linear_gelu_train: bad sizes");
+  ACAI_CHECK_ARG(dropout_p >= 0.0f && dropout_p < 1.0f, "acai_linear_gelu_train: dropout_p must be in [0, 1)");
+  if (M == 0) return ACAI_OK;
+  return acai::linear_gelu_train_tcgen05(a, lda, w, ldw, bias, z, ldz, h, ldh, M, N, K, dropout_p, dropout_seed, (cudaStream_t)stream);
+}
+
+// Its backward through the activation: dz = (dy @ wt^T) * gelu'(z) * mask, bf16, one GEMM (wt = the [N, K] transpose
+// of the down-projection weight).
+extern "C" int acai_linear_gelu_bwd(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
+                                    int64_t ldo, int32_t M, int32_t N, int32_t K, float dropout_p, uint64_t dropout_seed,
+                                    void* stream) {
+  ACAI_CHECK_ARG(dy && wt && z && dz, "acai_linear_gelu_bwd: null pointer");
+  ACAI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && ldd >= K && ldw >= K && ldz >= N && ldo >= N, "acai_linear_gelu_bwd: bad sizes");
+  ACAI_CHECK_ARG(dropout_p >= 0.0f && dropout_p < 1.0f, "acai_linear_gelu_bwd: dropout_p must be in [0, 1)");
+  ACAI_CHECK_ARG(ldz == N || dropout_p == 0.0f, "acai_linear_gelu_bwd: the dropout mask is indexed over a dense [M, N] tensor");
+  if (M == 0) return ACAI_OK;
+  return acai::linear_gelu_bwd_tcgen05(dy, ldd, wt, ldw, z, ldz, dz, ldo, M, N, K, dropout_p, dropout_seed, (cudaStream_t)stream);
 }

@@ -28,9 +28,17 @@ constexpr int UMMA_K = 16;
 constexpr int EPI_WARPS = 8;
 constexpr int THREADS = 64 + EPI_WARPS * 32;   // 320
 
+// Training-only epilogue modes (internal; the public acai_act values are 0 / 1):
+//   ACT_GELU_TRAIN: z = acc + bias is stored (bf16) through a second tensor map AND h = dropout(gelu_erf(z)) through the
+//                   first - the feed-forward GELU (+ its nn.Dropout) without a separate elementwise pass;
+//   ACT_GELU_BWD:   out = acc * gelu'(z) * dropout_mask, z read like a bf16 residual - the backward of the same.
+constexpr int ACT_GELU_TRAIN = 2, ACT_GELU_BWD = 3;
+
 struct Epi {
   const float* bias; const void* res; int res_dt; int64_t ldr; void* out; int out_dt; int64_t ldo; int act;
   const int32_t* res_rows;   // optional gather: residual row of output row m is res_rows[m] (position embeddings)
+  void* aux; int64_t ld_aux; // ACT_GELU_TRAIN: the pre-activation output
+  uint32_t drop_thr; float drop_rp; uint64_t drop_seed;   // dropout on the activation (thr = 0: none)
 };
 
 template <int BN> constexpr int stages() { return BN >= 256 ? 4 : (BN >= 128 ? 6 : 8); }
@@ -173,13 +181,83 @@ __device__ __forceinline__ void epi_half(int act, const uint32_t (&acc)[32], con
   }
 }
 
+// Phi(z) = 0.5 (1 + erf(z / sqrt 2)) and e = exp(-z^2 / 2) for the training epilogues: Abramowitz-Stegun 7.1.26
+// (|error| < 1.5e-7, far below the bf16 output's rounding) costs two MUFU ops and ~10 FMAs, about a third of erff - the
+// epilogue warps have roughly 16 instruction slots per element before they become the GEMM's critical path.
+__device__ __forceinline__ void phi_and_pdf(float z, float& cdf, float& e) {
+  const float x = fabsf(z) * 0.70710678118654752440f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, x, 1.0f)));
+  e = __expf(-x * x);
+  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
+  const float q = 0.5f * poly * e;                     // 0.5 erfc(|z| / sqrt 2)
+  cdf = z >= 0.0f ? 1.0f - q : q;
+}
+
+// Training epilogues on 32 columns of this thread's row, 8 columns (one 16-byte staging piece) at a time:
+//   MODE 1 (ACT_GELU_TRAIN): pass 0 stages z = acc + bias, pass 1 stages h = dropout(gelu(bf16(z)));
+//   MODE 2 (ACT_GELU_BWD):   stages acc * gelu'(z) * mask with z in the (bf16) residual registers.
+// `elem0`: linear index (row * N + column, even) of the first of the 32 elements - the dropout mask's counter.
+template <int MODE>
+__device__ __forceinline__ void epi_half_train(const Epi& ep, int pass, int64_t elem0, const uint32_t (&acc)[32], const float* sb,
+                                               const ResHalf<MODE == 2 ? 1 : 0>& rb, uint8_t* srow, uint32_t sw, int piece0) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float v[8];
+    const float4 b0 = reinterpret_cast<const float4*>(sb)[2 * q], b1 = reinterpret_cast<const float4*>(sb)[2 * q + 1];
+    v[0] = __uint_as_float(acc[8 * q]) + b0.x; v[1] = __uint_as_float(acc[8 * q + 1]) + b0.y;
+    v[2] = __uint_as_float(acc[8 * q + 2]) + b0.z; v[3] = __uint_as_float(acc[8 * q + 3]) + b0.w;
+    v[4] = __uint_as_float(acc[8 * q + 4]) + b1.x; v[5] = __uint_as_float(acc[8 * q + 5]) + b1.y;
+    v[6] = __uint_as_float(acc[8 * q + 6]) + b1.z; v[7] = __uint_as_float(acc[8 * q + 7]) + b1.w;
+    bool mask = false;
+    if constexpr (MODE == 1) {
+      if (pass == 1) {
+        mask = ep.drop_thr != 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float z = __bfloat162float(__float2bfloat16_rn(v[j]));   // what the backward will read
+          float cdf, e;
+          phi_and_pdf(z, cdf, e);
+          v[j] = z * cdf;
+        }
+      }
+    } else {
+      mask = ep.drop_thr != 0;
+      const __nv_bfloat162* zh = reinterpret_cast<const __nv_bfloat162*>(&rb.v[q]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 z = __bfloat1622float2(zh[i]);
+        float cdf, e;
+        phi_and_pdf(z.x, cdf, e);
+        v[2 * i] *= fmaf(z.x * 0.39894228040143267794f, e, cdf);
+        phi_and_pdf(z.y, cdf, e);
+        v[2 * i + 1] *= fmaf(z.y * 0.39894228040143267794f, e, cdf);
+      }
+    }
+    if (mask) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t bits = dropout_bits(ep.drop_seed, (uint64_t)(elem0 >> 1) + 4 * q + k);
+        v[2 * k] *= (bits & 0xffffu) >= ep.drop_thr ? ep.drop_rp : 0.0f;
+        v[2 * k + 1] *= (bits >> 16) >= ep.drop_thr ? ep.drop_rp : 0.0f;
+      }
+    }
+    uint4 pk; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(srow + ((((uint32_t)(piece0 + q)) ^ sw) << 4)) = pk;
+  }
+}
+
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory"); }
 
 // OUT: 0 = generic epilogue (any shape/alignment), 1 = bf16 output via TMA, 2 = fp32 output via TMA.
-template <int BN, int OUT, int RES>
+// MODE: 0 = inference / plain epilogue, 1 = ACT_GELU_TRAIN (OUT 1, RES 0), 2 = ACT_GELU_BWD (OUT 1, RES 1).
+template <int BN, int OUT, int RES, int MODE = 0>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                  const __grid_constant__ CUtensorMap tma_out, Epi ep, int M, int N, int K) {
+                  const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_aux, Epi ep, int M, int N,
+                  int K) {
   constexpr int STAGES = stages<BN>();
   constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // power of two for BN in {32,64,128,256}
@@ -303,18 +381,26 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
           }
-          if (lane == 0) ptx::tma_store_wait_read<0>();   // the staging tile's previous store has been read out
-          __syncwarp();
+          constexpr int PASSES = MODE == 1 ? 2 : 1;
 #pragma unroll
-          for (int hh = 0; hh < HALVES; ++hh) {
-            epi_half<OUT_BF16, RES>(ep.act, acc[hh], sb + c * CW + hh * 32, rb[hh], srow, sw, hh * (OUT_BF16 ? 4 : 0));
-            if (c + 1 < nch) res_prefetch<RES>(ep, rrow, col0 + (c + 1) * CW + hh * 32, N, rb[hh]);
-          }
-          ptx::fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            ptx::tma_store_2d(&tma_out, stage, col0 + c * CW, row0);
-            ptx::tma_store_commit();
+          for (int ps = 0; ps < PASSES; ++ps) {
+            if (lane == 0) ptx::tma_store_wait_read<0>();   // the staging tile's previous store has been read out
+            __syncwarp();
+#pragma unroll
+            for (int hh = 0; hh < HALVES; ++hh) {
+              if constexpr (MODE == 0)
+                epi_half<OUT_BF16, RES>(ep.act, acc[hh], sb + c * CW + hh * 32, rb[hh], srow, sw, hh * (OUT_BF16 ? 4 : 0));
+              else
+                epi_half_train<MODE>(ep, ps, (int64_t)grow * N + col0 + c * CW + hh * 32, acc[hh], sb + c * CW + hh * 32, rb[hh],
+                                     srow, sw, hh * 4);
+              if (ps == PASSES - 1 && c + 1 < nch) res_prefetch<RES>(ep, rrow, col0 + (c + 1) * CW + hh * 32, N, rb[hh]);
+            }
+            ptx::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              ptx::tma_store_2d(PASSES == 2 && ps == 0 ? &tma_aux : &tma_out, stage, col0 + c * CW, row0);
+              ptx::tma_store_commit();
+            }
           }
         }
       }
@@ -409,18 +495,18 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t 
   return make_tma_2d(map, ptr, ACAI_BF16, rows, cols, ld, box_rows, box_cols);
 }
 
-template <int BN, int OUT, int RES>
-static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const Epi& ep, int M, int N,
-                          int K, cudaStream_t st) {
+template <int BN, int OUT, int RES, int MODE = 0>
+static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& taux,
+                          const Epi& ep, int M, int N, int K, cudaStream_t st) {
   static bool attr_set = false;
   constexpr size_t smem = smem_bytes<BN>();
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05<BN, OUT, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ACAI_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05<BN, OUT, RES, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_bf16_tcgen05<BN, OUT, RES><<<grid, THREADS, smem, st>>>(ta, tb, to, ep, M, N, K);
+  gemm_bf16_tcgen05<BN, OUT, RES, MODE><<<grid, THREADS, smem, st>>>(ta, tb, to, taux, ep, M, N, K);
   return launch_status("gemm_bf16_tcgen05");
 }
 
@@ -437,22 +523,38 @@ static int launch_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, c
   const bool tma_ok = N % 8 == 0 && (ep.ldo * oes) % 16 == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 &&
                       (!ep.res || ((ep.ldr * res_es) % 16 == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
   // (BN = 64 serves small / skinny problems only; its 32-column warp slabs are narrower than a 128-byte bf16 chunk)
-  if (BN < 128 || !tma_ok) return launch_variant<BN, 0, 0>(ta, tb, ta, ep, M, N, K, st);
+  const bool train_act = ep.act == ACT_GELU_TRAIN || ep.act == ACT_GELU_BWD;   // only the TMA-store epilogue has these
+  if (BN < 128 || !tma_ok) return train_act ? ACAI_ERR_UNSUPPORTED : launch_variant<BN, 0, 0>(ta, tb, ta, ta, ep, M, N, K, st);
   if constexpr (BN >= 128) {
   rc = make_tma_2d(&to, ep.out, ep.out_dt, (uint64_t)M, (uint64_t)N, (uint64_t)ep.ldo, 32, ep.out_dt == ACAI_BF16 ? 64 : 32);
   if (rc) return rc;
   const int res = !ep.res ? 0 : (ep.res_dt == ACAI_BF16 ? 1 : 2);
-  if (ep.out_dt == ACAI_BF16) {
-    if (res == 0) return launch_variant<BN, 1, 0>(ta, tb, to, ep, M, N, K, st);
-    if (res == 1) return launch_variant<BN, 1, 1>(ta, tb, to, ep, M, N, K, st);
-    return launch_variant<BN, 1, 2>(ta, tb, to, ep, M, N, K, st);
+  if (ep.act == ACT_GELU_TRAIN) {
+    if (ep.out_dt != ACAI_BF16 || res != 0 || (ep.ld_aux * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(ep.aux) & 15))
+      return ACAI_ERR_UNSUPPORTED;
+    CUtensorMap taux;
+    rc = make_tma_2d(&taux, ep.aux, ACAI_BF16, (uint64_t)M, (uint64_t)N, (uint64_t)ep.ld_aux, 32, 64);
+    if (rc) return rc;
+    return launch_variant<BN, 1, 0, 1>(ta, tb, to, taux, ep, M, N, K, st);
   }
-  if (res == 0) return launch_variant<BN, 2, 0>(ta, tb, to, ep, M, N, K, st);
-  if (res == 1) return launch_variant<BN, 2, 1>(ta, tb, to, ep, M, N, K, st);
-  return launch_variant<BN, 2, 2>(ta, tb, to, ep, M, N, K, st);
+  if (ep.act == ACT_GELU_BWD) {
+    if (ep.out_dt != ACAI_BF16 || res != 1 || ep.res_rows) return ACAI_ERR_UNSUPPORTED;
+    return launch_variant<BN, 1, 1, 2>(ta, tb, to, to, ep, M, N, K, st);
+  }
+  if (ep.out_dt == ACAI_BF16) {
+    if (res == 0) return launch_variant<BN, 1, 0>(ta, tb, to, to, ep, M, N, K, st);
+    if (res == 1) return launch_variant<BN, 1, 1>(ta, tb, to, to, ep, M, N, K, st);
+    return launch_variant<BN, 1, 2>(ta, tb, to, to, ep, M, N, K, st);
+  }
+  if (res == 0) return launch_variant<BN, 2, 0>(ta, tb, to, to, ep, M, N, K, st);
+  if (res == 1) return launch_variant<BN, 2, 1>(ta, tb, to, to, ep, M, N, K, st);
+  return launch_variant<BN, 2, 2>(ta, tb, to, to, ep, M, N, K, st);
   }
   return ACAI_ERR_UNSUPPORTED;
 }
+
+static int dispatch_tiles(const void* a, int64_t lda, const void* w, int64_t ldw, const Epi& ep, int M, int N, int K,
+                          cudaStream_t st);
 
 int linear_tcgen05_ex(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res,
                       int res_dt, int64_t ldr, const int32_t* res_rows, void* out, int out_dt, int64_t ldo, int M, int N,
@@ -461,14 +563,45 @@ int linear_tcgen05_ex(const void* a, int64_t lda, const void* w, int64_t ldw, co
   if (K % BK != 0 || lda % 8 != 0 || ldw % 8 != 0 || (reinterpret_cast<uintptr_t>(a) & 15) ||
       (reinterpret_cast<uintptr_t>(w) & 15) || M < 1 || N < 8)
     return ACAI_ERR_UNSUPPORTED;
-  Epi ep{bias, res, res_dt, ldr, out, out_dt, ldo, act, res_rows};
+  Epi ep{bias, res, res_dt, ldr, out, out_dt, ldo, act, res_rows, nullptr, 0, 0u, 1.0f, 0ull};
+  return dispatch_tiles(a, lda, w, ldw, ep, M, N, K, st);
+}
+
+static int dispatch_tiles(const void* a, int64_t lda, const void* w, int64_t ldw, const Epi& ep, int M, int N, int K,
+                          cudaStream_t st) {
   // widest N tile that still yields about one tile per SM; skinny decode-step problems get narrow tiles so that
   // more SMs stream the weight matrix
   const int m_tiles = (M + BM - 1) / BM, sms = num_sms();
   auto tiles = [&](int bn) { return m_tiles * ((N + bn - 1) / bn); };
   if (N > 128 && tiles(256) >= sms) return launch_gemm<256>(a, lda, w, ldw, ep, M, N, K, st);
-  if (N > 64 && tiles(128) >= sms) return launch_gemm<128>(a, lda, w, ldw, ep, M, N, K, st);
+  if ((N > 64 && tiles(128) >= sms) || ep.act >= ACT_GELU_TRAIN) return launch_gemm<128>(a, lda, w, ldw, ep, M, N, K, st);
   return launch_gemm<64>(a, lda, w, ldw, ep, M, N, K, st);
+}
+
+static bool gemm_operands_ok(const void* a, int64_t lda, const void* w, int64_t ldw, int M, int N, int K) {
+  return !(K % BK != 0 || lda % 8 != 0 || ldw % 8 != 0 || (reinterpret_cast<uintptr_t>(a) & 15) ||
+           (reinterpret_cast<uintptr_t>(w) & 15) || M < 1 || N < 8);
+}
+
+// z = a @ w^T + bias (bf16, kept for the backward) and h = dropout(gelu(z)) from ONE pass over the accumulators.
+int linear_gelu_train_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* z, int64_t ldz,
+                              void* h, int64_t ldh, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st) {
+  if (!gemm_operands_ok(a, lda, w, ldw, M, N, K) || N % 2 != 0) return ACAI_ERR_UNSUPPORTED;
+  const uint32_t thr = dropout_threshold(dropout_p);
+  Epi ep{bias, nullptr, ACAI_BF16, 0, h, ACAI_BF16, ldh, ACT_GELU_TRAIN, nullptr, z, ldz, thr, thr ? 1.0f / (1.0f - dropout_p) : 1.0f,
+         seed};
+  if (ldh != N && thr) return ACAI_ERR_UNSUPPORTED;   // the dropout mask is indexed row * N + col like acai_gelu_fwd on a dense tensor
+  return dispatch_tiles(a, lda, w, ldw, ep, M, N, K, st);
+}
+
+// dz = (dh @ wt^T) * gelu'(z) * mask: the feed-forward's second GEMM backward with the GELU backward in its epilogue.
+int linear_gelu_bwd_tcgen05(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
+                            int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st) {
+  if (!gemm_operands_ok(dy, ldd, wt, ldw, M, N, K) || N % 2 != 0) return ACAI_ERR_UNSUPPORTED;
+  const uint32_t thr = dropout_threshold(dropout_p);
+  Epi ep{nullptr, z, ACAI_BF16, ldz, dz, ACAI_BF16, ldo, ACT_GELU_BWD, nullptr, nullptr, 0, thr,
+         thr ? 1.0f / (1.0f - dropout_p) : 1.0f, seed};
+  return dispatch_tiles(dy, ldd, wt, ldw, ep, M, N, K, st);
 }
 
 int linear_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res,

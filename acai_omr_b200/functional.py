@@ -136,6 +136,85 @@ def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None
     return _Linear.apply(x, weight, bias, residual, act, out_dtype or dt, rows, dropout_p, seed)
 
 
+def _weight_grad(weight, dz, x2):
+    """dW = dz^T x2: accumulated into the trainer-owned gradient (returns None) or returned as a fresh fp32 tensor."""
+    g = _owned_grad(weight)
+    if g is not None:
+        ops.wgrad_accumulate(dz, x2, g)
+        return None
+    return ops.wgrad_accumulate(dz, x2, torch.zeros(weight.shape, dtype=torch.float32, device=dz.device))
+
+
+def _bias_grad(bias, dz):
+    g = _owned_grad(bias)
+    if g is not None:
+        ops.colsum(dz, out=g, accumulate=True)
+        return None
+    return ops.colsum(dz)
+
+
+class _FeedForward(torch.autograd.Function):
+    """linear2(dropout(gelu(linear1(x)))) [+ x]: the feed-forward block as ONE tape node, so that the GELU (+ its dropout)
+    rides in the up-projection GEMM's epilogue (acai_linear_gelu_train) and the GELU backward in the epilogue of the
+    down-projection's dX GEMM (acai_linear_gelu_bwd); the block's residual gradient is fused into the last dX GEMM."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, add_residual, dropout_p, dropout_seed):
+        dt = x.dtype
+        x2 = x.reshape(-1, x.shape[-1])
+        if x2.stride(-1) != 1:
+            x2 = x2.contiguous()
+        W1, W2 = _weights().get(w1, dt, None), _weights().get(w2, dt, None)
+        zh = ops.linear_gelu_train(x2, W1, b1.detach(), dropout_p, dropout_seed) if dt == torch.bfloat16 else None
+        if zh is None:
+            z = ops.linear(x2, W1, b1.detach(), out_dtype=dt)
+            h = ops.gelu(z, out_dtype=dt, dropout_p=dropout_p, dropout_seed=dropout_seed)
+        else:
+            z, h = zh
+        y = ops.linear(h, W2, b2.detach(), residual=x2 if add_residual else None, out_dtype=dt)
+        ctx.save_for_backward(x2, z, h, w1, b1, w2, b2)
+        ctx.meta = (x.shape, add_residual, dropout_p, dropout_seed)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, z, h, w1, b1, w2, b2 = ctx.saved_tensors
+        shape, add_residual, p, seed = ctx.meta
+        dt = x2.dtype
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if dy2.dtype != dt:
+            dy2 = dy2.to(dt)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        w2t = _weights().get_t(w2, dt, None)                                  # [hidden, d]
+        dz = ops.linear_gelu_bwd(dy2, w2t, z, p, seed) if dt == torch.bfloat16 else None
+        if dz is None:
+            dz = ops.gelu_bwd(ops.linear(dy2, w2t, out_dtype=dt), z, out_dtype=dt, dropout_p=p, dropout_seed=seed)
+        dx = dw1 = db1 = dw2 = db2 = None
+        if ctx.needs_input_grad[3]:
+            dw2 = _weight_grad(w2, dy2, h)
+        if ctx.needs_input_grad[4]:
+            db2 = _bias_grad(b2, dy2)
+        if ctx.needs_input_grad[0]:
+            dx = ops.linear(dz, _weights().get_t(w1, dt, None), residual=dy2 if add_residual else None, out_dtype=dt).view(shape)
+        if ctx.needs_input_grad[1]:
+            dw1 = _weight_grad(w1, dz, x2)
+        if ctx.needs_input_grad[2]:
+            db1 = _bias_grad(b1, dz)
+        return dx, dw1, db1, dw2, db2, None, None, None
+
+
+def feed_forward(x, w1, b1, w2, b2, add_residual=True, dropout_p=0.0):
+    """linear2(dropout(gelu(linear1(x)))) (+ x): the feed-forward block of nn.Transformer*Layer up to (not including) its
+    outer dropout; `dropout_p` is the inner nn.Dropout's rate."""
+    dt = x.dtype
+    seed = ops.DropoutState.next_seed() if dropout_p > 0.0 else 0
+    if not needs_grad(x, w1, b1, w2, b2):
+        h = linear(x, w1, b1, act=ops.ACT_GELU, out_dtype=dt, dropout_p=dropout_p)
+        return linear(h, w2, b2, residual=x if add_residual else None, out_dtype=dt)
+    return _FeedForward.apply(x, w1, b1, w2, b2, add_residual, dropout_p, seed)
+
+
 # ------------------------------------------------------------------------------------------ LayerNorm
 class _LayerNorm(torch.autograd.Function):
     @staticmethod

@@ -230,10 +230,16 @@ class TransformerEncoderLayer(nn.Module):
 def _mlp_residual(layer, x, dt):
     """x + dropout2(linear2(dropout(gelu(linear1(x)))))  (the feed-forward block of nn.Transformer*Layer, post-norm)."""
     p = layer.dropout_p if layer.training else 0.0
-    h = F.linear(x, layer.linear1.weight, layer.linear1.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=p)
+    l1, l2 = layer.linear1, layer.linear2
+    if not ops.FUSE_GELU_GEMM or l1.bias is None or l2.bias is None or x.dtype != dt:
+        h = F.linear(x, l1.weight, l1.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=p)
+        if p > 0.0:
+            return F.dropout(F.linear(h, l2.weight, l2.bias, out_dtype=dt), p, True, residual=x)
+        return F.linear(h, l2.weight, l2.bias, residual=x, out_dtype=dt)
     if p > 0.0:
-        return F.dropout(F.linear(h, layer.linear2.weight, layer.linear2.bias, out_dtype=dt), p, True, residual=x)
-    return F.linear(h, layer.linear2.weight, layer.linear2.bias, residual=x, out_dtype=dt)
+        return F.dropout(F.feed_forward(x, l1.weight, l1.bias, l2.weight, l2.bias, add_residual=False, dropout_p=p), p, True,
+                         residual=x)
+    return F.feed_forward(x, l1.weight, l1.bias, l2.weight, l2.bias, add_residual=True)
 
 
 def _check_dropout(module, p):

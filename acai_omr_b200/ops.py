@@ -8,6 +8,7 @@ launch of one of this repo's sm_100a kernels.  CPU tensors are rejected: there i
 from __future__ import annotations
 
 import ctypes as C
+import os
 import math
 
 import torch
@@ -445,6 +446,70 @@ def wgrad_accumulate(dz, x, dw):
     else:
         dw += linear(transpose_pad(dz), transpose_pad(x), out_dtype=torch.float32)
     return dw
+
+
+ERR_UNSUPPORTED = -2
+# GELU (+ dropout) forward / backward inside the tcgen05 GEMM epilogues.  Parity-green but measured SLOWER than the
+# standalone 16-byte GELU kernels on B200 (teacher-forced step 208.7 ms vs 203.4 ms, profiles/r1g_gelu_epilogue.md): with
+# K = 768 / 1024 the GEMM's eight epilogue warps are already the critical path and ~27 extra instructions per element at
+# an issue rate of ~0.45 IPC cost more than a second pass over HBM.  Opt in with ACAI_FUSE_GELU_GEMM=1.
+FUSE_GELU_GEMM = os.environ.get("ACAI_FUSE_GELU_GEMM", "0") == "1"
+
+
+def _try_call(name, fn, *args, flops=0.0, nbytes=0.0):
+    """Like _call, but returns False (nothing launched) when the entry point reports ACAI_ERR_UNSUPPORTED."""
+    prof = Profile.active
+    if prof is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+    rc = fn(*args)
+    if rc == ERR_UNSUPPORTED:
+        return False
+    _lib.check(rc, name)
+    if prof is not None:
+        e1.record()
+        prof.records.append((name, e0, e1, flops, nbytes))
+    _bump()
+    return True
+
+
+def _gemm_fusable(*ts):
+    return all(t.dtype == torch.bfloat16 and t.dim() == 2 and t.stride(1) == 1 and t.stride(0) % 8 == 0 and
+                                  t.data_ptr() % 16 == 0 for t in ts)
+
+
+def linear_gelu_train(x, weight, bias, dropout_p=0.0, dropout_seed=0):
+    """(z, h) with z = x @ weight.T + bias and h = dropout(gelu(z)), both bf16, from one tcgen05 GEMM
+    (acai_linear_gelu_train); None when the operands do not qualify (the caller runs linear + gelu)."""
+    _cuda(x, weight, bias)
+    M, K = x.shape
+    N = weight.shape[0]
+    if not _gemm_fusable(x, weight) or M == 0:
+        return None
+    z = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    h = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    b = _f32c(bias)
+    name = "acai_linear_gelu_train" if Profile.active is None else f"acai_linear_gelu_train[{M}x{N}x{K}]"
+    ok = _try_call(name, _lib.load().acai_linear_gelu_train, _p(x), x.stride(0), _p(weight), weight.stride(0), _p(b), _p(z), N,
+                   _p(h), N, M, N, K, float(dropout_p), int(dropout_seed), _stream(), flops=2.0 * M * N * K,
+                   nbytes=2.0 * (M * K + N * K + 2 * M * N))
+    return (z, h) if ok else None
+
+
+def linear_gelu_bwd(dy, weight_t, z, dropout_p=0.0, dropout_seed=0):
+    """dz = (dy @ weight_t.T) * gelu'(z) * dropout_mask from one tcgen05 GEMM (acai_linear_gelu_bwd); None when the
+    operands do not qualify (the caller runs linear + gelu_bwd)."""
+    _cuda(dy, weight_t, z)
+    M, K = dy.shape
+    N = weight_t.shape[0]
+    if not _gemm_fusable(dy, weight_t, z) or M == 0 or z.shape != (M, N) or z.stride(0) != N:
+        return None
+    dz = torch.empty((M, N), dtype=torch.bfloat16, device=dy.device)
+    name = "acai_linear_gelu_bwd" if Profile.active is None else f"acai_linear_gelu_bwd[{M}x{N}x{K}]"
+    ok = _try_call(name, _lib.load().acai_linear_gelu_bwd, _p(dy), dy.stride(0), _p(weight_t), weight_t.stride(0), _p(z), N, _p(dz),
+                   N, M, N, K, float(dropout_p), int(dropout_seed), _stream(), flops=2.0 * M * N * K,
+                   nbytes=2.0 * (M * K + N * K + 2 * M * N))
+    return dz if ok else None
 
 
 def colsum(x, out=None, accumulate=False):

@@ -284,6 +284,21 @@ int acai_gumbel_softmax_bwd(const void* dy, int32_t dy_dtype, const float* y_sof
 int acai_mix_rows(const void* a, int32_t a_dtype, const int64_t* sel, const void* b, int32_t b_dtype, const float* pos,
                   int32_t period, int32_t rows, int32_t dim, void* out, int32_t out_dtype, void* stream);
 
+/* Feed-forward block, training (models.py:30-34 / nn.TransformerEncoderLayer's linear1 -> gelu -> dropout): one tcgen05
+ * GEMM whose epilogue stores the pre-activation z = a @ w^T + bias (bf16 [M, N], kept for the backward) AND
+ * h = dropout(gelu(z)) (bf16 [M, N]); the dropout mask is that of acai_gelu_fwd on a dense [M, N] tensor with the same
+ * (dropout_p, dropout_seed).  Returns ACAI_ERR_UNSUPPORTED (nothing written) when the operands do not qualify for the
+ * TMA-store epilogue; the caller then runs acai_linear_fwd + acai_gelu_fwd. */
+int acai_linear_gelu_train(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* z, int64_t ldz,
+                           void* h, int64_t ldh, int32_t M, int32_t N, int32_t K, float dropout_p, uint64_t dropout_seed,
+                           void* stream);
+
+/* Backward of the same block through the activation: dz = (dy @ wt^T) * gelu'(z) * dropout_mask (bf16 [M, N]), with
+ * dy [M, K] bf16, wt [N, K] bf16 (the transposed down-projection weight) and z the tensor acai_linear_gelu_train kept.
+ * Same fallback contract (acai_linear_fwd + acai_gelu_bwd). */
+int acai_linear_gelu_bwd(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
+                         int64_t ldo, int32_t M, int32_t N, int32_t K, float dropout_p, uint64_t dropout_seed, void* stream);
+
 /* Weight gradient of a linear layer, accumulated in place:  dw[n_out, k_in] += dz[tokens, n_out]^T . x[tokens, k_in]
  * (bf16 operands exactly as the forward/backward left them - no transposed copies; fp32 dw, typically the parameter's
  * slice of the flat gradient buffer).  tcgen05 GEMM with both operands MN-major, split over token ranges, partial

@@ -630,3 +630,79 @@ def test_gelu_linear_with_fused_dropout(dtype, tol):
     yr = torch.nn.functional.gelu(z) * keep / (1 - p)
     yr.backward(dy.float())
     assert rel_err(y, yr) < tol and rel_err(x.grad, xr.grad) < tol and rel_err(w.grad, wr.grad) < tol and rel_err(b.grad, br.grad) < tol
+
+
+# ------------------------------------------------------------------------------------------ GELU in the GEMM epilogues
+@pytest.mark.parametrize("M_,N,K", [(1000, 3072, 768), (129, 256, 64), (4100, 768, 3072), (37, 136, 128)])
+@pytest.mark.parametrize("p", [0.0, 0.25])
+def test_linear_gelu_train_epilogue(M_, N, K, p):
+    """acai_linear_gelu_train: z is the plain GEMM's output bit for bit, h = dropout(gelu(z)) with the standalone kernel's mask."""
+    x = rnd(M_, K, seed=111, dtype=torch.bfloat16)
+    w = (rnd(N, K, seed=112) / math.sqrt(K)).bfloat16()
+    b = 0.1 * rnd(N, seed=113)
+    seed = 0x1234567887654321
+    zh = ops.linear_gelu_train(x, w, b, p, seed)
+    assert zh is not None, "the TMA-store epilogue must take this shape"
+    z, h = zh
+    z_ref = ops.linear(x, w, b, out_dtype=torch.bfloat16)
+    assert torch.equal(z, z_ref)
+    h_ref = ops.gelu(z_ref, dropout_p=p, dropout_seed=seed)
+    if p > 0.0:
+        keep = ops.dropout_mask(M_ * N, p, seed, DEV).view(M_, N)
+        inner = (z.float().abs() < 4.0) & (z != 0)                 # gelu is only 0 at z = 0 or where 1 + erf underflows
+        assert torch.equal((h != 0)[inner], keep[inner]) and float(h[~keep].abs().max()) == 0.0
+    # Abramowitz-Stegun erf (1.5e-7) vs erff: at most the last bf16 bit
+    assert float((h.float() - h_ref.float()).abs().max()) <= 2.0 ** -7 * float(h_ref.float().abs().max())
+    assert rel_err(h, h_ref) < 2e-3
+
+
+@pytest.mark.parametrize("M_,N,K", [(1000, 3072, 768), (129, 256, 64), (37, 136, 128)])
+@pytest.mark.parametrize("p", [0.0, 0.25])
+def test_linear_gelu_bwd_epilogue(M_, N, K, p):
+    """acai_linear_gelu_bwd against fp32 torch: dz = (dy @ wt^T) * gelu'(z) * mask / (1 - p)."""
+    dy = rnd(M_, K, seed=121, dtype=torch.bfloat16)
+    wt = (rnd(N, K, seed=122) / math.sqrt(K)).bfloat16()
+    z = rnd(M_, N, seed=123, dtype=torch.bfloat16, scale=1.5)
+    seed = 0x0badcafe12345678
+    dz = ops.linear_gelu_bwd(dy, wt, z, p, seed)
+    assert dz is not None
+    zf = z.float().requires_grad_(True)
+    torch.nn.functional.gelu(zf).sum().backward()
+    ref = (dy.float() @ wt.float().t()) * zf.grad
+    if p > 0.0:
+        keep = ops.dropout_mask(M_ * N, p, seed, DEV).view(M_, N)
+        ref = ref * keep / (1 - p)
+        assert float(dz[~keep].abs().max()) == 0.0
+    assert rel_err(dz, ref) < 4e-3
+    unfused = ops.gelu_bwd(ops.linear(dy, wt, out_dtype=torch.bfloat16), z, dropout_p=p, dropout_seed=seed)
+    assert rel_err(dz, ref) <= rel_err(unfused, ref) * 1.05 + 1e-4       # fp32 accumulators into the derivative: no worse
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1.5e-2)])
+@pytest.mark.parametrize("p,add_residual", [(0.0, True), (0.2, False)])
+def test_feed_forward_node(dtype, tol, p, add_residual):
+    """The feed-forward block as one tape node (fused epilogues in bf16, plain kernels in fp32) against torch autograd."""
+    ops.DropoutState.manual_seed(9)
+    seed = ops.DropoutState.next_seed()
+    ops.DropoutState.manual_seed(9)
+    T, d, hdim = 333, 128, 512
+    w1 = (rnd(hdim, d, seed=131) / math.sqrt(d)).requires_grad_(True)
+    b1 = (0.1 * rnd(hdim, seed=132)).requires_grad_(True)
+    w2 = (rnd(d, hdim, seed=133) / math.sqrt(hdim)).requires_grad_(True)
+    b2 = (0.1 * rnd(d, seed=134)).requires_grad_(True)
+    x = rnd(T, d, seed=135, dtype=dtype).requires_grad_(True)
+    dy = rnd(T, d, seed=136, dtype=dtype)
+    y = F.feed_forward(x, w1, b1, w2, b2, add_residual=add_residual, dropout_p=p)
+    y.backward(dy)
+    rq = (lambda t: t) if dtype == torch.float32 else (lambda t: t.detach().bfloat16().float() + (t - t.detach()))
+    xr = x.detach().float().requires_grad_(True)
+    ps = [t.detach().clone().requires_grad_(True) for t in (w1, b1, w2, b2)]
+    z = rq(xr @ rq(ps[0]).t() + ps[1])
+    h = torch.nn.functional.gelu(z)
+    if p > 0.0:
+        h = h * ops.dropout_mask(T * hdim, p, seed, DEV).view(T, hdim).float() / (1 - p)
+    yr = rq(h) @ rq(ps[2]).t() + ps[3] + (xr if add_residual else 0.0)
+    yr.backward(dy.float())
+    assert rel_err(y, yr) < tol and rel_err(x.grad, xr.grad) < tol
+    for got, want in zip((w1, b1, w2, b2), ps):
+        assert rel_err(got.grad, want.grad) < tol

@@ -34,6 +34,33 @@ __global__ void attn_delta_kernel(AttnBwdArgs a) {
   if (lane == 0) const_cast<float*>(a.delta)[(int64_t)h * a.total_q + row] = s;
 }
 
+// bf16 fast path: one 16-byte piece of a row per thread (a warp reads 512 contiguous bytes of dO and of O), the G = d / 8
+// lanes of one (row, head) folded by shuffles; grid-stride.
+template <int G>
+__global__ void __launch_bounds__(256)
+attn_delta_bf16_kernel(AttnBwdArgs a) {
+  const int per_row = a.heads * G;
+  const int64_t items = (int64_t)a.total_q * per_row;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < items; base += stride) {
+    const int64_t i = base + (threadIdx.x & 31);
+    float s = 0.0f;
+    int row = 0, c8 = 0;
+    if (i < items) {
+      row = (int)(i / per_row); c8 = (int)(i - (int64_t)row * per_row);
+      const uint4 u = __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(a.dout) + (int64_t)row * a.dos + c8 * 8));
+      const uint4 w = __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(a.o) + (int64_t)row * a.os + c8 * 8));
+      const __nv_bfloat162* hu = reinterpret_cast<const __nv_bfloat162*>(&u);
+      const __nv_bfloat162* hw = reinterpret_cast<const __nv_bfloat162*>(&w);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { const float2 x = __bfloat1622float2(hu[e]), y = __bfloat1622float2(hw[e]); s = fmaf(x.x, y.x, fmaf(x.y, y.y, s)); }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (i < items && (c8 % G) == 0) const_cast<float*>(a.delta)[(int64_t)(c8 / G) * a.total_q + row] = s;
+  }
+}
+
 template <int DMAX>
 __device__ __forceinline__ float pair_dot(const float (&x)[DMAX / 2], const float* __restrict__ y) {
   float s0 = 0.0f, s1 = 0.0f;
@@ -200,7 +227,17 @@ extern "C" int acai_attn_varlen_bwd(const void* q, const void* k, const void* v,
                 cu_seqlens_q, cu_seqlens_k, total_q, heads, head_dim, causal, scale, scale * 1.4426950408889634f,
                 dq, dk, dv, grad_dtype, dq_stride, dk_stride, dv_stride, drop};
   const int64_t nw = (int64_t)total_q * heads;
-  attn_delta_kernel<<<(unsigned)((nw + 7) / 8), 256, 0, st>>>(a);
+  const bool delta_fast = dtype == ACAI_BF16 && (head_dim == 32 || head_dim == 64 || head_dim == 128) && do_stride % 8 == 0 &&
+                          o_stride % 8 == 0 && !((reinterpret_cast<uintptr_t>(dout) | reinterpret_cast<uintptr_t>(out)) & 15);
+  if (delta_fast) {
+    const int64_t items = nw * (head_dim / 8);
+    const int64_t want = (items + 255) / 256, cap = (int64_t)acai::num_sms() * 8;
+    const unsigned g = (unsigned)(want < cap ? want : cap);
+    if (head_dim == 32) attn_delta_bf16_kernel<4><<<g, 256, 0, st>>>(a);
+    else if (head_dim == 64) attn_delta_bf16_kernel<8><<<g, 256, 0, st>>>(a);
+    else attn_delta_bf16_kernel<16><<<g, 256, 0, st>>>(a);
+  } else
+    attn_delta_kernel<<<(unsigned)((nw + 7) / 8), 256, 0, st>>>(a);
   int rc = launch_status("attn_delta");
   if (rc) return rc;
   rc = acai::attn_bwd_tc(q, k, v, dtype, q_stride, k_stride, v_stride, dout, do_stride, lse, delta_ws, cu_seqlens_q, cu_seqlens_k,

@@ -248,11 +248,27 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
 }
 
 // ------------------------------------------------------------------------------------------ dK / dV
+// Shared memory of this kernel: K, V (resident), 2 stages of (Q_i, dO_i), and the bf16 P^T / dS^T tiles the elementwise
+// warps hand to the dV / dK MMAs.  P^T and dS^T go through shared memory (not back into TMEM over S^T / dP^T) so that the
+// S^T / dP^T columns are free as soon as they have been read into registers: the MMAs of block i + 1 then run underneath
+// the exponentials of block i even though TMEM only has room for one S^T / dP^T pair next to the two accumulators.
+namespace fkv {
+constexpr int STAGES = 2;
+constexpr uint32_t OFF_B0 = 2 * fb::BIGTILE, OFF_B1 = OFF_B0 + STAGES * fb::SMALLTILE;
+constexpr uint32_t OFF_P = OFF_B1 + STAGES * fb::SMALLTILE, OFF_DS = OFF_P + fb::BIGTILE;
+constexpr uint32_t OFF_VEC = OFF_DS + fb::BIGTILE, OFF_BAR = OFF_VEC + 2 * 256 * 4;
+constexpr size_t SMEM = OFF_BAR + 256;
+static_assert(SMEM == fb::SMEM, "both backward kernels are launched with fb::SMEM bytes of shared memory");
+}  // namespace fkv
+
 template <int DH, bool DROP>
 __global__ void __launch_bounds__(fb::THREADS, 2)
 attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant__ CUtensorMap tma_v,
                   const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_do, AttnBwdParams p) {
   using namespace fb;
+  constexpr int STAGES = fkv::STAGES;
+  constexpr uint32_t OFF_B0 = fkv::OFF_B0, OFF_B1 = fkv::OFF_B1, OFF_P = fkv::OFF_P, OFF_DS = fkv::OFF_DS, OFF_VEC = fkv::OFF_VEC,
+                     OFF_BAR = fkv::OFF_BAR;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* a_full = bars;                     // K and V tiles
@@ -261,7 +277,9 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
   uint64_t* sp_full = b_empty + STAGES;
   uint64_t* ds_full = sp_full + 1;
   uint64_t* acc_full = ds_full + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  uint64_t* sp_free = acc_full + 1;            // S^T / dP^T of the current block are in registers (256 arrivals)
+  uint64_t* pd_free = sp_free + 1;             // the dV / dK MMAs have consumed the P^T / dS^T tiles
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pd_free + 1);
   float* vec = reinterpret_cast<float*>(smem + OFF_VEC);          // [2][128]: L of 64 queries, then delta of 64 queries
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -279,6 +297,7 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
     ptx::mbar_init(a_full, 1);
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
     ptx::mbar_init(sp_full, 1); ptx::mbar_init(ds_full, 256); ptx::mbar_init(acc_full, 1);
+    ptx::mbar_init(sp_free, 256); ptx::mbar_init(pd_free, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 8) {
@@ -315,8 +334,9 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
       const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);
       const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024) + hoff;
       const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024) + hoff;
-      ptx::mbar_wait(a_full, 0);
-      for (int it = 0; it < n_it; ++it) {
+      const uint64_t pdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_P), 1024);
+      const uint64_t dsdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_DS), 1024);
+      auto issue_sp = [&](int it) {                // S^T_it and dP^T_it (waits for Q_it / dO_it to land)
         const int st = it % STAGES;
         ptx::mbar_wait(&b_full[st], (it / STAGES) & 1);
         ptx::tc_fence_after();
@@ -327,15 +347,28 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
 #pragma unroll
         for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, vdesc + 2 * k, dodesc + 2 * k, IDESC_S, k != 0); // dP^T
         ptx::umma_commit(sp_full);
+      };
+      ptx::mbar_wait(a_full, 0);
+      issue_sp(0);
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it % STAGES;
+        if (it + 1 < n_it) {                         // issued BEFORE dV / dK of block it: runs under block it's exponentials
+          ptx::mbar_wait(sp_free, it & 1);
+          ptx::tc_fence_after();
+          issue_sp(it + 1);
+        }
+        const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024) + hoff;
+        const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024) + hoff;
         ptx::mbar_wait(ds_full, it & 1);
         ptx::tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < SMALL / 16; ++kk)      // dV += P^T dO_i
-          ptx::umma_f16_ts(tmem_base + 128, tmem_base + (kk >> 1) * 32 + (kk & 1) * 8, dodesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+        for (int kk = 0; kk < SMALL / 16; ++kk)      // dV += P^T dO_i   (A = P^T [128 keys x 64 queries] K-major in smem)
+          ptx::umma_f16_ss(tmem_base + 128, pdesc + 2 * kk, dodesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
 #pragma unroll
         for (int kk = 0; kk < SMALL / 16; ++kk)      // dK += dS^T Q_i
-          ptx::umma_f16_ts(tmem_base + 192, tmem_base + 64 + (kk >> 1) * 32 + (kk & 1) * 8, qdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+          ptx::umma_f16_ss(tmem_base + 192, dsdesc + 2 * kk, qdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
         ptx::umma_commit(&b_empty[st]);
+        ptx::umma_commit(pd_free);
         if (it == n_it - 1) ptx::umma_commit(acc_full);
       }
     }
@@ -346,18 +379,30 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
     const bool valid = kr < lk;
     const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
     const float sl2 = p.scale_log2;
+    // Per query block the 64 L / delta values (and, with dropout, the 64 hash row constants / row bases) are staged in
+    // shared memory for broadcast reads.  The global loads for block it + 1 are issued BEFORE block it's math and land in
+    // the other half of `vec` after it, so their latency never sits between two blocks.
+    auto stage_load = [&](int it) -> uint32_t {
+      const int qbase = (i0 + it) * SMALL;
+      if (tid < 128) {
+        const int q = qbase + (tid & 63);
+        const float* src = tid < 64 ? p.lse : p.delta;
+        return __float_as_uint(q < lq ? __ldg(src + (int64_t)h * p.total_q + q0 + q) : (tid < 64 ? INFINITY : 0.0f));
+      }
+      if (DROP) {                                  // per query column: hash row constant (128..191) and low row base (192..255)
+        const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + qbase + (tid & 63));
+        return tid < 192 ? attn_drop_rowconst(p.drop.seed, rowkey) : (uint32_t)(rowkey << 15);
+      }
+      return 0u;
+    };
+    if (n_it > 0) {
+      reinterpret_cast<uint32_t*>(vec)[tid] = stage_load(0);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+    }
     for (int it = 0; it < n_it; ++it) {
       const int qbase = (i0 + it) * SMALL;
       float* vb = vec + (it & 1) * 256;
-      if (tid < 128) {                             // stage L / delta of this query block (broadcast reads below)
-        const int q = qbase + (tid & 63);
-        const float* src = tid < 64 ? p.lse : p.delta;
-        vb[tid] = q < lq ? src[(int64_t)h * p.total_q + q0 + q] : (tid < 64 ? INFINITY : 0.0f);
-      } else if (DROP) {                           // per query column: hash row constant (128..191) and low row base (192..255)
-        const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + qbase + (tid & 63));
-        reinterpret_cast<uint32_t*>(vb)[tid] = tid < 192 ? attn_drop_rowconst(p.drop.seed, rowkey) : (uint32_t)(rowkey << 15);
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const uint32_t staged_next = it + 1 < n_it ? stage_load(it + 1) : 0u;
       // first query column this key row may attend to (causal), all columns masked for rows past the sequence end
       const int cmin = !valid ? SMALL : (p.causal ? kr - shift - qbase : 0);
       ptx::mbar_wait(sp_full, it & 1);
@@ -366,6 +411,8 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
       ptx::tmem_ld_32x32(tmem_base + lane_addr + half * 32, s);
       ptx::tmem_ld_32x32(tmem_base + lane_addr + 64 + half * 32, dp);
       ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(sp_free);                   // the MMA warp may overwrite S^T / dP^T with block it + 1
       const float4* vl = reinterpret_cast<const float4*>(vb + half * 32);
       const float4* vd = reinterpret_cast<const float4*>(vb + 64 + half * 32);
 #pragma unroll
@@ -399,12 +446,25 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
         pk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hp0); pk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hp1);
         dk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hd0); dk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hd1);
       }
-      // P^T / dS^T go over the start of this warp's own halves of S^T / dP^T (columns 0..15 or 32..47, +64)
-      ptx::tmem_st_32x16(tmem_base + lane_addr + half * 32, pk);
-      ptx::tmem_st_32x16(tmem_base + lane_addr + 64 + half * 32, dk);
-      ptx::tmem_st_wait();
-      ptx::tc_fence_before();
+      // P^T / dS^T rows (this thread: key row r, 32 query columns = four 16-byte pieces) into the 128B-swizzled K-major
+      // tiles the dV / dK MMAs read as their A operand; block it - 1's MMAs must have finished with the tiles
+      if (it > 0) ptx::mbar_wait(pd_free, (it - 1) & 1);
+      {
+        uint8_t* prow = smem + OFF_P + r * 128;
+        uint8_t* drow = smem + OFF_DS + r * 128;
+        const uint32_t sw = (uint32_t)(r & 7);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t off = (((uint32_t)(half * 4 + c)) ^ sw) << 4;
+          *reinterpret_cast<uint4*>(prow + off) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+          *reinterpret_cast<uint4*>(drow + off) = make_uint4(dk[4 * c], dk[4 * c + 1], dk[4 * c + 2], dk[4 * c + 3]);
+        }
+      }
+      ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(ds_full);
+      // the other half of `vec` was last read in block it - 1, which every thread left before this block's barrier
+      reinterpret_cast<uint32_t*>(vec + ((it + 1) & 1) * 256)[tid] = staged_next;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
     }
     if (n_it > 0) {
       ptx::mbar_wait(acc_full, 0);

@@ -17,6 +17,8 @@
 // Q/K/V tiles arrive by TMA straight out of the fused [T, 3*H*64] QKV buffer (or separate Q and KV buffers for cross
 // attention); ragged sequence ends are masked in the softmax, never padded.
 //   warps 0-3: softmax + output     warp 4: TMA producer (+TMEM alloc)     warp 5: MMA issuer
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
@@ -47,7 +49,9 @@ struct AttnParams {
 
 // DH = head_dim (64 or 32).  Shared-memory tiles are always 64 columns (one 128-byte swizzle row) wide: for DH = 32 a
 // tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
-template <int DH, bool DROP>
+// POLY: how many of every 4 exponentials are evaluated with exp2_fma on the FMA pipe instead of MUFU.EX2 (0, 1 or 2).
+// The MUFU unit (16 results / clk / SM) is this kernel's busiest pipe; the FMA pipe is mostly idle.
+template <int DH, bool DROP, int POLY>
 __global__ void __launch_bounds__(THREADS, 2)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
@@ -196,8 +200,9 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
       uint32_t pk[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff));
-        const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff));
+        const float x0 = fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff), x1 = fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff);
+        const float p0 = fast_exp2(x0);
+        const float p1 = (POLY == 2 || (POLY == 1 && (i & 1))) ? exp2_fma(x1) : fast_exp2(x1);
         l0 += p0; l1 += p1;
         float d0 = p0, d1 = p1;
         if (DROP) {                                   // keys kbase + 2i, kbase + 2i + 1 = one hash pair
@@ -218,8 +223,9 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
       ptx::mbar_wait(o_full, 0);
       ptx::tc_fence_after();
     }
-    const float inv = l > 0.0f ? (DROP ? p.drop.rp : 1.0f) / l : 0.0f;
-    if (p.lse && valid) p.lse[(int64_t)h * p.total_q + q0 + qi] = l > 0.0f ? m * scale_log2 + log2f(l) : INFINITY;
+    const bool any_key = l > 0.0f && m > -INFINITY;   // (exp2_fma never returns an exact 0: a row without keys has m = -inf)
+    const float inv = any_key ? (DROP ? p.drop.rp : 1.0f) / l : 0.0f;
+    if (p.lse && valid) p.lse[(int64_t)h * p.total_q + q0 + qi] = any_key ? m * scale_log2 + log2f(l) : INFINITY;
     const int64_t off = (int64_t)(q0 + qi) * p.o_stride + (int64_t)h * DH;
 #pragma unroll
     for (int c = 0; c < DH / 32; ++c) {
@@ -257,6 +263,18 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
+template <int DH, bool DROP, int POLY>
+static int launch_fwd(dim3 grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
+                      cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    attr_set = true;
+  }
+  attn_fwd_tc<DH, DROP, POLY><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+  return ACAI_OK;
+}
+
 // returns ACAI_ERR_UNSUPPORTED when the problem does not qualify
 int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs,
                    const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
@@ -274,23 +292,17 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
   if (rc) return rc;
   rc = make_tma_2d_bf16(&tv, v, (uint64_t)total_k, cols, (uint64_t)vs, BKV, D);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    attr_set = true;
-  }
+  // share of the exponentials moved to the FMA pipe (see POLY); ACAI_ATTN_POLY overrides the tuned default for A/B runs
+  static const int poly = [] { const char* e = getenv("ACAI_ATTN_POLY"); const int v = e ? atoi(e) : 0; return v < 0 ? 0 : (v > 2 ? 2 : v); }();
   AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q, drop};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
-  if (drop.thr == 0) {
-    if (head_dim == 64) attn_fwd_tc<64, false><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
-    else attn_fwd_tc<32, false><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
-  } else {
-    if (head_dim == 64) attn_fwd_tc<64, true><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
-    else attn_fwd_tc<32, true><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
-  }
+#define ACAI_FWD(DH_, DROP_)                                                                                      \
+  (poly == 0 ? launch_fwd<DH_, DROP_, 0>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1>(grid, tq, tk, tv, p, st) \
+                                                                             : launch_fwd<DH_, DROP_, 2>(grid, tq, tk, tv, p, st))
+  if (drop.thr == 0) rc = head_dim == 64 ? ACAI_FWD(64, false) : ACAI_FWD(32, false);
+  else rc = head_dim == 64 ? ACAI_FWD(64, true) : ACAI_FWD(32, true);
+#undef ACAI_FWD
+  if (rc) return rc;
   return launch_status("attn_fwd_tc");
 }
 

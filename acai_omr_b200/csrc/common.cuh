@@ -97,6 +97,20 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// 2^x on the FMA / ALU pipes instead of the 16-lane MUFU unit: Cody-Waite split (round x to an integer n with the
+// 1.5 * 2^23 trick, f = x - n in [-0.5, 0.5]), a degree-3 minimax polynomial for 2^f (relative error 7.5e-5, well under
+// the 2e-3 half-ulp of the bf16 value it feeds) and n added straight into the exponent field.  x is clamped at -126 (the
+// result is then ~1e-38, not 0: callers that need an exact zero for masked positions must not rely on it).
+__device__ __forceinline__ float exp2_fma(float x) {
+  x = fmaxf(x, -126.0f);
+  const float xf = x + 12582912.0f;
+  const float f = x - (xf - 12582912.0f);
+  float p = fmaf(f, 0.055171653628349304f, 0.2426111251115799f);
+  p = fmaf(p, f, 0.6932609677314758f);
+  p = fmaf(p, f, 0.9999280571937561f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(xf) << 23));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -106,6 +106,86 @@ layernorm_warp_kernel(const void* __restrict__ x, int x_dt, const void* __restri
   }
 }
 
+// bf16 -> bf16 fast path (every LayerNorm of the bf16 model): a persistent grid of warps strides over the rows, and the
+// NEXT row's 16-byte loads are issued before the current row's two warp reductions, so each warp keeps two rows of HBM
+// traffic in flight and no CTA launch sits between rows (the one-row-per-warp kernel above reached ~50% of HBM peak).
+template <int NV>
+__global__ void __launch_bounds__(256, NV <= 2 ? 4 : (NV == 3 ? 3 : 2))
+layernorm_bf16_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, float eps, uint4* __restrict__ out, int rows, int cols) {
+  const int lane = threadIdx.x & 31, nwarps = gridDim.x * (blockDim.x >> 5);
+  const int c8 = cols >> 3;                                   // 16-byte pieces per row
+  int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  uint4 cur[NV], cur_r[NV];
+  auto fetch = [&](int r, uint4 (&a)[NV], uint4 (&b)[NV]) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 32 + lane;
+      if (c < c8) {
+        a[i] = __ldcs(x + (int64_t)r * c8 + c);
+        if (res) b[i] = __ldcs(res + (int64_t)r * c8 + c);
+      }
+    }
+  };
+  if (row < rows) fetch(row, cur, cur_r);
+  const float inv_n = 1.0f / (float)cols;
+  while (row < rows) {
+    const int next = row + nwarps;
+    uint4 nxt[NV], nxt_r[NV];
+    if (next < rows) fetch(next, nxt, nxt_r);
+    // the row stays in its packed bf16 form (few registers = many resident warps = many bytes in flight); each of the
+    // three passes unpacks it again, which costs two ALU ops per pair
+    auto unpack = [&](int i, float (&f)[8]) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&cur[i]);
+      const __nv_bfloat162* hr = reinterpret_cast<const __nv_bfloat162*>(&cur_r[i]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float2 t = __bfloat1622float2(h[e]);
+        if (res) { const float2 g = __bfloat1622float2(hr[e]); t.x += g.x; t.y += g.y; }
+        f[2 * e] = t.x; f[2 * e + 1] = t.y;
+      }
+    };
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      if (i * 32 + lane < c8) {
+        float f[8]; unpack(i, f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += f[e];
+      }
+    }
+    const float mu = warp_sum(s) * inv_n;
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      if (i * 32 + lane < c8) {
+        float f[8]; unpack(i, f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { const float d = f[e] - mu; q += d * d; }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(q) * inv_n + eps);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 32 + lane;
+      if (c < c8) {
+        float f[8]; unpack(i, f);
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c), g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c), b1 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c + 1);
+        uint4 o; __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+        ho[0] = __floats2bfloat162_rn((f[0] - mu) * rstd * g0.x + b0.x, (f[1] - mu) * rstd * g0.y + b0.y);
+        ho[1] = __floats2bfloat162_rn((f[2] - mu) * rstd * g0.z + b0.z, (f[3] - mu) * rstd * g0.w + b0.w);
+        ho[2] = __floats2bfloat162_rn((f[4] - mu) * rstd * g1.x + b1.x, (f[5] - mu) * rstd * g1.y + b1.y);
+        ho[3] = __floats2bfloat162_rn((f[6] - mu) * rstd * g1.z + b1.z, (f[7] - mu) * rstd * g1.w + b1.w);
+        __stcs(out + (int64_t)row * c8 + c, o);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) { cur[i] = nxt[i]; cur_r[i] = nxt_r[i]; }
+    row = next;
+  }
+}
+
 __global__ void embed_tokens_kernel(const int64_t* __restrict__ ids, const float* __restrict__ table,
                                     const float* __restrict__ pos, const int32_t* __restrict__ pos_ids,
                                     int pos_offset, int period, void* __restrict__ out, int out_dt, int dim) {
@@ -306,6 +386,15 @@ extern "C" int acai_layernorm_fwd(const void* x, int32_t x_dtype, const void* re
     const int nv = (cols / 8 + 31) / 32;
     dim3 grid((rows + 7) / 8);
     cudaStream_t st = (cudaStream_t)stream;
+    if (x_dtype == ACAI_BF16 && out_dtype == ACAI_BF16 && !out2 && (!residual || res_dtype == ACAI_BF16) && nv <= 4) {
+      const int ctas = (rows + 7) / 8, cap = acai::num_sms() * 6;
+      dim3 pg(ctas < cap ? ctas : cap);
+#define LNB(NV) acai::layernorm_bf16_kernel<NV><<<pg, 256, 0, st>>>((const uint4*)x, (const uint4*)residual, gamma, beta, eps, \
+                                                                   (uint4*)out, rows, cols)
+      if (nv <= 1) LNB(1); else if (nv <= 2) LNB(2); else if (nv <= 3) LNB(3); else LNB(4);
+#undef LNB
+      return launch_status("layernorm_bf16");
+    }
 #define LN(NV) layernorm_warp_kernel<NV><<<grid, 256, 0, st>>>(x, x_dtype, residual, res_dtype, gamma, beta, eps, out, \
                                                               out_dtype, out2, out2_dtype, rows, cols)
     if (nv <= 1) LN(1); else if (nv <= 2) LN(2); else if (nv <= 3) LN(3); else if (nv <= 4) LN(4); else LN(8);

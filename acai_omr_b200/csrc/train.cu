@@ -46,6 +46,59 @@ __global__ void colsum_final_kernel(const float* __restrict__ part, int slabs, i
   out[c] = accumulate ? out[c] + s : s;
 }
 
+// bf16 fast path: a CTA covers 256 columns x one slab of CS_SLAB rows as 32 column groups (one 16-byte load = 8 columns
+// per thread) x 8 row lanes; the 8 row lanes are folded through shared memory in a fixed order.
+constexpr int CS_SLAB = 256;
+__global__ void __launch_bounds__(256)
+colsum_partial_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, int64_t ld, int rows, int cols, float* __restrict__ part) {
+  __shared__ float red[8][256 + 8];
+  const int cg = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c = blockIdx.x * 256 + cg * 8;
+  const int r0 = blockIdx.y * CS_SLAB, r1 = min(rows, r0 + CS_SLAB);
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.0f;
+  if (c < cols) {
+#pragma unroll 4
+    for (int r = r0 + ry; r < r1; r += 8) {
+      const uint4 u = __ldcs(reinterpret_cast<const uint4*>(x + (int64_t)r * ld + c));
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { const float2 f = __bfloat1622float2(h[e]); acc[2 * e] += f.x; acc[2 * e + 1] += f.y; }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[ry][cg * 8 + e] = acc[e];
+  __syncthreads();
+  const int cc = blockIdx.x * 256 + threadIdx.x;
+  if (cc < cols) {
+    float t = 0.0f;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) t += red[y][threadIdx.x];
+    part[(int64_t)blockIdx.y * cols + cc] = t;
+  }
+}
+// stage 2, parallel over the slabs as well: 32 columns x 8 slab lanes per CTA, fixed summation order
+__global__ void __launch_bounds__(256)
+colsum_final_wide_kernel(const float* __restrict__ part, int slabs, int cols, float* __restrict__ out, int accumulate) {
+  __shared__ float red[8][33];
+  const int cx = threadIdx.x & 31, sy = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
+  float s = 0.0f;
+  if (c < cols) {
+#pragma unroll 4
+    for (int i = sy; i < slabs; i += 8) s += part[(int64_t)i * cols + c];
+  }
+  red[sy][cx] = s;
+  __syncthreads();
+  if (sy == 0 && c < cols) {
+    float t = 0.0f;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) t += red[y][cx];
+    out[c] = accumulate ? out[c] + t : t;
+  }
+}
+
 // exact-erf GELU and its derivative  d/dz [z Phi(z)] = Phi(z) + z phi(z)
 __device__ __forceinline__ float gelu_grad(float v) {
   const float cdf = 0.5f * (1.0f + erff(v * 0.70710678118654752440f));
@@ -421,6 +474,16 @@ extern "C" int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t row
                            int32_t accumulate, void* workspace, size_t workspace_bytes, void* stream) {
   ACAI_CHECK_ARG(x && out && workspace && rows > 0 && cols > 0 && dtype_valid(dtype), "acai_colsum: bad argument");
   ACAI_CHECK_ARG(workspace_bytes >= acai_colsum_workspace_bytes(rows, cols), "acai_colsum: workspace too small");
+  if (dtype == ACAI_BF16 && cols % 8 == 0 && ld % 8 == 0 && !(reinterpret_cast<uintptr_t>(x) & 15)) {
+    const int slabs = (rows + CS_SLAB - 1) / CS_SLAB;
+    colsum_partial_bf16x8_kernel<<<dim3((cols + 255) / 256, slabs), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), ld, rows, cols, reinterpret_cast<float*>(workspace));
+    int rc = launch_status("colsum_partial");
+    if (rc) return rc;
+    colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float*>(workspace), slabs, cols, out,
+                                                                               accumulate);
+    return launch_status("colsum_final");
+  }
   const int slabs = (rows + 127) / 128;
   colsum_partial_kernel<<<dim3((cols + 255) / 256, slabs), 256, 0, (cudaStream_t)stream>>>(x, dtype, ld, rows, cols,
                                                                                         reinterpret_cast<float*>(workspace));

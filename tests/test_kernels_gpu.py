@@ -71,6 +71,22 @@ def test_layernorm(rows, cols, eps):
     close(y16, ref16, 1e-2, 1e-2)
 
 
+@pytest.mark.parametrize("rows,cols", [(1, 768), (9, 8), (5000, 768), (12345, 1024), (4737, 200), (300, 96)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_layernorm_bf16_persistent(rows, cols, with_res):
+    """bf16 -> bf16 LayerNorm (persistent warp-per-row kernel with next-row prefetch), more rows than resident warps."""
+    x = (rnd(rows, cols, seed=5, scale=2.0) + 0.3).bfloat16()
+    r = rnd(rows, cols, seed=6).bfloat16() if with_res else None
+    g, b = rnd(cols, seed=7) * 0.1 + 1.0, rnd(cols, seed=8) * 0.1
+    y = ops.layernorm(x, g, b, 1e-5, residual=r, out_dtype=torch.bfloat16)
+    xin = x.float() + (r.float() if with_res else 0.0)
+    ref = torch.nn.functional.layer_norm(xin, (cols,), g, b, 1e-5)
+    assert y.dtype == torch.bfloat16
+    assert torch.equal(y, ref.bfloat16()) or float((y.float() - ref).abs().max()) <= 2.0 ** -7 * float(ref.abs().max())
+    y32 = ops.layernorm(x, g, b, 1e-5, residual=r, out_dtype=torch.float32)          # generic kernel, same statistics
+    close(y.float(), y32, 1.6e-2, 1.6e-2)
+
+
 def ref_varlen(q, k, v, lens_q, lens_k, H, d, causal):
     out = torch.zeros(q.shape[0], H * d, device=q.device)
     oq = ok = 0

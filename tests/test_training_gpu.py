@@ -29,7 +29,7 @@ def rnd(*shape, seed=0, dtype=torch.float32, scale=1.0):
 
 
 # ------------------------------------------------------------------------------------------ kernels
-@pytest.mark.parametrize("shape", [(1, 1), (70, 33), (257, 768), (1000, 64)])
+@pytest.mark.parametrize("shape", [(1, 1), (70, 33), (257, 768), (1000, 64), (5003, 3072), (513, 8)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_transpose_pad_and_colsum(shape, dtype):
     x = rnd(*shape, seed=1, dtype=dtype)

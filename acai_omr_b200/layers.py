@@ -174,13 +174,13 @@ class Packed:
         off = [0]
         for v in self.lens:
             off.append(off[-1] + v)
-        self.cu = torch.tensor(off, dtype=torch.int32).to(device, non_blocking=True)
+        self.cu = ops.upload_small(torch.tensor(off, dtype=torch.int32), device)
 
     def mask(self, device, max_len=None):
         """True = padding, (B, L_max)  (create_attention_mask, models.py:70-73)."""
         L = max_len or self.max_len
         m = torch.arange(L)[None, :] >= torch.tensor(self.lens)[:, None]
-        m = m.to(device, non_blocking=True)
+        m = ops.upload_small(m, device)
         m._acai_lens = self.lens  # lets downstream modules re-pack without a device sync
         return m
 

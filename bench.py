@@ -136,7 +136,10 @@ def run_ours(args, rank, world, device):
         torch.cuda.synchronize()
 
     def timed(fn, steps, wall=False):
-        total = 0.0
+        """Device time of `steps` calls of fn, the L2 flush between them excluded.  The device-timed leg queues all steps
+        (events around each, one synchronize at the end) so that the host's launch latency is hidden behind the previous
+        step as it is in a serving loop; the wall-clock leg synchronises around every step."""
+        total, events = 0.0, []
         for _ in range(steps):
             flush.zero_()
             if wall:
@@ -150,8 +153,10 @@ def run_ours(args, rank, world, device):
                 e0.record()
                 fn()
                 e1.record()
-                e1.synchronize()
-                total += e0.elapsed_time(e1)
+                events.append((e0, e1))
+        if events:
+            torch.cuda.synchronize()
+            total = sum(a.elapsed_time(b) for a, b in events)
         return total
 
     for _ in range(max(args.warmup, 3)):
@@ -162,18 +167,33 @@ def run_ours(args, rank, world, device):
         ms_total = timed(step_resident, args.steps)
         barrier()
     launches = ops.launch_count() - n0
-    step_e2e()
-    barrier()
-    e2e_ms = timed(step_e2e, max(2, min(args.steps, 5)), wall=True) / max(2, min(args.steps, 5))
-    barrier()
-    with ops.Profile() as prof:
+    with ops.Profile() as prof:          # per-kernel CUDA events, straight after the timed loop (same clocks / power state)
         step_resident()
     kern = prof.summary()
-
-    t = torch.tensor([ms_total, e2e_ms], dtype=torch.float64, device=device)
+    step_e2e()
+    barrier()
+    e2e_sync_ms = timed(step_e2e, max(2, min(args.steps, 5)), wall=True) / max(2, min(args.steps, 5))
+    barrier()
+    # the serving loop: the same public call, uploads / downloads of neighbouring batches overlapped with the kernels
+    from acai_omr_b200.pipeline import EncoderPipeline
+    pipe = EncoderPipeline(enc, device)
+    ke = max(4, args.steps)
+    for _ in pipe.run([imgs_host] * 2, before_step=flush.zero_):
+        pass
+    barrier()
+    t0 = time.perf_counter()
+    stamps = [t0]
+    for _ in pipe.run((imgs_host for _ in range(ke)), before_step=flush.zero_):
+        stamps.append(time.perf_counter())
+    torch.cuda.synchronize()
+    served = len(stamps) - 1
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / served
+    yield_ms = [round((b - a) * 1e3, 2) for a, b in zip(stamps, stamps[1:])]
+    barrier()
+    t = torch.tensor([ms_total, e2e_ms, e2e_sync_ms], dtype=torch.float64, device=device)
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    ms_step, e2e_ms = t[0].item() / args.steps, t[1].item()
+    ms_step, e2e_ms, e2e_sync_ms = t[0].item() / args.steps, t[1].item(), t[2].item()
     if rank != 0:
         return None
     peaks = load_peaks()
@@ -201,7 +221,11 @@ def run_ours(args, rank, world, device):
         "clocks": clocks.summary(),
         "e2e": {"value": world * NUM_SYSTEMS / (e2e_ms * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": sum(t.numel() * 4 for t in imgs_host),
-                "d2h_bytes_per_step": NUM_SYSTEMS * max(lens) * 768 * 4 + NUM_SYSTEMS * max(lens)},
+                "d2h_bytes_per_step": NUM_SYSTEMS * max(lens) * 768 * 4 + NUM_SYSTEMS * max(lens),
+                "mode": "EncoderPipeline.run: Encoder.forward per batch from pinned host images to pinned host latents, "
+                        "uploads / downloads of neighbouring batches overlapped with the kernels (3 streams)",
+                "steps": served, "ms_between_results": yield_ms, "synchronous_ms_per_step": e2e_sync_ms,
+                "synchronous_value": world * NUM_SYSTEMS / (e2e_sync_ms * 1e-3)},
         "gpu_launches": launches,
         "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05 (acai_linear_fwd)", "achieved": gemm_tflops,
                      "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
@@ -358,15 +382,16 @@ def run_train(args, rank, world, device, kind):
         torch.distributed.barrier()
     k = max(3, min(args.steps, 10))
     n0 = ops.launch_count()
-    total = 0.0
-    for _ in range(k):
+    events = []
+    for _ in range(k):                                    # queued back to back: one synchronize after the last step
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         sums = step()
         e1.record()
-        e1.synchronize()
-        total += e0.elapsed_time(e1)
+        events.append((e0, e1))
+    torch.cuda.synchronize()
+    total = sum(a.elapsed_time(b) for a, b in events)
     launches = (ops.launch_count() - n0) // k
     with ops.Profile() as prof:
         step()

@@ -402,13 +402,13 @@ class PatchGeometry:
         from .layers import Packed
         full_lens = [h * w for h, w in self.dims]
         full = Packed(full_lens, device)
-        lens = torch.tensor(self.pk.lens, device=device)
-        img = torch.repeat_interleave(torch.arange(len(self.dims), device=device), lens)
+        lens = ops.upload_small(torch.tensor(self.pk.lens), device)
+        img = torch.repeat_interleave(torch.arange(len(self.dims), device=device), lens, output_size=self.pk.total)
         if self.patch_index is not None:
             p = self.patch_index.to(device=device, dtype=torch.int64)
         else:
             p = torch.arange(self.pk.total, device=device) - self.pk.cu.long()[img]
-        wp = torch.tensor([w for _, w in self.dims], device=device)[img]
+        wp = ops.upload_small(torch.tensor([w for _, w in self.dims]), device)[img]
         return full, full.cu.long()[img] + p, (p // wp) * pe_w + p % wp
 
 
@@ -475,7 +475,7 @@ class _MaeRestore(torch.autograd.Function):
         dout = dout.contiguous()
         total = dout.shape[0]
         cuk, cuf = cu_keep.long(), cu_full.long()
-        img = torch.repeat_interleave(torch.arange(cuf.numel() - 1, device=dev), cuf[1:] - cuf[:-1])
+        img = torch.repeat_interleave(torch.arange(cuf.numel() - 1, device=dev), cuf[1:] - cuf[:-1], output_size=total)
         i = torch.arange(total, device=dev) - cuf[img]
         r = ids_restore.long()
         kept = r < (cuk[1:] - cuk[:-1])[img]

@@ -58,25 +58,33 @@ class _WeightCache:
                 self._shadow[id(p)] = (p._version, p.data_ptr(), sh[2], sh[3])
             return sh[2] if rows is None else sh[2][rows[0]:rows[1]]
         key = (id(p), dtype, rows)
-        hit = self._store.get(key)
-        ver = (p._version, p.data_ptr(), self.generation)
-        if hit is not None and hit[0] == ver:
-            return hit[1]
+        hit = self._lookup(key, p)
+        if hit is not None:
+            return hit
         src = p.detach() if rows is None else p.detach()[rows[0]:rows[1]]
-        t = src.to(dtype).contiguous()
-        self._store[key] = (ver, t)
+        return self._insert(key, p, src.to(dtype).contiguous())
+
+    # An entry belongs to ONE parameter object: `id(p)` (and even its data pointer and version counter) come back once
+    # that parameter has been freed, so every entry carries a weak reference that must still resolve to `p`, and dies
+    # (releasing its device copy) with the parameter.
+    def _lookup(self, key, p):
+        hit = self._store.get(key)
+        if hit is not None and hit[2]() is p and hit[0] == (p._version, p.data_ptr(), self.generation):
+            return hit[1]
+        return None
+
+    def _insert(self, key, p, t):
+        store = self._store
+        self._store[key] = ((p._version, p.data_ptr(), self.generation), t, weakref.ref(p, lambda _r, k=key: store.pop(k, None)))
         return t
 
     def get_t(self, p: torch.Tensor, dtype: torch.dtype, rows=None):
         """Transposed copy [in, out] of (a row slice of) `p` in `dtype`: the B operand of dX = dY W."""
         key = (id(p), dtype, rows, "T")
-        hit = self._store.get(key)
-        ver = (p._version, p.data_ptr(), self.generation)
-        if hit is not None and hit[0] == ver:
-            return hit[1]
-        t = ops.transpose_pad(self.get(p, dtype, rows), pad_to=1)
-        self._store[key] = (ver, t)
-        return t
+        hit = self._lookup(key, p)
+        if hit is not None:
+            return hit
+        return self._insert(key, p, ops.transpose_pad(self.get(p, dtype, rows), pad_to=1))
 
     def clear(self):
         self._store.clear()

@@ -230,7 +230,7 @@ class MAE(nn.Module):
         dev = latent_packed.device
         full = Packed(info["unmasked_seq_lens"], dev)
         ids = torch.cat([r.to(dev) for r in info["ids_restore"]]).to(torch.int64).contiguous()
-        wps = torch.tensor([w for _, w in info["patchified_dims"]], dtype=torch.int32).to(dev)
+        wps = ops.upload_small(torch.tensor([w for _, w in info["patchified_dims"]], dtype=torch.int32), dev)
         rows = F.mae_restore(latent_packed, pk_keep.cu, full.cu, ids, wps, full.total, self.mask_token,
                              self.decoder_pos_embedding, out_dtype)
         return rows, full

@@ -382,12 +382,14 @@ def run_train(args, rank, world, device, kind):
         torch.distributed.barrier()
     k = max(3, min(args.steps, 10))
     n0 = ops.launch_count()
-    events = []
+    events, host_s = [], 0.0
     for _ in range(k):                                    # queued back to back: one synchronize after the last step
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        h0 = time.perf_counter()
         sums = step()
+        host_s += time.perf_counter() - h0
         e1.record()
         events.append((e0, e1))
     torch.cuda.synchronize()
@@ -421,7 +423,8 @@ def run_train(args, rank, world, device, kind):
                         "trainable_parameters": numel, "l2": "flushed between steps",
                         "collective": "one NCCL all-reduce of the flat fp32 gradient buffer per step" if world > 1 else "none (1 GPU)"},
                        **work),
-        "loss_last_step": loss, "gpu_launches_per_step": launches, "peak_mem_gib": round(peak_mem, 1),
+        "loss_last_step": loss, "gpu_launches_per_step": launches, "host_enqueue_ms_per_step": round(host_s / k * 1e3, 2),
+        "peak_mem_gib": round(peak_mem, 1),
         "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05 + gemm_wgrad_tcgen05", "achieved": g_fl / (g_ms * 1e-3) / 1e12,
                      "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                      "frac": g_fl / (g_ms * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"],

@@ -60,6 +60,24 @@ def main():
     ms = e0.elapsed_time(e1) / 3
     print(f"{ms:.2f} ms/step  {n / ms * 1e3:.1f} systems/s  {(ops.launch_count() - l0) // 3} launches/step  "
           f"loss {float(sums[0] / sums[1]):.4f}  peak mem {torch.cuda.max_memory_allocated() / 2**30:.1f} GiB", flush=True)
+    if os.environ.get("ACAI_PROF_HOST") == "1":           # where the HOST time of a step goes (kernels are asynchronous)
+        import cProfile
+        import pstats
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            step()
+        t1 = time.perf_counter()
+        torch.cuda.synchronize()
+        print("host enqueue %.2f ms/step, until idle %.2f ms/step" % ((t1 - t0) * 1e3 / 3, (time.perf_counter() - t0) * 1e3 / 3))
+        pr = cProfile.Profile()
+        pr.enable()
+        for _ in range(2):
+            step()
+        pr.disable()
+        torch.cuda.synchronize()
+        pstats.Stats(pr).sort_stats("tottime").print_stats(35)
+        return
     with ops.Profile() as prof:
         step()
     rows = sorted(prof.summary().items(), key=lambda kv: -kv[1]["ms"])

@@ -140,3 +140,27 @@ def test_mae_mask_indices_roundtrip():
     shuffled = torch.argsort(restore)
     assert torch.equal(shuffled[:n], keep) and torch.equal(shuffled[restore], torch.arange(40))
     assert torch.equal(seq_mask[keep], torch.zeros(10, dtype=torch.int))
+
+
+def test_weight_cache_entries_die_with_their_parameter():
+    """The low-precision weight copies are keyed by id(parameter): a freed parameter's id, data pointer and version
+    counter all come back for the next allocation, so an entry must never outlive (or be served to a successor of) its
+    parameter.  CPython reuses ids immediately in a loop like this one."""
+    import gc
+
+    import torch
+    from acai_omr_b200.layers import WEIGHTS
+    WEIGHTS.clear()
+    for i in range(200):
+        p = torch.nn.Parameter(torch.full((4, 8), float(i)))
+        c = WEIGHTS.get(p, torch.bfloat16)
+        assert c.dtype == torch.bfloat16 and float(c[0, 0]) == float(i), i
+        assert WEIGHTS.get(p, torch.bfloat16) is c                        # cached while the parameter lives
+        r = WEIGHTS.get(p, torch.bfloat16, rows=(1, 3))
+        assert r.shape == (2, 8) and float(r[0, 0]) == float(i)
+        with torch.no_grad():
+            p.add_(1.0)                                                   # in-place update: version bump -> refreshed
+        assert float(WEIGHTS.get(p, torch.bfloat16)[0, 0]) == float(i) + 1.0
+        del p, c, r
+    gc.collect()
+    assert len(WEIGHTS._store) == 0

@@ -4,6 +4,8 @@
 //   * decode_attn_simt : one query per (sequence, head) against a strided (B,H,T,d) cache.
 // These are the exact-fp32 / odd-shape path.  The tensor-core (tcgen05) varlen kernel and the
 // paged split-KV decode kernel for head_dim 64/32 live in attn_tc.cu / decode_paged.cu.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace acai {
@@ -141,7 +143,6 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
                    const int32_t* cu_q, const int32_t* cu_k, int batch, int max_q, int64_t total_q, int64_t total_k,
                    int heads, int head_dim, int causal, float scale, void* out, int out_dt, int64_t os, float* lse,
                    AttnDropout drop, cudaStream_t st);
-
 }  // namespace acai
 
 using namespace acai;

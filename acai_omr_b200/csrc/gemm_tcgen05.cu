@@ -181,19 +181,6 @@ __device__ __forceinline__ void epi_half(int act, const uint32_t (&acc)[32], con
   }
 }
 
-// Phi(z) = 0.5 (1 + erf(z / sqrt 2)) and e = exp(-z^2 / 2) for the training epilogues: Abramowitz-Stegun 7.1.26
-// (|error| < 1.5e-7, far below the bf16 output's rounding) costs two MUFU ops and ~10 FMAs, about a third of erff - the
-// epilogue warps have roughly 16 instruction slots per element before they become the GEMM's critical path.
-__device__ __forceinline__ void phi_and_pdf(float z, float& cdf, float& e) {
-  const float x = fabsf(z) * 0.70710678118654752440f;
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, x, 1.0f)));
-  e = __expf(-x * x);
-  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
-  const float q = 0.5f * poly * e;                     // 0.5 erfc(|z| / sqrt 2)
-  cdf = z >= 0.0f ? 1.0f - q : q;
-}
-
 // Training epilogues on 32 columns of this thread's row, 8 columns (one 16-byte staging piece) at a time:
 //   MODE 1 (ACT_GELU_TRAIN): pass 0 stages z = acc + bias, pass 1 stages h = dropout(gelu(bf16(z)));
 //   MODE 2 (ACT_GELU_BWD):   stages acc * gelu'(z) * mask with z in the (bf16) residual registers.

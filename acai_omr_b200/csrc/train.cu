@@ -38,13 +38,6 @@ colsum_partial_kernel(const void* __restrict__ x, int dt, int64_t ld, int rows, 
   for (int r = r0; r < r1; ++r) s += ld_as_float(x, (int64_t)r * ld + c, dt);
   part[(int64_t)blockIdx.y * cols + c] = s;
 }
-__global__ void colsum_final_kernel(const float* __restrict__ part, int slabs, int cols, float* __restrict__ out, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
-  float s = 0.0f;
-  for (int i = 0; i < slabs; ++i) s += part[(int64_t)i * cols + c];
-  out[c] = accumulate ? out[c] + s : s;
-}
 
 // bf16 fast path: a CTA covers 256 columns x one slab of CS_SLAB rows as 32 column groups (one 16-byte load = 8 columns
 // per thread) x 8 row lanes; the 8 row lanes are folded through shared memory in a fixed order.
@@ -145,7 +138,10 @@ gelu_fwd_bf16x8_kernel(const uint4* __restrict__ z, uint4* __restrict__ out, int
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float2 f = __bfloat1622float2(h[k]);
-      h[k] = __floats2bfloat162_rn(gelu_erf(f.x) * m[2 * k], gelu_erf(f.y) * m[2 * k + 1]);
+      float c0, c1, e;
+      phi_and_pdf(f.x, c0, e);
+      phi_and_pdf(f.y, c1, e);
+      h[k] = __floats2bfloat162_rn(f.x * c0 * m[2 * k], f.y * c1 * m[2 * k + 1]);
     }
     out[i] = u;
   }
@@ -164,7 +160,11 @@ gelu_bwd_bf16x8_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ z
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float2 f = __bfloat1622float2(h[k]), d = __bfloat1622float2(gh[k]);
-      h[k] = __floats2bfloat162_rn(d.x * gelu_grad(f.x) * m[2 * k], d.y * gelu_grad(f.y) * m[2 * k + 1]);
+      float c0, c1, e0, e1;
+      phi_and_pdf(f.x, c0, e0);
+      phi_and_pdf(f.y, c1, e1);
+      h[k] = __floats2bfloat162_rn(d.x * fmaf(f.x * 0.39894228040143267794f, e0, c0) * m[2 * k],
+                                   d.y * fmaf(f.y * 0.39894228040143267794f, e1, c1) * m[2 * k + 1]);
     }
     dz[i] = u;
   }
@@ -200,7 +200,7 @@ dropout_bf16x8_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res
 // LayerNorm backward for y = (v - mu) * rstd * gamma + beta with v = x (+ residual):
 //   dv = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma ;  dgamma = sum_rows dy * xhat ;  dbeta = sum_rows dy
 // One warp per row; each CTA (8 rows per pass, grid-stride) keeps per-column partial sums in registers and writes one
-// slab of partials, folded by colsum_final_kernel (fixed order).
+// slab of partials, folded by colsum_final_wide_kernel (fixed order).
 template <int NV>   // cols <= NV * 32; lane owns columns lane + 32 * i
 __global__ void __launch_bounds__(256)
 layernorm_bwd_kernel(const void* __restrict__ dy, int dy_dt, const void* __restrict__ x, int x_dt,
@@ -489,8 +489,8 @@ extern "C" int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t row
                                                                                         reinterpret_cast<float*>(workspace));
   int rc = launch_status("colsum_partial");
   if (rc) return rc;
-  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float*>(workspace), slabs, cols,
-                                                                           out, accumulate);
+  colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float*>(workspace), slabs, cols, out,
+                                                                             accumulate);
   return launch_status("colsum_final");
 }
 
@@ -558,8 +558,8 @@ extern "C" int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* 
 #undef LNV
     int rc2 = launch_status("layernorm_bwd_vec");
     if (rc2) return rc2;
-    colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pg, grid, cols, dgamma, accumulate);
-    colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pb2, grid, cols, dbeta, accumulate);
+    colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, st>>>(pg, grid, cols, dgamma, accumulate);
+    colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, st>>>(pb2, grid, cols, dbeta, accumulate);
     return launch_status("layernorm_bwd_reduce");
   }
   float* pb = pg + (size_t)slabs * cols;
@@ -569,8 +569,8 @@ extern "C" int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* 
 #undef LNB
   int rc = launch_status("layernorm_bwd");
   if (rc) return rc;
-  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pg, slabs, cols, dgamma, accumulate);
-  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, st>>>(pb, slabs, cols, dbeta, accumulate);
+  colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, st>>>(pg, slabs, cols, dgamma, accumulate);
+  colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, st>>>(pb, slabs, cols, dbeta, accumulate);
   return launch_status("layernorm_bwd_reduce");
 }
 

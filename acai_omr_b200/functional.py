@@ -221,13 +221,17 @@ class _LayerNorm(torch.autograd.Function):
     def forward(ctx, x, residual, gamma, beta, eps, out_dtype):
         y = ops.layernorm(x, gamma.detach(), beta.detach(), eps, residual=residual, out_dtype=out_dtype)
         ctx.save_for_backward(x, residual, gamma)
-        ctx.eps = eps
+        ctx.eps, ctx.beta_ref = eps, beta
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, residual, gamma = ctx.saved_tensors
-        dv, dg, db = ops.layernorm_bwd(dy, x, residual, gamma.detach(), ctx.eps, dv_dtype=x.dtype)
+        gg, gb = _owned_grad(gamma), _owned_grad(ctx.beta_ref)
+        if gg is not None and gb is not None and ctx.needs_input_grad[2] and ctx.needs_input_grad[3]:
+            dv, dg, db = ops.layernorm_bwd(dy, x, residual, gamma.detach(), ctx.eps, dv_dtype=x.dtype, dgamma_acc=gg, dbeta_acc=gb)
+        else:
+            dv, dg, db = ops.layernorm_bwd(dy, x, residual, gamma.detach(), ctx.eps, dv_dtype=x.dtype)
         dres = None
         if residual is not None and ctx.needs_input_grad[1]:
             dres = dv if residual.dtype == dv.dtype else dv.to(residual.dtype)

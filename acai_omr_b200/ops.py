@@ -590,23 +590,32 @@ def gelu_bwd(dy, z, out_dtype=None, dropout_p=0.0, dropout_seed=0):
     return dz
 
 
-def layernorm_bwd(dy, x, residual, gamma, eps, dv_dtype=None):
-    """-> (dv [rows, cols], dgamma fp32, dbeta fp32) for y = LN(x + residual) * gamma + beta."""
+def layernorm_bwd(dy, x, residual, gamma, eps, dv_dtype=None, dgamma_acc=None, dbeta_acc=None):
+    """-> (dv [rows, cols], dgamma fp32, dbeta fp32) for y = LN(x + residual) * gamma + beta.  With `dgamma_acc` /
+    `dbeta_acc` (fp32 [cols], both or neither) the parameter gradients are ADDED into them instead (no temporaries, no
+    add kernels) and returned as None."""
     _cuda(dy, x, residual, gamma)
     cols = x.shape[-1]
     x2, dy2 = x.reshape(-1, cols).contiguous(), dy.reshape(-1, cols).contiguous()
     r2 = residual.reshape(-1, cols).contiguous() if residual is not None else None
     rows = x2.shape[0]
     dv = torch.empty((rows, cols), dtype=dv_dtype or x.dtype, device=x.device)
-    dg = torch.empty(cols, dtype=torch.float32, device=x.device)
-    db = torch.empty(cols, dtype=torch.float32, device=x.device)
+    acc = dgamma_acc is not None and dbeta_acc is not None
+    if acc:
+        if not (dgamma_acc.dtype == dbeta_acc.dtype == torch.float32 and dgamma_acc.is_contiguous() and dbeta_acc.is_contiguous()
+                and dgamma_acc.numel() == cols and dbeta_acc.numel() == cols):
+            raise AcaiError("layernorm_bwd: accumulation targets must be contiguous fp32 [cols]")
+        dg, db = dgamma_acc, dbeta_acc
+    else:
+        dg = torch.empty(cols, dtype=torch.float32, device=x.device)
+        db = torch.empty(cols, dtype=torch.float32, device=x.device)
     lib = _lib.load()
     ws = _ws(lib.acai_layernorm_bwd_workspace_bytes(rows, cols), x.device)
     _call("acai_layernorm_bwd", lib.acai_layernorm_bwd, _p(dy2), _dt(dy2), _p(x2), _dt(x2), _p(r2),
-          _dt(r2) if r2 is not None else 0, _p(_f32c(gamma)), float(eps), _p(dv), _dt(dv), _p(dg), _p(db), 0, rows, cols,
-          _p(ws), ws.numel(), _stream())
+          _dt(r2) if r2 is not None else 0, _p(_f32c(gamma)), float(eps), _p(dv), _dt(dv), _p(dg), _p(db), 1 if acc else 0, rows,
+          cols, _p(ws), ws.numel(), _stream())
     _bump(2)
-    return dv.view(x.shape), dg, db
+    return (dv.view(x.shape), None, None) if acc else (dv.view(x.shape), dg, db)
 
 
 def attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, max_q, max_k, heads, head_dim, causal, dq, dk, dv, scale=None,

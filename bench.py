@@ -96,6 +96,16 @@ def host_images(num, seed0=0):
     return [synth.synth_system(h, w, seed0 + i) for i, (h, w) in enumerate(synth.system_shapes(num))]
 
 
+def gemm_traffic():
+    """DRAM bytes per GEMM launch from the committed ncu capture (profiles/r1g_gemm_traffic.json), or None."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1g_gemm_traffic.json")
+    try:
+        with open(path) as f:
+            return json.load(f)["mean_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def build_encoder(device):
     from acai_omr_b200 import synth
     from acai_omr_b200.models import models as M
@@ -229,7 +239,7 @@ def run_ours(args, rank, world, device):
         "gpu_launches": launches,
         "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05 (acai_linear_fwd)", "achieved": gemm_tflops,
                      "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                     "frac": gemm_tflops / peaks["bf16_tflops_sustained"], "traffic": None,
+                     "frac": gemm_tflops / peaks["bf16_tflops_sustained"], "traffic": gemm_traffic(),
                      "peak_source": peaks["source"] + " (sustained bf16, MEASURED_PEAKS.json)",
                      "kernel_share_of_step": g["ms"] / total_ms, "launches_per_step": g["launches"],
                      "whole_step_tflops": flops / (ms_step * 1e-3) / 1e12,

@@ -706,3 +706,34 @@ def test_feed_forward_node(dtype, tol, p, add_residual):
     assert rel_err(y, yr) < tol and rel_err(x.grad, xr.grad) < tol
     for got, want in zip((w1, b1, w2, b2), ps):
         assert rel_err(got.grad, want.grad) < tol
+
+
+def test_owned_gradients_match_autograd_accumulation():
+    """With a FlatTrainer the backward kernels add straight into the flat gradient buffer (Linear weights / biases,
+    LayerNorm gamma / beta); the result must equal what autograd's own accumulation produces, over two backward passes."""
+    from acai_omr_b200 import layers, train
+
+    def build():
+        torch.manual_seed(11)
+        m = torch.nn.Sequential()
+        m.add_module("fc", layers.Linear(64, 128))
+        m.add_module("ln", layers.LayerNorm(128))
+        m.add_module("out", layers.Linear(128, 64))
+        return m.to(DEV).train()
+
+    def run(m, x):
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            h = m.fc(x)
+            h = m.ln(h, out_dtype=torch.bfloat16)
+            y = m.out(h)
+        (y.float() ** 2).mean().backward()
+
+    x1, x2 = rnd(300, 64, seed=1), rnd(300, 64, seed=2)
+    plain = build()
+    run(plain, x1); run(plain, x2)                        # autograd accumulates .grad over the two passes
+    owned = build()
+    tr = train.FlatTrainer(owned, lr=1e-3)
+    tr.zero_grad()
+    run(owned, x1); run(owned, x2)
+    for (n, p), (_, q) in zip(plain.named_parameters(), owned.named_parameters()):
+        assert q.grad.data_ptr() >= tr.flat_grad.data_ptr() and rel_err(q.grad, p.grad) < 2e-3, n

@@ -125,75 +125,96 @@ __device__ __forceinline__ void dropout_factors8(uint64_t seed, int64_t i8, uint
     f[2 * k + 1] = (bits >> 16) >= thr ? rp : 0.0f;
   }
 }
-// bf16 fast paths: 8 elements (16 bytes) per thread per step
+// bf16 fast paths: 8 elements (16 bytes) per vector, TWO vectors per thread per step with both loads issued before any
+// math (one 16-byte load in flight per thread left these kernels at ~50 % of HBM peak)
+__device__ __forceinline__ uint4 gelu_fwd_vec(uint4 u, int64_t i, uint32_t thr, float rp, uint64_t seed) {
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+  float m[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) m[k] = 1.0f;
+  if (thr) dropout_factors8(seed, i, thr, rp, m);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 f = __bfloat1622float2(h[k]);
+    float c0, c1, e;
+    phi_and_pdf(f.x, c0, e);
+    phi_and_pdf(f.y, c1, e);
+    h[k] = __floats2bfloat162_rn(f.x * c0 * m[2 * k], f.y * c1 * m[2 * k + 1]);
+  }
+  return u;
+}
+__device__ __forceinline__ uint4 gelu_bwd_vec(uint4 u, uint4 g, int64_t i, uint32_t thr, float rp, uint64_t seed) {
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+  const __nv_bfloat162* gh = reinterpret_cast<const __nv_bfloat162*>(&g);
+  float m[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) m[k] = 1.0f;
+  if (thr) dropout_factors8(seed, i, thr, rp, m);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 f = __bfloat1622float2(h[k]), d = __bfloat1622float2(gh[k]);
+    float c0, c1, e0, e1;
+    phi_and_pdf(f.x, c0, e0);
+    phi_and_pdf(f.y, c1, e1);
+    h[k] = __floats2bfloat162_rn(d.x * fmaf(f.x * 0.39894228040143267794f, e0, c0) * m[2 * k],
+                                 d.y * fmaf(f.y * 0.39894228040143267794f, e1, c1) * m[2 * k + 1]);
+  }
+  return u;
+}
+__device__ __forceinline__ uint4 dropout_vec(uint4 u, uint4 r, bool has_res, int64_t i, uint32_t thr, float rp, uint64_t seed) {
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+  const __nv_bfloat162* rh = reinterpret_cast<const __nv_bfloat162*>(&r);
+  float m[8];
+  dropout_factors8(seed, i, thr, rp, m);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 f = __bfloat1622float2(h[k]);
+    const float2 g = has_res ? __bfloat1622float2(rh[k]) : make_float2(0.0f, 0.0f);
+    h[k] = has_res ? __floats2bfloat162_rn(fmaf(f.x, m[2 * k], g.x), fmaf(f.y, m[2 * k + 1], g.y))
+                   : __floats2bfloat162_rn(f.x * m[2 * k], f.y * m[2 * k + 1]);
+  }
+  return u;
+}
+
 __global__ void __launch_bounds__(256)
 gelu_fwd_bf16x8_kernel(const uint4* __restrict__ z, uint4* __restrict__ out, int64_t n8, uint32_t thr, float rp, uint64_t seed) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
-    uint4 u = z[i];
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
-    float m[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) m[k] = 1.0f;
-    if (thr) dropout_factors8(seed, i, thr, rp, m);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float2 f = __bfloat1622float2(h[k]);
-      float c0, c1, e;
-      phi_and_pdf(f.x, c0, e);
-      phi_and_pdf(f.y, c1, e);
-      h[k] = __floats2bfloat162_rn(f.x * c0 * m[2 * k], f.y * c1 * m[2 * k + 1]);
-    }
-    out[i] = u;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += 2 * stride) {
+    const int64_t j = i + stride;
+    const bool two = j < n8;
+    const uint4 u0 = z[i];
+    const uint4 u1 = two ? z[j] : make_uint4(0u, 0u, 0u, 0u);
+    out[i] = gelu_fwd_vec(u0, i, thr, rp, seed);
+    if (two) out[j] = gelu_fwd_vec(u1, j, thr, rp, seed);
   }
 }
 __global__ void __launch_bounds__(256)
 gelu_bwd_bf16x8_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ z, uint4* __restrict__ dz, int64_t n8, uint32_t thr,
                        float rp, uint64_t seed) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
-    uint4 u = z[i], g = dy[i];
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
-    const __nv_bfloat162* gh = reinterpret_cast<const __nv_bfloat162*>(&g);
-    float m[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) m[k] = 1.0f;
-    if (thr) dropout_factors8(seed, i, thr, rp, m);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float2 f = __bfloat1622float2(h[k]), d = __bfloat1622float2(gh[k]);
-      float c0, c1, e0, e1;
-      phi_and_pdf(f.x, c0, e0);
-      phi_and_pdf(f.y, c1, e1);
-      h[k] = __floats2bfloat162_rn(d.x * fmaf(f.x * 0.39894228040143267794f, e0, c0) * m[2 * k],
-                                   d.y * fmaf(f.y * 0.39894228040143267794f, e1, c1) * m[2 * k + 1]);
-    }
-    dz[i] = u;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += 2 * stride) {
+    const int64_t j = i + stride;
+    const bool two = j < n8;
+    const uint4 u0 = z[i], g0 = dy[i];
+    const uint4 u1 = two ? z[j] : make_uint4(0u, 0u, 0u, 0u), g1 = two ? dy[j] : make_uint4(0u, 0u, 0u, 0u);
+    dz[i] = gelu_bwd_vec(u0, g0, i, thr, rp, seed);
+    if (two) dz[j] = gelu_bwd_vec(u1, g1, j, thr, rp, seed);
   }
 }
-// residual + dropout(x), bf16, 8 elements per thread
+// residual + dropout(x), bf16
 __global__ void __launch_bounds__(256)
 dropout_bf16x8_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint4* __restrict__ out, int64_t n8, uint32_t thr,
                       float rp, uint64_t seed) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
-    uint4 u = x[i];
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
-    float m[8];
-    dropout_factors8(seed, i, thr, rp, m);
-    if (res) {
-      const uint4 r = res[i];
-      const __nv_bfloat162* rh = reinterpret_cast<const __nv_bfloat162*>(&r);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float2 f = __bfloat1622float2(h[k]), g = __bfloat1622float2(rh[k]);
-        h[k] = __floats2bfloat162_rn(fmaf(f.x, m[2 * k], g.x), fmaf(f.y, m[2 * k + 1], g.y));
-      }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float2 f = __bfloat1622float2(h[k]);
-        h[k] = __floats2bfloat162_rn(f.x * m[2 * k], f.y * m[2 * k + 1]);
-      }
-    }
-    out[i] = u;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const bool has_res = res != nullptr;
+  const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += 2 * stride) {
+    const int64_t j = i + stride;
+    const bool two = j < n8;
+    const uint4 u0 = x[i], r0 = has_res ? res[i] : zero;
+    const uint4 u1 = two ? x[j] : zero, r1 = (two && has_res) ? res[j] : zero;
+    out[i] = dropout_vec(u0, r0, has_res, i, thr, rp, seed);
+    if (two) out[j] = dropout_vec(u1, r1, has_res, j, thr, rp, seed);
   }
 }
 
@@ -284,7 +305,9 @@ __device__ __forceinline__ void store8(void* p, int dt, int64_t i, const float (
   }
 }
 
-template <int TPR>
+// PRE (x, dy and the residual are all bf16): the NEXT row's 16-byte pieces are loaded before the current row's three
+// group reductions, so every thread keeps two rows of HBM traffic in flight.
+template <int TPR, bool PRE>
 __global__ void __launch_bounds__(384)
 layernorm_bwd_vec_kernel(const void* __restrict__ dy, int dy_dt, const void* __restrict__ x, int x_dt,
                          const void* __restrict__ res, int res_dt, const float* __restrict__ gamma, float eps,
@@ -310,12 +333,36 @@ layernorm_bwd_vec_kernel(const void* __restrict__ dy, int dy_dt, const void* __r
     for (int w = 0; w < NW; ++w) { ra += red[w * 6 + slot]; rb += red[w * 6 + slot + 1]; }
   };
   const float inv_n = 1.0f / (float)cols;
+  const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+  uint4 nx = zero4, nd = zero4, nr = zero4;
+  auto fetch_raw = [&](int r) {
+    const int64_t b8 = ((int64_t)r * cols + c0) >> 3;
+    nx = __ldcs(reinterpret_cast<const uint4*>(x) + b8);
+    nd = __ldcs(reinterpret_cast<const uint4*>(dy) + b8);
+    if (res) nr = __ldcs(reinterpret_cast<const uint4*>(res) + b8);
+  };
+  auto unpack8 = [](const uint4& u, float (&f)[8]) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const float2 t2 = __bfloat1622float2(h[k]); f[2 * k] = t2.x; f[2 * k + 1] = t2.y; }
+  };
+  if (PRE && active && blockIdx.x * G + g < rows) fetch_raw(blockIdx.x * G + g);
   for (int row = blockIdx.x * G + g; row < rows; row += gridDim.x * G) {
     const int64_t base = (int64_t)row * cols + c0;
     float v[8], d[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) { v[k] = 0.0f; d[k] = 0.0f; }
-    if (active) {
+    if (PRE) {
+      if (active) {
+        unpack8(nx, v);
+        unpack8(nd, d);
+        if (res) { float r8[8]; unpack8(nr, r8);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] += r8[k]; }
+        const int next = row + gridDim.x * G;
+        if (next < rows) fetch_raw(next);
+      }
+    } else if (active) {
       load8(x, x_dt, base, v);
       if (res) { float r8[8]; load8(res, res_dt, base, r8);
 #pragma unroll
@@ -552,10 +599,13 @@ extern "C" int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* 
     grid = (rows + G - 1) / G < 2 * num_sms() ? (rows + G - 1) / G : 2 * num_sms();
     float* pb2 = pg + (size_t)grid * cols;
     const size_t shm = sizeof(float) * (size_t)(2 * G * cols > G * 4 * 6 ? 2 * G * cols : G * 4 * 6);
-#define LNV(T) layernorm_bwd_vec_kernel<T><<<grid, G * T, shm, st>>>(dy, dy_dtype, x, x_dtype, residual, res_dtype, gamma, eps, \
-                                                                    dv, dv_dtype, pg, pb2, rows, cols)
+    const bool pre = dy_dtype == ACAI_BF16 && x_dtype == ACAI_BF16 && (!residual || res_dtype == ACAI_BF16);
+#define LNV2(T, P) layernorm_bwd_vec_kernel<T, P><<<grid, G * T, shm, st>>>(dy, dy_dtype, x, x_dtype, residual, res_dtype, gamma, \
+                                                                          eps, dv, dv_dtype, pg, pb2, rows, cols)
+#define LNV(T) do { if (pre) LNV2(T, true); else LNV2(T, false); } while (0)
     if (tpr == 32) LNV(32); else if (tpr == 64) LNV(64); else if (tpr == 96) LNV(96); else LNV(128);
 #undef LNV
+#undef LNV2
     int rc2 = launch_status("layernorm_bwd_vec");
     if (rc2) return rc2;
     colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, st>>>(pg, grid, cols, dgamma, accumulate);

@@ -160,12 +160,28 @@ class MAEEncoder(Encoder):
         imgs = self._image_list(x)
         P, dev = self.patch_size, self.pos_embedding.device
         keep, restore, masks, keep_lens, full_lens, dims = [], [], [], [], [], []
-        for i, t in enumerate(imgs):
+        for t in imgs:
             h_p, w_p = t.shape[-2] // P, t.shape[-1] // P
             self._grid_check(h_p, w_p)
-            ids_keep, ids_restore, seq_mask, len_keep = self.mask_indices(h_p * w_p, dev, None if noises is None else noises[i])
-            keep.append(ids_keep); restore.append(ids_restore); masks.append(seq_mask)
-            keep_lens.append(len_keep); full_lens.append(h_p * w_p); dims.append((h_p, w_p))
+            full_lens.append(h_p * w_p); dims.append((h_p, w_p))
+            keep_lens.append(int(h_p * w_p * (1 - self.mask_ratio)))
+        if noises is None:
+            # all images at once: one uniform draw [B, L_max] with the padding pushed behind every real patch, two batched
+            # argsorts; the per-image index vectors below are views (the per-image loop cost ~6 tiny kernels per image)
+            L_max = max(full_lens)
+            lens_t = ops.upload_small(torch.tensor(full_lens, dtype=torch.int64), dev)
+            noise = torch.rand((len(imgs), L_max), device=dev)
+            noise.masked_fill_(torch.arange(L_max, device=dev)[None, :] >= lens_t[:, None], 2.0)
+            ids_shuffle = torch.argsort(noise, dim=1)
+            ids_restore = torch.argsort(ids_shuffle, dim=1)
+            seq_masks = (ids_restore >= ops.upload_small(torch.tensor(keep_lens, dtype=torch.int64), dev)[:, None]).to(torch.int)
+            for i, (L, lk) in enumerate(zip(full_lens, keep_lens)):
+                keep.append(ids_shuffle[i, :lk]); restore.append(ids_restore[i, :L]); masks.append(seq_masks[i, :L])
+        else:
+            for i, L in enumerate(full_lens):
+                ids_keep, ids_restore, seq_mask, len_keep = self.mask_indices(L, dev, noises[i])
+                assert len_keep == keep_lens[i]
+                keep.append(ids_keep); restore.append(ids_restore); masks.append(seq_mask)
         patch_index = torch.cat(keep).to(torch.int32)
         h, pk = self.embed_packed(imgs, keep=(keep_lens, patch_index))
         info = dict(imgs=imgs, kept_seq_lens=keep_lens, unmasked_seq_lens=full_lens, seq_masks=masks, ids_restore=restore,
@@ -437,10 +453,20 @@ class OMRDecoder(nn.Module):
 
 def batchify_and_split_lmx_seqs(lmx_seqs, pad_idx, device):
     """models.py:531-540 (host-side index bookkeeping; no arithmetic)."""
-    T = max(int(s.shape[0]) for s in lmx_seqs)
-    padded = torch.full((len(lmx_seqs), T), pad_idx, dtype=torch.long, device=lmx_seqs[0].device)
-    for i, s in enumerate(lmx_seqs):
-        padded[i, : s.shape[0]] = s
+    lens = [int(s.shape[0]) for s in lmx_seqs]
+    T = max(lens)
+    src_dev = lmx_seqs[0].device
+    padded = torch.full((len(lmx_seqs), T), pad_idx, dtype=torch.long, device=src_dev)
+    if src_dev.type == "cuda" and len(lmx_seqs) > 1:
+        # one concatenation + one scatter instead of a copy kernel per sequence; the (row, column) tables are built on
+        # the host from the lengths and uploaded asynchronously
+        lens_t = torch.tensor(lens)
+        rows = torch.repeat_interleave(torch.arange(len(lens)), lens_t)
+        cols = torch.arange(int(lens_t.sum())) - torch.repeat_interleave(torch.cumsum(lens_t, 0) - lens_t, lens_t)
+        padded[ops.upload_small(rows, src_dev), ops.upload_small(cols, src_dev)] = torch.cat([s.to(torch.long) for s in lmx_seqs])
+    else:
+        for i, s in enumerate(lmx_seqs):
+            padded[i, : s.shape[0]] = s
     input_seqs, target_seqs = padded[:, :-1], padded[:, 1:]
     lmx_attention_mask = (input_seqs == pad_idx).to(device)
     return input_seqs, target_seqs, lmx_attention_mask

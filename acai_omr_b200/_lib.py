@@ -71,6 +71,7 @@ SIGNATURES = {
                                _i32, _i64, _p, _sz, _i64, _p],
     "acai_decode_embed": [_p, _i64, _p, _i32, _p, _p, _p, _i32, _i32, _p],
     "acai_greedy_update": [_p, _i32, _i64, _i32, _i32, _p, _p, _i64, _p, _p, _i32, _p],
+    "acai_topk_sample_update": [_p, _i32, _i64, _i32, _i32, _i32, _f32, _p, _i64, _p, _p, _p, _i64, _p, _p, _i32, _p],
     "acai_advance_step": [_p, _p],
     "acai_embed_tokens": [_p, _i32, _p, _p, _p, _i32, _i32, _p, _i32, _i32, _p],
     "acai_argmax_logprob": [_p, _i32, _i64, _i32, _i32, _p, _p, _p],

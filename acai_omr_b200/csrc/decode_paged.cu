@@ -222,6 +222,75 @@ __global__ void greedy_update_kernel(const void* __restrict__ logits, int dt, in
   }
 }
 
+// GRPO rollout step (GRPOViTOMR.cached_forward_rollout_policy, models.py:1003-1029): keep the top_k logits of the row,
+// draw the next token from softmax(top_k_logits / temperature), record log_softmax(top_k_logits)[token] (WITHOUT the
+// temperature, as the reference's cached path does).  One warp per row; the row is staged in shared memory.  Top-k
+// membership is exact: element c is kept when fewer than top_k elements beat it (larger value, or equal value and lower
+// index).  The draw is an inverse-CDF walk over the kept tokens in vocabulary order with a uniform u in [0, 1) that is
+// either supplied (uniforms[row, step]: parity tests) or hashed from (*seed_ptr, row, step) - any walk order samples the
+// same distribution as torch.multinomial; its random stream is not reproducible bit for bit.
+__global__ void topk_sample_update_kernel(const void* __restrict__ logits, int dt, int64_t ld, int rows, int vocab, int top_k,
+                                          float inv_temperature, const float* __restrict__ uniforms, int64_t u_stride,
+                                          const uint64_t* __restrict__ seed_ptr, const int32_t* __restrict__ step_ptr,
+                                          int64_t* __restrict__ seqs, int64_t seq_stride, float* __restrict__ logp,
+                                          uint8_t* __restrict__ finished, int eos) {
+  extern __shared__ float zs[];                                 // [warps][vocab]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (row >= rows) return;
+  float* z = zs + (size_t)warp * vocab;
+  float mx = -INFINITY;
+  for (int c = lane; c < vocab; c += 32) { const float v = ld_as_float(logits, (int64_t)row * ld + c, dt); z[c] = v; mx = fmaxf(mx, v); }
+  mx = warp_max(mx);
+  __syncwarp();
+  // pass 1: rank every element against the row; the element of rank top_k - 1 is the membership threshold
+  float sum_t = 0.0f, sum_1 = 0.0f, thr_v = -INFINITY;
+  int thr_c = -1;
+  for (int c = lane; c < vocab; c += 32) {
+    const float v = z[c];
+    int rank = 0;
+    for (int j = 0; j < vocab; ++j) { const float o = z[j]; rank += (o > v || (o == v && j < c)) ? 1 : 0; }
+    if (rank < top_k) { sum_t += __expf((v - mx) * inv_temperature); sum_1 += __expf(v - mx); }
+    if (rank == top_k - 1) { thr_v = v; thr_c = c; }
+  }
+  sum_t = warp_sum(sum_t); sum_1 = warp_sum(sum_1);
+  {
+    const unsigned owner = __ballot_sync(0xffffffffu, thr_c >= 0);       // exactly one lane holds the threshold element
+    const int src = __ffs(owner) - 1;
+    thr_v = __shfl_sync(0xffffffffu, thr_v, src);
+    thr_c = __shfl_sync(0xffffffffu, thr_c, src);
+  }
+  const int t = *step_ptr;
+  float u;
+  if (uniforms) u = uniforms[(int64_t)row * u_stride + t];
+  else u = (float)(dropout_bits(*seed_ptr, ((uint64_t)row << 24) + (uint64_t)t) >> 8) * (1.0f / 16777216.0f);
+  const float target = u * sum_t;
+  // pass 2: inverse-CDF walk in vocabulary order
+  float base = 0.0f;
+  int chosen = -1, last_kept = -1;
+  for (int c0 = 0; c0 < vocab && chosen < 0; c0 += 32) {
+    const int c = c0 + lane;
+    const float v = c < vocab ? z[c] : -INFINITY;
+    const bool keep = c < vocab && (v > thr_v || (v == thr_v && c <= thr_c));
+    float w = keep ? __expf((v - mx) * inv_temperature) : 0.0f;
+    float cum = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const float n = __shfl_up_sync(0xffffffffu, cum, o); if (lane >= o) cum += n; }
+    cum += base;
+    const unsigned hit = __ballot_sync(0xffffffffu, keep && cum > target);
+    const unsigned kept = __ballot_sync(0xffffffffu, keep);
+    if (kept) last_kept = c0 + 31 - __clz(kept);
+    if (hit) chosen = c0 + __ffs(hit) - 1;
+    base = __shfl_sync(0xffffffffu, cum, 31);
+  }
+  if (chosen < 0) chosen = last_kept;                            // u * sum rounded past the last bucket
+  if (lane == 0) {
+    seqs[(int64_t)row * seq_stride + t] = chosen;
+    logp[(int64_t)row * seq_stride + t] = (z[chosen] - mx) - __logf(sum_1);
+    if (chosen == eos) finished[row] = 1;
+  }
+}
+
 __global__ void advance_step_kernel(int32_t* step_ptr) { *step_ptr += 1; }
 
 }  // namespace acai
@@ -303,6 +372,22 @@ extern "C" int acai_greedy_update(const void* logits, int32_t dtype, int64_t ld,
   greedy_update_kernel<<<(rows + 3) / 4, 128, 0, (cudaStream_t)stream>>>(logits, dtype, ld, rows, vocab, step_ptr, seqs,
                                                                         seq_stride, log_probs, finished, eos_idx);
   return launch_status("greedy_update");
+}
+
+extern "C" int acai_topk_sample_update(const void* logits, int32_t dtype, int64_t ld, int32_t rows, int32_t vocab, int32_t top_k,
+                                       float temperature, const float* uniforms, int64_t uniforms_stride,
+                                       const uint64_t* seed_ptr, const int32_t* step_ptr, int64_t* seqs, int64_t seq_stride,
+                                       float* log_probs, uint8_t* finished, int32_t eos_idx, void* stream) {
+  ACAI_CHECK_ARG(logits && step_ptr && seqs && log_probs && finished && rows > 0 && vocab > 0 && dtype_valid(dtype),
+                 "acai_topk_sample_update: bad argument");
+  ACAI_CHECK_ARG(top_k >= 1 && temperature > 0.0f && (uniforms || seed_ptr), "acai_topk_sample_update: top_k >= 1, temperature > 0 and a "
+                 "source of randomness (uniforms or seed_ptr) are required");
+  ACAI_CHECK_ARG(vocab <= 8192, "acai_topk_sample_update: vocab %d > 8192 does not fit the shared-memory row buffer", vocab);
+  const int warps = vocab <= 2048 ? 4 : 1;
+  topk_sample_update_kernel<<<(rows + warps - 1) / warps, warps * 32, (size_t)warps * vocab * sizeof(float), (cudaStream_t)stream>>>(
+      logits, dtype, ld, rows, vocab, top_k < vocab ? top_k : vocab, 1.0f / temperature, uniforms, uniforms_stride, seed_ptr, step_ptr,
+      seqs, seq_stride, log_probs, finished, eos_idx);
+  return launch_status("topk_sample_update");
 }
 
 extern "C" int acai_advance_step(int32_t* step_ptr, void* stream) {

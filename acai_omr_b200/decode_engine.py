@@ -54,6 +54,11 @@ class GreedyDecodeEngine:
         self.ws_cross = None
         self.graph = None
         self.launches_per_step = 0
+        # sampling mode (GRPO rollouts): None = greedy; else (top_k, temperature).  The seed is device state so that the
+        # captured graph draws a new stream per rollout; `uniforms` (fp32 [B, max_len]) replaces the hash in parity tests.
+        self.sampling = None
+        self.seed = torch.zeros(1, dtype=torch.int64, device=device)
+        self.uniforms = None
 
     # ---- one decode step (what the graph captures) ------------------------------------------------------------
     def _step(self):
@@ -75,7 +80,11 @@ class GreedyDecodeEngine:
         if dec.decoder_blocks.norm is not None:
             x = dec.decoder_blocks.norm(x, out_dtype=dt)
         logits = ops.linear(x, w_(dec.unembed.weight, dt), dec.unembed.bias, out_dtype=dt)
-        ops.greedy_update(logits, self.step, self.seqs, self.logp, self.finished, dec.eos_idx)
+        if self.sampling is None:
+            ops.greedy_update(logits, self.step, self.seqs, self.logp, self.finished, dec.eos_idx)
+        else:
+            ops.topk_sample_update(logits, self.step, self.seqs, self.logp, self.finished, dec.eos_idx, self.sampling[0],
+                                   self.sampling[1], seed=self.seed, uniforms=self.uniforms)
         ops.advance_step(self.step)
 
     def _reset(self):
@@ -100,6 +109,22 @@ class GreedyDecodeEngine:
             self.max_mem_len = max(mp.max_len, self.max_mem_len)
             self.ws_cross = ops.decode_workspace(self.B, self.H, self.max_mem_len, self.device)
             self.graph = None
+
+    def set_sampling(self, sampling, seed=0, uniforms=None):
+        """sampling = None (greedy) or (top_k, temperature).  Changing the mode or the uniforms buffer re-captures the
+        graph; changing only the seed does not."""
+        if sampling is not None:
+            sampling = (int(sampling[0]), float(sampling[1]))
+        if uniforms is not None:
+            if self.uniforms is None or self.uniforms.shape != (self.B, self.max_len):
+                self.uniforms = torch.empty((self.B, self.max_len), dtype=torch.float32, device=self.device)
+                self.graph = None
+            self.uniforms[:, : uniforms.shape[1]].copy_(uniforms)
+        elif self.uniforms is not None:
+            self.uniforms, self.graph = None, None
+        if sampling != self.sampling:
+            self.sampling, self.graph = sampling, None
+        self.seed.fill_(int(seed) & 0x7FFFFFFFFFFFFFFF)
 
     def generate(self, stop_early=True):
         """Run steps t = 1 .. max_len-1 (or until every row has emitted <eos>); returns raw (seqs, log_probs)."""
@@ -133,8 +158,9 @@ def get_engine(vitomr, decoder, batch, max_len, mem_rows, dt, device):
     return eng
 
 
-def greedy_generate(vitomr, img_latent, latent_attention_mask, max_len, stop_early=True):
-    """Fast path of ViTOMR.cached_greedy_generate; returns None when the decoder does not qualify."""
+def greedy_generate(vitomr, img_latent, latent_attention_mask, max_len, stop_early=True, sampling=None, seed=0, uniforms=None):
+    """Fast path of ViTOMR.cached_greedy_generate (and, with `sampling` = (top_k, temperature), of
+    GRPOViTOMR.cached_forward_rollout_policy); returns None when the decoder does not qualify."""
     dec = vitomr.decoder
     dt = compute_dtype()
     if not img_latent.is_cuda or not eligible(dec, dt) or max_len > dec.max_lmx_seq_len or max_len < 2:
@@ -146,5 +172,6 @@ def greedy_generate(vitomr, img_latent, latent_attention_mask, max_len, stop_ear
     mem, mp = dec._memory_packed(img_latent, latent_attention_mask, dt)
     eng = get_engine(vitomr, dec, B, max_len, mp.total, dt, img_latent.device)
     eng.prefill(mem, mp)
+    eng.set_sampling(sampling, seed, uniforms)
     seqs, logp = eng.generate(stop_early=stop_early)
     return seqs.clone(), logp.clone()

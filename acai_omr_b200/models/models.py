@@ -674,6 +674,117 @@ class ScheduledSamplingViTOMR(TeacherForcedViTOMR):
         return super().forward(x)
 
 
+class GRPOViTOMR(ViTOMR):
+    """models.py:840-1049: the ViTOMR prepared for GRPO - a full (non-fine-tune) encoder and the transition head frozen
+    with their dropout off, weights taken from a TeacherForcedViTOMR state dict, and the rollout policy: top-k filtering,
+    temperature softmax and one multinomial draw per decode step.  The cached rollout runs on the CUDA-graphed decode
+    engine with the draw done on the device (`acai_topk_sample_update`), so a rollout has no per-step host round trip."""
+
+    def __init__(self, encoder, transition_head, decoder, teacher_forced_state_dict):
+        super().__init__(encoder, transition_head, decoder)
+        if isinstance(self.encoder, FineTuneOMREncoder):
+            teacher_forced_state_dict = self.convert_teacher_forced_state_dict(teacher_forced_state_dict,
+                                                                               encoder.num_frozen_layers)
+            e = self.encoder
+            self.encoder = OMREncoder(e.patch_size, e.pe_max_height, e.pe_max_width, e.num_layers, e.hidden_dim,
+                                      **encoder.superclass_kwargs)
+        self.load_state_dict(teacher_forced_state_dict)
+        self.freeze_component(self.encoder)
+        self.freeze_component(self.transition_head)
+
+    def freeze_component(self, component):
+        """models.py:855-860: no gradients, no dropout (nn.Dropout children and this package's `dropout_p` attributes)."""
+        for param in component.parameters():
+            param.requires_grad = False
+        for child in component.modules():
+            if isinstance(child, nn.Dropout):
+                child.p = 0.0
+            if hasattr(child, "dropout_p"):
+                child.dropout_p = 0.0
+
+    def convert_teacher_forced_state_dict(self, teacher_forced_state_dict, num_frozen_layers):
+        """models.py:862-882: `frozen_blocks.layers.N` -> `encoder_blocks.layers.N`, `fine_tune_blocks.layers.N` ->
+        `encoder_blocks.layers.(N + num_frozen_layers)`, the stack's final norm just renamed."""
+        out = {}
+        for name, value in teacher_forced_state_dict.items():
+            if "frozen_blocks" in name:
+                name = name.replace("frozen_blocks", "encoder_blocks")
+            elif "fine_tune_blocks" in name:
+                m = re.search(r"fine_tune_blocks\.layers\.(\d+)\.", name)
+                name = name.replace("fine_tune_blocks", "encoder_blocks")
+                if m is not None:
+                    n = int(m.group(1))
+                    name = name.replace(f"layers.{n}.", f"layers.{n + num_frozen_layers}.", 1)
+            out[name] = value
+        return out
+
+    def expand_img_latent_for_rollout(self, img_latent, latent_attention_mask, group_size):
+        """models.py:885-894: every latent (and its mask row) repeated `group_size` times, groups contiguous."""
+        B, T, E = img_latent.shape
+        latent = img_latent.unsqueeze(1).expand(B, group_size, T, E).flatten(0, 1)
+        mask = latent_attention_mask.unsqueeze(1).expand(B, group_size, T).flatten(0, 1)
+        lens = getattr(latent_attention_mask, "_acai_lens", None)
+        if lens is not None:                                   # keeps the no-sync re-packing path of the decoder alive
+            mask = mask.contiguous()
+            mask._acai_lens = [v for v in lens for _ in range(group_size)]
+        return latent, mask
+
+    def _finish_rollouts(self, rollouts, rollout_log_probs):
+        """models.py:1031-1049: mask after the first <eos>, clip to the longest rollout."""
+        rollout_mask = self.create_inference_mask(rollouts)
+        rollouts = rollouts.masked_fill(~rollout_mask, self.decoder.pad_idx)
+        max_rollout_len = int(torch.max(rollout_mask.sum(dim=-1)))
+        rollouts, rollout_log_probs = rollouts[:, :max_rollout_len], rollout_log_probs[:, :max_rollout_len]
+        rollout_mask = rollout_mask[:, :max_rollout_len]
+        return rollouts, rollout_log_probs.masked_fill(~rollout_mask, 0.0), rollout_mask
+
+    def cached_forward_rollout_policy(self, img_latent, latent_attention_mask, max_actions=768, top_k=50, temperature=1.2,
+                                      seed=None, uniforms=None):
+        """models.py:991-1049.  `seed` (int) makes a rollout replayable; `uniforms` (fp32 [R, max_actions], entry [r, t]
+        drives the draw of token t) replaces the random stream entirely (parity tests)."""
+        from ..decode_engine import greedy_generate
+        if seed is None:
+            seed = ops.DropoutState.next_seed()
+        if uniforms is not None:
+            uniforms = uniforms.to(device=img_latent.device, dtype=torch.float32).contiguous()
+        fast = greedy_generate(self, img_latent, latent_attention_mask, max_actions, sampling=(top_k, temperature), seed=seed,
+                               uniforms=uniforms)
+        if fast is not None:
+            return self._finish_rollouts(*fast)
+        # generic path (any head_dim / cache dtype): module-level cached API, the draw still on the device
+        rollouts, log_probs, finished = self.cached_set_up_inference(img_latent, max_actions)
+        finished = finished.to(torch.uint8)
+        seed_t = torch.full((1,), int(seed) & 0x7FFFFFFFFFFFFFFF, dtype=torch.int64, device=img_latent.device)
+        step = torch.zeros(1, dtype=torch.int32, device=img_latent.device)
+        for t in range(1, max_actions):
+            logits = self.decoder.cached_generate(rollouts[:, t - 1].unsqueeze(1), t, latent_attention_mask=latent_attention_mask)
+            step.fill_(t)
+            ops.topk_sample_update(logits.squeeze(1), step, rollouts, log_probs, finished, self.decoder.eos_idx, top_k,
+                                   temperature, seed=seed_t, uniforms=uniforms)
+            if t % self.EOS_POLL_INTERVAL == 0 and bool(finished.all()):
+                break
+        return self._finish_rollouts(rollouts, log_probs)
+
+    forward_rollout_policy = cached_forward_rollout_policy
+
+    def prepare_rollouts_for_policy_theta(self, rollouts, rollout_mask):
+        """models.py:949-958: right-shifted rollouts and their True = padding attention mask."""
+        lens = rollout_mask.sum(dim=-1, keepdim=True) - 1
+        pos = torch.arange(int(torch.max(lens)), device=rollouts.device).repeat([rollouts.shape[0], 1])
+        return rollouts[:, :-1], pos >= lens
+
+    def forward_teacher_forced(self, img_latent, latent_attention_mask, lmx_seqs, checkpoint_grads=False):
+        """models.py:963-967."""
+        input_seqs, target_seqs, lmx_attention_mask = batchify_and_split_lmx_seqs(lmx_seqs, self.decoder.pad_idx, img_latent.device)
+        pred = self.decoder(input_seqs, img_latent, lmx_attention_mask, latent_attention_mask, checkpoint_grads=checkpoint_grads)
+        return pred, target_seqs
+
+    def batch_policy_inference(self, imgs, max_actions, top_k, temperature):
+        """models.py:971-974 (one rollout per image; the caller applies the transition head as the reference does)."""
+        img_latent, latent_attention_mask = self.encoder(imgs)
+        return self.forward_rollout_policy(img_latent, latent_attention_mask, max_actions, top_k, temperature)
+
+
 class OMRCELoss(nn.Module):
     """models.py:784-796: token-level cross entropy over non-pad targets (acai_ce_loss forward + backward)."""
 

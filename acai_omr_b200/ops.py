@@ -402,6 +402,24 @@ def greedy_update(logits, step, seqs, log_probs, finished, eos_idx):
           seqs.stride(0), _p(log_probs), _p(finished), int(eos_idx), _stream())
 
 
+def topk_sample_update(logits, step, seqs, log_probs, finished, eos_idx, top_k, temperature, seed=None, uniforms=None):
+    """One GRPO rollout step on the device (acai_topk_sample_update): top-k filter, temperature softmax, one draw per
+    row.  `seed`: 1-element int64 device tensor (hashed with row and step); `uniforms`: fp32 [rows, >= seqs.shape[1]]
+    explicit draws in [0, 1) (tests)."""
+    _cuda(logits, step, seqs, log_probs, finished, seed, uniforms)
+    if seed is None and uniforms is None:
+        raise AcaiError("topk_sample_update: pass a device seed tensor or explicit uniforms")
+    l2, rows, vocab, ld = _rows2d(logits)
+    if uniforms is not None and (uniforms.dtype != torch.float32 or uniforms.stride(-1) != 1 or uniforms.shape[0] != rows):
+        raise AcaiError("topk_sample_update: uniforms must be fp32 [rows, steps] with a unit inner stride")
+    if seed is not None and (seed.dtype != torch.int64 or seed.numel() != 1):
+        raise AcaiError("topk_sample_update: seed must be a 1-element int64 device tensor")
+    lib = _lib.load()
+    _call("acai_topk_sample_update", lib.acai_topk_sample_update, _p(l2), _dt(l2), ld, rows, vocab, int(top_k), float(temperature),
+          _p(uniforms), uniforms.stride(0) if uniforms is not None else 0, _p(seed), _p(step), _p(seqs), seqs.stride(0),
+          _p(log_probs), _p(finished), int(eos_idx), _stream())
+
+
 def advance_step(step):
     _cuda(step)
     lib = _lib.load()

@@ -168,6 +168,17 @@ int acai_decode_attn_paged(const void* q, int64_t q_stride, const void* new_kv, 
                                                      bf16 streaming kernel); 0 = unknown -> register kernel */
                            void* stream);
 
+/* GRPO rollout step: GRPOViTOMR.cached_forward_rollout_policy models.py:1003-1029 (torch.topk, softmax(top_k_logits /
+ * temperature), torch.multinomial, log_softmax(top_k_logits).gather) for every row of `logits` [rows, vocab], device-step
+ * variant like acai_greedy_update: writes seqs[row, *step_ptr], log_probs[row, *step_ptr], sets finished[row] on <eos>.
+ * Randomness: `uniforms` (fp32 [rows, uniforms_stride], entry [row, *step_ptr] in [0, 1)) when given, else a counter-based
+ * hash of (*seed_ptr, row, *step_ptr) - the seed lives on the device so that a captured CUDA graph can be replayed with a
+ * new seed per rollout.  The token is drawn by inverse CDF over the kept tokens in vocabulary order. */
+int acai_topk_sample_update(const void* logits, int32_t dtype, int64_t ld, int32_t rows, int32_t vocab, int32_t top_k,
+                            float temperature, const float* uniforms, int64_t uniforms_stride, const uint64_t* seed_ptr,
+                            const int32_t* step_ptr, int64_t* seqs, int64_t seq_stride, float* log_probs, uint8_t* finished,
+                            int32_t eos_idx, void* stream);
+
 /* Greedy-loop bookkeeping driven by the device-side step counter t = *step_ptr (models.py:575-583, 603-610):
  *   acai_decode_embed : out[b] = table[seqs[b, t-1]] + pos[t]   (time_step = t for the token at t-1, models.py:576)
  *   acai_greedy_update: seqs[b, t] = argmax(logits[b]); log_probs[b, t] = log_softmax(logits[b])[argmax];

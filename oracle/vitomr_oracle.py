@@ -463,3 +463,76 @@ def scheduled_sampling_forward(batch, sd, cfg, tf_prob, tau, hard, rand, gumbel)
     mixed = torch.where(sample_mask.unsqueeze(-1), expected, gold)
     pred = decoder_forward_embeddings(mixed, lat, dec_sd, cfg["decoder_heads"], lmx_mask, lat_mask)
     return pred, tgt
+
+
+# ------------------------------------------------------------------------------------------ GRPO
+def topk_sample_step(logits, top_k, temperature, u):
+    """One step of GRPOViTOMR.cached_forward_rollout_policy (models.py:1003-1029) for a (R, V) fp32 logits matrix with the
+    multinomial draw written out: keep the top_k logits of each row (ties: lower index first), p = softmax(kept /
+    temperature), the token is the first kept index (in vocabulary order) whose cumulative probability exceeds u[r]
+    (inverse CDF - the same distribution torch.multinomial samples), log-prob = log_softmax(kept logits)[token] without
+    the temperature.  Pure-Python loops: small cases only."""
+    R, V = logits.shape
+    toks, lps = [], []
+    for r in range(R):
+        row = [float(v) for v in logits[r]]
+        order = sorted(range(V), key=lambda c: (-row[c], c))[: min(top_k, V)]
+        kept = sorted(order)
+        mx = max(row[c] for c in kept)
+        w = [math.exp((row[c] - mx) / temperature) for c in kept]
+        target, cum, choice = float(u[r]) * sum(w), 0.0, kept[-1]
+        for c, wc in zip(kept, w):
+            cum += wc
+            if cum > target:
+                choice = c
+                break
+        toks.append(choice)
+        lps.append((row[choice] - mx) - math.log(sum(math.exp(row[c] - mx) for c in kept)))
+    return torch.tensor(toks, dtype=torch.long), torch.tensor(lps, dtype=torch.float32)
+
+
+def cached_forward_rollout_policy(memory, sd, H, uniforms, mem_pad_mask=None, max_actions=768, top_k=50, temperature=1.2,
+                                  pad_idx=1, bos_idx=0, eos_idx=2):
+    """GRPOViTOMR.cached_forward_rollout_policy (models.py:991-1049) with the draws supplied: uniforms[r, t] drives
+    token t.  Same cached decoder step (and `time_step = t` quirk) as cached_greedy_generate above."""
+    R = memory.shape[0]
+    st = prepare_caches(memory, sd, H)
+    rollouts = torch.full((R, max_actions), pad_idx, dtype=torch.long)
+    rollouts[:, 0] = bos_idx
+    logp = torch.zeros(R, max_actions, dtype=torch.float32)
+    finished = torch.zeros(R, dtype=torch.bool)
+    for t in range(1, max_actions):
+        logits = cached_generate(rollouts[:, t - 1 : t], t, st, sd, H, mem_pad_mask).squeeze(1)
+        tok, lp = topk_sample_step(logits.float(), top_k, temperature, uniforms[:, t])
+        rollouts[:, t] = tok
+        logp[:, t] = lp
+        finished |= tok == eos_idx
+        if bool(finished.all()):
+            break
+    m = create_inference_mask(rollouts, eos_idx)
+    rollouts = rollouts.masked_fill(~m, pad_idx)
+    n = int(m.sum(dim=-1).max())
+    rollouts, logp, m = rollouts[:, :n], logp[:, :n], m[:, :n]
+    return rollouts, logp.masked_fill(~m, 0.0), m
+
+
+def grpo_objective(theta_logits, rollouts, rollout_attention_mask, old_policy_log_probs, advantages, epsilon, num_groups):
+    """omr_grpo_train.py:240-262, statement by statement."""
+    theta_log_probs = torch.log_softmax(theta_logits, dim=-1)
+    theta_log_probs = torch.gather(theta_log_probs, dim=-1, index=rollouts[:, 1:].unsqueeze(-1)).squeeze(-1)
+    ratios = torch.exp(theta_log_probs - old_policy_log_probs[:, 1:])
+    unclipped = ratios * advantages.unsqueeze(1)
+    clipped = torch.clip(ratios, min=1 - epsilon, max=1 + epsilon) * advantages.unsqueeze(1)
+    unclipped = unclipped.masked_fill(rollout_attention_mask, 0)
+    clipped = clipped.masked_fill(rollout_attention_mask, 0)
+    lens = (~rollout_attention_mask).sum(dim=-1)
+    obj = torch.sum(torch.min(unclipped, clipped), dim=-1) / lens
+    return torch.sum(obj) / num_groups
+
+
+def entropy_bonus(theta_logits, rollout_attention_mask, vocab_size):
+    """omr_grpo_train.py:265-282."""
+    probs = torch.softmax(theta_logits, dim=-1)
+    ent = (-probs * torch.log_softmax(theta_logits, dim=-1)).sum(dim=-1).masked_fill(rollout_attention_mask, 0)
+    ent = ent.sum(dim=-1) / (~rollout_attention_mask).sum(dim=-1)
+    return ent.mean() / torch.log(torch.tensor(float(vocab_size)))

@@ -34,3 +34,9 @@ def golden_grads():
     """Parameter gradients of the unmodified reference for the golden_small.pt training steps
     (tests/golden/make_golden_grads.py)."""
     return torch.load(os.path.join(ROOT, "tests", "golden", "golden_grads.pt"), map_location="cpu", weights_only=False)
+
+
+@pytest.fixture(scope="session")
+def golden_grpo():
+    """GRPO rollouts / objective of the unmodified reference (tests/golden/make_golden_grpo.py)."""
+    return torch.load(os.path.join(ROOT, "tests", "golden", "golden_grpo.pt"), map_location="cpu", weights_only=False)

@@ -179,3 +179,37 @@ def test_scheduled_sampling_forward_and_gradients_match_reference(golden, golden
         assert torch.allclose(loss.detach(), gg["loss"], **TOL)
         loss.backward()
         _check_grads(sd, gg["grads"], dict(atol=2e-5, rtol=1e-3))
+
+
+# ------------------------------------------------------------------------------------------ GRPO
+def test_grpo_objective_restatements_match_reference(golden_grpo):
+    """oracle.grpo_objective / entropy_bonus and the product-side acai_omr_b200.grpo functions against the values the
+    reference's own calc_grpo_objective / calc_entropy_bonus produced, including the gradient w.r.t. the logits."""
+    from acai_omr_b200 import grpo
+    g = golden_grpo
+    c = g["cfg"]
+    V = g["theta_logits"].shape[-1]
+    obj = O.grpo_objective(g["theta_logits"], g["rollouts"], g["attn_mask"], g["log_probs"], g["advantages"], c["epsilon"], c["num_groups"])
+    bonus = O.entropy_bonus(g["theta_logits"], g["attn_mask"], V)
+    assert torch.allclose(obj, g["objective"], atol=1e-6, rtol=1e-5) and torch.allclose(bonus, g["bonus"], atol=1e-6, rtol=1e-5)
+    z = g["theta_logits"].clone().requires_grad_(True)
+    obj2 = grpo.calc_grpo_objective(z, g["rollouts"], g["attn_mask"], g["log_probs"], g["advantages"], c["epsilon"], c["num_groups"])
+    bonus2 = grpo.calc_entropy_bonus(z, g["attn_mask"], V)
+    (obj2 + c["entropy_beta"] * bonus2).backward()
+    assert torch.allclose(obj2, g["objective"], atol=1e-6, rtol=1e-5) and torch.allclose(bonus2, g["bonus"], atol=1e-6, rtol=1e-5)
+    assert torch.allclose(z.grad, g["dlogits"], atol=1e-7, rtol=1e-4)
+    r = torch.tensor([[1.0, 2.0, 4.0], [0.5, 0.5, 2.0]])
+    adv = grpo.group_advantages(r)
+    assert adv.shape == (6,) and torch.allclose(adv.view(2, 3).mean(dim=1), torch.zeros(2), atol=1e-6)
+
+
+def test_oracle_rollout_policy_matches_reference(golden_grpo):
+    """The oracle's rollout (cached decoder step + written-out top-k / temperature / inverse-CDF draw) reproduces the
+    unmodified reference's rollouts, per-token log-probs and masks for the recorded uniforms."""
+    g = golden_grpo
+    c = g["cfg"]
+    sd = {k[len("decoder."):]: v for k, v in g["policy_sd"].items() if k.startswith("decoder.")}
+    rollouts, logp, mask = O.cached_forward_rollout_policy(g["xlatent"], sd, 4, g["uniforms"], g["xmask"], max_actions=c["max_actions"],
+                                                           top_k=c["top_k"], temperature=c["temperature"])
+    assert torch.equal(rollouts, g["rollouts"]) and torch.equal(mask, g["rollout_mask"])
+    assert torch.allclose(logp, g["log_probs"], atol=2e-5, rtol=1e-4)

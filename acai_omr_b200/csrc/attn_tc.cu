@@ -28,14 +28,27 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t 
                      uint32_t box_cols);
 
 namespace fa {
-constexpr int BQ = 128, BKV = 64, D = 64, KV_STAGES = 4;
-constexpr int THREADS = 192;
+constexpr int BQ = 128, BKV = 64, D = 64;
 constexpr uint32_t QTILE = BQ * D * 2;            // 16 KB
 constexpr uint32_t KTILE = BKV * D * 2;           // 8 KB
-constexpr uint32_t OFF_Q = 0, OFF_K = QTILE, OFF_V = OFF_K + KV_STAGES * KTILE, OFF_BAR = OFF_V + KV_STAGES * KTILE;
-constexpr size_t SMEM = OFF_BAR + 256;
-constexpr uint32_t TMEM_COLS = 256;               // S[0] 0..63, S[1] 64..127, O 128..191
 constexpr float RESCALE_LOG2 = 8.0f;
+// NBUF = number of S buffers in TMEM, CTAS = resident CTAs per SM.
+//   NBUF 2, CTAS 2: 256 TMEM columns (S[0] 0..63, S[1] 64..127, O 128..191), 4 K/V stages.
+//   NBUF 1, CTAS 3 / 4: 128 columns (S 0..63, O 64..127), 3 / 2 K/V stages.  A CTA's tensor-pipe round trip
+//   (P_j -> PV_j, S_{j+1}) is then exposed to its own softmax warps, but every scheduler holds three / four softmax warps
+//   of independent CTAs instead of two, which is what keeps its MUFU unit fed.  These variants launch 256 threads (setmaxnreg
+//   is a WARPGROUP-wide instruction, so the helper warps 4-7 form a full warpgroup; 6 and 7 idle): 64 / 80 registers per
+//   thread at launch, the helper warpgroup hands its share back (setmaxnreg 32 / 40) and the softmax warpgroup takes 96 / 120.
+template <int NBUF, int CTAS_> struct Cfg {
+  static constexpr int CTAS = CTAS_;
+  static constexpr int THREADS = CTAS == 2 ? 192 : 256;
+  static constexpr int KV_STAGES = CTAS == 2 ? 4 : (CTAS == 3 ? 3 : 2);
+  static constexpr uint32_t OFF_Q = 0, OFF_K = QTILE, OFF_V = OFF_K + KV_STAGES * KTILE, OFF_BAR = OFF_V + KV_STAGES * KTILE;
+  static constexpr size_t SMEM = OFF_BAR + 256;
+  static constexpr uint32_t TMEM_COLS = NBUF == 2 ? 256 : 128;
+  static constexpr uint32_t O_COL = NBUF * 64;
+  static_assert(NBUF * 64 + 64 <= (int)TMEM_COLS && CTAS * TMEM_COLS <= 512, "TMEM budget");
+};
 }  // namespace fa
 using namespace fa;
 
@@ -51,10 +64,14 @@ struct AttnParams {
 // tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
 // POLY: how many of every 4 exponentials are evaluated with exp2_fma on the FMA pipe instead of MUFU.EX2 (0, 1 or 2).
 // The MUFU unit (16 results / clk / SM) is this kernel's busiest pipe; the FMA pipe is mostly idle.
-template <int DH, bool DROP, int POLY>
-__global__ void __launch_bounds__(THREADS, 2)
+template <int DH, bool DROP, int POLY, int NBUF, int CTAS>
+__global__ void __launch_bounds__((Cfg<NBUF, CTAS>::THREADS), CTAS)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
+  using C = Cfg<NBUF, CTAS>;
+  constexpr int KV_STAGES = C::KV_STAGES;
+  constexpr uint32_t OFF_Q = C::OFF_Q, OFF_K = C::OFF_K, OFF_V = C::OFF_V, OFF_BAR = C::OFF_BAR, TMEM_COLS = C::TMEM_COLS,
+                     O_COL = C::O_COL;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* q_full = bars;                          // 1
@@ -91,6 +108,11 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // (CTAS 4: the register budget moves from the two helper warps to the softmax warps inside each role's own branch -
+  // ptxas sizes a branch by the setmaxnreg that dominates it)
+  constexpr int REG_LO = CTAS == 4 ? 32 : 40, REG_HI = CTAS == 4 ? 96 : 120;
+  if (warp >= 4) {
+  if constexpr (CTAS > 2) ptx::setmaxnreg_dec<REG_LO>();   // one instruction for the whole helper warpgroup
   if (warp == 4) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && n_kv > 0) {
@@ -120,59 +142,80 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
         const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024) + hoff;
 #pragma unroll
         for (int k = 0; k < DH / 16; ++k)
-          ptx::umma_f16_ss(tmem_base + (j & 1) * 64, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
-        ptx::umma_commit(&s_full[j & 1]);
+          ptx::umma_f16_ss(tmem_base + (j % NBUF) * 64, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+        ptx::umma_commit(&s_full[j % NBUF]);
       };
       ptx::mbar_wait(q_full, 0);
       issue_s(0);
-      if (n_kv > 1) issue_s(1);
+      if (NBUF == 2 && n_kv > 1) issue_s(1);
       for (int j = 0; j < n_kv; ++j) {
         const int st = j % KV_STAGES;
-        ptx::mbar_wait(&p_full[j & 1], (j >> 1) & 1);
+        ptx::mbar_wait(&p_full[j % NBUF], (j / NBUF) & 1);
         ptx::tc_fence_after();
         const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + st * KTILE), 1024) + hoff;
 #pragma unroll
         for (int kk = 0; kk < BKV / 16; ++kk)       // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
-          ptx::umma_f16_ts(tmem_base + 128, tmem_base + (j & 1) * 64 + kk * 8, vdesc + (uint64_t)kk * (16 * 128 >> 4),
+          ptx::umma_f16_ts(tmem_base + O_COL, tmem_base + (j % NBUF) * 64 + kk * 8, vdesc + (uint64_t)kk * (16 * 128 >> 4),
                            IDESC_O, (j | kk) != 0);
         ptx::umma_commit(&kv_empty[st]);
         ptx::umma_commit(o_step);
         if (j == n_kv - 1) ptx::umma_commit(o_full);
-        if (j + 2 < n_kv) issue_s(j + 2);            // overwrites P_j: tcgen05 ops execute in issue order
+        if (j + NBUF < n_kv) issue_s(j + NBUF);      // overwrites P_j: tcgen05 ops execute in issue order
       }
     }
+  }
   } else {
     // ------------------------------------------------------------------ softmax warps (thread = query row)
+    if constexpr (CTAS > 2) ptx::setmaxnreg_inc<REG_HI>();
     const int r = warp * 32 + lane;
     const int qi = qb * BQ + r;
     const bool valid = qi < lq;
     const int my_end = p.causal ? max(0, min(lk, qi + shift + 1)) : lk;     // exclusive key bound of this row
     const int warp_min_end = __shfl_sync(0xffffffffu, my_end, 0);          // rows ascend inside a warp
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
-    const uint32_t tmem_o = tmem_base + lane_addr + 128;
+    const uint32_t tmem_o = tmem_base + lane_addr + O_COL;
     const float scale_log2 = p.scale_log2;
     float m = -INFINITY, l = 0.0f;
     const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? qi : 0));
     const uint32_t rowconst = DROP ? attn_drop_rowconst(p.drop.seed, rowkey) : 0u;
 
     for (int j = 0; j < n_kv; ++j) {
-      const uint32_t tmem_s = tmem_base + lane_addr + (j & 1) * 64;
-      ptx::mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+      const uint32_t tmem_s = tmem_base + lane_addr + (j % NBUF) * 64;
+      ptx::mbar_wait(&s_full[j % NBUF], (j / NBUF) & 1);
       ptx::tc_fence_after();
-      uint32_t s[64];
-      ptx::tmem_ld_32x32(tmem_s, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
-      ptx::tmem_ld_32x32(tmem_s + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
-      ptx::tmem_ld_wait();
+      constexpr bool TWOPASS = CTAS == 4;           // S is read from TMEM twice (maximum, then exponentials): <= 32 values live
       const int kbase = j * BKV;
-      if (kbase + BKV > warp_min_end) {             // ragged end / causal diagonal: mask keys >= my_end
-#pragma unroll
-        for (int i = 0; i < 64; ++i) if (kbase + i >= my_end) s[i] = 0xff800000u;   // -inf
-      }
+      const bool edge = kbase + BKV > warp_min_end;  // ragged end / causal diagonal: mask keys >= my_end
+      uint32_t s[TWOPASS ? 32 : 64];
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      if constexpr (TWOPASS) {
 #pragma unroll
-      for (int i = 0; i < 64; i += 4) {
-        mx0 = fmaxf(mx0, __uint_as_float(s[i])); mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
-        mx2 = fmaxf(mx2, __uint_as_float(s[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
+        for (int hf = 0; hf < 2; ++hf) {
+          ptx::tmem_ld_32x32(tmem_s + hf * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+          ptx::tmem_ld_wait();
+          if (edge) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (kbase + hf * 32 + i >= my_end) s[i] = 0xff800000u;   // -inf
+          }
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            mx0 = fmaxf(mx0, __uint_as_float(s[i])); mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
+            mx2 = fmaxf(mx2, __uint_as_float(s[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
+          }
+        }
+      } else {
+        ptx::tmem_ld_32x32(tmem_s, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+        ptx::tmem_ld_32x32(tmem_s + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[TWOPASS ? 0 : 32]));
+        ptx::tmem_ld_wait();
+        if (edge) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) if (kbase + i >= my_end) s[TWOPASS ? 0 : i] = 0xff800000u;   // -inf
+        }
+#pragma unroll
+        for (int i = 0; i < (TWOPASS ? 0 : 64); i += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(s[i])); mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(s[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
+        }
       }
       const float m_new = fmaxf(m, fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)));
       const bool grow = (m_new - m) * scale_log2 > RESCALE_LOG2 || (m == -INFINITY && m_new > -INFINITY);
@@ -183,41 +226,70 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
         if (j > 0) {
           ptx::mbar_wait(o_step, (j - 1) & 1);      // O holds P_{j-1} V_{j-1}
           ptx::tc_fence_after();
+          if constexpr (CTAS == 2) {
 #pragma unroll
-          for (int c = 0; c < DH / 32; ++c) {
-            uint32_t o[32];
-            ptx::tmem_ld_32x32(tmem_o + c * 32, o);
-            ptx::tmem_ld_wait();
+            for (int c = 0; c < DH / 32; ++c) {
+              uint32_t o[32];
+              ptx::tmem_ld_32x32(tmem_o + c * 32, o);
+              ptx::tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
-            ptx::tmem_st_32x32(tmem_o + c * 32, o);
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+              ptx::tmem_st_32x32(tmem_o + c * 32, o);
+            }
+          } else {                                    // tighter register budget: 16 columns at a time (rare path)
+#pragma unroll 1
+            for (int c = 0; c < DH / 16; ++c) {
+              uint32_t o[16];
+              ptx::tmem_ld_32x16(tmem_o + c * 16, o);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+              ptx::tmem_st_32x16(tmem_o + c * 16, o);
+            }
           }
         }
         m = m_new;
       }
       const float moff = (m == -INFINITY ? 0.0f : m) * scale_log2;
       float l0 = 0.0f, l1 = 0.0f;
-      uint32_t pk[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float x0 = fmaf(__uint_as_float(s[2 * i]), scale_log2, -moff), x1 = fmaf(__uint_as_float(s[2 * i + 1]), scale_log2, -moff);
+      auto exp_pair = [&](uint32_t s0, uint32_t s1, int i) -> uint32_t {   // keys kbase + 2i, kbase + 2i + 1
+        const float x0 = fmaf(__uint_as_float(s0), scale_log2, -moff), x1 = fmaf(__uint_as_float(s1), scale_log2, -moff);
         const float p0 = fast_exp2(x0);
         const float p1 = (POLY == 2 || (POLY == 1 && (i & 1))) ? exp2_fma(x1) : fast_exp2(x1);
         l0 += p0; l1 += p1;
         float d0 = p0, d1 = p1;
-        if (DROP) {                                   // keys kbase + 2i, kbase + 2i + 1 = one hash pair
+        if (DROP) {                                   // one hash pair
           const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (BKV / 2) + i));
           if ((bits & 0xffffu) < p.drop.thr) d0 = 0.0f;
           if ((bits >> 16) < p.drop.thr) d1 = 0.0f;
         }
         const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
-        pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+        return *reinterpret_cast<const uint32_t*>(&hh);
+      };
+      if constexpr (TWOPASS) {
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {            // P columns 16 hf .. 16 hf + 15 only cover S columns already in registers
+          ptx::tmem_ld_32x32(tmem_s + hf * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+          ptx::tmem_ld_wait();
+          if (edge) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (kbase + hf * 32 + i >= my_end) s[i] = 0xff800000u;
+          }
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pk[i] = exp_pair(s[2 * i], s[2 * i + 1], hf * 16 + i);
+          ptx::tmem_st_32x16(tmem_s + hf * 16, pk);
+        }
+      } else {
+        uint32_t pk[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) pk[i] = exp_pair(s[TWOPASS ? 0 : 2 * i], s[TWOPASS ? 0 : 2 * i + 1], i);
+        ptx::tmem_st_32x32(tmem_s, pk);
       }
       l += l0 + l1;
-      ptx::tmem_st_32x32(tmem_s, pk);
       ptx::tmem_st_wait();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(&p_full[j & 1]);
+      ptx::mbar_arrive(&p_full[j % NBUF]);
     }
     if (n_kv > 0) {
       ptx::mbar_wait(o_full, 0);
@@ -263,15 +335,17 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
-template <int DH, bool DROP, int POLY>
+template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2>
 static int launch_fwd(dim3 grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                       cudaStream_t st) {
   static bool attr_set = false;
+  constexpr size_t SMEM = Cfg<NBUF, CTAS>::SMEM;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_set = true;
   }
-  attn_fwd_tc<DH, DROP, POLY><<<grid, THREADS, SMEM, st>>>(tq, tk, tv, p);
+  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS><<<grid, Cfg<NBUF, CTAS>::THREADS, SMEM, st>>>(tq, tk, tv, p);
   return ACAI_OK;
 }
 
@@ -294,14 +368,20 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
   if (rc) return rc;
   // share of the exponentials moved to the FMA pipe (see POLY); ACAI_ATTN_POLY overrides the tuned default for A/B runs
   static const int poly = [] { const char* e = getenv("ACAI_ATTN_POLY"); const int v = e ? atoi(e) : 0; return v < 0 ? 0 : (v > 2 ? 2 : v); }();
+  // resident CTAs per SM (see Cfg): 4 is the measured best (profiles/r1h_attention.md); ACAI_ATTN_CTAS = 2 / 3 for A/B runs
+  static const int ctas = [] { const char* e = getenv("ACAI_ATTN_CTAS"); const int v = e ? atoi(e) : 4; return v == 2 || v == 3 ? v : 4; }();
   AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q, drop};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
+#define ACAI_FWD4(DH_, DROP_)                                                                                     \
+  (poly == 0 ? launch_fwd<DH_, DROP_, 0, 1, 4>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1, 1, 4>(grid, tq, tk, tv, p, st) \
+                                                                                    : launch_fwd<DH_, DROP_, 2, 1, 4>(grid, tq, tk, tv, p, st))
 #define ACAI_FWD(DH_, DROP_)                                                                                      \
-  (poly == 0 ? launch_fwd<DH_, DROP_, 0>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1>(grid, tq, tk, tv, p, st) \
-                                                                             : launch_fwd<DH_, DROP_, 2>(grid, tq, tk, tv, p, st))
+  (ctas == 4 ? ACAI_FWD4(DH_, DROP_) : ctas == 3 ? launch_fwd<DH_, DROP_, 0, 1, 3>(grid, tq, tk, tv, p, st)       \
+             : launch_fwd<DH_, DROP_, 0, 2, 2>(grid, tq, tk, tv, p, st))
   if (drop.thr == 0) rc = head_dim == 64 ? ACAI_FWD(64, false) : ACAI_FWD(32, false);
   else rc = head_dim == 64 ? ACAI_FWD(64, true) : ACAI_FWD(32, true);
 #undef ACAI_FWD
+#undef ACAI_FWD4
   if (rc) return rc;
   return launch_status("attn_fwd_tc");
 }

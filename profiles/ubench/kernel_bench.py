@@ -72,11 +72,12 @@ def bench_colsum(rows, cols):
 
 if __name__ == "__main__":
     what = sys.argv[1:] or ["attn", "ln", "colsum"]
-    print("ACAI_ATTN_POLY =", os.environ.get("ACAI_ATTN_POLY", "(default)"))
+    print("ACAI_ATTN_POLY =", os.environ.get("ACAI_ATTN_POLY", "(default)"), " ACAI_ATTN_CTAS =", os.environ.get("ACAI_ATTN_CTAS", "(default)"))
     if "attn" in what or "attn_bwd" in what:
         bwd = "attn_bwd" in what
         bench_attn("encoder self (12 x 64)", 64, 995, 12, 64, False, bwd)
         bench_attn("decoder self (16 x 64, causal)", 64, 655, 16, 64, True, bwd)
+        bench_attn("MAE decoder self (16 x 32)", 64, 495, 16, 32, False, bwd)
     if "ln" in what:
         bench_ln(63664, 768)
         bench_ln(41976, 1024)

@@ -39,15 +39,18 @@ constexpr float RESCALE_LOG2 = 8.0f;
 //   of independent CTAs instead of two, which is what keeps its MUFU unit fed.  These variants launch 256 threads (setmaxnreg
 //   is a WARPGROUP-wide instruction, so the helper warps 4-7 form a full warpgroup; 6 and 7 idle): 64 / 80 registers per
 //   thread at launch, the helper warpgroup hands its share back (setmaxnreg 32 / 40) and the softmax warpgroup takes 96 / 120.
-template <int NBUF, int CTAS_> struct Cfg {
-  static constexpr int CTAS = CTAS_;
+//   NBUF 2, CTAS 4, SB 32: the softmax works on HALF key blocks (SB = 32 keys: S is 128 x 32, two buffers at columns 0..31 and
+//   32..63, O 64..127), so S is double-buffered again inside 128 columns: the tensor-pipe round trip leaves the softmax
+//   warps' critical path and a row's 32 values fit the register budget in one pass.
+template <int NBUF, int CTAS_, int SB_> struct Cfg {
+  static constexpr int CTAS = CTAS_, SB = SB_;
   static constexpr int THREADS = CTAS == 2 ? 192 : 256;
   static constexpr int KV_STAGES = CTAS == 2 ? 4 : (CTAS == 3 ? 3 : 2);
   static constexpr uint32_t OFF_Q = 0, OFF_K = QTILE, OFF_V = OFF_K + KV_STAGES * KTILE, OFF_BAR = OFF_V + KV_STAGES * KTILE;
   static constexpr size_t SMEM = OFF_BAR + 256;
-  static constexpr uint32_t TMEM_COLS = NBUF == 2 ? 256 : 128;
-  static constexpr uint32_t O_COL = NBUF * 64;
-  static_assert(NBUF * 64 + 64 <= (int)TMEM_COLS && CTAS * TMEM_COLS <= 512, "TMEM budget");
+  static constexpr uint32_t TMEM_COLS = NBUF * SB + 64 > 128 ? 256 : 128;
+  static constexpr uint32_t O_COL = NBUF * SB;
+  static_assert(CTAS * TMEM_COLS <= 512 && (SB == 32 || SB == 64), "TMEM budget");
 };
 }  // namespace fa
 using namespace fa;
@@ -64,11 +67,12 @@ struct AttnParams {
 // tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
 // POLY: how many of every 4 exponentials are evaluated with exp2_fma on the FMA pipe instead of MUFU.EX2 (0, 1 or 2).
 // The MUFU unit (16 results / clk / SM) is this kernel's busiest pipe; the FMA pipe is mostly idle.
-template <int DH, bool DROP, int POLY, int NBUF, int CTAS>
-__global__ void __launch_bounds__((Cfg<NBUF, CTAS>::THREADS), CTAS)
+template <int DH, bool DROP, int POLY, int NBUF, int CTAS, int SB>
+__global__ void __launch_bounds__((Cfg<NBUF, CTAS, SB>::THREADS), CTAS)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
-  using C = Cfg<NBUF, CTAS>;
+  using C = Cfg<NBUF, CTAS, SB>;
+  constexpr int R = BKV / SB;                        // softmax blocks per K/V tile
   constexpr int KV_STAGES = C::KV_STAGES;
   constexpr uint32_t OFF_Q = C::OFF_Q, OFF_K = C::OFF_K, OFF_V = C::OFF_V, OFF_BAR = C::OFF_BAR, TMEM_COLS = C::TMEM_COLS,
                      O_COL = C::O_COL;
@@ -90,7 +94,8 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   const int shift = lk - lq;
   int kv_end = lk;
   if (p.causal) { const int last = qb * BQ + BQ + shift; kv_end = last < lk ? (last < 0 ? 0 : last) : lk; }
-  const int n_kv = (kv_end + BKV - 1) / BKV;
+  const int n_kv = (kv_end + BKV - 1) / BKV;       // K/V tiles (TMA granularity)
+  const int n_sb = (kv_end + SB - 1) / SB;         // softmax blocks (S / P granularity)
 
   if (warp == 5 && lane == 0) {
     ptx::mbar_init(q_full, 1);
@@ -131,36 +136,37 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   } else if (warp == 5) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0 && n_kv > 0) {
-      constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BQ, BKV);
+      constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BQ, SB);
       constexpr uint32_t IDESC_O = ptx::idesc_bf16_f32(BQ, DH, false, true);  // B = V is MN-major
       const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);                 // this head's 16-byte units inside the 128 B row
       const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_Q), 1024) + hoff;
-      auto issue_s = [&](int j) {                    // S_j into buffer j & 1; K_j sits in stage j % KV_STAGES
-        const int st = j % KV_STAGES;
-        ptx::mbar_wait(&kv_full[st], (j / KV_STAGES) & 1);
+      auto issue_s = [&](int i) {                    // S_i into buffer i % NBUF; its keys are rows (i % R) * SB.. of tile i / R
+        const int t = i / R, st = t % KV_STAGES;
+        ptx::mbar_wait(&kv_full[st], (t / KV_STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024) + hoff;
+        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024) + hoff +
+                               (uint64_t)((i % R) * (SB * 128 >> 4));
 #pragma unroll
         for (int k = 0; k < DH / 16; ++k)
-          ptx::umma_f16_ss(tmem_base + (j % NBUF) * 64, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
-        ptx::umma_commit(&s_full[j % NBUF]);
+          ptx::umma_f16_ss(tmem_base + (i % NBUF) * SB, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+        ptx::umma_commit(&s_full[i % NBUF]);
       };
       ptx::mbar_wait(q_full, 0);
       issue_s(0);
-      if (NBUF == 2 && n_kv > 1) issue_s(1);
-      for (int j = 0; j < n_kv; ++j) {
-        const int st = j % KV_STAGES;
-        ptx::mbar_wait(&p_full[j % NBUF], (j / NBUF) & 1);
+      if (NBUF == 2 && n_sb > 1) issue_s(1);
+      for (int i = 0; i < n_sb; ++i) {
+        const int st = (i / R) % KV_STAGES;
+        ptx::mbar_wait(&p_full[i % NBUF], (i / NBUF) & 1);
         ptx::tc_fence_after();
         const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + st * KTILE), 1024) + hoff;
 #pragma unroll
-        for (int kk = 0; kk < BKV / 16; ++kk)       // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
-          ptx::umma_f16_ts(tmem_base + O_COL, tmem_base + (j % NBUF) * 64 + kk * 8, vdesc + (uint64_t)kk * (16 * 128 >> 4),
-                           IDESC_O, (j | kk) != 0);
-        ptx::umma_commit(&kv_empty[st]);
+        for (int kk = 0; kk < SB / 16; ++kk)        // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
+          ptx::umma_f16_ts(tmem_base + O_COL, tmem_base + (i % NBUF) * SB + kk * 8,
+                           vdesc + (uint64_t)((i % R) * (SB / 16) + kk) * (16 * 128 >> 4), IDESC_O, (i | kk) != 0);
+        if (i % R == R - 1 || i == n_sb - 1) ptx::umma_commit(&kv_empty[st]);   // last reader of this K/V tile
         ptx::umma_commit(o_step);
-        if (j == n_kv - 1) ptx::umma_commit(o_full);
-        if (j + NBUF < n_kv) issue_s(j + NBUF);      // overwrites P_j: tcgen05 ops execute in issue order
+        if (i == n_sb - 1) ptx::umma_commit(o_full);
+        if (i + NBUF < n_sb) issue_s(i + NBUF);      // overwrites P_i: tcgen05 ops execute in issue order
       }
     }
   }
@@ -179,40 +185,29 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
     const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? qi : 0));
     const uint32_t rowconst = DROP ? attn_drop_rowconst(p.drop.seed, rowkey) : 0u;
 
-    for (int j = 0; j < n_kv; ++j) {
-      const uint32_t tmem_s = tmem_base + lane_addr + (j % NBUF) * 64;
+    for (int j = 0; j < n_sb; ++j) {
+      const uint32_t tmem_s = tmem_base + lane_addr + (j % NBUF) * SB;
       ptx::mbar_wait(&s_full[j % NBUF], (j / NBUF) & 1);
       ptx::tc_fence_after();
-      constexpr bool TWOPASS = CTAS == 4;           // S is read from TMEM twice (maximum, then exponentials): <= 32 values live
-      const int kbase = j * BKV;
-      const bool edge = kbase + BKV > warp_min_end;  // ragged end / causal diagonal: mask keys >= my_end
-      uint32_t s[TWOPASS ? 32 : 64];
+      // (SB 64 with four CTAs: S is read from TMEM twice - maximum, then exponentials - so that <= 32 values are live)
+      constexpr bool TWOPASS = CTAS == 4 && SB == 64;
+      constexpr int NS = TWOPASS ? 32 : SB;          // values held in registers at a time
+      const int kbase = j * SB;
+      const bool edge = kbase + SB > warp_min_end;   // ragged end / causal diagonal: mask keys >= my_end
+      uint32_t s[NS];
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-      if constexpr (TWOPASS) {
 #pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {
-          ptx::tmem_ld_32x32(tmem_s + hf * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
-          ptx::tmem_ld_wait();
-          if (edge) {
+      for (int hf = 0; hf < SB / NS; ++hf) {        // (one trip unless TWOPASS)
 #pragma unroll
-            for (int i = 0; i < 32; ++i) if (kbase + hf * 32 + i >= my_end) s[i] = 0xff800000u;   // -inf
-          }
-#pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            mx0 = fmaxf(mx0, __uint_as_float(s[i])); mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
-            mx2 = fmaxf(mx2, __uint_as_float(s[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
-          }
-        }
-      } else {
-        ptx::tmem_ld_32x32(tmem_s, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
-        ptx::tmem_ld_32x32(tmem_s + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[TWOPASS ? 0 : 32]));
+        for (int c = 0; c < NS / 32; ++c)
+          ptx::tmem_ld_32x32(tmem_s + hf * NS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
         ptx::tmem_ld_wait();
         if (edge) {
 #pragma unroll
-          for (int i = 0; i < 64; ++i) if (kbase + i >= my_end) s[TWOPASS ? 0 : i] = 0xff800000u;   // -inf
+          for (int i = 0; i < NS; ++i) if (kbase + hf * NS + i >= my_end) s[i] = 0xff800000u;   // -inf
         }
 #pragma unroll
-        for (int i = 0; i < (TWOPASS ? 0 : 64); i += 4) {
+        for (int i = 0; i < NS; i += 4) {
           mx0 = fmaxf(mx0, __uint_as_float(s[i])); mx1 = fmaxf(mx1, __uint_as_float(s[i + 1]));
           mx2 = fmaxf(mx2, __uint_as_float(s[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(s[i + 3]));
         }
@@ -259,32 +254,28 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
         l0 += p0; l1 += p1;
         float d0 = p0, d1 = p1;
         if (DROP) {                                   // one hash pair
-          const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (BKV / 2) + i));
+          const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(kbase / 2 + i));
           if ((bits & 0xffffu) < p.drop.thr) d0 = 0.0f;
           if ((bits >> 16) < p.drop.thr) d1 = 0.0f;
         }
         const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
         return *reinterpret_cast<const uint32_t*>(&hh);
       };
-      if constexpr (TWOPASS) {
 #pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {            // P columns 16 hf .. 16 hf + 15 only cover S columns already in registers
+      for (int hf = 0; hf < SB / NS; ++hf) {        // P columns written by trip hf only cover S columns already in registers
+        if constexpr (TWOPASS) {
           ptx::tmem_ld_32x32(tmem_s + hf * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
           ptx::tmem_ld_wait();
           if (edge) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) if (kbase + hf * 32 + i >= my_end) s[i] = 0xff800000u;
           }
-          uint32_t pk[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) pk[i] = exp_pair(s[2 * i], s[2 * i + 1], hf * 16 + i);
-          ptx::tmem_st_32x16(tmem_s + hf * 16, pk);
         }
-      } else {
-        uint32_t pk[32];
+        uint32_t pk[NS / 2];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) pk[i] = exp_pair(s[TWOPASS ? 0 : 2 * i], s[TWOPASS ? 0 : 2 * i + 1], i);
-        ptx::tmem_st_32x32(tmem_s, pk);
+        for (int i = 0; i < NS / 2; ++i) pk[i] = exp_pair(s[2 * i], s[2 * i + 1], hf * (NS / 2) + i);
+        if constexpr (NS == 64) ptx::tmem_st_32x32(tmem_s, *reinterpret_cast<const uint32_t(*)[32]>(&pk[0]));
+        else ptx::tmem_st_32x16(tmem_s + hf * 16, *reinterpret_cast<const uint32_t(*)[16]>(&pk[0]));
       }
       l += l0 + l1;
       ptx::tmem_st_wait();
@@ -335,17 +326,17 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
-template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2>
+template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2, int SB = 64>
 static int launch_fwd(dim3 grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                       cudaStream_t st) {
   static bool attr_set = false;
-  constexpr size_t SMEM = Cfg<NBUF, CTAS>::SMEM;
+  constexpr size_t SMEM = Cfg<NBUF, CTAS, SB>::SMEM;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_set = true;
   }
-  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS><<<grid, Cfg<NBUF, CTAS>::THREADS, SMEM, st>>>(tq, tk, tv, p);
+  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB><<<grid, Cfg<NBUF, CTAS, SB>::THREADS, SMEM, st>>>(tq, tk, tv, p);
   return ACAI_OK;
 }
 
@@ -370,18 +361,21 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
   static const int poly = [] { const char* e = getenv("ACAI_ATTN_POLY"); const int v = e ? atoi(e) : 0; return v < 0 ? 0 : (v > 2 ? 2 : v); }();
   // resident CTAs per SM (see Cfg): 4 is the measured best (profiles/r1h_attention.md); ACAI_ATTN_CTAS = 2 / 3 for A/B runs
   static const int ctas = [] { const char* e = getenv("ACAI_ATTN_CTAS"); const int v = e ? atoi(e) : 4; return v == 2 || v == 3 ? v : 4; }();
+  // softmax block (keys per S / P round) of the four-CTA variant: 32 (half blocks, S double-buffered) is the measured best;
+  // ACAI_ATTN_SB = 64 selects the single-buffer two-pass variant for A/B runs
+  static const int sb = [] { const char* e = getenv("ACAI_ATTN_SB"); return e && atoi(e) == 64 ? 64 : 32; }();
   AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q, drop};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
-#define ACAI_FWD4(DH_, DROP_)                                                                                     \
-  (poly == 0 ? launch_fwd<DH_, DROP_, 0, 1, 4>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1, 1, 4>(grid, tq, tk, tv, p, st) \
-                                                                                    : launch_fwd<DH_, DROP_, 2, 1, 4>(grid, tq, tk, tv, p, st))
+#define ACAI_FWD32(DH_, DROP_)                                                                                    \
+  (poly == 0 ? launch_fwd<DH_, DROP_, 0, 2, 4, 32>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1, 2, 4, 32>(grid, tq, tk, tv, p, st) \
+                                                                                        : launch_fwd<DH_, DROP_, 2, 2, 4, 32>(grid, tq, tk, tv, p, st))
 #define ACAI_FWD(DH_, DROP_)                                                                                      \
-  (ctas == 4 ? ACAI_FWD4(DH_, DROP_) : ctas == 3 ? launch_fwd<DH_, DROP_, 0, 1, 3>(grid, tq, tk, tv, p, st)       \
+  (ctas == 4 && sb == 32 ? ACAI_FWD32(DH_, DROP_) : ctas == 4 ? launch_fwd<DH_, DROP_, 0, 1, 4>(grid, tq, tk, tv, p, st) : ctas == 3 ? launch_fwd<DH_, DROP_, 0, 1, 3>(grid, tq, tk, tv, p, st)       \
              : launch_fwd<DH_, DROP_, 0, 2, 2>(grid, tq, tk, tv, p, st))
   if (drop.thr == 0) rc = head_dim == 64 ? ACAI_FWD(64, false) : ACAI_FWD(32, false);
   else rc = head_dim == 64 ? ACAI_FWD(64, true) : ACAI_FWD(32, true);
 #undef ACAI_FWD
-#undef ACAI_FWD4
+#undef ACAI_FWD32
   if (rc) return rc;
   return launch_status("attn_fwd_tc");
 }

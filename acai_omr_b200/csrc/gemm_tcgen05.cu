@@ -39,6 +39,9 @@ struct Epi {
   const int32_t* res_rows;   // optional gather: residual row of output row m is res_rows[m] (position embeddings)
   void* aux; int64_t ld_aux; // ACT_GELU_TRAIN: the pre-activation output
   uint32_t drop_thr; float drop_rp; uint64_t drop_seed;   // dropout on the activation (thr = 0: none)
+  // split-K (small-M decode projections, generic epilogue only): tile = (k slice, m, n); slice ks accumulates k blocks
+  // [ks * kper, (ks + 1) * kper) and stores its raw fp32 accumulator to ws[ks][M][N]; splitk_reduce_kernel finishes the job
+  int splitk; int kper; float* ws;
 };
 
 template <int BN> constexpr int stages() { return BN >= 256 ? 4 : (BN >= 128 ? 6 : 8); }
@@ -260,7 +263,9 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN, num_tiles = num_m * num_n, num_k = K / BK;
+  const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN, num_mn = num_m * num_n, num_k = K / BK;
+  const int splitk = (OUT == 0 && ep.splitk > 1) ? ep.splitk : 1, kper = splitk > 1 ? ep.kper : num_k;
+  const int num_tiles = num_mn * splitk;
 
   if (warp == 0 && lane == 0) {
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
@@ -283,8 +288,10 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
-        for (int kb = 0; kb < num_k; ++kb) {
+        const int mn = tile % num_mn, ks = tile / num_mn;
+        const int m0 = (mn / num_n) * BM, n0 = (mn % num_n) * BN;
+        const int kb0 = ks * kper, kb1 = kb0 + kper < num_k ? kb0 + kper : num_k;
+        for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           ptx::mbar_arrive_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
           ptx::tma_load_2d(smem_a + stage * A_BYTES, &tma_a, &full_bar[stage], kb * BK, m0);
@@ -302,14 +309,15 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < num_k; ++kb) {
+        const int kb0 = (tile / num_mn) * kper, kb1 = kb0 + kper < num_k ? kb0 + kper : num_k;
+        for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
           const uint64_t adesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_a + stage * A_BYTES), 1024);
           const uint64_t bdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_b + stage * B_BYTES), 1024);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes along K inside the 128B swizzle row = +2 in the address field
-            ptx::umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb | k) != 0);
+            ptx::umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb != kb0 || k != 0) ? 1u : 0u);
           ptx::umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -333,7 +341,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
       const int etid = (int)threadIdx.x - 64;         // 0..255
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
         const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
+        const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;   // (no split-K with the TMA-store epilogue)
         const int row0 = m0 + lane_grp * 32, grow = row0 + lane, col0 = n0 + half * CPW;
         // everything that comes from global memory is requested before the wait on the accumulator
         float bv = 0.0f;
@@ -395,9 +403,16 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
     } else {
       const bool vec_ok = (N % 8 == 0) && (ep.ldo % 8 == 0) && ((reinterpret_cast<uintptr_t>(ep.out) & 15) == 0) &&
                           (!ep.res || ((ep.ldr % 8 == 0) && ((reinterpret_cast<uintptr_t>(ep.res) & 15) == 0)));
+      const bool vec_ws = (N % 8 == 0) && ((reinterpret_cast<uintptr_t>(ep.ws) & 15) == 0);
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
         const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
+        const int mn = tile % num_mn, ks = tile / num_mn;
+        const int m0 = (mn / num_n) * BM, n0 = (mn % num_n) * BN;
+        Epi et = ep;
+        if (splitk > 1) {                              // raw fp32 partial sums; bias / residual / activation come in the reduce
+          et.bias = nullptr; et.res = nullptr; et.act = ACAI_ACT_NONE;
+          et.out = ep.ws + (int64_t)ks * M * N; et.out_dt = ACAI_F32; et.ldo = N;
+        }
         ptx::mbar_wait(&tfull_bar[as], aphase);
         ptx::tc_fence_after();
         const int row = m0 + lane_grp * 32 + lane;
@@ -410,7 +425,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
           uint32_t acc[32];
           ptx::tmem_ld_32x32(taddr + c, acc);
           ptx::tmem_ld_wait();
-          if (row < M && col0 < N) epi_store_chunk(ep, acc, row, rrow, col0, N, vec_ok);
+          if (row < M && col0 < N) epi_store_chunk(et, acc, row, rrow, col0, N, splitk > 1 ? vec_ws : vec_ok);
         }
         ptx::tc_fence_before();
         __syncwarp();
@@ -421,6 +436,120 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 2) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---- split-K reduce (+ bias, activation, residual, LayerNorm) ---------------------------------------------------
+// One warp per output row: v = sum_ks ws[ks][row][:] + bias, activation, + residual; with gamma != nullptr the row is then
+// normalised (two-pass variance over the fp32 values, as acai_layernorm_fwd) - the decode step's out_proj / linear2 +
+// residual + LayerNorm in one pass over data that is still in L2.  VPL = float4 pieces per lane (N = 128 * VPL) when the
+// row has to stay in registers for the LayerNorm; VPL = 0 streams any N % 4 == 0 without it.
+template <int VPL>
+__global__ void __launch_bounds__(64)
+splitk_reduce_kernel(const float* __restrict__ ws, int splitk, int M, int N, const float* __restrict__ bias, const void* res,
+                     int res_dt, int64_t ldr, int act, const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                     void* out, int out_dt, int64_t ldo) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 2 + warp;
+  if (row >= M) return;
+  const int64_t slab = (int64_t)M * N;
+  const float* wrow = ws + (int64_t)row * N;
+  auto load = [&](int col) {
+    float4 a = *reinterpret_cast<const float4*>(wrow + col);
+    for (int ks = 1; ks < splitk; ++ks) {
+      const float4 b = *reinterpret_cast<const float4*>(wrow + ks * slab + col);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    if (bias) { const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col)); a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+    if (act == ACAI_ACT_GELU) { a.x = gelu_fast(a.x); a.y = gelu_fast(a.y); a.z = gelu_fast(a.z); a.w = gelu_fast(a.w); }
+    if (res) {
+      const int64_t o = (int64_t)row * ldr + col;
+      a.x += ld_as_float(res, o, res_dt); a.y += ld_as_float(res, o + 1, res_dt);
+      a.z += ld_as_float(res, o + 2, res_dt); a.w += ld_as_float(res, o + 3, res_dt);
+    }
+    return a;
+  };
+  auto store = [&](int col, float4 a) {
+    const int64_t o = (int64_t)row * ldo + col;
+    if (out_dt == ACAI_BF16) {
+      const __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
+      uint2 pk; pk.x = *reinterpret_cast<const uint32_t*>(&h0); pk.y = *reinterpret_cast<const uint32_t*>(&h1);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(out) + o) = pk;
+    } else {
+      st_from_float(out, o, out_dt, a.x); st_from_float(out, o + 1, out_dt, a.y);
+      st_from_float(out, o + 2, out_dt, a.z); st_from_float(out, o + 3, out_dt, a.w);
+    }
+  };
+  if constexpr (VPL == 0) {
+    for (int col = lane * 4; col < N; col += 128) store(col, load(col));
+  } else {
+    // all loads of one K slice are issued before any is consumed (a per-piece loop over the slices would serialise
+    // splitk * VPL L2 round trips per lane)
+    float4 v[VPL];
+#pragma unroll
+    for (int c = 0; c < VPL; ++c) v[c] = *reinterpret_cast<const float4*>(wrow + (c * 32 + lane) * 4);
+    for (int ks = 1; ks < splitk; ++ks) {
+      float4 t[VPL];
+#pragma unroll
+      for (int c = 0; c < VPL; ++c) t[c] = *reinterpret_cast<const float4*>(wrow + ks * slab + (c * 32 + lane) * 4);
+#pragma unroll
+      for (int c = 0; c < VPL; ++c) { v[c].x += t[c].x; v[c].y += t[c].y; v[c].z += t[c].z; v[c].w += t[c].w; }
+    }
+    if (bias) {
+#pragma unroll
+      for (int c = 0; c < VPL; ++c) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(bias + (c * 32 + lane) * 4));
+        v[c].x += b.x; v[c].y += b.y; v[c].z += b.z; v[c].w += b.w;
+      }
+    }
+    if (act == ACAI_ACT_GELU) {
+#pragma unroll
+      for (int c = 0; c < VPL; ++c) { v[c].x = gelu_fast(v[c].x); v[c].y = gelu_fast(v[c].y); v[c].z = gelu_fast(v[c].z); v[c].w = gelu_fast(v[c].w); }
+    }
+    if (res) {
+      if (res_dt == ACAI_BF16 && ldr % 4 == 0 && (reinterpret_cast<uintptr_t>(res) & 7) == 0) {
+        uint2 r[VPL];
+#pragma unroll
+        for (int c = 0; c < VPL; ++c)
+          r[c] = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(res) + (int64_t)row * ldr + (c * 32 + lane) * 4));
+#pragma unroll
+        for (int c = 0; c < VPL; ++c) {
+          const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r[c].x));
+          const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r[c].y));
+          v[c].x += f0.x; v[c].y += f0.y; v[c].z += f1.x; v[c].w += f1.y;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < VPL; ++c) {
+          const int64_t o = (int64_t)row * ldr + (c * 32 + lane) * 4;
+          v[c].x += ld_as_float(res, o, res_dt); v[c].y += ld_as_float(res, o + 1, res_dt);
+          v[c].z += ld_as_float(res, o + 2, res_dt); v[c].w += ld_as_float(res, o + 3, res_dt);
+        }
+      }
+    }
+    if (!gamma) {
+#pragma unroll
+      for (int c = 0; c < VPL; ++c) store((c * 32 + lane) * 4, v[c]);
+      return;
+    }
+    float sum = 0.0f;
+#pragma unroll
+    for (int c = 0; c < VPL; ++c) sum += (v[c].x + v[c].y) + (v[c].z + v[c].w);
+    const float mean = warp_sum(sum) / (float)N;
+    float sq = 0.0f;
+#pragma unroll
+    for (int c = 0; c < VPL; ++c) {
+      const float a = v[c].x - mean, b = v[c].y - mean, cc = v[c].z - mean, d = v[c].w - mean;
+      sq += (a * a + b * b) + (cc * cc + d * d);
+    }
+    const float rstd = rsqrtf(warp_sum(sq) / (float)N + eps);
+#pragma unroll
+    for (int c = 0; c < VPL; ++c) {
+      const int col = (c * 32 + lane) * 4;
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + col)), b = __ldg(reinterpret_cast<const float4*>(beta + col));
+      store(col, make_float4((v[c].x - mean) * rstd * g.x + b.x, (v[c].y - mean) * rstd * g.y + b.y,
+                             (v[c].z - mean) * rstd * g.z + b.z, (v[c].w - mean) * rstd * g.w + b.w));
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------ host
@@ -595,6 +724,71 @@ int linear_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const
                    int res_dt, int64_t ldr, void* out, int out_dt, int64_t ldo, int M, int N, int K, int act,
                    cudaStream_t st) {
   return linear_tcgen05_ex(a, lda, w, ldw, bias, res, res_dt, ldr, nullptr, out, out_dt, ldo, M, N, K, act, st);
+}
+
+// ---- small-M projections: split-K GEMM + fused reduce ----------------------------------------------------------------
+static int splitk_factor(int M, int N, int K) {
+  const int base = ((M + BM - 1) / BM) * ((N + 63) / 64), num_k = K / BK;
+  int sk = num_sms() / (base > 0 ? base : 1);
+  if (sk > 8) sk = 8;
+  if (sk > num_k / 2) sk = num_k / 2;
+  return sk < 1 ? 1 : sk;
+}
+
+size_t linear_splitk_workspace_bytes(int M, int N, int K) {
+  return (size_t)splitk_factor(M, N, K) * (size_t)M * (size_t)N * sizeof(float);
+}
+
+// out = LN?( act(a . w^T + bias) + residual ) for M <= 256 rows.  ACAI_ERR_UNSUPPORTED (nothing written) when the problem
+// does not qualify: operands not TMA-able, no K slices to gain, N % 4, LayerNorm rows that do not fit the register variant.
+int linear_splitk_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
+                          int64_t ldr, const float* gamma, const float* beta, float eps, void* out, int out_dt, int64_t ldo, int M,
+                          int N, int K, int act, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (!gemm_operands_ok(a, lda, w, ldw, M, N, K) || M > 256 || N % 4 != 0 || (reinterpret_cast<uintptr_t>(ws) & 15) ||
+      (out_dt == ACAI_BF16 && ((ldo % 4) || (reinterpret_cast<uintptr_t>(out) & 7))))
+    return ACAI_ERR_UNSUPPORTED;
+  const int sk = splitk_factor(M, N, K);
+  const bool in_regs = N % 128 == 0 && N / 128 <= 8;     // the row fits the register-resident reduce variants
+  const int vpl = in_regs ? N / 128 : 0;
+  if (sk < 2 || (gamma && (!in_regs || !beta))) return ACAI_ERR_UNSUPPORTED;
+  if (ws_bytes < (size_t)sk * M * N * sizeof(float)) return ACAI_ERR_UNSUPPORTED;
+  const int num_k = K / BK, kper = (num_k + sk - 1) / sk;
+  Epi ep{nullptr, nullptr, ACAI_BF16, 0, ws, ACAI_F32, N, ACAI_ACT_NONE, nullptr, nullptr, 0, 0u, 1.0f, 0ull,
+         (num_k + kper - 1) / kper, kper, static_cast<float*>(ws)};
+  CUtensorMap ta, tb;
+  int rc = make_tma_2d_bf16(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
+  if (rc) return rc;
+  rc = make_tma_2d_bf16(&tb, w, (uint64_t)N, (uint64_t)K, (uint64_t)ldw, 64, BK);
+  if (rc) return rc;
+  {
+    static bool attr_set = false;
+    constexpr size_t smem = smem_bytes<64>();
+    if (!attr_set) {
+      ACAI_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05<64, 0, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_set = true;
+    }
+    const int tiles = ((M + BM - 1) / BM) * ((N + 63) / 64) * ep.splitk;
+    const int grid = tiles < num_sms() ? tiles : num_sms();
+    gemm_bf16_tcgen05<64, 0, 0, 0><<<grid, THREADS, smem, st>>>(ta, tb, ta, ta, ep, M, N, K);
+    rc = launch_status("gemm_bf16_tcgen05 (split-K)");
+    if (rc) return rc;
+  }
+  const dim3 grid((M + 1) / 2);
+#define ACAI_RED(V) splitk_reduce_kernel<V><<<grid, 64, 0, st>>>(static_cast<const float*>(ws), ep.splitk, M, N, bias, res, res_dt, ldr, \
+                                                                act, gamma, beta, eps, out, out_dt, ldo)
+  switch (vpl) {
+    case 0: ACAI_RED(0); break;
+    case 1: ACAI_RED(1); break;
+    case 2: ACAI_RED(2); break;
+    case 3: ACAI_RED(3); break;
+    case 4: ACAI_RED(4); break;
+    case 5: ACAI_RED(5); break;
+    case 6: ACAI_RED(6); break;
+    case 7: ACAI_RED(7); break;
+    default: ACAI_RED(8); break;
+  }
+#undef ACAI_RED
+  return launch_status("splitk_reduce_kernel");
 }
 
 }  // namespace acai

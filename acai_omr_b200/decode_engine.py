@@ -13,6 +13,8 @@ positions that mask_and_clip_seqs discards, so outputs are identical to the refe
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import ops
@@ -52,6 +54,12 @@ class GreedyDecodeEngine:
         self.max_mem_len = 0
         self.ws_self = ops.decode_workspace(B, self.H, max_len, device)
         self.ws_cross = None
+        # small-M projections: split-K GEMM + fused bias / residual / LayerNorm reduce (ACAI_DECODE_SPLITK=0 switches it off)
+        self.use_splitk = os.environ.get("ACAI_DECODE_SPLITK", "1") != "0" and 4 < batch <= 256
+        self.ws_splitk = None
+        if self.use_splitk:
+            mlp = blocks.layers[0].linear1.out_features
+            self.ws_splitk = max((ops.splitk_workspace(batch, D, k, device) for k in (D, mlp)), key=lambda t: t.numel())
         self.graph = None
         self.launches_per_step = 0
         # sampling mode (GRPO rollouts): None = greedy; else (top_k, temperature).  The seed is device state so that the
@@ -61,6 +69,18 @@ class GreedyDecodeEngine:
         self.uniforms = None
 
     # ---- one decode step (what the graph captures) ------------------------------------------------------------
+    def _proj(self, x, weight, bias, residual=None, norm=None, act=ops.ACT_NONE):
+        """norm(act(x @ weight.T + bias) + residual): at decode batch sizes (<= 256 rows) one split-K GEMM + one reduce kernel
+        with the LayerNorm inside (acai_linear_splitk); otherwise acai_linear_fwd + acai_layernorm_fwd."""
+        dt = self.dt
+        if self.use_splitk and dt == torch.bfloat16:
+            ln = None if norm is None else (norm.weight, norm.bias, norm.eps)
+            y = ops.linear_splitk(x, weight, bias, act=act, residual=residual, ln=ln, out_dtype=dt, workspace=self.ws_splitk)
+            if y is not None:
+                return y
+        y = ops.linear(x, weight, bias, act=act, residual=residual, out_dtype=dt)
+        return y if norm is None else norm(y, out_dtype=dt)
+
     def _step(self):
         dec, dt, D, H = self.dec, self.dt, self.D, self.H
         x = ops.decode_embed(self.seqs, self.step, dec.vocab_embedding.weight, dec.pos_embedding, dt)
@@ -69,14 +89,13 @@ class GreedyDecodeEngine:
             qkv = ops.linear(x, w_(sa.in_proj_weight, dt), sa.in_proj_bias, out_dtype=dt)
             a = ops.decode_attn_paged(qkv[:, :D], qkv[:, D:], self.pool[i], H, 64, self.max_len, self.ws_self, dt,
                                       page_table=self.page_table, step=self.step, len_offset=-1)
-            y = ops.linear(a, w_(sa.out_proj.weight, dt), sa.out_proj.bias, residual=x, out_dtype=dt)
-            x = layer.norm1(y, out_dtype=dt)
-            qc = ops.linear(x, w_(ca.in_proj_weight, dt, rows=(0, D)), ca.in_proj_bias[:D], out_dtype=dt)
+            x = self._proj(a, w_(sa.out_proj.weight, dt), sa.out_proj.bias, residual=x, norm=layer.norm1)
+            qc = self._proj(x, w_(ca.in_proj_weight, dt, rows=(0, D)), ca.in_proj_bias[:D])
             c = ops.decode_attn_paged(qc, None, self.cross[i], H, 64, self.max_mem_len, self.ws_cross, dt,
                                       seq_start=self.seq_start, kv_lens=self.kv_lens)
-            y = ops.linear(c, w_(ca.out_proj.weight, dt), ca.out_proj.bias, residual=x, out_dtype=dt)
-            x = layer.norm2(y, out_dtype=dt)
-            x = layer.mlp_packed(x)
+            x = self._proj(c, w_(ca.out_proj.weight, dt), ca.out_proj.bias, residual=x, norm=layer.norm2)
+            h = ops.linear(x, w_(layer.linear1.weight, dt), layer.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+            x = self._proj(h, w_(layer.linear2.weight, dt), layer.linear2.bias, residual=x, norm=layer.norm3)
         if dec.decoder_blocks.norm is not None:
             x = dec.decoder_blocks.norm(x, out_dtype=dt)
         logits = ops.linear(x, w_(dec.unembed.weight, dt), dec.unembed.bias, out_dtype=dt)

@@ -539,6 +539,45 @@ def _gemm_fusable(*ts):
                                   t.data_ptr() % 16 == 0 for t in ts)
 
 
+def splitk_workspace(M, N, K, device):
+    """Workspace large enough for linear_splitk on [M, K] x [N, K] (acai_linear_splitk_workspace_bytes)."""
+    return _ws(_lib.load().acai_linear_splitk_workspace_bytes(int(M), int(N), int(K)), device)
+
+
+def linear_splitk(x, weight, bias=None, act=ACT_NONE, residual=None, ln=None, out_dtype=None, workspace=None):
+    """LayerNorm?(act(x @ weight.T + bias) + residual) for a SMALL number of rows (decode step): split-K tcgen05 GEMM +
+    one reduce kernel (acai_linear_splitk).  `ln` = (gamma, beta, eps) or None.  Returns None when the problem does not
+    qualify (the caller runs linear [+ layernorm]).  `workspace` (uint8) is reused when large enough."""
+    _cuda(x, weight, bias, residual)
+    if x.dim() != 2 or not _gemm_fusable(x, weight):
+        return None
+    M, K = x.shape
+    N = weight.shape[0]
+    if M == 0 or M > 256:
+        return None
+    lib = _lib.load()
+    need = lib.acai_linear_splitk_workspace_bytes(M, N, K)
+    if workspace is None or workspace.numel() < need:
+        workspace = _ws(need, x.device)
+    out_dtype = out_dtype or x.dtype
+    out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    r2, ldr, rdt = None, 0, 0
+    if residual is not None:
+        r2, rm, rn, ldr = _rows2d(residual)
+        if rm != M or rn != N:
+            raise AcaiError("linear_splitk: residual shape mismatch")
+        rdt = _dt(r2)
+    g, b2, eps = (None, None, 0.0) if ln is None else (_f32c(ln[0]), _f32c(ln[1]), float(ln[2]))
+    name = "acai_linear_splitk" if Profile.active is None else \
+        f"acai_linear_splitk[{M}x{N}x{K}{',gelu' if act else ''}{',res' if r2 is not None else ''}{',ln' if ln else ''}]"
+    ok = _try_call(name, lib.acai_linear_splitk, _p(x), x.stride(0), _p(weight), weight.stride(0), _p(_f32c(bias)), _p(r2), rdt, ldr,
+                   _p(g), _p(b2), eps, _p(out), _DT[out_dtype], out.stride(0), M, N, K, act, _p(workspace), workspace.numel(),
+                   _stream(), flops=2.0 * M * N * K, nbytes=2.0 * (M * K + N * K + M * N))
+    if ok:
+        _bump()                   # two kernels: the split-K GEMM and the reduce
+    return out if ok else None
+
+
 def linear_gelu_train(x, weight, bias, dropout_p=0.0, dropout_seed=0):
     """(z, h) with z = x @ weight.T + bias and h = dropout(gelu(z)), both bf16, from one tcgen05 GEMM
     (acai_linear_gelu_train); None when the operands do not qualify (the caller runs linear + gelu)."""

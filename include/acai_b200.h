@@ -84,6 +84,23 @@ int acai_linear_fwd(const void* a, int32_t a_dtype, int64_t lda,
                     void* out, int32_t out_dtype, int64_t ldo,
                     int32_t M, int32_t N, int32_t K, int32_t act, void* stream);
 
+/* Small-M projections of the decode step, fused with what follows them in the layer (kv_caching.py:193-223:
+ * x = norm1(x + out_proj(attn)), q = W_q x + b_q, x = norm2(x + out_proj(cross)), x = norm3(x + linear2(gelu(linear1 x)))):
+ *   out[M,N] = LayerNorm( act(a[M,K] . w[N,K]^T + bias) + residual )      (LayerNorm only when ln_gamma != NULL)
+ * for M <= 256 bf16 rows.  A skinny GEMM offers too few output tiles to fill 148 SMs, so K is SPLIT across CTAs (every SM
+ * streams a slice of the weight matrix), fp32 partial tiles go to `workspace`, and one reduce kernel - one warp per row,
+ * partials still in L2 - sums them and applies bias, activation, residual and the LayerNorm (two-pass variance in fp32).
+ * Returns ACAI_ERR_UNSUPPORTED, nothing written, when the problem does not qualify (operands not 16-byte aligned /
+ * K % 64, M > 256, no K slices to gain, N % 4, or a LayerNorm row that is not a multiple of 128 <= 1024 columns): the
+ * caller then runs acai_linear_fwd + acai_layernorm_fwd.  `workspace` holds acai_linear_splitk_workspace_bytes(M, N, K). */
+size_t acai_linear_splitk_workspace_bytes(int32_t M, int32_t N, int32_t K);
+int acai_linear_splitk(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias,
+                       const void* residual, int32_t res_dtype, int64_t ldr,
+                       const float* ln_gamma, const float* ln_beta, float ln_eps,
+                       void* out, int32_t out_dtype, int64_t ldo,
+                       int32_t M, int32_t N, int32_t K, int32_t act,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- K5: LayerNorm(x + residual) ---------------------------------------------------------
  * Post-norm sublayer tail `norm(x + sublayer(x))` (kv_caching.py:208,220,222; the
  * nn.TransformerEncoderLayer/DecoderLayer internals) and the final stack norm (eps 1e-6).

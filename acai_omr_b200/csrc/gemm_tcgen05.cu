@@ -487,12 +487,26 @@ splitk_reduce_kernel(const float* __restrict__ ws, int splitk, int M, int N, con
     float4 v[VPL];
 #pragma unroll
     for (int c = 0; c < VPL; ++c) v[c] = *reinterpret_cast<const float4*>(wrow + (c * 32 + lane) * 4);
-    for (int ks = 1; ks < splitk; ++ks) {
-      float4 t[VPL];
+    if (splitk == 4) {                               // the decode step's case: every slice's loads in flight at once
+      float4 t[3][VPL];
 #pragma unroll
-      for (int c = 0; c < VPL; ++c) t[c] = *reinterpret_cast<const float4*>(wrow + ks * slab + (c * 32 + lane) * 4);
+      for (int ks = 1; ks < 4; ++ks) {
 #pragma unroll
-      for (int c = 0; c < VPL; ++c) { v[c].x += t[c].x; v[c].y += t[c].y; v[c].z += t[c].z; v[c].w += t[c].w; }
+        for (int c = 0; c < VPL; ++c) t[ks - 1][c] = *reinterpret_cast<const float4*>(wrow + ks * slab + (c * 32 + lane) * 4);
+      }
+#pragma unroll
+      for (int ks = 1; ks < 4; ++ks) {               // (same summation order as the generic loop)
+#pragma unroll
+        for (int c = 0; c < VPL; ++c) { v[c].x += t[ks - 1][c].x; v[c].y += t[ks - 1][c].y; v[c].z += t[ks - 1][c].z; v[c].w += t[ks - 1][c].w; }
+      }
+    } else {
+      for (int ks = 1; ks < splitk; ++ks) {
+        float4 t[VPL];
+#pragma unroll
+        for (int c = 0; c < VPL; ++c) t[c] = *reinterpret_cast<const float4*>(wrow + ks * slab + (c * 32 + lane) * 4);
+#pragma unroll
+        for (int c = 0; c < VPL; ++c) { v[c].x += t[c].x; v[c].y += t[c].y; v[c].z += t[c].z; v[c].w += t[c].w; }
+      }
     }
     if (bias) {
 #pragma unroll

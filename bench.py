@@ -106,6 +106,17 @@ def gemm_traffic():
         return None
 
 
+def decode_attn_traffic():
+    """DRAM bytes of one cross-attention launch from the committed ncu capture (profiles/r1h_traffic.json), or None."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1h_traffic.json")
+    try:
+        with open(path) as f:
+            k = json.load(f)["decode_attn_tma_kernel"]
+        return k["dram_read_bytes"] + k["dram_write_bytes"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def build_encoder(device):
     from acai_omr_b200 import synth
     from acai_omr_b200.models import models as M
@@ -335,7 +346,7 @@ def run_decode(args, rank, world, device):
                           "algorithmic_bytes_per_step": step_bytes},
         "roofline": {"bound": "hbm", "kernel": "decode_attn_tma_kernel (+combine), cross-attention over one layer's memory cache",
                      "achieved": kern_bytes / (kern_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": kern_bytes / (kern_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                     "frac": kern_bytes / (kern_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": decode_attn_traffic(),
                      "algorithmic_bytes_per_launch": kern_bytes, "ms_per_launch": kern_ms,
                      "peak_source": peaks["source"] + " (HBM copy, MEASURED_PEAKS.json)"},
     }

@@ -42,15 +42,25 @@ constexpr float RESCALE_LOG2 = 8.0f;
 //   NBUF 2, CTAS 4, SB 32: the softmax works on HALF key blocks (SB = 32 keys: S is 128 x 32, two buffers at columns 0..31 and
 //   32..63, O 64..127), so S is double-buffered again inside 128 columns: the tensor-pipe round trip leaves the softmax
 //   warps' critical path and a row's 32 values fit the register budget in one pass.
-template <int NBUF, int CTAS_, int SB_> struct Cfg {
-  static constexpr int CTAS = CTAS_, SB = SB_;
+//   QT 1: Q lives in TMEM as the A operand of the S MMAs (TS form, like P for the PV MMAs) instead of shared memory: an S MMA
+//   then reads only its K slice from shared memory (the SS form re-reads 4 KB of Q per K = 16 step, which makes it
+//   operand-bandwidth bound).  The softmax warps load their own Q row from global memory once and tcgen05.st it.
+//     QT 1, NBUF 1, CTAS 4, SB 32: 128 columns = Q 0..31, S 32..63, O 64..127 (single S buffer);
+//     QT 1, NBUF 2, CTAS 3, SB 32: 128 columns = S 0..31 / 32..63, O 64..127, plus a SECOND 32-column allocation for Q (shared
+//     memory is sized so that a fourth CTA can never be resident: 4 x 128 columns would leave no room for anybody's Q).
+template <int NBUF, int CTAS_, int SB_, int QT_ = 0> struct Cfg {
+  static constexpr int CTAS = CTAS_, SB = SB_, QT = QT_;
   static constexpr int THREADS = CTAS == 2 ? 192 : 256;
-  static constexpr int KV_STAGES = CTAS == 2 ? 4 : (CTAS == 3 ? 3 : 2);
-  static constexpr uint32_t OFF_Q = 0, OFF_K = QTILE, OFF_V = OFF_K + KV_STAGES * KTILE, OFF_BAR = OFF_V + KV_STAGES * KTILE;
+  static constexpr int KV_STAGES = QT ? (CTAS == 3 ? 4 : 3) : (CTAS == 2 ? 4 : (CTAS == 3 ? 3 : 2));
+  static constexpr uint32_t OFF_Q = 0, OFF_K = QT ? 0 : QTILE, OFF_V = OFF_K + KV_STAGES * KTILE, OFF_BAR = OFF_V + KV_STAGES * KTILE;
   static constexpr size_t SMEM = OFF_BAR + 256;
-  static constexpr uint32_t TMEM_COLS = NBUF * SB + 64 > 128 ? 256 : 128;
-  static constexpr uint32_t O_COL = NBUF * SB;
-  static_assert(CTAS * TMEM_COLS <= 512 && (SB == 32 || SB == 64), "TMEM budget");
+  static constexpr bool Q_SECOND_ALLOC = QT && NBUF * SB + 64 + 32 > 128;
+  static constexpr uint32_t Q_COL = 0;                                       // (inside its own allocation when Q_SECOND_ALLOC)
+  static constexpr uint32_t S_COL = (QT && !Q_SECOND_ALLOC) ? 32 : 0;
+  static constexpr uint32_t TMEM_COLS = S_COL + NBUF * SB + 64 > 128 ? 256 : 128;
+  static constexpr uint32_t O_COL = S_COL + NBUF * SB;
+  static_assert(CTAS * (TMEM_COLS + (Q_SECOND_ALLOC ? 32 : 0)) <= 512 && (SB == 32 || SB == 64), "TMEM budget");
+  static_assert(!Q_SECOND_ALLOC || (CTAS + 1) * (SMEM + 1024) > 233472, "a surplus CTA could take TMEM columns and deadlock the Q allocations");
 };
 }  // namespace fa
 using namespace fa;
@@ -60,6 +70,7 @@ struct AttnParams {
   void* out; int out_dt; int64_t o_stride;
   int causal; float scale_log2;
   float* lse; int total_q;      // optional [heads, total_q] log2-domain log-sum-exp of every query row (for the backward)
+  const __nv_bfloat16* q; int64_t q_stride;   // raw Q rows (the QT variants load Q themselves)
   AttnDropout drop;             // attention-probability dropout (training): P is masked before P V, l sums the unmasked P
 };
 
@@ -67,15 +78,15 @@ struct AttnParams {
 // tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
 // POLY: how many of every 4 exponentials are evaluated with exp2_fma on the FMA pipe instead of MUFU.EX2 (0, 1 or 2).
 // The MUFU unit (16 results / clk / SM) is this kernel's busiest pipe; the FMA pipe is mostly idle.
-template <int DH, bool DROP, int POLY, int NBUF, int CTAS, int SB>
-__global__ void __launch_bounds__((Cfg<NBUF, CTAS, SB>::THREADS), CTAS)
+template <int DH, bool DROP, int POLY, int NBUF, int CTAS, int SB, int QT>
+__global__ void __launch_bounds__((Cfg<NBUF, CTAS, SB, QT>::THREADS), CTAS)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
-  using C = Cfg<NBUF, CTAS, SB>;
+  using C = Cfg<NBUF, CTAS, SB, QT>;
   constexpr int R = BKV / SB;                        // softmax blocks per K/V tile
   constexpr int KV_STAGES = C::KV_STAGES;
   constexpr uint32_t OFF_Q = C::OFF_Q, OFF_K = C::OFF_K, OFF_V = C::OFF_V, OFF_BAR = C::OFF_BAR, TMEM_COLS = C::TMEM_COLS,
-                     O_COL = C::O_COL;
+                     O_COL = C::O_COL, S_COL = C::S_COL;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* q_full = bars;                          // 1
@@ -98,7 +109,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   const int n_sb = (kv_end + SB - 1) / SB;         // softmax blocks (S / P granularity)
 
   if (warp == 5 && lane == 0) {
-    ptx::mbar_init(q_full, 1);
+    ptx::mbar_init(q_full, QT ? 128 : 1);
     for (int s = 0; s < KV_STAGES; ++s) { ptx::mbar_init(&kv_full[s], 1); ptx::mbar_init(&kv_empty[s], 1); }
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 128); }
     ptx::mbar_init(o_step, 1); ptx::mbar_init(o_full, 1);
@@ -106,12 +117,14 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   }
   if (warp == 4) {
     if (lane == 0) { ptx::prefetch_tensormap(&tma_q); ptx::prefetch_tensormap(&tma_k); ptx::prefetch_tensormap(&tma_v); }
+    if constexpr (C::Q_SECOND_ALLOC) ptx::tmem_alloc_keep_permit(tmem_slot + 1, 32);
     ptx::tmem_alloc(tmem_slot, TMEM_COLS);
   }
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_q = (C::Q_SECOND_ALLOC ? tmem_slot[1] : tmem_base) + C::Q_COL;
 
   // (CTAS 4: the register budget moves from the two helper warps to the softmax warps inside each role's own branch -
   // ptxas sizes a branch by the setmaxnreg that dominates it)
@@ -121,9 +134,11 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   if (warp == 4) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && n_kv > 0) {
-      ptx::mbar_arrive_expect_tx(q_full, QTILE);
       const int hcol = (h * DH) & ~63;
-      ptx::tma_load_2d(smem + OFF_Q, &tma_q, q_full, hcol, q0 + qb * BQ);
+      if constexpr (!QT) {
+        ptx::mbar_arrive_expect_tx(q_full, QTILE);
+        ptx::tma_load_2d(smem + OFF_Q, &tma_q, q_full, hcol, q0 + qb * BQ);
+      }
       int s = 0; uint32_t ph = 0;
       for (int j = 0; j < n_kv; ++j) {
         ptx::mbar_wait(&kv_empty[s], ph ^ 1);
@@ -147,8 +162,10 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
         const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024) + hoff +
                                (uint64_t)((i % R) * (SB * 128 >> 4));
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k)
-          ptx::umma_f16_ss(tmem_base + (i % NBUF) * SB, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+        for (int k = 0; k < DH / 16; ++k) {
+          if constexpr (QT) ptx::umma_f16_ts(tmem_base + S_COL + (i % NBUF) * SB, tmem_q + k * 8, kdesc + 2 * k, IDESC_S, k != 0);
+          else ptx::umma_f16_ss(tmem_base + S_COL + (i % NBUF) * SB, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+        }
         ptx::umma_commit(&s_full[i % NBUF]);
       };
       ptx::mbar_wait(q_full, 0);
@@ -161,7 +178,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
         const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + st * KTILE), 1024) + hoff;
 #pragma unroll
         for (int kk = 0; kk < SB / 16; ++kk)        // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
-          ptx::umma_f16_ts(tmem_base + O_COL, tmem_base + (i % NBUF) * SB + kk * 8,
+          ptx::umma_f16_ts(tmem_base + O_COL, tmem_base + S_COL + (i % NBUF) * SB + kk * 8,
                            vdesc + (uint64_t)((i % R) * (SB / 16) + kk) * (16 * 128 >> 4), IDESC_O, (i | kk) != 0);
         if (i % R == R - 1 || i == n_sb - 1) ptx::umma_commit(&kv_empty[st]);   // last reader of this K/V tile
         ptx::umma_commit(o_step);
@@ -184,9 +201,25 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
     float m = -INFINITY, l = 0.0f;
     const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? qi : 0));
     const uint32_t rowconst = DROP ? attn_drop_rowconst(p.drop.seed, rowkey) : 0u;
+    if constexpr (QT) {                             // this thread's Q row -> TMEM (bf16 pairs per column, the TS A-operand layout)
+      if (n_kv > 0) {
+        uint32_t qr[DH / 2];
+        const uint4* src = reinterpret_cast<const uint4*>(p.q + (int64_t)(q0 + (valid ? qi : 0)) * p.q_stride + (int64_t)h * DH);
+#pragma unroll
+        for (int c = 0; c < DH / 8; ++c) {
+          const uint4 v4 = valid ? __ldg(src + c) : make_uint4(0u, 0u, 0u, 0u);
+          qr[4 * c] = v4.x; qr[4 * c + 1] = v4.y; qr[4 * c + 2] = v4.z; qr[4 * c + 3] = v4.w;
+        }
+        if constexpr (DH == 64) ptx::tmem_st_32x32(tmem_q + lane_addr, qr);
+        else ptx::tmem_st_32x16(tmem_q + lane_addr, qr);
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(q_full);
+      }
+    }
 
     for (int j = 0; j < n_sb; ++j) {
-      const uint32_t tmem_s = tmem_base + lane_addr + (j % NBUF) * SB;
+      const uint32_t tmem_s = tmem_base + lane_addr + S_COL + (j % NBUF) * SB;
       ptx::mbar_wait(&s_full[j % NBUF], (j / NBUF) & 1);
       ptx::tc_fence_after();
       // (SB 64 with four CTAs: S is read from TMEM twice - maximum, then exponentials - so that <= 32 values are live)
@@ -329,20 +362,23 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 4) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  if (warp == 4) {
+    ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+    if constexpr (C::Q_SECOND_ALLOC) ptx::tmem_dealloc(tmem_slot[1], 32);
+  }
 }
 
-template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2, int SB = 64>
+template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2, int SB = 64, int QT = 0>
 static int launch_fwd(dim3 grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                       cudaStream_t st) {
   static bool attr_set = false;
-  constexpr size_t SMEM = Cfg<NBUF, CTAS, SB>::SMEM;
+  constexpr size_t SMEM = Cfg<NBUF, CTAS, SB, QT>::SMEM;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_set = true;
   }
-  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB><<<grid, Cfg<NBUF, CTAS, SB>::THREADS, SMEM, st>>>(tq, tk, tv, p);
+  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT><<<grid, Cfg<NBUF, CTAS, SB, QT>::THREADS, SMEM, st>>>(tq, tk, tv, p);
   return ACAI_OK;
 }
 
@@ -370,13 +406,17 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
   // softmax block (keys per S / P round) of the four-CTA variant: 32 (half blocks, S double-buffered) is the measured best;
   // ACAI_ATTN_SB = 64 selects the single-buffer two-pass variant for A/B runs
   static const int sb = [] { const char* e = getenv("ACAI_ATTN_SB"); return e && atoi(e) == 64 ? 64 : 32; }();
-  AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q, drop};
+  // Q as a TMEM-resident MMA operand (see Cfg): ACAI_ATTN_QT = 1 (four CTAs, single S buffer) / 2 (three CTAs, two S buffers)
+  static const int qt = [] { const char* e = getenv("ACAI_ATTN_QT"); const int v = e ? atoi(e) : 0; return v == 1 || v == 2 ? v : 0; }();
+  AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q,
+               static_cast<const __nv_bfloat16*>(q), qs, drop};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
 #define ACAI_FWD32(DH_, DROP_)                                                                                    \
   (poly == 0 ? launch_fwd<DH_, DROP_, 0, 2, 4, 32>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1, 2, 4, 32>(grid, tq, tk, tv, p, st) \
                                                                                         : launch_fwd<DH_, DROP_, 2, 2, 4, 32>(grid, tq, tk, tv, p, st))
 #define ACAI_FWD(DH_, DROP_)                                                                                      \
-  (ctas == 4 && sb == 32 ? ACAI_FWD32(DH_, DROP_) : ctas == 4 ? launch_fwd<DH_, DROP_, 0, 1, 4>(grid, tq, tk, tv, p, st) : ctas == 3 ? launch_fwd<DH_, DROP_, 0, 1, 3>(grid, tq, tk, tv, p, st)       \
+  (qt == 1 ? launch_fwd<DH_, DROP_, 0, 1, 4, 32, 1>(grid, tq, tk, tv, p, st) : qt == 2 ? launch_fwd<DH_, DROP_, 0, 2, 3, 32, 1>(grid, tq, tk, tv, p, st) : \
+   ctas == 4 && sb == 32 ? ACAI_FWD32(DH_, DROP_) : ctas == 4 ? launch_fwd<DH_, DROP_, 0, 1, 4>(grid, tq, tk, tv, p, st) : ctas == 3 ? launch_fwd<DH_, DROP_, 0, 1, 3>(grid, tq, tk, tv, p, st)       \
              : launch_fwd<DH_, DROP_, 0, 2, 2>(grid, tq, tk, tv, p, st))
   if (drop.thr == 0) rc = head_dim == 64 ? ACAI_FWD(64, false) : ACAI_FWD(32, false);
   else rc = head_dim == 64 ? ACAI_FWD(64, true) : ACAI_FWD(32, true);

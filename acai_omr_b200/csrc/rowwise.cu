@@ -1,7 +1,10 @@
 // Row-wise memory-bound kernels: LayerNorm(+residual), token embedding, greedy epilogue,
 // packed <-> padded conversion, KV append.  All HBM-bound; one CTA (or warp) per row,
 // coalesced loads along the feature dimension.
+#include <cstdlib>
+
 #include "common.cuh"
+#include "ptx_sm100.cuh"
 
 namespace acai {
 
@@ -184,6 +187,109 @@ layernorm_bf16_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res
     for (int i = 0; i < NV; ++i) { cur[i] = nxt[i]; cur_r[i] = nxt_r[i]; }
     row = next;
   }
+}
+
+// bf16 -> bf16, no residual, TMA version: every warp runs a private ring of LNT_STAGES row buffers in shared memory.  Lane 0
+// keeps LNT_STAGES - 1 bulk loads (cp.async.bulk, one whole row each) in flight, the warp normalises a landed row in place
+// and lane 0 sends it back with a bulk store - ~4 rows per warp x 24 warps per SM in flight without holding them in registers
+// (the register version above tops out at ~3.8 TB/s: its bytes in flight are bounded by registers x resident warps).
+constexpr int LNT_WARPS = 8, LNT_MAX_STAGES = 12;   // stages are chosen by the host so that two CTAs fill an SM's shared memory
+template <int NV>
+__global__ void __launch_bounds__(LNT_WARPS * 32)
+layernorm_bf16_tma_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                          float eps, __nv_bfloat16* __restrict__ out, int rows, int cols, int LNT_STAGES, int rpo) {
+  // one ring slot = one bulk copy = `rpo` consecutive rows (small rows are paired: a 1.5 KB copy per mbarrier round trip leaves
+  // the copy engine's per-operation overhead exposed)
+  extern __shared__ __align__(128) uint8_t lnt_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t row_bytes = (uint32_t)cols * 2, slot_bytes = row_bytes * (uint32_t)rpo;
+  uint8_t* ring = lnt_smem + (size_t)warp * LNT_STAGES * slot_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(lnt_smem + (size_t)LNT_WARPS * LNT_STAGES * slot_bytes) + warp * LNT_STAGES;
+  const int nwarps = gridDim.x * LNT_WARPS, first = blockIdx.x * LNT_WARPS + warp;
+  const int c8 = cols >> 3;
+  if (lane == 0) {
+    for (int s = 0; s < LNT_STAGES; ++s) ptx::mbar_init(&bars[s], 1);
+    ptx::fence_barrier_init();
+  }
+  __syncwarp();
+  const int items = (rows + rpo - 1) / rpo;           // an item = rpo rows (the last one may be short)
+  const int n_mine = first < items ? (items - first + nwarps - 1) / nwarps : 0;
+  auto item_rows = [&](int k) { const int r0 = (first + k * nwarps) * rpo; return rows - r0 < rpo ? rows - r0 : rpo; };
+  auto issue = [&](int k, int s) {                   // k-th item of this warp into slot s = k % LNT_STAGES (lane 0 only)
+    const uint32_t bytes = row_bytes * (uint32_t)item_rows(k);
+    ptx::mbar_arrive_expect_tx(&bars[s], bytes);
+    ptx::bulk_load_1d(ring + (size_t)s * slot_bytes, x + (int64_t)(first + (int64_t)k * nwarps) * rpo * cols, bytes, &bars[s]);
+  };
+  if (lane == 0) {
+    for (int k = 0; k < LNT_STAGES - 1 && k < n_mine; ++k) issue(k, k);
+  }
+  // gamma / beta of this lane's columns stay in registers for every row
+  float4 g[NV][2], b[NV][2];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = i * 32 + lane;
+    if (c < c8) {
+      g[i][0] = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c); g[i][1] = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * c + 1);
+      b[i][0] = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c); b[i][1] = __ldg(reinterpret_cast<const float4*>(beta) + 2 * c + 1);
+    }
+  }
+  const float inv_n = 1.0f / (float)cols;
+  int s = 0; uint32_t phase = 0;                     // slot and barrier parity of row k
+  for (int k = 0; k < n_mine; ++k) {
+    uint8_t* const slot0 = ring + (size_t)s * slot_bytes;
+    const int nr = item_rows(k);
+    ptx::mbar_wait(&bars[s], phase);
+    for (int rr = 0; rr < nr; ++rr) {
+    uint4* slot = reinterpret_cast<uint4*>(slot0 + (size_t)rr * row_bytes);
+    float f[NV][8];
+    float sum = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 32 + lane;
+      if (c < c8) {
+        const uint4 v = slot[c];
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float2 t = __bfloat1622float2(h[e]); f[i][2 * e] = t.x; f[i][2 * e + 1] = t.y; sum += t.x + t.y; }
+      }
+    }
+    const float mu = warp_sum(sum) * inv_n;
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      if (i * 32 + lane < c8) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { const float d = f[i][e] - mu; q += d * d; }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(q) * inv_n + eps);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 32 + lane;
+      if (c < c8) {
+        uint4 o; __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+        ho[0] = __floats2bfloat162_rn((f[i][0] - mu) * rstd * g[i][0].x + b[i][0].x, (f[i][1] - mu) * rstd * g[i][0].y + b[i][0].y);
+        ho[1] = __floats2bfloat162_rn((f[i][2] - mu) * rstd * g[i][0].z + b[i][0].z, (f[i][3] - mu) * rstd * g[i][0].w + b[i][0].w);
+        ho[2] = __floats2bfloat162_rn((f[i][4] - mu) * rstd * g[i][1].x + b[i][1].x, (f[i][5] - mu) * rstd * g[i][1].y + b[i][1].y);
+        ho[3] = __floats2bfloat162_rn((f[i][6] - mu) * rstd * g[i][1].z + b[i][1].z, (f[i][7] - mu) * rstd * g[i][1].w + b[i][1].w);
+        slot[c] = o;
+      }
+    }
+    }
+    ptx::fence_proxy_async_smem();                   // the generic-proxy writes above, before the bulk store reads them
+    __syncwarp();
+    if (lane == 0) {
+      ptx::bulk_store_1d(out + (int64_t)(first + (int64_t)k * nwarps) * rpo * cols, slot0, row_bytes * (uint32_t)nr);
+      ptx::tma_store_commit();
+      // slot (k - 1) % STAGES is refilled with row k - 1 + STAGES: its store (one behind this one) must have read the slot
+      ptx::tma_store_wait_read<1>();
+      // (k = 0 refills nothing: it takes the ring's last slot, which has not been used yet)
+      if (k + LNT_STAGES - 1 < n_mine) issue(k + LNT_STAGES - 1, s == 0 ? LNT_STAGES - 1 : s - 1);
+    }
+    __syncwarp();
+    if (++s == LNT_STAGES) { s = 0; phase ^= 1; }
+  }
+  if (lane == 0) ptx::tma_store_wait<0>();
 }
 
 __global__ void embed_tokens_kernel(const int64_t* __restrict__ ids, const float* __restrict__ table,
@@ -387,6 +493,30 @@ extern "C" int acai_layernorm_fwd(const void* x, int32_t x_dtype, const void* re
     dim3 grid((rows + 7) / 8);
     cudaStream_t st = (cudaStream_t)stream;
     if (x_dtype == ACAI_BF16 && out_dtype == ACAI_BF16 && !out2 && (!residual || res_dtype == ACAI_BF16) && nv <= 4) {
+      // large row counts without a residual: the per-warp TMA rings (ACAI_LN_TMA=0 keeps the register kernel for A/B runs)
+      static const bool use_tma = [] { const char* e = getenv("ACAI_LN_TMA"); return !(e && atoi(e) == 0); }();
+      if (use_tma && !residual && rows >= 4096) {
+        const int rpo = cols * 2 >= 2048 ? 1 : (cols * 2 >= 1024 ? 2 : 4);               // rows per bulk copy (>= 2 KB each)
+        int stages = (int)((size_t)100 * 1024 / ((size_t)acai::LNT_WARPS * rpo * cols * 2));   // ~100 KB per CTA, two CTAs per SM
+        stages = stages < 3 ? 3 : (stages > acai::LNT_MAX_STAGES ? acai::LNT_MAX_STAGES : stages);
+        const size_t smem = (size_t)acai::LNT_WARPS * stages * ((size_t)rpo * cols * 2 + 8);
+        const int per_sm = (int)(227 * 1024 / (smem + 1024));
+        const int want = ((rows + rpo - 1) / rpo + acai::LNT_WARPS - 1) / acai::LNT_WARPS, capt = acai::num_sms() * (per_sm < 1 ? 1 : per_sm);
+        dim3 tg(want < capt ? want : capt);
+#define LNT(NV)                                                                                                          \
+  do {                                                                                                                   \
+    static bool attr_set = false;                                                                                        \
+    if (!attr_set) {                                                                                                     \
+      ACAI_CUDA(cudaFuncSetAttribute(acai::layernorm_bf16_tma_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+      attr_set = true;                                                                                                   \
+    }                                                                                                                    \
+    acai::layernorm_bf16_tma_kernel<NV><<<tg, acai::LNT_WARPS * 32, smem, st>>>((const __nv_bfloat16*)x, gamma, beta, eps, \
+                                                                               (__nv_bfloat16*)out, rows, cols, stages, rpo); \
+  } while (0)
+        if (nv <= 1) LNT(1); else if (nv <= 2) LNT(2); else if (nv <= 3) LNT(3); else LNT(4);
+#undef LNT
+        return launch_status("layernorm_bf16_tma");
+      }
       const int ctas = (rows + 7) / 8, cap = acai::num_sms() * 6;
       dim3 pg(ctas < cap ? ctas : cap);
 #define LNB(NV) acai::layernorm_bf16_kernel<NV><<<pg, 256, 0, st>>>((const uint4*)x, (const uint4*)residual, gamma, beta, eps, \

@@ -71,10 +71,12 @@ def test_layernorm(rows, cols, eps):
     close(y16, ref16, 1e-2, 1e-2)
 
 
-@pytest.mark.parametrize("rows,cols", [(1, 768), (9, 8), (5000, 768), (12345, 1024), (4737, 200), (300, 96)])
+@pytest.mark.parametrize("rows,cols", [(1, 768), (9, 8), (5000, 768), (12345, 1024), (4737, 200), (300, 96), (4097, 768),
+                                       (70001, 512), (4099, 64)])
 @pytest.mark.parametrize("with_res", [False, True])
 def test_layernorm_bf16_persistent(rows, cols, with_res):
-    """bf16 -> bf16 LayerNorm (persistent warp-per-row kernel with next-row prefetch), more rows than resident warps."""
+    """bf16 -> bf16 LayerNorm: the persistent warp-per-row kernel with next-row prefetch (residual or < 4096 rows) and the
+    per-warp TMA rings (>= 4096 rows, no residual; 1 / 2 / 4 rows per bulk copy, short last item, more items than warps)."""
     x = (rnd(rows, cols, seed=5, scale=2.0) + 0.3).bfloat16()
     r = rnd(rows, cols, seed=6).bfloat16() if with_res else None
     g, b = rnd(cols, seed=7) * 0.1 + 1.0, rnd(cols, seed=8) * 0.1

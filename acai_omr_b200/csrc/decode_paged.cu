@@ -301,13 +301,16 @@ namespace acai {
 int decode_attn_tma(const void* q, int64_t q_stride, const void* new_kv, int64_t new_kv_stride, void* kv_rows,
                     int64_t kv_rows_total, const int32_t* page_table, int table_stride, const int32_t* seq_start,
                     const int32_t* kv_lens, const int32_t* step_ptr, int len_offset, int max_kv_len, int batch, int heads,
-                    float scale, float* ws, int max_chunks, int chunk_tokens, cudaStream_t st);
+                    float scale, float* ws, int max_chunks, int chunk_tokens, int32_t* counters, void* out, int out_dt,
+                    int64_t o_stride, cudaStream_t st);
+// the workspace starts with one int32 arrival counter per (sequence, head) for the in-kernel split-KV combine
+static inline size_t counter_bytes(int batch, int heads) { return (((size_t)batch * heads * sizeof(int32_t)) + 255) & ~(size_t)255; }
 constexpr int DCH_MIN = 64;   // smallest split-KV chunk (small batches: more CTAs)
 }
 
 extern "C" size_t acai_decode_workspace_bytes(int32_t batch, int32_t heads, int32_t max_kv_len) {
   const size_t chunks = (size_t)(max_kv_len + DCH_MIN - 1) / DCH_MIN;
-  return (size_t)batch * chunks * heads * (DHD + 2) * sizeof(float);
+  return counter_bytes(batch, heads) + (size_t)batch * chunks * heads * (DHD + 2) * sizeof(float);
 }
 
 extern "C" int acai_decode_attn_paged(const void* q, int64_t q_stride, const void* new_kv, int64_t new_kv_stride,
@@ -327,7 +330,8 @@ extern "C" int acai_decode_attn_paged(const void* q, int64_t q_stride, const voi
                  !((uintptr_t)kv_rows & 15) && !((uintptr_t)new_kv & 15), "acai_decode_attn_paged: operands must be 16-byte aligned");
   ACAI_CHECK_ARG(workspace_bytes >= acai_decode_workspace_bytes(batch, heads, max_kv_len), "acai_decode_attn_paged: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
-  float* ws = reinterpret_cast<float*>(workspace);
+  int32_t* counters = reinterpret_cast<int32_t*>(workspace);
+  float* ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + counter_bytes(batch, heads));
   int chunk_tokens = DCH, rc = ACAI_ERR_UNSUPPORTED;
   if (dtype == ACAI_BF16 && kv_rows_total > 0) {
     // TMA-streaming kernel; chunk length: the longest of 256/128/64 that still gives every SM a few CTAs
@@ -335,9 +339,9 @@ extern "C" int acai_decode_attn_paged(const void* q, int64_t q_stride, const voi
     int ct = 256;
     while (ct > DCH_MIN && (int64_t)((max_kv_len + ct - 1) / ct) * hg * batch < 4 * num_sms()) ct >>= 1;
     rc = decode_attn_tma(q, q_stride, new_kv, new_kv_stride, kv_rows, kv_rows_total, page_table, table_stride, seq_start,
-                         kv_lens, step_ptr, len_offset, max_kv_len, batch, heads, scale, ws, (max_kv_len + ct - 1) / ct, ct, st);
-    if (rc == ACAI_OK) chunk_tokens = ct;
-    else if (rc != ACAI_ERR_UNSUPPORTED) return rc;
+                         kv_lens, step_ptr, len_offset, max_kv_len, batch, heads, scale, ws, (max_kv_len + ct - 1) / ct, ct, counters, out,
+                         out_dtype, o_stride, st);
+    if (rc != ACAI_ERR_UNSUPPORTED) return rc;         // (the TMA kernel folds its own split-KV partials: no combine launch)
   }
   const int chunks = (max_kv_len + chunk_tokens - 1) / chunk_tokens;
   if (rc == ACAI_ERR_UNSUPPORTED) {

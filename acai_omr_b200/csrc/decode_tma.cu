@@ -8,7 +8,9 @@
 // swizzled tile (conflict-free: 16-byte piece c of row r sits at (c ^ (r & 7))), dots it with the head's query held
 // in registers, keeps a private online-softmax state (lazy rescale: the running maximum only moves when a score beats
 // it by more than 2^8) and accumulates p * V[token] into 64 private fp32 accumulators.  The 32 lane states are merged
-// once per chunk through shared memory; chunk partials go to the workspace that decode_combine folds.
+// once per chunk through shared memory.  Split-KV combine: a sequence with one chunk writes its output directly; otherwise
+// every warp publishes its chunk partial to the workspace, bumps an arrival counter of its (sequence, head), and the last
+// one in folds the partials in chunk order (same arithmetic as decode_combine_kernel) - no second launch.
 // The token appended this step (self-attention) is taken from the projection output, attended to, and written to the
 // cache by the CTA that owns its position (KVCache.update, kv_caching.py:57-109).
 #include "common.cuh"
@@ -34,6 +36,9 @@ struct DecodeTmaArgs {
   const int32_t* page_table; int table_stride;
   const int32_t* seq_start; const int32_t* kv_lens; const int32_t* step_ptr; int len_offset;
   int heads; float scale_log2; float* ws; int max_chunks; int chunk_tokens;
+  // split-KV combine inside this kernel: the LAST warp of a (sequence, head) to publish its partial folds all of them
+  int32_t* counters;            // [batch, heads], zero before the first launch; every launch leaves them zero
+  void* out; int out_dt; int64_t o_stride;
 };
 
 __device__ __forceinline__ void bf16x8_to_f32(const uint4& w, float (&f)[8]) {
@@ -93,7 +98,14 @@ decode_attn_tma_kernel(const __grid_constant__ CUtensorMap tma_kv, DecodeTmaArgs
   const int len = a.kv_lens ? a.kv_lens[b] : (*a.step_ptr + a.len_offset);     // tokens already in the cache
   const int total = len + (a.new_kv ? 1 : 0);
   const int t_begin = chunk * a.chunk_tokens;
-  if (t_begin >= total || h >= H) return;                                       // warp-uniform; no CTA-wide sync below
+  if (h >= H) return;                                                           // warp-uniform; no CTA-wide sync below
+  if (t_begin >= total) {
+    if (chunk == 0) {                                                           // no keys at all: the output row is zero
+      st_from_float(a.out, (int64_t)b * a.o_stride + h * HD + lane, a.out_dt, 0.0f);
+      st_from_float(a.out, (int64_t)b * a.o_stride + h * HD + 32 + lane, a.out_dt, 0.0f);
+    }
+    return;
+  }
   const int t_end = min(total, t_begin + a.chunk_tokens);
   const int c_end = min(len, t_end);                                            // cached tokens of this chunk
   const int n_st = c_end > t_begin ? (c_end - t_begin + TOK - 1) / TOK : 0;
@@ -170,16 +182,50 @@ decode_attn_tma_kernel(const __grid_constant__ CUtensorMap tma_kv, DecodeTmaArgs
   float o0 = 0.0f, o1 = 0.0f;
 #pragma unroll 8
   for (int r = 0; r < 32; ++r) { o0 += tr[r * 65 + lane]; o1 += tr[r * 65 + 32 + lane]; }
+  const int n_chunks = min(a.max_chunks, (total + a.chunk_tokens - 1) / a.chunk_tokens);   // chunks that reach this point
+  const int64_t orow = (int64_t)b * a.o_stride + h * HD;
+  if (n_chunks == 1) {                                  // nothing to fold (same arithmetic as the fold of one partial)
+    st_from_float(a.out, orow + lane, a.out_dt, lsum > 0.0f ? o0 / lsum : 0.0f);
+    st_from_float(a.out, orow + 32 + lane, a.out_dt, lsum > 0.0f ? o1 / lsum : 0.0f);
+    return;
+  }
   float* w = a.ws + (((int64_t)b * a.max_chunks + chunk) * H + h) * (HD + 2);
-  w[lane] = o0; w[32 + lane] = o1;
-  if (lane == 0) { w[HD] = M; w[HD + 1] = lsum; }
+  __stcg(w + lane, o0); __stcg(w + 32 + lane, o1);
+  if (lane == 0) { __stcg(w + HD, M); __stcg(w + HD + 1, lsum); }
+  __threadfence();                                      // this warp's partial is visible device-wide ...
+  __syncwarp();
+  int old = 0;
+  if (lane == 0) old = atomicAdd(a.counters + b * H + h, 1);   // ... before it is counted
+  old = __shfl_sync(0xffffffffu, old, 0);
+  if (old != n_chunks - 1) return;
+  // last one in: out[b, h*64 + e] = sum_c acc_c[e] 2^(m_c - M) / sum_c l_c 2^(m_c - M), chunks in ascending order
+  __threadfence();
+  if (lane == 0) a.counters[b * H + h] = 0;            // ready for the next launch
+  const float* w0 = a.ws + ((int64_t)b * a.max_chunks * H + h) * (HD + 2);
+  const int64_t cs = (int64_t)H * (HD + 2);
+  float Mx = -INFINITY;
+#pragma unroll 4
+  for (int c = 0; c < n_chunks; ++c) Mx = fmaxf(Mx, __ldcg(w0 + c * cs + HD));
+  float n0 = 0.0f, n1 = 0.0f, den = 0.0f;
+#pragma unroll 4
+  for (int c = 0; c < n_chunks; ++c) {
+    const float mc = __ldcg(w0 + c * cs + HD), lc = __ldcg(w0 + c * cs + HD + 1);
+    const float a0 = __ldcg(w0 + c * cs + lane), a1 = __ldcg(w0 + c * cs + 32 + lane);
+    if (mc > -INFINITY) {
+      const float fc = fast_exp2(mc - Mx);
+      n0 = fmaf(a0, fc, n0); n1 = fmaf(a1, fc, n1); den = fmaf(lc, fc, den);
+    }
+  }
+  st_from_float(a.out, orow + lane, a.out_dt, den > 0.0f ? n0 / den : 0.0f);
+  st_from_float(a.out, orow + 32 + lane, a.out_dt, den > 0.0f ? n1 / den : 0.0f);
 }
 
 // returns ACAI_ERR_UNSUPPORTED when the problem does not qualify (the caller then runs the register kernel)
 int decode_attn_tma(const void* q, int64_t q_stride, const void* new_kv, int64_t new_kv_stride, void* kv_rows,
                     int64_t kv_rows_total, const int32_t* page_table, int table_stride, const int32_t* seq_start,
                     const int32_t* kv_lens, const int32_t* step_ptr, int len_offset, int max_kv_len, int batch, int heads,
-                    float scale, float* ws, int max_chunks, int chunk_tokens, cudaStream_t st) {
+                    float scale, float* ws, int max_chunks, int chunk_tokens, int32_t* counters, void* out, int out_dt,
+                    int64_t o_stride, cudaStream_t st) {
   using namespace dt;
   if (kv_rows_total <= 0 || chunk_tokens % TOK != 0 || batch > 65535) return ACAI_ERR_UNSUPPORTED;
   CUtensorMap tm;
@@ -192,7 +238,7 @@ int decode_attn_tma(const void* q, int64_t q_stride, const void* new_kv, int64_t
   }
   DecodeTmaArgs a{reinterpret_cast<const __nv_bfloat16*>(q), q_stride, reinterpret_cast<const __nv_bfloat16*>(new_kv),
                   new_kv_stride, reinterpret_cast<__nv_bfloat16*>(kv_rows), page_table, table_stride, seq_start, kv_lens,
-                  step_ptr, len_offset, heads, scale * 1.4426950408889634f, ws, max_chunks, chunk_tokens};
+                  step_ptr, len_offset, heads, scale * 1.4426950408889634f, ws, max_chunks, chunk_tokens, counters, out, out_dt, o_stride};
   const int chunks = (max_kv_len + chunk_tokens - 1) / chunk_tokens;
   dim3 grid(chunks, (heads + WARPS - 1) / WARPS, batch);
   decode_attn_tma_kernel<<<grid, WARPS * 32, SMEM, st>>>(tm, a);

@@ -363,7 +363,7 @@ def pack_padded(padded, cu_seqlens, total, out_dtype=None):
 # ------------------------------------------------------------------------------------------ decode engine ops
 def decode_workspace(batch, heads, max_kv_len, device):
     n = _lib.load().acai_decode_workspace_bytes(batch, heads, max_kv_len)
-    return torch.empty(n, dtype=torch.uint8, device=device)
+    return torch.zeros(n, dtype=torch.uint8, device=device)       # starts with the (self-resetting) arrival counters: must be zero
 
 
 def decode_attn_paged(q, new_kv, kv_rows, heads, head_dim, max_kv_len, workspace, out_dtype, page_table=None,
@@ -380,7 +380,8 @@ def decode_attn_paged(q, new_kv, kv_rows, heads, head_dim, max_kv_len, workspace
           page_table.stride(0) if page_table is not None else 0, _p(seq_start), _p(kv_lens), _p(step), int(len_offset),
           int(max_kv_len), B, heads, head_dim, float(scale or 1.0 / math.sqrt(head_dim)), _p(out), _DT[out_dtype],
           out.stride(0), _p(workspace), workspace.numel(), kv_rows.shape[0], _stream(), nbytes=nbytes)
-    _bump()  # two kernels per call (split-KV pass + combine)
+    if q.dtype != torch.bfloat16:
+        _bump()  # fp32 caches: split-KV pass + a combine launch (the bf16 TMA kernel folds its partials itself)
     return out
 
 

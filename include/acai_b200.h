@@ -172,8 +172,11 @@ int acai_kv_append(const void* k_new, const void* v_new, int32_t src_dtype, int6
  * self-attention pool) or as seq_start[b] + t (the packed encoder-memory cache, no padding rows).  If `new_kv` is
  * given, this step's [K|V] row of every sequence is appended at position len (KVCache.update, kv_caching.py:57-109)
  * and attended to.  len = kv_lens[b], or *step_ptr + len_offset (device-side step counter, so that one captured
- * CUDA graph serves every step).  head_dim must be 64; q/new_kv/cache share `dtype`.  Split-KV over 256-token chunks
- * with a combine pass; `workspace` holds the partials (acai_decode_workspace_bytes). */
+ * CUDA graph serves every step).  head_dim must be 64; q/new_kv/cache share `dtype`.  Split-KV over 64..256-token chunks;
+ * `workspace` (acai_decode_workspace_bytes) holds one int32 arrival counter per (sequence, head) followed by the chunk
+ * partials.  bf16 caches: the last warp of a (sequence, head) to publish its partial folds them inside the same kernel;
+ * the counters must be ZERO before the first call with a given workspace (cudaMemset once) and every call leaves them
+ * zero.  fp32 caches: a separate combine launch. */
 size_t acai_decode_workspace_bytes(int32_t batch, int32_t heads, int32_t max_kv_len);
 int acai_decode_attn_paged(const void* q, int64_t q_stride, const void* new_kv, int64_t new_kv_stride,
                            void* kv_rows, int32_t dtype, const int32_t* page_table, int32_t table_stride,

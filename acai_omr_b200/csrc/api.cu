@@ -17,6 +17,11 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("ACAI_PDL"); return !(e && atoi(e) == 0); }();
+  return on;
+}
+
 int num_sms() {
   static int cached = 0;
   if (cached == 0) {

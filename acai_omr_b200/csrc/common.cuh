@@ -29,6 +29,26 @@ void set_error(const char* fmt, ...);
     }                                                                                   \
   } while (0)
 
+// ---- programmatic dependent launch (the decode step is ~150 kernels of a few microseconds each) -----------------------
+// A kernel launched through launch_pdl may be scheduled while its predecessor in the stream still runs; it must execute
+// pdl_wait() before it touches anything the predecessor writes (or writes anything the predecessor reads) - in this library
+// always before the first global-memory access and before any early return, so that "this grid has finished" implies "its
+// predecessors have finished".  pdl_launch_dependents() lets the NEXT kernel's CTAs be scheduled (they then sit in their
+// own pdl_wait).  Without the launch attribute both are no-ops.  ACAI_PDL=0 launches everything fully serialised.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 inline int launch_status(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {

@@ -88,6 +88,8 @@ __device__ __forceinline__ void token_update(bool valid, const float (&q)[64], f
 __global__ void __launch_bounds__(dt::WARPS * 32, 2)
 decode_attn_tma_kernel(const __grid_constant__ CUtensorMap tma_kv, DecodeTmaArgs a) {
   using namespace dt;
+  pdl_wait();
+  pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int chunk = blockIdx.x, h = blockIdx.y * WARPS + warp, b = blockIdx.z;
@@ -241,7 +243,7 @@ int decode_attn_tma(const void* q, int64_t q_stride, const void* new_kv, int64_t
                   step_ptr, len_offset, heads, scale * 1.4426950408889634f, ws, max_chunks, chunk_tokens, counters, out, out_dt, o_stride};
   const int chunks = (max_kv_len + chunk_tokens - 1) / chunk_tokens;
   dim3 grid(chunks, (heads + WARPS - 1) / WARPS, batch);
-  decode_attn_tma_kernel<<<grid, WARPS * 32, SMEM, st>>>(tm, a);
+  ACAI_CUDA(launch_pdl(decode_attn_tma_kernel, grid, dim3(WARPS * 32), SMEM, st, tm, a));
   return launch_status("decode_attn_tma");
 }
 

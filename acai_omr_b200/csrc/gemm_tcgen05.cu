@@ -283,6 +283,8 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                    // everything above (barriers, TMEM, tensor-map prefetch) may overlap the previous kernel's tail
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -448,6 +450,8 @@ __global__ void __launch_bounds__(64)
 splitk_reduce_kernel(const float* __restrict__ ws, int splitk, int M, int N, const float* __restrict__ bias, const void* res,
                      int res_dt, int64_t ldr, int act, const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                      void* out, int out_dt, int64_t ldo) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 2 + warp;
   if (row >= M) return;
@@ -636,7 +640,7 @@ static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_bf16_tcgen05<BN, OUT, RES, MODE><<<grid, THREADS, smem, st>>>(ta, tb, to, taux, ep, M, N, K);
+  ACAI_CUDA(launch_pdl(gemm_bf16_tcgen05<BN, OUT, RES, MODE>, dim3(grid), dim3(THREADS), smem, st, ta, tb, to, taux, ep, M, N, K));
   return launch_status("gemm_bf16_tcgen05");
 }
 
@@ -783,13 +787,13 @@ int linear_splitk_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw
     }
     const int tiles = ((M + BM - 1) / BM) * ((N + 63) / 64) * ep.splitk;
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    gemm_bf16_tcgen05<64, 0, 0, 0><<<grid, THREADS, smem, st>>>(ta, tb, ta, ta, ep, M, N, K);
+    ACAI_CUDA(launch_pdl(gemm_bf16_tcgen05<64, 0, 0, 0>, dim3(grid), dim3(THREADS), smem, st, ta, tb, ta, ta, ep, M, N, K));
     rc = launch_status("gemm_bf16_tcgen05 (split-K)");
     if (rc) return rc;
   }
   const dim3 grid((M + 1) / 2);
-#define ACAI_RED(V) splitk_reduce_kernel<V><<<grid, 64, 0, st>>>(static_cast<const float*>(ws), ep.splitk, M, N, bias, res, res_dt, ldr, \
-                                                                act, gamma, beta, eps, out, out_dt, ldo)
+#define ACAI_RED(V) ACAI_CUDA(launch_pdl(splitk_reduce_kernel<V>, grid, dim3(64), 0, st, static_cast<const float*>(ws), ep.splitk, M, N, \
+                                        bias, res, res_dt, ldr, act, gamma, beta, eps, out, out_dt, ldo))
   switch (vpl) {
     case 0: ACAI_RED(0); break;
     case 1: ACAI_RED(1); break;

@@ -185,38 +185,48 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
       ptx::tc_fence_before();
       ptx::mbar_arrive(dp_free);
       const int kbase = j * SMALL + half * 32;
+      // the fp32 arithmetic runs on packed pairs (FFMA2 / FADD2 / FMUL2: the same fma.rn / add.rn / mul.rn per element in half
+      // the issue slots - the elementwise warps of this kernel are issue bound)
+      const uint64_t sl2x = ptx::pack_f32x2(sl2, sl2), nLx = ptx::pack_f32x2(-L, -L), ndlx = ptx::pack_f32x2(-dl, -dl);
+      auto exp_pair = [&](int i, float& p0, float& p1) {
+        float x0, x1;
+        ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sl2x, nLx), x0, x1);
+        p0 = fast_exp2(x0); p1 = fast_exp2(x1);
+      };
+      auto ds_pair = [&](float p0, float p1, uint64_t t2) -> uint32_t {   // bf16 pair of P . (t - delta)
+        float d0, d1;
+        ptx::unpack_f32x2(ptx::mul_f32x2(ptx::pack_f32x2(p0, p1), ptx::add_f32x2(t2, ndlx)), d0, d1);
+        const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
+        return *reinterpret_cast<const uint32_t*>(&hh);
+      };
       if (DROP) {                                  // dS = P . (M dP / (1 - p) - delta), M = the forward's keep mask
+        const uint64_t rpx = ptx::pack_f32x2(rp, rp);
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
-          float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -L));
+          float p0, p1;
+          exp_pair(i, p0, p1);
           if (kbase + 2 * i >= my_end) p0 = 0.0f;
           if (kbase + 2 * i + 1 >= my_end) p1 = 0.0f;
           const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (SMALL / 2) + half * 16 + i));
-          const float t0 = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) * rp : 0.0f;
-          const float t1 = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) * rp : 0.0f;
-          const __nv_bfloat162 hh = __floats2bfloat162_rn(p0 * (t0 - dl), p1 * (t1 - dl));
-          pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+          const float k0 = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) : 0.0f;
+          const float k1 = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) : 0.0f;
+          pk[i] = ds_pair(p0, p1, ptx::mul_f32x2(ptx::pack_f32x2(k0, k1), rpx));
         }
       } else if (kbase + 32 <= my_end) {           // whole half visible (the common case): no masking instructions
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -L));
-          const __nv_bfloat162 hh = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[2 * i]) - dl),
-                                                          p1 * (__uint_as_float(dp[2 * i + 1]) - dl));
-          pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+          float p0, p1;
+          exp_pair(i, p0, p1);
+          pk[i] = ds_pair(p0, p1, ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1])));
         }
       } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          float p0 = fast_exp2(fmaf(__uint_as_float(s[2 * i]), sl2, -L));
-          float p1 = fast_exp2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -L));
+          float p0, p1;
+          exp_pair(i, p0, p1);
           if (kbase + 2 * i >= my_end) p0 = 0.0f;
           if (kbase + 2 * i + 1 >= my_end) p1 = 0.0f;
-          const __nv_bfloat162 hh = __floats2bfloat162_rn(p0 * (__uint_as_float(dp[2 * i]) - dl),
-                                                          p1 * (__uint_as_float(dp[2 * i + 1]) - dl));
-          pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+          pk[i] = ds_pair(p0, p1, ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1])));
         }
       }
       // dS (bf16, 16 columns) goes over the START of this warp's own S half, never over the half the sibling warp reads
@@ -413,16 +423,20 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       ptx::mbar_arrive(sp_free);                   // the MMA warp may overwrite S^T / dP^T with block it + 1
+      const uint64_t sl2x = ptx::pack_f32x2(sl2, sl2);
       const float4* vl = reinterpret_cast<const float4*>(vb + half * 32);
       const float4* vd = reinterpret_cast<const float4*>(vb + 64 + half * 32);
 #pragma unroll
       for (int i4 = 0; i4 < 8; ++i4) {
         const float4 l4 = vl[i4], d4 = vd[i4];
         const int c = half * 32 + 4 * i4;
-        float p0 = fast_exp2(fmaf(__uint_as_float(s[4 * i4]), sl2, -l4.x));
-        float p1 = fast_exp2(fmaf(__uint_as_float(s[4 * i4 + 1]), sl2, -l4.y));
-        float p2 = fast_exp2(fmaf(__uint_as_float(s[4 * i4 + 2]), sl2, -l4.z));
-        float p3 = fast_exp2(fmaf(__uint_as_float(s[4 * i4 + 3]), sl2, -l4.w));
+        // (packed fp32 pairs, see the dQ kernel)
+        float x0, x1, x2, x3;
+        ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[4 * i4]), __uint_as_float(s[4 * i4 + 1])), sl2x,
+                                         ptx::pack_f32x2(-l4.x, -l4.y)), x0, x1);
+        ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[4 * i4 + 2]), __uint_as_float(s[4 * i4 + 3])), sl2x,
+                                         ptx::pack_f32x2(-l4.z, -l4.w)), x2, x3);
+        float p0 = fast_exp2(x0), p1 = fast_exp2(x1), p2 = fast_exp2(x2), p3 = fast_exp2(x3);
         if (c < cmin) p0 = 0.0f;
         if (c + 1 < cmin) p1 = 0.0f;
         if (c + 2 < cmin) p2 = 0.0f;
@@ -438,11 +452,17 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
           m2 = ((mix32((rb.z + pair) ^ rc.z) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
           m3 = ((mix32((rb.w + pair) ^ rc.w) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
         }
-        const __nv_bfloat162 hp0 = __floats2bfloat162_rn(p0 * m0, p1 * m1), hp1 = __floats2bfloat162_rn(p2 * m2, p3 * m3);
-        const __nv_bfloat162 hd0 = __floats2bfloat162_rn(p0 * (m0 * __uint_as_float(dp[4 * i4]) - d4.x),
-                                                         p1 * (m1 * __uint_as_float(dp[4 * i4 + 1]) - d4.y));
-        const __nv_bfloat162 hd1 = __floats2bfloat162_rn(p2 * (m2 * __uint_as_float(dp[4 * i4 + 2]) - d4.z),
-                                                         p3 * (m3 * __uint_as_float(dp[4 * i4 + 3]) - d4.w));
+        const uint64_t pa = ptx::pack_f32x2(p0, p1), pb = ptx::pack_f32x2(p2, p3);
+        const uint64_t ma = ptx::pack_f32x2(m0, m1), mb = ptx::pack_f32x2(m2, m3);
+        float e0, e1, e2, e3, f0, f1, f2, f3;
+        ptx::unpack_f32x2(ptx::mul_f32x2(pa, ma), e0, e1);
+        ptx::unpack_f32x2(ptx::mul_f32x2(pb, mb), e2, e3);
+        ptx::unpack_f32x2(ptx::mul_f32x2(pa, ptx::fma_f32x2(ma, ptx::pack_f32x2(__uint_as_float(dp[4 * i4]), __uint_as_float(dp[4 * i4 + 1])),
+                                                           ptx::pack_f32x2(-d4.x, -d4.y))), f0, f1);
+        ptx::unpack_f32x2(ptx::mul_f32x2(pb, ptx::fma_f32x2(mb, ptx::pack_f32x2(__uint_as_float(dp[4 * i4 + 2]), __uint_as_float(dp[4 * i4 + 3])),
+                                                           ptx::pack_f32x2(-d4.z, -d4.w))), f2, f3);
+        const __nv_bfloat162 hp0 = __floats2bfloat162_rn(e0, e1), hp1 = __floats2bfloat162_rn(e2, e3);
+        const __nv_bfloat162 hd0 = __floats2bfloat162_rn(f0, f1), hd1 = __floats2bfloat162_rn(f2, f3);
         pk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hp0); pk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hp1);
         dk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hd0); dk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hd1);
       }

@@ -27,6 +27,14 @@ class ImageDesc(C.Structure):
                 ("hp", C.c_int32), ("wp", C.c_int32)]
 
 
+class ResizeDesc(C.Structure):
+    """acai_resize_desc"""
+    _fields_ = [("src", C.c_void_p), ("src_dtype", C.c_int32), ("src_h", C.c_int32), ("src_w", C.c_int32),
+                ("src_stride", C.c_int64), ("tmp", C.c_void_p), ("dst", C.c_void_p), ("dst_h", C.c_int32), ("dst_w", C.c_int32),
+                ("crop_top", C.c_int32), ("crop_left", C.c_int32), ("out_h", C.c_int32), ("out_w", C.c_int32),
+                ("dst_stride", C.c_int64)]
+
+
 _p, _i32, _i64, _f32, _sz, _u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t, C.c_uint64
 
 # name -> argtypes, in header order
@@ -59,6 +67,7 @@ SIGNATURES = {
     "acai_gumbel_softmax_fwd": [_p, _i32, _i64, _p, _i32, _i32, _f32, _i32, _p, _p, _i32, _p],
     "acai_gumbel_softmax_bwd": [_p, _i32, _p, _i32, _i32, _f32, _p, _i32, _p],
     "acai_mix_rows": [_p, _i32, _p, _p, _i32, _p, _i32, _i32, _i32, _p, _i32, _p],
+    "acai_dynamic_resize": [_p, _i32, _i32, _i32, _i32, _p],
     "acai_linear_splitk_workspace_bytes": [_i32, _i32, _i32],
     "acai_linear_splitk": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _p, _f32, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p, _sz, _p],
     "acai_linear_gelu_train": [_p, _i64, _p, _i64, _p, _p, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],

@@ -41,6 +41,29 @@ const char* acai_last_error(void);
 /* 1 if a CUDA device of compute capability 10.x is present and the kernels can launch. */
 int acai_device_ok(void);
 
+/* ---- input pipeline: DynamicResize --------------------------------------------------------------------------------
+ * Replaces v2.ToImage + v2.ToDtype(float32, scale=True) + DynamicResize (omr_teacher_force_train.py:278-282,
+ * pre_train.py:162-166, utils/utils.py:334-370) for a ragged batch of single-channel images: torchvision
+ * F.resize(BICUBIC, antialias=True) to (dst_h, dst_w) - torch's separable antialiased bicubic (a = -0.5, support
+ * 2 * max(in / out, 1), normalised weights; width first, then height) - the optional centre crop as an output window
+ * [crop_top, crop_top + out_h) x [crop_left, crop_left + out_w) of the resized image, and the final clamp to [0, 1].
+ * `src` is uint8 (scaled by 1/255 on load) or fp32; `tmp` holds src_h * out_w floats per image; `dst` is what
+ * acai_image_desc.pixels points at.  The host computes the target sizes (pure shape logic, DynamicResize.forward). */
+enum { ACAI_RESIZE_F32 = 0, ACAI_RESIZE_U8 = 1 };
+typedef struct {
+  const void* src;      /* (H, W) rows, uint8 or fp32                                   */
+  int32_t src_dtype;    /* ACAI_RESIZE_F32 / ACAI_RESIZE_U8                             */
+  int32_t src_h, src_w;
+  int64_t src_stride;   /* elements between source rows                                */
+  float* tmp;           /* [src_h, out_w] scratch of this image                        */
+  float* dst;           /* [out_h, out_w] fp32, row pitch dst_stride                   */
+  int32_t dst_h, dst_w; /* resize target (before the crop)                             */
+  int32_t crop_top, crop_left, out_h, out_w;
+  int64_t dst_stride;
+} acai_resize_desc;
+int acai_dynamic_resize(const acai_resize_desc* descs /* device array [num_images] */, int32_t num_images,
+                        int32_t max_src_h, int32_t max_out_h, int32_t max_out_w, void* stream);
+
 /* ---- K1: fused patchify + embed + 2-D position -----------------------------------------
  * Replaces Encoder.batchify / OMREncoder.batchify / MAEEncoder.batchify (models.py:36-66,
  * 304-332, 128-173): nn.Unfold im2col, nn.Linear(C*P*P -> E), + pos_embedding[:h_p,:w_p]

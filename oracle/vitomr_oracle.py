@@ -536,3 +536,67 @@ def entropy_bonus(theta_logits, rollout_attention_mask, vocab_size):
     ent = (-probs * torch.log_softmax(theta_logits, dim=-1)).sum(dim=-1).masked_fill(rollout_attention_mask, 0)
     ent = ent.sum(dim=-1) / (~rollout_attention_mask).sum(dim=-1)
     return ent.mean() / torch.log(torch.tensor(float(vocab_size)))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Input pipeline: v2.ToImage + v2.ToDtype(float32, scale=True) + DynamicResize (omr_teacher_force_train.py:278-282,
+# pre_train.py:162-166, utils/utils.py:334-370).  The arithmetic is torchvision F.resize(BICUBIC, antialias=True) =
+# torch's separable antialiased bicubic (third party: torch, aten/src/ATen/native/cpu/UpSampleKernel.cpp
+# `_compute_indices_min_size_weights_aa` + `HelperInterpCubic::aa_filter`), restated here as two explicit weight matrices.
+# Pinned by tests/golden/golden_resize.pt (outputs of the reference's own DynamicResize class).
+def dynamic_resize_target(height, width, patch_size, max_seq_len):
+    """utils/utils.py:346-354."""
+    if width > height:
+        aspect_ratio = width // height
+        target_height = patch_size * math.floor(math.sqrt(max_seq_len / aspect_ratio))
+        return target_height, target_height * aspect_ratio
+    aspect_ratio = height // width
+    target_width = patch_size * math.floor(math.sqrt(max_seq_len / aspect_ratio))
+    return target_width * aspect_ratio, target_width
+
+
+def _cubic_aa(x, a=-0.5):
+    x = abs(x)
+    if x < 1.0:
+        return ((a + 2.0) * x - (a + 3.0)) * x * x + 1.0
+    if x < 2.0:
+        return (((x - 5.0) * x + 8.0) * x - 4.0) * a
+    return 0.0
+
+
+def aa_bicubic_matrix(in_size, out_size):
+    """[out_size, in_size] fp32 matrix of normalised antialiased-bicubic weights (fp32 index arithmetic, as torch)."""
+    f32 = lambda v: torch.tensor(v, dtype=torch.float32).item()  # noqa: E731  (round every intermediate to fp32)
+    scale = f32(in_size / out_size)
+    support = f32(2.0 * scale) if scale >= 1.0 else 2.0
+    invscale = f32(1.0 / scale) if scale >= 1.0 else 1.0
+    m = torch.zeros(out_size, in_size, dtype=torch.float32)
+    for i in range(out_size):
+        center = f32(scale * (i + 0.5))
+        xmin = max(int(f32(center - support + 0.5)), 0)
+        xsize = min(int(f32(center + support + 0.5)), in_size) - xmin
+        w = [f32(_cubic_aa(f32(f32(j + xmin - center + 0.5) * invscale))) for j in range(xsize)]
+        total = f32(sum(w))
+        for j in range(xsize):
+            m[i, xmin + j] = w[j] / total
+    return m
+
+
+def dynamic_resize(img, patch_size, max_seq_len, pe_max_height, pe_max_width, crop_imgs):
+    """img: (1, H, W) uint8 or fp32 CPU tensor -> (1, h, w) fp32, utils/utils.py:343-370 statement by statement (the uint8
+    case first applies v2.ToDtype(float32, scale=True): x / 255)."""
+    x = img.to(torch.float32) / 255.0 if img.dtype == torch.uint8 else img.to(torch.float32)
+    height, width = x.shape[-2], x.shape[-1]
+    th, tw = dynamic_resize_target(height, width, patch_size, max_seq_len)
+    x = x @ aa_bicubic_matrix(width, tw).t()                 # width first (fp32 intermediate) ...
+    x = aa_bicubic_matrix(height, th) @ x                    # ... then height
+    if crop_imgs:
+        if th / patch_size > pe_max_height:
+            ch = pe_max_height * patch_size
+            top = int(round((th - ch) / 2.0))                # torchvision center_crop
+            x = x[..., top:top + ch, :]
+        if tw / patch_size > pe_max_width:
+            cw = pe_max_width * patch_size
+            left = int(round((tw - cw) / 2.0))
+            x = x[..., :, left:left + cw]
+    return x.clamp(0.0, 1.0)

@@ -2,9 +2,13 @@
 
 Golden entries were produced by the unmodified reference (tests/golden/make_golden.py).
 CPU only; this is the pin that lets the GPU tests trust the oracle."""
+import os
+
 import torch
 
 from oracle import vitomr_oracle as O
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 TOL = dict(atol=2e-5, rtol=1e-4)
 
@@ -213,3 +217,25 @@ def test_oracle_rollout_policy_matches_reference(golden_grpo):
                                                            top_k=c["top_k"], temperature=c["temperature"])
     assert torch.equal(rollouts, g["rollouts"]) and torch.equal(mask, g["rollout_mask"])
     assert torch.allclose(logp, g["log_probs"], atol=2e-5, rtol=1e-4)
+
+
+# ---- input pipeline: DynamicResize (utils/utils.py:334-370) ----------------------------------------------------------
+def test_oracle_dynamic_resize_matches_reference_golden():
+    """The explicit weight-matrix restatement of torch's antialiased bicubic against outputs of the reference's own
+    DynamicResize class (tests/golden/make_golden_resize.py): down / up-scaling, portrait, uint8 and fp32, centre crops."""
+    entries = torch.load(os.path.join(GOLDEN_DIR, "golden_resize.pt"))
+    assert len(entries) >= 9
+    for e in entries:
+        out = O.dynamic_resize(e["img"], *e["args"])
+        assert out.shape == e["out"].shape and out.dtype == torch.float32
+        assert float((out - e["out"]).abs().max()) <= 2e-6
+        assert float(out.min()) >= 0.0 and float(out.max()) <= 1.0
+
+
+def test_oracle_dynamic_resize_target_sizes():
+    """DynamicResize(16, N, 60, 200) shapes of SURVEY section 8(d): N = 1024 and N = 512 mixes."""
+    for (h, w), want in {(512, 512): (512, 512), (300, 650): (352, 704), (100, 310): (288, 864), (90, 400): (256, 1024),
+                         (80, 640): (176, 1408)}.items():
+        assert O.dynamic_resize_target(h, w, 16, 1024) == want
+    assert O.dynamic_resize_target(700, 300, 16, 512) == (512, 256)        # portrait: aspect = height // width
+    assert O.dynamic_resize_target(100, 420, 16, 512) == (176, 704)

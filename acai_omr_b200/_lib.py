@@ -67,7 +67,7 @@ SIGNATURES = {
     "acai_gumbel_softmax_fwd": [_p, _i32, _i64, _p, _i32, _i32, _f32, _i32, _p, _p, _i32, _p],
     "acai_gumbel_softmax_bwd": [_p, _i32, _p, _i32, _i32, _f32, _p, _i32, _p],
     "acai_mix_rows": [_p, _i32, _p, _p, _i32, _p, _i32, _i32, _i32, _p, _i32, _p],
-    "acai_dynamic_resize": [_p, _i32, _i32, _i32, _i32, _p],
+    "acai_dynamic_resize": [_p, _i32, _i32, _i32, _i32, _i32, _p],
     "acai_linear_splitk_workspace_bytes": [_i32, _i32, _i32],
     "acai_linear_splitk": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _p, _f32, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p, _sz, _p],
     "acai_linear_gelu_train": [_p, _i64, _p, _i64, _p, _p, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],

@@ -9,6 +9,7 @@ and stay in Python, exactly as the reference computes them; the arithmetic is th
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 from torch import nn
@@ -52,9 +53,8 @@ def resize_batch(images, patch_size, max_seq_len, pe_max_height, pe_max_width, c
     dev = images[0].device
     if dev.type != "cuda":
         raise AcaiError("resize_batch: images must be CUDA tensors (there is no CPU fallback)")
-    arr = (ResizeDesc * len(images))()
-    outs, keep, tmp_off, tmp_total = [], [], [], 0
-    plans = []
+    plans, keep = [], []
+    tmp_total = out_total = 0
     for t in images:
         if t.dim() == 3:
             if t.shape[0] != 1:
@@ -71,20 +71,27 @@ def resize_batch(images, patch_size, max_seq_len, pe_max_height, pe_max_width, c
         if th <= 0 or tw <= 0:
             raise ValueError(f"image of {H} x {W} pixels has no valid target size for max_seq_len {max_seq_len}")
         top, left, oh, ow = crop_window(th, tw, patch_size, pe_max_height, pe_max_width, crop_imgs)
-        plans.append((t, H, W, th, tw, top, left, oh, ow))
-        tmp_off.append(tmp_total)
+        plans.append((t.data_ptr(), RESIZE_U8 if t.dtype == torch.uint8 else RESIZE_F32, H, W, t.stride(0), tmp_total, out_total,
+                      th, tw, top, left, oh, ow))
         tmp_total += H * ow
+        out_total += (oh * ow + 3) & ~3                      # every image starts on a 16-byte boundary
         keep.append(t)
+    # ONE scratch and ONE output allocation for the whole batch (the returned images are views), one descriptor upload
     tmp = torch.empty(max(tmp_total, 1), dtype=torch.float32, device=dev)
-    for i, (t, H, W, th, tw, top, left, oh, ow) in enumerate(plans):
-        out = torch.empty((1, oh, ow), dtype=torch.float32, device=dev)
-        outs.append(out)
-        arr[i] = ResizeDesc(t.data_ptr(), RESIZE_U8 if t.dtype == torch.uint8 else RESIZE_F32, H, W, t.stride(0),
-                            tmp.data_ptr() + 4 * tmp_off[i], out.data_ptr(), th, tw, top, left, oh, ow, ow)
+    flat = torch.empty(out_total, dtype=torch.float32, device=dev)
+    tmp_base, out_base = tmp.data_ptr(), flat.data_ptr()
+    arr = (ResizeDesc * len(images))()
+    outs = []
+    for i, (src, sdt, H, W, stride, toff, ooff, th, tw, top, left, oh, ow) in enumerate(plans):
+        arr[i] = ResizeDesc(src, sdt, H, W, stride, tmp_base + 4 * toff, out_base + 4 * ooff, th, tw, top, left, oh, ow, ow)
+        outs.append(flat[ooff:ooff + oh * ow].view(1, oh, ow))
     host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
     descs = ops.upload_small(host, dev)
+    # widest filter window of the batch (either axis): support = 2 * max(in / out, 1) on each side of the centre
+    taps = max(2 * math.ceil(2.0 * max(p[2] / p[7], p[3] / p[8], 1.0)) + 2 for p in plans)
+    use_table = os.environ.get("ACAI_RESIZE_TABLE", "1") != "0"
     ops._call("acai_dynamic_resize", _lib.load().acai_dynamic_resize, ops._p(descs), len(images),
-              max(p[1] for p in plans), max(p[7] for p in plans), max(p[8] for p in plans), ops._stream())
+              max(p[2] for p in plans), max(p[11] for p in plans), max(p[12] for p in plans), taps if use_table else 0, ops._stream())
     ops._bump()                       # two kernels: rows pass, columns pass
     return outs
 

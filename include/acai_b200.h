@@ -61,8 +61,10 @@ typedef struct {
   int32_t crop_top, crop_left, out_h, out_w;
   int64_t dst_stride;
 } acai_resize_desc;
+/* max_taps: an upper bound of the filter window (taps) over the batch and both axes, e.g. 2 * ceil(2 * max(in / out, 1)) + 2:
+ * the weights of a strip of outputs are then tabulated once per CTA in shared memory; 0 = per-thread weights (any window). */
 int acai_dynamic_resize(const acai_resize_desc* descs /* device array [num_images] */, int32_t num_images,
-                        int32_t max_src_h, int32_t max_out_h, int32_t max_out_w, void* stream);
+                        int32_t max_src_h, int32_t max_out_h, int32_t max_out_w, int32_t max_taps, void* stream);
 
 /* ---- K1: fused patchify + embed + 2-D position -----------------------------------------
  * Replaces Encoder.batchify / OMREncoder.batchify / MAEEncoder.batchify (models.py:36-66,

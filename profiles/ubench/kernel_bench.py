@@ -70,6 +70,22 @@ def bench_colsum(rows, cols):
     print(f"colsum bf16 {rows}x{cols}: {us:8.1f} us  {2.0 * rows * cols / us / 1e3:7.1f} GB/s")
 
 
+def bench_resize(n=64):
+    """64 uint8 scans at ~1.7x the DynamicResize(16, 1024, 60, 200) target of their aspect ratio -> fp32 encoder inputs."""
+    from acai_omr_b200 import synth, transforms
+    g = torch.Generator().manual_seed(2)
+    scans = []
+    for h, w in synth.system_shapes(n):
+        H, W = int(h * 1.7) + 3, int(w * 1.7) + 5
+        scans.append(torch.randint(0, 256, (1, H, W), generator=g, dtype=torch.uint8).to(DEV))
+    mod = transforms.DynamicResize(16, 1024, 60, 200, False)
+    outs = mod.forward_batch(scans)
+    nbytes = sum(s_.numel() for s_ in scans) + 4 * sum(o.numel() for o in outs)
+    us = timed(lambda: mod.forward_batch(scans))
+    print(f"dynamic resize, {n} uint8 scans ({sum(s_.numel() for s_ in scans) / 1e6:.1f} MB) -> fp32 ({sum(o.numel() for o in outs) * 4 / 1e6:.1f} MB): "
+          f"{us:8.1f} us  {n / us * 1e6:9.0f} systems/s  {nbytes / us / 1e3:7.1f} GB/s (src + dst)")
+
+
 if __name__ == "__main__":
     what = sys.argv[1:] or ["attn", "ln", "colsum"]
     print("ACAI_ATTN_POLY =", os.environ.get("ACAI_ATTN_POLY", "(default)"), " ACAI_ATTN_CTAS =", os.environ.get("ACAI_ATTN_CTAS", "(default)"))
@@ -81,6 +97,8 @@ if __name__ == "__main__":
     if "ln" in what:
         bench_ln(63664, 768)
         bench_ln(41976, 1024)
+    if "resize" in what:
+        bench_resize()
     if "colsum" in what:
         bench_colsum(63664, 768)
         bench_colsum(63664, 3072)

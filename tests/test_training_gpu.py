@@ -395,6 +395,40 @@ def test_trainer_steps_reduce_the_loss_and_refresh_weight_copies():
     layers.WEIGHTS.clear()
 
 
+def test_trainer_checkpoint_resume():
+    """the run is resumable - model state_dict (reference key names) + FlatTrainer.state_dict (AdamW moments,
+    step, per-group learning rates) restored into fresh objects continue exactly like the uninterrupted run (up to the fp32
+    reduce-add order of the split-K weight gradients)."""
+    from acai_omr_b200 import layers, synth, train
+
+    def make():
+        enc = M.FineTuneOMREncoder(16, 12, 40, 1, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.0)
+        dec = M.OMRDecoder(48, VOCAB, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.0)
+        vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=128, transition_head_dropout=0.0)
+        synth.rerandomise_(vit, 6)
+        vit = vit.to(DEV).train()
+        groups, _ = vit.create_fine_tune_param_groups(2e-3, 1e-3, 0.9)
+        return vit, train.FlatTrainer(vit, groups)
+
+    imgs = [synth.synth_system(h, w, i).to(DEV) for i, (h, w) in enumerate([(64, 160), (32, 320)])]
+    batch = list(zip(imgs, [synth.synth_lmx(L, i).to(DEV) for i, L in enumerate([20, 33])]))
+    loss = lambda sums: float(sums[0] / sums[1])  # noqa: E731
+    vit, tr = make()
+    for _ in range(2):
+        train.teacher_forced_step(vit, batch, tr)
+    ckpt = {"model": {k: v.detach().clone() for k, v in vit.state_dict().items()}, "trainer": tr.state_dict()}
+    cont = [loss(train.teacher_forced_step(vit, batch, tr)) for _ in range(3)]
+    layers.WEIGHTS.clear()
+    vit2, tr2 = make()
+    vit2.load_state_dict(ckpt["model"])
+    tr2.load_state_dict(ckpt["trainer"])
+    assert tr2.step_count == 2
+    resumed = [loss(train.teacher_forced_step(vit2, batch, tr2)) for _ in range(3)]
+    assert torch.allclose(torch.tensor(resumed), torch.tensor(cont), rtol=2e-3, atol=2e-3), (cont, resumed)
+    assert resumed[-1] < resumed[0]
+    layers.WEIGHTS.clear()
+
+
 @pytest.mark.parametrize("T,n_out,k_in", [(1000, 768, 768), (63, 128, 256), (5000, 3072, 768), (777, 200, 136), (4096, 64, 64),
                                           (20000, 1024, 4096), (130, 8, 1024)])
 def test_wgrad_accumulate_tensor_core(T, n_out, k_in):

@@ -444,7 +444,8 @@ def run_train(args, rank, world, device, kind):
                         "trainable_parameters": numel, "l2": "flushed between steps",
                         "collective": "one NCCL all-reduce of the flat fp32 gradient buffer per step" if world > 1 else "none (1 GPU)"},
                        **work),
-        "loss_last_step": loss, "gpu_launches_per_step": launches, "host_enqueue_ms_per_step": round(host_s / k * 1e3, 2),
+        "loss_last_step": loss, "gpu_launches_per_step": launches, "host_ms_in_step_call": round(host_s / k * 1e3, 2),   # includes blocking on the full launch queue: the host alone
+        # needs ~32 ms to enqueue such a step (profiles/ubench/train_host_time.py), the step is GPU bound
         "peak_mem_gib": round(peak_mem, 1),
         "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05 + gemm_wgrad_tcgen05", "achieved": g_fl / (g_ms * 1e-3) / 1e12,
                      "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",

@@ -603,6 +603,9 @@ class TeacherForcedViTOMR(ViTOMR):
         """models.py:722-736: list[(img, lmx_seq)] -> (pred (B,T,V), target_seqs (B,T))."""
         imgs, lmx_seqs = zip(*x)
         img_latent, latent_attention_mask = self.encoder(imgs)
+        hook = getattr(self, "_acai_latent_hook", None)       # train.teacher_forced_step: gradient all-reduce overlap
+        if hook is not None:
+            hook(img_latent)
         img_latent = self.transition_head(img_latent)
         input_seqs, target_seqs, lmx_attention_mask = batchify_and_split_lmx_seqs(lmx_seqs, self.decoder.pad_idx,
                                                                                   img_latent.device)

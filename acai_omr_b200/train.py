@@ -17,6 +17,8 @@ from __future__ import annotations
 
 import ctypes as C
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -43,6 +45,18 @@ def shard(items, rank, world, cost=None):
         if r == rank:
             mine.append(i)
     return [items[i] for i in sorted(mine)]
+
+
+def _complement(ranges, total):
+    """The parts of [0, total) not covered by `ranges` (a list of (start, end))."""
+    out, pos = [], 0
+    for a, b in sorted(ranges):
+        if a > pos:
+            out.append((pos, a))
+        pos = max(pos, b)
+    if pos < total:
+        out.append((pos, total))
+    return out
 
 
 def _world(group):
@@ -88,6 +102,7 @@ class FlatTrainer:
                 p.data = view
                 p.grad = self.flat_grad[o:o + p.numel()].view(p.shape)
                 p._acai_grad_owned = True      # backward GEMMs accumulate into .grad directly (functional._owned_grad)
+        self._works, self._reduced = [], []      # gradient all-reduces in flight / flat ranges they cover (this step)
         self.shadow = None
         if shadow_dtype is not None:
             self.shadow = self.flat_param.to(shadow_dtype)
@@ -112,9 +127,43 @@ class FlatTrainer:
         return c
 
     def allreduce_gradients(self):
-        """Sum the flat gradient buffer over ranks (one collective); the 1/world is folded into the AdamW kernel."""
+        """Sum the flat gradient buffer over ranks; the 1/world is folded into the AdamW kernel.  Whatever
+        `allreduce_ready` has not already put in flight goes out now (one collective per remaining contiguous range);
+        then the step waits for all of them."""
         if _world(self.group) > 1:
-            dist.all_reduce(self.flat_grad, group=self.group)
+            for a, b in _complement(self._reduced, self.numel):
+                self._works.append(dist.all_reduce(self.flat_grad[a:b], group=self.group, async_op=True))
+            for w in self._works:
+                w.wait()
+        self._works, self._reduced = [], []
+
+    def allreduce_ready(self, params):
+        """Overlap: the gradients of `params` are final (their part of the backward has run) - start their all-reduce now,
+        asynchronously, while the rest of the backward keeps the SMs busy.  Called from a tensor hook at a point of the
+        backward that dominates those parameters (`grad_ready_hook`).  The flat layout makes this one collective per
+        contiguous run of parameters (the decoder + transition head of ViTOMR are one run: 2/3 of the 1.22 GB)."""
+        if _world(self.group) <= 1:
+            return
+        want = {id(p) for p in params}
+        runs = []
+        for p, o in zip(self.params, self.offsets):
+            if id(p) in want:
+                end = o + (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+                if runs and runs[-1][1] == o:
+                    runs[-1][1] = end
+                else:
+                    runs.append([o, end])
+        for a, b in runs:
+            if any(a < rb and ra < b for ra, rb in self._reduced):
+                raise RuntimeError("FlatTrainer.allreduce_ready: range reduced twice in one step")
+            self._reduced.append((a, b))
+            self._works.append(dist.all_reduce(self.flat_grad[a:b], group=self.group, async_op=True))
+
+    def grad_ready_hook(self, tensor, modules):
+        """Register `allreduce_ready(parameters of modules)` to run when the gradient w.r.t. `tensor` has been computed."""
+        if _world(self.group) > 1 and tensor.requires_grad and os.environ.get("ACAI_DP_OVERLAP", "1") != "0":
+            params = [p for m in modules for p in m.parameters() if p.requires_grad]
+            tensor.register_hook(lambda g: (self.allreduce_ready(params), None)[1])
 
     def step(self):
         if self.flat_param.device.type != "cuda":
@@ -153,11 +202,17 @@ def teacher_forced_step(vit, batch, trainer: FlatTrainer, autocast=True):
     """One data-parallel step of omr_teacher_force_train.py:113-127 on this rank's shard (no gradient accumulation):
     returns the device tensor [sum of token losses, token count] of the shard."""
     trainer.zero_grad()
-    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
-        pred, tgt = vit(batch)
-        tgt = tgt.to(pred.device)
-        norm = trainer.mean_count((tgt != vit.decoder.pad_idx).sum())
-        loss, sums = F.ce_loss(pred, tgt, vit.decoder.pad_idx, normaliser=norm)
+    # data parallel: once the backward reaches the encoder's output, the decoder's and the transition head's gradients are
+    # final - their all-reduce (2/3 of the buffer) runs under the encoder's backward
+    vit._acai_latent_hook = lambda lat: trainer.grad_ready_hook(lat, [vit.decoder, vit.transition_head])
+    try:
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            pred, tgt = vit(batch)
+            tgt = tgt.to(pred.device)
+            norm = trainer.mean_count((tgt != vit.decoder.pad_idx).sum())
+            loss, sums = F.ce_loss(pred, tgt, vit.decoder.pad_idx, normaliser=norm)
+    finally:
+        vit._acai_latent_hook = None
     loss.backward()
     trainer.allreduce_gradients()
     trainer.step()

@@ -44,6 +44,23 @@ def _worker(rank, world, port, out):
         gathered = [torch.zeros_like(local) for _ in range(world)]
         dist.all_gather(gathered, local)
         ok &= torch.allclose(tr.flat_grad, sum(gathered))
+        # overlapped variant: the last layer's gradients are reduced from a tensor hook while the backward still runs, the rest
+        # at the end - same sums, every element reduced exactly once
+        tr.zero_grad()
+        h = m[1](m[0](x))
+        tr.grad_ready_hook(h, [m[2]])                                                            # fires once d loss / d h exists
+        m[2](h).sum().backward()
+        local2 = local.clone()
+        ok &= tr._reduced == [(next(o for p, o in zip(tr.params, tr.offsets) if p is m[2].weight), tr.numel)] and len(tr._works) == 1
+        tr.allreduce_gradients()
+        ok &= tr._works == [] and tr._reduced == []
+        ok &= torch.allclose(tr.flat_grad, sum(gathered))
+        ok &= torch.equal(local2, local)
+        try:
+            tr.allreduce_ready(m[2].parameters()); tr.allreduce_ready(m[2].parameters())
+            ok = False                                                                           # a range must not be reduced twice
+        except RuntimeError:
+            tr.allreduce_gradients()
         norm = tr.mean_count(torch.tensor(10 * (rank + 1)))
         ok &= float(norm) == sum(10 * (r + 1) for r in range(world)) / world
         try:
@@ -61,6 +78,13 @@ def test_two_rank_gloo_flat_allreduce():
     out = mp.get_context("spawn").Manager().dict()
     mp.spawn(_worker, args=(world, port, out), nprocs=world, join=True)
     assert dict(out) == {0: True, 1: True}
+
+
+def test_complement_of_reduced_ranges():
+    assert train._complement([], 10) == [(0, 10)]
+    assert train._complement([(4, 10)], 10) == [(0, 4)]
+    assert train._complement([(6, 8), (0, 2)], 10) == [(2, 6), (8, 10)]
+    assert train._complement([(0, 10)], 10) == []
 
 
 def test_shard_partitions_the_batch():

@@ -15,6 +15,8 @@
 //       dV += P^T dO_i , dK += dS^T Q_i        TS, B = dO_i / Q_i MN-major
 // Seven GEMMs instead of the five of a fused single pass, but no atomics and no cross-CTA reduction: every output
 // element has exactly one writer and a fixed summation order (bitwise reproducible gradients).
+#include <type_traits>
+
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
@@ -199,36 +201,33 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
         const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
         return *reinterpret_cast<const uint32_t*>(&hh);
       };
-      if (DROP) {                                  // dS = P . (M dP / (1 - p) - delta), M = the forward's keep mask
+      // Columns [vis, 32) of this thread's half are masked (causal diagonal, rows / keys past the sequence end).  A warp whose
+      // 32 rows all see the whole half - every block but the diagonal and the last one - runs the variant without the
+      // compare / select instructions.  With dropout: dS = P . (M dP / (1 - p) - delta), M = the forward's keep mask.
+      const int vis = my_end - kbase;
+      auto block_math = [&](auto masked_tag) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
         const uint64_t rpx = ptx::pack_f32x2(rp, rp);
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float p0, p1;
           exp_pair(i, p0, p1);
-          if (kbase + 2 * i >= my_end) p0 = 0.0f;
-          if (kbase + 2 * i + 1 >= my_end) p1 = 0.0f;
-          const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (SMALL / 2) + half * 16 + i));
-          const float k0 = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) : 0.0f;
-          const float k1 = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) : 0.0f;
-          pk[i] = ds_pair(p0, p1, ptx::mul_f32x2(ptx::pack_f32x2(k0, k1), rpx));
+          if (MASKED) {
+            if (2 * i >= vis) p0 = 0.0f;
+            if (2 * i + 1 >= vis) p1 = 0.0f;
+          }
+          if (DROP) {
+            const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (SMALL / 2) + half * 16 + i));
+            const float k0 = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) : 0.0f;
+            const float k1 = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) : 0.0f;
+            pk[i] = ds_pair(p0, p1, ptx::mul_f32x2(ptx::pack_f32x2(k0, k1), rpx));
+          } else {
+            pk[i] = ds_pair(p0, p1, ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1])));
+          }
         }
-      } else if (kbase + 32 <= my_end) {           // whole half visible (the common case): no masking instructions
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float p0, p1;
-          exp_pair(i, p0, p1);
-          pk[i] = ds_pair(p0, p1, ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1])));
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float p0, p1;
-          exp_pair(i, p0, p1);
-          if (kbase + 2 * i >= my_end) p0 = 0.0f;
-          if (kbase + 2 * i + 1 >= my_end) p1 = 0.0f;
-          pk[i] = ds_pair(p0, p1, ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1])));
-        }
-      }
+      };
+      if (__all_sync(0xffffffffu, vis >= 32)) block_math(std::false_type{});
+      else block_math(std::true_type{});
       // dS (bf16, 16 columns) goes over the START of this warp's own S half, never over the half the sibling warp reads
       ptx::tmem_st_32x16(tmem_s, pk);
       ptx::tmem_st_wait();
@@ -426,46 +425,60 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
       const uint64_t sl2x = ptx::pack_f32x2(sl2, sl2);
       const float4* vl = reinterpret_cast<const float4*>(vb + half * 32);
       const float4* vd = reinterpret_cast<const float4*>(vb + 64 + half * 32);
+      // Columns [0, cm) of this thread's 32 are masked.  Only the diagonal blocks of a causal problem and the last key tile
+      // of a sequence mask anything: every other warp takes the variant without the 64 compare / select instructions
+      // (the elementwise warps are issue bound, their time follows the instruction count).
+      const int cm = cmin - half * 32;
+      auto block_math = [&](auto masked_tag) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
 #pragma unroll
-      for (int i4 = 0; i4 < 8; ++i4) {
-        const float4 l4 = vl[i4], d4 = vd[i4];
-        const int c = half * 32 + 4 * i4;
-        // (packed fp32 pairs, see the dQ kernel)
-        float x0, x1, x2, x3;
-        ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[4 * i4]), __uint_as_float(s[4 * i4 + 1])), sl2x,
-                                         ptx::pack_f32x2(-l4.x, -l4.y)), x0, x1);
-        ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[4 * i4 + 2]), __uint_as_float(s[4 * i4 + 3])), sl2x,
-                                         ptx::pack_f32x2(-l4.z, -l4.w)), x2, x3);
-        float p0 = fast_exp2(x0), p1 = fast_exp2(x1), p2 = fast_exp2(x2), p3 = fast_exp2(x3);
-        if (c < cmin) p0 = 0.0f;
-        if (c + 1 < cmin) p1 = 0.0f;
-        if (c + 2 < cmin) p2 = 0.0f;
-        if (c + 3 < cmin) p3 = 0.0f;
-        float m0 = 1.0f, m1 = 1.0f, m2 = 1.0f, m3 = 1.0f;         // M / (1 - p) of (query column, this key)
-        if (DROP) {
-          const uint4 rc = reinterpret_cast<const uint4*>(vb + 128 + half * 32)[i4];
-          const uint4 rb = reinterpret_cast<const uint4*>(vb + 192 + half * 32)[i4];
-          const uint32_t pair = (uint32_t)kr >> 1, sh = (kr & 1) * 16, thr = p.drop.thr;
-          const float rp = p.drop.rp;
-          m0 = ((mix32((rb.x + pair) ^ rc.x) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-          m1 = ((mix32((rb.y + pair) ^ rc.y) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-          m2 = ((mix32((rb.z + pair) ^ rc.z) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-          m3 = ((mix32((rb.w + pair) ^ rc.w) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 l4 = vl[i4], d4 = vd[i4];
+          // (packed fp32 pairs, see the dQ kernel)
+          float x0, x1, x2, x3;
+          ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[4 * i4]), __uint_as_float(s[4 * i4 + 1])), sl2x,
+                                           ptx::pack_f32x2(-l4.x, -l4.y)), x0, x1);
+          ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[4 * i4 + 2]), __uint_as_float(s[4 * i4 + 3])), sl2x,
+                                           ptx::pack_f32x2(-l4.z, -l4.w)), x2, x3);
+          float p0 = fast_exp2(x0), p1 = fast_exp2(x1), p2 = fast_exp2(x2), p3 = fast_exp2(x3);
+          if (MASKED) {
+            if (4 * i4 < cm) p0 = 0.0f;
+            if (4 * i4 + 1 < cm) p1 = 0.0f;
+            if (4 * i4 + 2 < cm) p2 = 0.0f;
+            if (4 * i4 + 3 < cm) p3 = 0.0f;
+          }
+          const uint64_t pa = ptx::pack_f32x2(p0, p1), pb = ptx::pack_f32x2(p2, p3);
+          const uint64_t dpa = ptx::pack_f32x2(__uint_as_float(dp[4 * i4]), __uint_as_float(dp[4 * i4 + 1]));
+          const uint64_t dpb = ptx::pack_f32x2(__uint_as_float(dp[4 * i4 + 2]), __uint_as_float(dp[4 * i4 + 3]));
+          const uint64_t nda = ptx::pack_f32x2(-d4.x, -d4.y), ndb = ptx::pack_f32x2(-d4.z, -d4.w);
+          float e0, e1, e2, e3, f0, f1, f2, f3;
+          if (DROP) {                                                 // M / (1 - p) of (query column, this key)
+            const uint4 rc = reinterpret_cast<const uint4*>(vb + 128 + half * 32)[i4];
+            const uint4 rb = reinterpret_cast<const uint4*>(vb + 192 + half * 32)[i4];
+            const uint32_t pair = (uint32_t)kr >> 1, sh = (kr & 1) * 16, thr = p.drop.thr;
+            const float rp = p.drop.rp;
+            const float m0 = ((attn_drop_mix((rb.x + pair) ^ rc.x) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+            const float m1 = ((attn_drop_mix((rb.y + pair) ^ rc.y) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+            const float m2 = ((attn_drop_mix((rb.z + pair) ^ rc.z) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+            const float m3 = ((attn_drop_mix((rb.w + pair) ^ rc.w) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+            const uint64_t ma = ptx::pack_f32x2(m0, m1), mb = ptx::pack_f32x2(m2, m3);
+            ptx::unpack_f32x2(ptx::mul_f32x2(pa, ma), e0, e1);
+            ptx::unpack_f32x2(ptx::mul_f32x2(pb, mb), e2, e3);
+            ptx::unpack_f32x2(ptx::mul_f32x2(pa, ptx::fma_f32x2(ma, dpa, nda)), f0, f1);
+            ptx::unpack_f32x2(ptx::mul_f32x2(pb, ptx::fma_f32x2(mb, dpb, ndb)), f2, f3);
+          } else {                                                    // P^T as it is, dS^T = P^T (dP^T - delta)
+            e0 = p0; e1 = p1; e2 = p2; e3 = p3;
+            ptx::unpack_f32x2(ptx::mul_f32x2(pa, ptx::add_f32x2(dpa, nda)), f0, f1);
+            ptx::unpack_f32x2(ptx::mul_f32x2(pb, ptx::add_f32x2(dpb, ndb)), f2, f3);
+          }
+          const __nv_bfloat162 hp0 = __floats2bfloat162_rn(e0, e1), hp1 = __floats2bfloat162_rn(e2, e3);
+          const __nv_bfloat162 hd0 = __floats2bfloat162_rn(f0, f1), hd1 = __floats2bfloat162_rn(f2, f3);
+          pk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hp0); pk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hp1);
+          dk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hd0); dk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hd1);
         }
-        const uint64_t pa = ptx::pack_f32x2(p0, p1), pb = ptx::pack_f32x2(p2, p3);
-        const uint64_t ma = ptx::pack_f32x2(m0, m1), mb = ptx::pack_f32x2(m2, m3);
-        float e0, e1, e2, e3, f0, f1, f2, f3;
-        ptx::unpack_f32x2(ptx::mul_f32x2(pa, ma), e0, e1);
-        ptx::unpack_f32x2(ptx::mul_f32x2(pb, mb), e2, e3);
-        ptx::unpack_f32x2(ptx::mul_f32x2(pa, ptx::fma_f32x2(ma, ptx::pack_f32x2(__uint_as_float(dp[4 * i4]), __uint_as_float(dp[4 * i4 + 1])),
-                                                           ptx::pack_f32x2(-d4.x, -d4.y))), f0, f1);
-        ptx::unpack_f32x2(ptx::mul_f32x2(pb, ptx::fma_f32x2(mb, ptx::pack_f32x2(__uint_as_float(dp[4 * i4 + 2]), __uint_as_float(dp[4 * i4 + 3])),
-                                                           ptx::pack_f32x2(-d4.z, -d4.w))), f2, f3);
-        const __nv_bfloat162 hp0 = __floats2bfloat162_rn(e0, e1), hp1 = __floats2bfloat162_rn(e2, e3);
-        const __nv_bfloat162 hd0 = __floats2bfloat162_rn(f0, f1), hd1 = __floats2bfloat162_rn(f2, f3);
-        pk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hp0); pk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hp1);
-        dk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hd0); dk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hd1);
-      }
+      };
+      if (__any_sync(0xffffffffu, cm > 0)) block_math(std::true_type{});
+      else block_math(std::false_type{});
       // P^T / dS^T rows (this thread: key row r, 32 query columns = four 16-byte pieces) into the 128B-swizzled K-major
       // tiles the dV / dK MMAs read as their A operand; block it - 1's MMAs must have finished with the tiles
       if (it > 0) ptx::mbar_wait(pd_free, (it - 1) & 1);

@@ -39,20 +39,23 @@ def ragged(n, mean, seed):
     return lens, cu.to(DEV)
 
 
-def bench_attn(name, n, mean, H, d, causal, bwd):
+def bench_attn(name, n, mean, H, d, causal, bwd, drop=0.0):
     lens, cu = ragged(n, mean, 1)
     T, mx = int(lens.sum()), int(lens.max())
     qkv = torch.randn(T, 3 * H * d, device=DEV).bfloat16()
     q, k, v = qkv[:, :H * d], qkv[:, H * d:2 * H * d], qkv[:, 2 * H * d:]
     flops = float(4 * H * d * (lens.double() ** 2).sum()) * (0.5 if causal else 1.0)
-    us = timed(lambda: ops.attn_varlen(q, k, v, cu, cu, mx, H, d, causal=causal))
+    dk_ = dict(dropout_p=drop, dropout_seed=1234) if drop else {}
+    if drop:
+        name = f"{name} p={drop}"
+    us = timed(lambda: ops.attn_varlen(q, k, v, cu, cu, mx, H, d, causal=causal, **dk_))
     print(f"{name:28s} fwd  {us:9.1f} us  {flops / us / 1e6:7.1f} TFLOP/s  (T={T})")
     if bwd:
-        out, lse = ops.attn_varlen(q, k, v, cu, cu, mx, H, d, causal=causal, return_lse=True)
+        out, lse = ops.attn_varlen(q, k, v, cu, cu, mx, H, d, causal=causal, return_lse=True, **dk_)
         dout = torch.randn_like(out)
         dqkv = torch.empty_like(qkv)
         dq, dk, dv = dqkv[:, :H * d], dqkv[:, H * d:2 * H * d], dqkv[:, 2 * H * d:]
-        us = timed(lambda: ops.attn_varlen_bwd(q, k, v, out, dout, lse, cu, cu, mx, mx, H, d, causal, dq, dk, dv))
+        us = timed(lambda: ops.attn_varlen_bwd(q, k, v, out, dout, lse, cu, cu, mx, mx, H, d, causal, dq, dk, dv, **dk_))
         print(f"{name:28s} bwd  {us:9.1f} us  {2.5 * flops / us / 1e6:7.1f} TFLOP/s")
 
 
@@ -94,6 +97,9 @@ if __name__ == "__main__":
         bench_attn("encoder self (12 x 64)", 64, 995, 12, 64, False, bwd)
         bench_attn("decoder self (16 x 64, causal)", 64, 655, 16, 64, True, bwd)
         bench_attn("MAE decoder self (16 x 32)", 64, 495, 16, 32, False, bwd)
+        if "drop" in what:
+            bench_attn("encoder self (12 x 64)", 64, 995, 12, 64, False, bwd, 0.05)
+            bench_attn("decoder self (16 x 64, causal)", 64, 655, 16, 64, True, bwd, 0.1)
     if "ln" in what:
         bench_ln(63664, 768)
         bench_ln(41976, 1024)

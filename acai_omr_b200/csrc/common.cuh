@@ -96,8 +96,14 @@ __host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
   x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
   return x;
 }
+// (split in two so that kernels hashing a run of pairs with the same high word - 4 pairs per 16-byte vector - pay the
+// inner round once: dropout_bits(seed, pair) == dropout_bits_lo(dropout_bits_hi(seed, pair >> 32), (uint32_t)pair))
+__host__ __device__ __forceinline__ uint32_t dropout_bits_hi(uint64_t seed, uint32_t pair_hi) {
+  return mix32(pair_hi ^ (uint32_t)seed) ^ (uint32_t)(seed >> 32);
+}
+__host__ __device__ __forceinline__ uint32_t dropout_bits_lo(uint32_t hi_const, uint32_t pair_lo) { return mix32(pair_lo ^ hi_const); }
 __host__ __device__ __forceinline__ uint32_t dropout_bits(uint64_t seed, uint64_t pair) {
-  return mix32((uint32_t)pair ^ mix32((uint32_t)(pair >> 32) ^ (uint32_t)seed) ^ (uint32_t)(seed >> 32));
+  return dropout_bits_lo(dropout_bits_hi(seed, (uint32_t)(pair >> 32)), (uint32_t)pair);
 }
 __host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, uint32_t thr) {
   return ((dropout_bits(seed, idx >> 1) >> ((idx & 1) * 16)) & 0xffffu) >= thr;

@@ -225,9 +225,12 @@ __device__ __forceinline__ void epi_half_train(const Epi& ep, int pass, int64_t 
       }
     }
     if (mask) {
+      // elem0 is a multiple of 8 (N % 8 == 0, 32-column halves): the 4 pairs of this piece share their high word
+      const uint64_t pair0 = (uint64_t)(elem0 >> 1) + 4 * q;
+      const uint32_t hc = dropout_bits_hi(ep.drop_seed, (uint32_t)(pair0 >> 32));
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const uint32_t bits = dropout_bits(ep.drop_seed, (uint64_t)(elem0 >> 1) + 4 * q + k);
+        const uint32_t bits = dropout_bits_lo(hc, (uint32_t)pair0 + k);
         v[2 * k] *= (bits & 0xffffu) >= ep.drop_thr ? ep.drop_rp : 0.0f;
         v[2 * k + 1] *= (bits >> 16) >= ep.drop_thr ? ep.drop_rp : 0.0f;
       }

@@ -118,9 +118,11 @@ __global__ void gelu_bwd_kernel(const void* __restrict__ dy, int dy_dt, const vo
 }
 // keep factors (rp or 0) of the 8 consecutive elements 8*i8 .. 8*i8+7 = hash pairs 4*i8 .. 4*i8+3
 __device__ __forceinline__ void dropout_factors8(uint64_t seed, int64_t i8, uint32_t thr, float rp, float (&f)[8]) {
+  const uint64_t pair0 = (uint64_t)(4 * i8);             // a multiple of 4: the four pairs share their high word
+  const uint32_t hc = dropout_bits_hi(seed, (uint32_t)(pair0 >> 32));
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const uint32_t bits = dropout_bits(seed, (uint64_t)(4 * i8 + k));
+    const uint32_t bits = dropout_bits_lo(hc, (uint32_t)pair0 + k);
     f[2 * k] = (bits & 0xffffu) >= thr ? rp : 0.0f;
     f[2 * k + 1] = (bits >> 16) >= thr ? rp : 0.0f;
   }

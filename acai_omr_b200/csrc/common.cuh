@@ -88,6 +88,22 @@ __device__ __forceinline__ void phi_and_pdf(float z, float& cdf, float& e) {
   cdf = z >= 0.0f ? 1.0f - q : q;
 }
 
+// GELU for the bf16 paths (GEMM epilogues, the 16-byte forward kernel): x * Phi(x) with Phi(x) = 0.5 * (1 + tanh(u(x))), u an odd degree-5 polynomial
+// fitted so that |gelu_fast - exact erf GELU| <= 2.6e-5 before the MUFU's own error (tanh.approx.f32: rel 2^-11),
+// i.e. well inside the bf16 rounding of the stored activation.  9 issue slots + 1 MUFU per element (the A&S erfc
+// form it replaces cost 16 + 2 MUFU and made the GELU GEMM epilogue-bound).  u's polynomial turns over past
+// |x| = 7.25, where tanh has long saturated, hence the clamp.
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float xc = fminf(fmaxf(x, -7.0f), 7.0f);
+  const float x2 = xc * xc;
+  float p = fmaf(x2, -3.51708639e-04f, 3.70068271e-02f);
+  p = fmaf(x2, p, 7.97506586e-01f);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(xc * p));
+  const float hx = 0.5f * x;
+  return fmaf(hx, t, hx);
+}
+
 // ---- counter-based dropout randomness ---------------------------------------------------------------------------
 // One 32-bit avalanche hash (two multiply / xor-shift rounds) of (seed, index of an element PAIR) yields two 16-bit
 // uniforms; an element is kept when its 16 bits are >= thr = round(p * 65536).  Stateless, so the backward kernels

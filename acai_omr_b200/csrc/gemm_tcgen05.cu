@@ -53,22 +53,6 @@ template <int BN> constexpr size_t smem_bytes() {
 
 using namespace g5;
 
-// GELU for the bf16 tensor-core path: x * Phi(x) with Phi(x) = 0.5 * (1 + tanh(u(x))), u an odd degree-5 polynomial
-// fitted so that |gelu_fast - exact erf GELU| <= 2.6e-5 before the MUFU's own error (tanh.approx.f32: rel 2^-11),
-// i.e. well inside the bf16 rounding of the stored activation.  9 issue slots + 1 MUFU per element (the A&S erfc
-// form it replaces cost 16 + 2 MUFU and made the GELU GEMM epilogue-bound).  u's polynomial turns over past
-// |x| = 7.25, where tanh has long saturated, hence the clamp.
-__device__ __forceinline__ float gelu_fast(float x) {
-  const float xc = fminf(fmaxf(x, -7.0f), 7.0f);
-  const float x2 = xc * xc;
-  float p = fmaf(x2, -3.51708639e-04f, 3.70068271e-02f);
-  p = fmaf(x2, p, 7.97506586e-01f);
-  float t;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(xc * p));
-  const float hx = 0.5f * x;
-  return fmaf(hx, t, hx);
-}
-
 __device__ __forceinline__ void epi_store_chunk(const Epi& ep, const uint32_t (&acc)[32], int row, int64_t rrow, int col0,
                                                 int N, bool vec_ok) {
   // this thread owns out[row, col0 .. col0+31]

@@ -138,10 +138,9 @@ __device__ __forceinline__ uint4 gelu_fwd_vec(uint4 u, int64_t i, uint32_t thr, 
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     const float2 f = __bfloat1622float2(h[k]);
-    float c0, c1, e;
-    phi_and_pdf(f.x, c0, e);
-    phi_and_pdf(f.y, c1, e);
-    h[k] = __floats2bfloat162_rn(f.x * c0 * m[2 * k], f.y * c1 * m[2 * k + 1]);
+    // tanh form (one MUFU + 9 issue slots, 2.6e-5 from the exact erf GELU: far inside the bf16 rounding of h); the backward
+    // differentiates the exact form from the saved z
+    h[k] = __floats2bfloat162_rn(gelu_fast(f.x) * m[2 * k], gelu_fast(f.y) * m[2 * k + 1]);
   }
   return u;
 }

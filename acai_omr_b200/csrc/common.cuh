@@ -162,6 +162,20 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// d/dz [z Phi(z)] = Phi(z) + z phi(z) with Phi from gelu_fast's tanh fit (|Phi_fit - Phi| < 1e-4) and phi from one ex2:
+// 2 MUFU + 12 issue slots per element (the A&S form of phi_and_pdf: 2 MUFU + 18).  For the bf16 backward kernels, whose
+// result is rounded to 8 bits of mantissa.
+__device__ __forceinline__ float gelu_grad_fast(float z) {
+  const float zc = fminf(fmaxf(z, -7.0f), 7.0f);
+  const float z2 = zc * zc;
+  float p = fmaf(z2, -3.51708639e-04f, 3.70068271e-02f);
+  p = fmaf(z2, p, 7.97506586e-01f);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(zc * p));
+  const float e = fast_exp2(z2 * -0.72134752044448170368f);          // exp(-z^2 / 2)
+  return fmaf(zc * 0.39894228040143267794f, e, fmaf(0.5f, t, 0.5f));
+}
+
 // 2^x on the FMA / ALU pipes instead of the 16-lane MUFU unit: Cody-Waite split (round x to an integer n with the
 // 1.5 * 2^23 trick, f = x - n in [-0.5, 0.5]), a degree-3 minimax polynomial for 2^f (relative error 7.5e-5, well under
 // the 2e-3 half-ulp of the bf16 value it feeds) and n added straight into the exponent field.  x is clamped at -126 (the

@@ -154,11 +154,7 @@ __device__ __forceinline__ uint4 gelu_bwd_vec(uint4 u, uint4 g, int64_t i, uint3
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     const float2 f = __bfloat1622float2(h[k]), d = __bfloat1622float2(gh[k]);
-    float c0, c1, e0, e1;
-    phi_and_pdf(f.x, c0, e0);
-    phi_and_pdf(f.y, c1, e1);
-    h[k] = __floats2bfloat162_rn(d.x * fmaf(f.x * 0.39894228040143267794f, e0, c0) * m[2 * k],
-                                 d.y * fmaf(f.y * 0.39894228040143267794f, e1, c1) * m[2 * k + 1]);
+    h[k] = __floats2bfloat162_rn(d.x * gelu_grad_fast(f.x) * m[2 * k], d.y * gelu_grad_fast(f.y) * m[2 * k + 1]);
   }
   return u;
 }

@@ -190,9 +190,7 @@ __device__ __forceinline__ void epi_half_train(const Epi& ep, int pass, int64_t 
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float z = __bfloat162float(__float2bfloat16_rn(v[j]));   // what the backward will read
-          float cdf, e;
-          phi_and_pdf(z, cdf, e);
-          v[j] = z * cdf;
+          v[j] = gelu_fast(z);
         }
       }
     } else {
@@ -201,11 +199,8 @@ __device__ __forceinline__ void epi_half_train(const Epi& ep, int pass, int64_t 
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float2 z = __bfloat1622float2(zh[i]);
-        float cdf, e;
-        phi_and_pdf(z.x, cdf, e);
-        v[2 * i] *= fmaf(z.x * 0.39894228040143267794f, e, cdf);
-        phi_and_pdf(z.y, cdf, e);
-        v[2 * i + 1] *= fmaf(z.y * 0.39894228040143267794f, e, cdf);
+        v[2 * i] *= gelu_grad_fast(z.x);
+        v[2 * i + 1] *= gelu_grad_fast(z.y);
       }
     }
     if (mask) {

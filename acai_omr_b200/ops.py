@@ -511,11 +511,12 @@ def wgrad_accumulate(dz, x, dw):
 
 
 ERR_UNSUPPORTED = -2
-# GELU (+ dropout) forward / backward inside the tcgen05 GEMM epilogues.  Parity-green but measured SLOWER than the
-# standalone 16-byte GELU kernels on B200 (teacher-forced step 208.7 ms vs 203.4 ms, profiles/r1g_gelu_epilogue.md): with
-# K = 768 / 1024 the GEMM's eight epilogue warps are already the critical path and ~27 extra instructions per element at
-# an issue rate of ~0.45 IPC cost more than a second pass over HBM.  Opt in with ACAI_FUSE_GELU_GEMM=1.
-FUSE_GELU_GEMM = os.environ.get("ACAI_FUSE_GELU_GEMM", "0") == "1"
+# GELU (+ dropout) forward / backward inside the tcgen05 GEMM epilogues (acai_linear_gelu_train / acai_linear_gelu_bwd).
+# With the A&S erf form (~27 extra instructions per element on eight epilogue warps that are already the critical path at
+# K = 768 / 1024) this was slower than the standalone 16-byte GELU kernels (208.7 vs 203.4 ms, profiles/r1g_gelu_epilogue.md);
+# with the tanh-fit forms of round 1i (gelu_fast / gelu_grad_fast, 10 / 14 instructions) it wins: teacher-forced step
+# 178.3 -> 174.6 ms, MAE step unchanged.  ACAI_FUSE_GELU_GEMM=0 selects the standalone kernels.
+FUSE_GELU_GEMM = os.environ.get("ACAI_FUSE_GELU_GEMM", "1") != "0"
 
 
 def _try_call(name, fn, *args, flops=0.0, nbytes=0.0):

@@ -56,6 +56,7 @@ SIGNATURES = {
     "acai_colsum": [_p, _i32, _i64, _i32, _i32, _p, _i32, _p, _sz, _p],
     "acai_gelu_fwd": [_p, _i32, _p, _i32, _i64, _f32, _u64, _p],
     "acai_gelu_bwd": [_p, _i32, _p, _i32, _p, _i32, _i64, _f32, _u64, _p],
+    "acai_linear_dropout": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],
     "acai_layernorm_bwd_workspace_bytes": [_i32, _i32],
     "acai_layernorm_bwd": [_p, _i32, _p, _i32, _p, _i32, _p, _f32, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _sz, _p],
     "acai_ce_loss": [_p, _i32, _i64, _p, _i32, _i32, _i32, _p, _p, _p, _p, _i32, _i64, _p, _p],

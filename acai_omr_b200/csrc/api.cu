@@ -48,6 +48,8 @@ size_t linear_splitk_workspace_bytes(int M, int N, int K);
 int linear_splitk_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
                           int64_t ldr, const float* gamma, const float* beta, float eps, void* out, int out_dt, int64_t ldo, int M,
                           int N, int K, int act, void* ws, size_t ws_bytes, cudaStream_t st);
+int linear_dropout_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
+                           int64_t ldr, void* out, int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
 int linear_gelu_train_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* z, int64_t ldz,
                               void* h, int64_t ldh, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
 int linear_gelu_bwd_tcgen05(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
@@ -114,6 +116,21 @@ extern "C" int acai_linear_splitk(const void* a, int64_t lda, const void* w, int
   if (M == 0) return ACAI_OK;
   return acai::linear_splitk_tcgen05(a, lda, w, ldw, bias, residual, res_dtype, ldr, ln_gamma, ln_beta, ln_eps, out, out_dtype, ldo,
                                      M, N, K, act, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+// out = residual + dropout(a @ w^T + bias): the sub-layer output projection of a post-norm block with its nn.Dropout and
+// residual add in the GEMM epilogue (bf16 operands and output, dense [M, N] output).  ACAI_ERR_UNSUPPORTED, nothing written,
+// when the problem does not qualify - the caller then runs acai_linear_fwd + acai_dropout (same mask).
+extern "C" int acai_linear_dropout(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* residual,
+                                   int32_t res_dtype, int64_t ldr, void* out, int64_t ldo, int32_t M, int32_t N, int32_t K,
+                                   float dropout_p, uint64_t dropout_seed, void* stream) {
+  ACAI_CHECK_ARG(a && w && out, "acai_linear_dropout: null pointer");
+  ACAI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && lda >= K && ldw >= K && ldo >= N && (!residual || ldr >= N), "acai_linear_dropout: bad sizes");
+  ACAI_CHECK_ARG(dropout_p > 0.0f && dropout_p < 1.0f, "acai_linear_dropout: dropout_p must be in (0, 1)");
+  ACAI_CHECK_ARG(!residual || res_dtype == ACAI_BF16 || res_dtype == ACAI_F32, "acai_linear_dropout: bad residual dtype");
+  if (M == 0) return ACAI_OK;
+  return acai::linear_dropout_tcgen05(a, lda, w, ldw, bias, residual, res_dtype, ldr, out, ldo, M, N, K, dropout_p, dropout_seed,
+                                      (cudaStream_t)stream);
 }
 
 // Feed-forward up-projection for training: z = a @ w^T + bias and h = dropout(gelu(z)), both bf16, one GEMM.

@@ -126,8 +126,9 @@ __device__ __forceinline__ void res_prefetch(const Epi& ep, int64_t rrow, int co
 // bias (broadcast from smem) / GELU / residual on 32 columns, then the row's 16-byte pieces go to the 128B-swizzled
 // staging tile: piece p of row r lives at r*128 + ((p ^ (r & 7)) << 4), conflict-free for thread = row.
 template <bool OUT_BF16, int RES>
-__device__ __forceinline__ void epi_half(int act, const uint32_t (&acc)[32], const float* sb, const ResHalf<RES>& rb,
+__device__ __forceinline__ void epi_half(const Epi& ep, int64_t elem0, const uint32_t (&acc)[32], const float* sb, const ResHalf<RES>& rb,
                                          uint8_t* srow, uint32_t sw, int piece0) {
+  const int act = ep.act;
   float v[32];
 #pragma unroll
   for (int q = 0; q < 8; ++q) {
@@ -138,6 +139,15 @@ __device__ __forceinline__ void epi_half(int act, const uint32_t (&acc)[32], con
   if (act == ACAI_ACT_GELU) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
+  }
+  if (ep.drop_thr) {   // out = residual + dropout(a w^T + bias): the post-norm blocks' nn.Dropout, mask counter = row * N + column
+    const uint32_t pair0 = (uint32_t)(elem0 >> 1), hc = dropout_bits_hi(ep.drop_seed, (uint32_t)(elem0 >> 33));
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {      // elem0 is a multiple of 32: the 16 pairs share their high word
+      const uint32_t bits = dropout_bits_lo(hc, pair0 + k);
+      v[2 * k] *= (bits & 0xffffu) >= ep.drop_thr ? ep.drop_rp : 0.0f;
+      v[2 * k + 1] *= (bits >> 16) >= ep.drop_thr ? ep.drop_rp : 0.0f;
+    }
   }
   if constexpr (RES == 1) {
 #pragma unroll
@@ -368,7 +378,8 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
 #pragma unroll
             for (int hh = 0; hh < HALVES; ++hh) {
               if constexpr (MODE == 0)
-                epi_half<OUT_BF16, RES>(ep.act, acc[hh], sb + c * CW + hh * 32, rb[hh], srow, sw, hh * (OUT_BF16 ? 4 : 0));
+                epi_half<OUT_BF16, RES>(ep, (int64_t)grow * N + col0 + c * CW + hh * 32, acc[hh], sb + c * CW + hh * 32, rb[hh], srow, sw,
+                                        hh * (OUT_BF16 ? 4 : 0));
               else
                 epi_half_train<MODE>(ep, ps, (int64_t)grow * N + col0 + c * CW + hh * 32, acc[hh], sb + c * CW + hh * 32, rb[hh],
                                      srow, sw, hh * 4);
@@ -640,7 +651,7 @@ static int launch_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, c
                       (!ep.res || ((ep.ldr * res_es) % 16 == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
   // (BN = 64 serves small / skinny problems only; its 32-column warp slabs are narrower than a 128-byte bf16 chunk)
   const bool train_act = ep.act == ACT_GELU_TRAIN || ep.act == ACT_GELU_BWD;   // only the TMA-store epilogue has these
-  if (BN < 128 || !tma_ok) return train_act ? ACAI_ERR_UNSUPPORTED : launch_variant<BN, 0, 0>(ta, tb, ta, ta, ep, M, N, K, st);
+  if (BN < 128 || !tma_ok) return (train_act || ep.drop_thr) ? ACAI_ERR_UNSUPPORTED : launch_variant<BN, 0, 0>(ta, tb, ta, ta, ep, M, N, K, st);
   if constexpr (BN >= 128) {
   rc = make_tma_2d(&to, ep.out, ep.out_dt, (uint64_t)M, (uint64_t)N, (uint64_t)ep.ldo, 32, ep.out_dt == ACAI_BF16 ? 64 : 32);
   if (rc) return rc;
@@ -718,6 +729,16 @@ int linear_gelu_bwd_tcgen05(const void* dy, int64_t ldd, const void* wt, int64_t
   Epi ep{nullptr, z, ACAI_BF16, ldz, dz, ACAI_BF16, ldo, ACT_GELU_BWD, nullptr, nullptr, 0, thr,
          thr ? 1.0f / (1.0f - dropout_p) : 1.0f, seed};
   return dispatch_tiles(dy, ldd, wt, ldw, ep, M, N, K, st);
+}
+
+// out = residual + dropout(a @ w^T + bias), bf16, dense [M, N] output (the mask counter is row * N + column, the one
+// acai_dropout uses on the same tensor).  ACAI_ERR_UNSUPPORTED unless the TMA-store epilogue serves the problem.
+int linear_dropout_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
+                           int64_t ldr, void* out, int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st) {
+  if (!gemm_operands_ok(a, lda, w, ldw, M, N, K) || N % 32 != 0 || ldo != N) return ACAI_ERR_UNSUPPORTED;
+  const uint32_t thr = dropout_threshold(dropout_p);
+  Epi ep{bias, res, res_dt, ldr, out, ACAI_BF16, ldo, ACAI_ACT_NONE, nullptr, nullptr, 0, thr, thr ? 1.0f / (1.0f - dropout_p) : 1.0f, seed};
+  return dispatch_tiles(a, lda, w, ldw, ep, M, N, K, st);
 }
 
 int linear_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res,

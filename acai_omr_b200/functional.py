@@ -71,6 +71,9 @@ class _Linear(torch.autograd.Function):
                 raise ops.AcaiError("linear: GELU + residual is not used by the model")
             z = ops.linear(x2, w, b, out_dtype=dt)
             y = ops.gelu(z, out_dtype=out_dtype, dropout_p=dropout_p, dropout_seed=dropout_seed)
+        elif dropout_p > 0.0:           # y = residual + dropout(x W^T + b): the post-norm blocks' nn.Dropout, in the GEMM epilogue
+            y = _linear_out_dropout(x2, w, b, residual.reshape(-1, w.shape[0]).detach() if residual is not None else None,
+                                    out_dtype, dropout_p, dropout_seed)
         else:
             y = ops.linear(x2, w, b, residual=residual.detach() if residual is not None else None, out_dtype=out_dtype)
         ctx.save_for_backward(x2, weight, z)
@@ -91,6 +94,8 @@ class _Linear(torch.autograd.Function):
             dz = dy2 if dy2.dtype == dt else dy2.to(dt)
             if not dz.is_contiguous():
                 dz = dz.contiguous()
+            if ctx.drop[0] > 0.0:        # through the output dropout (same counter-based mask)
+                dz = ops.dropout(dz, ctx.drop[0], ctx.drop[1])
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
             wt = _weights().get_t(weight, dt, rows)                      # [K, N]
@@ -122,13 +127,25 @@ class _Linear(torch.autograd.Function):
         return dx, dw, db, dres, None, None, None, None, None
 
 
+def _linear_out_dropout(x2, w, b, residual, out_dtype, p, seed):
+    y = ops.linear_dropout(x2, w, b, residual, p, seed) if out_dtype == torch.bfloat16 and x2.dtype == torch.bfloat16 else None
+    if y is None:
+        y = ops.dropout(ops.linear(x2, w, b, out_dtype=out_dtype), p, seed, residual=residual)
+    return y
+
+
 def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None, rows=None, dropout_p=0.0):
     """dropout(act(x @ weight[rows].T + bias[rows])) + residual; `weight` / `bias` are the (fp32 master) parameters.
-    `dropout_p` > 0 (only with the GELU activation: the feed-forward block's inner nn.Dropout) is fused into the GELU kernel."""
+    `dropout_p` > 0: with the GELU activation the feed-forward block's inner nn.Dropout (fused into the GELU kernel); without
+    an activation `residual + dropout(x W^T + b)`, the sub-layer output dropout (fused into the GEMM epilogue)."""
     dt = x.dtype
-    if dropout_p > 0.0 and act != ops.ACT_GELU:
-        raise ops.AcaiError("linear: fused dropout is the GELU path's; use functional.dropout for the others")
     seed = ops.DropoutState.next_seed() if dropout_p > 0.0 else 0
+    if dropout_p > 0.0 and act != ops.ACT_GELU and not needs_grad(x, weight, bias, residual):
+        x2 = x.reshape(-1, x.shape[-1])
+        w = _weights().get(weight, dt, rows)
+        y = _linear_out_dropout(x2 if x2.stride(-1) == 1 else x2.contiguous(), w, _slice(bias, rows),
+                                residual.reshape(-1, w.shape[0]) if residual is not None else None, out_dtype or dt, dropout_p, seed)
+        return y.view(*x.shape[:-1], y.shape[-1])
     if not needs_grad(x, weight, bias, residual):
         y = ops.linear(x, _weights().get(weight, dt, rows), _slice(bias, rows), act=act, residual=residual,
                        out_dtype=out_dtype or dt)

@@ -145,9 +145,8 @@ class MultiheadAttention(nn.Module):
 
     def _out(self, a, residual, dt):
         p = self._p()
-        if p > 0.0:      # residual + dropout(out_proj(a)): the residual add moves out of the GEMM epilogue
-            return F.dropout(F.linear(a, self.out_proj.weight, self.out_proj.bias, out_dtype=dt), p, True, residual=residual)
-        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt)
+        # residual + dropout(out_proj(a)): dropout and residual add both in the GEMM epilogue (acai_linear_dropout)
+        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt, dropout_p=p)
 
     def self_attention_packed(self, x, pk, causal, residual):
         """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D]."""
@@ -241,9 +240,7 @@ def _mlp_residual(layer, x, dt):
     l1, l2 = layer.linear1, layer.linear2
     if not ops.FUSE_GELU_GEMM or l1.bias is None or l2.bias is None or x.dtype != dt:
         h = F.linear(x, l1.weight, l1.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=p)
-        if p > 0.0:
-            return F.dropout(F.linear(h, l2.weight, l2.bias, out_dtype=dt), p, True, residual=x)
-        return F.linear(h, l2.weight, l2.bias, residual=x, out_dtype=dt)
+        return F.linear(h, l2.weight, l2.bias, residual=x, out_dtype=dt, dropout_p=p)
     if p > 0.0:
         return F.dropout(F.feed_forward(x, l1.weight, l1.bias, l2.weight, l2.bias, add_residual=False, dropout_p=p), p, True,
                          residual=x)

@@ -598,6 +598,30 @@ def linear_gelu_train(x, weight, bias, dropout_p=0.0, dropout_seed=0):
     return (z, h) if ok else None
 
 
+FUSE_DROPOUT_GEMM = os.environ.get("ACAI_FUSE_DROPOUT_GEMM", "1") != "0"
+
+
+def linear_dropout(x, weight, bias, residual, dropout_p, dropout_seed):
+    """residual + dropout(x @ weight.T + bias), bf16, from one tcgen05 GEMM (acai_linear_dropout; the mask is `dropout`'s on
+    the dense [M, N] output); None when the operands do not qualify (the caller runs linear + dropout)."""
+    _cuda(x, weight, bias, residual)
+    M, K = x.shape
+    N = weight.shape[0]
+    if not FUSE_DROPOUT_GEMM or not _gemm_fusable(x, weight) or M == 0:
+        return None
+    if residual is not None and (residual.dim() != 2 or residual.shape != (M, N) or residual.stride(1) != 1 or
+                                 residual.dtype not in (torch.bfloat16, torch.float32)):
+        return None
+    out = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    b = _f32c(bias)
+    name = "acai_linear_dropout" if Profile.active is None else f"acai_linear_dropout[{M}x{N}x{K}]"
+    ok = _try_call(name, _lib.load().acai_linear_dropout, _p(x), x.stride(0), _p(weight), weight.stride(0), _p(b), _p(residual),
+                   _dt(residual) if residual is not None else 1, residual.stride(0) if residual is not None else 0, _p(out), N,
+                   M, N, K, float(dropout_p), C.c_uint64(dropout_seed), _stream(), flops=2.0 * M * N * K,
+                   nbytes=2.0 * (M * K + N * K + 2 * M * N))
+    return out if ok else None
+
+
 def linear_gelu_bwd(dy, weight_t, z, dropout_p=0.0, dropout_seed=0):
     """dz = (dy @ weight_t.T) * gelu'(z) * dropout_mask from one tcgen05 GEMM (acai_linear_gelu_bwd); None when the
     operands do not qualify (the caller runs linear + gelu_bwd)."""

@@ -340,6 +340,15 @@ int acai_gumbel_softmax_bwd(const void* dy, int32_t dy_dtype, const float* y_sof
 int acai_mix_rows(const void* a, int32_t a_dtype, const int64_t* sel, const void* b, int32_t b_dtype, const float* pos,
                   int32_t period, int32_t rows, int32_t dim, void* out, int32_t out_dtype, void* stream);
 
+/* out = residual + dropout(a @ w^T + bias): output projection + nn.Dropout + residual add of a post-norm sub-layer
+ * (reference: self.dropout1(self.self_attn(...)) + x and self.dropout2(self.linear2(...)) + x inside
+ * nn.TransformerEncoderLayer / nn.TransformerDecoderLayer, which the reference's models instantiate) in one GEMM.  bf16
+ * operands and output, dense [M, N] output (ldo == N): the mask is acai_dropout's on the same tensor (counter = row * N +
+ * column), so acai_dropout(dy, dropout_p, dropout_seed) is its backward.  residual may be NULL.  Returns
+ * ACAI_ERR_UNSUPPORTED, nothing written, when the problem does not qualify (then: acai_linear_fwd + acai_dropout). */
+int acai_linear_dropout(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* residual,
+                        int32_t res_dtype, int64_t ldr, void* out, int64_t ldo, int32_t M, int32_t N, int32_t K, float dropout_p,
+                        uint64_t dropout_seed, void* stream);
 /* Feed-forward block, training (models.py:30-34 / nn.TransformerEncoderLayer's linear1 -> gelu -> dropout): one tcgen05
  * GEMM whose epilogue stores the pre-activation z = a @ w^T + bias (bf16 [M, N], kept for the backward) AND
  * h = dropout(gelu(z)) (bf16 [M, N]); the dropout mask is that of acai_gelu_fwd on a dense [M, N] tensor with the same

@@ -712,6 +712,43 @@ def test_linear_gelu_bwd_epilogue(M_, N, K, p):
     assert rel_err(dz, ref) <= rel_err(unfused, ref) * 1.05 + 1e-4       # fp32 accumulators into the derivative: no worse
 
 
+@pytest.mark.parametrize("M_,N,K", [(1000, 768, 768), (513, 1024, 4096), (300, 128, 64)])
+@pytest.mark.parametrize("with_res", [True, False])
+def test_linear_dropout_epilogue(M_, N, K, with_res):
+    """acai_linear_dropout: residual + dropout(x W^T + b) from one GEMM, the mask being acai_dropout's on the dense output."""
+    x = rnd(M_, K, seed=131, dtype=torch.bfloat16)
+    w = (rnd(N, K, seed=132) / math.sqrt(K)).bfloat16()
+    b = 0.1 * rnd(N, seed=133)
+    res = rnd(M_, N, seed=134, dtype=torch.bfloat16) if with_res else None
+    p, seed = 0.1, 0x5eed0000beef
+    y = ops.linear_dropout(x, w, b, res, p, seed)
+    keep = ops.dropout_mask(M_ * N, p, seed, DEV).view(M_, N)
+    ref = (x.float() @ w.float().t() + b) * keep / (1 - p) + (res.float() if with_res else 0.0)
+    unfused = ops.dropout(ops.linear(x, w, b, out_dtype=torch.bfloat16), p, seed, residual=res)
+    if y is not None:                    # (small problems are served by tiles without the TMA-store epilogue: not fused)
+        assert rel_err(y, ref) < 4e-3
+        assert rel_err(y, ref) <= rel_err(unfused, ref) * 1.05 + 1e-4
+        if not with_res:
+            assert float(y[~keep].abs().max()) == 0.0
+    else:
+        assert M_ * N < 148 * 128 * 128
+    # through autograd (fused or not): the gradients of residual + dropout(linear)
+    xr = x.clone().requires_grad_(True)
+    wr = w.float().clone().requires_grad_(True)
+    br = b.clone().requires_grad_(True)
+    ops.DropoutState.manual_seed(5)
+    out = F.linear(xr, wr, br, residual=res, out_dtype=torch.bfloat16, dropout_p=p)
+    dy = rnd(M_, N, seed=135, dtype=torch.bfloat16)
+    out.backward(dy)
+    ops.DropoutState.manual_seed(5)
+    keep2 = ops.dropout_mask(M_ * N, p, ops.DropoutState.next_seed(), DEV).view(M_, N)
+    assert rel_err(out, (x.float() @ w.float().t() + b) * keep2 / (1 - p) + (res.float() if with_res else 0.0)) < 4e-3
+    dz = dy.float() * keep2 / (1 - p)
+    assert rel_err(xr.grad, dz @ w.float()) < 1e-2
+    assert rel_err(wr.grad, dz.t() @ x.float()) < 1e-2
+    assert rel_err(br.grad, dz.sum(0)) < 1e-2
+
+
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1.5e-2)])
 @pytest.mark.parametrize("p,add_residual", [(0.0, True), (0.2, False)])
 def test_feed_forward_node(dtype, tol, p, add_residual):

@@ -23,6 +23,7 @@ have no stored fixture in the reference itself ("pinned by live oracle").
 """
 from __future__ import annotations
 
+import contextlib
 import math
 from dataclasses import dataclass, field
 
@@ -32,24 +33,72 @@ PAD_TOKEN, BOS_TOKEN, EOS_TOKEN = "<pad>", "<bos>", "<eos>"  # acai_omr/config.p
 
 
 # --------------------------------------------------------------------------- #
+# precision mode
+# --------------------------------------------------------------------------- #
+# The reference's production inference runs the transition head and the cached greedy loop under
+# `torch.autocast(dtype=torch.bfloat16)` with bf16 KV caches, the encoder in fp32 outside it
+# (acai_omr/inference/vitomr_inference.py:79-86,94).  `autocast_bf16()` restates what autocast does to the ops on that
+# path: `F.linear` / `nn.Linear` and `F.scaled_dot_product_attention` take bf16 operands (fp32 accumulation, ONE rounding
+# of the result to bf16); GELU runs in its input's dtype (bf16 after a Linear); residual adds promote to the fp32 stream
+# (the token embedding + position rows are fp32 parameters), so every LayerNorm sees and returns fp32; the logits come
+# out of `unembed` in bf16 and argmax / log_softmax read those.  Pinned by tests/golden/golden_bf16.pt (the unmodified
+# reference under `torch.autocast("cpu", torch.bfloat16)`; tests/golden/make_golden_bf16.py).
+_AUTOCAST_BF16 = False
+_ROUNDED = {}          # bf16-rounded copies of weight tensors, alive for the duration of one autocast_bf16() block
+
+
+@contextlib.contextmanager
+def autocast_bf16(enabled=True):
+    global _AUTOCAST_BF16
+    prev, _AUTOCAST_BF16 = _AUTOCAST_BF16, bool(enabled)
+    try:
+        yield
+    finally:
+        _AUTOCAST_BF16 = prev
+        if not prev:
+            _ROUNDED.clear()
+
+
+def _r(x):
+    """Round to bf16, keep computing in fp32."""
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+def _rw(w):
+    """`_r` of a weight (slice), cached by storage address + shape: a decode loop reads the same weights every step."""
+    key = (w.data_ptr(), tuple(w.shape), tuple(w.stride()))
+    hit = _ROUNDED.get(key)
+    if hit is None:
+        hit = _ROUNDED[key] = (_r(w), w)      # the source tensor is kept alive so that its address cannot be reused
+    return hit[0]
+
+
+# --------------------------------------------------------------------------- #
 # primitives
 # --------------------------------------------------------------------------- #
 def linear(x, w, b=None):
     """y = x W^T + b  (torch `F.linear`; used at kv_caching.py:193,215,244)."""
+    if _AUTOCAST_BF16:
+        y = _r(x) @ _rw(w).t()
+        if b is not None:
+            y = y + _rw(b)
+        return y.to(torch.bfloat16)
     y = x @ w.t()
     return y if b is None else y + b
 
 
 def gelu(x):
     """Exact-erf GELU (`activation="gelu"`, models.py:31; `nn.GELU()`, models.py:657)."""
-    return 0.5 * x * (1.0 + torch.erf(x * (1.0 / math.sqrt(2.0))))
+    xf = x.float()
+    return (0.5 * xf * (1.0 + torch.erf(xf * (1.0 / math.sqrt(2.0))))).to(x.dtype)
 
 
 def layer_norm(x, w, b, eps):
-    """LayerNorm over the last dim with biased variance (torch semantics)."""
-    mu = x.mean(dim=-1, keepdim=True)
-    var = ((x - mu) ** 2).mean(dim=-1, keepdim=True)
-    return (x - mu) / torch.sqrt(var + eps) * w + b
+    """LayerNorm over the last dim with biased variance (torch semantics; fp32 statistics for any input dtype)."""
+    xf = x.float()
+    mu = xf.mean(dim=-1, keepdim=True)
+    var = ((xf - mu) ** 2).mean(dim=-1, keepdim=True)
+    return ((xf - mu) / torch.sqrt(var + eps) * w + b).to(x.dtype)
 
 
 def patchify(img, P):
@@ -98,14 +147,14 @@ def mha(x_q, x_kv, in_w, in_b, out_w, out_b, H, key_pad_mask=None, causal=False)
     q = linear(x_q, in_w[:D], in_b[:D]).view(B, Tq, H, d).transpose(1, 2)
     k = linear(x_kv, in_w[D : 2 * D], in_b[D : 2 * D]).view(B, Tk, H, d).transpose(1, 2)
     v = linear(x_kv, in_w[2 * D :], in_b[2 * D :]).view(B, Tk, H, d).transpose(1, 2)
-    s = (q @ k.transpose(-1, -2)) / math.sqrt(d)
+    s = (q.float() @ k.float().transpose(-1, -2)) / math.sqrt(d)
     if causal:
         tri = torch.triu(torch.ones(Tq, Tk, dtype=torch.bool, device=s.device), diagonal=1)
         s = s.masked_fill(tri, float("-inf"))
     if key_pad_mask is not None:
         s = s.masked_fill(key_pad_mask[:, None, None, :], float("-inf"))
     p = torch.softmax(s, dim=-1)
-    o = (p @ v).transpose(1, 2).reshape(B, Tq, D)
+    o = (p @ v.float()).to(q.dtype).transpose(1, 2).reshape(B, Tq, D)
     return linear(o, out_w, out_b)
 
 
@@ -250,19 +299,21 @@ def prepare_caches(memory, sd, H, stack="decoder_blocks"):
         pre = f"{stack}.layers.{i}.multihead_attn."
         kv = linear(memory, sd[pre + "in_proj_weight"][D:], sd[pre + "in_proj_bias"][D:])
         k, v = kv.chunk(2, dim=-1)
-        st.k_cross.append(k.view(B, S, H, d).transpose(1, 2))
-        st.v_cross.append(v.view(B, S, H, d).transpose(1, 2))
-        st.k_self.append(memory.new_zeros(B, H, 0, d))
-        st.v_self.append(memory.new_zeros(B, H, 0, d))
+        # .float().contiguous(): in bf16 mode the caches hold bf16-rounded VALUES in fp32 containers (exact), laid out
+        # head-major, so that the per-step attention neither re-converts nor re-strides the whole cache
+        st.k_cross.append(k.view(B, S, H, d).transpose(1, 2).float().contiguous())
+        st.v_cross.append(v.view(B, S, H, d).transpose(1, 2).float().contiguous())
+        st.k_self.append(torch.zeros(B, H, 0, d))
+        st.v_self.append(torch.zeros(B, H, 0, d))
     return st
 
 
 def _attend_one(q, K, V, mask=None):
     """CachedMultiheadAttention.cached_forward's SDPA (kv_caching.py:123-136); q:(B,H,1,d)."""
-    s = (q @ K.transpose(-1, -2)) / math.sqrt(q.shape[-1])
+    s = (q.float() @ K.float().transpose(-1, -2)) / math.sqrt(q.shape[-1])
     if mask is not None:
         s = s.masked_fill(mask[:, None, None, :], float("-inf"))
-    o = torch.softmax(s, dim=-1) @ V
+    o = (torch.softmax(s, dim=-1) @ V.float()).to(q.dtype)
     return o.transpose(1, 2).flatten(start_dim=-2)
 
 
@@ -274,8 +325,8 @@ def cached_decoder_step(x, st, sd, H, mem_pad_mask=None, stack="decoder_blocks")
         pre = f"{stack}.layers.{i}."
         qkv = linear(x, sd[pre + "self_attn.in_proj_weight"], sd[pre + "self_attn.in_proj_bias"])
         q, k, v = (t.view(B, H, 1, d) for t in qkv.chunk(3, dim=-1))  # kv_caching.py:194-202 (a view, not a transpose)
-        st.k_self[i] = torch.cat([st.k_self[i], k], dim=2)
-        st.v_self[i] = torch.cat([st.v_self[i], v], dim=2)
+        st.k_self[i] = torch.cat([st.k_self[i], k.float()], dim=2)
+        st.v_self[i] = torch.cat([st.v_self[i], v.float()], dim=2)
         a = linear(_attend_one(q, st.k_self[i], st.v_self[i]),
                    sd[pre + "self_attn.out_proj.weight"], sd[pre + "self_attn.out_proj.bias"])
         x = layer_norm(x + a, sd[pre + "norm1.weight"], sd[pre + "norm1.bias"], 1e-5)
@@ -332,6 +383,18 @@ def cached_greedy_generate(memory, sd, H, mem_pad_mask=None, max_len=1536, pad_i
     logp = logp.masked_fill(~m, 0.0)
     n = int(m.sum(dim=-1).max())
     return seqs[:, :n], logp[:, :n], m[:, :n], all_logits
+
+
+def cached_forced_logits(memory, sd, H, tokens, mem_pad_mask=None):
+    """The cached decoder step of cached_greedy_generate driven by GIVEN tokens: logits[:, t-1] is what the loop sees at
+    step t (input tokens[:, t-1], `time_step = t`, models.py:575-577) -> (B, T-1, V).  Lets a second implementation be
+    compared step by step on the same prefix, where a free-running comparison stops meaning anything after the first
+    near-tie flips."""
+    st = prepare_caches(memory, sd, H)
+    out = []
+    for t in range(1, tokens.shape[1]):
+        out.append(cached_generate(tokens[:, t - 1 : t], t, st, sd, H, mem_pad_mask).squeeze(1))
+    return torch.stack(out, dim=1)
 
 
 def batchify_and_split_lmx_seqs(lmx_seqs, pad_idx):

@@ -1,9 +1,8 @@
 """The oracle (oracle/vitomr_oracle.py) against the reference's own outputs and known answers.
-
 Golden entries were produced by the unmodified reference (tests/golden/make_golden.py).
 CPU only; this is the pin that lets the GPU tests trust the oracle."""
 import os
-
+import pytest
 import torch
 
 from oracle import vitomr_oracle as O
@@ -239,3 +238,37 @@ def test_oracle_dynamic_resize_target_sizes():
         assert O.dynamic_resize_target(h, w, 16, 1024) == want
     assert O.dynamic_resize_target(700, 300, 16, 512) == (512, 256)        # portrait: aspect = height // width
     assert O.dynamic_resize_target(100, 420, 16, 512) == (176, 704)
+
+
+# ---- bf16 inference mode (vitomr_inference.py:79-86,94) pinned to the unmodified reference's own bf16 run ------------
+@pytest.mark.parametrize("name", ["flat", "peaked"])
+def test_oracle_bf16_mode_matches_reference_recorded_run(name):
+    """tests/golden/golden_bf16.pt = the reference's transition head + cached greedy loop under
+    torch.autocast("cpu", bfloat16) with bf16 KV caches (make_golden_bf16.py).  The oracle's `autocast_bf16()` mode,
+    driven by the reference's tokens, must give the reference's per-step logits within the bf16 gate (2e-2; measured
+    8e-3 / 1.1e-2: one bf16 ulp of the largest logit - torch's CPU bf16 kernels round partial sums differently), agree on
+    every argmax except inside the tie band, and every free-running divergence must sit at a tie."""
+    import os
+    from oracle import parity as P
+    g = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_bf16.pt"),
+                   map_location="cpu", weights_only=False)[name]
+    sd, H, max_len = g["sd"], g["cfg"]["num_heads"], g["cfg"]["max_len"]
+    dec = {k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}
+    with torch.no_grad(), O.autocast_bf16():
+        head = O.transition_head(g["latent"], sd)
+        forced = O.cached_forced_logits(head, dec, H, g["seqs"], g["mask"])
+        seqs, logp, m, _ = O.cached_greedy_generate(head, dec, H, g["mask"], max_len=max_len)
+    assert head.dtype == torch.bfloat16 and forced.dtype == torch.bfloat16
+    n = forced.shape[1]
+    valid = g["seq_mask"][:, :n]
+    assert P.errors(head, g["head"], ~g["mask"])["max_rel"] < 4e-3
+    e = P.errors(forced, g["logits"][:, :n], valid)
+    assert e["max_rel"] < P.BF16_TOL and e["l2_rel"] < P.BF16_TOL, e
+    a = P.argmax_agreement(forced, g["logits"][:, :n], P.BF16_TOL, valid)
+    assert a["not_tie_disagreements"] == 0 and a["agree"] > 0.9, a
+    d = P.divergence_report(seqs, g["seqs"], g["logits"], P.BF16_TOL)
+    assert d["exact_or_tie_flip_rate"] == 1.0, d
+    # the fp32 oracle sits inside the same gate: the 2e-2 tolerance is about bf16 rounding, not about the algorithm
+    with torch.no_grad():
+        forced32 = O.cached_forced_logits(O.transition_head(g["latent"], sd), dec, H, g["seqs"], g["mask"])
+    assert P.errors(forced32, g["logits"][:, :n], valid)["max_rel"] < P.BF16_TOL

@@ -18,7 +18,7 @@ import os
 import torch
 
 from . import ops
-from .layers import Packed, compute_dtype, lens_from_mask, w_
+from .layers import WEIGHTS, Packed, compute_dtype, lens_from_mask, w_
 
 PAGE = 64
 POLL = 32
@@ -62,6 +62,9 @@ class GreedyDecodeEngine:
             self.ws_splitk = max((ops.splitk_workspace(batch, D, k, device) for k in (D, mlp)), key=lambda t: t.numel())
         self.graph = None
         self.launches_per_step = 0
+        self.logits = None                  # [B, V] logits of the last step (static graph memory once captured)
+        self._params_seen = None            # (version, data_ptr) of every decoder parameter + the weight-cache generation
+        self._operands_seen = None          # device addresses the captured graph reads its weights from
         # sampling mode (GRPO rollouts): None = greedy; else (top_k, temperature).  The seed is device state so that the
         # captured graph draws a new stream per rollout; `uniforms` (fp32 [B, max_len]) replaces the hash in parity tests.
         self.sampling = None
@@ -99,6 +102,7 @@ class GreedyDecodeEngine:
         if dec.decoder_blocks.norm is not None:
             x = dec.decoder_blocks.norm(x, out_dtype=dt)
         logits = ops.linear(x, w_(dec.unembed.weight, dt), dec.unembed.bias, out_dtype=dt)
+        self.logits = logits
         if self.sampling is None:
             ops.greedy_update(logits, self.step, self.seqs, self.logp, self.finished, dec.eos_idx)
         else:
@@ -145,8 +149,37 @@ class GreedyDecodeEngine:
             self.sampling, self.graph = sampling, None
         self.seed.fill_(int(seed) & 0x7FFFFFFFFFFFFFFF)
 
-    def generate(self, stop_early=True):
-        """Run steps t = 1 .. max_len-1 (or until every row has emitted <eos>); returns raw (seqs, log_probs)."""
+    # ---- the captured graph holds raw device addresses of the weights: notice when they go stale ---------------------
+    def _param_state(self):
+        return (WEIGHTS.generation,) + tuple((p._version, p.data_ptr()) for p in self.dec.parameters())
+
+    def _operand_addresses(self):
+        """Every weight address `_step` hands to a kernel (the bf16 operand copies `w_` returns, refreshed here if their
+        parameter changed, and the fp32 parameters the kernels read directly: biases, LayerNorm rows, embedding tables)."""
+        dec, dt, D = self.dec, self.dt, self.D
+        ptrs = [p.data_ptr() for p in dec.parameters()]
+        for layer in dec.decoder_blocks.layers:
+            sa, ca = layer.self_attn, layer.multihead_attn
+            for t in (w_(sa.in_proj_weight, dt), w_(sa.out_proj.weight, dt), w_(ca.in_proj_weight, dt, rows=(0, D)),
+                      w_(ca.out_proj.weight, dt), w_(layer.linear1.weight, dt), w_(layer.linear2.weight, dt)):
+                ptrs.append(t.data_ptr())
+        ptrs.append(w_(dec.unembed.weight, dt).data_ptr())
+        return tuple(ptrs)
+
+    def _check_weights(self):
+        """Drop the graph when a weight it reads has moved (`load_state_dict`, an optimiser step through torch, `.to()`):
+        the bf16 operand copy of an updated parameter is a NEW tensor and the old one is freed, so replaying would read
+        stale or released memory.  Copies that are refreshed in place (train.FlatTrainer's shadows) keep their address and
+        the graph stays valid."""
+        state = self._param_state()
+        if state == self._params_seen:
+            return
+        self._params_seen = state
+        if self.graph is not None and self._operand_addresses() != self._operands_seen:
+            self.graph = None
+
+    def _ensure_graph(self):
+        self._check_weights()
         if self.graph is None:
             self._reset()
             n0 = ops.launch_count()
@@ -158,12 +191,34 @@ class GreedyDecodeEngine:
             with torch.cuda.graph(g):
                 self._step()
             self.graph = g
+            self._operands_seen = self._operand_addresses()
+            self._params_seen = self._param_state()
+
+    def generate(self, stop_early=True):
+        """Run steps t = 1 .. max_len-1 (or until every row has emitted <eos>); returns raw (seqs, log_probs)."""
+        self._ensure_graph()
         self._reset()
         for t in range(1, self.max_len):
             self.graph.replay()
             if stop_early and t % POLL == 0 and bool(self.finished.all()):
                 break
         return self.seqs, self.logp
+
+    def forced_logits(self, tokens):
+        """The captured step driven by GIVEN tokens (B, T): returns (B, T-1, V) logits, entry [:, t-1] being what the greedy
+        loop sees at step t after the prefix tokens[:, :t] (input token tokens[:, t-1], position row t, models.py:575-577).
+        Same graph, same kernels as `generate`; only the token written back after each step is the caller's.  Parity
+        tests compare these step by step with the oracle / the reference's recorded logits."""
+        self._ensure_graph()
+        self._reset()
+        tokens = tokens.to(self.device, torch.long)
+        T = min(tokens.shape[1], self.max_len)
+        out = []
+        for t in range(1, T):
+            self.seqs[:, t - 1] = tokens[:, t - 1]
+            self.graph.replay()
+            out.append(self.logits.float().clone())
+        return torch.stack(out, dim=1)
 
 
 def get_engine(vitomr, decoder, batch, max_len, mem_rows, dt, device):

@@ -1,7 +1,9 @@
 """The oracle (oracle/vitomr_oracle.py) against the reference's own outputs and known answers.
+
 Golden entries were produced by the unmodified reference (tests/golden/make_golden.py).
 CPU only; this is the pin that lets the GPU tests trust the oracle."""
 import os
+
 import pytest
 import torch
 

@@ -54,6 +54,8 @@ SIGNATURES = {
     "acai_transpose": [_p, _i32, _i64, _i32, _i32, _p, _i64, _p],
     "acai_colsum_workspace_bytes": [_i32, _i32],
     "acai_colsum": [_p, _i32, _i64, _i32, _i32, _p, _i32, _p, _sz, _p],
+    "acai_colsum_static_max_workspace_bytes": [],
+    "acai_colsum_static": [_p, _i32, _i64, _i32, _i32, _p, _i32, _p],
     "acai_gelu_fwd": [_p, _i32, _p, _i32, _i64, _f32, _u64, _p],
     "acai_gelu_bwd": [_p, _i32, _p, _i32, _p, _i32, _i64, _f32, _u64, _p],
     "acai_linear_dropout": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],

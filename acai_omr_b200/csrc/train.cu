@@ -3,6 +3,7 @@
 // the operand transposes they need plus the memory-bound pieces (bias gradients, GELU, LayerNorm, cross-entropy,
 // embedding / position scatter-adds, MAE glue).  All reductions that feed parameters have a fixed order or use fp32
 // atomics on distinct rows only where the reference's own autograd is non-deterministic too (index_add).
+#include <mutex>
 #include "common.cuh"
 
 namespace acai {
@@ -536,6 +537,46 @@ extern "C" int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t row
   colsum_final_wide_kernel<<<(cols + 31) / 32, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float*>(workspace), slabs, cols, out,
                                                                              accumulate);
   return launch_status("colsum_final");
+}
+
+// ---- acai_colsum_static: the same two kernels with the slab partials in a file-scope device array ---------------------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): no
+// workspace argument, no cudaMalloc / cudaFree / allocating library call anywhere on this path.  The array is part of the
+// module image: every GPU that loads the library holds its 4 MiB until the process exits.  In host code the NAME of a
+// __device__ array is a host-side stand-in, not a device address, so the address each device gave the array is looked up
+// once per device with cudaGetSymbolAddress (that device current) and passed to the kernels like any other workspace.
+// All calls share the array: it keeps the last call's partials (nothing has to start at zero - every slot a call reads
+// was written by that call's first kernel), and two calls that overlap on the GPU (different streams) race on it.
+constexpr size_t COLSUM_STATIC_BYTES = size_t(4) << 20;
+static __device__ __align__(256) float g_colsum_static_scratch[COLSUM_STATIC_BYTES / sizeof(float)];
+constexpr int COLSUM_STATIC_MAX_DEVICES = 64;
+static float* g_colsum_static_ptr[COLSUM_STATIC_MAX_DEVICES] = {};
+static std::mutex g_colsum_static_mutex;
+
+extern "C" size_t acai_colsum_static_max_workspace_bytes(void) { return COLSUM_STATIC_BYTES; }
+
+extern "C" int acai_colsum_static(const void* x, int32_t dtype, int64_t ld, int32_t rows, int32_t cols, float* out,
+                                  int32_t accumulate, void* stream) {
+  ACAI_CHECK_ARG(x && out && rows > 0 && cols > 0 && dtype_valid(dtype), "acai_colsum_static: bad argument");
+  const size_t need = acai_colsum_workspace_bytes(rows, cols);
+  ACAI_CHECK_ARG(need <= COLSUM_STATIC_BYTES,
+                 "acai_colsum_static: %d rows x %d columns need %zu bytes of slab partials, the static scratch holds %zu "
+                 "(ceil(rows / 128) * cols * 4 <= 4 MiB); use acai_colsum with a caller workspace",
+                 rows, cols, need, COLSUM_STATIC_BYTES);
+  int dev = -1;
+  ACAI_CUDA(cudaGetDevice(&dev));
+  ACAI_CHECK_ARG(dev >= 0 && dev < COLSUM_STATIC_MAX_DEVICES, "acai_colsum_static: device ordinal %d out of range", dev);
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_colsum_static_mutex);
+    if (!g_colsum_static_ptr[dev]) {               // set-up, once per device, with that device current
+      void* sym = nullptr;
+      ACAI_CUDA(cudaGetSymbolAddress(&sym, g_colsum_static_scratch));
+      g_colsum_static_ptr[dev] = reinterpret_cast<float*>(sym);
+    }
+    scratch = g_colsum_static_ptr[dev];
+  }
+  return acai_colsum(x, dtype, ld, rows, cols, out, accumulate, scratch, COLSUM_STATIC_BYTES, stream);
 }
 
 extern "C" int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, float dropout_p,

@@ -292,6 +292,19 @@ int acai_transpose(const void* in, int32_t dtype, int64_t ld_in, int32_t rows, i
 size_t acai_colsum_workspace_bytes(int32_t rows, int32_t cols);
 int acai_colsum(const void* x, int32_t dtype, int64_t ld, int32_t rows, int32_t cols, float* out, int32_t accumulate,
                 void* workspace, size_t workspace_bytes, void* stream);
+/* acai_colsum_static: acai_colsum without a workspace argument.  NO COUNTERPART IN THE REFERENCE - added
+ * for callers that cannot allocate scratch memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  The slab partials live in a file-scope `static __device__` array of
+ * acai_colsum_static_max_workspace_bytes() = 4 MiB (every GPU that loads the library holds it until the process exits);
+ * the entry point calls no cudaMalloc / cudaFree / allocating library routine.  Limit: acai_colsum_workspace_bytes(rows,
+ * cols) = ceil(rows / 128) * cols * 4 must not exceed 4 MiB (e.g. 65 536 rows x 2 048 columns); larger problems return
+ * ACAI_ERR_INVALID with the sizes in acai_last_error().  Same kernels, same fixed summation order, bit-identical results
+ * to acai_colsum.  Every call shares the one array per device (it keeps the previous call's partials; nothing needs to
+ * start at zero): calls that overlap on the GPU - different streams, or concurrent graph branches - RACE on it and must
+ * be serialised by the caller.  The device current at the call must be the one `x` / `out` live on. */
+size_t acai_colsum_static_max_workspace_bytes(void);
+int acai_colsum_static(const void* x, int32_t dtype, int64_t ld, int32_t rows, int32_t cols, float* out, int32_t accumulate,
+                       void* stream);
 int acai_gelu_fwd(const void* z, int32_t z_dtype, void* out, int32_t out_dtype, int64_t n, float dropout_p,
                   uint64_t dropout_seed, void* stream);     /* out = dropout(gelu(z)): the feed-forward block's nn.Dropout fused */
 int acai_gelu_bwd(const void* dy, int32_t dy_dtype, const void* z, int32_t z_dtype, void* dz, int32_t dz_dtype, int64_t n,

@@ -72,7 +72,8 @@ SIGNATURES = {
     "acai_mix_rows": [_p, _i32, _p, _p, _i32, _p, _i32, _i32, _i32, _p, _i32, _p],
     "acai_dynamic_resize": [_p, _i32, _i32, _i32, _i32, _i32, _p],
     "acai_linear_splitk_workspace_bytes": [_i32, _i32, _i32],
-    "acai_linear_splitk": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _p, _f32, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p, _sz, _p],
+    "acai_linear_splitk": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _p, _f32, _p, _i32, _i64, _p, _i32, _i64, _i32, _i32, _i32,
+                           _i32, _p, _sz, _p],
     "acai_linear_gelu_train": [_p, _i64, _p, _i64, _p, _p, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],
     "acai_linear_gelu_bwd": [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],
     "acai_wgrad_accumulate": [_p, _i64, _p, _i64, _i32, _p, _i64, _i32, _i32, _i32, _p],
@@ -83,7 +84,7 @@ SIGNATURES = {
     "acai_decode_workspace_bytes": [_i32, _i32, _i32],
     "acai_decode_attn_paged": [_p, _i64, _p, _i64, _p, _i32, _p, _i32, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _f32, _p,
                                _i32, _i64, _p, _sz, _i64, _p],
-    "acai_decode_embed": [_p, _i64, _p, _i32, _p, _p, _p, _i32, _i32, _p],
+    "acai_decode_embed": [_p, _i64, _p, _i32, _p, _p, _p, _i32, _p, _i32, _i32, _p],
     "acai_greedy_update": [_p, _i32, _i64, _i32, _i32, _p, _p, _i64, _p, _p, _i32, _p],
     "acai_topk_sample_update": [_p, _i32, _i64, _i32, _i32, _i32, _f32, _p, _i64, _p, _p, _p, _i64, _p, _p, _i32, _p],
     "acai_advance_step": [_p, _p],

@@ -46,7 +46,8 @@ int linear_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const
                    cudaStream_t st);
 size_t linear_splitk_workspace_bytes(int M, int N, int K);
 int linear_splitk_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
-                          int64_t ldr, const float* gamma, const float* beta, float eps, void* out, int out_dt, int64_t ldo, int M,
+                          int64_t ldr, const float* gamma, const float* beta, float eps, void* out, int out_dt, int64_t ldo,
+                          void* out2, int out2_dt, int64_t ldo2, int M,
                           int N, int K, int act, void* ws, size_t ws_bytes, cudaStream_t st);
 int linear_dropout_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
                            int64_t ldr, void* out, int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
@@ -106,16 +107,18 @@ extern "C" size_t acai_linear_splitk_workspace_bytes(int32_t M, int32_t N, int32
 
 extern "C" int acai_linear_splitk(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* residual,
                                   int32_t res_dtype, int64_t ldr, const float* ln_gamma, const float* ln_beta, float ln_eps,
-                                  void* out, int32_t out_dtype, int64_t ldo, int32_t M, int32_t N, int32_t K, int32_t act,
+                                  void* out, int32_t out_dtype, int64_t ldo, void* out2, int32_t out2_dtype, int64_t ldo2,
+                                  int32_t M, int32_t N, int32_t K, int32_t act,
                                   void* workspace, size_t workspace_bytes, void* stream) {
   ACAI_CHECK_ARG(a && w && out && workspace, "acai_linear_splitk: null pointer");
   ACAI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && lda >= K && ldw >= K && ldo >= N, "acai_linear_splitk: bad sizes M=%d N=%d K=%d", M, N, K);
   ACAI_CHECK_ARG(dtype_valid(out_dtype) && (!residual || (dtype_valid(res_dtype) && ldr >= N)), "acai_linear_splitk: bad dtype/ldr");
   ACAI_CHECK_ARG(act == ACAI_ACT_NONE || act == ACAI_ACT_GELU, "acai_linear_splitk: bad activation %d", act);
   ACAI_CHECK_ARG(!ln_gamma == !ln_beta, "acai_linear_splitk: ln_gamma and ln_beta come together");
+  ACAI_CHECK_ARG(!out2 || (dtype_valid(out2_dtype) && ldo2 >= N), "acai_linear_splitk: bad out2 dtype / ldo2");
   if (M == 0) return ACAI_OK;
   return acai::linear_splitk_tcgen05(a, lda, w, ldw, bias, residual, res_dtype, ldr, ln_gamma, ln_beta, ln_eps, out, out_dtype, ldo,
-                                     M, N, K, act, workspace, workspace_bytes, (cudaStream_t)stream);
+                                     out2, out2_dtype, ldo2, M, N, K, act, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 // out = residual + dropout(a @ w^T + bias): the sub-layer output projection of a post-norm block with its nn.Dropout and

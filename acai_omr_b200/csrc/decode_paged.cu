@@ -189,11 +189,14 @@ decode_combine_kernel(const float* __restrict__ ws, int max_chunks, int chunk_to
 // step counter so that one captured CUDA graph can be replayed for every step ----
 __global__ void decode_embed_kernel(const int64_t* __restrict__ seqs, int64_t seq_stride, const int32_t* __restrict__ step_ptr,
                                     const float* __restrict__ table, const float* __restrict__ pos,
-                                    void* __restrict__ out, int out_dt, int dim) {
+                                    void* __restrict__ out, int out_dt, void* __restrict__ out2, int out2_dt, int dim) {
   const int b = blockIdx.x, t = *step_ptr;
   const int64_t tok = seqs[(int64_t)b * seq_stride + t - 1];      // token at index t-1 ...
-  for (int c = threadIdx.x; c < dim; c += blockDim.x)             // ... gets pos_embedding[t] (reference quirk, models.py:576)
-    st_from_float(out, (int64_t)b * dim + c, out_dt, __ldg(table + tok * dim + c) + __ldg(pos + (int64_t)t * dim + c));
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) {           // ... gets pos_embedding[t] (reference quirk, models.py:576)
+    const float v = __ldg(table + tok * dim + c) + __ldg(pos + (int64_t)t * dim + c);
+    st_from_float(out, (int64_t)b * dim + c, out_dt, v);
+    if (out2) st_from_float(out2, (int64_t)b * dim + c, out2_dt, v);   // fp32 residual stream + its bf16 GEMM operand
+  }
 }
 
 __global__ void greedy_update_kernel(const void* __restrict__ logits, int dt, int64_t ld, int rows, int vocab,
@@ -359,12 +362,12 @@ extern "C" int acai_decode_attn_paged(const void* q, int64_t q_stride, const voi
 }
 
 extern "C" int acai_decode_embed(const int64_t* seqs, int64_t seq_stride, const int32_t* step_ptr, int32_t batch,
-                                 const float* table, const float* pos, void* out, int32_t out_dtype, int32_t dim,
-                                 void* stream) {
-  ACAI_CHECK_ARG(seqs && step_ptr && table && pos && out && batch > 0 && dim > 0 && dtype_valid(out_dtype),
-                 "acai_decode_embed: bad argument");
+                                 const float* table, const float* pos, void* out, int32_t out_dtype, void* out2,
+                                 int32_t out2_dtype, int32_t dim, void* stream) {
+  ACAI_CHECK_ARG(seqs && step_ptr && table && pos && out && batch > 0 && dim > 0 && dtype_valid(out_dtype) &&
+                 (!out2 || dtype_valid(out2_dtype)), "acai_decode_embed: bad argument");
   decode_embed_kernel<<<batch, dim >= 512 ? 256 : 64, 0, (cudaStream_t)stream>>>(seqs, seq_stride, step_ptr, table, pos,
-                                                                              out, out_dtype, dim);
+                                                                              out, out_dtype, out2, out2_dtype, dim);
   return launch_status("decode_embed");
 }
 

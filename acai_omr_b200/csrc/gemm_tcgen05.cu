@@ -442,7 +442,7 @@ template <int VPL>
 __global__ void __launch_bounds__(64)
 splitk_reduce_kernel(const float* __restrict__ ws, int splitk, int M, int N, const float* __restrict__ bias, const void* res,
                      int res_dt, int64_t ldr, int act, const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
-                     void* out, int out_dt, int64_t ldo) {
+                     void* out, int out_dt, int64_t ldo, void* out2, int out2_dt, int64_t ldo2) {
   pdl_wait();
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -465,7 +465,19 @@ splitk_reduce_kernel(const float* __restrict__ ws, int splitk, int M, int N, con
     }
     return a;
   };
+  // out2 (optional): a second copy of the row in another dtype - the fp32 residual stream keeps `out` = fp32 and hands the
+  // next GEMM its bf16 operand through `out2` (what torch.autocast does to a LayerNorm output that feeds a Linear)
   auto store = [&](int col, float4 a) {
+    if (out2) {
+      const int64_t o2 = (int64_t)row * ldo2 + col;
+      if (out2_dt == ACAI_BF16) {
+        const __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
+        uint2 pk; pk.x = *reinterpret_cast<const uint32_t*>(&h0); pk.y = *reinterpret_cast<const uint32_t*>(&h1);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(out2) + o2) = pk;
+      } else {
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(out2) + o2) = a;
+      }
+    }
     const int64_t o = (int64_t)row * ldo + col;
     if (out_dt == ACAI_BF16) {
       const __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
@@ -763,11 +775,13 @@ size_t linear_splitk_workspace_bytes(int M, int N, int K) {
 // out = LN?( act(a . w^T + bias) + residual ) for M <= 256 rows.  ACAI_ERR_UNSUPPORTED (nothing written) when the problem
 // does not qualify: operands not TMA-able, no K slices to gain, N % 4, LayerNorm rows that do not fit the register variant.
 int linear_splitk_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, const void* res, int res_dt,
-                          int64_t ldr, const float* gamma, const float* beta, float eps, void* out, int out_dt, int64_t ldo, int M,
+                          int64_t ldr, const float* gamma, const float* beta, float eps, void* out, int out_dt, int64_t ldo,
+                          void* out2, int out2_dt, int64_t ldo2, int M,
                           int N, int K, int act, void* ws, size_t ws_bytes, cudaStream_t st) {
   if (!gemm_operands_ok(a, lda, w, ldw, M, N, K) || M > 256 || N % 4 != 0 || (reinterpret_cast<uintptr_t>(ws) & 15) ||
       (out_dt == ACAI_BF16 && ((ldo % 4) || (reinterpret_cast<uintptr_t>(out) & 7))))
     return ACAI_ERR_UNSUPPORTED;
+  if (out2 && ((ldo2 % 4) || (reinterpret_cast<uintptr_t>(out2) & (out2_dt == ACAI_BF16 ? 7 : 15)))) return ACAI_ERR_UNSUPPORTED;
   const int sk = splitk_factor(M, N, K);
   const bool in_regs = N % 128 == 0 && N / 128 <= 8;     // the row fits the register-resident reduce variants
   const int vpl = in_regs ? N / 128 : 0;
@@ -796,7 +810,7 @@ int linear_splitk_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw
   }
   const dim3 grid((M + 1) / 2);
 #define ACAI_RED(V) ACAI_CUDA(launch_pdl(splitk_reduce_kernel<V>, grid, dim3(64), 0, st, static_cast<const float*>(ws), ep.splitk, M, N, \
-                                        bias, res, res_dt, ldr, act, gamma, beta, eps, out, out_dt, ldo))
+                                        bias, res, res_dt, ldr, act, gamma, beta, eps, out, out_dt, ldo, out2, out2_dt, ldo2))
   switch (vpl) {
     case 0: ACAI_RED(0); break;
     case 1: ACAI_RED(1); break;

@@ -7,6 +7,12 @@ Layout in HBM (dtype = compute dtype, bf16 under autocast / fp32 otherwise):
   per step     x [B, D], qkv [B, 3D], mlp hidden [B, M], logits [B, V]
 Per step and layer: qkv GEMM -> paged split-KV attention (appends this step's K|V row) -> out-proj GEMM (+residual)
 -> LN -> cross-q GEMM -> attention over the memory cache -> out-proj GEMM (+residual) -> LN -> MLP GEMMs -> LN.
+Precision of the bf16 mode = what torch.autocast does to the reference's cached loop (vitomr_inference.py:82-84): Linear
+and attention operands / results in bf16, but the RESIDUAL STREAM in fp32 - the embedding rows are fp32 parameters, a
+bf16 sub-layer output added to them promotes to fp32, and LayerNorm runs (and returns) fp32 under autocast.  So the step
+carries x twice: `x` fp32 [B, D] (residual operand of the next reduce / LayerNorm) and `xb` bf16 (operand of the next
+GEMM), both written by the same kernel.  ACAI_DECODE_STREAM=bf16 restores round 1's single bf16 stream (1.7x the logit
+error against the oracle, profiles/r2a_parity.md).
 The step index lives in device memory; the embedding, attention and greedy-update kernels read it, so the same
 graph serves every step.  `finished` is polled every POLL steps; extra steps past the all-finished point only write
 positions that mask_and_clip_seqs discards, so outputs are identical to the reference loop.
@@ -56,6 +62,8 @@ class GreedyDecodeEngine:
         self.ws_cross = None
         # small-M projections: split-K GEMM + fused bias / residual / LayerNorm reduce (ACAI_DECODE_SPLITK=0 switches it off)
         self.use_splitk = os.environ.get("ACAI_DECODE_SPLITK", "1") != "0" and 4 < batch <= 256
+        # fp32 residual stream under bf16 autocast (the reference's semantics); in fp32 mode there is only one stream anyway
+        self.stream_dt = torch.float32 if os.environ.get("ACAI_DECODE_STREAM", "fp32") != "bf16" else dt
         self.ws_splitk = None
         if self.use_splitk:
             mlp = blocks.layers[0].linear1.out_features
@@ -74,34 +82,48 @@ class GreedyDecodeEngine:
     # ---- one decode step (what the graph captures) ------------------------------------------------------------
     def _proj(self, x, weight, bias, residual=None, norm=None, act=ops.ACT_NONE):
         """norm(act(x @ weight.T + bias) + residual): at decode batch sizes (<= 256 rows) one split-K GEMM + one reduce kernel
-        with the LayerNorm inside (acai_linear_splitk); otherwise acai_linear_fwd + acai_layernorm_fwd."""
-        dt = self.dt
+        with the LayerNorm inside (acai_linear_splitk); otherwise acai_linear_fwd + acai_layernorm_fwd.  With a norm the
+        result is the pair (stream row in `stream_dt`, GEMM operand row in `dt`) - one tensor twice when the dtypes agree."""
+        dt, sdt = self.dt, self.stream_dt
+        two = norm is not None and sdt != dt
+        odt = sdt if norm is not None else dt
         if self.use_splitk and dt == torch.bfloat16:
             ln = None if norm is None else (norm.weight, norm.bias, norm.eps)
-            y = ops.linear_splitk(x, weight, bias, act=act, residual=residual, ln=ln, out_dtype=dt, workspace=self.ws_splitk)
+            y = ops.linear_splitk(x, weight, bias, act=act, residual=residual, ln=ln, out_dtype=odt, workspace=self.ws_splitk,
+                                  out2_dtype=dt if two else None)
             if y is not None:
-                return y
-        y = ops.linear(x, weight, bias, act=act, residual=residual, out_dtype=dt)
-        return y if norm is None else norm(y, out_dtype=dt)
+                return y if (two or norm is None) else (y, y)
+        y = ops.linear(x, weight, bias, act=act, residual=residual, out_dtype=odt)
+        if norm is None:
+            return y
+        if two:
+            return norm(y, out_dtype=sdt, out2_dtype=dt)
+        y = norm(y, out_dtype=dt)
+        return y, y
 
     def _step(self):
         dec, dt, D, H = self.dec, self.dt, self.D, self.H
-        x = ops.decode_embed(self.seqs, self.step, dec.vocab_embedding.weight, dec.pos_embedding, dt)
+        # x: the residual stream (stream_dt), xb: the same rows as the GEMM operand (dt)
+        if self.stream_dt != dt:
+            x, xb = ops.decode_embed(self.seqs, self.step, dec.vocab_embedding.weight, dec.pos_embedding, self.stream_dt,
+                                     out2_dtype=dt)
+        else:
+            x = xb = ops.decode_embed(self.seqs, self.step, dec.vocab_embedding.weight, dec.pos_embedding, dt)
         for i, layer in enumerate(dec.decoder_blocks.layers):
             sa, ca = layer.self_attn, layer.multihead_attn
-            qkv = ops.linear(x, w_(sa.in_proj_weight, dt), sa.in_proj_bias, out_dtype=dt)
+            qkv = ops.linear(xb, w_(sa.in_proj_weight, dt), sa.in_proj_bias, out_dtype=dt)
             a = ops.decode_attn_paged(qkv[:, :D], qkv[:, D:], self.pool[i], H, 64, self.max_len, self.ws_self, dt,
                                       page_table=self.page_table, step=self.step, len_offset=-1)
-            x = self._proj(a, w_(sa.out_proj.weight, dt), sa.out_proj.bias, residual=x, norm=layer.norm1)
-            qc = self._proj(x, w_(ca.in_proj_weight, dt, rows=(0, D)), ca.in_proj_bias[:D])
+            x, xb = self._proj(a, w_(sa.out_proj.weight, dt), sa.out_proj.bias, residual=x, norm=layer.norm1)
+            qc = self._proj(xb, w_(ca.in_proj_weight, dt, rows=(0, D)), ca.in_proj_bias[:D])
             c = ops.decode_attn_paged(qc, None, self.cross[i], H, 64, self.max_mem_len, self.ws_cross, dt,
                                       seq_start=self.seq_start, kv_lens=self.kv_lens)
-            x = self._proj(c, w_(ca.out_proj.weight, dt), ca.out_proj.bias, residual=x, norm=layer.norm2)
-            h = ops.linear(x, w_(layer.linear1.weight, dt), layer.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
-            x = self._proj(h, w_(layer.linear2.weight, dt), layer.linear2.bias, residual=x, norm=layer.norm3)
+            x, xb = self._proj(c, w_(ca.out_proj.weight, dt), ca.out_proj.bias, residual=x, norm=layer.norm2)
+            h = ops.linear(xb, w_(layer.linear1.weight, dt), layer.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+            x, xb = self._proj(h, w_(layer.linear2.weight, dt), layer.linear2.bias, residual=x, norm=layer.norm3)
         if dec.decoder_blocks.norm is not None:
-            x = dec.decoder_blocks.norm(x, out_dtype=dt)
-        logits = ops.linear(x, w_(dec.unembed.weight, dt), dec.unembed.bias, out_dtype=dt)
+            xb = dec.decoder_blocks.norm(x, out_dtype=dt)
+        logits = ops.linear(xb, w_(dec.unembed.weight, dt), dec.unembed.bias, out_dtype=dt)
         self.logits = logits
         if self.sampling is None:
             ops.greedy_update(logits, self.step, self.seqs, self.logp, self.finished, dec.eos_idx)

@@ -8,10 +8,18 @@ Precision policy (mirrors the reference's use of autocast, vitomr_inference.py:8
   * inside `torch.autocast("cuda", dtype=torch.bfloat16)`  -> bf16 operands / fp32 accumulate,
     weights cached as bf16 copies, LayerNorm statistics in fp32;
   * otherwise -> fp32 end to end (the token-exact mode).
+Residual stream under bf16: torch.autocast keeps it in fp32 - LayerNorm autocasts to fp32 and a bf16 sub-layer output
+added to an fp32 stream promotes - and only the Linear / attention operands are bf16.  Inference (no autograd) does the
+same here (`stream_dtype`): every block carries the pair (x: fp32 stream rows, xb: the same rows in bf16 as the next GEMM's
+operand), the out-projection / linear2 GEMMs read the fp32 residual and write fp32, LayerNorm writes both copies in one
+pass.  Against the fp32 oracle the full-size encoder's error halves (l2 1.1e-2 -> 0.6e-2, profiles/r2a_parity.md) for
+~10 % more time; ACAI_STREAM=bf16 selects round 1's single bf16 stream.  Training (autograd on) keeps the bf16 stream: it is
+what the saved-for-backward tensors are.
 """
 from __future__ import annotations
 
 import math
+import os
 import weakref
 
 import torch
@@ -25,6 +33,30 @@ def compute_dtype() -> torch.dtype:
     if torch.is_autocast_enabled("cuda") and torch.get_autocast_dtype("cuda") == torch.bfloat16:
         return torch.bfloat16
     return torch.float32
+
+
+STREAM_FP32 = os.environ.get("ACAI_STREAM", "fp32") != "bf16"
+
+
+def stream_dtype(dt: torch.dtype) -> torch.dtype:
+    """dtype of the residual stream for compute dtype `dt` (see the module docstring)."""
+    if dt == torch.bfloat16 and STREAM_FP32 and not torch.is_grad_enabled():
+        return torch.float32
+    return dt
+
+
+def to_stream(h):
+    """Packed rows `h` (compute dtype) -> (stream rows, GEMM operand rows)."""
+    sdt = stream_dtype(h.dtype)
+    return (h if sdt == h.dtype else h.to(sdt)), h
+
+
+def norm_pair(norm, y, dt):
+    """LayerNorm of stream rows y -> (stream rows, the same rows in the GEMM operand dtype `dt`), one kernel."""
+    if y.dtype != dt:
+        return norm(y, out_dtype=y.dtype, out2_dtype=dt)
+    x = norm(y, out_dtype=dt)
+    return x, x
 
 
 class _WeightCache:
@@ -145,11 +177,13 @@ class MultiheadAttention(nn.Module):
 
     def _out(self, a, residual, dt):
         p = self._p()
-        # residual + dropout(out_proj(a)): dropout and residual add both in the GEMM epilogue (acai_linear_dropout)
-        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual, out_dtype=dt, dropout_p=p)
+        # residual + dropout(out_proj(a)): dropout and residual add both in the GEMM epilogue (acai_linear_dropout); the
+        # sum comes out in the residual's dtype (fp32 when the stream is fp32)
+        return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual,
+                        out_dtype=dt if residual is None else residual.dtype, dropout_p=p)
 
     def self_attention_packed(self, x, pk, causal, residual):
-        """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D]."""
+        """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D] (x: GEMM operand rows, residual: stream rows)."""
         dt, D = x.dtype, self.embed_dim
         qkv = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt)
         a = F.self_attention(qkv, pk, self.num_heads, self.head_dim, causal,
@@ -227,17 +261,26 @@ class TransformerEncoderLayer(nn.Module):
         self.norm2 = LayerNorm(d_model, eps=layer_norm_eps, **kw)
         self.dropout_p = dropout
 
-    def forward_packed(self, x, pk: Packed):
-        dt = x.dtype
-        y = self.self_attn.self_attention_packed(x, pk, False, residual=x)
-        x = self.norm1(y, out_dtype=dt)
-        return self.norm2(_mlp_residual(self, x, dt), out_dtype=dt)
+    def forward_packed(self, x, pk: Packed, xb=None):
+        """x: stream rows, xb: the same rows as GEMM operand (None: x) -> the pair after the layer (one tensor when xb is
+        None, for callers that carry a single stream)."""
+        single = xb is None
+        xb = x if single else xb
+        dt = xb.dtype
+        y = self.self_attn.self_attention_packed(xb, pk, False, residual=x)
+        x, xb = norm_pair(self.norm1, y, dt)
+        x, xb = norm_pair(self.norm2, _mlp_residual(self, xb, dt, stream=x), dt)
+        return x if single else (x, xb)
 
 
-def _mlp_residual(layer, x, dt):
-    """x + dropout2(linear2(dropout(gelu(linear1(x)))))  (the feed-forward block of nn.Transformer*Layer, post-norm)."""
+def _mlp_residual(layer, x, dt, stream=None):
+    """x + dropout2(linear2(dropout(gelu(linear1(x)))))  (the feed-forward block of nn.Transformer*Layer, post-norm).
+    `stream`: the residual rows when they are kept apart from the GEMM operand rows x (fp32 stream)."""
     p = layer.dropout_p if layer.training else 0.0
     l1, l2 = layer.linear1, layer.linear2
+    if stream is not None and stream is not x:
+        h = F.linear(x, l1.weight, l1.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=p)
+        return F.linear(h, l2.weight, l2.bias, residual=stream, out_dtype=stream.dtype, dropout_p=p)
     if not ops.FUSE_GELU_GEMM or l1.bias is None or l2.bias is None or x.dtype != dt:
         h = F.linear(x, l1.weight, l1.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=p)
         return F.linear(h, l2.weight, l2.bias, residual=x, out_dtype=dt, dropout_p=p)
@@ -264,13 +307,17 @@ class TransformerEncoder(nn.Module):
         for layer in self.layers[1:]:
             layer.load_state_dict(self.layers[0].state_dict())
 
-    def forward_packed(self, x, pk: Packed, final_dtype=None):
+    def forward_packed(self, x, pk: Packed, final_dtype=None, xb=None, return_pair=False):
+        """x: packed rows [sum L, D].  A caller that chains stacks passes the pair (x = stream rows, xb = operand rows) and
+        asks for it back (`return_pair`); otherwise the pair is made and dropped here."""
+        if xb is None:
+            x, xb = to_stream(x)
         for layer in self.layers:
             _check_dropout(self, layer.dropout_p)
-            x = layer.forward_packed(x, pk)
+            x, xb = layer.forward_packed(x, pk, xb)
         if self.norm is not None:
-            x = self.norm(x, out_dtype=final_dtype or x.dtype)
-        return x
+            x = xb = self.norm(x, out_dtype=final_dtype or xb.dtype)
+        return (x, xb) if return_pair else (x if self.norm is not None else xb)
 
     def forward(self, src, mask=None, src_key_padding_mask=None):
         """Padded API: src (B, L, D), src_key_padding_mask (B, L) True = padding."""
@@ -308,17 +355,23 @@ class TransformerDecoderLayer(nn.Module):
     def _make_attention(self, d_model, nhead, dropout, **kw):
         return MultiheadAttention(d_model, nhead, dropout=dropout, **kw)
 
-    def mlp_packed(self, x):
-        return self.norm3(_mlp_residual(self, x, x.dtype), out_dtype=x.dtype)
+    def mlp_packed(self, x, xb=None):
+        if xb is None:
+            return self.norm3(_mlp_residual(self, x, x.dtype), out_dtype=x.dtype)
+        return norm_pair(self.norm3, _mlp_residual(self, xb, xb.dtype, stream=x), xb.dtype)
 
-    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True):
-        dt = x.dtype
-        y = self.self_attn.self_attention_packed(x, tgt, causal, residual=x)
-        x = self.norm1(y, out_dtype=dt)
+    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True, xb=None):
+        """x: stream rows, xb: operand rows (None: x; then one tensor comes back)."""
+        single = xb is None
+        xb = x if single else xb
+        dt = xb.dtype
+        y = self.self_attn.self_attention_packed(xb, tgt, causal, residual=x)
+        x, xb = norm_pair(self.norm1, y, dt)
         kv = self.multihead_attn.project_memory_packed(mem)
-        y = self.multihead_attn.cross_attention_packed(x, kv, tgt, mem_pk, residual=x)
-        x = self.norm2(y, out_dtype=dt)
-        return self.mlp_packed(x)
+        y = self.multihead_attn.cross_attention_packed(xb, kv, tgt, mem_pk, residual=x)
+        x, xb = norm_pair(self.norm2, y, dt)
+        x, xb = self.mlp_packed(x, xb)
+        return x if single else (x, xb)
 
 
 class TransformerDecoder(nn.Module):
@@ -332,13 +385,20 @@ class TransformerDecoder(nn.Module):
         for layer in self.layers[1:]:
             layer.load_state_dict(self.layers[0].state_dict())
 
-    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True, final_dtype=None):
+    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True, final_dtype=None, stream=None):
+        """x: operand rows (compute dtype); `stream`: the same rows before they were rounded to it (fp32 embedding sum), if
+        the caller has them."""
+        if stream is not None and stream_dtype(x.dtype) == stream.dtype:
+            xb = x
+            x = stream
+        else:
+            x, xb = to_stream(x)
         for layer in self.layers:
             _check_dropout(self, layer.dropout_p)
-            x = layer.forward_packed(x, tgt, mem, mem_pk, causal)
+            x, xb = layer.forward_packed(x, tgt, mem, mem_pk, causal, xb)
         if self.norm is not None:
-            x = self.norm(x, out_dtype=final_dtype or x.dtype)
-        return x
+            return self.norm(x, out_dtype=final_dtype or xb.dtype)
+        return xb
 
     def forward(self, tgt, memory, tgt_mask=None, memory_mask=None, tgt_key_padding_mask=None,
                 memory_key_padding_mask=None, tgt_is_causal=None, memory_is_causal=False):

@@ -17,7 +17,7 @@ from torch import nn
 
 from .. import ops
 from ..layers import (LayerNorm, Linear, MultiheadAttention, TransformerDecoder, TransformerDecoderLayer,
-                      compute_dtype, w_)
+                      compute_dtype, norm_pair, stream_dtype, w_)
 
 
 class KVCache(nn.Module):
@@ -66,7 +66,8 @@ class CachedMultiheadAttention(MultiheadAttention):
                             out_dtype=q_t.dtype)
         dt = a.dtype
         out = ops.linear(a, w_(self.out_proj.weight, dt), self.out_proj.bias,
-                         residual=None if residual is None else residual.reshape(B, H * d), out_dtype=dt)
+                         residual=None if residual is None else residual.reshape(B, H * d),
+                         out_dtype=dt if residual is None else residual.dtype)      # the sum joins the residual stream
         return out.view(B, 1, H * d)
 
 
@@ -86,22 +87,24 @@ class CachedTransformerDecoderLayer(TransformerDecoderLayer):
     def cached_forward(self, tgt_t, self_attn_kv_cache: KVCache, cached_kv_mem, memory_key_padding_mask=None):
         """One decode step for one layer (kv_caching.py:190-223); tgt_t (B,1,D)."""
         dt = compute_dtype()
-        if tgt_t.dtype != dt:
-            tgt_t = tgt_t.to(dt)
+        sdt = stream_dtype(dt)               # the residual stream (fp32 under bf16 autocast, as in the reference); xb = its
+        x = tgt_t if tgt_t.dtype == sdt else tgt_t.to(sdt)          # copy in the GEMM operand dtype
+        xb = x if sdt == dt else x.to(dt)
         B, D, H, d = tgt_t.shape[0], self.hidden_dim, self.num_heads, self.head_dim
-        qkv = ops.linear(tgt_t, w_(self.self_attn.in_proj_weight, dt), self.self_attn.in_proj_bias, out_dtype=dt)
+        qkv = ops.linear(xb, w_(self.self_attn.in_proj_weight, dt), self.self_attn.in_proj_bias, out_dtype=dt)
         q_t, k_t, v_t = (c.view(B, H, 1, d) for c in qkv.chunk(3, dim=-1))
         K_t, V_t = self_attn_kv_cache.update(k_t, v_t)
-        y = self.self_attn.cached_forward(q_t, K_t, V_t, residual=tgt_t)
-        tgt_t = self.norm1(y, out_dtype=dt)
+        y = self.self_attn.cached_forward(q_t, K_t, V_t, residual=x)
+        x, xb = norm_pair(self.norm1, y, dt)
 
-        q_c = ops.linear(tgt_t, w_(self.multihead_attn.in_proj_weight, dt, rows=(0, D)),
+        q_c = ops.linear(xb, w_(self.multihead_attn.in_proj_weight, dt, rows=(0, D)),
                          self.multihead_attn.in_proj_bias[:D], out_dtype=dt).view(B, H, 1, d)
         K_cross, V_cross = cached_kv_mem
         y = self.multihead_attn.cached_forward(q_c, K_cross, V_cross, memory_key_padding_mask=memory_key_padding_mask,
-                                               residual=tgt_t)
-        tgt_t = self.norm2(y, out_dtype=dt)
-        return self.mlp_packed(tgt_t.view(B, D)).view(B, 1, D)
+                                               residual=x)
+        x, xb = norm_pair(self.norm2, y, dt)
+        x, xb = self.mlp_packed(x.view(B, D), xb.view(B, D))
+        return x.view(B, 1, D)
 
 
 class MemoryCache(nn.Module):
@@ -161,5 +164,7 @@ class CachedTransformerDecoder(TransformerDecoder):
             x = layer.cached_forward(x, self.self_attn_caches[i], self.cross_attn_caches[i].get_cached_keys_and_vals(),
                                      memory_key_padding_mask=memory_key_padding_mask)
         if self.norm is not None:
-            x = self.norm(x, out_dtype=x.dtype)
+            x = self.norm(x, out_dtype=compute_dtype())
+        elif x.dtype != compute_dtype():
+            x = x.to(compute_dtype())
         return x

@@ -18,7 +18,7 @@ from .. import functional as F
 from .. import ops
 from ..config import LMX_BOS_TOKEN, LMX_EOS_TOKEN, LMX_PAD_TOKEN
 from ..layers import (LayerNorm, Linear, Packed, TransformerDecoder, TransformerDecoderLayer, TransformerEncoder,
-                      TransformerEncoderLayer, compute_dtype, gelu_mlp_head, lens_from_mask, w_)
+                      TransformerEncoderLayer, compute_dtype, gelu_mlp_head, lens_from_mask, stream_dtype, to_stream, w_)
 from .kv_caching import CachedTransformerDecoder, CachedTransformerDecoderLayer
 
 NUM_CHANNELS = 1  # models.py:11
@@ -91,9 +91,9 @@ class Encoder(nn.Module):
     def encode_packed(self, x):
         """Ragged images -> (packed latent rows after all layers + final norm (fp32), Packed)."""
         h, pk = self.embed_packed(x)
-        stacks = self._stacks()
-        for s in stacks:
-            h = s.forward_packed(h, pk, final_dtype=torch.float32 if s.norm is not None else None)
+        h, hb = to_stream(h)                 # (residual stream rows, GEMM operand rows): one tensor unless bf16 inference
+        for s in self._stacks():
+            h, hb = s.forward_packed(h, pk, final_dtype=torch.float32 if s.norm is not None else None, xb=hb, return_pair=True)
         return h, pk
 
     # ---- reference API --------------------------------------------------------------------------
@@ -404,16 +404,20 @@ class OMRDecoder(nn.Module):
         dt = compute_dtype()
         dev = self.pos_embedding.device
         tp = Packed(tgt_lens, dev)
+        stream = None
         if token_idxs_input:
-            x = F.embed_tokens(input_seqs, self.vocab_embedding.weight, self.pos_embedding, dt,
+            sdt = stream_dtype(dt)           # fp32 embedding + position sum when the residual stream is fp32
+            x = F.embed_tokens(input_seqs, self.vocab_embedding.weight, self.pos_embedding, sdt,
                                padding_idx=self.vocab_embedding.padding_idx)  # (B,T,D)
             x = F.pack_padded(x, tp.cu, tp.total)
+            if sdt != dt:
+                stream, x = x, x.to(dt)
         else:   # embedding-space inputs (scheduled sampling, models.py:463-470): add the position table, then pack
             x = input_seqs if input_seqs.dtype == dt else input_seqs.to(dt)
             x = F.mix_rows(x, pos=self.pos_embedding, period=T)
             x = F.pack_padded(x, tp.cu, tp.total)
         mem, mp = self._memory_packed(img_latent, latent_attention_mask, dt)
-        h = self.decoder_blocks.forward_packed(x, tp, mem, mp, causal=True)
+        h = self.decoder_blocks.forward_packed(x, tp, mem, mp, causal=True, stream=stream)
         logits = F.linear(h, self.unembed.weight, self.unembed.bias, out_dtype=dt)
         return F.unpack_padded(logits, tp.cu, B, T)
 
@@ -446,7 +450,7 @@ class OMRDecoder(nn.Module):
         if time_step >= self.max_lmx_seq_len:
             raise RuntimeError(f"{time_step + 1} decoding steps is too long for max sequence length of {self.max_lmx_seq_len}")
         dt = compute_dtype()
-        emb = ops.embed_tokens(token_t, self.vocab_embedding.weight, self.pos_embedding, dt, pos_offset=time_step)
+        emb = ops.embed_tokens(token_t, self.vocab_embedding.weight, self.pos_embedding, stream_dtype(dt), pos_offset=time_step)
         h = self.decoder_blocks.cached_generate(emb, memory_key_padding_mask=latent_attention_mask)
         return ops.linear(h, w_(self.unembed.weight, dt), self.unembed.bias, out_dtype=dt)
 

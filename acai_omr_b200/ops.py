@@ -385,14 +385,15 @@ def decode_attn_paged(q, new_kv, kv_rows, heads, head_dim, max_kv_len, workspace
     return out
 
 
-def decode_embed(seqs, step, table, pos, out_dtype):
+def decode_embed(seqs, step, table, pos, out_dtype, out2_dtype=None):
     _cuda(seqs, step, table, pos)
     B, dim = seqs.shape[0], table.shape[1]
     out = torch.empty((B, dim), dtype=out_dtype, device=seqs.device)
+    out2 = torch.empty((B, dim), dtype=out2_dtype, device=seqs.device) if out2_dtype is not None else None
     lib = _lib.load()
     _call("acai_decode_embed", lib.acai_decode_embed, _p(seqs), seqs.stride(0), _p(step), B, _p(_f32c(table)),
-          _p(_f32c(pos)), _p(out), _DT[out_dtype], dim, _stream())
-    return out
+          _p(_f32c(pos)), _p(out), _DT[out_dtype], _p(out2), _DT[out2_dtype] if out2 is not None else 0, dim, _stream())
+    return out if out2 is None else (out, out2)
 
 
 def greedy_update(logits, step, seqs, log_probs, finished, eos_idx):
@@ -546,10 +547,12 @@ def splitk_workspace(M, N, K, device):
     return _ws(_lib.load().acai_linear_splitk_workspace_bytes(int(M), int(N), int(K)), device)
 
 
-def linear_splitk(x, weight, bias=None, act=ACT_NONE, residual=None, ln=None, out_dtype=None, workspace=None):
+def linear_splitk(x, weight, bias=None, act=ACT_NONE, residual=None, ln=None, out_dtype=None, workspace=None,
+                  out2_dtype=None):
     """LayerNorm?(act(x @ weight.T + bias) + residual) for a SMALL number of rows (decode step): split-K tcgen05 GEMM +
     one reduce kernel (acai_linear_splitk).  `ln` = (gamma, beta, eps) or None.  Returns None when the problem does not
-    qualify (the caller runs linear [+ layernorm]).  `workspace` (uint8) is reused when large enough."""
+    qualify (the caller runs linear [+ layernorm]).  `workspace` (uint8) is reused when large enough.  With `out2_dtype`
+    the result is (out, out2): the same rows in a second dtype (fp32 residual stream + bf16 GEMM operand)."""
     _cuda(x, weight, bias, residual)
     if x.dim() != 2 or not _gemm_fusable(x, weight):
         return None
@@ -563,6 +566,7 @@ def linear_splitk(x, weight, bias=None, act=ACT_NONE, residual=None, ln=None, ou
         workspace = _ws(need, x.device)
     out_dtype = out_dtype or x.dtype
     out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    out2 = torch.empty((M, N), dtype=out2_dtype, device=x.device) if out2_dtype is not None else None
     r2, ldr, rdt = None, 0, 0
     if residual is not None:
         r2, rm, rn, ldr = _rows2d(residual)
@@ -573,11 +577,14 @@ def linear_splitk(x, weight, bias=None, act=ACT_NONE, residual=None, ln=None, ou
     name = "acai_linear_splitk" if Profile.active is None else \
         f"acai_linear_splitk[{M}x{N}x{K}{',gelu' if act else ''}{',res' if r2 is not None else ''}{',ln' if ln else ''}]"
     ok = _try_call(name, lib.acai_linear_splitk, _p(x), x.stride(0), _p(weight), weight.stride(0), _p(_f32c(bias)), _p(r2), rdt, ldr,
-                   _p(g), _p(b2), eps, _p(out), _DT[out_dtype], out.stride(0), M, N, K, act, _p(workspace), workspace.numel(),
+                   _p(g), _p(b2), eps, _p(out), _DT[out_dtype], out.stride(0), _p(out2),
+                   _DT[out2_dtype] if out2 is not None else 0, N, M, N, K, act, _p(workspace), workspace.numel(),
                    _stream(), flops=2.0 * M * N * K, nbytes=2.0 * (M * K + N * K + M * N))
     if ok:
         _bump()                   # two kernels: the split-K GEMM and the reduce
-    return out if ok else None
+    if not ok:
+        return None
+    return out if out2 is None else (out, out2)
 
 
 def linear_gelu_train(x, weight, bias, dropout_p=0.0, dropout_seed=0):

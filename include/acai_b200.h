@@ -117,12 +117,16 @@ int acai_linear_fwd(const void* a, int32_t a_dtype, int64_t lda,
  * partials still in L2 - sums them and applies bias, activation, residual and the LayerNorm (two-pass variance in fp32).
  * Returns ACAI_ERR_UNSUPPORTED, nothing written, when the problem does not qualify (operands not 16-byte aligned /
  * K % 64, M > 256, no K slices to gain, N % 4, or a LayerNorm row that is not a multiple of 128 <= 1024 columns): the
- * caller then runs acai_linear_fwd + acai_layernorm_fwd.  `workspace` holds acai_linear_splitk_workspace_bytes(M, N, K). */
+ * caller then runs acai_linear_fwd + acai_layernorm_fwd.  `workspace` holds acai_linear_splitk_workspace_bytes(M, N, K).
+ * `out2`: under torch.autocast the reference keeps the residual stream in fp32 (LayerNorm and the residual adds run in
+ * fp32, vitomr_inference.py:82-84) and only the Linear operands are bf16: out = fp32 row (the next residual), out2 = the
+ * same row in bf16 (the next GEMM's operand), written by the same reduce kernel. */
 size_t acai_linear_splitk_workspace_bytes(int32_t M, int32_t N, int32_t K);
 int acai_linear_splitk(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias,
                        const void* residual, int32_t res_dtype, int64_t ldr,
                        const float* ln_gamma, const float* ln_beta, float ln_eps,
                        void* out, int32_t out_dtype, int64_t ldo,
+                       void* out2, int32_t out2_dtype, int64_t ldo2,   /* optional second copy of the result (NULL: none) */
                        int32_t M, int32_t N, int32_t K, int32_t act,
                        void* workspace, size_t workspace_bytes, void* stream);
 
@@ -230,7 +234,8 @@ int acai_topk_sample_update(const void* logits, int32_t dtype, int64_t ld, int32
  *                       finished[b] |= (argmax == eos)
  *   acai_advance_step : *step_ptr += 1 */
 int acai_decode_embed(const int64_t* seqs, int64_t seq_stride, const int32_t* step_ptr, int32_t batch,
-                      const float* table, const float* pos, void* out, int32_t out_dtype, int32_t dim, void* stream);
+                      const float* table, const float* pos, void* out, int32_t out_dtype, void* out2, int32_t out2_dtype,
+                      int32_t dim, void* stream);                  /* out2: optional second copy (NULL: none) */
 int acai_greedy_update(const void* logits, int32_t dtype, int64_t ld, int32_t rows, int32_t vocab,
                        const int32_t* step_ptr, int64_t* seqs, int64_t seq_stride, float* log_probs,
                        uint8_t* finished, int32_t eos_idx, void* stream);

@@ -95,6 +95,24 @@ def test_splitk_linear_residual_layernorm(M, N, K, out_dtype):
     check_splitk(M, N, K, res_dtype=torch.bfloat16, ln=True, out_dtype=out_dtype)
 
 
+@pytest.mark.parametrize("M,N,K,ln", [(256, 1024, 1024, True), (37, 1024, 4096, True), (16, 1024, 1024, False), (100, 228, 1024, False)])
+def test_splitk_linear_second_output(M, N, K, ln):
+    """out (fp32 residual stream) + out2 (bf16 GEMM operand) from the same reduce kernel: out2 == out rounded once, and
+    out equals the single-output call bit for bit."""
+    x = rnd(M, K, seed=1).bfloat16()
+    w = rnd(N, K, seed=2, scale=K ** -0.5).bfloat16()
+    b, r = rnd(N, seed=3), rnd(M, N, seed=4)                      # fp32 residual
+    lnp = (1.0 + 0.1 * rnd(N, seed=7), 0.1 * rnd(N, seed=8), 1e-5) if ln else None
+    one = ops.linear_splitk(x, w, b, residual=r, ln=lnp, out_dtype=torch.float32)
+    two = ops.linear_splitk(x, w, b, residual=r, ln=lnp, out_dtype=torch.float32, out2_dtype=torch.bfloat16)
+    assert one is not None and two is not None
+    y, y2 = two
+    assert y.dtype == torch.float32 and y2.dtype == torch.bfloat16
+    assert torch.equal(y, one) and torch.equal(y2, one.bfloat16())
+    y32, y32b = ops.linear_splitk(x, w, b, residual=r, ln=lnp, out_dtype=torch.bfloat16, out2_dtype=torch.float32)
+    assert torch.equal(y32b, one) and torch.equal(y32, one.bfloat16())
+
+
 @pytest.mark.parametrize("act", [ops.ACT_NONE, ops.ACT_GELU])
 @pytest.mark.parametrize("res_dtype", [None, torch.float32, torch.bfloat16])
 def test_splitk_linear_plain(act, res_dtype):

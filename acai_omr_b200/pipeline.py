@@ -15,8 +15,9 @@ import torch
 
 
 class EncoderPipeline:
-    """`depth` pinned result slots; a yielded (latent, mask) pair stays valid until `depth` more results have been
-    yielded (copy it out if it has to live longer)."""
+    """`depth` batches in flight over `depth + 1` pinned result slots: a yielded (latent, mask) pair stays valid until the
+    NEXT result is yielded (the slot a new batch downloads into is the one whose result was handed out two yields ago);
+    copy it out if it has to live longer."""
 
     def __init__(self, encoder, device, depth=2, autocast_dtype=torch.bfloat16):
         if depth < 1:
@@ -24,7 +25,7 @@ class EncoderPipeline:
         self.encoder, self.device, self.depth, self.autocast_dtype = encoder, torch.device(device), depth, autocast_dtype
         self.h2d = torch.cuda.Stream(self.device)
         self.d2h = torch.cuda.Stream(self.device)
-        self._slots = [None] * depth
+        self._slots = [None] * (depth + 1)
 
     def _host_buffers(self, slot, out, mask):
         cur = self._slots[slot]
@@ -64,7 +65,7 @@ class EncoderPipeline:
             done.record(compute)
             if len(pending) == self.depth:                                 # frees the slot this batch is about to use
                 yield self._finish(pending.popleft())
-            out_host, mask_host = self._host_buffers(i % self.depth, out, mask)
+            out_host, mask_host = self._host_buffers(i % (self.depth + 1), out, mask)
             with torch.cuda.stream(self.d2h):
                 self.d2h.wait_event(done)
                 out_host.copy_(out, non_blocking=True)

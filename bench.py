@@ -406,7 +406,7 @@ def run_decode(args, rank, world, device):
         e2e_tokens = B * (out_host[0].shape[1] - 1)
         e2e_d2h = sum(h_.numel() * h_.element_size() for h_ in out_host)
         # the dominant kernel alone (cross-attention over the 1 GB memory cache of one layer), CUDA events per launch
-        qc = torch.randn(B, DEC_D, device=device, generator=g).bfloat16()
+        qc = torch.randn(B, DEC_D, generator=g).bfloat16().to(device)
         reps, kern_ms = 20, 0.0
         for i in range(reps + 3):
             k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

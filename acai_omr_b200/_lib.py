@@ -61,7 +61,7 @@ SIGNATURES = {
     "acai_linear_dropout": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],
     "acai_layernorm_bwd_workspace_bytes": [_i32, _i32],
     "acai_layernorm_bwd": [_p, _i32, _p, _i32, _p, _i32, _p, _f32, _p, _i32, _p, _p, _i32, _i32, _i32, _p, _sz, _p],
-    "acai_ce_loss": [_p, _i32, _i64, _p, _i32, _i32, _i32, _p, _p, _p, _p, _i32, _i64, _p, _p],
+    "acai_ce_loss": [_p, _i32, _i64, _p, _i32, _i32, _i32, _p, _p, _p, _p, _i32, _i64, _p, _f32, _p],
     "acai_scatter_add_rows": [_p, _i32, _i64, _p, _i32, _i32, _p, _f32, _p],
     "acai_gather_rows": [_p, _i32, _p, _i32, _i32, _p, _i32, _p],
     "acai_mae_loss_bwd": [_p, _i32, _p, _p, _i32, _i32, _p, _p, _i32, _p],

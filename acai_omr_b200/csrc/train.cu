@@ -414,13 +414,15 @@ layernorm_bwd_vec_kernel(const void* __restrict__ dy, int dy_dt, const void* __r
   }
 }
 
-// Cross-entropy with ignore_index (OMRCELoss, models.py:784-796), one warp per row:
-//   row_loss = logsumexp(z) - z[target]   (0 for ignored rows);  dlogits = softmax(z) - onehot(target)  (0 for ignored rows)
+// Cross-entropy with ignore_index and label smoothing e (OMRCELoss, models.py:784-796 = nn.CrossEntropyLoss(ignore_index,
+// label_smoothing)), one warp per row, with q = (1 - e) onehot(target) + e / V:
+//   row_loss = -sum_c q_c log softmax(z)_c = lse - (1 - e) z[target] - (e / V) sum_c z_c   (0 for ignored rows)
+//   dlogits  = softmax(z) - q                                                             (0 for ignored rows)
 // dlogits is scaled by *scale_ptr (= upstream gradient / count, a device scalar).  `valid[row]` = 1 for counted rows.
 __global__ void ce_fwd_bwd_kernel(const void* __restrict__ logits, int dt, int64_t ld, const int64_t* __restrict__ targets,
                                   int rows, int vocab, int ignore_index, float* __restrict__ row_loss,
                                   uint8_t* __restrict__ valid, void* __restrict__ dlogits, int dl_dt, int64_t ldd,
-                                  const float* __restrict__ scale_ptr) {
+                                  const float* __restrict__ scale_ptr, float smoothing) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= rows) return;
   const int64_t tgt = targets[row];
@@ -428,19 +430,30 @@ __global__ void ce_fwd_bwd_kernel(const void* __restrict__ logits, int dt, int64
   float mx = -INFINITY;
   for (int c = lane; c < vocab; c += 32) mx = fmaxf(mx, ld_as_float(logits, (int64_t)row * ld + c, dt));
   mx = warp_max(mx);
-  float s = 0.0f;
-  for (int c = lane; c < vocab; c += 32) s += expf(ld_as_float(logits, (int64_t)row * ld + c, dt) - mx);
+  float s = 0.0f, zsum = 0.0f;
+  for (int c = lane; c < vocab; c += 32) {
+    const float z = ld_as_float(logits, (int64_t)row * ld + c, dt);
+    s += expf(z - mx);
+    zsum += z;
+  }
   s = warp_sum(s);
   const float lse = mx + logf(s);
+  const float uni = smoothing / (float)vocab;
+  if (smoothing != 0.0f) zsum = warp_sum(zsum);
   if (lane == 0 && row_loss) {
-    row_loss[row] = ok ? lse - ld_as_float(logits, (int64_t)row * ld + tgt, dt) : 0.0f;
+    float l = 0.0f;
+    if (ok) {
+      l = lse - ld_as_float(logits, (int64_t)row * ld + tgt, dt);
+      if (smoothing != 0.0f) l = (1.0f - smoothing) * l + uni * ((float)vocab * lse - zsum);
+    }
+    row_loss[row] = l;
     valid[row] = ok ? 1 : 0;
   }
   if (dlogits) {
     const float sc = *scale_ptr;
     for (int c = lane; c < vocab; c += 32) {
       float g = 0.0f;
-      if (ok) g = sc * (expf(ld_as_float(logits, (int64_t)row * ld + c, dt) - lse) - (c == tgt ? 1.0f : 0.0f));
+      if (ok) g = sc * (expf(ld_as_float(logits, (int64_t)row * ld + c, dt) - lse) - (c == tgt ? 1.0f - smoothing : 0.0f) - uni);
       st_from_float(dlogits, (int64_t)row * ldd + c, dl_dt, g);
     }
   }
@@ -664,12 +677,14 @@ extern "C" int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* 
 
 extern "C" int acai_ce_loss(const void* logits, int32_t dtype, int64_t ld, const int64_t* targets, int32_t rows,
                             int32_t vocab, int32_t ignore_index, float* row_loss, uint8_t* valid, float* sums,
-                            void* dlogits, int32_t dlogits_dtype, int64_t ldd, const float* scale, void* stream) {
+                            void* dlogits, int32_t dlogits_dtype, int64_t ldd, const float* scale, float label_smoothing,
+                            void* stream) {
   ACAI_CHECK_ARG(logits && targets && rows > 0 && vocab > 0 && dtype_valid(dtype), "acai_ce_loss: bad argument");
+  ACAI_CHECK_ARG(label_smoothing >= 0.0f && label_smoothing <= 1.0f, "acai_ce_loss: label_smoothing %f outside [0, 1]", label_smoothing);
   ACAI_CHECK_ARG((row_loss && valid && sums) || (dlogits && scale && dtype_valid(dlogits_dtype)), "acai_ce_loss: nothing to compute");
   cudaStream_t st = (cudaStream_t)stream;
   ce_fwd_bwd_kernel<<<(rows + 3) / 4, 128, 0, st>>>(logits, dtype, ld, targets, rows, vocab, ignore_index, row_loss, valid,
-                                                    dlogits, dlogits_dtype, ldd, scale);
+                                                    dlogits, dlogits_dtype, ldd, scale, label_smoothing);
   int rc = launch_status("ce_loss");
   if (rc || !row_loss) return rc;
   masked_sum_kernel<<<1, 1024, 0, st>>>(row_loss, valid, rows, sums);

@@ -524,14 +524,14 @@ def mae_restore(latent, cu_keep, cu_full, ids_restore, wps, total_rows, mask_tok
 
 # ------------------------------------------------------------------------------------------ losses
 class _CELoss(torch.autograd.Function):
-    """OMRCELoss (models.py:784-796), label_smoothing 0: mean over non-pad targets of -log softmax(logits)[target]."""
+    """OMRCELoss (models.py:784-796): mean over non-pad targets of the (label-smoothed) cross entropy."""
 
     @staticmethod
-    def forward(ctx, logits, targets, ignore_index, normaliser):
-        sums = ops.ce_loss(logits, targets, ignore_index)
+    def forward(ctx, logits, targets, ignore_index, normaliser, label_smoothing):
+        sums = ops.ce_loss(logits, targets, ignore_index, label_smoothing=label_smoothing)
         denom = sums[1] if normaliser is None else normaliser
         ctx.save_for_backward(logits, targets, denom)
-        ctx.ignore_index = ignore_index
+        ctx.ignore_index, ctx.label_smoothing = ignore_index, label_smoothing
         ctx.mark_non_differentiable(sums)
         return sums[0] / denom, sums
 
@@ -539,16 +539,17 @@ class _CELoss(torch.autograd.Function):
     def backward(ctx, g, _gs):
         logits, targets, denom = ctx.saved_tensors
         scale = (g.float() / denom).reshape(1).contiguous()
-        return ops.ce_loss(logits, targets, ctx.ignore_index, dlogits_scale=scale, dlogits_dtype=logits.dtype), None, None, None
+        return (ops.ce_loss(logits, targets, ctx.ignore_index, dlogits_scale=scale, dlogits_dtype=logits.dtype,
+                            label_smoothing=ctx.label_smoothing), None, None, None, None)
 
 
-def ce_loss(logits, targets, ignore_index, normaliser=None):
+def ce_loss(logits, targets, ignore_index, normaliser=None, label_smoothing=0.0):
     """-> (loss, sums = [sum of token losses, token count]).  `normaliser` (1-element device tensor) replaces the local
     count, e.g. the global token count divided by the world size under data parallelism."""
     if not needs_grad(logits):
-        sums = ops.ce_loss(logits, targets, ignore_index)
+        sums = ops.ce_loss(logits, targets, ignore_index, label_smoothing=label_smoothing)
         return sums[0] / (sums[1] if normaliser is None else normaliser), sums
-    return _CELoss.apply(logits, targets, ignore_index, normaliser)
+    return _CELoss.apply(logits, targets, ignore_index, normaliser, float(label_smoothing))
 
 
 class _MAELoss(torch.autograd.Function):

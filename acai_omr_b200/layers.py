@@ -223,15 +223,33 @@ class Packed:
         m = torch.arange(L)[None, :] >= torch.tensor(self.lens)[:, None]
         m = ops.upload_small(m, device)
         m._acai_lens = self.lens  # lets downstream modules re-pack without a device sync
+        m._acai_lens_version = m._version
         return m
+
+
+def attach_packed(t, packed):
+    """Remember the packed rows a padded tensor was made from.  The note is honoured only while `t` has not been written
+    to since (`Tensor._version`): after `t.mul_()`, `t[i] = ...` the consumer re-packs from the tensor's contents, as the
+    reference - which only ever sees the padded tensor - would."""
+    t._acai_packed = (t._version, packed)
+
+
+def attached_packed(t):
+    note = getattr(t, "_acai_packed", None)
+    if note is None or note[0] != t._version:
+        return None
+    return note[1]
 
 
 def lens_from_mask(mask, batch, length):
     """Host lengths from a (B, L) True=padding mask.  Uses the lengths attached by `Packed.mask`
-    when present; otherwise reads the mask back (one sync) and requires suffix-only padding."""
+    when present (and the mask has not been edited since); otherwise reads the mask back (one sync) and requires
+    suffix-only padding."""
     if mask is None:
         return [length] * batch
     lens = getattr(mask, "_acai_lens", None)
+    if lens is not None and getattr(mask, "_acai_lens_version", mask._version) != mask._version:
+        lens = None                                          # written in place since: read the contents
     if lens is not None and len(lens) == batch and mask.shape[1] == length:
         return list(lens)
     m = mask.bool()
@@ -374,6 +392,26 @@ class TransformerDecoderLayer(nn.Module):
         return x if single else (x, xb)
 
 
+class _Replayable:
+    """fn for torch.utils.checkpoint: the first call (the forward) notes the dropout seed counter it starts from and lets it
+    advance as usual; every later call (the re-run inside the backward) rewinds the counter to that value for its duration,
+    so that it regenerates the first run's masks and leaves the seeds drawn around it alone."""
+
+    def __init__(self, fn):
+        self.fn, self.start = fn, None
+
+    def __call__(self, *args):
+        if self.start is None:
+            self.start = ops.DropoutState.counter
+            return self.fn(*args)
+        saved = ops.DropoutState.counter
+        ops.DropoutState.counter = self.start
+        try:
+            return self.fn(*args)
+        finally:
+            ops.DropoutState.counter = saved
+
+
 class TransformerDecoder(nn.Module):
     """nn.TransformerDecoder-shaped container (models.py:422-426)."""
 
@@ -385,9 +423,18 @@ class TransformerDecoder(nn.Module):
         for layer in self.layers[1:]:
             layer.load_state_dict(self.layers[0].state_dict())
 
-    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True, final_dtype=None, stream=None):
+    def forward_packed(self, x, tgt: Packed, mem, mem_pk: Packed, causal=True, final_dtype=None, stream=None, checkpoint=False):
         """x: operand rows (compute dtype); `stream`: the same rows before they were rounded to it (fp32 embedding sum), if
-        the caller has them."""
+        the caller has them.  `checkpoint` (OMRDecoder.forward(checkpoint_grads=True), models.py:470-478): per-layer
+        activation checkpointing - only each layer's input is kept for the backward and the layer is run again there, with
+        the same dropout masks (the seed counter is rewound to the value the first run started from)."""
+        if checkpoint and torch.is_grad_enabled() and x.requires_grad:
+            from torch.utils.checkpoint import checkpoint as ckpt
+            for layer in self.layers:
+                x = ckpt(_Replayable(layer.forward_packed), x, tgt, mem, mem_pk, causal, use_reentrant=False)
+            if self.norm is not None:
+                x = self.norm(x, out_dtype=final_dtype or x.dtype)
+            return x
         if stream is not None and stream_dtype(x.dtype) == stream.dtype:
             xb = x
             x = stream

@@ -18,7 +18,8 @@ from .. import functional as F
 from .. import ops
 from ..config import LMX_BOS_TOKEN, LMX_EOS_TOKEN, LMX_PAD_TOKEN
 from ..layers import (LayerNorm, Linear, Packed, TransformerDecoder, TransformerDecoderLayer, TransformerEncoder,
-                      TransformerEncoderLayer, compute_dtype, gelu_mlp_head, lens_from_mask, stream_dtype, to_stream, w_)
+                      TransformerEncoderLayer, attach_packed, attached_packed, compute_dtype, gelu_mlp_head, lens_from_mask,
+                      stream_dtype, to_stream, w_)
 from .kv_caching import CachedTransformerDecoder, CachedTransformerDecoderLayer
 
 NUM_CHANNELS = 1  # models.py:11
@@ -119,7 +120,7 @@ class Encoder(nn.Module):
         h, pk = self.encode_packed(x)
         out = F.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
         mask = pk.mask(out.device)
-        out._acai_packed = (h, pk)  # lets ViTOMR feed the decoder without re-packing
+        attach_packed(out, (h, pk))  # lets ViTOMR feed the decoder without re-packing (dropped if `out` is edited in place)
         return out, mask
 
     def embed_single_image(self, x):
@@ -154,6 +155,18 @@ class MAEEncoder(Encoder):
         seq_mask = torch.ones(seq_len, device=device, dtype=torch.int)
         seq_mask[:len_keep] = 0
         return ids_shuffle[:len_keep], ids_restore, seq_mask.index_select(0, ids_restore), len_keep
+
+    def mask_sequence(self, t, h_p, w_p, noise=None):
+        """models.py:106-125: shuffle + mask one unfolded image t (1, C*P*P, L) -> (t_masked (1, C*P*P, L_keep),
+        pos_embed_slice (L_keep, E), unmasked_seq_len, len_keep, seq_mask (L,) int, ids_restore (L,)).  Index bookkeeping
+        only (the packed forward path gathers the kept patches inside the patch-embedding kernel instead); `noise`
+        replaces the torch.rand draw."""
+        unmasked_seq_len = t.shape[-1]
+        ids_keep, ids_restore, seq_mask, len_keep = self.mask_indices(unmasked_seq_len, t.device, noise)
+        t_masked = t.index_select(dim=-1, index=ids_keep)
+        pos_embed_slice = self.pos_embedding[:h_p, :w_p, :].reshape(-1, self.hidden_dim).index_select(dim=0, index=ids_keep.to(
+            self.pos_embedding.device))
+        return t_masked, pos_embed_slice, unmasked_seq_len, len_keep, seq_mask, ids_restore
 
     def embed_masked_packed(self, x, noises=None):
         """-> (packed kept-patch embeddings, Packed(kept), info dict for the decoder side)."""
@@ -206,7 +219,7 @@ class MAEEncoder(Encoder):
         """models.py:176-180."""
         h, pk, info = self.encode_masked_packed(x, noises)
         out = F.unpack_padded(h, pk.cu, pk.batch, pk.max_len, fill=self._pad_fill())
-        out._acai_packed = (h, pk, info)
+        attach_packed(out, (h, pk, info))
         full = Packed(info["unmasked_seq_lens"], out.device)
         return (out, full.mask(out.device), info["kept_seq_lens"], info["unmasked_seq_lens"],
                 torch.nested.as_nested_tensor(info["seq_masks"], layout=torch.jagged),
@@ -333,7 +346,7 @@ class TransitionHead(nn.Sequential):
 
     def forward(self, x):
         p = self[2].p if self.training else 0.0
-        packed = getattr(x, "_acai_packed", None)
+        packed = attached_packed(x)
         if packed is None:
             return gelu_mlp_head(x, self[0], self[3], dropout_p=p)
         # came straight from the encoder: run on the packed rows of valid patches only and re-pad with zeros
@@ -341,7 +354,7 @@ class TransitionHead(nn.Sequential):
         h, pk = packed
         hp = gelu_mlp_head(h, self[0], self[3], dropout_p=p)
         out = F.unpack_padded(hp, pk.cu, pk.batch, x.shape[1])
-        out._acai_packed = (hp, pk)
+        attach_packed(out, (hp, pk))
         return out
 
 
@@ -390,7 +403,7 @@ class OMRDecoder(nn.Module):
 
     # ---- teacher-forced / uncached -----------------------------------------------------------
     def _memory_packed(self, img_latent, latent_attention_mask, dt):
-        packed = getattr(img_latent, "_acai_packed", None)
+        packed = attached_packed(img_latent)
         B, S = img_latent.shape[0], img_latent.shape[1]
         lens = lens_from_mask(latent_attention_mask, B, S)
         if packed is not None and packed[1].lens == lens:
@@ -399,7 +412,7 @@ class OMRDecoder(nn.Module):
         mp = Packed(lens, img_latent.device)
         return F.pack_padded(img_latent, mp.cu, mp.total, out_dtype=dt), mp
 
-    def _decode_packed(self, input_seqs, img_latent, tgt_lens, latent_attention_mask, token_idxs_input):
+    def _decode_packed(self, input_seqs, img_latent, tgt_lens, latent_attention_mask, token_idxs_input, checkpoint_grads=False):
         B, T = input_seqs.shape[0], input_seqs.shape[1]
         dt = compute_dtype()
         dev = self.pos_embedding.device
@@ -417,7 +430,7 @@ class OMRDecoder(nn.Module):
             x = F.mix_rows(x, pos=self.pos_embedding, period=T)
             x = F.pack_padded(x, tp.cu, tp.total)
         mem, mp = self._memory_packed(img_latent, latent_attention_mask, dt)
-        h = self.decoder_blocks.forward_packed(x, tp, mem, mp, causal=True, stream=stream)
+        h = self.decoder_blocks.forward_packed(x, tp, mem, mp, causal=True, stream=stream, checkpoint=checkpoint_grads)
         logits = F.linear(h, self.unembed.weight, self.unembed.bias, out_dtype=dt)
         return F.unpack_padded(logits, tp.cu, B, T)
 
@@ -429,7 +442,8 @@ class OMRDecoder(nn.Module):
         if T > self.max_lmx_seq_len:
             raise ValueError(f"{T} long lmx sequence length is too long for max sequence length of {self.max_lmx_seq_len}")
         lens = lens_from_mask(lmx_attention_mask, input_seqs.shape[0], T)
-        return self._decode_packed(input_seqs, img_latent, lens, latent_attention_mask, token_idxs_input)
+        return self._decode_packed(input_seqs, img_latent, lens, latent_attention_mask, token_idxs_input,
+                                   checkpoint_grads=checkpoint_grads)
 
     def generate(self, input_seqs, img_latent, latent_attention_mask=None):
         """models.py:487-500."""
@@ -609,7 +623,10 @@ class TeacherForcedViTOMR(ViTOMR):
         img_latent, latent_attention_mask = self.encoder(imgs)
         hook = getattr(self, "_acai_latent_hook", None)       # train.teacher_forced_step: gradient all-reduce overlap
         if hook is not None:
-            hook(img_latent)
+            # the gradient reaches the encoder through the PACKED rows the transition head consumes (the padded tensor is a
+            # dead end of the tape when its packed note is used), so that is where the hook belongs
+            packed = attached_packed(img_latent)
+            hook(packed[0] if packed is not None else img_latent)
         img_latent = self.transition_head(img_latent)
         input_seqs, target_seqs, lmx_attention_mask = batchify_and_split_lmx_seqs(lmx_seqs, self.decoder.pad_idx,
                                                                                   img_latent.device)
@@ -617,6 +634,13 @@ class TeacherForcedViTOMR(ViTOMR):
         lmx_attention_mask._acai_lens = [min(int(s.shape[0]), T) for s in lmx_seqs]
         pred = self.decoder(input_seqs, img_latent, lmx_attention_mask, latent_attention_mask)
         return pred, target_seqs
+
+    def generate(self, img_latent, seqs):
+        """models.py:749-757: next-token log-distribution (num_seqs, vocab) for `seqs` (num_seqs, T) that all continue the
+        one image whose latent (1, S, E) is given (beam-search style expansion)."""
+        img_latent = img_latent.expand(seqs.shape[0], -1, -1)
+        logits = self.decoder.generate(seqs, img_latent)
+        return torch.log_softmax(logits[:, -1, :].float(), dim=-1).to(logits.dtype)
 
     def create_fine_tune_param_groups(self, base_lr, fine_tune_base_lr, fine_tune_decay_factor):
         """models.py:761-781."""
@@ -797,13 +821,10 @@ class OMRCELoss(nn.Module):
 
     def __init__(self, pad_idx, label_smoothing=0.0):
         super().__init__()
-        if label_smoothing != 0.0:
-            raise NotImplementedError("label_smoothing != 0 is not implemented (the reference trains with 0.0, "
-                                      "omr_teacher_force_train.py:48)")
-        self.pad_idx, self.label_smoothing = pad_idx, label_smoothing
+        self.pad_idx, self.label_smoothing = pad_idx, float(label_smoothing)
 
     def forward(self, pred, target_seqs):
-        return F.ce_loss(pred, target_seqs.to(pred.device), self.pad_idx)[0]
+        return F.ce_loss(pred, target_seqs.to(pred.device), self.pad_idx, label_smoothing=self.label_smoothing)[0]
 
 
 def default_vocab_path():

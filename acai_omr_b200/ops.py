@@ -724,9 +724,10 @@ def attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, max_q, max_k, heads, he
     _bump(2)
 
 
-def ce_loss(logits, targets, ignore_index, dlogits_scale=None, dlogits_dtype=None):
+def ce_loss(logits, targets, ignore_index, dlogits_scale=None, dlogits_dtype=None, label_smoothing=0.0):
     """OMRCELoss pieces (acai_ce_loss).  Forward (dlogits_scale None): returns sums[2] = {sum, count}.
-    Backward (dlogits_scale = 1-element fp32 device tensor): returns dlogits = scale * (softmax - onehot)."""
+    Backward (dlogits_scale = 1-element fp32 device tensor): returns dlogits = scale * (softmax - q), q the smoothed
+    target distribution."""
     _cuda(logits, targets, dlogits_scale)
     V = logits.shape[-1]
     l2 = logits.reshape(-1, V)
@@ -740,12 +741,12 @@ def ce_loss(logits, targets, ignore_index, dlogits_scale=None, dlogits_dtype=Non
         valid = torch.empty(rows, dtype=torch.uint8, device=logits.device)
         sums = torch.empty(2, dtype=torch.float32, device=logits.device)
         _call("acai_ce_loss", lib.acai_ce_loss, _p(l2), _dt(l2), l2.stride(0), _p(t), rows, V, int(ignore_index), _p(row_loss),
-              _p(valid), _p(sums), None, 0, 0, None, _stream())
+              _p(valid), _p(sums), None, 0, 0, None, float(label_smoothing), _stream())
         _bump()
         return sums
     dl = torch.empty((rows, V), dtype=dlogits_dtype or logits.dtype, device=logits.device)
     _call("acai_ce_loss", lib.acai_ce_loss, _p(l2), _dt(l2), l2.stride(0), _p(t), rows, V, int(ignore_index), None, None, None,
-          _p(dl), _dt(dl), V, _p(dlogits_scale), _stream())
+          _p(dl), _dt(dl), V, _p(dlogits_scale), float(label_smoothing), _stream())
     return dl.view(logits.shape)
 
 

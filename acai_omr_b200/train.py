@@ -103,6 +103,7 @@ class FlatTrainer:
                 p.grad = self.flat_grad[o:o + p.numel()].view(p.shape)
                 p._acai_grad_owned = True      # backward GEMMs accumulate into .grad directly (functional._owned_grad)
         self._works, self._reduced = [], []      # gradient all-reduces in flight / flat ranges they cover (this step)
+        self.overlapped_elements = 0
         self.shadow = None
         if shadow_dtype is not None:
             self.shadow = self.flat_param.to(shadow_dtype)
@@ -135,6 +136,7 @@ class FlatTrainer:
                 self._works.append(dist.all_reduce(self.flat_grad[a:b], group=self.group, async_op=True))
             for w in self._works:
                 w.wait()
+        self.overlapped_elements = sum(b - a for a, b in self._reduced)     # what went out before the backward had finished
         self._works, self._reduced = [], []
 
     def allreduce_ready(self, params):

@@ -288,8 +288,9 @@ int acai_mae_loss_fwd(const void* pred, int32_t pred_dtype, const float* target,
  *   acai_colsum    : out[c] (+)= sum_r x[r, c] in a fixed order (bias gradients)
  *   acai_gelu_fwd / acai_gelu_bwd : exact-erf GELU on a saved pre-activation (training keeps z)
  *   acai_layernorm_bwd : dv for v = x + residual, dgamma / dbeta (+)= column reductions (fixed order)
- *   acai_ce_loss   : OMRCELoss (models.py:784-796): row_loss / valid / sums = {sum, count} and/or
- *                    dlogits = *scale * (softmax - onehot) for non-ignored rows
+ *   acai_ce_loss   : OMRCELoss (models.py:784-796 = nn.CrossEntropyLoss(ignore_index, label_smoothing)): with
+ *                    q = (1 - label_smoothing) onehot + label_smoothing / vocab, row_loss = -sum_c q_c log softmax_c,
+ *                    valid, sums = {sum, count} and/or dlogits = *scale * (softmax - q) for non-ignored rows
  *   acai_scatter_add_rows / acai_gather_rows : embedding, position-table and MAE-restore gradients
  *   acai_mae_loss_bwd : dpred = mask * *scale * 2 (pred - normalised target) / feats */
 int acai_transpose(const void* in, int32_t dtype, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,
@@ -321,7 +322,7 @@ int acai_layernorm_bwd(const void* dy, int32_t dy_dtype, const void* x, int32_t 
                        void* workspace, size_t workspace_bytes, void* stream);
 int acai_ce_loss(const void* logits, int32_t dtype, int64_t ld, const int64_t* targets, int32_t rows, int32_t vocab,
                  int32_t ignore_index, float* row_loss, uint8_t* valid, float* sums,
-                 void* dlogits, int32_t dlogits_dtype, int64_t ldd, const float* scale, void* stream);
+                 void* dlogits, int32_t dlogits_dtype, int64_t ldd, const float* scale, float label_smoothing, void* stream);
 int acai_scatter_add_rows(const void* src, int32_t dtype, int64_t ld, const int64_t* index, int32_t rows, int32_t dim,
                           float* dst, float scale, void* stream);
 int acai_gather_rows(const void* src, int32_t dtype, const int64_t* index, int32_t rows, int32_t dim, void* out,

@@ -28,17 +28,21 @@ batch = list(zip(imgs, [synth.synth_lmx(L, 10 * rank + i).to(dev) for i, L in en
 tr.step = lambda: None                                     # keep the parameters fixed: compare gradients only
 train.teacher_forced_step(vit, batch, tr)                  # overlapped
 g_overlap = tr.flat_grad.clone()
+overlapped = tr.overlapped_elements
+assert overlapped > 0, "the gradient-ready hook never fired: nothing was reduced under the backward"
 n_ranges = None
 orig = tr.grad_ready_hook
 tr.grad_ready_hook = lambda t, mods: None                  # no hook: allreduce_gradients reduces [0, numel) in one collective
 train.teacher_forced_step(vit, batch, tr)
 g_plain = tr.flat_grad.clone()
+assert tr.overlapped_elements == 0
 tr.grad_ready_hook = orig
 err = float((g_overlap - g_plain).abs().max() / g_plain.abs().max())
 both = [torch.zeros_like(g_plain) for _ in range(2)]
 dist.all_gather(both, g_plain)
 same = bool(torch.equal(both[0], both[1]))
 if rank == 0:
-    print(f"overlap vs single all-reduce: rel max diff {err:.2e}; ranks hold the same reduced buffer: {same}; |g|max {float(g_plain.abs().max()):.3e}")
+    print(f"{overlapped} of {tr.numel} gradient elements were reduced under the backward; "
+          f"overlap vs single all-reduce: rel max diff {err:.2e}; ranks hold the same reduced buffer: {same}; |g|max {float(g_plain.abs().max()):.3e}")
 assert err < 1e-4 and same
 dist.destroy_process_group()

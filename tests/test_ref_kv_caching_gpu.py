@@ -141,3 +141,32 @@ def test_omr_decoder_with_caching():
     with pytest.raises(RuntimeError):
         for t in range(16):
             cac.cached_generate(torch.randint(0, 227, (B, 1)).to(DEV), t, latent_attention_mask=mask.to(DEV))
+
+
+def test_cached_decoder_layer():
+    """reference tests/test_kv_caching.py:113-184: CachedTransformerDecoderLayer.cached_forward, token by token, against
+    the uncached layer on the whole sequence with a causal mask - without and with a memory padding mask, a fresh KVCache
+    per batch.  The "stock torch" side is the CPU oracle's post-norm decoder layer on the same weights."""
+    layer = CachedTransformerDecoderLayer(**LAYER_KW).to(DEV).eval()
+    D, H, d, B, S, T = 12, 2, 6, 2, 8, 3
+    sd = cpu_sd(layer, "l.")
+    latent = torch.rand(B, S, D)
+    mc = MemoryCache()
+    mc.cache_memory_keys_and_vals(latent.to(DEV), layer)
+    cached_kv_mem = mc.get_cached_keys_and_vals()
+    assert cached_kv_mem[0].shape == (B, H, S, d)
+    latent_mask = torch.full([B, S], False)
+    latent_mask[0, 6:] = True
+    latent_mask[1, 3:] = True
+    for mask in (None, latent_mask):
+        cache = KVCache(B, 200, H, d, dtype=torch.float).to(DEV)         # "have to initialize fresh KV caches between batches"
+        full, out = torch.empty(B, T, D), torch.empty(B, T, D)
+        for t in range(T):
+            tok = torch.rand(B, 1, D)
+            full[:, t] = tok.squeeze(1)
+            x = layer.cached_forward(tok.to(DEV), cache, cached_kv_mem,
+                                     memory_key_padding_mask=None if mask is None else mask.to(DEV))
+            assert x.shape == (B, 1, D) and cache.size == t + 1
+            out[:, t] = x.squeeze(1).cpu()
+        ref = O.decoder_layer(full, latent, sd, "l.", H, True, None, mask)
+        assert torch.allclose(out, ref, **TOL)

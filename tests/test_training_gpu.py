@@ -156,6 +156,27 @@ def test_ce_loss_fwd_bwd(dtype, tol):
     assert abs(float(loss_g) - float(sums[0]) / 10.0) < 1e-5 * abs(float(loss_g))
 
 
+@pytest.mark.parametrize("eps", [0.1, 0.3])
+def test_ce_loss_label_smoothing(eps):
+    """OMRCELoss(pad_idx, label_smoothing) = nn.CrossEntropyLoss(ignore_index, label_smoothing) (models.py:785-788)."""
+    from acai_omr_b200.models import models as M
+    B, T, V, pad = 3, 17, 227, 1
+    logits = rnd(B, T, V, seed=21, scale=2.0).requires_grad_(True)
+    g = torch.Generator().manual_seed(22)
+    tgt = torch.randint(0, V, (B, T), generator=g)
+    tgt[1, 9:] = pad
+    tgt = tgt.to(DEV)
+    loss = M.OMRCELoss(pad, label_smoothing=eps)(logits, tgt)
+    (loss * 0.7).backward()
+    lr = logits.detach().clone().requires_grad_(True)
+    ref = torch.nn.CrossEntropyLoss(ignore_index=pad, label_smoothing=eps)(lr.reshape(-1, V), tgt.reshape(-1))
+    (ref * 0.7).backward()
+    assert abs(float(loss.detach()) - float(ref.detach())) < 1e-5 * abs(float(ref.detach()))
+    assert torch.allclose(logits.grad, lr.grad, atol=1e-7, rtol=1e-4)
+    with torch.no_grad():                                   # the no-autograd path
+        assert abs(float(M.OMRCELoss(pad, eps)(logits.detach(), tgt)) - float(ref.detach())) < 1e-5 * abs(float(ref.detach()))
+
+
 def test_scatter_gather_rows():
     src = rnd(300, 48, seed=16)
     g = torch.Generator().manual_seed(17)

@@ -45,6 +45,7 @@ SIGNATURES = {
     "acai_patch_embed_workspace_bytes": [_i32, _i32, _i32, _i32],
     "acai_patch_embed_fwd": [_p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _i32, _i32, _p, _sz, _p],
     "acai_linear_fwd": [_p, _i32, _i64, _p, _i32, _i64, _p, _p, _i32, _i64, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p],
+    "acai_linear_layernorm": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _p, _f32, _p, _i64, _p, _i64, _i32, _i32, _i32, _p],
     "acai_layernorm_fwd": [_p, _i32, _p, _i32, _p, _p, _f32, _p, _i32, _p, _i32, _i32, _i32, _p],
     "acai_attn_varlen_fwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32,
                              _i64, _p, _f32, _u64, _p],

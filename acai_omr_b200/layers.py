@@ -59,6 +59,26 @@ def norm_pair(norm, y, dt):
     return x, x
 
 
+def linear_residual_norm(a, lin, residual, norm, dt, dropout_p=0.0):
+    """norm(residual + dropout(lin(a))) -> (stream rows, GEMM operand rows): the tail of a post-norm sub-layer.  Inference in
+    bf16 runs it as ONE kernel (acai_linear_layernorm: the LayerNorm in the GEMM's epilogue across a thread-block cluster);
+    otherwise the projection (+ residual in its epilogue) and the LayerNorm are two launches."""
+    if (dropout_p == 0.0 and dt == torch.bfloat16 and a.dtype == dt and a.dim() == 2 and lin.bias is not None
+            and not F.needs_grad(a, residual, lin.weight, lin.bias, norm.weight, norm.bias)):
+        fused = ops.linear_layernorm(a, w_(lin.weight, dt), lin.bias, residual, norm.weight, norm.bias, norm.eps,
+                                     want_f32=residual.dtype == torch.float32)
+        if fused is not None:
+            xb, x32 = fused
+            return (xb, xb) if x32 is None else (x32, xb)
+    y = F.linear(a, lin.weight, lin.bias, residual=residual, out_dtype=residual.dtype, dropout_p=dropout_p)
+    return norm_pair(norm, y, dt)
+
+
+def _can_fuse_tail(layer, x, dt):
+    return (ops.FUSE_LINEAR_LN and dt == torch.bfloat16 and not (layer.training and layer.dropout_p > 0.0)
+            and not torch.is_grad_enabled() and x.dim() == 2)
+
+
 class _WeightCache:
     """bf16 copies of fp32 master parameters, refreshed when the parameter is updated in place."""
 
@@ -182,25 +202,30 @@ class MultiheadAttention(nn.Module):
         return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual,
                         out_dtype=dt if residual is None else residual.dtype, dropout_p=p)
 
-    def self_attention_packed(self, x, pk, causal, residual):
-        """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D] (x: GEMM operand rows, residual: stream rows)."""
+    def self_attention_core(self, x, pk, causal):
+        """softmax(q k^T) v over packed rows x:[T, D], heads concatenated, before the output projection."""
         dt, D = x.dtype, self.embed_dim
         qkv = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt)
-        a = F.self_attention(qkv, pk, self.num_heads, self.head_dim, causal,
-                             flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0), dropout_p=self._p())
-        return self._out(a, residual, dt)
+        return F.self_attention(qkv, pk, self.num_heads, self.head_dim, causal,
+                                flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0), dropout_p=self._p())
+
+    def self_attention_packed(self, x, pk, causal, residual):
+        """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D] (x: GEMM operand rows, residual: stream rows)."""
+        return self._out(self.self_attention_core(x, pk, causal), residual, x.dtype)
 
     def project_memory_packed(self, mem):
         """[K | V] = mem . W_kv^T + b_kv  (kv_caching.py:241-245) over packed memory rows."""
         dt, D = mem.dtype, self.embed_dim
         return F.linear(mem, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(D, 3 * D))
 
-    def cross_attention_packed(self, x, kv, pq, pk, residual):
+    def cross_attention_core(self, x, kv, pq, pk):
         dt, D = x.dtype, self.embed_dim
         q = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(0, D))
-        a = F.cross_attention(q, kv, pq, pk, self.num_heads, self.head_dim,
-                              flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)), dropout_p=self._p())
-        return self._out(a, residual, dt)
+        return F.cross_attention(q, kv, pq, pk, self.num_heads, self.head_dim,
+                                 flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)), dropout_p=self._p())
+
+    def cross_attention_packed(self, x, kv, pq, pk, residual):
+        return self._out(self.cross_attention_core(x, kv, pq, pk), residual, x.dtype)
 
 
 class Packed:
@@ -285,6 +310,12 @@ class TransformerEncoderLayer(nn.Module):
         single = xb is None
         xb = x if single else xb
         dt = xb.dtype
+        if _can_fuse_tail(self, xb, dt):
+            a = self.self_attn.self_attention_core(xb, pk, False)
+            x, xb = linear_residual_norm(a, self.self_attn.out_proj, x, self.norm1, dt)
+            h = F.linear(xb, self.linear1.weight, self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+            x, xb = linear_residual_norm(h, self.linear2, x, self.norm2, dt)
+            return x if single else (x, xb)
         y = self.self_attn.self_attention_packed(xb, pk, False, residual=x)
         x, xb = norm_pair(self.norm1, y, dt)
         x, xb = norm_pair(self.norm2, _mlp_residual(self, xb, dt, stream=x), dt)
@@ -383,6 +414,15 @@ class TransformerDecoderLayer(nn.Module):
         single = xb is None
         xb = x if single else xb
         dt = xb.dtype
+        if _can_fuse_tail(self, xb, dt):
+            a = self.self_attn.self_attention_core(xb, tgt, causal)
+            x, xb = linear_residual_norm(a, self.self_attn.out_proj, x, self.norm1, dt)
+            kv = self.multihead_attn.project_memory_packed(mem)
+            c = self.multihead_attn.cross_attention_core(xb, kv, tgt, mem_pk)
+            x, xb = linear_residual_norm(c, self.multihead_attn.out_proj, x, self.norm2, dt)
+            h = F.linear(xb, self.linear1.weight, self.linear1.bias, act=ops.ACT_GELU, out_dtype=dt)
+            x, xb = linear_residual_norm(h, self.linear2, x, self.norm3, dt)
+            return x if single else (x, xb)
         y = self.self_attn.self_attention_packed(xb, tgt, causal, residual=x)
         x, xb = norm_pair(self.norm1, y, dt)
         kv = self.multihead_attn.project_memory_packed(mem)

@@ -587,6 +587,32 @@ def linear_splitk(x, weight, bias=None, act=ACT_NONE, residual=None, ln=None, ou
     return out if out2 is None else (out, out2)
 
 
+FUSE_LINEAR_LN = os.environ.get("ACAI_FUSE_LINEAR_LN", "1") != "0"
+
+
+def linear_layernorm(x, weight, bias, residual, gamma, beta, eps, want_f32):
+    """LayerNorm(x @ weight.T + bias + residual) * gamma + beta as one cluster kernel (acai_linear_layernorm): returns
+    (out_bf16, out_f32 or None), or None when the problem does not qualify (the caller runs linear + layernorm)."""
+    if not FUSE_LINEAR_LN:
+        return None
+    _cuda(x, weight, bias, residual, gamma, beta)
+    if x.dim() != 2 or residual.dim() != 2 or not _gemm_fusable(x, weight) or residual.stride(1) != 1:
+        return None
+    M, K = x.shape
+    N = weight.shape[0]
+    if M == 0 or N not in (512, 768, 1024) or residual.shape != (M, N):
+        return None
+    out16 = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    out32 = torch.empty((M, N), dtype=torch.float32, device=x.device) if want_f32 else None
+    lib = _lib.load()
+    name = "acai_linear_layernorm" if Profile.active is None else f"acai_linear_layernorm[{M}x{N}x{K}{',f32' if want_f32 else ''}]"
+    ok = _try_call(name, lib.acai_linear_layernorm, _p(x), x.stride(0), _p(weight), weight.stride(0), _p(_f32c(bias)), _p(residual),
+                   _dt(residual), residual.stride(0), _p(_f32c(gamma)), _p(_f32c(beta)), float(eps), _p(out16), N, _p(out32), N,
+                   M, N, K, _stream(), flops=2.0 * M * N * K,
+                   nbytes=2.0 * (M * K + N * K) + M * N * (residual.element_size() + 2 + (4 if want_f32 else 0)))
+    return (out16, out32) if ok else None
+
+
 def linear_gelu_train(x, weight, bias, dropout_p=0.0, dropout_seed=0):
     """(z, h) with z = x @ weight.T + bias and h = dropout(gelu(z)), both bf16, from one tcgen05 GEMM
     (acai_linear_gelu_train); None when the operands do not qualify (the caller runs linear + gelu)."""

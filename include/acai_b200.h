@@ -130,6 +130,21 @@ int acai_linear_splitk(const void* a, int64_t lda, const void* w, int64_t ldw, c
                        int32_t M, int32_t N, int32_t K, int32_t act,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- K2 + K5 fused: out = LayerNorm(a . w^T + bias + residual) * gamma + beta ------------------------------------------
+ * The tail of every post-norm sub-layer (x = norm1(x + out_proj(attn)), x = norm2(x + linear2(...)): nn.TransformerEncoderLayer
+ * / DecoderLayer with norm_first = False, models.py:31,423; spelled out at kv_caching.py:208,220,222) as ONE tcgen05 kernel:
+ * a thread-block cluster of N / 256 CTAs owns a 128-row tile, each CTA computes 256 columns into TMEM, adds bias and residual
+ * in place, and the row moments are merged across the cluster through distributed shared memory (two-pass variance per
+ * thread, Chan's formula across threads and CTAs), so the pre-norm sum never goes to HBM.  Writes the bf16 copy (`out_bf16`,
+ * the next GEMM's operand) and optionally the fp32 copy (`out_f32`, the residual stream under autocast semantics; NULL: none).
+ * bf16 operands, N in {512, 768, 1024}, K % 64 == 0, 16-byte aligned rows; otherwise ACAI_ERR_UNSUPPORTED and nothing is
+ * launched (the caller runs acai_linear_fwd + acai_layernorm_fwd).  `out_*` must not alias `residual`. */
+int acai_linear_layernorm(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias,
+                          const void* residual, int32_t res_dtype, int64_t ldr,
+                          const float* gamma, const float* beta, float eps,
+                          void* out_bf16, int64_t ldo16, void* out_f32, int64_t ldo32,
+                          int32_t M, int32_t N, int32_t K, void* stream);
+
 /* ---- K5: LayerNorm(x + residual) ---------------------------------------------------------
  * Post-norm sublayer tail `norm(x + sublayer(x))` (kv_caching.py:208,220,222; the
  * nn.TransformerEncoderLayer/DecoderLayer internals) and the final stack norm (eps 1e-6).

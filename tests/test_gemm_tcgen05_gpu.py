@@ -150,3 +150,42 @@ def test_splitk_matches_two_kernel_path_in_decode_engine(monkeypatch):
     assert same[:, :6].all(dim=1).float().mean().item() >= 0.75, same[:, :6]
     assert same.float().mean().item() >= 0.6, f"token agreement {same.float().mean().item()}"
     assert torch.allclose(outs[0][1][:, :4], outs[1][1][:, :4], atol=5e-2)
+
+
+# ---- GEMM + residual + LayerNorm in one cluster kernel (acai_linear_layernorm) ------------------------------------------
+@pytest.mark.parametrize("M,N,K", [(300, 768, 768), (1000, 768, 3072), (129, 1024, 1024), (4100, 1024, 4096), (64, 512, 3072),
+                                   (20000, 768, 768), (1, 768, 64)])
+@pytest.mark.parametrize("res_dtype", [torch.float32, torch.bfloat16])
+def test_linear_layernorm_cluster_kernel(M, N, K, res_dtype):
+    """out = LayerNorm(x W^T + b + residual) * gamma + beta against fp32 torch math on the same bf16 operands: ragged M
+    tails, every cluster size (N = 512 / 768 / 1024 -> 2 / 3 / 4 CTAs), more tiles than resident clusters, both residual
+    dtypes; the fp32 copy is the exact (unrounded) row, the bf16 copy its rounding; equal to the two-launch path."""
+    x = rnd(M, K, seed=M + 1).bfloat16()
+    w = rnd(N, K, seed=K + 2, scale=K ** -0.5).bfloat16()
+    b = rnd(N, seed=3)
+    r = (2.0 * rnd(M, N, seed=4) + 0.5).to(res_dtype)                   # non-zero row means: exercises the centred moments
+    g, be = 1.0 + 0.1 * rnd(N, seed=7), 0.1 * rnd(N, seed=8)
+    want32 = res_dtype == torch.float32
+    got = ops.linear_layernorm(x, w, b, r, g, be, 1e-5, want_f32=want32)
+    assert got is not None, "the fused kernel refused a qualifying problem"
+    y16, y32 = got
+    ref = torch.nn.functional.layer_norm(x.float() @ w.float().t() + b + r.float(), (N,), g, be, 1e-5)
+    assert y16.dtype == torch.bfloat16 and y16.shape == (M, N)
+    if want32:
+        assert y32.dtype == torch.float32
+        assert torch.allclose(y32, ref, rtol=2e-4, atol=2e-4), (y32 - ref).abs().max().item()
+        assert torch.equal(y16, y32.bfloat16())
+    else:
+        assert y32 is None
+        assert torch.allclose(y16.float(), ref, rtol=1e-2, atol=1e-2), (y16.float() - ref).abs().max().item()
+    # the two-launch path on the same operands
+    y = ops.linear(x, w, b, residual=r, out_dtype=torch.float32)
+    two = ops.layernorm(y, g, be, 1e-5, out_dtype=torch.float32)
+    assert torch.allclose((y32 if want32 else y16.float()), two, rtol=1e-2 if not want32 else 2e-4, atol=1e-2 if not want32 else 2e-4)
+
+
+def test_linear_layernorm_refuses_what_it_cannot_do():
+    x = rnd(64, 768, seed=1).bfloat16()
+    g, be = torch.ones(640, device=DEV), torch.zeros(640, device=DEV)
+    w = rnd(640, 768, seed=2).bfloat16()
+    assert ops.linear_layernorm(x, w, rnd(640, seed=3), rnd(64, 640, seed=4), g, be, 1e-5, True) is None      # N not 512 / 768 / 1024

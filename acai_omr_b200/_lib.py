@@ -11,7 +11,7 @@ import os
 import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libacai_b200.so")
+LIB_PATH = os.environ.get("ACAI_LIB_PATH") or os.path.join(_HERE, "libacai_b200.so")     # (override: kernel A/B experiments)
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "acai_b200.h")
 
 _lib = None
@@ -46,6 +46,7 @@ SIGNATURES = {
     "acai_patch_embed_fwd": [_p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _i32, _i32, _p, _sz, _p],
     "acai_linear_fwd": [_p, _i32, _i64, _p, _i32, _i64, _p, _p, _i32, _i64, _p, _i32, _i64, _i32, _i32, _i32, _i32, _p],
     "acai_linear_layernorm": [_p, _i64, _p, _i64, _p, _p, _i32, _i64, _p, _p, _f32, _p, _i64, _p, _i64, _i32, _i32, _i32, _p],
+    "acai_linear_layernorm_resident_clusters": [_i32],
     "acai_layernorm_fwd": [_p, _i32, _p, _i32, _p, _p, _f32, _p, _i32, _p, _i32, _i32, _i32, _p],
     "acai_attn_varlen_fwd": [_p, _p, _p, _i32, _i64, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _p, _i32,
                              _i64, _p, _f32, _u64, _p],

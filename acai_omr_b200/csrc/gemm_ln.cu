@@ -31,6 +31,13 @@ namespace acai {
 int make_tma_2d(CUtensorMap* map, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
                 uint32_t box_cols);
 
+#ifndef GLN_RDEPTH
+#define GLN_RDEPTH 1
+#endif
+#ifndef GLN_SBUF
+#define GLN_SBUF 1
+#endif
+
 namespace gln {
 constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, EPI_WARPS = 8, THREADS = 64 + EPI_WARPS * 32, STAGES = 3;
 constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
@@ -41,7 +48,7 @@ struct Params {
 };
 
 template <int CL> constexpr size_t smem_bytes() {
-  return (size_t)STAGES * (A_BYTES + B_BYTES) + EPI_WARPS * 4096 /*store staging*/ + 3 * BN * 4 /*bias, gamma, beta*/ +
+  return (size_t)STAGES * (A_BYTES + B_BYTES) + GLN_SBUF * EPI_WARPS * 4096 /*store staging*/ + 3 * BN * 4 /*bias, gamma, beta*/ +
          2 * BM * 8 /*half combine*/ + 2 * CL * BM * 8 /*cluster moments, double-buffered*/ + 256 /*barriers*/;
 }
 
@@ -53,12 +60,12 @@ __device__ __forceinline__ uint32_t num_clusters() { uint32_t r; asm volatile("m
 __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
   uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
 }
-__device__ __forceinline__ void st_cluster_f32x2(uint32_t addr, float a, float b) {
-  asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
-}
-// release at cluster scope: the store above is visible to whoever observes this arrival with an acquire
-__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+// asynchronous remote store: the 8 bytes land in the peer's shared memory and complete 8 bytes of the peer's mbarrier
+// transaction count when they do - the data IS the signal, no fence and no separate arrive (a release-arrive at cluster
+// scope costs a MEMBAR.GPU per peer)
+__device__ __forceinline__ void st_async_f32x2(uint32_t cluster_addr, float a, float b, uint32_t cluster_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
+               ::"r"(cluster_addr), "f"(a), "f"(b), "r"(cluster_bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -112,8 +119,8 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * A_BYTES;
-  uint8_t* staging = smem + STAGES * (A_BYTES + B_BYTES);                 // 8 warps x 4 KB
-  float* sbias = reinterpret_cast<float*>(staging + EPI_WARPS * 4096);    // [BN]
+  uint8_t* staging = smem + STAGES * (A_BYTES + B_BYTES);                 // 8 warps x 2 x 4 KB
+  float* sbias = reinterpret_cast<float*>(staging + GLN_SBUF * EPI_WARPS * 4096);    // [BN]
   float* sgamma = sbias + BN;
   float* sbeta = sgamma + BN;
   float2* comb = reinterpret_cast<float2*>(sbeta + BN);                   // [2 halves][BM] (mean, M2) of 128 columns
@@ -122,7 +129,7 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint64_t* stat_bar = tempty_bar + 2;                                    // [2]: CL * BM remote arrivals per tile
+  uint64_t* stat_bar = tempty_bar + 2;                                    // [2]: CL * BM * 8 bytes of peer moments per tile
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stat_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -141,7 +148,7 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < 2; ++s) {
-      ptx::mbar_init(&tfull_bar[s], 1); ptx::mbar_init(&tempty_bar[s], EPI_WARPS); ptx::mbar_init(&stat_bar[s], CL * BM);
+      ptx::mbar_init(&tfull_bar[s], 1); ptx::mbar_init(&tempty_bar[s], EPI_WARPS); ptx::mbar_init(&stat_bar[s], 1);
     }
     ptx::fence_barrier_init();
   }
@@ -151,8 +158,8 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   cluster_sync_all();            // every CTA's barriers exist before anyone arrives on them remotely
-  pdl_wait();
-  pdl_launch_dependents();
+  // (launched in plain stream order, without programmatic dependent launch: dependents that start early take SMs a
+  // cluster still needs - measured 18.2 vs 16.6 ms for the 12-layer encoder step, profiles/r2b_linear_layernorm.md)
 
   if (warp == 0) {
     if (lane == 0) {
@@ -196,9 +203,9 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     const int half = ew >> 2;            // column half of the CTA's 256 columns
     const int trow = lane_grp * 32 + lane;                       // row inside the tile, 0..127
     const int etid = (int)threadIdx.x - 64;                      // 0..255
-    uint8_t* const stage = staging + ew * 4096;
-    uint8_t* const srow = stage + lane * 128;
-    const uint32_t sw = (uint32_t)(lane & 7);
+    uint8_t* const stage0 = staging + ew * (GLN_SBUF * 4096);                 // two 4 KB tiles: one is being read out by TMA while the
+    const uint32_t sw = (uint32_t)(lane & 7);                    // other is filled
+    int sbuf = 0;
     // the CTA's columns never change: parameters are staged once
     sbias[etid] = p.bias ? __ldg(p.bias + n0 + etid) : 0.0f;
     sgamma[etid] = __ldg(p.gamma + n0 + etid);
@@ -213,15 +220,19 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       const int row0 = mt * BM + lane_grp * 32, grow = row0 + lane;
       const int64_t rrow = grow < M ? (int64_t)grow : -1;
-      ResChunk<RES> rc;
-      res_load<RES>(p, rrow, ccol0, rc);                          // in flight while the MMAs finish
+      if (etid == 0) ptx::mbar_arrive_expect_tx(&stat_bar[as], CL * BM * 8);   // this tile's moments: 8 bytes per row and peer
+      constexpr int RDEPTH = RES == 2 ? GLN_RDEPTH : (GLN_RDEPTH == 3 ? 4 : GLN_RDEPTH);   // residual chunks in flight (register budget: 168)
+      ResChunk<RES> rc[RDEPTH];
+#pragma unroll
+      for (int c = 0; c < RDEPTH; ++c) res_load<RES>(p, rrow, ccol0 + c * 32, rc[c]);     // issued under the MMAs
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + as * BN + half * CPW;
       // ---- pass A1: v = acc + bias + residual -> TMEM, row sum
       float sum = 0.0f;
-#pragma unroll 1
-      for (int c = 0; c < CPW; c += 32) {
+#pragma unroll
+      for (int ci = 0; ci < CPW / 32; ++ci) {
+        const int c = ci * 32;
         uint32_t acc[32];
         ptx::tmem_ld_32x32(taddr + c, acc);
         ptx::tmem_ld_wait();
@@ -232,8 +243,8 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           v[4 * q] = __uint_as_float(acc[4 * q]) + b4.x; v[4 * q + 1] = __uint_as_float(acc[4 * q + 1]) + b4.y;
           v[4 * q + 2] = __uint_as_float(acc[4 * q + 2]) + b4.z; v[4 * q + 3] = __uint_as_float(acc[4 * q + 3]) + b4.w;
         }
-        res_add<RES>(rc, v);
-        if (c + 32 < CPW) res_load<RES>(p, rrow, ccol0 + c + 32, rc);
+        res_add<RES>(rc[ci % RDEPTH], v);
+        if (ci + RDEPTH < CPW / 32) res_load<RES>(p, rrow, ccol0 + (ci + RDEPTH) * 32, rc[ci % RDEPTH]);
 #pragma unroll
         for (int j = 0; j < 32; ++j) { sum += v[j]; acc[j] = __float_as_uint(v[j]); }
         ptx::tmem_st_32x32(taddr + c, acc);
@@ -261,10 +272,7 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         const uint32_t slot = ptx::smem_u32(&moments[(as * CL + (int)rank) * BM + trow]);
         const uint32_t bar = ptx::smem_u32(&stat_bar[as]);
 #pragma unroll
-        for (int r = 0; r < CL; ++r) {
-          st_cluster_f32x2(mapa(slot, (uint32_t)r), mean_c, m2_c);
-          mbar_arrive_remote(mapa(bar, (uint32_t)r));
-        }
+        for (int r = 0; r < CL; ++r) st_async_f32x2(mapa(slot, (uint32_t)r), mean_c, m2_c, mapa(bar, (uint32_t)r));
       }
       mbar_wait_cluster(&stat_bar[as], aphase);
       float mean = 0.0f;
@@ -302,7 +310,10 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           }
         }
         // bf16 copy: 64 columns = 128 bytes of this thread's row
-        if (lane == 0) ptx::tma_store_wait_read<0>();
+        uint8_t* stage = stage0 + sbuf * 4096;
+        uint8_t* srow = stage + lane * 128;
+        sbuf ^= (GLN_SBUF - 1);
+        if (lane == 0) ptx::tma_store_wait_read<GLN_SBUF - 1>();               // the store that last used THIS tile has been read out
         __syncwarp();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
@@ -318,7 +329,10 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         if constexpr (OUT32) {
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
-            if (lane == 0) ptx::tma_store_wait_read<0>();
+            stage = stage0 + sbuf * 4096;
+            srow = stage + lane * 128;
+            sbuf ^= (GLN_SBUF - 1);
+            if (lane == 0) ptx::tma_store_wait_read<GLN_SBUF - 1>();
             __syncwarp();
 #pragma unroll
             for (int q = 0; q < 8; ++q)
@@ -375,12 +389,10 @@ static int launch_ln(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   const int clusters = num_m < resident ? num_m : resident;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(clusters * CL)); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = smem_bytes<CL>(); cfg.stream = st;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
   ACAI_CUDA(cudaLaunchKernelEx(&cfg, gemm_ln_tcgen05<CL, RES, OUT32>, ta, tb, t16, t32, p, M, K));
   return launch_status("gemm_ln_tcgen05");
 }
@@ -395,6 +407,16 @@ static int dispatch_ln(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
 }  // namespace acai
 
 using namespace acai;
+
+// Diagnostics: how many clusters of `cluster_size` CTAs (2, 3 or 4) of the kernel can be resident on this device (0: none).
+extern "C" int acai_linear_layernorm_resident_clusters(int32_t cluster_size) {
+  switch (cluster_size) {
+    case 2: return resident_clusters<2, 2, true>();
+    case 3: return resident_clusters<3, 2, true>();
+    case 4: return resident_clusters<4, 2, true>();
+    default: return 0;
+  }
+}
 
 // C ABI: see include/acai_b200.h.  ACAI_ERR_UNSUPPORTED (nothing launched) when the problem does not qualify; the caller
 // then runs acai_linear_fwd + acai_layernorm_fwd.

@@ -144,6 +144,8 @@ int acai_linear_layernorm(const void* a, int64_t lda, const void* w, int64_t ldw
                           const float* gamma, const float* beta, float eps,
                           void* out_bf16, int64_t ldo16, void* out_f32, int64_t ldo32,
                           int32_t M, int32_t N, int32_t K, void* stream);
+/* clusters of `cluster_size` (= N / 256: 2, 3, 4) CTAs of that kernel the device can hold at once (its grid size) */
+int acai_linear_layernorm_resident_clusters(int32_t cluster_size);
 
 /* ---- K5: LayerNorm(x + residual) ---------------------------------------------------------
  * Post-norm sublayer tail `norm(x + sublayer(x))` (kv_caching.py:208,220,222; the

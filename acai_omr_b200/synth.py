@@ -19,6 +19,14 @@ def system_shapes(num_systems: int, max_tokens: int = 1024, aspects=(1, 2, 3, 4,
     return [dynamic_resize_shape(aspects[i % len(aspects)], max_tokens) for i in range(num_systems)]
 
 
+def stress_mix_shapes(num_systems: int, budgets=(256, 512, 1024), aspects=(1, 2, 3, 4, 5, 6, 7, 8)):
+    """SURVEY 8(d)'s "stress mix": token budgets N in {256, 512, 1024} x the eight aspect ratios (24 distinct shapes,
+    L from 192 to 1024) - a heterogeneous batch whose padded form wastes about half of its rows and whose per-rank token
+    sums depend on how it is sharded."""
+    combos = [(n, a) for n in budgets for a in aspects]
+    return [dynamic_resize_shape(combos[(7 * i) % len(combos)][1], combos[(7 * i) % len(combos)][0]) for i in range(num_systems)]
+
+
 def synth_system(h: int, w: int, seed: int) -> torch.Tensor:
     """White canvas, 2 x 5 staff lines of 2 px, ~60 dark ellipses/stems, Gaussian noise 0.03; fp32 (1,H,W) in [0,1]."""
     g = torch.Generator().manual_seed(1234 + seed)

@@ -248,6 +248,10 @@ def run_ours(args, rank, world, device):
                 "d2h_bytes_per_step": NUM_SYSTEMS * max(lens) * 768 * 4 + NUM_SYSTEMS * max(lens),
                 "mode": "EncoderPipeline.run: Encoder.forward per batch from pinned host images to pinned host latents, "
                         "uploads / downloads of neighbouring batches overlapped with the kernels (3 streams)",
+                "host_link_gb_per_s_per_rank": {"h2d": sum(t.numel() * 4 for t in imgs_host) / (e2e_ms * 1e-3) / 1e9,
+                                                "d2h": (NUM_SYSTEMS * max(lens) * 768 * 4) / (e2e_ms * 1e-3) / 1e9,
+                                                "what": "bytes per step / time between results: what each rank asks of its PCIe "
+                                                        "link and of host DRAM while the kernels run"},
                 "steps": served, "ms_between_results": yield_ms, "synchronous_ms_per_step": e2e_sync_ms,
                 "synchronous_value": world * NUM_SYSTEMS / (e2e_sync_ms * 1e-3)},
         "gpu_launches": launches,
@@ -322,6 +326,58 @@ def torch_eager_encoder(enc, imgs_dev, lens, ours_cpu, steps=5):
     return {"timing": dict(out, what="stock torch.nn.TransformerEncoder + per-image unfold/linear/PE loop, same weights, same 64 "
                                      "systems, same GPU; no kernel of this repo on that path"),
             "parity": dict(P.errors(ours_cpu, ref, valid), systems=NUM_SYSTEMS, tokens=int(valid.sum()), gate=P.BF16_TOL)}
+
+
+# ------------------------------------------------------------------------------------------ strong scaling: ONE batch, sharded
+STRONG_SYSTEMS = 512
+
+
+def run_strong(args, rank, world, device, enc):
+    """the path shards by partitioning ONE ragged batch.  A fixed heterogeneous batch of 512 systems (the stress
+    mix: token budgets 256 / 512 / 1024 x 8 aspect ratios) is split over the ranks by train.shard with cost = patch tokens
+    (greedy bin packing, every rank computes the same assignment), each rank encodes its share through the public call, time =
+    max over ranks.  Total work is fixed: "strong" scaling; the per-rank token sums show the balance."""
+    from acai_omr_b200 import synth, train
+    shapes = synth.stress_mix_shapes(STRONG_SYSTEMS)
+    mine = train.shard(list(range(STRONG_SYSTEMS)), rank, world, cost=lambda i: (shapes[i][0] // 16) * (shapes[i][1] // 16))
+    loads = []
+    for r in range(world):
+        idx = train.shard(list(range(STRONG_SYSTEMS)), r, world, cost=lambda i: (shapes[i][0] // 16) * (shapes[i][1] // 16))
+        loads.append(sum((shapes[i][0] // 16) * (shapes[i][1] // 16) for i in idx))
+    stride = [sum((shapes[i][0] // 16) * (shapes[i][1] // 16) for i in range(r, STRONG_SYSTEMS, world)) for r in range(world)]
+    imgs = [synth.synth_system(shapes[i][0], shapes[i][1], i).to(device) for i in mine]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+
+    def step():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            return enc(imgs)[0]
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    k, events = max(3, min(args.steps, 10)), []
+    for _ in range(k):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); step(); e1.record()
+        events.append((e0, e1))
+    torch.cuda.synchronize()
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b in events) / k], dtype=torch.float64, device=device)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    del imgs
+    if rank != 0:
+        return None
+    ms = float(t[0])
+    total = sum(loads)
+    return {"metric": "ragged encoder systems/sec, ONE 512-system batch sharded over the ranks", "value": STRONG_SYSTEMS / (ms * 1e-3),
+            "unit": UNIT, "scaling": "strong", "n_gpus": world, "ms_per_step": ms,
+            "config": {"workload": "512 systems of the stress mix (token budgets 256/512/1024 x aspects 1..8), sum L = %d, padded "
+                                   "B * L_max would be %d rows" % (total, STRONG_SYSTEMS * 1024),
+                       "partition": "train.shard(cost = patch tokens): greedy bin packing, no data-path collective"},
+            "tokens_per_rank": loads, "imbalance_max_over_mean": max(loads) / (total / world),
+            "imbalance_of_stride_sharding": max(stride) / (total / world)}
 
 
 # ------------------------------------------------------------------------------------------ decode leg (configs[2])
@@ -602,7 +658,9 @@ def run_train(args, rank, world, device, kind):
     from acai_omr_b200.models import models as M
     n = TRAIN_SYSTEMS
     torch.manual_seed(0)
-    imgs = [synth.synth_system(h, w, rank * n + i).to(device) for i, (h, w) in enumerate(synth.system_shapes(n))]
+    # configs[3] trains on the N = 1024 token budget (omr_teacher_force_train.py:24), configs[4] on N = 512 (pre_train.py:18)
+    shapes = synth.system_shapes(n) if kind == "tf" else synth.system_shapes(n, max_tokens=512, aspects=(1, 2, 3, 4, 5, 6, 8))
+    imgs = [synth.synth_system(h, w, rank * n + i).to(device) for i, (h, w) in enumerate(shapes)]
     lens = [(t.shape[-2] // 16) * (t.shape[-1] // 16) for t in imgs]
     if kind == "tf":
         enc = M.FineTuneOMREncoder(**encoder_kwargs(), transformer_dropout=0.05)
@@ -629,7 +687,7 @@ def run_train(args, rank, world, device, kind):
         step = lambda: train.mae_step(model, batch, tr)
         work = {}
         flops = None
-        name = "configs[4]: MAE pre-training fwd/bwd + grad all-reduce + AdamW"
+        name = "configs[4]: MAE pre-training fwd/bwd + grad all-reduce + AdamW, N = 512 token budget shapes (pre_train.py:18)"
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
     for _ in range(3):
         sums = step()
@@ -651,6 +709,39 @@ def run_train(args, rank, world, device, kind):
     torch.cuda.synchronize()
     total = sum(a.elapsed_time(b) for a, b in events)
     launches = (ops.launch_count() - n0) // k
+    overlapped_elements = getattr(tr, "overlapped_elements", 0)
+    collective = None
+    if world > 1:
+        # what the gradient exchange costs: the same step with the all-reduce after the backward (no overlap hook) and with
+        # the collective skipped altogether (gradients stay rank-local: timing only), 3 steps each, max over ranks
+        def timed_variant(setup, restore):
+            setup()
+            try:
+                step()
+                torch.cuda.synchronize()
+                torch.distributed.barrier()
+                ev = []
+                for _ in range(3):
+                    flush.zero_()
+                    a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a_.record(); step(); b_.record()
+                    ev.append((a_, b_))
+                torch.cuda.synchronize()
+                return sum(x.elapsed_time(y) for x, y in ev) / 3
+            finally:
+                restore()
+        hook, reduce_ = tr.grad_ready_hook, tr.allreduce_gradients
+        serial = timed_variant(lambda: setattr(tr, "grad_ready_hook", lambda t_, m_: None), lambda: setattr(tr, "grad_ready_hook", hook))
+
+        def skip():
+            tr.grad_ready_hook = lambda t_, m_: None
+            tr.allreduce_gradients = lambda: None
+        skipped = timed_variant(skip, lambda: (setattr(tr, "grad_ready_hook", hook), setattr(tr, "allreduce_gradients", reduce_)))
+        tv = torch.tensor([serial, skipped], dtype=torch.float64, device=device)
+        torch.distributed.all_reduce(tv, op=torch.distributed.ReduceOp.MAX)
+        collective = {"serial_after_backward_ms": float(tv[0]), "skipped_ms": float(tv[1]),
+                      "overlapped_elements": int(overlapped_elements), "gradient_elements": int(tr.numel),
+                      "bytes": int(tr.numel) * 4}
     with ops.Profile() as prof:
         step()
     kern = prof.summary()
@@ -659,6 +750,9 @@ def run_train(args, rank, world, device, kind):
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms = float(t[0])
+    if collective is not None:
+        collective.update(overlapped_ms=ms, exposed_ms_overlapped=ms - collective["skipped_ms"],
+                          exposed_ms_serial=collective["serial_after_backward_ms"] - collective["skipped_ms"])
     peak_mem = torch.cuda.max_memory_allocated() / 2 ** 30
     numel = tr.numel
     del tr, model, batch
@@ -679,7 +773,7 @@ def run_train(args, rank, world, device, kind):
                         "trainable_parameters": numel, "l2": "flushed between steps",
                         "collective": "one NCCL all-reduce of the flat fp32 gradient buffer per step" if world > 1 else "none (1 GPU)"},
                        **work),
-        "loss_last_step": loss, "gpu_launches_per_step": launches, "host_ms_in_step_call": round(host_s / k * 1e3, 2),   # includes blocking on the full launch queue: the host alone
+        "collective": collective, "loss_last_step": loss, "gpu_launches_per_step": launches, "host_ms_in_step_call": round(host_s / k * 1e3, 2),   # includes blocking on the full launch queue: the host alone
         # needs ~32 ms to enqueue such a step (profiles/ubench/train_host_time.py), the step is GPU bound
         "peak_mem_gib": round(peak_mem, 1),
         "roofline": {"bound": "tensor", "kernel": "gemm_bf16_tcgen05 + gemm_wgrad_tcgen05", "achieved": g_fl / (g_ms * 1e-3) / 1e12,
@@ -778,6 +872,9 @@ def secondary_summary(line):
             out[f"{tag}_systems_per_s"] = round(t["value"], 1)
             out[f"{tag}_ms_per_step"] = round(t["ms_per_step"], 2)
             out[f"{tag}_gemm_frac"] = round(t["roofline"]["frac"], 4)
+            if t.get("collective"):
+                out[f"{tag}_allreduce_exposed_ms"] = round(t["collective"]["exposed_ms_overlapped"], 2)
+                out[f"{tag}_allreduce_exposed_ms_serial"] = round(t["collective"]["exposed_ms_serial"], 2)
             if "whole_step_tflops" in t["roofline"]:
                 out[f"{tag}_whole_step_tflops"] = round(t["roofline"]["whole_step_tflops"], 1)
     c0 = line.get("config0")
@@ -786,6 +883,9 @@ def secondary_summary(line):
                    config0_gpu_fp32_tokens_per_s=round(c0["gpu_fp32"]["tokens_per_s"], 1),
                    config0_cpu_tokens_per_s=round(c0["cpu_oracle"]["tokens_per_s"], 2) if c0.get("cpu_oracle") else None,
                    config0_fp32_tokens_exact=c0.get("fp32_tokens_exact"))
+    ss = line.get("strong_scaling")
+    if ss:
+        out.update(strong_512_systems_per_s=round(ss["value"], 1), strong_imbalance=round(ss["imbalance_max_over_mean"], 4))
     te = line.get("torch_eager_b200")
     if te:
         out.update(torch_eager_bf16_systems_per_s=round(te["bf16_autocast"]["value"], 1),
@@ -803,6 +903,7 @@ def main():
     ap.add_argument("--no-decode", action="store_true", help="skip the configs[2] decode leg")
     ap.add_argument("--no-train", action="store_true", help="skip the configs[3]/[4] training legs")
     ap.add_argument("--no-torch-eager", action="store_true", help="skip the stock-torch-on-the-same-GPU baseline")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (one 512-system batch sharded)")
     ap.add_argument("--no-config0", action="store_true", help="skip the configs[0] single-image greedy leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -829,6 +930,8 @@ def main():
         torch.distributed.init_process_group("nccl", device_id=device)
     line = run_ours(args, rank, world, device)
     torch.cuda.empty_cache()
+    strong = None if args.no_strong else run_strong(args, rank, world, device, build_encoder(device))
+    torch.cuda.empty_cache()
     dec = None if args.no_decode else run_decode(args, rank, world, device)
     torch.cuda.empty_cache()
     c0 = run_config0(args, device) if (rank == 0 and world == 1 and not args.no_config0) else None
@@ -840,6 +943,8 @@ def main():
             line["decode"] = dec
         if c0 is not None:
             line["config0"] = c0
+        if strong is not None:
+            line["strong_scaling"] = strong
         if tf is not None:
             line["train_teacher_forced"] = tf
         if mae is not None:

@@ -32,7 +32,7 @@ int make_tma_2d(CUtensorMap* map, const void* ptr, int dtype, uint64_t rows, uin
                 uint32_t box_cols);
 
 #ifndef GLN_RDEPTH
-#define GLN_RDEPTH 1
+#define GLN_RDEPTH 2
 #endif
 #ifndef GLN_SBUF
 #define GLN_SBUF 1
@@ -82,31 +82,57 @@ __device__ __forceinline__ void cluster_sync_all() {
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory"); }
 
-// 32 residual values of this thread's row starting at column col (RES: 1 = bf16, 2 = fp32), as raw 16-byte pieces
+// The residual chunk of a warp: 32 rows x 32 columns (RES: 1 = bf16 -> 64 bytes per row, 2 = fp32 -> 128 bytes per row).
+// Loaded COALESCED - the PPR lanes that share a row read its consecutive 16-byte pieces, so one warp instruction touches
+// 32 / PPR rows instead of 32 (thread = row loads are 32 cache lines per instruction and made the LSU the bottleneck of
+// the epilogue: 49 of 160 us, profiles/r2b_linear_layernorm.md) - and transposed to thread = row through the warp's
+// swizzled staging tile.
 template <int RES> struct ResChunk { uint4 v[RES == 2 ? 8 : 4]; };
 template <int RES>
-__device__ __forceinline__ void res_load(const Params& p, int64_t rrow, int col, ResChunk<RES>& rc) {
-  constexpr int NV = RES == 2 ? 8 : 4;
-  const uint4* base = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p.res) + (rrow * p.ldr + col) * (RES == 2 ? 4 : 2));
+__device__ __forceinline__ void res_load(const Params& p, int row0, int M, int col, int lane, ResChunk<RES>& rc) {
+  constexpr int PPR = RES == 2 ? 8 : 4, RPI = 32 / PPR;          // pieces per row, rows per warp instruction
+  const int r = lane / PPR, pc = lane % PPR;
 #pragma unroll
-  for (int i = 0; i < NV; ++i) rc.v[i] = rrow >= 0 ? __ldg(base + i) : make_uint4(0u, 0u, 0u, 0u);
+  for (int j = 0; j < PPR; ++j) {
+    const int row = row0 + j * RPI + r;
+#ifdef GLN_ABL_NORES
+    rc.v[j] = make_uint4(0u, 0u, 0u, 0u);
+#else
+    rc.v[j] = row < M ? __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p.res) +
+                                                              ((int64_t)row * p.ldr + col) * (RES == 2 ? 4 : 2)) + pc)
+                      : make_uint4(0u, 0u, 0u, 0u);
+#endif
+  }
 }
+// staging tile <- the chunk (row rr, piece pc at rr * 128 + ((pc ^ (rr & 7)) << 4)); then v += this thread's row
 template <int RES>
-__device__ __forceinline__ void res_add(const ResChunk<RES>& rc, float (&v)[32]) {
+__device__ __forceinline__ void res_add(const ResChunk<RES>& rc, uint8_t* stage, int lane, float (&v)[32]) {
+  constexpr int PPR = RES == 2 ? 8 : 4, RPI = 32 / PPR;
+  const int r = lane / PPR, pc = lane % PPR;
+#pragma unroll
+  for (int j = 0; j < PPR; ++j) {
+    const int rr = j * RPI + r;
+    *reinterpret_cast<uint4*>(stage + rr * 128 + ((pc ^ (rr & 7)) << 4)) = rc.v[j];
+  }
+  __syncwarp();
+  const uint8_t* mine = stage + lane * 128;
+  const int sw = lane & 7;
   if constexpr (RES == 1) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rc.v[q]);
+      const uint4 raw = *reinterpret_cast<const uint4*>(mine + ((q ^ sw) << 4));
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
 #pragma unroll
       for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); v[8 * q + 2 * i] += f.x; v[8 * q + 2 * i + 1] += f.y; }
     }
   } else {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      const float4 f = *reinterpret_cast<const float4*>(&rc.v[q]);
+      const float4 f = *reinterpret_cast<const float4*>(mine + ((q ^ sw) << 4));
       v[4 * q] += f.x; v[4 * q + 1] += f.y; v[4 * q + 2] += f.z; v[4 * q + 3] += f.w;
     }
   }
+  __syncwarp();
 }
 
 // RES: 1 = bf16 residual, 2 = fp32 residual.  OUT32: also store the normalised rows in fp32 (the residual stream copy).
@@ -219,12 +245,16 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     for (int mt = first; mt < num_m; mt += step, ++it) {
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       const int row0 = mt * BM + lane_grp * 32, grow = row0 + lane;
-      const int64_t rrow = grow < M ? (int64_t)grow : -1;
+      (void)grow;
+#ifndef GLN_ABL_NOSTAT
       if (etid == 0) ptx::mbar_arrive_expect_tx(&stat_bar[as], CL * BM * 8);   // this tile's moments: 8 bytes per row and peer
+#endif
       constexpr int RDEPTH = RES == 2 ? GLN_RDEPTH : (GLN_RDEPTH == 3 ? 4 : GLN_RDEPTH);   // residual chunks in flight (register budget: 168)
       ResChunk<RES> rc[RDEPTH];
 #pragma unroll
-      for (int c = 0; c < RDEPTH; ++c) res_load<RES>(p, rrow, ccol0 + c * 32, rc[c]);     // issued under the MMAs
+      for (int c = 0; c < RDEPTH; ++c) res_load<RES>(p, row0, M, ccol0 + c * 32, lane, rc[c]);     // issued under the MMAs
+      if (lane == 0) ptx::tma_store_wait_read<0>();               // the staging tile doubles as the transpose buffer: the previous
+      __syncwarp();                                               // tile's last store must have been read out of it
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + as * BN + half * CPW;
@@ -243,8 +273,8 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
           v[4 * q] = __uint_as_float(acc[4 * q]) + b4.x; v[4 * q + 1] = __uint_as_float(acc[4 * q + 1]) + b4.y;
           v[4 * q + 2] = __uint_as_float(acc[4 * q + 2]) + b4.z; v[4 * q + 3] = __uint_as_float(acc[4 * q + 3]) + b4.w;
         }
-        res_add<RES>(rc[ci % RDEPTH], v);
-        if (ci + RDEPTH < CPW / 32) res_load<RES>(p, rrow, ccol0 + (ci + RDEPTH) * 32, rc[ci % RDEPTH]);
+        res_add<RES>(rc[ci % RDEPTH], stage0, lane, v);
+        if (ci + RDEPTH < CPW / 32) res_load<RES>(p, row0, M, ccol0 + (ci + RDEPTH) * 32, lane, rc[ci % RDEPTH]);
 #pragma unroll
         for (int j = 0; j < 32; ++j) { sum += v[j]; acc[j] = __float_as_uint(v[j]); }
         ptx::tmem_st_32x32(taddr + c, acc);
@@ -253,6 +283,9 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       const float mean_t = sum * (1.0f / CPW);
       // ---- pass A2: centred second moment of the thread's 128 columns
       float m2 = 0.0f;
+#ifdef GLN_ABL_NOA2
+      if (false)
+#endif
 #pragma unroll 1
       for (int c = 0; c < CPW; c += 32) {
         uint32_t acc[32];
@@ -271,10 +304,16 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         const float m2_c = m2 + o.y + d * d * (0.5f * CPW);       // Chan: n_a n_b / (n_a + n_b) = 64
         const uint32_t slot = ptx::smem_u32(&moments[(as * CL + (int)rank) * BM + trow]);
         const uint32_t bar = ptx::smem_u32(&stat_bar[as]);
+#ifndef GLN_ABL_NOSTAT
 #pragma unroll
         for (int r = 0; r < CL; ++r) st_async_f32x2(mapa(slot, (uint32_t)r), mean_c, m2_c, mapa(bar, (uint32_t)r));
+#else
+        (void)slot; (void)bar; moments[(as * CL) * BM + trow] = make_float2(mean_c, m2_c);
+#endif
       }
+#ifndef GLN_ABL_NOSTAT
       mbar_wait_cluster(&stat_bar[as], aphase);
+#endif
       float mean = 0.0f;
       float2 mo[CL];
 #pragma unroll
@@ -325,7 +364,9 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         }
         ptx::fence_proxy_async_smem();
         __syncwarp();
+        #ifndef GLN_ABL_NOSTORE
         if (lane == 0) { ptx::tma_store_2d(&tma_out16, stage, ccol0 + c, row0); ptx::tma_store_commit(); }
+#endif
         if constexpr (OUT32) {
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
@@ -340,7 +381,9 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
                   make_float4(y[hh][4 * q], y[hh][4 * q + 1], y[hh][4 * q + 2], y[hh][4 * q + 3]);
             ptx::fence_proxy_async_smem();
             __syncwarp();
+            #ifndef GLN_ABL_NOSTORE
             if (lane == 0) { ptx::tma_store_2d(&tma_out32, stage, ccol0 + c + hh * 32, row0); ptx::tma_store_commit(); }
+#endif
           }
         }
       }

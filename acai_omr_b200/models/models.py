@@ -349,11 +349,18 @@ class TransitionHead(nn.Sequential):
         packed = attached_packed(x)
         if packed is None:
             return gelu_mlp_head(x, self[0], self[3], dropout_p=p)
-        # came straight from the encoder: run on the packed rows of valid patches only and re-pad with zeros
-        # (the reference computes head(padding row) there; those rows are masked everywhere downstream)
+        # came straight from the encoder: run on the packed rows of valid patches only.  The reference applies the head to
+        # the padding rows too; in eval mode those all hold the same vector (the encoder's final-norm bias), so the head
+        # maps them to ONE row, computed once here and used as the fill.  (Train mode: the reference's padding rows are
+        # unspecified finite values and nothing downstream reads them; they are zero here.)
         h, pk = packed
         hp = gelu_mlp_head(h, self[0], self[3], dropout_p=p)
-        out = F.unpack_padded(hp, pk.cu, pk.batch, x.shape[1])
+        fill = None
+        if not self.training:
+            short = next((b for b, n in enumerate(pk.lens) if n < x.shape[1]), None)
+            if short is not None:
+                fill = gelu_mlp_head(x[short, pk.lens[short]].reshape(1, -1), self[0], self[3]).reshape(-1).float()
+        out = F.unpack_padded(hp, pk.cu, pk.batch, x.shape[1], fill=fill)
         attach_packed(out, (hp, pk))
         return out
 

@@ -184,8 +184,14 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   cluster_sync_all();            // every CTA's barriers exist before anyone arrives on them remotely
-  // (launched in plain stream order, without programmatic dependent launch: dependents that start early take SMs a
-  // cluster still needs - measured 18.2 vs 16.6 ms for the 12-layer encoder step, profiles/r2b_linear_layernorm.md)
+  // Programmatic dependent launch, one way only (profiles/r2b_linear_layernorm.md, 12-layer encoder step): THIS kernel is
+  // launched in plain stream order - started early, its CTAs take whole SMs and all 512 TMEM columns while the previous
+  // kernel (attention: several waves of 4 CTAs per SM) still has CTAs to place: 17.7 vs 16.4 ms - but it lets ITS dependents
+  // start early (they can only land on the SMs no cluster could use): 16.4 -> 16.15 ms.  -DGLN_PDL_WAIT restores the former.
+#ifdef GLN_PDL_WAIT
+  pdl_wait();
+#endif
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -432,10 +438,15 @@ static int launch_ln(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   const int clusters = num_m < resident ? num_m : resident;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(clusters * CL)); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = smem_bytes<CL>(); cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
+#ifdef GLN_PDL_WAIT
+  if (pdl_enabled()) cfg.numAttrs = 2;
+#endif
   ACAI_CUDA(cudaLaunchKernelEx(&cfg, gemm_ln_tcgen05<CL, RES, OUT32>, ta, tb, t16, t32, p, M, K));
   return launch_status("gemm_ln_tcgen05");
 }

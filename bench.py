@@ -193,7 +193,27 @@ def run_ours(args, rank, world, device):
         out_all = step_resident()
     kern = prof.summary()
     out_all = out_all.float().cpu()      # [64, L_max, 768]: compared with the oracle (first 8 systems) and with stock torch
-    stock = torch_eager_encoder(enc, imgs_dev, lens, out_all) if (rank == 0 and not args.no_torch_eager) else None
+    # the same step with round 1's single bf16 residual stream (ACAI_STREAM=bf16): faster, about twice the error
+    from acai_omr_b200 import layers
+    alt = None
+    if layers.STREAM_FP32:
+        layers.STREAM_FP32 = False
+        try:
+            for _ in range(2):
+                step_resident()
+            ka = max(3, min(args.steps, 5))
+            alt_ms = timed(step_resident, ka) / ka
+            alt_out = step_resident().float().cpu()
+        finally:
+            layers.STREAM_FP32 = True
+        ta = torch.tensor([alt_ms], dtype=torch.float64, device=device)
+        if world > 1:
+            torch.distributed.all_reduce(ta, op=torch.distributed.ReduceOp.MAX)
+        alt = {"ms_per_step": float(ta[0]), "value": world * NUM_SYSTEMS / (float(ta[0]) * 1e-3), "unit": UNIT,
+               "what": "ACAI_STREAM=bf16: one bf16 residual stream (LayerNorm outputs and pre-norm sums rounded to bf16)"}
+    stock = None
+    if rank == 0 and not args.no_torch_eager:
+        stock = torch_eager_encoder(enc, imgs_dev, lens, {"ours": out_all, **({"bf16_stream": alt_out} if alt else {})})
     step_e2e()
     barrier()
     e2e_sync_ms = timed(step_e2e, max(2, min(args.steps, 5)), wall=True) / max(2, min(args.steps, 5))
@@ -227,7 +247,14 @@ def run_ours(args, rank, world, device):
             for f_ in g:
                 g[f_] += v_[f_]
     gemm_shapes = {k_: {"ms": round(v_["ms"], 3), "tflops": round(v_["flops"] / (v_["ms"] * 1e-3) / 1e12, 1),
-                        "launches": v_["launches"]} for k_, v_ in kern.items() if k_.startswith("acai_linear_fwd")}
+                        "launches": v_["launches"]} for k_, v_ in kern.items()
+                   if k_.startswith("acai_linear_fwd") or k_.startswith("acai_linear_layernorm")}
+    fused = dict(ms=0.0, flops=0.0, launches=0, bytes=0.0)
+    for k_, v_ in kern.items():
+        if k_.startswith("acai_linear_layernorm"):
+            for f_ in ("ms", "flops", "launches"):
+                fused[f_] += v_[f_]
+            fused["bytes"] += v_.get("bytes", 0.0)
     merged = {}
     for k_, v_ in kern.items():
         merged.setdefault(k_.split("[")[0], dict(ms=0.0))["ms"] += v_["ms"]
@@ -261,7 +288,19 @@ def run_ours(args, rank, world, device):
                      "peak_source": peaks["source"] + " (sustained bf16, MEASURED_PEAKS.json)",
                      "kernel_share_of_step": g["ms"] / total_ms, "launches_per_step": g["launches"],
                      "whole_step_tflops": flops / (ms_step * 1e-3) / 1e12,
-                     "whole_step_frac": flops / (ms_step * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]},
+                     "whole_step_frac": flops / (ms_step * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"],
+                     # the out_proj / linear2 projections run inside gemm_ln_tcgen05 (GEMM + residual + LayerNorm in one cluster
+                     # kernel): their time includes the LayerNorm's memory traffic, so they are listed apart from the plain GEMMs
+                     "fused_gemm_layernorm": None if not fused["launches"] else {
+                         "kernel": "gemm_ln_tcgen05 (acai_linear_layernorm)", "launches_per_step": fused["launches"],
+                         "ms_per_step": fused["ms"], "tflops": fused["flops"] / (fused["ms"] * 1e-3) / 1e12,
+                         "algorithmic_gb_per_s": fused["bytes"] / (fused["ms"] * 1e-3) / 1e9,
+                         "hbm_frac": fused["bytes"] / (fused["ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"]},
+                     "all_tcgen05_gemm_launches": {
+                         "achieved": (g["flops"] + fused["flops"]) / ((g["ms"] + fused["ms"]) * 1e-3) / 1e12,
+                         "frac": (g["flops"] + fused["flops"]) / ((g["ms"] + fused["ms"]) * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"],
+                         "share_of_step": (g["ms"] + fused["ms"]) / total_ms,
+                         "note": "includes the LayerNorm work that round 1 ran (and timed) as separate kernels"}},
         "kernels_ms_per_step": {k: round(v["ms"], 3) for k, v in sorted(merged.items(), key=lambda kv: -kv[1]["ms"])},
         "gemm_shapes": gemm_shapes,
     }
@@ -269,13 +308,17 @@ def run_ours(args, rank, world, device):
     line["config"]["residual_stream"] = ("fp32 (what torch.autocast does to the reference: LayerNorm and residual adds in fp32, "
                                          "bf16 Linear / attention operands)" if layers.STREAM_FP32 else "bf16 (ACAI_STREAM=bf16)")
     line["_encoder_out_first8"] = out_all[:8]          # popped by main(): parity against the CPU oracle's output
+    if alt is not None:
+        line["encoder_bf16_stream"] = alt
     if stock is not None:
         line["torch_eager_b200"] = stock["timing"]
-        line["parity"] = {"encoder_bf16_vs_stock_torch_fp32_on_gpu": stock["parity"]}
+        line["parity"] = {"encoder_bf16_vs_stock_torch_fp32_on_gpu": stock["parity"]["ours"]}
+        if alt is not None:
+            alt["parity_vs_stock_torch_fp32_on_gpu"] = stock["parity"]["bf16_stream"]
     return line
 
 
-def torch_eager_encoder(enc, imgs_dev, lens, ours_cpu, steps=5):
+def torch_eager_encoder(enc, imgs_dev, lens, ours, steps=5):
     """Stock torch 2.11 eager on the SAME B200, the number SURVEY 6 / 8(d) calls the one to beat: the reference's encoder is
     nn.Unfold + nn.Linear + a position slice per image in a Python loop, then nn.TransformerEncoder (models.py:36-79).  Built
     here from torch.nn alone with this bench's weights (the state_dict keys are torch's own), run the two ways the reference
@@ -325,7 +368,8 @@ def torch_eager_encoder(enc, imgs_dev, lens, ours_cpu, steps=5):
     from oracle import parity as P
     return {"timing": dict(out, what="stock torch.nn.TransformerEncoder + per-image unfold/linear/PE loop, same weights, same 64 "
                                      "systems, same GPU; no kernel of this repo on that path"),
-            "parity": dict(P.errors(ours_cpu, ref, valid), systems=NUM_SYSTEMS, tokens=int(valid.sum()), gate=P.BF16_TOL)}
+            "parity": {name: dict(P.errors(t_, ref, valid), systems=NUM_SYSTEMS, tokens=int(valid.sum()), gate=P.BF16_TOL)
+                       for name, t_ in ours.items()}}
 
 
 # ------------------------------------------------------------------------------------------ strong scaling: ONE batch, sharded
@@ -883,6 +927,11 @@ def secondary_summary(line):
                    config0_gpu_fp32_tokens_per_s=round(c0["gpu_fp32"]["tokens_per_s"], 1),
                    config0_cpu_tokens_per_s=round(c0["cpu_oracle"]["tokens_per_s"], 2) if c0.get("cpu_oracle") else None,
                    config0_fp32_tokens_exact=c0.get("fp32_tokens_exact"))
+    ab = line.get("encoder_bf16_stream")
+    if ab:
+        out.update(encoder_bf16_stream_systems_per_s=round(ab["value"], 1))
+        if "parity_vs_stock_torch_fp32_on_gpu" in ab:
+            out["encoder_bf16_stream_max_rel"] = round(ab["parity_vs_stock_torch_fp32_on_gpu"]["max_rel"], 5)
     ss = line.get("strong_scaling")
     if ss:
         out.update(strong_512_systems_per_s=round(ss["value"], 1), strong_imbalance=round(ss["imbalance_max_over_mean"], 4))

@@ -523,9 +523,11 @@ def run_decode(args, rank, world, device):
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms_total, ms_prefill, kern_ms, ms_t512, e2e_wall = (float(v) for v in t)
-    cpu = parity = None
+    cpu = parity = stock = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu, parity = decode_cpu_baseline_and_parity(dec, vit, lat_host, mask_host, device)
+    if rank == 0 and not args.no_torch_eager:
+        stock = torch_eager_decode(dec, lat_dev, mask_dev)
     pages_per_seq = eng.pages_per_seq
     del eng
     vit.__dict__.pop("_acai_engines", None)
@@ -549,6 +551,8 @@ def run_decode(args, rank, world, device):
              "residual_stream": "fp32" if eng_stream_fp32() else "bf16"}
     if cpu is not None:
         extra["cpu_baseline"], extra["parity"] = cpu, parity
+    if stock is not None:
+        extra["torch_eager_b200"] = stock
     return dict(extra, **{
         "metric": "batched KV-cached LMX greedy decode tokens/sec", "value": world * B * steps / (ms_total * 1e-3),
         "unit": "tokens/s", "ms_per_step": ms_step, "prefill_ms": ms_prefill,
@@ -566,6 +570,67 @@ def run_decode(args, rank, world, device):
                      "algorithmic_bytes_per_launch": kern_bytes, "ms_per_launch": kern_ms,
                      "peak_source": peaks["source"] + " (HBM copy, MEASURED_PEAKS.json)"},
     })
+
+
+def torch_eager_decode(dec, lat_dev, mask_dev, steps=64):
+    """Stock torch 2.11 eager on the same B200 for the decode leg: the reference's cached greedy step (kv_caching.py:190-223,
+    292-302; models.py:575-583) written with torch.nn.functional only - F.linear, F.scaled_dot_product_attention,
+    F.layer_norm, pre-allocated (B, H, T, d) bf16 caches updated by slice assignment - under bf16 autocast, with this
+    bench's weights.  No kernel of this repo on that path.  `steps` greedy steps at the full batch after the cross-KV
+    prefill; tokens/s is quoted on the steps (their self-attention caches are still short: an upper bound for stock torch)."""
+    import torch.nn.functional as TF
+    B, S, D = lat_dev.shape
+    H, d = DEC_H, DEC_D // DEC_H
+    P = {k: v.detach() for k, v in dec.named_parameters()}
+    L = DEC_LAYERS
+    dev = lat_dev.device
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        kc = [torch.zeros(B, H, steps + 1, d, dtype=torch.bfloat16, device=dev) for _ in range(L)]
+        vc = [torch.zeros(B, H, steps + 1, d, dtype=torch.bfloat16, device=dev) for _ in range(L)]
+        cross = []
+        for i in range(L):
+            pre = f"decoder_blocks.layers.{i}.multihead_attn."
+            kv = TF.linear(lat_dev, P[pre + "in_proj_weight"][D:], P[pre + "in_proj_bias"][D:])
+            k, v = kv.chunk(2, dim=-1)
+            cross.append((k.view(B, S, H, d).transpose(1, 2), v.view(B, S, H, d).transpose(1, 2)))
+        amask = (~mask_dev)[:, None, None, :]
+        seqs = torch.zeros(B, steps + 1, dtype=torch.long, device=dev)
+
+        def step(t):
+            x = P["vocab_embedding.weight"][seqs[:, t - 1]] + P["pos_embedding"][t]
+            x = x[:, None, :]
+            for i in range(L):
+                pre = f"decoder_blocks.layers.{i}."
+                qkv = TF.linear(x, P[pre + "self_attn.in_proj_weight"], P[pre + "self_attn.in_proj_bias"])
+                q, k, v = (c.view(B, H, 1, d) for c in qkv.chunk(3, dim=-1))
+                kc[i][:, :, t - 1:t] = k
+                vc[i][:, :, t - 1:t] = v
+                a = TF.scaled_dot_product_attention(q, kc[i][:, :, :t], vc[i][:, :, :t]).transpose(1, 2).flatten(2)
+                x = TF.layer_norm(x + TF.linear(a, P[pre + "self_attn.out_proj.weight"], P[pre + "self_attn.out_proj.bias"]), (D,),
+                                  P[pre + "norm1.weight"], P[pre + "norm1.bias"], 1e-5)
+                qc = TF.linear(x, P[pre + "multihead_attn.in_proj_weight"][:D], P[pre + "multihead_attn.in_proj_bias"][:D]).view(B, H, 1, d)
+                c = TF.scaled_dot_product_attention(qc, cross[i][0], cross[i][1], attn_mask=amask).transpose(1, 2).flatten(2)
+                x = TF.layer_norm(x + TF.linear(c, P[pre + "multihead_attn.out_proj.weight"], P[pre + "multihead_attn.out_proj.bias"]),
+                                  (D,), P[pre + "norm2.weight"], P[pre + "norm2.bias"], 1e-5)
+                f = TF.linear(TF.gelu(TF.linear(x, P[pre + "linear1.weight"], P[pre + "linear1.bias"])),
+                              P[pre + "linear2.weight"], P[pre + "linear2.bias"])
+                x = TF.layer_norm(x + f, (D,), P[pre + "norm3.weight"], P[pre + "norm3.bias"], 1e-5)
+            x = TF.layer_norm(x, (D,), P["decoder_blocks.norm.weight"], P["decoder_blocks.norm.bias"], 1e-6)
+            logits = TF.linear(x, P["unembed.weight"], P["unembed.bias"]).squeeze(1)
+            seqs[:, t] = torch.argmax(logits, dim=-1)
+        for t in (1, 2):
+            step(t)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for t in range(3, steps + 1):
+            step(t)
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / (steps - 2)
+    return {"ms_per_step": ms, "value": B / (ms * 1e-3), "unit": "tokens/s", "steps": steps - 2,
+            "what": "stock torch.nn.functional cached greedy step (F.linear / SDPA / F.layer_norm, bf16 autocast, bf16 caches), "
+                    "B = %d, the first %d steps: the self-attention caches are still short, so this flatters stock torch" % (B, steps)}
 
 
 def eng_stream_fp32():
@@ -909,7 +974,8 @@ def secondary_summary(line):
                    decode_attn_kernel_hbm_frac=round(d["roofline"]["frac"], 4),
                    decode_e2e_tokens_per_s=round(d["e2e"]["value"], 1),
                    decode_cpu_tokens_per_s=round(d["cpu_baseline"]["value"], 2) if d.get("cpu_baseline") else None,
-                   decode_launches_per_step=d["gpu_launches_per_step"])
+                   decode_launches_per_step=d["gpu_launches_per_step"],
+                   decode_torch_eager_tokens_per_s=round(d["torch_eager_b200"]["value"], 1) if d.get("torch_eager_b200") else None)
     for key, tag in (("train_teacher_forced", "tf"), ("train_mae", "mae")):
         t = line.get(key)
         if t:

@@ -15,6 +15,7 @@
 //       dV += P^T dO_i , dK += dS^T Q_i        TS, B = dO_i / Q_i MN-major
 // Seven GEMMs instead of the five of a fused single pass, but no atomics and no cross-CTA reduction: every output
 // element has exactly one writer and a fixed summation order (bitwise reproducible gradients).
+#include <cstdlib>
 #include <type_traits>
 
 #include "common.cuh"
@@ -105,63 +106,85 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // (helper warps: converged loops, one elected lane issues - see ptx::elect_one_sync)
+  const int u_nkv = __shfl_sync(0xffffffffu, n_kv, 0);
   if (warp == 8) {
-    if (lane == 0 && n_kv > 0) {
+    if (u_nkv > 0) {
       const int hcol = (h * DH) & ~63;
-      ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
-      ptx::tma_load_2d(smem + OFF_A0, &tma_q, a_full, hcol, q0 + qb * BIG);
-      ptx::tma_load_2d(smem + OFF_A1, &tma_do, a_full, hcol, q0 + qb * BIG);
+      const int qrow = __shfl_sync(0xffffffffu, q0 + qb * BIG, 0);
+      int krow = __shfl_sync(0xffffffffu, k0, 0);
+      if (ptx::elect_one_sync()) {
+        ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
+        ptx::tma_load_2d(smem + OFF_A0, &tma_q, a_full, hcol, qrow);
+        ptx::tma_load_2d(smem + OFF_A1, &tma_do, a_full, hcol, qrow);
+      }
+      __syncwarp();
       int s = 0; uint32_t ph = 0;
-      for (int j = 0; j < n_kv; ++j) {
+      for (int j = 0; j < u_nkv; ++j, krow += SMALL) {
         ptx::mbar_wait(&b_empty[s], ph ^ 1);
-        ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
-        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_k, &b_full[s], hcol, k0 + j * SMALL);
-        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_v, &b_full[s], hcol, k0 + j * SMALL);
+        if (ptx::elect_one_sync()) {
+          ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
+          ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_k, &b_full[s], hcol, krow);
+          ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_v, &b_full[s], hcol, krow);
+        }
+        __syncwarp();
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 9) {
-    if (lane == 0 && n_kv > 0) {
+    if (u_nkv > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
       constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, DH, false, true);     // B MN-major
+      const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0);
       const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);    // DH = 32: the tile holds a head pair, 64-byte start offset
       const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024) + hoff;
       const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024) + hoff;
-      auto kdesc_of = [&](int j) { return ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + (j % STAGES) * SMALLTILE), 1024) + hoff; };
-      auto vdesc_of = [&](int j) { return ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + (j % STAGES) * SMALLTILE), 1024) + hoff; };
+      const uint64_t kdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0), 1024) + hoff;
+      const uint64_t vdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1), 1024) + hoff;
+      auto kdesc_of = [&](int j) { return kdesc0 + (uint64_t)((j % STAGES) * (SMALLTILE >> 4)); };
+      auto vdesc_of = [&](int j) { return vdesc0 + (uint64_t)((j % STAGES) * (SMALLTILE >> 4)); };
       auto issue_s = [&](int j) {                  // S_j into buffer j & 1 (waits for K_j / V_j to land)
         ptx::mbar_wait(&b_full[j % STAGES], (j / STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t kd = kdesc_of(j);
+        if (ptx::elect_one_sync()) {
+          const uint64_t kd = kdesc_of(j);
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + (j & 1) * 64, qdesc + 2 * k, kd + 2 * k, IDESC_S, k != 0);
+          for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tb0 + (j & 1) * 64, qdesc + 2 * k, kd + 2 * k, IDESC_S, k != 0);
+        }
+        __syncwarp();
       };
       auto issue_dp = [&](int j) {                 // dP_j, then S_j and dP_j are announced together
-        const uint64_t vd = vdesc_of(j);
+        if (ptx::elect_one_sync()) {
+          const uint64_t vd = vdesc_of(j);
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + 128, dodesc + 2 * k, vd + 2 * k, IDESC_S, k != 0);
-        ptx::umma_commit(&sp_full[j & 1]);
+          for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tb0 + 128, dodesc + 2 * k, vd + 2 * k, IDESC_S, k != 0);
+          ptx::umma_commit(&sp_full[j & 1]);
+        }
+        __syncwarp();
       };
       ptx::mbar_wait(a_full, 0);
       issue_s(0);
       issue_dp(0);
-      if (n_kv > 1) issue_s(1);
-      for (int j = 0; j < n_kv; ++j) {
-        if (j + 1 < n_kv) {
+      if (u_nkv > 1) issue_s(1);
+      for (int j = 0; j < u_nkv; ++j) {
+        if (j + 1 < u_nkv) {
           ptx::mbar_wait(dp_free, j & 1);          // block j's dP is in registers: the buffer can take dP_{j+1}
           ptx::tc_fence_after();
           issue_dp(j + 1);
         }
         ptx::mbar_wait(&ds_full[j & 1], (j >> 1) & 1);
         ptx::tc_fence_after();
-        const uint64_t kd = kdesc_of(j);
+        if (ptx::elect_one_sync()) {
+          const uint64_t kd = kdesc_of(j);
 #pragma unroll
-        for (int kk = 0; kk < SMALL / 16; ++kk)
-          ptx::umma_f16_ts(tmem_base + 192, tmem_base + (j & 1) * 64 + (kk >> 1) * 32 + (kk & 1) * 8,
-                           kd + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (j | kk) != 0);
-        ptx::umma_commit(&b_empty[j % STAGES]);
-        if (j == n_kv - 1) ptx::umma_commit(acc_full);
-        if (j + 2 < n_kv) issue_s(j + 2);          // overwrites dS_j: tcgen05 ops execute in issue order
+          for (int kk = 0; kk < SMALL / 16; ++kk)
+            ptx::umma_f16_ts(tb0 + 192, tb0 + (j & 1) * 64 + (kk >> 1) * 32 + (kk & 1) * 8,
+                             kd + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (j | kk) != 0);
+          ptx::umma_commit(&b_empty[j % STAGES]);
+          if (j == u_nkv - 1) ptx::umma_commit(acc_full);
+        }
+        __syncwarp();
+        if (j + 2 < u_nkv) issue_s(j + 2);          // overwrites dS_j: tcgen05 ops execute in issue order
       }
     }
   } else {
@@ -321,64 +344,81 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // (helper warps: converged loops, one elected lane issues - see ptx::elect_one_sync)
+  const int u_nit = __shfl_sync(0xffffffffu, n_it, 0);
   if (warp == 8) {
-    if (lane == 0 && n_it > 0) {
-      ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
+    if (u_nit > 0) {
       const int hcol = (h * DH) & ~63;
-      ptx::tma_load_2d(smem + OFF_A0, &tma_k, a_full, hcol, k0 + kb * BIG);
-      ptx::tma_load_2d(smem + OFF_A1, &tma_v, a_full, hcol, k0 + kb * BIG);
+      const int krow = __shfl_sync(0xffffffffu, k0 + kb * BIG, 0);
+      int qrow = __shfl_sync(0xffffffffu, q0 + i0 * SMALL, 0);
+      if (ptx::elect_one_sync()) {
+        ptx::mbar_arrive_expect_tx(a_full, 2 * BIGTILE);
+        ptx::tma_load_2d(smem + OFF_A0, &tma_k, a_full, hcol, krow);
+        ptx::tma_load_2d(smem + OFF_A1, &tma_v, a_full, hcol, krow);
+      }
+      __syncwarp();
       int s = 0; uint32_t ph = 0;
-      for (int it = 0; it < n_it; ++it) {
+      for (int it = 0; it < u_nit; ++it, qrow += SMALL) {
         ptx::mbar_wait(&b_empty[s], ph ^ 1);
-        ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
-        ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_q, &b_full[s], hcol, q0 + (i0 + it) * SMALL);
-        ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_do, &b_full[s], hcol, q0 + (i0 + it) * SMALL);
+        if (ptx::elect_one_sync()) {
+          ptx::mbar_arrive_expect_tx(&b_full[s], 2 * SMALLTILE);
+          ptx::tma_load_2d(smem + OFF_B0 + s * SMALLTILE, &tma_q, &b_full[s], hcol, qrow);
+          ptx::tma_load_2d(smem + OFF_B1 + s * SMALLTILE, &tma_do, &b_full[s], hcol, qrow);
+        }
+        __syncwarp();
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 9) {
-    if (lane == 0 && n_it > 0) {
+    if (u_nit > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SMALL);
       constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, DH, false, true);
+      const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0);
       const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);
       const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A0), 1024) + hoff;
       const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_A1), 1024) + hoff;
       const uint64_t pdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_P), 1024);
       const uint64_t dsdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_DS), 1024);
+      const uint64_t qdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0), 1024) + hoff;
+      const uint64_t dodesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1), 1024) + hoff;
       auto issue_sp = [&](int it) {                // S^T_it and dP^T_it (waits for Q_it / dO_it to land)
         const int st = it % STAGES;
         ptx::mbar_wait(&b_full[st], (it / STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024) + hoff;
-        const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024) + hoff;
+        if (ptx::elect_one_sync()) {
+          const uint64_t qdesc = qdesc0 + (uint64_t)(st * (SMALLTILE >> 4)), dodesc = dodesc0 + (uint64_t)(st * (SMALLTILE >> 4));
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base, kdesc + 2 * k, qdesc + 2 * k, IDESC_S, k != 0);       // S^T
+          for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tb0, kdesc + 2 * k, qdesc + 2 * k, IDESC_S, k != 0);       // S^T
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tmem_base + 64, vdesc + 2 * k, dodesc + 2 * k, IDESC_S, k != 0); // dP^T
-        ptx::umma_commit(sp_full);
+          for (int k = 0; k < DH / 16; ++k) ptx::umma_f16_ss(tb0 + 64, vdesc + 2 * k, dodesc + 2 * k, IDESC_S, k != 0); // dP^T
+          ptx::umma_commit(sp_full);
+        }
+        __syncwarp();
       };
       ptx::mbar_wait(a_full, 0);
       issue_sp(0);
-      for (int it = 0; it < n_it; ++it) {
+      for (int it = 0; it < u_nit; ++it) {
         const int st = it % STAGES;
-        if (it + 1 < n_it) {                         // issued BEFORE dV / dK of block it: runs under block it's exponentials
+        if (it + 1 < u_nit) {                         // issued BEFORE dV / dK of block it: runs under block it's exponentials
           ptx::mbar_wait(sp_free, it & 1);
           ptx::tc_fence_after();
           issue_sp(it + 1);
         }
-        const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0 + st * SMALLTILE), 1024) + hoff;
-        const uint64_t dodesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1 + st * SMALLTILE), 1024) + hoff;
         ptx::mbar_wait(ds_full, it & 1);
         ptx::tc_fence_after();
+        if (ptx::elect_one_sync()) {
+          const uint64_t qdesc = qdesc0 + (uint64_t)(st * (SMALLTILE >> 4)), dodesc = dodesc0 + (uint64_t)(st * (SMALLTILE >> 4));
 #pragma unroll
-        for (int kk = 0; kk < SMALL / 16; ++kk)      // dV += P^T dO_i   (A = P^T [128 keys x 64 queries] K-major in smem)
-          ptx::umma_f16_ss(tmem_base + 128, pdesc + 2 * kk, dodesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+          for (int kk = 0; kk < SMALL / 16; ++kk)      // dV += P^T dO_i   (A = P^T [128 keys x 64 queries] K-major in smem)
+            ptx::umma_f16_ss(tb0 + 128, pdesc + 2 * kk, dodesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
 #pragma unroll
-        for (int kk = 0; kk < SMALL / 16; ++kk)      // dK += dS^T Q_i
-          ptx::umma_f16_ss(tmem_base + 192, dsdesc + 2 * kk, qdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
-        ptx::umma_commit(&b_empty[st]);
-        ptx::umma_commit(pd_free);
-        if (it == n_it - 1) ptx::umma_commit(acc_full);
+          for (int kk = 0; kk < SMALL / 16; ++kk)      // dK += dS^T Q_i
+            ptx::umma_f16_ss(tb0 + 192, dsdesc + 2 * kk, qdesc + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, (it | kk) != 0);
+          ptx::umma_commit(&b_empty[st]);
+          ptx::umma_commit(pd_free);
+          if (it == u_nit - 1) ptx::umma_commit(acc_full);
+        }
+        __syncwarp();
       }
     }
   } else {
@@ -526,6 +566,396 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
   if (warp == 8) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
+// ------------------------------------------------------------------------------------------ grouped variant (head_dim 64)
+// Round 2.  The two kernels above are bound by none of their pipes: their elementwise warps sit in hand-off latencies
+// (profiles/r1i_attention_backward.md) and two CTAs per SM give the SM only two independent chains of 64 columns.  What
+// limits the work in flight is TMEM (fp32 S and dP cost 128 columns per 64-wide block) and the shared-memory operand
+// traffic of small MMAs.  This variant:
+//   * keeps the CTA's 128 resident rows (K and V for dK/dV, Q and dO for dQ) in TMEM as the A operands (TS form, 32 columns
+//     each, written once by the elementwise threads): an S MMA then reads only its 1 KB B slice from shared memory, which
+//     is what makes N = 32 MMAs affordable (A from shared memory would be 5 KB per 16 clk of math);
+//   * streams the other operand in 32-row sub-blocks; sub-block s belongs to group s % G = four warps (thread = resident
+//     row, 32 columns) with its OWN TMEM columns: S, dP (fp32) and the bf16 operands P^T / dS^T it hands back;
+//   * splits the MMA issue over two warps: one issues S / dP of a group's NEXT sub-block as soon as the group has the
+//     current one in registers (so the tensor-pipe round trip runs under the group's own exponentials), the other issues
+//     the accumulating MMAs (dV / dK or dQ) when the bf16 operands are written; every true dependency between the two is
+//     an mbarrier, none relies on issue order across threads;
+//   * touches shared memory only for the streamed tiles (4 KB each, read twice) and the 32 L / delta of a sub-block.
+// TMEM (one CTA per SM): resident rows 0..63; group g at 64 + 96 g: S, dP (32 + 32), P^T, dS^T (16 + 16); accumulators after
+// the groups.  MODE 0 = dK/dV: 3 groups, 480 columns;  MODE 1 = dQ: 4 groups, 512 columns.
+// Per 128 x 64 block-equivalent: tensor pipe 512 clk (dK/dV) / 384 clk (dQ), MUFU 512 clk, shared memory 256 clk.
+namespace fg {
+constexpr int BIG = 128, SUB = 32, D = 64;
+constexpr int groups(int mode) { return mode == 0 ? 3 : 4; }
+constexpr int stages(int mode) { return 4 * groups(mode); }      // a multiple of 2 G: see the helper warps
+constexpr int issuers(int mode) { return mode == 0 ? 1 : 2; }             // S / dP issuer warps
+constexpr int threads(int mode) { return (groups(mode) * 4 + 2 + issuers(mode)) * 32; }   // + TMA producer, S / dP issuers, accumulate issuer
+constexpr uint32_t SUBTILE = SUB * D * 2;           // 4 KB
+constexpr int MAX_STAGES = 16;
+constexpr uint32_t OFF_B0 = 0, OFF_B1 = MAX_STAGES * SUBTILE, OFF_VEC = 2 * MAX_STAGES * SUBTILE;
+constexpr uint32_t OFF_BAR = OFF_VEC + 4 * 2 * 128 * 4;   // per group 2 x (32 L, 32 delta, 32 hash row constants, 32 row bases)
+constexpr size_t SMEM = OFF_BAR + 512;
+constexpr uint32_t TMEM_COLS = 512, COL_R0 = 0, COL_R1 = 32, COL_G = 64, GSTRIDE = 96;
+constexpr uint32_t col_acc0(int mode) { return COL_G + groups(mode) * GSTRIDE; }
+}  // namespace fg
+
+struct G4Rows { const __nv_bfloat16* r0; const __nv_bfloat16* r1; int64_t s0, s1; };   // the resident operands and their row strides
+
+template <int MODE, bool DROP>
+__global__ void __launch_bounds__(fg::threads(MODE), 1)
+attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ CUtensorMap tma_b1, AttnBwdParams p, G4Rows rr) {
+  using namespace fg;
+  constexpr int G = groups(MODE), EW = G * 4, STAGES = stages(MODE), NI = issuers(MODE);
+  static_assert(STAGES <= MAX_STAGES && STAGES % (2 * G) == 0, "stage ring");
+  constexpr uint32_t COL_ACC0 = col_acc0(MODE), COL_ACC1 = COL_ACC0 + 64;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+  uint64_t* b_full = bars;                     // STAGES: streamed sub-block s (both tiles) has landed
+  uint64_t* b_empty = b_full + MAX_STAGES;     // STAGES: the last MMA reading it has completed
+  uint64_t* r_ready = b_empty + MAX_STAGES;    // the resident rows are in TMEM (8 warps)
+  uint64_t* sp_full = r_ready + 1;             // 4: S and dP of the group's sub-block are in TMEM
+  uint64_t* sp_free = sp_full + 4;             // 4: ... and in the group's registers (4 warps)
+  uint64_t* ds_full = sp_free + 4;             // 4: the group's bf16 operands are in TMEM (4 warps)
+  uint64_t* pd_free = ds_full + 4;             // 4: the accumulating MMAs have consumed them
+  uint64_t* acc_full = pd_free + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  float* vec = reinterpret_cast<float*>(smem + OFF_VEC);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z, h = blockIdx.y, tb = blockIdx.x;
+  const int q0 = p.cu_q[b], lq = p.cu_q[b + 1] - q0, k0 = p.cu_k[b], lk = p.cu_k[b + 1] - k0;
+  const int rows_len = MODE == 0 ? lk : lq;
+  if (tb * BIG >= rows_len) return;
+  const int shift = lk - lq;
+  int s0 = 0, n_sub;                           // first streamed sub-block and how many this tile needs
+  if (MODE == 0) {                             // causal: key kr is seen by queries q >= kr - shift
+    if (p.causal) { const int first = tb * BIG - shift; s0 = first > 0 ? first / SUB : 0; }
+    const int n_all = (lq + SUB - 1) / SUB;
+    n_sub = n_all > s0 ? n_all - s0 : 0;
+  } else {
+    int kv_end = lk;
+    if (p.causal) { const int last = tb * BIG + BIG + shift; kv_end = last < lk ? (last < 0 ? 0 : last) : lk; }
+    n_sub = (kv_end + SUB - 1) / SUB;
+  }
+  const int res_base = MODE == 0 ? k0 : q0, str_base = MODE == 0 ? q0 : k0;
+
+  if (warp == EW + NI + 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
+    ptx::mbar_init(r_ready, 8);
+    for (int g = 0; g < 4; ++g) {
+      ptx::mbar_init(&sp_full[g], 1); ptx::mbar_init(&sp_free[g], 4); ptx::mbar_init(&ds_full[g], 4); ptx::mbar_init(&pd_free[g], 1);
+    }
+    ptx::mbar_init(acc_full, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == EW) {
+    if (lane == 0) { ptx::prefetch_tensormap(&tma_b0); ptx::prefetch_tensormap(&tma_b1); }
+    ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp >= EW) {
+    // The three helper warps walk their loops CONVERGED (every lane polls the barriers) and one elected lane issues; all
+    // operands are provably warp-uniform (shuffles of lane 0), see ptx::elect_one_sync.  The loops are unrolled over one
+    // round of the stage ring (STAGES = a multiple of 2 G): stage, group and every group-barrier parity are then compile-time
+    // constants and the descriptors constant offsets from two uniform registers - with run-time stage / group arithmetic one
+    // trip of the S / dP loop cost ~500 clk of (dependent, single-warp) issue and was the bound of the whole kernel.
+    const int nsub = __shfl_sync(0xffffffffu, n_sub, 0);
+    const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t d0_base = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B0), 1024);
+    const uint64_t d1_base = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_B1), 1024);
+    if (warp == EW) {
+      // ---------------------------------------------------------------- TMA producer
+      int row = __shfl_sync(0xffffffffu, str_base + s0 * SUB, 0);
+      uint32_t ph = 0;
+      for (int sb = 0; sb < nsub; sb += STAGES, ph ^= 1) {
+#pragma unroll
+        for (int u = 0; u < STAGES; ++u) {
+          if (sb + u >= nsub) break;
+          ptx::mbar_wait(&b_empty[u], ph ^ 1);
+          if (ptx::elect_one_sync()) {
+            ptx::mbar_arrive_expect_tx(&b_full[u], 2 * SUBTILE);
+            ptx::tma_load_2d(smem + OFF_B0 + u * SUBTILE, &tma_b0, &b_full[u], h * D, row);
+            ptx::tma_load_2d(smem + OFF_B1 + u * SUBTILE, &tma_b1, &b_full[u], h * D, row);
+          }
+          __syncwarp();
+          row += SUB;
+        }
+      }
+    } else if (warp <= EW + NI) {
+      // ---------------------------------------------------------------- S / dP issuers: NI warps, warp i serves the groups
+      // g % NI == i (one trip costs ~400 clk of dependent single-warp issue, more than a sub-block's share of any pipe).
+      // A group's sub-blocks must stay with ONE issuer: its sp_free parity wait is only safe in program order.
+      if (nsub > 0) {
+        constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BIG, SUB);
+        const int mine = warp - (EW + 1);
+        ptx::mbar_wait(r_ready, 0);
+        ptx::tc_fence_after();
+        uint32_t ph = 0;
+        for (int sb = 0; sb < nsub; sb += STAGES, ph ^= 1) {
+#pragma unroll
+          for (int u = 0; u < STAGES; ++u) {
+            if ((u % G) % NI != mine) continue;
+            if (sb + u >= nsub) break;
+            const int g = u % G;                           // (compile-time after unrolling; STAGES / G is even, so is the parity)
+            if (sb + u >= G) ptx::mbar_wait(&sp_free[g], (uint32_t)((u / G - 1) & 1));   // the group holds its previous S / dP in registers
+            ptx::mbar_wait(&b_full[u], ph);
+            ptx::tc_fence_after();
+            if (ptx::elect_one_sync()) {
+              const uint64_t d0 = d0_base + (uint64_t)(u * (SUBTILE >> 4)), d1 = d1_base + (uint64_t)(u * (SUBTILE >> 4));
+              const uint32_t cs = tb0 + COL_G + g * GSTRIDE;
+#pragma unroll
+              for (int k = 0; k < D / 16; ++k) {           // S and dP k-steps alternate
+                ptx::umma_f16_ts(cs, tb0 + COL_R0 + k * 8, d0 + 2 * k, IDESC_S, k != 0);
+                ptx::umma_f16_ts(cs + 32, tb0 + COL_R1 + k * 8, d1 + 2 * k, IDESC_S, k != 0);
+              }
+              ptx::umma_commit(&sp_full[g]);
+            }
+            __syncwarp();
+          }
+        }
+      }
+    } else {
+      // ---------------------------------------------------------------- accumulate issuer
+      if (nsub > 0) {
+        constexpr uint32_t IDESC_ACC = ptx::idesc_bf16_f32(BIG, D, false, true);        // B MN-major
+        uint32_t ph = 0;
+        for (int sb = 0; sb < nsub; sb += STAGES, ph ^= 1) {
+#pragma unroll
+          for (int u = 0; u < STAGES; ++u) {
+            if (sb + u >= nsub) break;
+            const int g = u % G;
+            ptx::mbar_wait(&ds_full[g], (uint32_t)((u / G) & 1));
+            ptx::mbar_wait(&b_full[u], ph);                // (completed long ago: orders this thread after the TMA writes)
+            ptx::tc_fence_after();
+            if (ptx::elect_one_sync()) {
+              const uint64_t d0 = d0_base + (uint64_t)(u * (SUBTILE >> 4)), d1 = d1_base + (uint64_t)(u * (SUBTILE >> 4));
+              const uint32_t cp = tb0 + COL_G + g * GSTRIDE + 64;    // P^T (16 columns), dS^T / dS at + 16
+              const uint32_t acc = (sb + u) != 0;
+              if (MODE == 0) {
+#pragma unroll
+                for (int kk = 0; kk < SUB / 16; ++kk) {
+                  // dV += P^T dO_s   (16 queries = 8 packed columns per step)
+                  ptx::umma_f16_ts(tb0 + COL_ACC0, cp + kk * 8, d1 + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, kk ? 1u : acc);
+                  // dK += dS^T Q_s
+                  ptx::umma_f16_ts(tb0 + COL_ACC1, cp + 16 + kk * 8, d0 + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, kk ? 1u : acc);
+                }
+              } else {
+#pragma unroll
+                for (int kk = 0; kk < SUB / 16; ++kk)      // dQ += dS K_s
+                  ptx::umma_f16_ts(tb0 + COL_ACC0, cp + 16 + kk * 8, d0 + (uint64_t)kk * (16 * 128 >> 4), IDESC_ACC, kk ? 1u : acc);
+              }
+              ptx::umma_commit(&b_empty[u]);
+              ptx::umma_commit(&pd_free[g]);
+              if (sb + u == nsub - 1) ptx::umma_commit(acc_full);
+            }
+            __syncwarp();
+          }
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ elementwise warps (thread = resident row)
+    const int qtr = warp & 3, g = warp >> 2, r = qtr * 32 + lane;
+    const int row = tb * BIG + r;
+    const bool valid = row < rows_len;
+    const uint32_t lane_addr = (uint32_t)(qtr * 32) << 16;
+    const float sl2 = p.scale_log2;
+    if (n_sub > 0 && g < 2) {                    // groups 0 / 1 bring the two resident operands into TMEM (bf16 pairs per column)
+      const __nv_bfloat16* base = g == 0 ? rr.r0 : rr.r1;
+      const int64_t stride = g == 0 ? rr.s0 : rr.s1;
+      const uint4* src = reinterpret_cast<const uint4*>(base + (int64_t)(res_base + (valid ? row : 0)) * stride + (int64_t)h * D);
+      uint32_t rv[32];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint4 v4 = valid ? __ldg(src + c) : make_uint4(0u, 0u, 0u, 0u);
+        rv[4 * c] = v4.x; rv[4 * c + 1] = v4.y; rv[4 * c + 2] = v4.z; rv[4 * c + 3] = v4.w;
+      }
+      ptx::tmem_st_32x32(tmem_base + lane_addr + (g == 0 ? COL_R0 : COL_R1), rv);
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(r_ready);
+    }
+    const uint32_t tmem_s = tmem_base + lane_addr + COL_G + g * GSTRIDE;      // S, dP at + 32, P^T at + 64, dS^T / dS at + 80
+    // MODE 1: per-row constants
+    float L = INFINITY, dl = 0.0f;
+    int my_end = 0;
+    uint64_t rowkey = 0; uint32_t rowconst = 0;
+    if (MODE == 1) {
+      if (valid) {
+        L = p.lse[(int64_t)h * p.total_q + q0 + row];
+        dl = p.delta[(int64_t)h * p.total_q + q0 + row];
+        my_end = p.causal ? max(0, min(lk, row + shift + 1)) : lk;
+      }
+      rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? row : 0));
+      if (DROP) rowconst = attn_drop_rowconst(p.drop.seed, rowkey);
+    }
+    // MODE 0: the sub-block's 32 L / delta (and hash constants) are staged per group, one value per thread, one sub-block ahead
+    float* vg = vec + g * 256;
+    auto stage_load = [&](int s) -> uint32_t {
+      const int q = (s0 + s) * SUB + (r & 31), which = r >> 5;
+      if (which == 0) return __float_as_uint(q < lq ? __ldg(p.lse + (int64_t)h * p.total_q + q0 + q) : INFINITY);
+      if (which == 1) return __float_as_uint(q < lq ? __ldg(p.delta + (int64_t)h * p.total_q + q0 + q) : 0.0f);
+      if (DROP) {
+        const uint64_t rk = (uint64_t)h * p.total_q + (uint64_t)(q0 + q);
+        return which == 2 ? attn_drop_rowconst(p.drop.seed, rk) : (uint32_t)(rk << 15);
+      }
+      return 0u;
+    };
+    auto group_sync = [&]() { asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory"); };
+    if (MODE == 0 && g < n_sub) {
+      reinterpret_cast<uint32_t*>(vg)[r] = stage_load(g);
+      group_sync();
+    }
+    int n = 0;
+    for (int s = g; s < n_sub; s += G, ++n) {
+      const int cbase = (s0 + s) * SUB;            // first streamed row of this sub-block (query for MODE 0, key for MODE 1)
+      const float* vb = vg + (n & 1) * 128;
+      uint32_t staged_next = 0u;
+      if (MODE == 0 && s + G < n_sub) staged_next = stage_load(s + G);
+      ptx::mbar_wait(&sp_full[g], n & 1);
+      ptx::tc_fence_after();
+      uint32_t sv[32], dp[32], pk[16], dk[16];
+      ptx::tmem_ld_32x32(tmem_s, sv);
+      ptx::tmem_ld_32x32(tmem_s + 32, dp);
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&sp_free[g]);   // S / dP of this group's next sub-block may be issued
+      const uint64_t sl2x = ptx::pack_f32x2(sl2, sl2);
+      if (MODE == 0) {
+        // columns [0, cm) are masked: queries before the causal diagonal of this key row; everything for rows past the end
+        const int cm = !valid ? SUB : (p.causal ? row - shift - cbase : 0);
+        const float4* vl = reinterpret_cast<const float4*>(vb);
+        const float4* vd = reinterpret_cast<const float4*>(vb + 32);
+        auto block_math = [&](auto masked_tag) {
+          constexpr bool MASKED = decltype(masked_tag)::value;
+#pragma unroll
+          for (int i4 = 0; i4 < 8; ++i4) {
+            const float4 l4 = vl[i4], d4 = vd[i4];
+            float x0, x1, x2, x3;
+            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[4 * i4]), __uint_as_float(sv[4 * i4 + 1])), sl2x,
+                                             ptx::pack_f32x2(-l4.x, -l4.y)), x0, x1);
+            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[4 * i4 + 2]), __uint_as_float(sv[4 * i4 + 3])), sl2x,
+                                             ptx::pack_f32x2(-l4.z, -l4.w)), x2, x3);
+            float p0 = fast_exp2(x0), p1 = fast_exp2(x1), p2 = fast_exp2(x2), p3 = fast_exp2(x3);
+            if (MASKED) {
+              if (4 * i4 < cm) p0 = 0.0f;
+              if (4 * i4 + 1 < cm) p1 = 0.0f;
+              if (4 * i4 + 2 < cm) p2 = 0.0f;
+              if (4 * i4 + 3 < cm) p3 = 0.0f;
+            }
+            const uint64_t pa = ptx::pack_f32x2(p0, p1), pb = ptx::pack_f32x2(p2, p3);
+            const uint64_t dpa = ptx::pack_f32x2(__uint_as_float(dp[4 * i4]), __uint_as_float(dp[4 * i4 + 1]));
+            const uint64_t dpb = ptx::pack_f32x2(__uint_as_float(dp[4 * i4 + 2]), __uint_as_float(dp[4 * i4 + 3]));
+            const uint64_t nda = ptx::pack_f32x2(-d4.x, -d4.y), ndb = ptx::pack_f32x2(-d4.z, -d4.w);
+            float e0, e1, e2, e3, f0, f1, f2, f3;
+            if (DROP) {                                                 // M / (1 - p) of (query column, this key)
+              const uint4 rc = reinterpret_cast<const uint4*>(vb + 64)[i4];
+              const uint4 rb = reinterpret_cast<const uint4*>(vb + 96)[i4];
+              const uint32_t pair = (uint32_t)row >> 1, sh = (row & 1) * 16, thr = p.drop.thr;
+              const float rp = p.drop.rp;
+              const float m0 = ((attn_drop_mix((rb.x + pair) ^ rc.x) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+              const float m1 = ((attn_drop_mix((rb.y + pair) ^ rc.y) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+              const float m2 = ((attn_drop_mix((rb.z + pair) ^ rc.z) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+              const float m3 = ((attn_drop_mix((rb.w + pair) ^ rc.w) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+              const uint64_t ma = ptx::pack_f32x2(m0, m1), mb = ptx::pack_f32x2(m2, m3);
+              ptx::unpack_f32x2(ptx::mul_f32x2(pa, ma), e0, e1);
+              ptx::unpack_f32x2(ptx::mul_f32x2(pb, mb), e2, e3);
+              ptx::unpack_f32x2(ptx::mul_f32x2(pa, ptx::fma_f32x2(ma, dpa, nda)), f0, f1);
+              ptx::unpack_f32x2(ptx::mul_f32x2(pb, ptx::fma_f32x2(mb, dpb, ndb)), f2, f3);
+            } else {
+              e0 = p0; e1 = p1; e2 = p2; e3 = p3;
+              ptx::unpack_f32x2(ptx::mul_f32x2(pa, ptx::add_f32x2(dpa, nda)), f0, f1);
+              ptx::unpack_f32x2(ptx::mul_f32x2(pb, ptx::add_f32x2(dpb, ndb)), f2, f3);
+            }
+            const __nv_bfloat162 hp0 = __floats2bfloat162_rn(e0, e1), hp1 = __floats2bfloat162_rn(e2, e3);
+            const __nv_bfloat162 hd0 = __floats2bfloat162_rn(f0, f1), hd1 = __floats2bfloat162_rn(f2, f3);
+            pk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hp0); pk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hp1);
+            dk[2 * i4] = *reinterpret_cast<const uint32_t*>(&hd0); dk[2 * i4 + 1] = *reinterpret_cast<const uint32_t*>(&hd1);
+          }
+        };
+        if (__any_sync(0xffffffffu, cm > 0)) block_math(std::true_type{});
+        else block_math(std::false_type{});
+      } else {
+        // columns [vis, 32) are masked: keys past this query row's causal bound / the sequence end
+        const int vis = my_end - cbase;
+        const uint64_t nLx = ptx::pack_f32x2(-L, -L), ndlx = ptx::pack_f32x2(-dl, -dl), rpx = ptx::pack_f32x2(p.drop.rp, p.drop.rp);
+        auto block_math = [&](auto masked_tag) {
+          constexpr bool MASKED = decltype(masked_tag)::value;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float x0, x1;
+            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[2 * i]), __uint_as_float(sv[2 * i + 1])), sl2x, nLx), x0, x1);
+            float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+            if (MASKED) {
+              if (2 * i >= vis) p0 = 0.0f;
+              if (2 * i + 1 >= vis) p1 = 0.0f;
+            }
+            uint64_t t2;
+            if (DROP) {
+              const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(cbase / 2 + i));
+              const float k0_ = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) : 0.0f;
+              const float k1_ = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) : 0.0f;
+              t2 = ptx::mul_f32x2(ptx::pack_f32x2(k0_, k1_), rpx);
+            } else {
+              t2 = ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1]));
+            }
+            float d0, d1;
+            ptx::unpack_f32x2(ptx::mul_f32x2(ptx::pack_f32x2(p0, p1), ptx::add_f32x2(t2, ndlx)), d0, d1);
+            const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
+            dk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+          }
+        };
+        if (__all_sync(0xffffffffu, vis >= SUB)) block_math(std::false_type{});
+        else block_math(std::true_type{});
+      }
+      // the accumulating MMAs of this group's previous sub-block have read the bf16 operand columns
+      if (n > 0) { ptx::mbar_wait(&pd_free[g], (n - 1) & 1); ptx::tc_fence_after(); }
+      if (MODE == 0) ptx::tmem_st_32x16(tmem_s + 64, pk);   // P^T
+      ptx::tmem_st_32x16(tmem_s + 80, dk);                  // dS^T (MODE 0) / dS (MODE 1)
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&ds_full[g]);
+      if (MODE == 0) {
+        // the other half of the group's `vec` was last read in sub-block n - 1, which every thread of the group has left
+        reinterpret_cast<uint32_t*>(vg + ((n + 1) & 1) * 128)[r] = staged_next;
+        group_sync();
+      }
+    }
+    if (n_sub > 0) {
+      ptx::mbar_wait(acc_full, 0);
+      ptx::tc_fence_after();
+    }
+    // 32-column output pieces: MODE 0: dV 0..31, dV 32..63, dK 0..31, dK 32..63 (piece i to group i % 3); MODE 1: dQ 0..31, 32..63
+    constexpr int PIECES = MODE == 0 ? 4 : 2;
+    for (int piece = g; piece < PIECES; piece += G) {
+      const bool second = MODE == 0 && piece >= 2;
+      uint32_t o[32];
+      if (n_sub > 0) {
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + (second ? COL_ACC1 : COL_ACC0) + (piece & 1) * 32, o);
+        ptx::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = 0u;
+      }
+      if (valid) {
+        if (MODE == 1) store_row_bf16(p.dq + (int64_t)(q0 + row) * p.dqs + (int64_t)h * D + (piece & 1) * 32, o, p.scale);
+        else if (!second) store_row_bf16(p.dv + (int64_t)(k0 + row) * p.dvs + (int64_t)h * D + (piece & 1) * 32, o, 1.0f);
+        else store_row_bf16(p.dk + (int64_t)(k0 + row) * p.dks + (int64_t)h * D + (piece & 1) * 32, o, p.scale);
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == EW) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
 // returns ACAI_ERR_UNSUPPORTED when the problem does not qualify (the caller then runs the SIMT kernels)
 int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t qs, int64_t ks, int64_t vs, const void* dout,
                 int64_t dos, const float* lse, const float* delta, const int32_t* cu_q, const int32_t* cu_k, int batch,
@@ -563,14 +993,48 @@ int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t 
                   (__nv_bfloat16*)dq, (__nv_bfloat16*)dk, (__nv_bfloat16*)dv, dqs, dks, dvs, drop};
   const dim3 gq((max_q + BIG - 1) / BIG, heads, batch), gk((max_k + BIG - 1) / BIG, heads, batch);
   const bool dr = drop.thr != 0;
+  // head_dim 64: the grouped kernels (attn_bwd_g4); ACAI_ATTN_BWD_G4 = 0 / 1 / 2 / 3 (bit 0: dK/dV, bit 1: dQ) for A/B runs.
+  // Default 1: the grouped dK/dV kernel is 1.2 - 1.3x the two-CTA kernel on sequences of ~1000 tokens and level at ~650 causal;
+  // the grouped dQ kernel is not faster than attn_bwd_dq_tc (profiles/r2d_attention_issue.md).
+  // Unset: dK/dV grouped for non-causal problems (encoder self-attention 1 211 -> 1 080 us, decoder cross-attention 1 036 -> 987 us;
+  // causal decoder self-attention 621 -> 644 us: its key tiles see too few query sub-blocks to amortise a one-CTA-per-SM prologue).
+  static const int g4 = [] { const char* e = getenv("ACAI_ATTN_BWD_G4"); const int v = e ? atoi(e) : -1; return v < 0 || v > 3 ? -1 : v; }();
+  const int use_g4 = head_dim != 64 ? 0 : (g4 >= 0 ? g4 : (causal ? 0 : 1));
+  CUtensorMap q_sub, do_sub, k_sub, v_sub;
+  if (use_g4 & 1) {
+    if ((rc = make_tma_2d_bf16(&q_sub, q, (uint64_t)total_q, cols, (uint64_t)qs, fg::SUB, D))) return rc;
+    if ((rc = make_tma_2d_bf16(&do_sub, dout, (uint64_t)total_q, cols, (uint64_t)dos, fg::SUB, D))) return rc;
+  }
+  if (use_g4 & 2) {
+    if ((rc = make_tma_2d_bf16(&k_sub, k, (uint64_t)total_k, cols, (uint64_t)ks, fg::SUB, D))) return rc;
+    if ((rc = make_tma_2d_bf16(&v_sub, v, (uint64_t)total_k, cols, (uint64_t)vs, fg::SUB, D))) return rc;
+  }
+  static bool g4_attr_set = false;
+  if (use_g4 && !g4_attr_set) {
+#define ACAI_SET(K) ACAI_CUDA(cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fg::SMEM))
+    ACAI_SET((attn_bwd_g4<0, false>)); ACAI_SET((attn_bwd_g4<0, true>)); ACAI_SET((attn_bwd_g4<1, false>)); ACAI_SET((attn_bwd_g4<1, true>));
+#undef ACAI_SET
+    g4_attr_set = true;
+  }
+  const G4Rows rows_q{(const __nv_bfloat16*)q, (const __nv_bfloat16*)dout, qs, dos}, rows_k{(const __nv_bfloat16*)k, (const __nv_bfloat16*)v, ks, vs};
 #define ACAI_LAUNCH(K, G, ...) do { if (head_dim == 64) { if (dr) K<64, true><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); else K<64, false><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); } \
                                     else { if (dr) K<32, true><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); else K<32, false><<<G, THREADS, SMEM, st>>>(__VA_ARGS__); } } while (0)
-  ACAI_LAUNCH(attn_bwd_dq_tc, gq, q_big, do_big, k_small, v_small, p);
-  rc = launch_status("attn_bwd_dq_tc");
+  if (use_g4 & 2) {
+    if (dr) attn_bwd_g4<1, true><<<gq, fg::threads(1), fg::SMEM, st>>>(k_sub, v_sub, p, rows_q);
+    else attn_bwd_g4<1, false><<<gq, fg::threads(1), fg::SMEM, st>>>(k_sub, v_sub, p, rows_q);
+  } else {
+    ACAI_LAUNCH(attn_bwd_dq_tc, gq, q_big, do_big, k_small, v_small, p);
+  }
+  rc = launch_status("attn_bwd_dq");
   if (rc) return rc;
-  ACAI_LAUNCH(attn_bwd_dkv_tc, gk, k_big, v_big, q_small, do_small, p);
+  if (use_g4 & 1) {
+    if (dr) attn_bwd_g4<0, true><<<gk, fg::threads(0), fg::SMEM, st>>>(q_sub, do_sub, p, rows_k);
+    else attn_bwd_g4<0, false><<<gk, fg::threads(0), fg::SMEM, st>>>(q_sub, do_sub, p, rows_k);
+  } else {
+    ACAI_LAUNCH(attn_bwd_dkv_tc, gk, k_big, v_big, q_small, do_small, p);
+  }
 #undef ACAI_LAUNCH
-  return launch_status("attn_bwd_dkv_tc");
+  return launch_status("attn_bwd_dkv");
 }
 
 }  // namespace acai

@@ -131,59 +131,79 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   constexpr int REG_LO = CTAS == 4 ? 32 : 40, REG_HI = CTAS == 4 ? 96 : 120;
   if (warp >= 4) {
   if constexpr (CTAS > 2) ptx::setmaxnreg_dec<REG_LO>();   // one instruction for the whole helper warpgroup
+  // Both helper warps walk their loops CONVERGED (every lane polls the barriers) and one elected lane issues: with the
+  // operands provably warp-uniform (shuffles of lane 0) the TMA / tcgen05 instructions take them from uniform registers
+  // directly; under `if (lane == 0)` every one of them is a waterfall loop of ~100 clk (ptx::elect_one_sync).
+  const int u_nkv = __shfl_sync(0xffffffffu, n_kv, 0), u_nsb = __shfl_sync(0xffffffffu, n_sb, 0);
   if (warp == 4) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0 && n_kv > 0) {
+    if (u_nkv > 0) {
       const int hcol = (h * DH) & ~63;
+      const int qrow = __shfl_sync(0xffffffffu, q0 + qb * BQ, 0);
+      int krow = __shfl_sync(0xffffffffu, k0, 0);
       if constexpr (!QT) {
-        ptx::mbar_arrive_expect_tx(q_full, QTILE);
-        ptx::tma_load_2d(smem + OFF_Q, &tma_q, q_full, hcol, q0 + qb * BQ);
+        if (ptx::elect_one_sync()) {
+          ptx::mbar_arrive_expect_tx(q_full, QTILE);
+          ptx::tma_load_2d(smem + OFF_Q, &tma_q, q_full, hcol, qrow);
+        }
+        __syncwarp();
       }
       int s = 0; uint32_t ph = 0;
-      for (int j = 0; j < n_kv; ++j) {
+      for (int j = 0; j < u_nkv; ++j, krow += BKV) {
         ptx::mbar_wait(&kv_empty[s], ph ^ 1);
-        ptx::mbar_arrive_expect_tx(&kv_full[s], 2 * KTILE);
-        ptx::tma_load_2d(smem + OFF_K + s * KTILE, &tma_k, &kv_full[s], hcol, k0 + j * BKV);
-        ptx::tma_load_2d(smem + OFF_V + s * KTILE, &tma_v, &kv_full[s], hcol, k0 + j * BKV);
+        if (ptx::elect_one_sync()) {
+          ptx::mbar_arrive_expect_tx(&kv_full[s], 2 * KTILE);
+          ptx::tma_load_2d(smem + OFF_K + s * KTILE, &tma_k, &kv_full[s], hcol, krow);
+          ptx::tma_load_2d(smem + OFF_V + s * KTILE, &tma_v, &kv_full[s], hcol, krow);
+        }
+        __syncwarp();
         if (++s == KV_STAGES) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 5) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0 && n_kv > 0) {
+    if (u_nkv > 0) {
       constexpr uint32_t IDESC_S = ptx::idesc_bf16_f32(BQ, SB);
       constexpr uint32_t IDESC_O = ptx::idesc_bf16_f32(BQ, DH, false, true);  // B = V is MN-major
+      const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0), tq0 = __shfl_sync(0xffffffffu, tmem_q, 0);
       const uint64_t hoff = (uint64_t)(((h * DH) & 63) >> 3);                 // this head's 16-byte units inside the 128 B row
       const uint64_t qdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_Q), 1024) + hoff;
+      const uint64_t kdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K), 1024) + hoff;
+      const uint64_t vdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V), 1024) + hoff;
       auto issue_s = [&](int i) {                    // S_i into buffer i % NBUF; its keys are rows (i % R) * SB.. of tile i / R
         const int t = i / R, st = t % KV_STAGES;
         ptx::mbar_wait(&kv_full[st], (t / KV_STAGES) & 1);
         ptx::tc_fence_after();
-        const uint64_t kdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_K + st * KTILE), 1024) + hoff +
-                               (uint64_t)((i % R) * (SB * 128 >> 4));
+        if (ptx::elect_one_sync()) {
+          const uint64_t kdesc = kdesc0 + (uint64_t)(st * (KTILE >> 4)) + (uint64_t)((i % R) * (SB * 128 >> 4));
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) {
-          if constexpr (QT) ptx::umma_f16_ts(tmem_base + S_COL + (i % NBUF) * SB, tmem_q + k * 8, kdesc + 2 * k, IDESC_S, k != 0);
-          else ptx::umma_f16_ss(tmem_base + S_COL + (i % NBUF) * SB, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+          for (int k = 0; k < DH / 16; ++k) {
+            if constexpr (QT) ptx::umma_f16_ts(tb0 + S_COL + (i % NBUF) * SB, tq0 + k * 8, kdesc + 2 * k, IDESC_S, k != 0);
+            else ptx::umma_f16_ss(tb0 + S_COL + (i % NBUF) * SB, qdesc + 2 * k, kdesc + 2 * k, IDESC_S, k != 0);
+          }
+          ptx::umma_commit(&s_full[i % NBUF]);
         }
-        ptx::umma_commit(&s_full[i % NBUF]);
+        __syncwarp();
       };
       ptx::mbar_wait(q_full, 0);
       issue_s(0);
-      if (NBUF == 2 && n_sb > 1) issue_s(1);
-      for (int i = 0; i < n_sb; ++i) {
+      if (NBUF == 2 && u_nsb > 1) issue_s(1);
+      for (int i = 0; i < u_nsb; ++i) {
         const int st = (i / R) % KV_STAGES;
         ptx::mbar_wait(&p_full[i % NBUF], (i / NBUF) & 1);
         ptx::tc_fence_after();
-        const uint64_t vdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem + OFF_V + st * KTILE), 1024) + hoff;
+        if (ptx::elect_one_sync()) {
+          const uint64_t vdesc = vdesc0 + (uint64_t)(st * (KTILE >> 4));
 #pragma unroll
-        for (int kk = 0; kk < SB / 16; ++kk)        // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
-          ptx::umma_f16_ts(tmem_base + O_COL, tmem_base + S_COL + (i % NBUF) * SB + kk * 8,
-                           vdesc + (uint64_t)((i % R) * (SB / 16) + kk) * (16 * 128 >> 4), IDESC_O, (i | kk) != 0);
-        if (i % R == R - 1 || i == n_sb - 1) ptx::umma_commit(&kv_empty[st]);   // last reader of this K/V tile
-        ptx::umma_commit(o_step);
-        if (i == n_sb - 1) ptx::umma_commit(o_full);
-        if (i + NBUF < n_sb) issue_s(i + NBUF);      // overwrites P_i: tcgen05 ops execute in issue order
+          for (int kk = 0; kk < SB / 16; ++kk)        // A: 16 keys = 8 packed TMEM columns; B: 16 V rows = 2048 bytes
+            ptx::umma_f16_ts(tb0 + O_COL, tb0 + S_COL + (i % NBUF) * SB + kk * 8,
+                             vdesc + (uint64_t)((i % R) * (SB / 16) + kk) * (16 * 128 >> 4), IDESC_O, (i | kk) != 0);
+          if (i % R == R - 1 || i == u_nsb - 1) ptx::umma_commit(&kv_empty[st]);   // last reader of this K/V tile
+          ptx::umma_commit(o_step);
+          if (i == u_nsb - 1) ptx::umma_commit(o_full);
+        }
+        __syncwarp();
+        if (i + NBUF < u_nsb) issue_s(i + NBUF);      // overwrites P_i: tcgen05 ops execute in issue order
       }
     }
   }

@@ -116,6 +116,19 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, ui
       "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
       ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// One lane of a CONVERGED warp (elect.sync): the form the compiler recognises as "a single thread issues this", so that the
+// operands of the tcgen05 instructions inside `if (elect_one_sync())` go through the uniform datapath directly.  The
+// `if (lane == 0)` form makes every UTCHMMA a waterfall loop (ELECT / R2UR / BRA.U.ANY, ~100 clk per instruction): fine for
+// a 128 x 256 x 16 GEMM step, the bottleneck for attention's 128 x 32 / 64 x 16 steps.
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred) : "r"(0xffffffffu));
+  return pred != 0;
+}
 // mbarrier arrive once all previously issued tcgen05.mma of this thread have completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");

@@ -59,6 +59,25 @@ def bench_attn(name, n, mean, H, d, causal, bwd, drop=0.0):
         print(f"{name:28s} bwd  {us:9.1f} us  {2.5 * flops / us / 1e6:7.1f} TFLOP/s")
 
 
+def bench_cross(name, n, mean_q, mean_k, H, d, drop=0.0):
+    """decoder cross-attention: queries = target tokens, keys = encoder memory (fwd + bwd)"""
+    lq, cu_q = ragged(n, mean_q, 3)
+    lk, cu_k = ragged(n, mean_k, 1)
+    Tq, Tk, mq, mk = int(lq.sum()), int(lk.sum()), int(lq.max()), int(lk.max())
+    q = torch.randn(Tq, H * d, device=DEV).bfloat16()
+    kv = torch.randn(Tk, 2 * H * d, device=DEV).bfloat16()
+    k, v = kv[:, :H * d], kv[:, H * d:]
+    flops = float(4 * H * d * (lq.double() * lk.double()).sum())
+    dk_ = dict(dropout_p=drop, dropout_seed=1234) if drop else {}
+    us = timed(lambda: ops.attn_varlen(q, k, v, cu_q, cu_k, mq, H, d, causal=False, **dk_))
+    print(f"{name:28s} fwd  {us:9.1f} us  {flops / us / 1e6:7.1f} TFLOP/s  (Tq={Tq}, Tk={Tk})")
+    out, lse = ops.attn_varlen(q, k, v, cu_q, cu_k, mq, H, d, causal=False, return_lse=True, **dk_)
+    dout = torch.randn_like(out)
+    dq, dkv = torch.empty_like(q), torch.empty_like(kv)
+    us = timed(lambda: ops.attn_varlen_bwd(q, k, v, out, dout, lse, cu_q, cu_k, mq, mk, H, d, False, dq, dkv[:, :H * d], dkv[:, H * d:], **dk_))
+    print(f"{name:28s} bwd  {us:9.1f} us  {2.5 * flops / us / 1e6:7.1f} TFLOP/s")
+
+
 def bench_ln(rows, cols):
     x = torch.randn(rows, cols, device=DEV).bfloat16()
     g, b = torch.ones(cols, device=DEV), torch.zeros(cols, device=DEV)
@@ -97,6 +116,8 @@ if __name__ == "__main__":
         bench_attn("encoder self (12 x 64)", 64, 995, 12, 64, False, bwd)
         bench_attn("decoder self (16 x 64, causal)", 64, 655, 16, 64, True, bwd)
         bench_attn("MAE decoder self (16 x 32)", 64, 495, 16, 32, False, bwd)
+        if bwd:
+            bench_cross("decoder cross (16 x 64)", 64, 655, 995, 16, 64)
         if "drop" in what:
             bench_attn("encoder self (12 x 64)", 64, 995, 12, 64, False, bwd, 0.05)
             bench_attn("decoder self (16 x 64, causal)", 64, 655, 16, 64, True, bwd, 0.1)

@@ -91,7 +91,9 @@ decode_attn_tma_kernel(const __grid_constant__ CUtensorMap tma_kv, DecodeTmaArgs
   pdl_wait();
   pdl_launch_dependents();
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // (the warp index through a shuffle: provably warp-uniform, so that everything the TMA issue below derives from it - head
+  // column, ring slot, barrier - lives in uniform registers; see ptx::elect_one_sync)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int chunk = blockIdx.x, h = blockIdx.y * WARPS + warp, b = blockIdx.z;
   const int H = a.heads;
   uint8_t* wbuf = smem + warp * WARP_SMEM;
@@ -119,16 +121,20 @@ decode_attn_tma_kernel(const __grid_constant__ CUtensorMap tma_kv, DecodeTmaArgs
     ptx::fence_barrier_init();
   }
   __syncwarp();
-  auto issue = [&](int i) {                                                     // stage i -> ring slot i % NST (lane 0)
+  auto issue = [&](int i) {                                                     // stage i -> ring slot i % NST; the whole warp calls
     const int t0 = t_begin + i * TOK;
-    const int row = tbl ? tbl[t0 / PAGE] * PAGE + (t0 % PAGE) : row0 + t0;
-    uint8_t* dst = wbuf + (i % NST) * 2 * BOX;
-    ptx::mbar_arrive_expect_tx(&full[i % NST], 2 * BOX);
-    ptx::tma_load_2d(dst, &tma_kv, &full[i % NST], h * HD, row);
-    ptx::tma_load_2d(dst + BOX, &tma_kv, &full[i % NST], (H + h) * HD, row);
+    const int row = __shfl_sync(0xffffffffu, tbl ? tbl[t0 / PAGE] * PAGE + (t0 % PAGE) : row0 + t0, 0);
+    if (ptx::elect_one_sync()) {
+      uint8_t* dst = wbuf + (i % NST) * 2 * BOX;
+      ptx::mbar_arrive_expect_tx(&full[i % NST], 2 * BOX);
+      ptx::tma_load_2d(dst, &tma_kv, &full[i % NST], h * HD, row);
+      ptx::tma_load_2d(dst + BOX, &tma_kv, &full[i % NST], (H + h) * HD, row);
+    }
+    __syncwarp();
   };
-  if (lane == 0) {
-    for (int i = 0; i < NST && i < n_st; ++i) issue(i);
+  {
+    const int n_u = __shfl_sync(0xffffffffu, n_st, 0);
+    for (int i = 0; i < NST && i < n_u; ++i) issue(i);
   }
 
   float q[64];
@@ -156,7 +162,7 @@ decode_attn_tma_kernel(const __grid_constant__ CUtensorMap tma_kv, DecodeTmaArgs
                  [&](int c) { return *reinterpret_cast<const uint4*>(kb + ((((uint32_t)c) ^ sw) << 4)); },
                  [&](int c) { return *reinterpret_cast<const uint4*>(vb + ((((uint32_t)c) ^ sw) << 4)); });
     __syncwarp();                                     // every lane is done with the slot before it is refilled
-    if (lane == 0 && i + NST < n_st) issue(i + NST);
+    if (i + NST < n_st) issue(i + NST);
   }
   if (a.new_kv && len >= t_begin && len < t_end) {    // the token appended this step: lane 0 attends to it ...
     const __nv_bfloat16* nk = a.new_kv + (int64_t)b * a.new_kv_stride + h * HD;

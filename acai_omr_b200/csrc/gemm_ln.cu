@@ -158,7 +158,7 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
   uint64_t* stat_bar = tempty_bar + 2;                                    // [2]: CL * BM * 8 bytes of peer moments per tile
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stat_bar + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // (provably warp-uniform: ptx::elect_one_sync)
   const uint32_t rank = cluster_ctarank();
   const int n0 = (int)rank * BN;
   const int num_m = (M + BM - 1) / BM, num_k = K / BK;
@@ -193,40 +193,45 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
 #endif
   pdl_launch_dependents();
 
+  // (producer / issuer: converged loops, one elected lane issues - see ptx::elect_one_sync)
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      for (int mt = first; mt < num_m; mt += step) {
-        for (int kb = 0; kb < num_k; ++kb) {
-          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+    int stage = 0; uint32_t phase = 0;
+    for (int mt = first; mt < num_m; mt += step) {
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (ptx::elect_one_sync()) {
           ptx::mbar_arrive_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
           ptx::tma_load_2d(smem_a + stage * A_BYTES, &tma_a, &full_bar[stage], kb * BK, mt * BM);
           ptx::tma_load_2d(smem_b + stage * B_BYTES, &tma_b, &full_bar[stage], kb * BK, n0);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN);
-      int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int mt = first; mt < num_m; mt += step, ++it) {
-        const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+    constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN);
+    const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t adesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_a), 1024);
+    const uint64_t bdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_b), 1024);
+    int stage = 0; uint32_t phase = 0; int it = 0;
+    for (int mt = first; mt < num_m; mt += step, ++it) {
+      const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
+      ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tb0 + as * BN;
+      for (int kb = 0; kb < num_k; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < num_k; ++kb) {
-          ptx::mbar_wait(&full_bar[stage], phase);
-          ptx::tc_fence_after();
-          const uint64_t adesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_a + stage * A_BYTES), 1024);
-          const uint64_t bdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_b + stage * B_BYTES), 1024);
+        if (ptx::elect_one_sync()) {
+          const uint64_t adesc = adesc0 + (uint64_t)(stage * (A_BYTES >> 4)), bdesc = bdesc0 + (uint64_t)(stage * (B_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
             ptx::umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb != 0 || k != 0) ? 1u : 0u);
           ptx::umma_commit(&empty_bar[stage]);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (kb == num_k - 1) ptx::umma_commit(&tfull_bar[as]);
         }
-        ptx::umma_commit(&tfull_bar[as]);
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else {

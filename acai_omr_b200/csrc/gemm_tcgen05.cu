@@ -254,7 +254,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // (provably warp-uniform: ptx::elect_one_sync)
   const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN, num_mn = num_m * num_n, num_k = K / BK;
   const int splitk = (OUT == 0 && ep.splitk > 1) ? ep.splitk : 1, kper = splitk > 1 ? ep.kper : num_k;
   const int num_tiles = num_mn * splitk;
@@ -278,44 +278,51 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
   pdl_wait();                    // everything above (barriers, TMEM, tensor-map prefetch) may overlap the previous kernel's tail
   pdl_launch_dependents();
 
+  // Producer and issuer warps walk their loops CONVERGED (every lane polls the barriers) and one elected lane issues
+  // (ptx::elect_one_sync): the TMA / tcgen05 operands then come straight from uniform registers.  Under `if (lane == 0)`
+  // every UTMALDG / UTCHMMA was a waterfall loop of ~100 clk - next to the 128 clk a 128 x 256 x 16 MMA takes.
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int mn = tile % num_mn, ks = tile / num_mn;
-        const int m0 = (mn / num_n) * BM, n0 = (mn % num_n) * BN;
-        const int kb0 = ks * kper, kb1 = kb0 + kper < num_k ? kb0 + kper : num_k;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+    int stage = 0; uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int mn = tile % num_mn, ks = tile / num_mn;
+      const int m0 = (mn / num_n) * BM, n0 = (mn % num_n) * BN;
+      const int kb0 = ks * kper, kb1 = kb0 + kper < num_k ? kb0 + kper : num_k;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (ptx::elect_one_sync()) {
           ptx::mbar_arrive_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
           ptx::tma_load_2d(smem_a + stage * A_BYTES, &tma_a, &full_bar[stage], kb * BK, m0);
           ptx::tma_load_2d(smem_b + stage * B_BYTES, &tma_b, &full_bar[stage], kb * BK, n0);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN);
-      int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+    constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN);
+    const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t adesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_a), 1024);
+    const uint64_t bdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_b), 1024);
+    int stage = 0; uint32_t phase = 0; int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
+      ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tb0 + as * BN;
+      const int kb0 = (tile / num_mn) * kper, kb1 = kb0 + kper < num_k ? kb0 + kper : num_k;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        const int kb0 = (tile / num_mn) * kper, kb1 = kb0 + kper < num_k ? kb0 + kper : num_k;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait(&full_bar[stage], phase);
-          ptx::tc_fence_after();
-          const uint64_t adesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_a + stage * A_BYTES), 1024);
-          const uint64_t bdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_b + stage * B_BYTES), 1024);
+        if (ptx::elect_one_sync()) {
+          const uint64_t adesc = adesc0 + (uint64_t)(stage * (A_BYTES >> 4)), bdesc = bdesc0 + (uint64_t)(stage * (B_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes along K inside the 128B swizzle row = +2 in the address field
             ptx::umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb != kb0 || k != 0) ? 1u : 0u);
           ptx::umma_commit(&empty_bar[stage]);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (kb == kb1 - 1) ptx::umma_commit(&tfull_bar[as]);
         }
-        ptx::umma_commit(&tfull_bar[as]);
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else {

@@ -44,7 +44,7 @@ gemm_wgrad_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_const
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // (provably warp-uniform: ptx::elect_one_sync)
   const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN, num_tiles = num_m * num_n;
   const int nk = (T + BK - 1) / BK, kper = (nk + splits - 1) / splits;
   const int num_items = num_tiles * splits;          // item = split * num_tiles + tile: neighbours share a token range
@@ -63,15 +63,16 @@ gemm_wgrad_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_const
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // (producer / issuer: converged loops, one elected lane issues - see ptx::elect_one_sync)
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-        const int tile = item % num_tiles, split = item / num_tiles;
-        const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
-        const int kb0 = split * kper, kb1 = min(nk, kb0 + kper);
-        for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+    int stage = 0; uint32_t phase = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int tile = item % num_tiles, split = item / num_tiles;
+      const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
+      const int kb0 = split * kper, kb1 = min(nk, kb0 + kper);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (ptx::elect_one_sync()) {
           ptx::mbar_arrive_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
 #pragma unroll
           for (int i = 0; i < BM / 64; ++i)
@@ -79,36 +80,40 @@ gemm_wgrad_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_const
 #pragma unroll
           for (int i = 0; i < BN / 64; ++i)
             ptx::tma_load_2d(smem_b + stage * B_BYTES + i * BOX, &tma_b, &full_bar[stage], n0 + 64 * i, kb * BK);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN, true, true);
-      int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-        const int split = item / num_tiles;
-        const int kb0 = split * kper, kb1 = min(nk, kb0 + kper);
-        if (kb1 <= kb0) continue;                      // empty token range: nothing to add (all roles skip alike)
-        const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
-        ++it;
-        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+    constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN, true, true);
+    const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t adesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_a), 1024, BOX);
+    const uint64_t bdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_b), 1024, BOX);
+    int stage = 0; uint32_t phase = 0; int it = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int split = item / num_tiles;
+      const int kb0 = split * kper, kb1 = min(nk, kb0 + kper);
+      if (kb1 <= kb0) continue;                      // empty token range: nothing to add (all roles skip alike)
+      const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
+      ++it;
+      ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tb0 + as * BN;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait(&full_bar[stage], phase);
-          ptx::tc_fence_after();
-          const uint64_t adesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_a + stage * A_BYTES), 1024, BOX);
-          const uint64_t bdesc = ptx::smem_desc_sw128(ptx::smem_u32(smem_b + stage * B_BYTES), 1024, BOX);
+        if (ptx::elect_one_sync()) {
+          const uint64_t adesc = adesc0 + (uint64_t)(stage * (A_BYTES >> 4)), bdesc = bdesc0 + (uint64_t)(stage * (B_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)             // 16 tokens = 16 rows of 128 bytes
             ptx::umma_f16_ss(d_tmem, adesc + (uint64_t)k * (16 * 128 >> 4), bdesc + (uint64_t)k * (16 * 128 >> 4), IDESC,
                              (kb > kb0 || k != 0));
           ptx::umma_commit(&empty_bar[stage]);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (kb == kb1 - 1) ptx::umma_commit(&tfull_bar[as]);
         }
-        ptx::umma_commit(&tfull_bar[as]);
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else {

@@ -995,7 +995,7 @@ int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t 
   const bool dr = drop.thr != 0;
   // head_dim 64: the grouped kernels (attn_bwd_g4); ACAI_ATTN_BWD_G4 = 0 / 1 / 2 / 3 (bit 0: dK/dV, bit 1: dQ) for A/B runs.
   // Default 1: the grouped dK/dV kernel is 1.2 - 1.3x the two-CTA kernel on sequences of ~1000 tokens and level at ~650 causal;
-  // the grouped dQ kernel is not faster than attn_bwd_dq_tc (profiles/r2d_attention_issue.md).
+  // the grouped dQ kernel is not faster than attn_bwd_dq_tc (profiles/r2d_issue_path.md).
   // Unset: dK/dV grouped for non-causal problems (encoder self-attention 1 211 -> 1 080 us, decoder cross-attention 1 036 -> 987 us;
   // causal decoder self-attention 621 -> 644 us: its key tiles see too few query sub-blocks to amortise a one-CTA-per-SM prologue).
   static const int g4 = [] { const char* e = getenv("ACAI_ATTN_BWD_G4"); const int v = e ? atoi(e) : -1; return v < 0 || v > 3 ? -1 : v; }();

@@ -4,7 +4,9 @@
 
 UTCHMMA / UTCQMMA = tcgen05.mma, LDTM / STTM = tcgen05.ld / st (TMEM), UTMALDG / UTMASTG / UTMAREDG = TMA tensor load /
 store / reduce-add, UBLKCP = bulk (1-D) TMA copy, SYNCS = mbarrier, UTCBAR = tcgen05.commit; FFMA2 etc. are listed to show
-the packed-pair math.  See /opt/skills/guides/B200_PROFILING.md for the mnemonics."""
+the packed-pair math.  BRA.U.ANY = the back edge of a waterfall loop ptxas wraps around an instruction whose uniform-register
+operands it cannot prove warp-uniform (0 for the hot kernels since round 2d, profiles/r2d_issue_path.md); ELECT = elect.sync.
+See /opt/skills/guides/B200_PROFILING.md for the mnemonics."""
 import collections
 import os
 import re
@@ -13,7 +15,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "acai_omr_b200", "libacai_b200.so")
-OPS = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UBLKCP", "UTCBAR", "SYNCS", "FFMA2", "HMMA", "MUFU.EX2"]
+OPS = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UBLKCP", "UTCBAR", "SYNCS", "FFMA2", "HMMA", "MUFU.EX2", "ELECT",
+       "BRA.U.ANY"]
 
 
 def demangle(names):

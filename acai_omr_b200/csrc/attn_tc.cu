@@ -78,7 +78,7 @@ struct AttnParams {
 // tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
 // POLY: how many of every 4 exponentials are evaluated with exp2_fma on the FMA pipe instead of MUFU.EX2 (0, 1 or 2).
 // The MUFU unit (16 results / clk / SM) is this kernel's busiest pipe; the FMA pipe is mostly idle.
-template <int DH, bool DROP, int POLY, int NBUF, int CTAS, int SB, int QT>
+template <int DH, bool DROP, int POLY, int NBUF, int CTAS, int SB, int QT, int PIPE = 0>
 __global__ void __launch_bounds__((Cfg<NBUF, CTAS, SB, QT>::THREADS), CTAS)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
@@ -238,6 +238,87 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
       }
     }
 
+    if constexpr (PIPE) {
+      // Software-pipelined variant (NBUF 2, SB 32): S_{j+1} is requested from TMEM (the other S buffer is already complete)
+      // BEFORE the exponentials of block j, so that the tcgen05.ld round trip and the wait for S never sit between two
+      // blocks' MUFU phases.  Costs 32 more live registers per thread.
+      static_assert(!PIPE || (NBUF == 2 && SB == 32 && QT == 0), "pipelined softmax: two 32-key S buffers");
+      uint32_t sa[32], sb2[32];
+      auto request = [&](int j, uint32_t (&sv)[32]) {          // wait for S_j, start its tcgen05.ld (no wait)
+        ptx::mbar_wait(&s_full[j % NBUF], (j / NBUF) & 1);
+        ptx::tc_fence_after();
+        ptx::tmem_ld_32x32(tmem_base + lane_addr + S_COL + (j % NBUF) * SB, sv);
+      };
+      auto block = [&](int j, uint32_t (&sv)[32], uint32_t (&sn)[32]) {
+        const uint32_t tmem_s = tmem_base + lane_addr + S_COL + (j % NBUF) * SB;
+        const int kbase = j * SB;
+        if (kbase + SB > warp_min_end) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) if (kbase + i >= my_end) sv[i] = 0xff800000u;   // -inf
+        }
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(sv[i])); mx1 = fmaxf(mx1, __uint_as_float(sv[i + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(sv[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(sv[i + 3]));
+        }
+        const float m_new = fmaxf(m, fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)));
+        const bool grow = (m_new - m) * scale_log2 > RESCALE_LOG2 || (m == -INFINITY && m_new > -INFINITY);
+        if (__any_sync(0xffffffffu, grow)) {
+          const float m_use = m_new == -INFINITY ? 0.0f : m_new;
+          const float corr = m == -INFINITY ? 0.0f : fast_exp2((m - m_use) * scale_log2);
+          l *= corr;
+          if (j > 0) {
+            ptx::mbar_wait(o_step, (j - 1) & 1);      // O holds P_{j-1} V_{j-1}
+            ptx::tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < DH / 16; ++c) {
+              uint32_t o[16];
+              ptx::tmem_ld_32x16(tmem_o + c * 16, o);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+              ptx::tmem_st_32x16(tmem_o + c * 16, o);
+            }
+          }
+          m = m_new;
+        }
+        const float moff = (m == -INFINITY ? 0.0f : m) * scale_log2;
+        const uint64_t sc2 = ptx::pack_f32x2(scale_log2, scale_log2), mo2 = ptx::pack_f32x2(-moff, -moff);
+        uint64_t l2 = ptx::pack_f32x2(0.0f, 0.0f);
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float x0, x1;
+          ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[2 * i]), __uint_as_float(sv[2 * i + 1])), sc2, mo2), x0, x1);
+          const float p0 = fast_exp2(x0);
+          const float p1 = (POLY == 2 || (POLY == 1 && (i & 1))) ? exp2_fma(x1) : fast_exp2(x1);
+          l2 = ptx::add_f32x2(l2, ptx::pack_f32x2(p0, p1));
+          float d0 = p0, d1 = p1;
+          if (DROP) {
+            const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(kbase / 2 + i));
+            if ((bits & 0xffffu) < p.drop.thr) d0 = 0.0f;
+            if ((bits >> 16) < p.drop.thr) d1 = 0.0f;
+          }
+          const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
+          pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+        }
+        ptx::tmem_st_32x16(tmem_s, pk);
+        if (j + 1 < n_sb) request(j + 1, sn);            // S_{j+1}'s round trip runs under the store / fence / arrive of P_j
+        float l0, l1;
+        ptx::unpack_f32x2(l2, l0, l1);
+        l += l0 + l1;
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(&p_full[j % NBUF]);
+        if (j + 1 < n_sb) ptx::tmem_ld_wait();
+      };
+      if (n_sb > 0) { request(0, sa); ptx::tmem_ld_wait(); }
+      for (int j = 0; j < n_sb; j += 2) {
+        block(j, sa, sb2);
+        if (j + 1 < n_sb) block(j + 1, sb2, sa);
+      }
+    } else
     for (int j = 0; j < n_sb; ++j) {
       const uint32_t tmem_s = tmem_base + lane_addr + S_COL + (j % NBUF) * SB;
       ptx::mbar_wait(&s_full[j % NBUF], (j / NBUF) & 1);
@@ -388,17 +469,17 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   }
 }
 
-template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2, int SB = 64, int QT = 0>
+template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2, int SB = 64, int QT = 0, int PIPE = 0>
 static int launch_fwd(dim3 grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                       cudaStream_t st) {
   static bool attr_set = false;
   constexpr size_t SMEM = Cfg<NBUF, CTAS, SB, QT>::SMEM;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_set = true;
   }
-  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT><<<grid, Cfg<NBUF, CTAS, SB, QT>::THREADS, SMEM, st>>>(tq, tk, tv, p);
+  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE><<<grid, Cfg<NBUF, CTAS, SB, QT>::THREADS, SMEM, st>>>(tq, tk, tv, p);
   return ACAI_OK;
 }
 
@@ -434,8 +515,13 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
 #define ACAI_FWD32(DH_, DROP_)                                                                                    \
   (poly == 0 ? launch_fwd<DH_, DROP_, 0, 2, 4, 32>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1, 2, 4, 32>(grid, tq, tk, tv, p, st) \
                                                                                         : launch_fwd<DH_, DROP_, 2, 2, 4, 32>(grid, tq, tk, tv, p, st))
+  // software-pipelined softmax (PIPE, see the kernel), for A/B runs: ACAI_ATTN_PIPE = 1 three CTAs per SM / 2 four CTAs per SM.  Measured
+  // on one box, encoder shape: 337.0 us off, 335.0 us with 2 (three runs each), 355 us with 1; with dropout the extra live registers
+  // spill (564 -> 590 us).  S_{j+1} requested BEFORE the exponentials of block j is slower (374 us): S is not ready that early.
+  static const int pipe = [] { const char* e = getenv("ACAI_ATTN_PIPE"); const int v = e ? atoi(e) : 0; return v == 1 || v == 2 ? v : 0; }();
 #define ACAI_FWD(DH_, DROP_)                                                                                      \
-  (qt == 1 ? launch_fwd<DH_, DROP_, 0, 1, 4, 32, 1>(grid, tq, tk, tv, p, st) : qt == 2 ? launch_fwd<DH_, DROP_, 0, 2, 3, 32, 1>(grid, tq, tk, tv, p, st) : \
+  (pipe == 1 ? launch_fwd<DH_, DROP_, 0, 2, 3, 32, 0, 1>(grid, tq, tk, tv, p, st) : pipe == 2 ? launch_fwd<DH_, DROP_, 0, 2, 4, 32, 0, 1>(grid, tq, tk, tv, p, st) : \
+   qt == 1 ? launch_fwd<DH_, DROP_, 0, 1, 4, 32, 1>(grid, tq, tk, tv, p, st) : qt == 2 ? launch_fwd<DH_, DROP_, 0, 2, 3, 32, 1>(grid, tq, tk, tv, p, st) : \
    ctas == 4 && sb == 32 ? ACAI_FWD32(DH_, DROP_) : ctas == 4 ? launch_fwd<DH_, DROP_, 0, 1, 4>(grid, tq, tk, tv, p, st) : ctas == 3 ? launch_fwd<DH_, DROP_, 0, 1, 3>(grid, tq, tk, tv, p, st)       \
              : launch_fwd<DH_, DROP_, 0, 2, 2>(grid, tq, tk, tv, p, st))
   if (drop.thr == 0) rc = head_dim == 64 ? ACAI_FWD(64, false) : ACAI_FWD(32, false);

@@ -998,7 +998,8 @@ int attn_bwd_tc(const void* q, const void* k, const void* v, int dtype, int64_t 
   // the grouped dQ kernel is not faster than attn_bwd_dq_tc (profiles/r2d_issue_path.md).
   // Unset: dK/dV grouped for non-causal problems (encoder self-attention 1 211 -> 1 080 us, decoder cross-attention 1 036 -> 987 us;
   // causal decoder self-attention 621 -> 644 us: its key tiles see too few query sub-blocks to amortise a one-CTA-per-SM prologue).
-  static const int g4 = [] { const char* e = getenv("ACAI_ATTN_BWD_G4"); const int v = e ? atoi(e) : -1; return v < 0 || v > 3 ? -1 : v; }();
+  // (read on every call - the tests switch it inside one process)
+  const int g4 = [] { const char* e = getenv("ACAI_ATTN_BWD_G4"); const int v = e ? atoi(e) : -1; return v < 0 || v > 3 ? -1 : v; }();
   const int use_g4 = head_dim != 64 ? 0 : (g4 >= 0 ? g4 : (causal ? 0 : 1));
   CUtensorMap q_sub, do_sub, k_sub, v_sub;
   if (use_g4 & 1) {

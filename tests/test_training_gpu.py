@@ -115,6 +115,39 @@ def test_self_attention_backward(H, d, dtype, causal):
         assert rel_err(qkv.grad[:, i * D:(i + 1) * D], ref_in.grad[:, i * D:(i + 1) * D]) < tol, name
 
 
+@pytest.mark.parametrize("causal,p_drop", [(False, 0.0), (True, 0.0), (False, 0.1), (True, 0.1)])
+def test_grouped_backward_kernels_match_two_cta_kernels_on_long_sequences(monkeypatch, causal, p_drop):
+    """head_dim 64: the grouped dK/dV and dQ kernels (attn_bwd_g4: several trips round their 12 / 16-stage rings, ragged tails,
+    causal first sub-blocks, dropout) against the two-CTA kernels on the same inputs, and both against fp32 torch math on the
+    shortest sequence.  ACAI_ATTN_BWD_G4 selects the kernels per call."""
+    H, d = 2, 64
+    lens = [1031, 517, 2053, 64, 1]
+    pk = Packed(lens, DEV)
+    D = H * d
+    qkv = rnd(pk.total, 3 * D, seed=31, dtype=torch.bfloat16, scale=0.7)
+    dout = rnd(pk.total, D, seed=32, dtype=torch.bfloat16)
+    kw = dict(dropout_p=p_drop, dropout_seed=77) if p_drop else {}
+    grads = {}
+    for flag in ("0", "1", "3"):
+        monkeypatch.setenv("ACAI_ATTN_BWD_G4", flag)
+        x = qkv.clone().requires_grad_(True)
+        F.self_attention(x, pk, H, d, causal, **kw).backward(dout)
+        grads[flag] = x.grad.float()
+    for flag in ("1", "3"):
+        for i, name in enumerate("qkv"):
+            a, b = grads[flag][:, i * D:(i + 1) * D], grads["0"][:, i * D:(i + 1) * D]
+            assert rel_err(a, b) < 4e-3, (flag, name, rel_err(a, b))          # same bf16 operands, fp32 sums in another order
+    assert not torch.equal(grads["3"][:, :D], torch.zeros_like(grads["3"][:, :D]))
+    if not p_drop:                                                             # torch math on one mid-sized sequence
+        o0 = sum(lens[:1])
+        sl = slice(o0, o0 + lens[1])
+        ref_in = qkv[sl].float().requires_grad_(True)
+        ref = torch_attention(ref_in[:, :D], ref_in[:, D:2 * D], ref_in[:, 2 * D:], [lens[1]], [lens[1]], H, causal)
+        ref.backward(dout[sl].float())
+        for i, name in enumerate("qkv"):
+            assert rel_err(grads["3"][sl, i * D:(i + 1) * D], ref_in.grad[:, i * D:(i + 1) * D]) < 2e-2, name
+
+
 @pytest.mark.parametrize("H,d", [(4, 12), (3, 32), (2, 64), (16, 64)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_cross_attention_backward(H, d, dtype):

@@ -10,14 +10,13 @@
 // statistics are combined ACROSS CTAs: a thread-block cluster of CL = N / 256 CTAs owns one 128-row M tile, CTA r of the
 // cluster computes columns [256 r, 256 r + 256) exactly like gemm_bf16_tcgen05<256> (TMA producer warp / single-thread
 // tcgen05.mma issuer / 8 epilogue warps, fp32 accumulator double-buffered in TMEM), and the epilogue does
-//   pass A1  v = acc + bias + residual, written back over the accumulator in TMEM (tcgen05.st); row sum over this thread's
-//            128 columns
-//   pass A2  centred sum of squares around the thread's own mean (second TMEM read - no cancellation)
+//   pass A   v = acc + bias + residual, written back over the accumulator in TMEM (tcgen05.st); sum and sum of squares of this
+//            thread's 128 columns around a pivot (the row's first value), converted to (mean, centred M2)
 //   combine  the two column halves of the CTA through shared memory, then (mean, M2) of the CTA's 256 columns is PUSHED to
 //            every CTA of the cluster through distributed shared memory (st.shared::cluster + a remote mbarrier arrive);
-//            Chan's parallel-variance formula merges the CL partial moments: exactly the two-pass variance of
-//            acai_layernorm_fwd up to fp32 rounding
-//   pass B   third TMEM read, normalise, scale / shift, stage 128-byte row pieces in swizzled shared memory and TMA-store
+//            Chan's parallel-variance formula merges the CL partial moments: the two-pass variance of acai_layernorm_fwd up
+//            to fp32 rounding
+//   pass B   second TMEM read, normalise, scale / shift, stage 128-byte row pieces in swizzled shared memory and TMA-store
 //            the bf16 copy (the next GEMM's operand) and, for an fp32 residual stream, the fp32 copy.
 // y never exists in HBM.  Persistent: one CTA per SM, cluster c walks M tiles c, c + #clusters, ...; every CTA of a
 // cluster runs the same tile sequence, so the push / wait pairs line up without any other synchronisation.
@@ -269,8 +268,10 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + as * BN + half * CPW;
-      // ---- pass A1: v = acc + bias + residual -> TMEM, row sum
-      float sum = 0.0f;
+      // ---- pass A1: v = acc + bias + residual -> TMEM; moments of the thread's 128 columns around a pivot (its first value:
+      // within a few standard deviations of the row mean, so S2 - S1^2 / n loses a bit or two, not the cancellation of raw
+      // E[x^2] - mean^2) - one pass, where the centred second moment used to cost a second TMEM read of the row
+      float s1 = 0.0f, s2 = 0.0f, pivot = 0.0f;
 #pragma unroll
       for (int ci = 0; ci < CPW / 32; ++ci) {
         const int c = ci * 32;
@@ -286,25 +287,14 @@ gemm_ln_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
         }
         res_add<RES>(rc[ci % RDEPTH], stage0, lane, v);
         if (ci + RDEPTH < CPW / 32) res_load<RES>(p, row0, M, ccol0 + (ci + RDEPTH) * 32, lane, rc[ci % RDEPTH]);
+        if (ci == 0) pivot = v[0];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) { sum += v[j]; acc[j] = __float_as_uint(v[j]); }
+        for (int j = 0; j < 32; ++j) { const float d = v[j] - pivot; s1 += d; s2 = fmaf(d, d, s2); acc[j] = __float_as_uint(v[j]); }
         ptx::tmem_st_32x32(taddr + c, acc);
       }
       ptx::tmem_st_wait();
-      const float mean_t = sum * (1.0f / CPW);
-      // ---- pass A2: centred second moment of the thread's 128 columns
-      float m2 = 0.0f;
-#ifdef GLN_ABL_NOA2
-      if (false)
-#endif
-#pragma unroll 1
-      for (int c = 0; c < CPW; c += 32) {
-        uint32_t acc[32];
-        ptx::tmem_ld_32x32(taddr + c, acc);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) { const float d = __uint_as_float(acc[j]) - mean_t; m2 = fmaf(d, d, m2); }
-      }
+      const float mean_t = pivot + s1 * (1.0f / CPW);
+      const float m2 = fmaxf(s2 - s1 * s1 * (1.0f / CPW), 0.0f);
       // ---- the two halves of the CTA -> (mean, M2) over 256 columns; half 0 pushes it to every CTA of the cluster
       comb[half * BM + trow] = make_float2(mean_t, m2);
       epi_bar_sync();

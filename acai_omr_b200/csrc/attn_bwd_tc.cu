@@ -198,6 +198,7 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
     const float dl = valid ? p.delta[(int64_t)h * p.total_q + q0 + qi] : 0.0f;
     const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? qi : 0));
     const uint32_t rowconst = DROP ? attn_drop_rowconst(p.drop.seed, rowkey) : 0u;
+    const uint32_t rowbase = DROP ? attn_drop_rowbase(rowkey) : 0u;
     const float rp = p.drop.rp;
     for (int j = 0; j < n_kv; ++j) {
       const uint32_t tmem_s = tmem_base + lane_addr + (j & 1) * 64 + half * 32;
@@ -228,6 +229,8 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
       // 32 rows all see the whole half - every block but the diagonal and the last one - runs the variant without the
       // compare / select instructions.  With dropout: dS = P . (M dP / (1 - p) - delta), M = the forward's keep mask.
       const int vis = my_end - kbase;
+      // the forward's 32 keep decisions of this row's keys kbase .. kbase + 31 (attn_drop_word: one prmt + and per element)
+      const uint32_t dw = DROP ? attn_drop_word(rowconst, rowbase, (uint32_t)(kbase >> 5), p.drop.thr) : 0u;
       auto block_math = [&](auto masked_tag) {
         constexpr bool MASKED = decltype(masked_tag)::value;
         const uint64_t rpx = ptx::pack_f32x2(rp, rp);
@@ -240,9 +243,9 @@ attn_bwd_dq_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant_
             if (2 * i + 1 >= vis) p1 = 0.0f;
           }
           if (DROP) {
-            const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(j * (SMALL / 2) + half * 16 + i));
-            const float k0 = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) : 0.0f;
-            const float k1 = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) : 0.0f;
+            const uint32_t ws = dw << (i >> 1);
+            const float k0 = __uint_as_float(dp[2 * i] & attn_drop_full_mask(ws, 2 * (i & 1)));
+            const float k1 = __uint_as_float(dp[2 * i + 1] & attn_drop_full_mask(ws, 2 * (i & 1) + 1));
             pk[i] = ds_pair(p0, p1, ptx::mul_f32x2(ptx::pack_f32x2(k0, k1), rpx));
           } else {
             pk[i] = ds_pair(p0, p1, ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1])));
@@ -440,7 +443,7 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
       }
       if (DROP) {                                  // per query column: hash row constant (128..191) and low row base (192..255)
         const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + qbase + (tid & 63));
-        return tid < 192 ? attn_drop_rowconst(p.drop.seed, rowkey) : (uint32_t)(rowkey << 15);
+        return tid < 192 ? attn_drop_rowconst(p.drop.seed, rowkey) : attn_drop_rowbase(rowkey);
       }
       return 0u;
     };
@@ -469,6 +472,11 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
       // of a sequence mask anything: every other warp takes the variant without the 64 compare / select instructions
       // (the elementwise warps are issue bound, their time follows the instruction count).
       const int cm = cmin - half * 32;
+      // dropout: the keep decisions of (this thread's 32 query columns, this key) as one word - lane l hashes the key-block
+      // word of query column perm(l), a 32 x 32 bit transpose across the warp turns rows into columns (common.cuh)
+      const uint32_t dw = DROP ? attn_drop_word_transposed(reinterpret_cast<const uint32_t*>(vb + 128 + half * 32),
+                                                           reinterpret_cast<const uint32_t*>(vb + 192 + half * 32),
+                                                           (uint32_t)kr >> 5, p.drop.thr, lane) : 0u;
       auto block_math = [&](auto masked_tag) {
         constexpr bool MASKED = decltype(masked_tag)::value;
 #pragma unroll
@@ -493,14 +501,9 @@ attn_bwd_dkv_tc(const __grid_constant__ CUtensorMap tma_k, const __grid_constant
           const uint64_t nda = ptx::pack_f32x2(-d4.x, -d4.y), ndb = ptx::pack_f32x2(-d4.z, -d4.w);
           float e0, e1, e2, e3, f0, f1, f2, f3;
           if (DROP) {                                                 // M / (1 - p) of (query column, this key)
-            const uint4 rc = reinterpret_cast<const uint4*>(vb + 128 + half * 32)[i4];
-            const uint4 rb = reinterpret_cast<const uint4*>(vb + 192 + half * 32)[i4];
-            const uint32_t pair = (uint32_t)kr >> 1, sh = (kr & 1) * 16, thr = p.drop.thr;
-            const float rp = p.drop.rp;
-            const float m0 = ((attn_drop_mix((rb.x + pair) ^ rc.x) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-            const float m1 = ((attn_drop_mix((rb.y + pair) ^ rc.y) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-            const float m2 = ((attn_drop_mix((rb.z + pair) ^ rc.z) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-            const float m3 = ((attn_drop_mix((rb.w + pair) ^ rc.w) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+            const uint32_t ws = dw << i4, rpb = __float_as_uint(p.drop.rp);
+            const float m0 = __uint_as_float(rpb & attn_drop_full_mask(ws, 0)), m1 = __uint_as_float(rpb & attn_drop_full_mask(ws, 1));
+            const float m2 = __uint_as_float(rpb & attn_drop_full_mask(ws, 2)), m3 = __uint_as_float(rpb & attn_drop_full_mask(ws, 3));
             const uint64_t ma = ptx::pack_f32x2(m0, m1), mb = ptx::pack_f32x2(m2, m3);
             ptx::unpack_f32x2(ptx::mul_f32x2(pa, ma), e0, e1);
             ptx::unpack_f32x2(ptx::mul_f32x2(pb, mb), e2, e3);
@@ -784,7 +787,7 @@ attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ 
     // MODE 1: per-row constants
     float L = INFINITY, dl = 0.0f;
     int my_end = 0;
-    uint64_t rowkey = 0; uint32_t rowconst = 0;
+    uint64_t rowkey = 0; uint32_t rowconst = 0, rowbase = 0;
     if (MODE == 1) {
       if (valid) {
         L = p.lse[(int64_t)h * p.total_q + q0 + row];
@@ -792,7 +795,7 @@ attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ 
         my_end = p.causal ? max(0, min(lk, row + shift + 1)) : lk;
       }
       rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? row : 0));
-      if (DROP) rowconst = attn_drop_rowconst(p.drop.seed, rowkey);
+      if (DROP) { rowconst = attn_drop_rowconst(p.drop.seed, rowkey); rowbase = attn_drop_rowbase(rowkey); }
     }
     // MODE 0: the sub-block's 32 L / delta (and hash constants) are staged per group, one value per thread, one sub-block ahead
     float* vg = vec + g * 256;
@@ -802,7 +805,7 @@ attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ 
       if (which == 1) return __float_as_uint(q < lq ? __ldg(p.delta + (int64_t)h * p.total_q + q0 + q) : 0.0f);
       if (DROP) {
         const uint64_t rk = (uint64_t)h * p.total_q + (uint64_t)(q0 + q);
-        return which == 2 ? attn_drop_rowconst(p.drop.seed, rk) : (uint32_t)(rk << 15);
+        return which == 2 ? attn_drop_rowconst(p.drop.seed, rk) : attn_drop_rowbase(rk);
       }
       return 0u;
     };
@@ -832,6 +835,9 @@ attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ 
         const int cm = !valid ? SUB : (p.causal ? row - shift - cbase : 0);
         const float4* vl = reinterpret_cast<const float4*>(vb);
         const float4* vd = reinterpret_cast<const float4*>(vb + 32);
+        // dropout: (32 query columns, this key) decisions as one word (attn_drop_word_transposed, common.cuh)
+        const uint32_t dw = DROP ? attn_drop_word_transposed(reinterpret_cast<const uint32_t*>(vb + 64), reinterpret_cast<const uint32_t*>(vb + 96),
+                                                             (uint32_t)row >> 5, p.drop.thr, lane) : 0u;
         auto block_math = [&](auto masked_tag) {
           constexpr bool MASKED = decltype(masked_tag)::value;
 #pragma unroll
@@ -855,14 +861,9 @@ attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ 
             const uint64_t nda = ptx::pack_f32x2(-d4.x, -d4.y), ndb = ptx::pack_f32x2(-d4.z, -d4.w);
             float e0, e1, e2, e3, f0, f1, f2, f3;
             if (DROP) {                                                 // M / (1 - p) of (query column, this key)
-              const uint4 rc = reinterpret_cast<const uint4*>(vb + 64)[i4];
-              const uint4 rb = reinterpret_cast<const uint4*>(vb + 96)[i4];
-              const uint32_t pair = (uint32_t)row >> 1, sh = (row & 1) * 16, thr = p.drop.thr;
-              const float rp = p.drop.rp;
-              const float m0 = ((attn_drop_mix((rb.x + pair) ^ rc.x) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-              const float m1 = ((attn_drop_mix((rb.y + pair) ^ rc.y) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-              const float m2 = ((attn_drop_mix((rb.z + pair) ^ rc.z) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
-              const float m3 = ((attn_drop_mix((rb.w + pair) ^ rc.w) >> sh) & 0xffffu) >= thr ? rp : 0.0f;
+              const uint32_t ws = dw << i4, rpb = __float_as_uint(p.drop.rp);
+              const float m0 = __uint_as_float(rpb & attn_drop_full_mask(ws, 0)), m1 = __uint_as_float(rpb & attn_drop_full_mask(ws, 1));
+              const float m2 = __uint_as_float(rpb & attn_drop_full_mask(ws, 2)), m3 = __uint_as_float(rpb & attn_drop_full_mask(ws, 3));
               const uint64_t ma = ptx::pack_f32x2(m0, m1), mb = ptx::pack_f32x2(m2, m3);
               ptx::unpack_f32x2(ptx::mul_f32x2(pa, ma), e0, e1);
               ptx::unpack_f32x2(ptx::mul_f32x2(pb, mb), e2, e3);
@@ -885,6 +886,7 @@ attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ 
         // columns [vis, 32) are masked: keys past this query row's causal bound / the sequence end
         const int vis = my_end - cbase;
         const uint64_t nLx = ptx::pack_f32x2(-L, -L), ndlx = ptx::pack_f32x2(-dl, -dl), rpx = ptx::pack_f32x2(p.drop.rp, p.drop.rp);
+        const uint32_t dw = DROP ? attn_drop_word(rowconst, rowbase, (uint32_t)(cbase >> 5), p.drop.thr) : 0u;
         auto block_math = [&](auto masked_tag) {
           constexpr bool MASKED = decltype(masked_tag)::value;
 #pragma unroll
@@ -898,9 +900,9 @@ attn_bwd_g4(const __grid_constant__ CUtensorMap tma_b0, const __grid_constant__ 
             }
             uint64_t t2;
             if (DROP) {
-              const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(cbase / 2 + i));
-              const float k0_ = (bits & 0xffffu) >= p.drop.thr ? __uint_as_float(dp[2 * i]) : 0.0f;
-              const float k1_ = (bits >> 16) >= p.drop.thr ? __uint_as_float(dp[2 * i + 1]) : 0.0f;
+              const uint32_t ws = dw << (i >> 1);
+              const float k0_ = __uint_as_float(dp[2 * i] & attn_drop_full_mask(ws, 2 * (i & 1)));
+              const float k1_ = __uint_as_float(dp[2 * i + 1] & attn_drop_full_mask(ws, 2 * (i & 1) + 1));
               t2 = ptx::mul_f32x2(ptx::pack_f32x2(k0_, k1_), rpx);
             } else {
               t2 = ptx::pack_f32x2(__uint_as_float(dp[2 * i]), __uint_as_float(dp[2 * i + 1]));

@@ -221,6 +221,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
     float m = -INFINITY, l = 0.0f;
     const uint64_t rowkey = (uint64_t)h * p.total_q + (uint64_t)(q0 + (valid ? qi : 0));
     const uint32_t rowconst = DROP ? attn_drop_rowconst(p.drop.seed, rowkey) : 0u;
+    const uint32_t rowbase = DROP ? attn_drop_rowbase(rowkey) : 0u;
     if constexpr (QT) {                             // this thread's Q row -> TMEM (bf16 pairs per column, the TS A-operand layout)
       if (n_kv > 0) {
         uint32_t qr[DH / 2];
@@ -287,6 +288,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
         const uint64_t sc2 = ptx::pack_f32x2(scale_log2, scale_log2), mo2 = ptx::pack_f32x2(-moff, -moff);
         uint64_t l2 = ptx::pack_f32x2(0.0f, 0.0f);
         uint32_t pk[16];
+        const uint32_t dw = DROP ? attn_drop_word(rowconst, rowbase, (uint32_t)(kbase >> 5), p.drop.thr) : 0u;   // 32 keep decisions
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float x0, x1;
@@ -294,14 +296,9 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
           const float p0 = fast_exp2(x0);
           const float p1 = (POLY == 2 || (POLY == 1 && (i & 1))) ? exp2_fma(x1) : fast_exp2(x1);
           l2 = ptx::add_f32x2(l2, ptx::pack_f32x2(p0, p1));
-          float d0 = p0, d1 = p1;
-          if (DROP) {
-            const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(kbase / 2 + i));
-            if ((bits & 0xffffu) < p.drop.thr) d0 = 0.0f;
-            if ((bits >> 16) < p.drop.thr) d1 = 0.0f;
-          }
-          const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
+          const __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
           pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+          if (DROP) pk[i] &= attn_drop_pair_mask(dw << (i >> 1), i & 1);
         }
         ptx::tmem_st_32x16(tmem_s, pk);
         if (j + 1 < n_sb) request(j + 1, sn);            // S_{j+1}'s round trip runs under the store / fence / arrive of P_j
@@ -384,20 +381,19 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
       // per element in half the issue slots - this loop issues ~0.9 instructions per MUFU cycle, see profiles/r1h_attention.md)
       const uint64_t sc2 = ptx::pack_f32x2(scale_log2, scale_log2), mo2 = ptx::pack_f32x2(-moff, -moff);
       uint64_t l2 = ptx::pack_f32x2(0.0f, 0.0f);
+      uint32_t dw[SB / 32];                           // keep decisions of this block's keys, 32 per word
+#pragma unroll
+      for (int c = 0; c < SB / 32; ++c) dw[c] = DROP ? attn_drop_word(rowconst, rowbase, (uint32_t)(kbase >> 5) + c, p.drop.thr) : 0u;
       auto exp_pair = [&](uint32_t s0, uint32_t s1, int i) -> uint32_t {   // keys kbase + 2i, kbase + 2i + 1
         float x0, x1;
         ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s0), __uint_as_float(s1)), sc2, mo2), x0, x1);
         const float p0 = fast_exp2(x0);
         const float p1 = (POLY == 2 || (POLY == 1 && (i & 1))) ? exp2_fma(x1) : fast_exp2(x1);
         l2 = ptx::add_f32x2(l2, ptx::pack_f32x2(p0, p1));
-        float d0 = p0, d1 = p1;
-        if (DROP) {                                   // one hash pair
-          const uint32_t bits = attn_drop_bits(rowconst, rowkey, (uint32_t)(kbase / 2 + i));
-          if ((bits & 0xffffu) < p.drop.thr) d0 = 0.0f;
-          if ((bits >> 16) < p.drop.thr) d1 = 0.0f;
-        }
-        const __nv_bfloat162 hh = __floats2bfloat162_rn(d0, d1);
-        return *reinterpret_cast<const uint32_t*>(&hh);
+        const __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+        uint32_t pkv = *reinterpret_cast<const uint32_t*>(&hh);
+        if (DROP) pkv &= attn_drop_pair_mask(dw[i >> 4] << ((i & 15) >> 1), i & 1);   // (see attn_drop_word: one prmt per pair)
+        return pkv;
       };
 #pragma unroll
       for (int hf = 0; hf < SB / NS; ++hf) {        // P columns written by trip hf only cover S columns already in registers

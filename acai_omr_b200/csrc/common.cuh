@@ -129,31 +129,83 @@ __host__ __device__ __forceinline__ uint32_t dropout_threshold(float p) {
   return t <= 0.0f ? 0u : (t >= 65536.0f ? 65536u : (uint32_t)t);
 }
 
-// Attention-probability dropout (nn.MultiheadAttention(dropout=p) in training mode): element (head h, global query row
-// q, key position k inside its sequence) belongs to pair (rowkey << 15) + (k >> 1) with rowkey = h * total_q + q, and
-// takes the low / high 16 bits of that pair's hash for even / odd k.  All attention kernels (tensor-core and SIMT,
-// forward and both backward passes) derive the mask from these three functions, so they agree bit for bit.
+// Attention-probability dropout (nn.MultiheadAttention(dropout=p) in training mode), BIT-PARALLEL: the keep decisions of
+// the 32 keys [32 kb, 32 kb + 32) of one probability row (rowkey = h * total_q + global query row) are the 32 bits of ONE
+// word.  Sixteen pseudo-random words w_0 .. w_15 are hashed from (seed, rowkey, kb); bit position b of the sixteen words
+// is a 16-bit uniform u_b (w_i supplies bit i), and the bit-sliced comparison u_b >= thr = round(p * 65536) runs on all 32
+// positions at once - one LOP3 per word:  ge <- thr_i ? (w_i & ge) : (w_i | ge), from the least significant slice up.
+// ~55 instructions per 32 decisions where the per-pair hash + 16-bit compare / select of rounds 1 - 2 took ~190; the
+// same drop rate resolution (2^-16).  Words: two multiply-fold rounds of the block counter (the hash of rounds 1 - 2: a
+// 32 x 32 -> 64 bit product, high ^ low word, IMAD.WIDE + LOP3; one round alone is a Weyl sequence on consecutive
+// counters) and a third round per word with its own odd multiplier.  Drop rate, key / row / diagonal neighbour
+// correlations (|r| < 2e-3 on 4 M samples), the variance of per-row, per-column and per-block rates against the binomial
+// (ratio 0.92 - 1.06) checked for p = 0.05 .. 0.25 (tests/test_host.py restates the function in numpy).
+// Bit layout: key 32 kb + 4 s + j (s = 0 .. 7, j = 0 .. 3) is bit 8 j + 7 - s, so that `word << s` has the four decisions
+// of keys 4 s .. 4 s + 3 in the sign bits of its four bytes and ONE prmt (sign-replicating byte select) turns them into
+// a 0 / ~0 mask for a packed bf16 pair or a whole fp32 word.  All attention kernels (tensor-core and SIMT, forward and both
+// backward passes) derive the mask from these functions, so they agree bit for bit.
 struct AttnDropout { uint64_t seed; uint32_t thr; float rp; };        // thr = 0: no dropout; rp = 1 / (1 - p)
-__host__ __device__ __forceinline__ uint32_t attn_drop_rowconst(uint64_t seed, uint64_t rowkey) {
-  return mix32((uint32_t)((rowkey << 15) >> 32) ^ (uint32_t)seed) ^ (uint32_t)(seed >> 32);
-}
-// The per-pair hash sits in the inner loop of three issue-bound kernels, so it is two multiply-fold rounds (32 x 32 -> 64
-// bit product, high ^ low word: IMAD.WIDE + LOP3 each) instead of mix32's two multiplies and three xor-shifts - 5
-// instructions per pair instead of 10.  One round alone is a Weyl sequence on the consecutive (row, pair) counters
-// (drops of neighbouring rows anti-correlated at -0.1); two rounds are statistically indistinguishable from mix32 here
-// (drop rate, neighbour / row / column correlations and the variance of per-row rates, checked for p = 0.05 .. 0.25).
 __host__ __device__ __forceinline__ uint32_t fold32(uint32_t x, uint32_t k) {
   const uint64_t m = (uint64_t)x * k;
   return (uint32_t)m ^ (uint32_t)(m >> 32);
 }
-__host__ __device__ __forceinline__ uint32_t attn_drop_mix(uint32_t x) { return fold32(fold32(x, 0x9E3779B1u), 0x85EBCA77u); }
-__host__ __device__ __forceinline__ uint32_t attn_drop_bits(uint32_t rowconst, uint64_t rowkey, uint32_t pair_in_row) {
-  return attn_drop_mix(((uint32_t)(rowkey << 15) + pair_in_row) ^ rowconst);
+// block counter = (rowkey << 11) + kb: its low word is rowbase + kb, its high word goes through mix32 with the seed
+__host__ __device__ __forceinline__ uint32_t attn_drop_rowconst(uint64_t seed, uint64_t rowkey) {
+  return mix32((uint32_t)((rowkey << 11) >> 32) ^ (uint32_t)seed) ^ (uint32_t)(seed >> 32);
 }
+__host__ __device__ __forceinline__ uint32_t attn_drop_rowbase(uint64_t rowkey) { return (uint32_t)(rowkey << 11); }
+__host__ __device__ __forceinline__ uint32_t attn_drop_word(uint32_t rowconst, uint32_t rowbase, uint32_t kb, uint32_t thr) {
+  constexpr uint32_t K3[16] = {0xC2B2AE3Du, 0x27D4EB2Fu, 0x165667B1u, 0xD3A2646Du, 0xFD7046C5u, 0xB55A4F09u, 0x7FEB352Du, 0x846CA68Bu,
+                               0xCC9E2D51u, 0x1B873593u, 0xE6546B65u, 0x2C1B3C6Du, 0x297A2D39u, 0x5BD1E995u, 0x68E31DA5u, 0xB5297A4Du};
+  const uint32_t h = fold32(fold32((rowbase + kb) ^ rowconst, 0x9E3779B1u), 0x85EBCA77u);
+  uint32_t ge = 0xffffffffu;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const uint32_t w = fold32(h, K3[i]);
+    const uint32_t t = 0u - ((thr >> i) & 1u);          // (uniform: thr is a kernel parameter)
+    ge = (w & ge) | ((w | ge) & ~t);
+  }
+  return thr >= 65536u ? 0u : ge;
+}
+__host__ __device__ __forceinline__ int attn_drop_bit_of_key(int k) { return 8 * (k & 3) + 7 - ((k & 31) >> 2); }
 __host__ __device__ __forceinline__ bool attn_drop_keep(const AttnDropout& d, uint64_t rowkey, int k) {
-  const uint32_t bits = attn_drop_bits(attn_drop_rowconst(d.seed, rowkey), rowkey, (uint32_t)k >> 1);
-  return ((bits >> ((k & 1) * 16)) & 0xffffu) >= d.thr;
+  const uint32_t w = attn_drop_word(attn_drop_rowconst(d.seed, rowkey), attn_drop_rowbase(rowkey), (uint32_t)k >> 5, d.thr);
+  return (w >> attn_drop_bit_of_key(k)) & 1u;
 }
+#ifdef __CUDACC__
+// 0 / ~0 masks out of a word shifted so that the wanted decisions are byte sign bits (ws = word << s for keys 4 s .. 4 s + 3):
+// attn_drop_pair_mask(ws, 0 / 1): both 16-bit halves for keys (4 s, 4 s + 1) / (4 s + 2, 4 s + 3); attn_drop_full_mask(ws, j): key 4 s + j
+// (pair / j are compile-time constants after unrolling at every call site)
+// (inline PTX: the __byte_perm intrinsic only honours three bits per selector nibble, the sign-replicate flag is the fourth)
+__device__ __forceinline__ uint32_t prmt_sign(uint32_t a, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(0u), "r"(sel));
+  return d;
+}
+__device__ __forceinline__ uint32_t attn_drop_pair_mask(uint32_t ws, int pair) { return prmt_sign(ws, pair ? 0xBBAAu : 0x9988u); }
+__device__ __forceinline__ uint32_t attn_drop_full_mask(uint32_t ws, int j) { return prmt_sign(ws, 0x8888u + 0x1111u * (uint32_t)j); }
+// 32 x 32 bit transpose across a warp: lane b ends up with bit l = bit b of lane l's x.  Used by the kernels whose threads own a
+// KEY (dK / dV orientation): lane l builds the word of query column l, the transpose hands every key its 32 query decisions.
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+  for (int k = 16; k >= 1; k >>= 1) {
+    const uint32_t m = k == 16 ? 0x0000ffffu : k == 8 ? 0x00ff00ffu : k == 4 ? 0x0f0f0f0fu : k == 2 ? 0x33333333u : 0x55555555u;
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, k);
+    x = (lane & k) ? ((x & ~m) | ((y & ~m) >> k)) : ((x & m) | ((y & m) << k));
+  }
+  return x;
+}
+// Thread = key row (lane = key & 31, the warp's 32 keys are one aligned block kb), 32 query columns c = 0 .. 31 with hash
+// constants rc[c] / rb[c] (attn_drop_rowconst / attn_drop_rowbase of the column's row): returns the word whose bit
+// 8 j + 7 - s is the decision of (column 4 s + j, this thread's key) - the same layout along the columns as attn_drop_word has
+// along the keys, so the callers use the same shift + prmt.  Lane l hashes column perm(l), perm(8 j + 7 - s) = 4 s + j.
+__device__ __forceinline__ uint32_t attn_drop_word_transposed(const uint32_t* rc, const uint32_t* rb, uint32_t kb, uint32_t thr, int lane) {
+  const int c = 4 * (7 - (lane & 7)) + (lane >> 3);
+  const uint32_t w = attn_drop_word(rc[c], rb[c], kb, thr);              // bit 8 j + 7 - s: key 4 s + j of column c
+  const uint32_t t = warp_transpose32(w, lane);                          // lane b: bit l = (column perm(l), key of bit b)
+  return __shfl_sync(0xffffffffu, t, attn_drop_bit_of_key(lane));        // the lane that holds this thread's key
+}
+#endif
 
 // 2^x on the MUFU pipe (ex2.approx.ftz): ~2 ulp, no denormal fix-up code around it
 __device__ __forceinline__ float fast_exp2(float x) {

@@ -164,3 +164,73 @@ def test_weight_cache_entries_die_with_their_parameter():
         del p, c, r
     gc.collect()
     assert len(WEIGHTS._store) == 0
+
+
+# ---- attention-probability dropout: the bit-parallel mask function of csrc/common.cuh, restated in numpy ---------------
+def _attn_drop_word(seed, rowkey, kb, thr):
+    """attn_drop_word(attn_drop_rowconst(seed, rowkey), attn_drop_rowbase(rowkey), kb, thr) of common.cuh: the 32 keep
+    decisions of keys [32 kb, 32 kb + 32) of probability row `rowkey`; key 4 s + j is bit 8 j + 7 - s."""
+    import numpy as np
+    m32, u = np.uint64(0xFFFFFFFF), np.uint64
+    k3 = [0xC2B2AE3D, 0x27D4EB2F, 0x165667B1, 0xD3A2646D, 0xFD7046C5, 0xB55A4F09, 0x7FEB352D, 0x846CA68B,
+          0xCC9E2D51, 0x1B873593, 0xE6546B65, 0x2C1B3C6D, 0x297A2D39, 0x5BD1E995, 0x68E31DA5, 0xB5297A4D]
+
+    def mix32(x):
+        x = x & m32
+        x = x ^ (x >> u(16)); x = (x * u(0x7FEB352D)) & m32
+        x = x ^ (x >> u(15)); x = (x * u(0x846CA68B)) & m32
+        return x ^ (x >> u(16))
+
+    def fold32(x, k):
+        m = (x & m32) * u(k)
+        return (m ^ (m >> u(32))) & m32
+
+    rowkey, kb = np.asarray(rowkey, dtype=np.uint64), np.asarray(kb, dtype=np.uint64)
+    sh = rowkey << u(11)
+    rc = mix32((sh >> u(32)) ^ u(seed & 0xFFFFFFFF)) ^ u(seed >> 32)
+    h = fold32(fold32((((sh & m32) + kb) & m32) ^ rc, 0x9E3779B1), 0x85EBCA77)
+    ge = np.full(h.shape, 0xFFFFFFFF, dtype=np.uint64)
+    for i in range(16):                                        # bit-sliced u >= thr, least significant slice first
+        w = fold32(h, k3[i])
+        ge = (w & ge) if (thr >> i) & 1 else (w | ge)
+    return ge
+
+
+def test_attention_dropout_mask_function_known_answers():
+    """Values printed by a HOST build of common.cuh (the functions are __host__ __device__): pins the numpy restatement
+    below to the kernels' definition; tests/test_training_gpu.py pins every kernel to acai_attn_dropout_mask."""
+    import numpy as np
+    want = {(0, 0): 4294918143, (0, 1): 3200253695, (0, 37): 3154116575, (1, 0): 4290772991, (1, 1): 4026507263,
+            (1, 37): 4278188031, (5000000, 0): 4294696927, (5000000, 1): 4294964987, (5000000, 37): 3220699135,
+            ((1 << 33) + 17, 0): 2885681151, ((1 << 33) + 17, 1): 4294959039, ((1 << 33) + 17, 37): 4269785023}
+    thr = 6554                                                 # dropout_threshold(0.1f)
+    for (rk, kb), v in want.items():
+        assert int(_attn_drop_word(0xACA100000042, np.array([rk]), np.array([kb]), thr)[0]) == v
+
+
+@pytest.mark.parametrize("p", [0.05, 0.1, 0.25])
+def test_attention_dropout_mask_statistics(p):
+    """Drop rate, neighbour correlations along keys / rows / the diagonal, and the variance of per-row, per-column and
+    per-32-key-block drop counts against the binomial, on 2 048 rows x 1 024 keys of one head."""
+    import numpy as np
+    thr = int(p * 65536 + 0.5)
+    rows, nkeys = 2048, 1024
+    rk = np.arange(rows, dtype=np.uint64) + np.uint64(123457)
+    w = _attn_drop_word(99, rk[:, None], np.arange(nkeys // 32, dtype=np.uint64)[None, :], thr)
+    kk = np.arange(32)
+    bit = (8 * (kk & 3) + 7 - (kk >> 2)).astype(np.uint64)
+    drop = 1.0 - ((w[:, :, None] >> bit[None, None, :]) & np.uint64(1)).reshape(rows, nkeys).astype(np.float64)
+    n = drop.size
+    assert abs(drop.mean() - thr / 65536) < 4 * (p * (1 - p) / n) ** 0.5
+
+    def corr(a, b):
+        a, b = a - a.mean(), b - b.mean()
+        return float((a * b).mean() / ((a * a).mean() * (b * b).mean()) ** 0.5)
+
+    lim = 5 / n ** 0.5                                          # five standard errors of a zero correlation
+    for a, b in ((drop[:, :-1], drop[:, 1:]), (drop[:, :-2], drop[:, 2:]), (drop[:, :-4], drop[:, 4:]),
+                 (drop[:, :-32], drop[:, 32:]), (drop[:-1], drop[1:]), (drop[:-2], drop[2:]), (drop[:-1, :-1], drop[1:, 1:])):
+        assert abs(corr(a, b)) < lim
+    assert 0.85 < drop.mean(axis=1).var() / (p * (1 - p) / nkeys) < 1.15
+    assert 0.85 < drop.mean(axis=0).var() / (p * (1 - p) / rows) < 1.15
+    assert 0.95 < drop.reshape(rows, nkeys // 32, 32).sum(axis=2).var() / (32 * p * (1 - p)) < 1.05

@@ -159,7 +159,9 @@ __host__ __device__ __forceinline__ uint32_t attn_drop_word(uint32_t rowconst, u
                                0xCC9E2D51u, 0x1B873593u, 0xE6546B65u, 0x2C1B3C6Du, 0x297A2D39u, 0x5BD1E995u, 0x68E31DA5u, 0xB5297A4Du};
   const uint32_t h = fold32(fold32((rowbase + kb) ^ rowconst, 0x9E3779B1u), 0x85EBCA77u);
   uint32_t ge = 0xffffffffu;
+#ifdef __CUDA_ARCH__
 #pragma unroll
+#endif
   for (int i = 0; i < 16; ++i) {
     const uint32_t w = fold32(h, K3[i]);
     const uint32_t t = 0u - ((thr >> i) & 1u);          // (uniform: thr is a kernel parameter)

@@ -752,16 +752,25 @@ extern "C" int acai_adamw_step(float* param, const float* grad, float* exp_avg, 
 }
 
 namespace acai {
-int wgrad_tcgen05(const void* dz, int64_t ldz, const void* x, int64_t ldx, float* dw, int64_t ldo, int n_out, int k_in, int T,
-                  cudaStream_t st);
+int wgrad_tcgen05(const void* dz, int64_t ldz, const void* x, int64_t ldx, float* dw, int64_t ldo, float* dbias, int n_out, int k_in,
+                  int T, cudaStream_t st);
 }
 
 extern "C" int acai_wgrad_accumulate(const void* dz, int64_t ldz, const void* x, int64_t ldx, int32_t dtype, float* dw,
                                      int64_t ldw, int32_t n_out, int32_t k_in, int32_t tokens, void* stream) {
   ACAI_CHECK_ARG(dz && x && dw && n_out > 0 && k_in > 0 && tokens > 0, "acai_wgrad_accumulate: bad argument");
   if (dtype != ACAI_BF16) { set_error("acai_wgrad_accumulate: only bf16 operands run on the tensor-core path"); return ACAI_ERR_UNSUPPORTED; }
-  int rc = acai::wgrad_tcgen05(dz, ldz, x, ldx, dw, ldw, n_out, k_in, tokens, (cudaStream_t)stream);
+  int rc = acai::wgrad_tcgen05(dz, ldz, x, ldx, dw, ldw, nullptr, n_out, k_in, tokens, (cudaStream_t)stream);
   if (rc == ACAI_ERR_UNSUPPORTED) set_error("acai_wgrad_accumulate: operands are not TMA-addressable (16-byte aligned rows needed)");
+  return rc;
+}
+
+extern "C" int acai_wgrad_bias_accumulate(const void* dz, int64_t ldz, const void* x, int64_t ldx, int32_t dtype, float* dw,
+                                          int64_t ldw, float* dbias, int32_t n_out, int32_t k_in, int32_t tokens, void* stream) {
+  ACAI_CHECK_ARG(dz && x && dw && dbias && n_out > 0 && k_in > 0 && tokens > 0, "acai_wgrad_bias_accumulate: bad argument");
+  if (dtype != ACAI_BF16) { set_error("acai_wgrad_bias_accumulate: only bf16 operands run on the tensor-core path"); return ACAI_ERR_UNSUPPORTED; }
+  int rc = acai::wgrad_tcgen05(dz, ldz, x, ldx, dw, ldw, dbias, n_out, k_in, tokens, (cudaStream_t)stream);
+  if (rc == ACAI_ERR_UNSUPPORTED) set_error("acai_wgrad_bias_accumulate: operands are not TMA-addressable (16-byte aligned rows needed)");
   return rc;
 }
 

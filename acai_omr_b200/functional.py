@@ -100,25 +100,27 @@ class _Linear(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             wt = _weights().get_t(weight, dt, rows)                      # [K, N]
             dx = ops.linear(dz, wt, out_dtype=dt).view(ctx.x_shape)
+        # the bias gradient rides in the weight-gradient kernel's pass over dz when both are wanted (ops.wgrad_accumulate)
+        want_b = ctx.has_bias and ctx.needs_input_grad[2]
+        db_target = db_full = None
+        if want_b:
+            g = _owned_grad(ctx.bias_ref)
+            if g is not None:
+                db_target = g if rows is None else g[rows[0]:rows[1]]
+            else:
+                db_full = torch.zeros(weight.shape[0], dtype=torch.float32, device=dz.device)
+                db_target = db_full if rows is None else db_full[rows[0]:rows[1]]
+                db = db_full
         if ctx.needs_input_grad[1]:
             g = _owned_grad(weight)
             if g is not None:            # accumulate straight into the (flat) gradient buffer: no temporary, no add kernel
-                ops.wgrad_accumulate(dz, x2, g if rows is None else g[rows[0]:rows[1]])
+                ops.wgrad_accumulate(dz, x2, g if rows is None else g[rows[0]:rows[1]], dbias=db_target)
             else:
                 dw = torch.zeros(weight.shape if rows is None else (rows[1] - rows[0], weight.shape[1]), dtype=torch.float32,
                                  device=dz.device)
-                dw = _full_rows(ops.wgrad_accumulate(dz, x2, dw), weight, rows)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            bias = ctx.bias_ref
-            g = _owned_grad(bias)
-            if g is not None:
-                ops.colsum(dz, out=g if rows is None else g[rows[0]:rows[1]], accumulate=True)
-            else:
-                db = ops.colsum(dz)
-                if rows is not None:
-                    full = torch.zeros(weight.shape[0], dtype=torch.float32, device=db.device)
-                    full[rows[0]:rows[1]] = db
-                    db = full
+                dw = _full_rows(ops.wgrad_accumulate(dz, x2, dw, dbias=db_target), weight, rows)
+        elif want_b:
+            ops.colsum(dz, out=db_target, accumulate=True)
         if ctx.res_meta is not None and ctx.needs_input_grad[3]:
             shape, rdt = ctx.res_meta
             dres = dy.reshape(shape)
@@ -170,6 +172,18 @@ def _bias_grad(bias, dz):
     return ops.colsum(dz)
 
 
+def _weight_bias_grad(weight, bias, dz, x2, need_w, need_b):
+    """(dW, db) of one nn.Linear: when both are wanted, the bias gradient comes out of the weight-gradient kernel's own pass
+    over dz (ops.wgrad_accumulate(dbias=...)); entries are None where the trainer owns the gradient buffer (or not needed)."""
+    if not (need_w and need_b):
+        return (_weight_grad(weight, dz, x2) if need_w else None), (_bias_grad(bias, dz) if need_b else None)
+    gw, gb = _owned_grad(weight), _owned_grad(bias)
+    dw = gw if gw is not None else torch.zeros(weight.shape, dtype=torch.float32, device=dz.device)
+    db = gb if gb is not None else torch.zeros(bias.shape, dtype=torch.float32, device=dz.device)
+    ops.wgrad_accumulate(dz, x2, dw, dbias=db)
+    return (None if gw is not None else dw), (None if gb is not None else db)
+
+
 class _FeedForward(torch.autograd.Function):
     """linear2(dropout(gelu(linear1(x)))) [+ x]: the feed-forward block as ONE tape node, so that the GELU (+ its dropout)
     rides in the up-projection GEMM's epilogue (acai_linear_gelu_train) and the GELU backward in the epilogue of the
@@ -208,16 +222,10 @@ class _FeedForward(torch.autograd.Function):
         if dz is None:
             dz = ops.gelu_bwd(ops.linear(dy2, w2t, out_dtype=dt), z, out_dtype=dt, dropout_p=p, dropout_seed=seed)
         dx = dw1 = db1 = dw2 = db2 = None
-        if ctx.needs_input_grad[3]:
-            dw2 = _weight_grad(w2, dy2, h)
-        if ctx.needs_input_grad[4]:
-            db2 = _bias_grad(b2, dy2)
+        dw2, db2 = _weight_bias_grad(w2, b2, dy2, h, ctx.needs_input_grad[3], ctx.needs_input_grad[4])
         if ctx.needs_input_grad[0]:
             dx = ops.linear(dz, _weights().get_t(w1, dt, None), residual=dy2 if add_residual else None, out_dtype=dt).view(shape)
-        if ctx.needs_input_grad[1]:
-            dw1 = _weight_grad(w1, dz, x2)
-        if ctx.needs_input_grad[2]:
-            db1 = _bias_grad(b1, dz)
+        dw1, db1 = _weight_bias_grad(w1, b1, dz, x2, ctx.needs_input_grad[1], ctx.needs_input_grad[2])
         return dx, dw1, db1, dw2, db2, None, None, None
 
 

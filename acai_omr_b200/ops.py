@@ -492,22 +492,38 @@ def wgrad_supported(dz, x, dw):
             dw.data_ptr() % 16 == 0 and x.shape[1] >= 8)
 
 
-def wgrad_accumulate(dz, x, dw):
+# bias gradients from the weight-gradient kernel's own pass over dz (acai_wgrad_bias_accumulate); ACAI_FUSE_BIAS_GRAD=0 runs
+# acai_wgrad_accumulate + acai_colsum (the fixed-order two-stage column sum) instead
+FUSE_BIAS_GRAD = os.environ.get("ACAI_FUSE_BIAS_GRAD", "1") != "0"
+
+
+def wgrad_accumulate(dz, x, dw, dbias=None):
     """dw[n_out, k_in] += dz[T, n_out]^T @ x[T, k_in] in place on the tensor cores (acai_wgrad_accumulate), reading both
-    operands token-major; falls back to explicit transposes + the forward GEMM when TMA cannot address the operands."""
+    operands token-major; falls back to explicit transposes + the forward GEMM when TMA cannot address the operands.
+    `dbias` (fp32 [n_out], contiguous): += the column sums of dz, from the same pass over dz where the tensor-core kernel runs
+    (acai_wgrad_bias_accumulate), by acai_colsum otherwise."""
     _cuda(dz, x, dw)
     T, n_out = dz.shape
     k_in = x.shape[1]
     if dw.shape != (n_out, k_in) or x.shape[0] != T:
         raise AcaiError("wgrad_accumulate: shape mismatch")
+    if dbias is not None and (dbias.dtype != torch.float32 or dbias.shape != (n_out,) or not dbias.is_contiguous()):
+        raise AcaiError("wgrad_accumulate: dbias must be a contiguous fp32 vector of n_out elements")
     if T == 0:
         return dw
     if wgrad_supported(dz, x, dw):
+        if dbias is not None and FUSE_BIAS_GRAD:
+            name = "acai_wgrad_bias_accumulate" if Profile.active is None else f"acai_wgrad_bias_accumulate[{n_out}x{k_in}x{T}]"
+            _call(name, _lib.load().acai_wgrad_bias_accumulate, _p(dz), dz.stride(0), _p(x), x.stride(0), _dt(dz), _p(dw),
+                  dw.stride(0), _p(dbias), n_out, k_in, T, _stream(), flops=2.0 * T * n_out * k_in)
+            return dw
         name = "acai_wgrad_accumulate" if Profile.active is None else f"acai_wgrad_accumulate[{n_out}x{k_in}x{T}]"
         _call(name, _lib.load().acai_wgrad_accumulate, _p(dz), dz.stride(0), _p(x), x.stride(0), _dt(dz), _p(dw), dw.stride(0),
               n_out, k_in, T, _stream(), flops=2.0 * T * n_out * k_in)
     else:
         dw += linear(transpose_pad(dz), transpose_pad(x), out_dtype=torch.float32)
+    if dbias is not None:
+        colsum(dz, out=dbias, accumulate=True)
     return dw
 
 

@@ -408,6 +408,15 @@ int acai_linear_gelu_bwd(const void* dy, int64_t ldd, const void* wt, int64_t ld
 int acai_wgrad_accumulate(const void* dz, int64_t ldz, const void* x, int64_t ldx, int32_t dtype, float* dw, int64_t ldw,
                           int32_t n_out, int32_t k_in, int32_t tokens, void* stream);
 
+/* The same with the BIAS gradient from the same pass:  dbias[n_out] += column sums of dz (fp32, accumulated with atomic
+ * adds: like the split-K reduce-adds of dw, not in a fixed order).  Autograd of nn.Linear's bias inside every
+ * nn.Transformer*Layer of the reference's training step (omr_teacher_force_train.py:120, pre_train.py:57): the dz boxes
+ * the weight-gradient pipeline stages in shared memory are summed there by four extra warps, so dz is not read a second
+ * time by acai_colsum.  Same ACAI_ERR_UNSUPPORTED contract (nothing written; the caller runs acai_wgrad_accumulate's
+ * fallback and acai_colsum). */
+int acai_wgrad_bias_accumulate(const void* dz, int64_t ldz, const void* x, int64_t ldx, int32_t dtype, float* dw, int64_t ldw,
+                               float* dbias, int32_t n_out, int32_t k_in, int32_t tokens, void* stream);
+
 /* One AdamW update (torch.optim.AdamW semantics; omr_teacher_force_train.py:207, mae_pre_train.py) of a flat fp32
  * parameter segment, `grad_scale` applied to the gradient first (1/world_size after a summed all-reduce).
  * `param_bf16` (may be NULL) receives the bf16 copy of the updated parameters that the tensor-core GEMMs read. */

@@ -504,6 +504,49 @@ def test_wgrad_accumulate_tensor_core(T, n_out, k_in):
         assert not bool(dwf[:n_out].any()) and not bool(dwf[2 * n_out:].any())
 
 
+@pytest.mark.parametrize("T,n_out,k_in", [(1000, 768, 768), (63, 128, 256), (5000, 3072, 768), (777, 200, 136), (4096, 64, 64),
+                                          (20000, 1024, 4096), (130, 8, 1024), (1, 264, 72), (64 * 37 + 1, 2304, 768)])
+def test_wgrad_with_bias_gradient_from_the_same_pass(T, n_out, k_in):
+    """acai_wgrad_bias_accumulate: dW as acai_wgrad_accumulate AND db += column sums of dZ, summed from the dZ boxes the
+    pipeline stages in shared memory (ragged token / feature tails are TMA zero fill); against fp64 and acai_colsum."""
+    dz = rnd(T, n_out, seed=64, dtype=torch.bfloat16)
+    x = rnd(T, k_in, seed=65, dtype=torch.bfloat16)
+    dw0, db0 = rnd(n_out, k_in, seed=66), rnd(n_out, seed=67)
+    dw, db = dw0.clone(), db0.clone()
+    assert ops.wgrad_supported(dz, x, dw) and ops.FUSE_BIAS_GRAD
+    n0 = ops.launch_count()
+    ops.wgrad_accumulate(dz, x, dw, dbias=db)
+    assert ops.launch_count() - n0 == 1                                      # one kernel: no column-sum pass
+    assert rel_err(dw, dw0.double() + dz.double().t() @ x.double()) < 1e-5
+    assert rel_err(db, db0.double() + dz.double().sum(0)) < 1e-5
+    assert rel_err(db - db0, ops.colsum(dz)) < 1e-5
+    # a strided dZ view (the K slice of a fused QKV gradient) into row slices of the destinations
+    if n_out % 8 == 0:
+        big = rnd(T, 3 * n_out, seed=68, dtype=torch.bfloat16)
+        dwf, dbf = torch.zeros(3 * n_out, k_in, device=DEV), torch.zeros(3 * n_out, device=DEV)
+        ops.wgrad_accumulate(big[:, n_out:2 * n_out], x, dwf[n_out:2 * n_out], dbias=dbf[n_out:2 * n_out])
+        assert rel_err(dbf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().sum(0)) < 1e-5
+        assert not bool(dbf[:n_out].any()) and not bool(dbf[2 * n_out:].any())
+        assert rel_err(dwf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().t() @ x.double()) < 1e-5
+
+
+def test_linear_autograd_bias_gradient_fused_and_separate_agree(monkeypatch):
+    """functional.linear's backward with the bias gradient inside the weight-gradient kernel (default) and through acai_colsum."""
+    x = rnd(300, 256, seed=70, dtype=torch.bfloat16)
+    w = rnd(520, 256, seed=71).requires_grad_(True)
+    b = rnd(520, seed=72).requires_grad_(True)
+    dy = rnd(300, 520, seed=73, dtype=torch.bfloat16)
+    grads = []
+    for fuse in (True, False):
+        monkeypatch.setattr(ops, "FUSE_BIAS_GRAD", fuse)
+        w.grad = b.grad = None
+        F.linear(x, w, b, rows=(8, 520 - 8)).backward(dy[:, 8:-8])
+        grads.append((w.grad.clone(), b.grad.clone()))
+    assert rel_err(grads[0][0], grads[1][0]) < 1e-6 and rel_err(grads[0][1], grads[1][1]) < 1e-5
+    assert not bool(grads[0][1][:8].any()) and not bool(grads[0][1][-8:].any())
+    assert rel_err(grads[0][1][8:-8], dy[:, 8:-8].double().sum(0)) < 1e-5
+
+
 @pytest.mark.parametrize("hard", [False, True])
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1.5e-2)])
 def test_gumbel_softmax_fwd_bwd(hard, dtype, tol):

@@ -15,6 +15,8 @@ images) and the second LayerNorm output used by the cached decoder.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import ops
@@ -50,14 +52,42 @@ def _full_rows(grad_rows, like, rows):
     return full
 
 
+# ------------------------------------------------------------------------------------------ residual-gradient hand-over
+class GradBox:
+    """A post-norm sub-layer reads its input rows x twice: as the operand of its first GEMM and as the residual added to its
+    output.  Autograd would add the two gradients of x with an elementwise kernel (71 `at::add` launches, 2.5 ms of the
+    teacher-forced step).  Instead the node that owns the residual add (`put`: out_proj / the block's output dropout) leaves
+    the residual gradient here and reports none, and the node of the first GEMM (`take`: in_proj / linear1), whose backward
+    always runs later, adds it inside its dX GEMM's epilogue (`residual=`).  Only used when both uses are the SAME tensor."""
+    __slots__ = ("grad",)
+
+    def __init__(self):
+        self.grad = None
+
+    def take(self, like):
+        g, self.grad = self.grad, None
+        if g is not None and (g.dtype != like.dtype or g.numel() != like.numel()):
+            g = g.to(like.dtype)
+        return g
+
+
+GRAD_BOX = os.environ.get("ACAI_GRAD_BOX", "1") != "0"
+
+
+def grad_box(x, residual):
+    """A GradBox when `residual` is the very tensor `x` and it needs a gradient (else None: the plain autograd path)."""
+    return GradBox() if (GRAD_BOX and residual is x and x is not None and x.requires_grad and torch.is_grad_enabled()) else None
+
+
 # ------------------------------------------------------------------------------------------ linear (+GELU, +residual)
 class _Linear(torch.autograd.Function):
     """y = act(x W^T + b) + residual.   dX = dZ W,  dW = dZ^T X (fp32 out),  db = colsum(dZ),  dres = dY.
     In training the GELU is not fused into the GEMM epilogue: the pre-activation z is kept for the backward."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, act, out_dtype, rows, dropout_p=0.0, dropout_seed=0):
+    def forward(ctx, x, weight, bias, residual, act, out_dtype, rows, dropout_p=0.0, dropout_seed=0, box_put=None, box_take=None):
         dt = x.dtype
+        ctx.box_put, ctx.box_take = box_put, box_take
         K = x.shape[-1]
         x2 = x.reshape(-1, K)
         if x2.stride(-1) != 1:
@@ -99,7 +129,9 @@ class _Linear(torch.autograd.Function):
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
             wt = _weights().get_t(weight, dt, rows)                      # [K, N]
-            dx = ops.linear(dz, wt, out_dtype=dt).view(ctx.x_shape)
+            # (the residual gradient of the block this GEMM opens, left by the node that closed it: GradBox)
+            rg = ctx.box_take.take(x2) if ctx.box_take is not None else None
+            dx = ops.linear(dz, wt, residual=rg.reshape(x2.shape) if rg is not None else None, out_dtype=dt).view(ctx.x_shape)
         # the bias gradient rides in the weight-gradient kernel's pass over dz when both are wanted (ops.wgrad_accumulate)
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         db_target = db_full = None
@@ -126,7 +158,9 @@ class _Linear(torch.autograd.Function):
             dres = dy.reshape(shape)
             if dres.dtype != rdt:
                 dres = dres.to(rdt)
-        return dx, dw, db, dres, None, None, None, None, None
+            if ctx.box_put is not None:
+                ctx.box_put.grad, dres = dres, None
+        return dx, dw, db, dres, None, None, None, None, None, None, None
 
 
 def _linear_out_dropout(x2, w, b, residual, out_dtype, p, seed):
@@ -136,8 +170,10 @@ def _linear_out_dropout(x2, w, b, residual, out_dtype, p, seed):
     return y
 
 
-def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None, rows=None, dropout_p=0.0):
+def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None, rows=None, dropout_p=0.0, box_put=None,
+           box_take=None):
     """dropout(act(x @ weight[rows].T + bias[rows])) + residual; `weight` / `bias` are the (fp32 master) parameters.
+    `box_put` / `box_take`: see GradBox (the residual gradient leaves through / the input gradient absorbs the box).
     `dropout_p` > 0: with the GELU activation the feed-forward block's inner nn.Dropout (fused into the GELU kernel); without
     an activation `residual + dropout(x W^T + b)`, the sub-layer output dropout (fused into the GEMM epilogue)."""
     dt = x.dtype
@@ -152,7 +188,7 @@ def linear(x, weight, bias=None, act=ops.ACT_NONE, residual=None, out_dtype=None
         y = ops.linear(x, _weights().get(weight, dt, rows), _slice(bias, rows), act=act, residual=residual,
                        out_dtype=out_dtype or dt)
         return ops.dropout(y, dropout_p, seed) if dropout_p > 0.0 else y
-    return _Linear.apply(x, weight, bias, residual, act, out_dtype or dt, rows, dropout_p, seed)
+    return _Linear.apply(x, weight, bias, residual, act, out_dtype or dt, rows, dropout_p, seed, box_put, box_take)
 
 
 def _weight_grad(weight, dz, x2):
@@ -190,8 +226,9 @@ class _FeedForward(torch.autograd.Function):
     down-projection's dX GEMM (acai_linear_gelu_bwd); the block's residual gradient is fused into the last dX GEMM."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, add_residual, dropout_p, dropout_seed):
+    def forward(ctx, x, w1, b1, w2, b2, add_residual, dropout_p, dropout_seed, box_take=None):
         dt = x.dtype
+        ctx.box_take = box_take
         x2 = x.reshape(-1, x.shape[-1])
         if x2.stride(-1) != 1:
             x2 = x2.contiguous()
@@ -224,20 +261,22 @@ class _FeedForward(torch.autograd.Function):
         dx = dw1 = db1 = dw2 = db2 = None
         dw2, db2 = _weight_bias_grad(w2, b2, dy2, h, ctx.needs_input_grad[3], ctx.needs_input_grad[4])
         if ctx.needs_input_grad[0]:
-            dx = ops.linear(dz, _weights().get_t(w1, dt, None), residual=dy2 if add_residual else None, out_dtype=dt).view(shape)
+            rg = dy2 if add_residual else (ctx.box_take.take(x2) if ctx.box_take is not None else None)
+            dx = ops.linear(dz, _weights().get_t(w1, dt, None), residual=rg.reshape(x2.shape) if rg is not None else None,
+                            out_dtype=dt).view(shape)
         dw1, db1 = _weight_bias_grad(w1, b1, dz, x2, ctx.needs_input_grad[1], ctx.needs_input_grad[2])
-        return dx, dw1, db1, dw2, db2, None, None, None
+        return dx, dw1, db1, dw2, db2, None, None, None, None
 
 
-def feed_forward(x, w1, b1, w2, b2, add_residual=True, dropout_p=0.0):
+def feed_forward(x, w1, b1, w2, b2, add_residual=True, dropout_p=0.0, box_take=None):
     """linear2(dropout(gelu(linear1(x)))) (+ x): the feed-forward block of nn.Transformer*Layer up to (not including) its
-    outer dropout; `dropout_p` is the inner nn.Dropout's rate."""
+    outer dropout; `dropout_p` is the inner nn.Dropout's rate.  `box_take`: GradBox of the residual add that follows."""
     dt = x.dtype
     seed = ops.DropoutState.next_seed() if dropout_p > 0.0 else 0
     if not needs_grad(x, w1, b1, w2, b2):
         h = linear(x, w1, b1, act=ops.ACT_GELU, out_dtype=dt, dropout_p=dropout_p)
         return linear(h, w2, b2, residual=x if add_residual else None, out_dtype=dt)
-    return _FeedForward.apply(x, w1, b1, w2, b2, add_residual, dropout_p, seed)
+    return _FeedForward.apply(x, w1, b1, w2, b2, add_residual, dropout_p, seed, box_take)
 
 
 # ------------------------------------------------------------------------------------------ LayerNorm
@@ -720,8 +759,9 @@ class _Dropout(torch.autograd.Function):
     """y = residual + dropout(x): nn.Dropout followed by the residual add of a post-norm block."""
 
     @staticmethod
-    def forward(ctx, x, residual, p, seed):
+    def forward(ctx, x, residual, p, seed, box_put=None):
         ctx.meta = (p, seed, residual is not None and residual.dtype)
+        ctx.box_put = box_put
         return ops.dropout(x, p, seed, residual=residual)
 
     @staticmethod
@@ -731,14 +771,16 @@ class _Dropout(torch.autograd.Function):
         dres = None
         if rdt is not False and ctx.needs_input_grad[1]:
             dres = dy if dy.dtype == rdt else dy.to(rdt)
-        return dx, dres, None, None
+            if ctx.box_put is not None:
+                ctx.box_put.grad, dres = dres, None
+        return dx, dres, None, None, None
 
 
-def dropout(x, p, training, residual=None):
+def dropout(x, p, training, residual=None, box_put=None):
     """nn.Dropout(p)(x) (+ residual).  Identity (or a plain add folded elsewhere by the caller) when not training or p == 0."""
     if not training or p <= 0.0:
         raise ops.AcaiError("functional.dropout: call only when a mask is needed (training and p > 0)")
     seed = ops.DropoutState.next_seed()
     if not needs_grad(x, residual):
         return ops.dropout(x, p, seed, residual=residual)
-    return _Dropout.apply(x, residual, p, seed)
+    return _Dropout.apply(x, residual, p, seed, box_put)

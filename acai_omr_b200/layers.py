@@ -195,37 +195,40 @@ class MultiheadAttention(nn.Module):
         the owning layer applies the same p to the block output before the residual add (dropout1/dropout2)."""
         return self.dropout if self.training else 0.0
 
-    def _out(self, a, residual, dt):
+    def _out(self, a, residual, dt, box=None):
         p = self._p()
         # residual + dropout(out_proj(a)): dropout and residual add both in the GEMM epilogue (acai_linear_dropout); the
         # sum comes out in the residual's dtype (fp32 when the stream is fp32)
         return F.linear(a, self.out_proj.weight, self.out_proj.bias, residual=residual,
-                        out_dtype=dt if residual is None else residual.dtype, dropout_p=p)
+                        out_dtype=dt if residual is None else residual.dtype, dropout_p=p, box_put=box)
 
-    def self_attention_core(self, x, pk, causal):
-        """softmax(q k^T) v over packed rows x:[T, D], heads concatenated, before the output projection."""
+    def self_attention_core(self, x, pk, causal, box=None):
+        """softmax(q k^T) v over packed rows x:[T, D], heads concatenated, before the output projection.
+        `box`: functional.GradBox of the block's residual add (training, residual rows = x)."""
         dt, D = x.dtype, self.embed_dim
-        qkv = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt)
+        qkv = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, box_take=box)
         return F.self_attention(qkv, pk, self.num_heads, self.head_dim, causal,
                                 flops=4.0 * D * pk.sum_sq * (0.5 if causal else 1.0), dropout_p=self._p())
 
     def self_attention_packed(self, x, pk, causal, residual):
         """out_proj(softmax(q k^T) v) + residual over packed rows x:[T, D] (x: GEMM operand rows, residual: stream rows)."""
-        return self._out(self.self_attention_core(x, pk, causal), residual, x.dtype)
+        box = F.grad_box(x, residual)
+        return self._out(self.self_attention_core(x, pk, causal, box), residual, x.dtype, box)
 
     def project_memory_packed(self, mem):
         """[K | V] = mem . W_kv^T + b_kv  (kv_caching.py:241-245) over packed memory rows."""
         dt, D = mem.dtype, self.embed_dim
         return F.linear(mem, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(D, 3 * D))
 
-    def cross_attention_core(self, x, kv, pq, pk):
+    def cross_attention_core(self, x, kv, pq, pk, box=None):
         dt, D = x.dtype, self.embed_dim
-        q = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(0, D))
+        q = F.linear(x, self.in_proj_weight, self.in_proj_bias, out_dtype=dt, rows=(0, D), box_take=box)
         return F.cross_attention(q, kv, pq, pk, self.num_heads, self.head_dim,
                                  flops=4.0 * D * sum(a_ * b_ for a_, b_ in zip(pq.lens, pk.lens)), dropout_p=self._p())
 
     def cross_attention_packed(self, x, kv, pq, pk, residual):
-        return self._out(self.cross_attention_core(x, kv, pq, pk), residual, x.dtype)
+        box = F.grad_box(x, residual)
+        return self._out(self.cross_attention_core(x, kv, pq, pk, box), residual, x.dtype, box)
 
 
 class Packed:
@@ -334,8 +337,9 @@ def _mlp_residual(layer, x, dt, stream=None):
         h = F.linear(x, l1.weight, l1.bias, act=ops.ACT_GELU, out_dtype=dt, dropout_p=p)
         return F.linear(h, l2.weight, l2.bias, residual=x, out_dtype=dt, dropout_p=p)
     if p > 0.0:
-        return F.dropout(F.feed_forward(x, l1.weight, l1.bias, l2.weight, l2.bias, add_residual=False, dropout_p=p), p, True,
-                         residual=x)
+        box = F.grad_box(x, x)
+        return F.dropout(F.feed_forward(x, l1.weight, l1.bias, l2.weight, l2.bias, add_residual=False, dropout_p=p, box_take=box),
+                         p, True, residual=x, box_put=box)
     return F.feed_forward(x, l1.weight, l1.bias, l2.weight, l2.bias, add_residual=True)
 
 

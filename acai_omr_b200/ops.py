@@ -59,12 +59,24 @@ class Profile:
         return out
 
 
+# ACAI_NVTX=1: every C-ABI call sits in an NVTX range named after its entry point (the kernel family), so that
+# `ncu --nvtx --nvtx-include "acai_attn_varlen_fwd/"` (or any NVTX-aware tool) can pick launches by family.  SURVEY section 5.
+NVTX = os.environ.get("ACAI_NVTX", "0") == "1"
+
+
 def _call(name, fn, *args, flops=0.0, nbytes=0.0):
     prof = Profile.active
     if prof is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-    _lib.check(fn(*args), name)
+    if NVTX:
+        torch.cuda.nvtx.range_push(name)
+        try:
+            _lib.check(fn(*args), name)
+        finally:
+            torch.cuda.nvtx.range_pop()
+    else:
+        _lib.check(fn(*args), name)
     if prof is not None:
         e1.record()
         prof.records.append((name, e0, e1, flops, nbytes))

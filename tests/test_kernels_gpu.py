@@ -357,3 +357,16 @@ def test_linear_bf16_decode_step_shapes(M, N, K):
     big = rnd(M, 3 * K, seed=75).bfloat16()
     y = ops.linear(big[:, K:2 * K], w, b, out_dtype=torch.float32)
     close(y, (big[:, K:2 * K].double() @ w.double().t() + b.double()).float(), 1e-3, 2e-3)
+
+
+def test_nvtx_ranges_around_entry_points(monkeypatch):
+    """ACAI_NVTX=1: every C-ABI call is wrapped in an NVTX range named after its entry point (push / pop balanced, results unchanged)."""
+    pushed, popped = [], []
+    monkeypatch.setattr(ops, "NVTX", True)
+    monkeypatch.setattr(torch.cuda.nvtx, "range_push", lambda name: pushed.append(name))
+    monkeypatch.setattr(torch.cuda.nvtx, "range_pop", lambda: popped.append(1))
+    x = torch.randn(33, 64, device="cuda")
+    g, b = torch.ones(64, device="cuda"), torch.zeros(64, device="cuda")
+    y = ops.layernorm(x, g, b, 1e-5)
+    assert pushed and len(pushed) == len(popped) and pushed[0].startswith("acai_layernorm")
+    assert torch.allclose(y, torch.nn.functional.layer_norm(x, (64,), g, b, 1e-5), atol=1e-5)

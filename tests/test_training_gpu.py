@@ -739,6 +739,39 @@ def test_training_mode_with_reference_dropout_rates():
     assert first == losses[0]                                  # manual_seed replays the run
 
 
+@pytest.mark.parametrize("autocast", [False, True])
+def test_residual_gradient_hand_over_matches_autograd_adds(monkeypatch, autocast):
+    """functional.GradBox: the residual gradient of every post-norm block (self-attention, cross-attention, feed-forward with
+    its output dropout) is added inside the block's first dX GEMM instead of by an autograd add - same masks (replayed seed),
+    same gradients as the plain autograd path up to the one bf16 rounding the fused add saves."""
+    from acai_omr_b200 import synth
+    from acai_omr_b200 import functional as Fn
+    enc = M.FineTuneOMREncoder(16, 12, 40, 2, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.05)
+    dec = M.OMRDecoder(48, VOCAB, num_layers=2, hidden_dim=128, num_heads=2, mlp_dim=256, transformer_dropout=0.1)
+    vit = M.TeacherForcedViTOMR(enc, None, dec, transition_head_dim=128, transition_head_dropout=0.05)
+    synth.rerandomise_(vit, 6)
+    vit = vit.to(DEV).train()
+    imgs = [synth.synth_system(h, w, i).to(DEV) for i, (h, w) in enumerate([(64, 160), (32, 320), (96, 96)])]
+    batch = list(zip(imgs, [synth.synth_lmx(L, i).to(DEV) for i, L in enumerate([20, 33, 12])]))
+    runs = []
+    for box in (True, False):
+        monkeypatch.setattr(Fn, "GRAD_BOX", box)
+        ops.DropoutState.manual_seed(3)
+        vit.zero_grad()
+        n0 = ops.launch_count()
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            pred, tgt = vit(batch)
+            loss = M.OMRCELoss(vit.decoder.pad_idx)(pred, tgt)
+        loss.backward()
+        runs.append((float(loss.detach()), {n: p.grad.clone() for n, p in vit.named_parameters() if p.grad is not None},
+                     ops.launch_count() - n0))
+    assert runs[0][0] == runs[1][0]                            # identical forward
+    assert runs[0][1].keys() == runs[1][1].keys()
+    tol = 2e-2 if autocast else 1e-5
+    for name, g in runs[0][1].items():
+        assert rel_err(g, runs[1][1][name]) < tol, name
+
+
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1.5e-2)])
 def test_gelu_linear_with_fused_dropout(dtype, tol):
     """Linear -> GELU -> Dropout as one autograd node (dropout fused into the GELU kernels, mask regenerated in the backward)."""

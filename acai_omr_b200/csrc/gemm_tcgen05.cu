@@ -16,6 +16,8 @@
 #include <mutex>
 #include <unordered_map>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
@@ -719,7 +721,15 @@ static int dispatch_tiles(const void* a, int64_t lda, const void* w, int64_t ldw
   // more SMs stream the weight matrix
   const int m_tiles = (M + BM - 1) / BM, sms = num_sms();
   auto tiles = [&](int bn) { return m_tiles * ((N + bn - 1) / bn); };
-  if (N > 128 && tiles(256) >= sms) return launch_gemm<256>(a, lda, w, ldw, ep, M, N, K, st);
+  // Wave quantisation: the persistent CTAs walk the tiles in rounds of #SMs, so a problem of a few rounds pays for its
+  // last, partly empty one (MAE encoder, 7 962 x 768: 189 tiles of 256 columns = 2 rounds at 64 %; 378 of 128 = 3 half-size
+  // rounds at 85 %).  Cost model: rounds x tile width; the narrower tile must win by more than 6 % (it reads A twice as often).
+  auto cost = [&](int bn) { return ((tiles(bn) + sms - 1) / sms) * bn; };
+  static const bool quant = [] { const char* e = getenv("ACAI_GEMM_WAVE_QUANT"); return !e || atoi(e) != 0; }();
+  if (N > 128 && tiles(256) >= sms) {
+    if (quant && cost(128) * 100 < cost(256) * 94) return launch_gemm<128>(a, lda, w, ldw, ep, M, N, K, st);
+    return launch_gemm<256>(a, lda, w, ldw, ep, M, N, K, st);
+  }
   if ((N > 64 && tiles(128) >= sms) || ep.act >= ACT_GELU_TRAIN) return launch_gemm<128>(a, lda, w, ldw, ep, M, N, K, st);
   return launch_gemm<64>(a, lda, w, ldw, ep, M, N, K, st);
 }

@@ -21,6 +21,8 @@
 // swizzle - fold the eight row classes with shuffles when the item ends and atomicAdd 128 sums into db.  The stage is
 // released by the MMAs' commit AND these warps (empty barrier count 5).  The separate column-sum pass over dZ (a whole
 // extra read of every gradient tensor: 5.7 ms of the 158 ms teacher-forced step) disappears.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 
@@ -237,10 +239,30 @@ static int launch_wgrad(const CUtensorMap& ta, const CUtensorMap& tb, const CUte
     attr_set = true;
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN), nk = (T + BK - 1) / BK, sms = num_sms();
-  // enough (tile, token-range) items for two waves, each range at least 8 stages long
+  // How many token ranges?  The persistent CTAs take the (tile, range) items in rounds of #SMs and every item costs its
+  // k-blocks plus an epilogue (a 128 x BN fp32 reduce-add, about a dozen k-blocks' worth): pick the split that minimises
+  // rounds x (k-blocks per item + epilogue), each range at least 8 stages long.  (Round 1's rule - just over two waves of
+  // items - left a third, almost empty round: 768 x 768 ran 306 items on 148 SMs, 69 % busy, 897 TFLOP/s against 1 300 for
+  // the shapes that happened to divide well.)  ACAI_WGRAD_SPLIT=0 restores that rule for A/B runs.
+  static const bool tuned = [] { const char* e = getenv("ACAI_WGRAD_SPLIT"); return !e || atoi(e) != 0; }();
   int splits = (2 * sms + tiles - 1) / tiles;
   if (splits > nk / 8) splits = nk / 8;
   if (splits < 1) splits = 1;
+  if (tuned) {
+    const int max_splits = nk / 8 < 1 ? 1 : nk / 8;
+    constexpr int EPI = 12;
+    long best_cost = -1;
+    // (a range is ONE fp32 accumulation chain in TMEM; the tensor core's adds truncate, so the error against fp64 grows
+    // linearly with the chain: 1.1e-5 relative per 10 k tokens, profiles/ubench/wgrad_precision.py - chains stay <= 32 k tokens,
+    // <= 4e-5, forty times below one bf16 rounding of the same sum)
+    constexpr int MAX_KPER = 512;
+    for (int sp = 1; sp <= max_splits && (long)tiles * sp <= 4L * sms + tiles; ++sp) {
+      const int kp = (nk + sp - 1) / sp, real = (nk + kp - 1) / kp;        // (empty trailing ranges are dropped)
+      if (kp > MAX_KPER && sp < max_splits) continue;
+      const long rounds = ((long)tiles * real + sms - 1) / sms, cost = rounds * (kp + EPI);
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = real; }
+    }
+  }
   const int kper = (nk + splits - 1) / splits;
   splits = (nk + kper - 1) / kper;                     // drop empty trailing ranges
   const int items = tiles * splits;

@@ -155,6 +155,15 @@ def linear(x, weight, bias=None, act=ACT_NONE, residual=None, out_dtype=None, ou
         rdt = _dt(r2)
     b = _f32c(bias)
     lib = _lib.load()
+    # A long bf16 GEMM whose contraction is not a multiple of 64 (the 227-class head's dX in training: [tokens, 227] x [1024, 227],
+    # 0.7 ms per step on the SIMT kernel) runs on the tensor cores behind two zero-padded operand copies (~20 MB).
+    if K % 64 != 0 and K > 64 and M >= 1024 and N >= 64 and x2.dtype == torch.bfloat16 and w.dtype == torch.bfloat16:
+        Kp = (K + 63) // 64 * 64
+        xp = torch.zeros((M, Kp), dtype=torch.bfloat16, device=x2.device)
+        xp[:, :K].copy_(x2)
+        wp = torch.zeros((N, Kp), dtype=torch.bfloat16, device=x2.device)
+        wp[:, :K].copy_(w)
+        x2, w, K, lda = xp, wp, Kp, Kp
     name = "acai_linear_fwd" if Profile.active is None else \
         f"acai_linear_fwd[{M}x{N}x{K}{',gelu' if act else ''}{',res' if r2 is not None else ''}]"
     _call(name, lib.acai_linear_fwd, _p(x2), _dt(x2), lda, _p(w), _dt(w), w.stride(0), _p(b), _p(r2), rdt, ldr,

@@ -189,3 +189,15 @@ def test_linear_layernorm_refuses_what_it_cannot_do():
     g, be = torch.ones(640, device=DEV), torch.zeros(640, device=DEV)
     w = rnd(640, 768, seed=2).bfloat16()
     assert ops.linear_layernorm(x, w, rnd(640, seed=3), rnd(64, 640, seed=4), g, be, 1e-5, True) is None      # N not 512 / 768 / 1024
+
+
+def test_ragged_contraction_is_padded_onto_the_tensor_cores():
+    """K = 227 (the vocabulary head's dX in training): ops.linear pads the contraction with zero columns; same result as fp64."""
+    x = torch.randn(1500, 227, device="cuda").bfloat16()
+    w = (torch.randn(256, 227, device="cuda") * 227 ** -0.5).bfloat16()
+    r = torch.randn(1500, 256, device="cuda").bfloat16()
+    with ops.Profile() as prof:
+        y = ops.linear(x, w, residual=r)
+    assert any(k.startswith("acai_linear_fwd[1500x256x256") for k in prof.summary()), list(prof.summary())   # contraction 227 -> 256
+    ref = x.double() @ w.double().t() + r.double()
+    assert float((y.double() - ref).norm() / ref.norm()) < 5e-3

@@ -494,13 +494,16 @@ def test_wgrad_accumulate_tensor_core(T, n_out, k_in):
     assert ops.wgrad_supported(dz, x, dw)
     ops.wgrad_accumulate(dz, x, dw)
     ref = dw0.double() + dz.double().t() @ x.double()
-    assert rel_err(dw, ref) < 1e-5
+    # (a token range is one fp32 accumulation chain on the tensor core, whose adds truncate: 1.1e-5 per 10 k tokens against
+    # fp64, chains are capped at 32 k tokens - profiles/ubench/wgrad_precision.py; a bf16-output matmul of the same operands is
+    # at 1.7e-3)
+    assert rel_err(dw, ref) < 4e-5
     # strided views (a slice of a fused QKV gradient buffer) and a row slice of the destination
     big = rnd(T, 3 * n_out, seed=63, dtype=torch.bfloat16)
     if n_out % 8 == 0:
         dwf = torch.zeros(3 * n_out, k_in, device=DEV)
         ops.wgrad_accumulate(big[:, n_out:2 * n_out], x, dwf[n_out:2 * n_out])
-        assert rel_err(dwf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().t() @ x.double()) < 1e-5
+        assert rel_err(dwf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().t() @ x.double()) < 4e-5
         assert not bool(dwf[:n_out].any()) and not bool(dwf[2 * n_out:].any())
 
 
@@ -517,7 +520,7 @@ def test_wgrad_with_bias_gradient_from_the_same_pass(T, n_out, k_in):
     n0 = ops.launch_count()
     ops.wgrad_accumulate(dz, x, dw, dbias=db)
     assert ops.launch_count() - n0 == 1                                      # one kernel: no column-sum pass
-    assert rel_err(dw, dw0.double() + dz.double().t() @ x.double()) < 1e-5
+    assert rel_err(dw, dw0.double() + dz.double().t() @ x.double()) < 4e-5
     assert rel_err(db, db0.double() + dz.double().sum(0)) < 1e-5
     assert rel_err(db - db0, ops.colsum(dz)) < 1e-5
     # a strided dZ view (the K slice of a fused QKV gradient) into row slices of the destinations
@@ -527,7 +530,7 @@ def test_wgrad_with_bias_gradient_from_the_same_pass(T, n_out, k_in):
         ops.wgrad_accumulate(big[:, n_out:2 * n_out], x, dwf[n_out:2 * n_out], dbias=dbf[n_out:2 * n_out])
         assert rel_err(dbf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().sum(0)) < 1e-5
         assert not bool(dbf[:n_out].any()) and not bool(dbf[2 * n_out:].any())
-        assert rel_err(dwf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().t() @ x.double()) < 1e-5
+        assert rel_err(dwf[n_out:2 * n_out], big[:, n_out:2 * n_out].double().t() @ x.double()) < 4e-5
 
 
 def test_linear_autograd_bias_gradient_fused_and_separate_agree(monkeypatch):

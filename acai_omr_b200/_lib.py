@@ -78,6 +78,7 @@ SIGNATURES = {
                            _i32, _p, _sz, _p],
     "acai_linear_gelu_train": [_p, _i64, _p, _i64, _p, _p, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],
     "acai_linear_gelu_bwd": [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],
+    "acai_linear_dgrad": [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _i32, _i32, _i32, _f32, _u64, _p],
     "acai_wgrad_accumulate": [_p, _i64, _p, _i64, _i32, _p, _i64, _i32, _i32, _i32, _p],
     "acai_wgrad_bias_accumulate": [_p, _i64, _p, _i64, _i32, _p, _i64, _p, _i32, _i32, _i32, _p],
     "acai_adamw_step": [_p, _p, _p, _p, _p, _i64, _f32, _f32, _f32, _f32, _f32, _i32, _f32, _p],

@@ -53,6 +53,8 @@ int linear_dropout_tcgen05(const void* a, int64_t lda, const void* w, int64_t ld
                            int64_t ldr, void* out, int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
 int linear_gelu_train_tcgen05(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* z, int64_t ldz,
                               void* h, int64_t ldh, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
+int linear_dgrad_tcgen05(const void* dz, int64_t ldz, const void* w, int64_t ldw, const void* res, int64_t ldr, const void* z,
+                         int64_t ldzz, void* out, int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
 int linear_gelu_bwd_tcgen05(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
                             int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st);
 
@@ -149,6 +151,21 @@ extern "C" int acai_linear_gelu_train(const void* a, int64_t lda, const void* w,
 
 // Its backward through the activation: dz = (dy @ wt^T) * gelu'(z) * mask, bf16, one GEMM (wt = the [N, K] transpose
 // of the down-projection weight).
+extern "C" int acai_linear_dgrad(const void* dz, int64_t ldz, const void* w, int64_t ldw, const void* residual, int64_t ldr,
+                                const void* z, int64_t ldzz, void* dx, int64_t ldo, int32_t M, int32_t N, int32_t K, float dropout_p,
+                                uint64_t dropout_seed, void* stream) {
+  ACAI_CHECK_ARG(dz && w && dx, "acai_linear_dgrad: null pointer");
+  ACAI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && ldz >= K && ldw >= N && ldo >= N && (!residual || ldr >= N) && (!z || ldzz >= N),
+                 "acai_linear_dgrad: bad sizes M=%d N=%d K=%d", M, N, K);
+  ACAI_CHECK_ARG(!(z && residual), "acai_linear_dgrad: z (GELU backward) and residual are exclusive");
+  ACAI_CHECK_ARG(dropout_p >= 0.0f && dropout_p < 1.0f, "acai_linear_dgrad: dropout_p must be in [0, 1)");
+  ACAI_CHECK_ARG(!z || ldzz == N || dropout_p == 0.0f, "acai_linear_dgrad: the dropout mask is indexed over a dense [M, N] tensor");
+  if (M == 0) return ACAI_OK;
+  int rc = acai::linear_dgrad_tcgen05(dz, ldz, w, ldw, residual, ldr, z, ldzz, dx, ldo, M, N, K, dropout_p, dropout_seed, (cudaStream_t)stream);
+  if (rc == ACAI_ERR_UNSUPPORTED) acai::set_error("acai_linear_dgrad: operands are not TMA-addressable (bf16, 16-byte aligned rows, N >= 128, K %% 64 == 0)");
+  return rc;
+}
+
 extern "C" int acai_linear_gelu_bwd(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
                                     int64_t ldo, int32_t M, int32_t N, int32_t K, float dropout_p, uint64_t dropout_seed,
                                     void* stream) {

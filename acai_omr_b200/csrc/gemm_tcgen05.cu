@@ -237,7 +237,11 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" 
 
 // OUT: 0 = generic epilogue (any shape/alignment), 1 = bf16 output via TMA, 2 = fp32 output via TMA.
 // MODE: 0 = inference / plain epilogue, 1 = ACT_GELU_TRAIN (OUT 1, RES 0), 2 = ACT_GELU_BWD (OUT 1, RES 1).
-template <int BN, int OUT, int RES, int MODE = 0>
+// BKN: the B operand is given as W[K, N] (contraction index = ROW: "MN-major" in UMMA terms) instead of W[N, K] - the dX = dZ W
+// GEMMs of the backward read the forward's weight copy as it lies in HBM, no transposed copy per step.  TMA brings
+// [64 contraction rows x 64 output columns] boxes, the descriptor walks them with LBO = 8 KB (next 64 output columns) and a
+// K step is 16 rows of 128 bytes - exactly how gemm_wgrad_tcgen05 reads both of its operands.
+template <int BN, int OUT, int RES, int MODE = 0, bool BKN = false>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                   const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_aux, Epi ep, int M, int N,
@@ -294,17 +298,23 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
         if (ptx::elect_one_sync()) {
           ptx::mbar_arrive_expect_tx(&full_bar[stage], A_BYTES + B_BYTES);
           ptx::tma_load_2d(smem_a + stage * A_BYTES, &tma_a, &full_bar[stage], kb * BK, m0);
-          ptx::tma_load_2d(smem_b + stage * B_BYTES, &tma_b, &full_bar[stage], kb * BK, n0);
+          if constexpr (BKN) {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i)
+              ptx::tma_load_2d(smem_b + stage * B_BYTES + i * 8192, &tma_b, &full_bar[stage], n0 + 64 * i, kb * BK);
+          } else {
+            ptx::tma_load_2d(smem_b + stage * B_BYTES, &tma_b, &full_bar[stage], kb * BK, n0);
+          }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN);
+    constexpr uint32_t IDESC = ptx::idesc_bf16_f32(BM, BN, false, BKN);
     const uint32_t tb0 = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint64_t adesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_a), 1024);
-    const uint64_t bdesc0 = ptx::smem_desc_sw128(ptx::smem_u32(smem_b), 1024);
+    const uint64_t bdesc0 = BKN ? ptx::smem_desc_sw128(ptx::smem_u32(smem_b), 1024, 8192) : ptx::smem_desc_sw128(ptx::smem_u32(smem_b), 1024);
     int stage = 0; uint32_t phase = 0; int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
@@ -319,7 +329,8 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
           const uint64_t adesc = adesc0 + (uint64_t)(stage * (A_BYTES >> 4)), bdesc = bdesc0 + (uint64_t)(stage * (B_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes along K inside the 128B swizzle row = +2 in the address field
-            ptx::umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, (kb != kb0 || k != 0) ? 1u : 0u);
+            ptx::umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + (BKN ? (uint64_t)k * (16 * 128 >> 4) : (uint64_t)(2 * k)), IDESC,
+                             (kb != kb0 || k != 0) ? 1u : 0u);
           ptx::umma_commit(&empty_bar[stage]);
           if (kb == kb1 - 1) ptx::umma_commit(&tfull_bar[as]);
         }
@@ -643,19 +654,34 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t 
   return make_tma_2d(map, ptr, ACAI_BF16, rows, cols, ld, box_rows, box_cols);
 }
 
-template <int BN, int OUT, int RES, int MODE = 0>
+template <int BN, int OUT, int RES, int MODE = 0, bool BKN = false>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& taux,
                           const Epi& ep, int M, int N, int K, cudaStream_t st) {
   static bool attr_set = false;
   constexpr size_t smem = smem_bytes<BN>();
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05<BN, OUT, RES, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ACAI_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05<BN, OUT, RES, MODE, BKN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  ACAI_CUDA(launch_pdl(gemm_bf16_tcgen05<BN, OUT, RES, MODE>, dim3(grid), dim3(THREADS), smem, st, ta, tb, to, taux, ep, M, N, K));
+  ACAI_CUDA(launch_pdl(gemm_bf16_tcgen05<BN, OUT, RES, MODE, BKN>, dim3(grid), dim3(THREADS), smem, st, ta, tb, to, taux, ep, M, N, K));
   return launch_status("gemm_bf16_tcgen05");
+}
+
+// dX = dZ[M, K] . W[K, N] (+ residual, or x gelu'(z) x mask): bf16 in, bf16 out through the TMA-store epilogue only
+template <int BN>
+static int launch_gemm_kn(const void* a, int64_t lda, const void* w, int64_t ldw, const Epi& ep, int M, int N, int K, cudaStream_t st) {
+  CUtensorMap ta, tb, to;
+  int rc = make_tma_2d_bf16(&ta, a, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
+  if (rc) return rc;
+  rc = make_tma_2d_bf16(&tb, w, (uint64_t)K, (uint64_t)N, (uint64_t)ldw, 64, 64);
+  if (rc) return rc;
+  rc = make_tma_2d(&to, ep.out, ACAI_BF16, (uint64_t)M, (uint64_t)N, (uint64_t)ep.ldo, 32, 64);
+  if (rc) return rc;
+  if (ep.act == ACT_GELU_BWD) return launch_variant<BN, 1, 1, 2, true>(ta, tb, to, to, ep, M, N, K, st);
+  if (!ep.res) return launch_variant<BN, 1, 0, 0, true>(ta, tb, to, to, ep, M, N, K, st);
+  return launch_variant<BN, 1, 1, 0, true>(ta, tb, to, to, ep, M, N, K, st);
 }
 
 template <int BN>
@@ -721,15 +747,10 @@ static int dispatch_tiles(const void* a, int64_t lda, const void* w, int64_t ldw
   // more SMs stream the weight matrix
   const int m_tiles = (M + BM - 1) / BM, sms = num_sms();
   auto tiles = [&](int bn) { return m_tiles * ((N + bn - 1) / bn); };
-  // Wave quantisation: the persistent CTAs walk the tiles in rounds of #SMs, so a problem of a few rounds pays for its
-  // last, partly empty one (MAE encoder, 7 962 x 768: 189 tiles of 256 columns = 2 rounds at 64 %; 378 of 128 = 3 half-size
-  // rounds at 85 %).  Cost model: rounds x tile width; the narrower tile must win by more than 6 % (it reads A twice as often).
-  auto cost = [&](int bn) { return ((tiles(bn) + sms - 1) / sms) * bn; };
-  static const bool quant = [] { const char* e = getenv("ACAI_GEMM_WAVE_QUANT"); return !e || atoi(e) != 0; }();
-  if (N > 128 && tiles(256) >= sms) {
-    if (quant && cost(128) * 100 < cost(256) * 94) return launch_gemm<128>(a, lda, w, ldw, ep, M, N, K, st);
-    return launch_gemm<256>(a, lda, w, ldw, ep, M, N, K, st);
-  }
+  // (Round 2f tried a wave-quantisation rule here - 128-column tiles when the last round of 256-column tiles would be mostly
+  // empty, e.g. MAE encoder 7 962 x 768: 189 tiles = 2 rounds at 64 % - and measured NO gain on the MAE step of the bench
+  // (20.29 vs 19.85 ms, in-box A/B): the narrower tile re-reads A twice as often and pays twice the epilogues.  Not kept.)
+  if (N > 128 && tiles(256) >= sms) return launch_gemm<256>(a, lda, w, ldw, ep, M, N, K, st);
   if ((N > 64 && tiles(128) >= sms) || ep.act >= ACT_GELU_TRAIN) return launch_gemm<128>(a, lda, w, ldw, ep, M, N, K, st);
   return launch_gemm<64>(a, lda, w, ldw, ep, M, N, K, st);
 }
@@ -758,6 +779,22 @@ int linear_gelu_bwd_tcgen05(const void* dy, int64_t ldd, const void* wt, int64_t
   Epi ep{nullptr, z, ACAI_BF16, ldz, dz, ACAI_BF16, ldo, ACT_GELU_BWD, nullptr, nullptr, 0, thr,
          thr ? 1.0f / (1.0f - dropout_p) : 1.0f, seed};
   return dispatch_tiles(dy, ldd, wt, ldw, ep, M, N, K, st);
+}
+
+// dX[M, N] = dZ[M, K] . W[K, N] with W as the forward keeps it ([out = K, in = N] rows): + residual (bf16), or, with z,
+// x gelu'(z) x dropout mask (the ACT_GELU_BWD epilogue).  ACAI_ERR_UNSUPPORTED unless TMA serves every operand.
+int linear_dgrad_tcgen05(const void* dz, int64_t ldz, const void* w, int64_t ldw, const void* res, int64_t ldr, const void* z,
+                         int64_t ldzz, void* out, int64_t ldo, int M, int N, int K, float dropout_p, uint64_t seed, cudaStream_t st) {
+  auto mis = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) != 0; };
+  if (K % BK != 0 || ldz % 8 != 0 || ldw % 8 != 0 || ldo % 8 != 0 || N % 8 != 0 || N < 128 || M < 1 || mis(dz) || mis(w) || mis(out) ||
+      (res && (mis(res) || ldr % 8 != 0)) || (z && (mis(z) || ldzz % 8 != 0 || res)))
+    return ACAI_ERR_UNSUPPORTED;
+  const uint32_t thr = dropout_threshold(dropout_p);
+  Epi ep{nullptr, z ? z : res, ACAI_BF16, z ? ldzz : ldr, out, ACAI_BF16, ldo, z ? ACT_GELU_BWD : ACAI_ACT_NONE, nullptr, nullptr, 0,
+         z ? thr : 0u, (z && thr) ? 1.0f / (1.0f - dropout_p) : 1.0f, seed};
+  const int m_tiles = (M + BM - 1) / BM;
+  if (N > 128 && m_tiles * ((N + 255) / 256) >= num_sms()) return launch_gemm_kn<256>(dz, ldz, w, ldw, ep, M, N, K, st);
+  return launch_gemm_kn<128>(dz, ldz, w, ldw, ep, M, N, K, st);
 }
 
 // out = residual + dropout(a @ w^T + bias), bf16, dense [M, N] output (the mask counter is row * N + column, the one

@@ -128,10 +128,14 @@ class _Linear(torch.autograd.Function):
                 dz = ops.dropout(dz, ctx.drop[0], ctx.drop[1])
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
-            wt = _weights().get_t(weight, dt, rows)                      # [K, N]
             # (the residual gradient of the block this GEMM opens, left by the node that closed it: GradBox)
             rg = ctx.box_take.take(x2) if ctx.box_take is not None else None
-            dx = ops.linear(dz, wt, residual=rg.reshape(x2.shape) if rg is not None else None, out_dtype=dt).view(ctx.x_shape)
+            rg = rg.reshape(x2.shape) if rg is not None else None
+            # dX = dZ W straight from the forward's [out, in] weight copy (MN-major B operand); else from a transposed copy
+            dx = ops.linear_dgrad(dz, _weights().get(weight, dt, rows), residual=rg) if dz.dim() == 2 else None
+            if dx is None:
+                dx = ops.linear(dz, _weights().get_t(weight, dt, rows), residual=rg, out_dtype=dt)
+            dx = dx.view(ctx.x_shape)
         # the bias gradient rides in the weight-gradient kernel's pass over dz when both are wanted (ops.wgrad_accumulate)
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         db_target = db_full = None
@@ -254,16 +258,21 @@ class _FeedForward(torch.autograd.Function):
             dy2 = dy2.to(dt)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        w2t = _weights().get_t(w2, dt, None)                                  # [hidden, d]
-        dz = ops.linear_gelu_bwd(dy2, w2t, z, p, seed) if dt == torch.bfloat16 else None
+        dz = ops.linear_dgrad(dy2, _weights().get(w2, dt, None), z=z, dropout_p=p, dropout_seed=seed) if ops.FUSE_GELU_GEMM else None
         if dz is None:
-            dz = ops.gelu_bwd(ops.linear(dy2, w2t, out_dtype=dt), z, out_dtype=dt, dropout_p=p, dropout_seed=seed)
+            w2t = _weights().get_t(w2, dt, None)                              # [hidden, d]
+            dz = ops.linear_gelu_bwd(dy2, w2t, z, p, seed) if dt == torch.bfloat16 else None
+            if dz is None:
+                dz = ops.gelu_bwd(ops.linear(dy2, w2t, out_dtype=dt), z, out_dtype=dt, dropout_p=p, dropout_seed=seed)
         dx = dw1 = db1 = dw2 = db2 = None
         dw2, db2 = _weight_bias_grad(w2, b2, dy2, h, ctx.needs_input_grad[3], ctx.needs_input_grad[4])
         if ctx.needs_input_grad[0]:
             rg = dy2 if add_residual else (ctx.box_take.take(x2) if ctx.box_take is not None else None)
-            dx = ops.linear(dz, _weights().get_t(w1, dt, None), residual=rg.reshape(x2.shape) if rg is not None else None,
-                            out_dtype=dt).view(shape)
+            rg = rg.reshape(x2.shape) if rg is not None else None
+            dx = ops.linear_dgrad(dz, _weights().get(w1, dt, None), residual=rg)
+            if dx is None:
+                dx = ops.linear(dz, _weights().get_t(w1, dt, None), residual=rg, out_dtype=dt)
+            dx = dx.view(shape)
         dw1, db1 = _weight_bias_grad(w1, b1, dz, x2, ctx.needs_input_grad[1], ctx.needs_input_grad[2])
         return dx, dw1, db1, dw2, db2, None, None, None, None
 

@@ -548,6 +548,35 @@ def wgrad_accumulate(dz, x, dw, dbias=None):
     return dw
 
 
+# dX GEMMs read the forward's [out, in] weight copy as an MN-major B operand (acai_linear_dgrad); ACAI_DGRAD_KN=0 makes the
+# callers transpose the weight every step and run acai_linear_fwd / acai_linear_gelu_bwd on it
+DGRAD_KN = os.environ.get("ACAI_DGRAD_KN", "1") != "0"
+
+
+def linear_dgrad(dz, weight, residual=None, z=None, dropout_p=0.0, dropout_seed=0):
+    """dx = dz @ weight (+ residual | * gelu'(z) * dropout mask) with `weight` the forward's [out, in] bf16 copy
+    (acai_linear_dgrad); None when the problem does not qualify (the caller runs the transposed-weight path)."""
+    if not DGRAD_KN or dz.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16 or dz.dim() != 2 or weight.dim() != 2:
+        return None
+    _cuda(dz, weight, residual, z)
+    M, K = dz.shape
+    N = weight.shape[1]
+    if weight.shape[0] != K or M == 0 or dz.stride(1) != 1 or weight.stride(1) != 1:
+        return None
+    for t in (residual, z):
+        if t is not None and (t.dtype != torch.bfloat16 or t.shape != (M, N) or t.stride(1) != 1):
+            return None
+    if z is not None and (residual is not None or z.stride(0) != N):
+        return None
+    out = torch.empty((M, N), dtype=torch.bfloat16, device=dz.device)
+    name = "acai_linear_dgrad" if Profile.active is None else \
+        f"acai_linear_dgrad[{M}x{N}x{K}{',gelu_bwd' if z is not None else ''}{',res' if residual is not None else ''}]"
+    ok = _try_call(name, _lib.load().acai_linear_dgrad, _p(dz), dz.stride(0), _p(weight), weight.stride(0), _p(residual),
+                   residual.stride(0) if residual is not None else 0, _p(z), z.stride(0) if z is not None else 0, _p(out),
+                   out.stride(0), M, N, K, float(dropout_p), C.c_uint64(dropout_seed), _stream(), flops=2.0 * M * N * K)
+    return out if ok else None
+
+
 ERR_UNSUPPORTED = -2
 # GELU (+ dropout) forward / backward inside the tcgen05 GEMM epilogues (acai_linear_gelu_train / acai_linear_gelu_bwd).
 # With the A&S erf form (~27 extra instructions per element on eight epilogue warps that are already the critical path at

@@ -400,6 +400,18 @@ int acai_linear_gelu_train(const void* a, int64_t lda, const void* w, int64_t ld
 int acai_linear_gelu_bwd(const void* dy, int64_t ldd, const void* wt, int64_t ldw, const void* z, int64_t ldz, void* dz,
                          int64_t ldo, int32_t M, int32_t N, int32_t K, float dropout_p, uint64_t dropout_seed, void* stream);
 
+/* Input gradient of a linear layer from the weight AS THE FORWARD HOLDS IT:  dx[M, N] = dz[M, K] . w[K, N]  with w the
+ * layer's [out_features = K, in_features = N] bf16 operand copy (autograd of F.linear inside every nn.Transformer*Layer,
+ * omr_teacher_force_train.py:120) - the contraction index is w's ROW, which tcgen05 reads as an "MN-major" B operand, so no
+ * transposed weight copy is made per step (acai_transpose + acai_linear_fwd on w^T was 139 launches of the teacher-forced
+ * step).  Epilogue: + residual (bf16 [M, N], optional: the residual-stream gradient of the block), or, with z (bf16 [M, N],
+ * the pre-activation acai_linear_gelu_train kept), x gelu'(z) x the dropout mask of (dropout_p, dropout_seed) - the
+ * acai_linear_gelu_bwd epilogue; z and residual are exclusive.  bf16 in / out.  ACAI_ERR_UNSUPPORTED (nothing launched)
+ * unless K % 64 == 0, N >= 128, N % 8 == 0 and every operand has 16-byte aligned rows; the caller then transposes. */
+int acai_linear_dgrad(const void* dz, int64_t ldz, const void* w, int64_t ldw, const void* residual, int64_t ldr, const void* z,
+                      int64_t ldzz, void* dx, int64_t ldo, int32_t M, int32_t N, int32_t K, float dropout_p, uint64_t dropout_seed,
+                      void* stream);
+
 /* Weight gradient of a linear layer, accumulated in place:  dw[n_out, k_in] += dz[tokens, n_out]^T . x[tokens, k_in]
  * (bf16 operands exactly as the forward/backward left them - no transposed copies; fp32 dw, typically the parameter's
  * slice of the flat gradient buffer).  tcgen05 GEMM with both operands MN-major, split over token ranges, partial

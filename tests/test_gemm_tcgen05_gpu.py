@@ -201,3 +201,36 @@ def test_ragged_contraction_is_padded_onto_the_tensor_cores():
     assert any(k.startswith("acai_linear_fwd[1500x256x256") for k in prof.summary()), list(prof.summary())   # contraction 227 -> 256
     ref = x.double() @ w.double().t() + r.double()
     assert float((y.double() - ref).norm() / ref.norm()) < 5e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 768, 2304), (63, 128, 64), (5000, 3072, 768), (777, 200, 192), (4096, 1024, 4096), (300, 136, 128)])
+def test_linear_dgrad_reads_the_forward_weight_copy(M, N, K):
+    """acai_linear_dgrad: dX = dZ W with W as [out = K, in = N] rows (MN-major B operand of tcgen05) - bit-identical to the GEMM on a
+    transposed copy of W (same MMAs in the same order), with and without the residual epilogue, ragged M / N tails."""
+    dz = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(K, N, device="cuda") * K ** -0.5).bfloat16()
+    r = torch.randn(M, N, device="cuda").bfloat16()
+    wt = w.t().contiguous()
+    for res in (None, r):
+        got = ops.linear_dgrad(dz, w, residual=res)
+        assert got is not None
+        assert torch.equal(got, ops.linear(dz, wt, residual=res, out_dtype=torch.bfloat16))
+        ref = dz.double() @ w.double() + (res.double() if res is not None else 0.0)
+        assert float((got.double() - ref).norm() / ref.norm()) < 5e-3
+    # a row slice of a fused [3D, D] weight (the q rows of the cross-attention in_proj) is a valid operand too
+    big = (torch.randn(3 * K, N, device="cuda") * K ** -0.5).bfloat16()
+    got = ops.linear_dgrad(dz, big[K:2 * K])
+    assert torch.equal(got, ops.linear(dz, big[K:2 * K].t().contiguous(), out_dtype=torch.bfloat16))
+
+
+@pytest.mark.parametrize("p", [0.0, 0.1])
+def test_linear_dgrad_gelu_backward_epilogue(p):
+    """... x gelu'(z) x dropout mask in the epilogue: the same numbers as acai_linear_gelu_bwd on the transposed weight."""
+    M, N, K = 1500, 1024, 256
+    dy = torch.randn(M, K, device="cuda").bfloat16()
+    w2 = (torch.randn(K, N, device="cuda") * K ** -0.5).bfloat16()          # linear2.weight: [d, hidden]
+    z = torch.randn(M, N, device="cuda").bfloat16()
+    got = ops.linear_dgrad(dy, w2, z=z, dropout_p=p, dropout_seed=77)
+    want = ops.linear_gelu_bwd(dy, w2.t().contiguous(), z, p, 77)
+    assert got is not None and want is not None and torch.equal(got, want)
+    assert ops.linear_dgrad(dy.float(), w2) is None                          # fp32: the caller's transposed-weight path

@@ -28,6 +28,9 @@ constexpr int BM = 128;           // UMMA_M (cta_group::1)
 constexpr int BK = 64;            // 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int EPI_WARPS = 8;
+#ifndef GEMM_EPI16_DEFAULT
+#define GEMM_EPI16_DEFAULT 1
+#endif
 constexpr int THREADS = 64 + EPI_WARPS * 32;   // 320
 
 // Training-only epilogue modes (internal; the public acai_act values are 0 / 1):
@@ -47,8 +50,12 @@ struct Epi {
 };
 
 template <int BN> constexpr int stages() { return BN >= 256 ? 4 : (BN >= 128 ? 6 : 8); }
-template <int BN> constexpr size_t smem_bytes() {
-  return (size_t)stages<BN>() * (BM * BK * 2 + BN * BK * 2) + EPI_WARPS * 4096 /*epilogue staging*/ +
+// EW = epilogue warps: 8, or 16 for the training epilogues (ACT_GELU_TRAIN / ACT_GELU_BWD), whose ~30 dependent instructions per
+// element run at ~0.45 IPC on two warps per scheduler and outlast the K = 768 main loop: four warps per scheduler, 64-column slabs,
+// three pipeline stages (the sixteen 4 KB staging tiles take the fourth stage's room)
+template <int BN, int EW> constexpr int stages_ew() { return EW == 16 ? 3 : stages<BN>(); }
+template <int BN, int EW = EPI_WARPS> constexpr size_t smem_bytes() {
+  return (size_t)stages_ew<BN, EW>() * (BM * BK * 2 + BN * BK * 2) + EW * 4096 /*epilogue staging*/ +
          2 * BN * 4 /*bias slices*/ + 256 /*barriers*/;
 }
 }  // namespace g5
@@ -233,7 +240,7 @@ __device__ __forceinline__ void epi_half_train(const Epi& ep, int pass, int64_t 
   }
 }
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory"); }
+template <int EW> __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory"); }
 
 // OUT: 0 = generic epilogue (any shape/alignment), 1 = bf16 output via TMA, 2 = fp32 output via TMA.
 // MODE: 0 = inference / plain epilogue, 1 = ACT_GELU_TRAIN (OUT 1, RES 0), 2 = ACT_GELU_BWD (OUT 1, RES 1).
@@ -241,19 +248,19 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" 
 // GEMMs of the backward read the forward's weight copy as it lies in HBM, no transposed copy per step.  TMA brings
 // [64 contraction rows x 64 output columns] boxes, the descriptor walks them with LBO = 8 KB (next 64 output columns) and a
 // K step is 16 rows of 128 bytes - exactly how gemm_wgrad_tcgen05 reads both of its operands.
-template <int BN, int OUT, int RES, int MODE = 0, bool BKN = false>
-__global__ void __launch_bounds__(THREADS, 1)
+template <int BN, int OUT, int RES, int MODE = 0, bool BKN = false, int EW = EPI_WARPS>
+__global__ void __launch_bounds__(64 + EW * 32, 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                   const __grid_constant__ CUtensorMap tma_out, const __grid_constant__ CUtensorMap tma_aux, Epi ep, int M, int N,
                   int K) {
-  constexpr int STAGES = stages<BN>();
+  constexpr int STAGES = stages_ew<BN, EW>();
   constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // power of two for BN in {32,64,128,256}
   extern __shared__ __align__(1024) uint8_t smem[];            // SWIZZLE_128B tiles need 1024-byte alignment
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * A_BYTES;
   uint8_t* staging = smem + STAGES * (A_BYTES + B_BYTES);                 // 8 warps x 4 KB
-  float* sbias = reinterpret_cast<float*>(staging + EPI_WARPS * 4096);    // [2][BN]
+  float* sbias = reinterpret_cast<float*>(staging + EW * 4096);           // [2][BN]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(sbias + 2 * BN);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
@@ -273,7 +280,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
-    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull_bar[s], 1); ptx::mbar_init(&tempty_bar[s], EPI_WARPS); }
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(&tfull_bar[s], 1); ptx::mbar_init(&tempty_bar[s], EW); }
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
@@ -339,10 +346,10 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
       }
     }
   } else {
-    const int ew = warp - 2;             // 0..7
+    const int ew = warp - 2;             // 0..EW-1
     const int lane_grp = warp & 3;       // TMEM lanes this warp may touch: 32*(warp%4) ..
-    const int half = ew >> 2;            // which half of the BN columns
-    constexpr int CPW = BN / 2;          // columns per warp
+    const int half = ew >> 2;            // which half (EW 16: quarter) of the BN columns
+    constexpr int CPW = BN / (EW / 4);   // columns per warp
     int it = 0;
     if constexpr (OUT != 0) {
       constexpr bool OUT_BF16 = OUT == 1;
@@ -370,7 +377,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap tma_a, const __grid_consta
           for (int hh = 0; hh < HALVES; ++hh) res_prefetch<RES>(ep, rrow, col0 + hh * 32, N, rb[hh]);
         }
         if (etid < BN) sbias[as * BN + etid] = bv;
-        epi_bar_sync();
+        epi_bar_sync<EW>();
         ptx::mbar_wait(&tfull_bar[as], aphase);
         ptx::tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + as * BN + half * CPW;
@@ -654,19 +661,29 @@ int make_tma_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t 
   return make_tma_2d(map, ptr, ACAI_BF16, rows, cols, ld, box_rows, box_cols);
 }
 
-template <int BN, int OUT, int RES, int MODE = 0, bool BKN = false>
+template <int BN, int OUT, int RES, int MODE = 0, bool BKN = false, int EW = EPI_WARPS>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const CUtensorMap& taux,
                           const Epi& ep, int M, int N, int K, cudaStream_t st) {
   static bool attr_set = false;
-  constexpr size_t smem = smem_bytes<BN>();
+  constexpr size_t smem = smem_bytes<BN, EW>();
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05<BN, OUT, RES, MODE, BKN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ACAI_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05<BN, OUT, RES, MODE, BKN, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  ACAI_CUDA(launch_pdl(gemm_bf16_tcgen05<BN, OUT, RES, MODE, BKN>, dim3(grid), dim3(THREADS), smem, st, ta, tb, to, taux, ep, M, N, K));
+  ACAI_CUDA(launch_pdl(gemm_bf16_tcgen05<BN, OUT, RES, MODE, BKN, EW>, dim3(grid), dim3(64 + EW * 32), smem, st, ta, tb, to, taux, ep, M, N, K));
   return launch_status("gemm_bf16_tcgen05");
+}
+
+// Sixteen epilogue warps for the 256-column ACT_GELU_TRAIN epilogue (see smem_bytes).  Measured in one box
+// (profiles/r2f_training_step.md): 63 664 x 3 072 x 768: 401 -> 325 us, 41 976 x 4 096 x 1 024: 373 -> 324 us - on by default.
+// The same on ACT_GELU_BWD is SLOWER (401 -> 592 us with both accumulator halves live: 576 threads are allocated as 640, 96
+// registers per thread, spills; 388 -> 413 us one half at a time, no spills) and on the output-dropout epilogue too
+// (90 -> 125 us): both stay on eight warps.  ACAI_GEMM_EPI16=0 selects eight warps everywhere (A/B runs, read per call).
+static bool epi16(int bit) {
+  const char* e = getenv("ACAI_GEMM_EPI16");
+  return (((e ? atoi(e) : GEMM_EPI16_DEFAULT) >> bit) & 1) != 0;
 }
 
 // dX = dZ[M, K] . W[K, N] (+ residual, or x gelu'(z) x mask): bf16 in, bf16 out through the TMA-store epilogue only
@@ -709,6 +726,7 @@ static int launch_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, c
     CUtensorMap taux;
     rc = make_tma_2d(&taux, ep.aux, ACAI_BF16, (uint64_t)M, (uint64_t)N, (uint64_t)ep.ld_aux, 32, 64);
     if (rc) return rc;
+    if constexpr (BN == 256) { if (epi16(0)) return launch_variant<BN, 1, 0, 1, false, 16>(ta, tb, to, taux, ep, M, N, K, st); }
     return launch_variant<BN, 1, 0, 1>(ta, tb, to, taux, ep, M, N, K, st);
   }
   if (ep.act == ACT_GELU_BWD) {
@@ -717,7 +735,7 @@ static int launch_gemm(const void* a, int64_t lda, const void* w, int64_t ldw, c
   }
   if (ep.out_dt == ACAI_BF16) {
     if (res == 0) return launch_variant<BN, 1, 0>(ta, tb, to, to, ep, M, N, K, st);
-    if (res == 1) return launch_variant<BN, 1, 1>(ta, tb, to, to, ep, M, N, K, st);
+    if (res == 1) return launch_variant<BN, 1, 1>(ta, tb, to, to, ep, M, N, K, st);   // (16 warps on the output-dropout epilogue: 1.08 -> 1.50 ms, spills)
     return launch_variant<BN, 1, 2>(ta, tb, to, to, ep, M, N, K, st);
   }
   if (res == 0) return launch_variant<BN, 2, 0>(ta, tb, to, to, ep, M, N, K, st);

@@ -796,7 +796,7 @@ def layernorm_bwd(dy, x, residual, gamma, eps, dv_dtype=None, dgamma_acc=None, d
     _call("acai_layernorm_bwd", lib.acai_layernorm_bwd, _p(dy2), _dt(dy2), _p(x2), _dt(x2), _p(r2),
           _dt(r2) if r2 is not None else 0, _p(_f32c(gamma)), float(eps), _p(dv), _dt(dv), _p(dg), _p(db), 1 if acc else 0, rows,
           cols, _p(ws), ws.numel(), _stream())
-    _bump(2)
+    _bump(1)
     return (dv.view(x.shape), None, None) if acc else (dv.view(x.shape), dg, db)
 
 

@@ -1,7 +1,10 @@
 mkdir -p gpurun_out
+F="ms/step\|gelu_bwd\|,res\]\|linear_dropout"
 {
 echo "== gpu tests"; timeout 900 python -m pytest tests -q -m gpu -x 2>&1 | tail -3
-echo "== tf"; timeout 600 python profiles/prof_train.py tf 2>&1 | grep "ms/step\|layernorm" | head -5
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"layernorm_bwd_vec" --launch-skip 70 --launch-count 2 -f -o gpurun_out/r2h_lnbwd python profiles/prof_train.py tf > gpurun_out/r2h_ncu_ln.log 2>&1; echo "ncu rc=$?"
-} > gpurun_out/r2h_b.log 2>&1
-tail -12 gpurun_out/r2h_b.log
+echo "== tf coalesced residual loads"; timeout 600 python profiles/prof_train.py tf 2>&1 | grep "$F" | head -14
+echo "== tf ACAI_GEMM_RES_COALESCED=0"; ACAI_GEMM_RES_COALESCED=0 timeout 600 python profiles/prof_train.py tf 2>&1 | grep "$F" | head -14
+echo "== mae"; timeout 600 python profiles/prof_train.py mae 2>&1 | grep "ms/step" | head -2
+echo "== mae ACAI_GEMM_RES_COALESCED=0"; ACAI_GEMM_RES_COALESCED=0 timeout 600 python profiles/prof_train.py mae 2>&1 | grep "ms/step" | head -2
+} > gpurun_out/r2h_c.log 2>&1
+tail -50 gpurun_out/r2h_c.log

@@ -78,7 +78,12 @@ struct AttnParams {
 // tile holds a PAIR of heads and this CTA's head is addressed by a 64-byte start offset in the MMA descriptors.
 // POLY: how many of every 4 exponentials are evaluated with exp2_fma on the FMA pipe instead of MUFU.EX2 (0, 1 or 2).
 // The MUFU unit (16 results / clk / SM) is this kernel's busiest pipe; the FMA pipe is mostly idle.
-template <int DH, bool DROP, int POLY, int NBUF, int CTAS, int SB, int QT, int PIPE = 0>
+// SPEC: the exponentials of block j use the reference maximum as block j - 1 left it and do NOT wait for block j's own row
+// maximum (which runs on the ALU pipe beside the MUFU work): any reference gives the same softmax after the division by l, the
+// maximum only has to be advanced before the values overflow.  The check moves behind the P hand-off: a row whose maximum grew by
+// more than 2^8 has O / l rescaled once PV_j has landed, before block j + 1; a jump of more than 2^60 inside ONE block (which
+// would overflow bf16 P) recomputes the block the old way.  Takes the max -> vote -> branch chain out of every block's critical path.
+template <int DH, bool DROP, int POLY, int NBUF, int CTAS, int SB, int QT, int PIPE = 0, int SPEC = 0>
 __global__ void __launch_bounds__((Cfg<NBUF, CTAS, SB, QT>::THREADS), CTAS)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
               const __grid_constant__ CUtensorMap tma_v, AttnParams p) {
@@ -326,6 +331,68 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
       const int kbase = j * SB;
       const bool edge = kbase + SB > warp_min_end;   // ragged end / causal diagonal: mask keys >= my_end
       uint32_t s[NS];
+      if constexpr (SPEC && !TWOPASS && SB == 32) {
+        if (j > 0 && !__any_sync(0xffffffffu, m == -INFINITY)) {
+          ptx::tmem_ld_32x32(tmem_s, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+          ptx::tmem_ld_wait();
+          if (edge) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (kbase + i >= my_end) s[i] = 0xff800000u;   // -inf
+          }
+          const float moff = m * scale_log2;
+          const uint64_t sc2 = ptx::pack_f32x2(scale_log2, scale_log2), mo2 = ptx::pack_f32x2(-moff, -moff);
+          uint64_t l2 = ptx::pack_f32x2(0.0f, 0.0f);
+          const uint32_t dw0 = DROP ? attn_drop_word(rowconst, rowbase, (uint32_t)(kbase >> 5), p.drop.thr) : 0u;
+          uint32_t pk[16];
+          float a0 = -INFINITY, a1 = -INFINITY, a2 = -INFINITY, a3 = -INFINITY;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float x0, x1;
+            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, mo2), x0, x1);
+            const float p0 = fast_exp2(x0);
+            const float p1 = (POLY == 2 || (POLY == 1 && (i & 1))) ? exp2_fma(x1) : fast_exp2(x1);
+            l2 = ptx::add_f32x2(l2, ptx::pack_f32x2(p0, p1));
+            const __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+            pk[i] = *reinterpret_cast<const uint32_t*>(&hh);
+            if (DROP) pk[i] &= attn_drop_pair_mask(dw0 << (i >> 1), i & 1);
+            if (i & 1) { a2 = fmaxf(a2, __uint_as_float(s[2 * i])); a3 = fmaxf(a3, __uint_as_float(s[2 * i + 1])); }
+            else { a0 = fmaxf(a0, __uint_as_float(s[2 * i])); a1 = fmaxf(a1, __uint_as_float(s[2 * i + 1])); }
+          }
+          const float m_new = fmaxf(m, fmaxf(fmaxf(a0, a1), fmaxf(a2, a3)));
+          const float growth = (m_new - m) * scale_log2;
+          if (!__any_sync(0xffffffffu, growth > 60.0f)) {     // (else: fall through to the block computed under its own maximum)
+            ptx::tmem_st_32x16(tmem_s, pk);
+            float l0, l1;
+            ptx::unpack_f32x2(l2, l0, l1);
+            l += l0 + l1;
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(&p_full[j % NBUF]);
+            if (__any_sync(0xffffffffu, growth > RESCALE_LOG2)) {   // advance the reference for the blocks to come
+              const float corr = fast_exp2((m - m_new) * scale_log2);
+              l *= corr;
+              // O holds P_j V_j: o_step completes one phase per PV and is only looked at here, so a parity wait is only safe one
+              // phase ahead of what is KNOWN to have completed - s_full(j) implies PV_(j-2); step through PV_(j-1), then PV_j
+              ptx::mbar_wait(o_step, (j - 1) & 1);
+              ptx::mbar_wait(o_step, j & 1);
+              ptx::tc_fence_after();
+#pragma unroll 1
+              for (int c = 0; c < DH / 16; ++c) {
+                uint32_t o[16];
+                ptx::tmem_ld_32x16(tmem_o + c * 16, o);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * corr);
+                ptx::tmem_st_32x16(tmem_o + c * 16, o);
+              }
+              ptx::tmem_st_wait();
+              ptx::tc_fence_before();
+              m = m_new;
+            }
+            continue;
+          }
+        }
+      }
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
       for (int hf = 0; hf < SB / NS; ++hf) {        // (one trip unless TWOPASS)
@@ -465,17 +532,17 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ C
   }
 }
 
-template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2, int SB = 64, int QT = 0, int PIPE = 0>
+template <int DH, bool DROP, int POLY, int NBUF = 2, int CTAS = 2, int SB = 64, int QT = 0, int PIPE = 0, int SPEC = 0>
 static int launch_fwd(dim3 grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                       cudaStream_t st) {
   static bool attr_set = false;
   constexpr size_t SMEM = Cfg<NBUF, CTAS, SB, QT>::SMEM;
   if (!attr_set) {
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE, SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    ACAI_CUDA(cudaFuncSetAttribute(attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE, SPEC>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     attr_set = true;
   }
-  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE><<<grid, Cfg<NBUF, CTAS, SB, QT>::THREADS, SMEM, st>>>(tq, tk, tv, p);
+  attn_fwd_tc<DH, DROP, POLY, NBUF, CTAS, SB, QT, PIPE, SPEC><<<grid, Cfg<NBUF, CTAS, SB, QT>::THREADS, SMEM, st>>>(tq, tk, tv, p);
   return ACAI_OK;
 }
 
@@ -508,8 +575,15 @@ int attn_varlen_tc(const void* q, const void* k, const void* v, int dtype, int64
   AttnParams p{cu_q, cu_k, out, out_dt, os, causal, scale * 1.4426950408889634f, lse, (int)total_q,
                static_cast<const __nv_bfloat16*>(q), qs, drop};
   dim3 grid((max_q + BQ - 1) / BQ, heads, batch);
+  // speculative reference maximum (SPEC, see the kernel).  Measured (kernel_bench, two pairs in one box, gpurun_out/r2h_e.log):
+  // encoder layer 339.5 / 338.2 -> 333.3 / 333.0 us, causal decoder 163.3 -> 162.2 us; with dropout 448.9 -> 456.3 us and for
+  // head_dim 32 123.6 -> 124.7 us - so it is the default for head_dim 64 without dropout only.  ACAI_ATTN_SPEC = 0 / 1 forces it
+  // off / on everywhere (A/B runs, read per call).
+  const int spec_env = [] { const char* e = getenv("ACAI_ATTN_SPEC"); return e ? (atoi(e) != 0 ? 1 : 0) : -1; }();   // (per call: tests toggle it)
+  const bool spec = spec_env >= 0 ? spec_env != 0 : (head_dim == 64 && drop.thr == 0);
 #define ACAI_FWD32(DH_, DROP_)                                                                                    \
-  (poly == 0 ? launch_fwd<DH_, DROP_, 0, 2, 4, 32>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1, 2, 4, 32>(grid, tq, tk, tv, p, st) \
+  (poly == 0 && spec ? launch_fwd<DH_, DROP_, 0, 2, 4, 32, 0, 0, 1>(grid, tq, tk, tv, p, st) :                    \
+   poly == 0 ? launch_fwd<DH_, DROP_, 0, 2, 4, 32>(grid, tq, tk, tv, p, st) : poly == 1 ? launch_fwd<DH_, DROP_, 1, 2, 4, 32>(grid, tq, tk, tv, p, st) \
                                                                                         : launch_fwd<DH_, DROP_, 2, 2, 4, 32>(grid, tq, tk, tv, p, st))
   // software-pipelined softmax (PIPE, see the kernel), for A/B runs: ACAI_ATTN_PIPE = 1 three CTAs per SM / 2 four CTAs per SM.  Measured
   // on one box, encoder shape: 337.0 us off, 335.0 us with 2 (three runs each), 355 us with 1; with dropout the extra live registers

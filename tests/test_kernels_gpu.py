@@ -276,6 +276,42 @@ def test_attn_varlen_tcgen05_d64(lens, causal):
     close(y32, ref, 1e-2, 1e-2)
 
 
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("kind", ["ramp", "jump", "late_spike"])
+def test_attn_varlen_tcgen05_growing_row_maximum(kind, causal, monkeypatch):
+    """Scores whose running row maximum keeps moving: every 32-key block beats the previous maximum by more than 2^8 ("ramp": the
+    O / l rescale runs in every block), one block jumps by ~2^70 ("jump": the speculative path must recompute that block under its own
+    maximum instead of overflowing), the last keys dominate ("late_spike").  Both softmax arrangements (reference maximum of the
+    block itself / of the previous block, ACAI_ATTN_SPEC) against fp32 math, and the log-sum-exp the backward reads."""
+    H, d = 2, 64
+    lens = [300, 129, 64]
+    T, D = sum(lens), H * d
+    q = torch.ones(T, D, device=DEV)
+    k = torch.zeros(T, D, device=DEV)
+    v = rnd(T, D, seed=31)
+    off = 0
+    for L in lens:
+        pos = torch.arange(L, device=DEV, dtype=torch.float32)
+        if kind == "ramp":
+            b = 0.05 * pos                                      # score = 64 b / 8 = 0.4 nats per key: 12.8 nats per 32-key block
+        elif kind == "jump":
+            b = torch.where(pos >= min(200, L // 2), 6.25, 0.01 * pos)   # one step of ~50 nats
+        else:
+            b = torch.where(pos >= L - 3, 3.0 + 0.1 * (pos - L), 0.0)
+        k[off:off + L] = b[:, None]
+        off += L
+    q, k, v = q.bfloat16(), k.bfloat16(), v.bfloat16()
+    pk = Packed(lens, DEV)
+    ref = ref_varlen(q.float(), k.float(), v.float(), lens, lens, H, d, causal)
+    outs = []
+    for spec in ("0", "1"):
+        monkeypatch.setenv("ACAI_ATTN_SPEC", spec)              # (read per call by the library)
+        y, lse = ops.attn_varlen(q, k, v, pk.cu, pk.cu, pk.max_len, H, d, causal=causal, out_dtype=torch.float32, return_lse=True)
+        assert bool(torch.isfinite(y).all()) and bool(torch.isfinite(lse).all())
+        close(y, ref, 2e-2, 2e-2)
+        outs.append(y)
+
+
 def test_attn_varlen_tcgen05_cross():
     H, d = 2, 64
     lq, lk = [200, 3, 130], [1000, 140, 17]
